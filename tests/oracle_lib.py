@@ -1,0 +1,226 @@
+"""ctypes bindings for the CPU checkers under oracle/ (test infrastructure only).
+
+`Oracle`  -> oracle/liborb_oracle.so          (our restatement, built by oracle/Makefile)
+`RefExtractor` -> oracle/_ref/libref_orbextractor.so (the unmodified reference ORBextractor.cc on the cv shim)
+"""
+import ctypes as C
+import os
+import subprocess
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE_SO = os.path.join(ROOT, "oracle", "liborb_oracle.so")
+REF_SO = os.path.join(ROOT, "oracle", "_ref", "libref_orbextractor.so")
+
+KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"), ("response", "<f4"),
+                     ("octave", "<i4"), ("class_id", "<i4")])
+assert KP_DTYPE.itemsize == 28
+
+TUM1 = dict(nfeatures=1000, scaleFactor=1.2, nlevels=8, iniThFAST=20, minThFAST=7, patchSize=31, halfPatchSize=15,
+            edgeThreshold=19)
+
+_u8p = C.POINTER(C.c_uint8)
+
+
+def _p(a, t=C.c_void_p):
+    return a.ctypes.data_as(t)
+
+
+def build_oracle():
+    if not os.path.exists(ORACLE_SO) or (os.path.isdir("/root/reference") and not os.path.exists(REF_SO)):
+        subprocess.check_call(["make", "-C", os.path.join(ROOT, "oracle")], stdout=subprocess.DEVNULL)
+
+
+def _load(path):
+    lib = C.CDLL(path)
+    return lib
+
+
+class _ExtractorBase:
+    prefix = None
+
+    def __init__(self, lib, **kw):
+        p = dict(TUM1); p.update(kw)
+        self.params = p
+        self.lib = lib
+        f = getattr(lib, self.prefix + "_create"); f.restype = C.c_void_p
+        f.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]
+        self.h = C.c_void_p(f(p["nfeatures"], p["scaleFactor"], p["nlevels"], p["iniThFAST"], p["minThFAST"],
+                              p["patchSize"], p["halfPatchSize"], p["edgeThreshold"]))
+        self._fn("destroy").argtypes = [C.c_void_p]
+        e = self._fn("extract"); e.restype = C.c_int
+        e.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_size_t, C.c_void_p, C.c_void_p, C.c_int]
+        self._fn("level_size").argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+        self._fn("level_copy").argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int]
+        self._fn("tables").argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+
+    def _fn(self, name):
+        return getattr(self.lib, self.prefix + "_" + name)
+
+    def __del__(self):
+        try:
+            self._fn("destroy")(self.h)
+        except Exception:
+            pass
+
+    def extract(self, img, cap=None):
+        img = np.ascontiguousarray(img, np.uint8)
+        h, w = img.shape
+        cap = cap or (self.params["nfeatures"] * 2 + 64)
+        kps = np.zeros(cap, KP_DTYPE); desc = np.zeros((cap, 32), np.uint8)
+        n = self._fn("extract")(self.h, _p(img), w, h, w, _p(kps), _p(desc), cap)
+        assert n >= 0, "capacity too small"
+        return kps[:n].copy(), desc[:n].copy()
+
+    def level_size(self, l):
+        w = C.c_int(); h = C.c_int()
+        self._fn("level_size")(self.h, l, C.byref(w), C.byref(h))
+        return w.value, h.value
+
+    def level(self, l, with_border=False):
+        w, h = self.level_size(l)
+        e = self.params["edgeThreshold"] if with_border else 0
+        out = np.zeros((h + 2 * e, w + 2 * e), np.uint8)
+        self._fn("level_copy")(self.h, l, _p(out), int(with_border))
+        return out
+
+    def tables(self):
+        n = self.params["nlevels"]
+        t = np.zeros(4 * n, np.float32); pl = np.zeros(n, np.int32); um = np.zeros(self.params["halfPatchSize"] + 1, np.int32)
+        self._fn("tables")(self.h, _p(t), _p(pl), _p(um))
+        return t.reshape(4, n), pl, um
+
+
+class Oracle(_ExtractorBase):
+    prefix = "orc"
+
+    def __init__(self, **kw):
+        build_oracle()
+        lib = _load(ORACLE_SO)
+        super().__init__(lib, **kw)
+        lib.orc_cand_count.argtypes = [C.c_void_p, C.c_int]
+        lib.orc_cand_copy.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+        lib.orc_sel_count.argtypes = [C.c_void_p, C.c_int]
+        lib.orc_blur_copy.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+        lib.orc_set_tiebreak.argtypes = [C.c_void_p, C.c_int]
+
+    def candidates(self, l):
+        n = self.lib.orc_cand_count(self.h, l)
+        out = np.zeros((n, 3), np.int32)
+        if n:
+            self.lib.orc_cand_copy(self.h, l, _p(out))
+        return out
+
+    def blurred(self, l):
+        w, h = self.level_size(l)
+        out = np.zeros((h, w), np.uint8)
+        self.lib.orc_blur_copy(self.h, l, _p(out))
+        return out
+
+    def set_tiebreak(self, m):
+        self.lib.orc_set_tiebreak(self.h, m)
+
+
+class RefExtractor(_ExtractorBase):
+    prefix = "ref"
+
+    def __init__(self, **kw):
+        build_oracle()
+        super().__init__(_load(REF_SO), **kw)
+
+
+def have_ref():
+    build_oracle()
+    return os.path.exists(REF_SO)
+
+
+class OraclePrims:
+    """Stand-alone primitives + matcher loops of the oracle."""
+
+    def __init__(self):
+        build_oracle()
+        self.lib = L = _load(ORACLE_SO)
+        L.orc_resize.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int]
+        L.orc_border.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int]
+        L.orc_blur.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+        L.orc_fast.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int]
+        L.orc_fast_atan2.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+        L.orc_hamming.argtypes = [C.c_void_p, C.c_void_p]
+        for f in (L.orc_knn2, L.orc_knn2_popcnt):
+            f.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.orc_window_search.argtypes = [C.c_void_p, C.c_int] + [C.c_void_p] * 8
+        L.orc_stereo_match.restype = C.c_int
+        L.orc_stereo_match.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p,
+                                       C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int,
+                                       C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_float,
+                                       C.c_void_p, C.c_void_p, C.c_void_p]
+
+    def resize(self, src, dw, dh):
+        src = np.ascontiguousarray(src, np.uint8); out = np.zeros((dh, dw), np.uint8)
+        self.lib.orc_resize(_p(src), src.shape[1], src.shape[0], _p(out), dw, dh)
+        return out
+
+    def border(self, src, e):
+        src = np.ascontiguousarray(src, np.uint8)
+        out = np.zeros((src.shape[0] + 2 * e, src.shape[1] + 2 * e), np.uint8)
+        self.lib.orc_border(_p(src), src.shape[1], src.shape[0], _p(out), e)
+        return out
+
+    def blur(self, src):
+        src = np.ascontiguousarray(src, np.uint8); out = np.zeros_like(src)
+        self.lib.orc_blur(_p(src), src.shape[1], src.shape[0], _p(out))
+        return out
+
+    def fast(self, img, th):
+        img = np.ascontiguousarray(img, np.uint8)
+        cap = img.size // 4 + 16
+        out = np.zeros((cap, 3), np.int32)
+        n = self.lib.orc_fast(_p(img), img.shape[1], img.shape[0], th, _p(out), cap)
+        return out[:n].copy()
+
+    def fast_atan2(self, y, x):
+        y = np.ascontiguousarray(y, np.float32); x = np.ascontiguousarray(x, np.float32)
+        out = np.zeros_like(y)
+        self.lib.orc_fast_atan2(_p(y), _p(x), _p(out), y.size)
+        return out
+
+    def hamming(self, a, b):
+        a = np.ascontiguousarray(a, np.uint8); b = np.ascontiguousarray(b, np.uint8)
+        return self.lib.orc_hamming(_p(a), _p(b))
+
+    def knn2(self, q, t, popcnt=False):
+        q = np.ascontiguousarray(q, np.uint8); t = np.ascontiguousarray(t, np.uint8)
+        i1 = np.zeros(len(q), np.int32); d1 = np.zeros(len(q), np.uint16); d2 = np.zeros(len(q), np.uint16)
+        (self.lib.orc_knn2_popcnt if popcnt else self.lib.orc_knn2)(_p(q), len(q), _p(t), len(t), _p(i1), _p(d1), _p(d2))
+        return i1, d1, d2
+
+    def window_search(self, q, off, idx, skip, t):
+        q = np.ascontiguousarray(q, np.uint8); t = np.ascontiguousarray(t, np.uint8)
+        off = np.ascontiguousarray(off, np.int32); idx = np.ascontiguousarray(idx, np.int32)
+        nq = len(q)
+        bi = np.zeros(nq, np.int32); bd = np.zeros(nq, np.uint16); sd = np.zeros(nq, np.uint16); si = np.zeros(nq, np.int32)
+        sk = None if skip is None else np.ascontiguousarray(skip, np.uint8)
+        self.lib.orc_window_search(_p(q), nq, _p(off), _p(idx), None if sk is None else _p(sk), _p(t),
+                                   _p(bi), _p(bd), _p(sd), _p(si))
+        return bi, bd, sd, si
+
+    def stereo_match(self, kL, dL, kR, dR, pyrL, pyrR, scale, inv_scale, mbf, minD, maxD):
+        """pyrL/pyrR: lists of contiguous 2-D uint8 level interiors (un-blurred)."""
+        nl = len(pyrL)
+        PL = (C.c_void_p * nl)(*[p.ctypes.data for p in pyrL]); PR = (C.c_void_p * nl)(*[p.ctypes.data for p in pyrR])
+        lw = np.array([p.shape[1] for p in pyrL], np.int32); lh = np.array([p.shape[0] for p in pyrL], np.int32)
+        pl = np.array([p.strides[0] for p in pyrL], np.int32); pr = np.array([p.strides[0] for p in pyrR], np.int32)
+        sc = np.ascontiguousarray(scale, np.float32); isc = np.ascontiguousarray(inv_scale, np.float32)
+        NL = len(kL)
+        ur = np.zeros(NL, np.float32); dp = np.zeros(NL, np.float32); sad = np.zeros(NL, np.int32)
+        kL = np.ascontiguousarray(kL); kR = np.ascontiguousarray(kR)
+        dL = np.ascontiguousarray(dL, np.uint8); dR = np.ascontiguousarray(dR, np.uint8)
+        n = self.lib.orc_stereo_match(_p(kL), NL, _p(dL), _p(kR), len(kR), _p(dR), PL, PR, _p(lw), _p(lh), _p(pl), _p(pr),
+                                      nl, _p(sc), _p(isc), mbf, minD, maxD, _p(ur), _p(dp), _p(sad))
+        return ur, dp, sad, n
+
+
+def canonical(kps, desc):
+    """Sort (level, y, x) — the order-free comparison key of SURVEY.md §7 H8."""
+    order = np.lexsort((kps["x"], kps["y"], kps["octave"]))
+    return kps[order], desc[order]
