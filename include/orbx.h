@@ -1,0 +1,144 @@
+/* orbx.h — C ABI of the B200-native ORB front end (liborbx.so).
+ *
+ * This is the drop-in boundary for ONE hot path of fabrizioromanelli/ORBSLAM2: ORB extraction and 256-bit Hamming
+ * matching. The reference has no FFI layer for this path; the boundary it exposes is the C++ class API
+ *   ORB_SLAM2::ORBextractor   /root/reference/include/ORBextractor.h:45-112, src/ORBextractor.cc:405-947
+ *   ORB_SLAM2::ORBmatcher     /root/reference/include/ORBmatcher.h:38-102,   src/ORBmatcher.cc:1643-1659 + search loops
+ *   Frame::ComputeStereoMatches /root/reference/include/Frame.h:92,          src/Frame.cc:464-642
+ * Each entry point below names the reference interface it replaces. include/ORBextractor.h and include/ORBmatcher.h
+ * (this repo) are the C++ wrappers with the reference's own signatures on top of this ABI; orbslam2_b200/ is the
+ * Python mirror (ctypes). All functions return an ORBX_* status (0 = OK), never throw, never abort.
+ * All kernels are hand-written CUDA for sm_100a; there is NO CPU fallback: without a CUDA device orbx_create and
+ * orbm_create fail with ORBX_ECUDA.
+ */
+#ifndef ORBX_H
+#define ORBX_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ORBX_MAX_LEVELS 16
+
+enum {
+    ORBX_OK = 0,
+    ORBX_EINVAL = 1, /* bad argument */
+    ORBX_ESHAPE = 2, /* image shape unsupported (a pyramid level too small for one 30-px cell, w < h/2, ...) */
+    ORBX_ECAP = 3,   /* caller's capacity too small; *n holds the required value */
+    ORBX_ECUDA = 4,  /* CUDA runtime error or no device; see orbx_last_error_string() */
+    ORBX_ESTATE = 5  /* call order (e.g. pyramid requested before any extract) */
+};
+
+enum { ORBX_MEM_HOST = 0, ORBX_MEM_DEVICE = 1 };
+
+/* The eight constructor arguments of ORB_SLAM2::ORBextractor (include/ORBextractor.h:51, src/ORBextractor.cc:405-407). */
+typedef struct {
+    int nfeatures;
+    float scaleFactor;
+    int nlevels;
+    int iniThFAST;
+    int minThFAST;
+    int patchSize;     /* 31 */
+    int halfPatchSize; /* 15 */
+    int edgeThreshold; /* 19 */
+} orbx_params;
+
+/* Layout-identical to cv::KeyPoint (28 bytes) so a wrapper can memcpy into std::vector<cv::KeyPoint>. */
+typedef struct {
+    float x, y;     /* pt, level-0 coordinates */
+    float size;     /* (int)(patchSize * scale[octave]) */
+    float angle;    /* degrees [0,360) */
+    float response; /* FAST score */
+    int octave;
+    int class_id;   /* -1 */
+} orbx_kp;
+
+typedef struct orbx_handle orbx_t;
+typedef struct orbm_handle orbm_t;
+
+/* ---- extractor: replaces ORBextractor::ORBextractor / ~ORBextractor (src/ORBextractor.cc:405-464) ------------------ */
+int orbx_create(const orbx_params* p, int device, orbx_t** out);
+int orbx_destroy(orbx_t* h);
+/* Where the caller's image / result pointers live (default: host for both). Device pointers must be on `device`. */
+int orbx_set_memory_space(orbx_t* h, int input_space, int output_space);
+
+/* Replaces ORBextractor::operator() (src/ORBextractor.cc:858-919) for one 8-bit grey image. Keypoints come out
+ * level-major and, inside a level, in canonical (y, x) order; desc is n x 32 bytes. */
+int orbx_extract(orbx_t* h, const uint8_t* img, int w, int hgt, size_t stride, orbx_kp* kps, uint8_t* desc, int cap,
+                 int* n);
+/* Same for `batch` equally-shaped frames: frame f starts at imgs + f*img_stride; its results go to
+ * kps + f*cap_per_frame, desc + f*cap_per_frame*32, n[f]. */
+int orbx_extract_batch(orbx_t* h, const uint8_t* imgs, int batch, int w, int hgt, size_t stride, size_t img_stride,
+                       orbx_kp* kps, uint8_t* desc, int cap_per_frame, int* n);
+/* Smallest cap_per_frame that can never return ORBX_ECAP for this shape (sum over levels of quota + slack). */
+int orbx_max_keypoints(orbx_t* h, int w, int hgt, int* cap);
+
+/* Replaces the getters GetLevels / GetScaleFactors / GetInverseScaleFactors / GetScaleSigmaSquares /
+ * GetInverseScaleSigmaSquares (include/ORBextractor.h:62-82) and exposes mnFeaturesPerLevel / umax
+ * (src/ORBextractor.cc:411-463). Any output pointer may be NULL. */
+int orbx_level_count(orbx_t* h);
+int orbx_tables(orbx_t* h, float* scale, float* inv_scale, float* sigma2, float* inv_sigma2, int* features_per_level,
+                int* umax /* halfPatchSize+1 */);
+
+/* Replaces reads of the public member mvImagePyramid (include/ORBextractor.h:84; src/ORBextractor.cc:921-946) after the
+ * last extract call: level size and pixels of frame `frame`; with_border adds the edgeThreshold-px BORDER_REFLECT_101
+ * frame, i.e. the full padded buffer the reference's ROI lives in. dst is always a HOST pointer. */
+int orbx_level_size(orbx_t* h, int level, int* w, int* hgt);
+int orbx_pyramid_level(orbx_t* h, int frame, int level, uint8_t* dst, size_t dst_stride, int with_border);
+
+/* Parity/debug taps (host outputs): the 7x7 sigma-2 blurred level (src/ORBextractor.cc:899-900) and the per-cell FAST
+ * candidates handed to DistributeOctTree (src/ORBextractor.cc:783-823) as (x, y, score) int triples in level pixel
+ * coordinates, unordered. */
+int orbx_blurred_level(orbx_t* h, int frame, int level, uint8_t* dst, size_t dst_stride);
+int orbx_candidates(orbx_t* h, int frame, int level, int32_t* xys, int cap, int* n);
+
+/* ---- stereo: replaces Frame::ComputeStereoMatches (src/Frame.cc:464-642) ------------------------------------------
+ * `left` and `right` must have just extracted the left and right images (same shape, same batch); works on frame
+ * `frame` of each, entirely on the device (keypoints, descriptors and un-blurred pyramids are still resident).
+ * minD/maxD are explicit (the reference derives maxD = mbf/mb; src/Frame.cc:498-500). uRight/depth: N_left floats
+ * (-1 = no match), in the memory space selected for `left`'s outputs. */
+int orbx_stereo_match(orbx_t* left, orbx_t* right, int frame, float mbf, float minD, float maxD, float* uRight,
+                      float* depth);
+/* All frames of the last batch; uRight/depth are batch x cap_per_frame. */
+int orbx_stereo_match_batch(orbx_t* left, orbx_t* right, float mbf, float minD, float maxD, float* uRight,
+                            float* depth, int cap_per_frame);
+
+/* ---- matcher: replaces ORBmatcher::DescriptorDistance (src/ORBmatcher.cc:1643-1659) and the candidate-scan inner
+ * loop shared by every ORBmatcher search (best / second-best with strict '<') -------------------- */
+int orbm_create(int device, orbm_t** out);
+int orbm_destroy(orbm_t* m);
+int orbm_set_memory_space(orbm_t* m, int input_space, int output_space);
+/* Upload (or adopt, for device memory) a train descriptor matrix nt x 32 that later calls reuse. */
+int orbm_set_train(orbm_t* m, const uint8_t* t, int nt);
+/* Brute-force 2-NN of every query against the train set: i1 = index of the best (lowest index wins ties),
+ * d1 = its distance, d2 = second-smallest distance with multiplicity (256 if nt < 2). t == NULL reuses set_train. */
+int orbm_knn2(orbm_t* m, const uint8_t* q, int nq, const uint8_t* t, int nt, int32_t* i1, uint16_t* d1, uint16_t* d2);
+/* Windowed search: query a scans candidates cand_idx[cand_off[a] .. cand_off[a+1]) in list order, skipping entries
+ * with cand_skip[c] != 0 (cand_skip may be NULL). Outputs best/second index (-1 = none) and distance (256 = none). */
+int orbm_window_search(orbm_t* m, const uint8_t* q, int nq, const int32_t* cand_off, const int32_t* cand_idx,
+                       const uint8_t* cand_skip, const uint8_t* t, int nt, int32_t* best_idx, uint16_t* best_d,
+                       uint16_t* second_d, int32_t* second_idx);
+/* Batched DescriptorDistance: d[i] = hamming(a[i], b[i]). */
+int orbm_distance(orbm_t* m, const uint8_t* a, const uint8_t* b, int n, uint16_t* d);
+
+/* ---- instrumentation ---------------------------------------------------------------------------------------------- */
+/* CUDA stream (cudaStream_t) the handle launches on — for timing with events on the launching stream. */
+int orbx_stream(orbx_t* h, void** stream);
+int orbm_stream(orbm_t* m, void** stream);
+/* Kernels launched by this handle since creation. */
+int64_t orbx_launch_count(orbx_t* h);
+int64_t orbm_launch_count(orbm_t* m);
+/* Device milliseconds spent per stage during the last extract call (CUDA events on the handle's stream):
+ * [0] H2D/ingest, [1] pyramid, [2] FAST, [3] quadtree, [4] blur, [5] orient+descriptor, [6] D2H. */
+int orbx_stage_ms(orbx_t* h, float* ms7);
+int orbx_set_profiling(orbx_t* h, int on);
+const char* orbx_last_error_string(void);
+const char* orbx_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ORBX_H */

@@ -1,0 +1,79 @@
+"""ctypes loader for liborbx.so — the C-ABI CUDA library declared in include/orbx.h. No fallback of any kind:
+if the library is missing it is built with nvcc; if that fails, or no CUDA device exists, calls raise."""
+import ctypes as C
+import os
+
+from . import build as _build
+
+_LIB = None
+
+ORBX_OK, ORBX_EINVAL, ORBX_ESHAPE, ORBX_ECAP, ORBX_ECUDA, ORBX_ESTATE = range(6)
+MEM_HOST, MEM_DEVICE = 0, 1
+_NAMES = {1: "ORBX_EINVAL", 2: "ORBX_ESHAPE", 3: "ORBX_ECAP", 4: "ORBX_ECUDA", 5: "ORBX_ESTATE"}
+
+
+class OrbxError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"{_NAMES.get(code, code)}: {msg}")
+        self.code = code
+
+
+class OrbxParams(C.Structure):
+    _fields_ = [("nfeatures", C.c_int), ("scaleFactor", C.c_float), ("nlevels", C.c_int), ("iniThFAST", C.c_int),
+                ("minThFAST", C.c_int), ("patchSize", C.c_int), ("halfPatchSize", C.c_int), ("edgeThreshold", C.c_int)]
+
+
+# every symbol include/orbx.h declares (tests check the export table against this list and the header)
+SYMBOLS = ["orbx_create", "orbx_destroy", "orbx_set_memory_space", "orbx_extract", "orbx_extract_batch",
+           "orbx_max_keypoints", "orbx_level_count", "orbx_tables", "orbx_level_size", "orbx_pyramid_level",
+           "orbx_blurred_level", "orbx_candidates", "orbx_stereo_match", "orbx_stereo_match_batch", "orbm_create",
+           "orbm_destroy", "orbm_set_memory_space", "orbm_set_train", "orbm_knn2", "orbm_window_search", "orbm_distance",
+           "orbx_stream", "orbm_stream", "orbx_launch_count", "orbm_launch_count", "orbx_stage_ms", "orbx_set_profiling",
+           "orbx_last_error_string", "orbx_version"]
+
+
+def lib():
+    global _LIB
+    if _LIB is not None:
+        return _LIB
+    path = _build.LIB
+    if not os.path.exists(path):
+        _build.build()
+    L = C.CDLL(path)
+    vp, ci, cf, sz = C.c_void_p, C.c_int, C.c_float, C.c_size_t
+    L.orbx_create.argtypes = [C.POINTER(OrbxParams), ci, C.POINTER(vp)]
+    L.orbx_destroy.argtypes = [vp]
+    L.orbx_set_memory_space.argtypes = [vp, ci, ci]
+    L.orbx_extract.argtypes = [vp, vp, ci, ci, sz, vp, vp, ci, vp]
+    L.orbx_extract_batch.argtypes = [vp, vp, ci, ci, ci, sz, sz, vp, vp, ci, vp]
+    L.orbx_max_keypoints.argtypes = [vp, ci, ci, C.POINTER(ci)]
+    L.orbx_level_count.argtypes = [vp]
+    L.orbx_tables.argtypes = [vp] + [vp] * 6
+    L.orbx_level_size.argtypes = [vp, ci, C.POINTER(ci), C.POINTER(ci)]
+    L.orbx_pyramid_level.argtypes = [vp, ci, ci, vp, sz, ci]
+    L.orbx_blurred_level.argtypes = [vp, ci, ci, vp, sz]
+    L.orbx_candidates.argtypes = [vp, ci, ci, vp, ci, C.POINTER(ci)]
+    L.orbx_stereo_match.argtypes = [vp, vp, ci, cf, cf, cf, vp, vp]
+    L.orbx_stereo_match_batch.argtypes = [vp, vp, cf, cf, cf, vp, vp, ci]
+    L.orbm_create.argtypes = [ci, C.POINTER(vp)]
+    L.orbm_destroy.argtypes = [vp]
+    L.orbm_set_memory_space.argtypes = [vp, ci, ci]
+    L.orbm_set_train.argtypes = [vp, vp, ci]
+    L.orbm_knn2.argtypes = [vp, vp, ci, vp, ci, vp, vp, vp]
+    L.orbm_window_search.argtypes = [vp, vp, ci, vp, vp, vp, vp, ci, vp, vp, vp, vp]
+    L.orbm_distance.argtypes = [vp, vp, vp, ci, vp]
+    L.orbx_stream.argtypes = [vp, C.POINTER(vp)]
+    L.orbm_stream.argtypes = [vp, C.POINTER(vp)]
+    L.orbx_launch_count.argtypes = [vp]; L.orbx_launch_count.restype = C.c_int64
+    L.orbm_launch_count.argtypes = [vp]; L.orbm_launch_count.restype = C.c_int64
+    L.orbx_stage_ms.argtypes = [vp, vp]
+    L.orbx_set_profiling.argtypes = [vp, ci]
+    L.orbx_last_error_string.restype = C.c_char_p
+    L.orbx_version.restype = C.c_char_p
+    _LIB = L
+    return L
+
+
+def check(rc):
+    if rc != ORBX_OK:
+        raise OrbxError(rc, lib().orbx_last_error_string().decode())

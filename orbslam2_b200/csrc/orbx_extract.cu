@@ -1,0 +1,551 @@
+// orbx_extract.cu — host side of the extractor half of the C ABI (include/orbx.h): plan construction (level
+// geometry, bilinear tables, TMA tensor maps, device arenas), the launch sequence and the result copies.
+// Mirrors ORB_SLAM2::ORBextractor (/root/reference/src/ORBextractor.cc:405-464 ctor tables, :858-919 operator()).
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <mutex>
+#include <vector>
+
+#include "orbx_kernels.cuh"
+
+// ------------------------------------------------------------------------------------------------ errors
+static thread_local char g_err[512] = "";
+void orbx_set_err(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+extern "C" const char* orbx_last_error_string(void) { return g_err; }
+extern "C" const char* orbx_version(void) { return "orbx 0.1 (sm_100a)"; }
+
+// ------------------------------------------------------------------------------------------------ handle
+struct orbx_handle {
+    orbx_params prm;
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    int inSpace = ORBX_MEM_HOST, outSpace = ORBX_MEM_HOST;
+    // reference ctor tables
+    std::vector<float> sf, isf, sig2, isig2;
+    std::vector<int> perLevel, umax;
+    // plan
+    int planW = 0, planH = 0, planBatch = 0;
+    DevPlan hp;             // host copy
+    DevPlan* dPlan = nullptr;
+    TmapPack maps;
+    uint8_t* dPyr = nullptr;
+    uint8_t* dBlur = nullptr;
+    size_t pyrBytes = 0;
+    int2* dTabs = nullptr;
+    u64* dCand = nullptr;
+    int* dNodeOf = nullptr;
+    int* dCandCount = nullptr;
+    uint2* dSel = nullptr;
+    int* dSelCount = nullptr;
+    orbx_kp* dKps = nullptr;
+    uint8_t* dDesc = nullptr;
+    int* dNOut = nullptr;
+    int* dErr = nullptr;
+    uint8_t* dExport = nullptr;
+    size_t exportBytes = 0;
+    int* hCounts = nullptr;  // pinned: [batch] nOut + [1] err
+    int qtC = 0, qtC2 = 0, qtThreads = 256;
+    size_t qtSmem = 0, fastSmem = 0;
+    int lastBatch = 0;
+    bool blurValid = false;
+    int64_t launches = 0;
+    bool profiling = false;
+    cudaEvent_t ev[8] = {};
+    float stageMs[7] = {};
+};
+
+static inline int round_half_even_f(float v) { return (int)lrintf(v); }
+
+// ORBextractor ctor tables, src/ORBextractor.cc:409-463 (same expressions, same types).
+static void init_tables(orbx_handle* h) {
+    const orbx_params& p = h->prm;
+    const int n = p.nlevels;
+    const double scaleFactor = p.scaleFactor;  // the class member is a double initialised from the float argument
+    h->sf.assign(n, 1.0f);
+    h->sig2.assign(n, 1.0f);
+    for (int i = 1; i < n; i++) {
+        h->sf[i] = (float)(h->sf[i - 1] * scaleFactor);
+        h->sig2[i] = h->sf[i] * h->sf[i];
+    }
+    h->isf.resize(n);
+    h->isig2.resize(n);
+    for (int i = 0; i < n; i++) {
+        h->isf[i] = 1.0f / h->sf[i];
+        h->isig2[i] = 1.0f / h->sig2[i];
+    }
+    h->perLevel.resize(n);
+    const float factor = (float)(1.0f / scaleFactor);
+    float nDesired = p.nfeatures * (1 - factor) / (1 - (float)pow((double)factor, (double)n));
+    int sum = 0;
+    for (int l = 0; l < n - 1; l++) {
+        h->perLevel[l] = round_half_even_f(nDesired);
+        sum += h->perLevel[l];
+        nDesired *= factor;
+    }
+    h->perLevel[n - 1] = std::max(p.nfeatures - sum, 0);
+    const int hpz = p.halfPatchSize;
+    h->umax.assign(hpz + 2, 0);
+    const int vmax = (int)floor(hpz * sqrtf(2.f) / 2 + 1);
+    const int vmin = (int)ceil(hpz * sqrtf(2.f) / 2);
+    const double hp2 = (double)hpz * hpz;
+    for (int v = 0; v <= vmax; ++v) h->umax[v] = (int)lrint(sqrt(hp2 - v * v));
+    for (int v = hpz, v0 = 0; v >= vmin; --v) {
+        while (h->umax[v0] == h->umax[v0 + 1]) ++v0;
+        h->umax[v] = v0;
+        ++v0;
+    }
+    h->umax.resize(hpz + 1);
+}
+
+// OpenCV's INTER_LINEAR coefficient tables for one axis (resize.cpp: fx = (float)((d+0.5)*scale-0.5), 11-bit fixed point).
+static void linear_table(int src, int dst, bool clampFrac, std::vector<int2>& out) {
+    const double inv_scale = (double)dst / src;
+    const double scale = 1.0 / inv_scale;
+    for (int d = 0; d < dst; d++) {
+        float f = (float)((d + 0.5) * scale - 0.5);
+        int s = (int)floorf(f);
+        f -= s;
+        if (clampFrac) {
+            if (s < 0) { f = 0; s = 0; }
+            if (s >= src - 1) { f = 0; s = src - 1; }
+        }
+        const int a0 = (short)lrintf((1.f - f) * 2048.f), a1 = (short)lrintf(f * 2048.f);
+        out.push_back(make_int2(s, (a0 & 0xffff) | (a1 << 16)));
+    }
+}
+
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static PFN_encodeTiled get_encode() {
+    static PFN_encodeTiled fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = (PFN_encodeTiled)p;
+    });
+    return fn;
+}
+
+static void free_plan(orbx_handle* h) {
+    cudaFree(h->dPlan); cudaFree(h->dPyr); cudaFree(h->dBlur); cudaFree(h->dTabs); cudaFree(h->dCand);
+    cudaFree(h->dNodeOf); cudaFree(h->dCandCount); cudaFree(h->dSel); cudaFree(h->dSelCount); cudaFree(h->dKps);
+    cudaFree(h->dDesc); cudaFree(h->dNOut); cudaFree(h->dExport);
+    if (h->hCounts) cudaFreeHost(h->hCounts);
+    h->dPlan = nullptr; h->dPyr = h->dBlur = nullptr; h->dTabs = nullptr; h->dCand = nullptr; h->dNodeOf = nullptr;
+    h->dCandCount = nullptr; h->dSel = nullptr; h->dSelCount = nullptr; h->dKps = nullptr; h->dDesc = nullptr;
+    h->dNOut = nullptr; h->dExport = nullptr; h->exportBytes = 0; h->hCounts = nullptr;
+    h->planW = h->planH = h->planBatch = 0;
+}
+
+static int build_plan(orbx_handle* h, int w, int hgt, int batch) {
+    if (h->planW == w && h->planH == hgt && h->planBatch >= batch) return ORBX_OK;
+    // grow the batch capacity geometrically so a caller alternating batch sizes does not rebuild every call
+    if (h->planW == w && h->planH == hgt) batch = std::max(batch, h->planBatch * 2);
+    free_plan(h);
+    const orbx_params& p = h->prm;
+    const int e = p.edgeThreshold;
+    DevPlan& D = h->hp;
+    memset(&D, 0, sizeof(D));
+    D.nlevels = p.nlevels;
+    D.batch = batch;
+    D.iniTh = p.iniThFAST;
+    D.minTh = p.minThFAST;
+    D.halfPatch = p.halfPatchSize;
+    D.edge = e;
+    for (int v = 0; v <= p.halfPatchSize; v++) D.umax[v] = h->umax[v];
+
+    std::vector<int2> tabs;
+    long long pyrOff = 0, candOff = 0;
+    int cellBase = 0, selOff = 0, blurBase = 0, maxSel = 0;
+    size_t fastSmem = 0;
+    for (int l = 0; l < p.nlevels; l++) {
+        LevelGeo& G = D.lv[l];
+        G.w = round_half_even_f((float)w * h->isf[l]);  // src/ORBextractor.cc:925-926
+        G.h = round_half_even_f((float)hgt * h->isf[l]);
+        const int minB = e - 3, maxBX = G.w - e + 3, maxBY = G.h - e + 3;
+        const float width = (float)(maxBX - minB), height = (float)(maxBY - minB);
+        G.nCols = (int)(width / 30.f);
+        G.nRows = (int)(height / 30.f);
+        if (G.nCols < 1 || G.nRows < 1)
+            FAIL(ORBX_ESHAPE, "level %d is %dx%d: smaller than one 30-px FAST cell inside the %d-px border", l, G.w, G.h, e);
+        G.wCell = (int)ceilf(width / G.nCols);
+        G.hCell = (int)ceilf(height / G.nRows);
+        if (G.wCell > 63 || G.hCell > 63 || G.nCols > 1023 || G.nRows > 1023)
+            FAIL(ORBX_ESHAPE, "level %d cell grid %dx%d of %dx%d px exceeds the candidate key layout", l, G.nCols, G.nRows,
+                 G.wCell, G.hCell);
+        G.pitch = (G.w + 63) & ~63;
+        G.frameStride = (long long)G.pitch * G.h;
+        G.pyrOff = pyrOff;
+        pyrOff += ((G.frameStride * batch + 255) / 256) * 256;
+        G.cellBase = cellBase;
+        cellBase += G.nCols * G.nRows;
+        G.boxW = (G.wCell + 6 + 15) & ~15;
+        G.boxH = G.hCell + 6;
+        G.maxSurv = ((G.wCell + 1) / 2) * ((G.hCell + 1) / 2);
+        G.quota = h->perLevel[l];
+        G.treeW = maxBX - minB;
+        G.treeH = maxBY - minB;
+        G.nIni = (int)roundf((float)G.treeW / (float)G.treeH);  // src/ORBextractor.cc:537
+        if (G.nIni < 1) FAIL(ORBX_ESHAPE, "level %d: width/height rounds to 0 initial quadtree nodes (portrait image)", l);
+        G.hX = (float)G.treeW / (float)G.nIni;
+        G.candCap = G.nCols * G.nRows * G.maxSurv;
+        G.candOff = candOff;
+        candOff += (long long)G.candCap * batch;
+        G.selCap = std::max(G.quota + 3, 4 * G.nIni) + 1;
+        G.selOff = selOff;
+        selOff += G.selCap;
+        maxSel = std::max(maxSel, G.selCap);
+        G.scale = h->sf[l];
+        G.sizeField = (float)(int)(p.patchSize * h->sf[l]);  // src/ORBextractor.cc:831
+        G.blurTilesX = (G.w + BLUR_TW - 1) / BLUR_TW;
+        G.blurTilesY = (G.h + BLUR_TH - 1) / BLUR_TH;
+        G.blurTileBase = blurBase;
+        blurBase += G.blurTilesX * G.blurTilesY;
+        if (l > 0) {
+            G.xtabOff = (int)tabs.size();
+            linear_table(D.lv[l - 1].w, G.w, true, tabs);
+            G.ytabOff = (int)tabs.size();
+            linear_table(D.lv[l - 1].h, G.h, false, tabs);
+        }
+        size_t sm = ((size_t)(G.boxW * G.boxH + 127) & ~(size_t)127) + (((G.wCell + 2) * (G.hCell + 2) + 15) & ~15) +
+                    (size_t)G.maxSurv * 8 + 8 + 16;
+        fastSmem = std::max(fastSmem, sm);
+    }
+    D.totalCells = cellBase;
+    D.totalBlurTiles = blurBase;
+    D.selStride = selOff;
+    h->fastSmem = fastSmem;
+    h->qtC = (maxSel + 7) & ~7;
+    if (h->qtC > 4096) FAIL(ORBX_ESHAPE, "per-level keypoint quota %d exceeds the quadtree kernel's node capacity", maxSel);
+    h->qtC2 = 1;
+    while (h->qtC2 < h->qtC) h->qtC2 <<= 1;
+    h->qtSmem = (size_t)8 * h->qtC2 + (size_t)(16 + 8 + 7 * 4 + 32) * h->qtC + 40 * 4 + 64;
+    h->qtThreads = h->qtC > 1024 ? 1024 : (h->qtC > 512 ? 512 : 256);
+    h->pyrBytes = (size_t)pyrOff + 256;
+
+    CK(cudaMalloc(&h->dPlan, sizeof(DevPlan)));
+    CK(cudaMalloc(&h->dPyr, h->pyrBytes));
+    CK(cudaMalloc(&h->dBlur, h->pyrBytes));
+    CK(cudaMalloc(&h->dTabs, std::max<size_t>(tabs.size(), 1) * sizeof(int2)));
+    CK(cudaMalloc(&h->dCand, (size_t)candOff * sizeof(u64)));
+    CK(cudaMalloc(&h->dNodeOf, (size_t)candOff * sizeof(int)));
+    CK(cudaMalloc(&h->dCandCount, (size_t)batch * p.nlevels * sizeof(int)));
+    CK(cudaMalloc(&h->dSelCount, (size_t)batch * p.nlevels * sizeof(int)));
+    CK(cudaMalloc(&h->dSel, (size_t)batch * D.selStride * sizeof(uint2)));
+    CK(cudaMalloc(&h->dKps, (size_t)batch * D.selStride * sizeof(orbx_kp)));
+    CK(cudaMalloc(&h->dDesc, (size_t)batch * D.selStride * 32));
+    CK(cudaMalloc(&h->dNOut, (size_t)batch * sizeof(int)));
+    CK(cudaMallocHost(&h->hCounts, (size_t)(batch + 1) * sizeof(int)));
+    CK(cudaMemcpyAsync(h->dPlan, &D, sizeof(DevPlan), cudaMemcpyHostToDevice, h->stream));
+    if (!tabs.empty())
+        CK(cudaMemcpyAsync(h->dTabs, tabs.data(), tabs.size() * sizeof(int2), cudaMemcpyHostToDevice, h->stream));
+    CK(cudaMemsetAsync(h->dPyr, 0, h->pyrBytes, h->stream));
+    CK(cudaMemsetAsync(h->dBlur, 0, h->pyrBytes, h->stream));
+    CK(cudaStreamSynchronize(h->stream));  // tabs is a local
+
+    // TMA descriptors: one 3-D (x, y, frame) uint8 tensor per level, box = one FAST cell ROI
+    PFN_encodeTiled enc = get_encode();
+    if (!enc) FAIL(ORBX_ECUDA, "cuTensorMapEncodeTiled entry point not available from the driver");
+    for (int l = 0; l < p.nlevels; l++) {
+        const LevelGeo& G = D.lv[l];
+        cuuint64_t gdim[3] = {(cuuint64_t)G.w, (cuuint64_t)G.h, (cuuint64_t)batch};
+        cuuint64_t gstr[2] = {(cuuint64_t)G.pitch, (cuuint64_t)G.frameStride};
+        cuuint32_t box[3] = {(cuuint32_t)G.boxW, (cuuint32_t)G.boxH, 1};
+        cuuint32_t estr[3] = {1, 1, 1};
+        CUresult r = enc(&h->maps.m[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, h->dPyr + G.pyrOff, gdim, gstr, box, estr,
+                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) FAIL(ORBX_ECUDA, "cuTensorMapEncodeTiled failed for level %d (CUresult %d)", l, (int)r);
+    }
+    CK(cudaFuncSetAttribute(k_fast, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->fastSmem));
+    CK(cudaFuncSetAttribute(k_quadtree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->qtSmem));
+    h->planW = w;
+    h->planH = hgt;
+    h->planBatch = batch;
+    h->lastBatch = 0;
+    return ORBX_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ ABI
+extern "C" int orbx_create(const orbx_params* p, int device, orbx_t** out) {
+    if (!p || !out) FAIL(ORBX_EINVAL, "null argument");
+    if (p->nlevels < 1 || p->nlevels > ORBX_MAX_LEVELS) FAIL(ORBX_EINVAL, "nlevels must be in [1,%d]", ORBX_MAX_LEVELS);
+    if (p->nfeatures < 1 || !(p->scaleFactor > 1.0f)) FAIL(ORBX_EINVAL, "nfeatures >= 1 and scaleFactor > 1 required");
+    if (p->minThFAST < 1 || p->iniThFAST < p->minThFAST || p->iniThFAST > 254)
+        FAIL(ORBX_EINVAL, "need 1 <= minThFAST <= iniThFAST <= 254");
+    if (p->halfPatchSize < 1 || p->halfPatchSize > 31 || p->patchSize < 1) FAIL(ORBX_EINVAL, "halfPatchSize in [1,31]");
+    if (p->edgeThreshold < 19 || p->edgeThreshold < p->halfPatchSize + 4)
+        FAIL(ORBX_EINVAL, "edgeThreshold must cover the descriptor reach (>= 19) and the orientation patch");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        FAIL(ORBX_ECUDA, "no CUDA device: liborbx has no CPU path");
+    }
+    if (device < 0 || device >= ndev) FAIL(ORBX_EINVAL, "device %d out of range (%d devices)", device, ndev);
+    CK(cudaSetDevice(device));
+    orbx_handle* h = new orbx_handle();
+    h->prm = *p;
+    h->device = device;
+    init_tables(h);
+    cudaError_t e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
+    if (e != cudaSuccess) {
+        delete h;
+        FAIL(ORBX_ECUDA, "cudaStreamCreate: %s", cudaGetErrorString(e));
+    }
+    for (int i = 0; i < 8; i++) cudaEventCreate(&h->ev[i]);
+    cudaMalloc(&h->dErr, sizeof(int));
+    cudaMemset(h->dErr, 0, sizeof(int));
+    cudaMemcpyToSymbol(c_pattern, kOrbPattern, 1024);
+    *out = h;
+    return ORBX_OK;
+}
+
+extern "C" int orbx_destroy(orbx_t* h) {
+    if (!h) return ORBX_OK;
+    cudaSetDevice(h->device);
+    cudaStreamSynchronize(h->stream);
+    free_plan(h);
+    cudaFree(h->dErr);
+    for (int i = 0; i < 8; i++) cudaEventDestroy(h->ev[i]);
+    cudaStreamDestroy(h->stream);
+    delete h;
+    return ORBX_OK;
+}
+
+extern "C" int orbx_set_memory_space(orbx_t* h, int in, int out) {
+    if (!h || in < 0 || in > 1 || out < 0 || out > 1) FAIL(ORBX_EINVAL, "bad memory space");
+    h->inSpace = in;
+    h->outSpace = out;
+    return ORBX_OK;
+}
+
+extern "C" int orbx_level_count(orbx_t* h) { return h ? h->prm.nlevels : 0; }
+
+extern "C" int orbx_tables(orbx_t* h, float* scale, float* inv_scale, float* sigma2, float* inv_sigma2, int* fpl,
+                           int* umax) {
+    if (!h) FAIL(ORBX_EINVAL, "null handle");
+    const int n = h->prm.nlevels;
+    for (int i = 0; i < n; i++) {
+        if (scale) scale[i] = h->sf[i];
+        if (inv_scale) inv_scale[i] = h->isf[i];
+        if (sigma2) sigma2[i] = h->sig2[i];
+        if (inv_sigma2) inv_sigma2[i] = h->isig2[i];
+        if (fpl) fpl[i] = h->perLevel[i];
+    }
+    if (umax)
+        for (int v = 0; v <= h->prm.halfPatchSize; v++) umax[v] = h->umax[v];
+    return ORBX_OK;
+}
+
+extern "C" int orbx_max_keypoints(orbx_t* h, int w, int hgt, int* cap) {
+    if (!h || !cap) FAIL(ORBX_EINVAL, "null argument");
+    int total = 0;
+    for (int l = 0; l < h->prm.nlevels; l++) {
+        const int lw = round_half_even_f((float)w * h->isf[l]), lh = round_half_even_f((float)hgt * h->isf[l]);
+        const int e = h->prm.edgeThreshold;
+        const int tw = lw - 2 * e + 6, th = lh - 2 * e + 6;
+        if (tw < 30 || th < 30) FAIL(ORBX_ESHAPE, "level %d too small", l);
+        const int nIni = (int)roundf((float)tw / (float)th);
+        total += std::max(h->perLevel[l] + 3, 4 * nIni) + 1;
+    }
+    *cap = total;
+    return ORBX_OK;
+}
+
+static inline void stamp(orbx_handle* h, int i) {
+    if (h->profiling) cudaEventRecord(h->ev[i], h->stream);
+}
+
+extern "C" int orbx_extract_batch(orbx_t* h, const uint8_t* imgs, int batch, int w, int hgt, size_t stride,
+                                  size_t img_stride, orbx_kp* kps, uint8_t* desc, int cap, int* n) {
+    if (!h || !n) FAIL(ORBX_EINVAL, "null argument");
+    if (batch < 1) FAIL(ORBX_EINVAL, "batch must be >= 1");
+    if (!imgs || w <= 0 || hgt <= 0) {  // empty image: the reference returns silently with outputs untouched (:861-862)
+        for (int f = 0; f < batch; f++) n[f] = 0;
+        return ORBX_OK;
+    }
+    if (stride < (size_t)w || (batch > 1 && img_stride < stride * (size_t)hgt)) FAIL(ORBX_EINVAL, "bad strides");
+    if (cap < 0 || (cap > 0 && (!kps || !desc))) FAIL(ORBX_EINVAL, "null output");
+    CK(cudaSetDevice(h->device));
+    int rc = build_plan(h, w, hgt, batch);
+    if (rc != ORBX_OK) return rc;
+    const DevPlan& D = h->hp;
+    cudaStream_t st = h->stream;
+    const int nl = D.nlevels;
+
+    stamp(h, 0);
+    // ingest: level 0 of the pyramid IS the input image (src/ORBextractor.cc:939-943); one strided copy
+    const cudaMemcpyKind kin = h->inSpace == ORBX_MEM_HOST ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToDevice;
+    const LevelGeo& L0 = D.lv[0];
+    if (batch == 1 || img_stride == stride * (size_t)hgt) {
+        CK(cudaMemcpy2DAsync(h->dPyr + L0.pyrOff, L0.pitch, imgs, stride, w, (size_t)hgt * batch, kin, st));
+    } else {
+        for (int f = 0; f < batch; f++)
+            CK(cudaMemcpy2DAsync(h->dPyr + L0.pyrOff + f * L0.frameStride, L0.pitch, imgs + f * img_stride, stride, w, hgt,
+                                 kin, st));
+    }
+    CK(cudaMemsetAsync(h->dCandCount, 0, (size_t)batch * nl * sizeof(int), st));
+    stamp(h, 1);
+    for (int l = 1; l < nl; l++) {
+        const LevelGeo& G = D.lv[l];
+        dim3 grid((G.w + 255) / 256, (G.h + 3) / 4, batch), block(64, 4);
+        k_resize<<<grid, block, 0, st>>>(h->dPlan, l, h->dPyr, h->dTabs);
+        h->launches++;
+    }
+    stamp(h, 2);
+    k_fast<<<dim3(D.totalCells, batch), 256, h->fastSmem, st>>>(h->maps, h->dPlan, h->dCand, h->dCandCount, h->dErr);
+    h->launches++;
+    stamp(h, 3);
+    k_quadtree<<<dim3(nl, batch), h->qtThreads, h->qtSmem, st>>>(h->dPlan, h->dCand, h->dCandCount, h->dNodeOf, h->dSel,
+                                                                  h->dSelCount, h->qtC, h->qtC2, h->dErr);
+    h->launches++;
+    stamp(h, 4);
+    k_blur<<<dim3(D.totalBlurTiles, batch), 256, 0, st>>>(h->dPlan, h->dPyr, h->dBlur);
+    h->launches++;
+    stamp(h, 5);
+    k_orient_desc<<<dim3((D.selStride + 7) / 8, batch), 256, 0, st>>>(h->dPlan, h->dPyr, h->dBlur, h->dSel, h->dSelCount,
+                                                                      h->dKps, h->dDesc, h->dNOut);
+    h->launches++;
+    stamp(h, 6);
+    CK(cudaGetLastError());
+    h->lastBatch = batch;
+    h->blurValid = true;
+
+    // results: counts first (they gate the error code), then one strided copy per array
+    CK(cudaMemcpyAsync(h->hCounts, h->dNOut, (size_t)batch * sizeof(int), cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(h->hCounts + batch, h->dErr, sizeof(int), cudaMemcpyDeviceToHost, st));
+    const cudaMemcpyKind kout = h->outSpace == ORBX_MEM_HOST ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice;
+    const int rows = std::min(cap, D.selStride);
+    if (rows > 0) {
+        CK(cudaMemcpy2DAsync(kps, (size_t)cap * sizeof(orbx_kp), h->dKps, (size_t)D.selStride * sizeof(orbx_kp),
+                             (size_t)rows * sizeof(orbx_kp), batch, kout, st));
+        CK(cudaMemcpy2DAsync(desc, (size_t)cap * 32, h->dDesc, (size_t)D.selStride * 32, (size_t)rows * 32, batch, kout, st));
+    }
+    stamp(h, 7);
+    CK(cudaStreamSynchronize(st));
+    if (h->profiling)
+        for (int i = 0; i < 7; i++) cudaEventElapsedTime(&h->stageMs[i], h->ev[i], h->ev[i + 1]);
+    if (h->hCounts[batch] != 0) {
+        const int code = h->hCounts[batch];
+        cudaMemsetAsync(h->dErr, 0, sizeof(int), st);
+        FAIL(ORBX_ECUDA, "device-side error flag %d (2 = TMA wait timed out, 3 = candidate overflow, 4/5 = quadtree bound)", code);
+    }
+    int worst = 0;
+    for (int f = 0; f < batch; f++) {
+        if (h->outSpace == ORBX_MEM_HOST || n) n[f] = h->hCounts[f];
+        worst = std::max(worst, h->hCounts[f]);
+    }
+    if (worst > cap) FAIL(ORBX_ECAP, "cap_per_frame %d < %d keypoints found", cap, worst);
+    return ORBX_OK;
+}
+
+extern "C" int orbx_extract(orbx_t* h, const uint8_t* img, int w, int hgt, size_t stride, orbx_kp* kps, uint8_t* desc,
+                            int cap, int* n) {
+    return orbx_extract_batch(h, img, 1, w, hgt, stride, stride * (size_t)(hgt > 0 ? hgt : 0), kps, desc, cap, n);
+}
+
+extern "C" int orbx_level_size(orbx_t* h, int level, int* w, int* hgt) {
+    if (!h || level < 0 || level >= h->prm.nlevels) FAIL(ORBX_EINVAL, "bad level");
+    if (!h->planW) FAIL(ORBX_ESTATE, "no image has been extracted yet");
+    if (w) *w = h->hp.lv[level].w;
+    if (hgt) *hgt = h->hp.lv[level].h;
+    return ORBX_OK;
+}
+
+static int export_level(orbx_handle* h, const uint8_t* base, int frame, int level, uint8_t* dst, size_t dst_stride, int e) {
+    if (!h || !dst || level < 0 || level >= h->prm.nlevels) FAIL(ORBX_EINVAL, "bad argument");
+    if (!h->lastBatch || frame < 0 || frame >= h->lastBatch) FAIL(ORBX_ESTATE, "frame %d not in the last extracted batch", frame);
+    CK(cudaSetDevice(h->device));
+    const LevelGeo& G = h->hp.lv[level];
+    const int W = G.w + 2 * e, H = G.h + 2 * e;
+    if (dst_stride < (size_t)W) FAIL(ORBX_EINVAL, "dst_stride too small");
+    const size_t need = (size_t)W * H;
+    if (need > h->exportBytes) {
+        cudaFree(h->dExport);
+        h->dExport = nullptr;
+        h->exportBytes = 0;
+        CK(cudaMalloc(&h->dExport, need));
+        h->exportBytes = need;
+    }
+    dim3 block(32, 8), grid((W + 31) / 32, (H + 7) / 8);
+    k_export<<<grid, block, 0, h->stream>>>(h->dPlan, base, level, frame, e, h->dExport);
+    h->launches++;
+    CK(cudaGetLastError());
+    CK(cudaMemcpy2DAsync(dst, dst_stride, h->dExport, W, W, H, cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    return ORBX_OK;
+}
+
+extern "C" int orbx_pyramid_level(orbx_t* h, int frame, int level, uint8_t* dst, size_t dst_stride, int with_border) {
+    if (!h) FAIL(ORBX_EINVAL, "null handle");
+    return export_level(h, h->dPyr, frame, level, dst, dst_stride, with_border ? h->prm.edgeThreshold : 0);
+}
+
+extern "C" int orbx_blurred_level(orbx_t* h, int frame, int level, uint8_t* dst, size_t dst_stride) {
+    if (!h) FAIL(ORBX_EINVAL, "null handle");
+    if (!h->blurValid) FAIL(ORBX_ESTATE, "no blurred pyramid resident");
+    return export_level(h, h->dBlur, frame, level, dst, dst_stride, 0);
+}
+
+extern "C" int orbx_candidates(orbx_t* h, int frame, int level, int32_t* xys, int cap, int* n) {
+    if (!h || !n || level < 0 || level >= h->prm.nlevels) FAIL(ORBX_EINVAL, "bad argument");
+    if (!h->lastBatch || frame < 0 || frame >= h->lastBatch) FAIL(ORBX_ESTATE, "frame %d not in the last extracted batch", frame);
+    CK(cudaSetDevice(h->device));
+    const LevelGeo& G = h->hp.lv[level];
+    int cnt = 0;
+    CK(cudaMemcpyAsync(&cnt, h->dCandCount + frame * h->prm.nlevels + level, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    *n = cnt;
+    if (cnt > cap) FAIL(ORBX_ECAP, "cap %d < %d candidates", cap, cnt);
+    if (cnt == 0) return ORBX_OK;
+    std::vector<u64> rec(cnt);
+    CK(cudaMemcpyAsync(rec.data(), h->dCand + G.candOff + (long long)frame * G.candCap, (size_t)cnt * sizeof(u64),
+                       cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    for (int i = 0; i < cnt; i++) {  // pure unpacking of the device records (layout documented in orbx_internal.cuh)
+        int x, y, s;
+        cand_unpack(rec[i], G, x, y, s);
+        xys[3 * i] = x + h->prm.edgeThreshold - 3;
+        xys[3 * i + 1] = y + h->prm.edgeThreshold - 3;
+        xys[3 * i + 2] = s;
+    }
+    return ORBX_OK;
+}
+
+extern "C" int orbx_stream(orbx_t* h, void** stream) {
+    if (!h || !stream) FAIL(ORBX_EINVAL, "null argument");
+    *stream = (void*)h->stream;
+    return ORBX_OK;
+}
+extern "C" int64_t orbx_launch_count(orbx_t* h) { return h ? h->launches : 0; }
+extern "C" int orbx_set_profiling(orbx_t* h, int on) {
+    if (!h) FAIL(ORBX_EINVAL, "null handle");
+    h->profiling = on != 0;
+    return ORBX_OK;
+}
+extern "C" int orbx_stage_ms(orbx_t* h, float* ms7) {
+    if (!h || !ms7) FAIL(ORBX_EINVAL, "null argument");
+    for (int i = 0; i < 7; i++) ms7[i] = h->stageMs[i];
+    return ORBX_OK;
+}
+
+// accessors used by orbx_match.cu (stereo works on the extractor's resident state)
+struct OrbxView {
+    const DevPlan* hp; DevPlan* dPlan; uint8_t* dPyr; orbx_kp* dKps; uint8_t* dDesc; int* dNOut; int lastBatch;
+    cudaStream_t stream; int device; int outSpace; int* hCounts;
+};
+OrbxView orbx_view(orbx_handle* h) {
+    return OrbxView{&h->hp, h->dPlan, h->dPyr, h->dKps, h->dDesc, h->dNOut, h->lastBatch, h->stream, h->device, h->outSpace,
+                    h->hCounts};
+}
+void orbx_count_launch(orbx_handle* h, int k) { h->launches += k; }

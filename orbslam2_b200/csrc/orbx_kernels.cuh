@@ -1,0 +1,727 @@
+// orbx_kernels.cuh — extraction kernels (sm_100a). Included once by orbx_extract.cu.
+//
+// K1 k_resize      bilinear 8U pyramid level from the previous level       (ref: src/ORBextractor.cc:921-946 + cv::resize)
+// K2 k_fast        per-cell FAST-9/16 score + cell-local NMS + ini/min retry (ref: :759-823 + cv::FAST); tile via TMA
+// K3 k_quadtree    DistributeOctTree as a level-synchronous CTA algorithm    (ref: :475-757)
+// K4 k_blur        7x7 sigma-2 fixed-point Gaussian                          (ref: :899-900 + cv::GaussianBlur)
+// K5 k_orient_desc IC_Angle + steered BRIEF + keypoint assembly              (ref: :72-142, :835-841, :909-917)
+// K6 k_export      padded (reflect-101) copy of one level                    (ref: :936-942 + cv::copyMakeBorder)
+#pragma once
+#include "orbx_internal.cuh"
+#include "../../include/orbx_pattern.inc"
+
+__device__ __constant__ signed char c_pattern[1024];
+
+// ------------------------------------------------------------------------------------------------ helpers
+__device__ __forceinline__ int reflect101(int p, int len) {
+    if (len == 1) return 0;
+    while (p < 0 || p >= len) p = p < 0 ? -p : 2 * len - 2 - p;
+    return p;
+}
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+// Exclusive scan in place over a[0..m) in shared memory; every thread of the block must call; returns the total.
+// ws: 33 ints of shared scratch.
+__device__ int block_excl_scan(int* a, int m, int* ws) {
+    const int tid = threadIdx.x, T = blockDim.x, lane = tid & 31, wid = tid >> 5, nw = T >> 5;
+    int carry = 0;
+    for (int base = 0; base < m; base += T) {
+        const int i = base + tid;
+        const int v = (i < m) ? a[i] : 0;
+        int x = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            int y = __shfl_up_sync(0xffffffffu, x, o);
+            if (lane >= o) x += y;
+        }
+        if (lane == 31) ws[wid] = x;
+        __syncthreads();
+        if (wid == 0) {
+            const int s = (lane < nw) ? ws[lane] : 0;
+            int t = s;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                int y = __shfl_up_sync(0xffffffffu, t, o);
+                if (lane >= o) t += y;
+            }
+            ws[lane] = t - s;
+            if (lane == 31) ws[32] = t;
+        }
+        __syncthreads();
+        if (i < m) a[i] = carry + ws[wid] + x - v;
+        carry += ws[32];
+        __syncthreads();
+    }
+    return carry;
+}
+
+// Ascending bitonic sort of a[0..P2) (P2 a power of two) in shared memory.
+__device__ void block_bitonic_sort(u64* a, int P2) {
+    for (int k = 2; k <= P2; k <<= 1)
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int i = threadIdx.x; i < P2; i += blockDim.x) {
+                const int ixj = i ^ j;
+                if (ixj > i) {
+                    const bool up = ((i & k) == 0);
+                    const u64 x = a[i], y = a[ixj];
+                    if ((x > y) == up) {
+                        a[i] = y;
+                        a[ixj] = x;
+                    }
+                }
+            }
+            __syncthreads();
+        }
+}
+
+__device__ __forceinline__ int next_pow2(int v) {
+    int p = 1;
+    while (p < v) p <<= 1;
+    return p;
+}
+
+// ------------------------------------------------------------------------------------------------ K1 resize
+// OpenCV 8U INTER_LINEAR fixed point: H = S[s]*a0 + S[s+1]*a1 (scale 2^11); out = ((b0*(H0>>4))>>16 + (b1*(H1>>4))>>16 + 2)>>2.
+// Tables (host-computed with OpenCV's float/double expressions): int2 {source index, a0 | a1<<16}.
+// One thread = 4 consecutive output pixels (one aligned 32-bit store).
+__global__ void __launch_bounds__(256) k_resize(const DevPlan* __restrict__ P, int level, uint8_t* __restrict__ pyr,
+                                                const int2* __restrict__ tabs) {
+    const LevelGeo& D = P->lv[level];
+    const LevelGeo& S = P->lv[level - 1];
+    const int x4 = (blockIdx.x * 64 + threadIdx.x) * 4;
+    const int y = blockIdx.y * 4 + threadIdx.y;
+    const int f = blockIdx.z;
+    if (x4 >= D.w || y >= D.h) return;
+    const uint8_t* src = pyr + S.pyrOff + (long long)f * S.frameStride;
+    uint8_t* dst = pyr + D.pyrOff + (long long)f * D.frameStride + (long long)y * D.pitch + x4;
+    uint32_t out = 0;
+    if (S.w == 2 * D.w && S.h == 2 * D.h) {  // OpenCV's exact-2x INTER_AREA shortcut
+        const uint8_t* r0 = src + (long long)(2 * y) * S.pitch;
+        const uint8_t* r1 = r0 + S.pitch;
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            const int x = x4 + i;
+            if (x < D.w) {
+                int v = (r0[2 * x] + r0[2 * x + 1] + r1[2 * x] + r1[2 * x + 1] + 2) >> 2;
+                out |= (uint32_t)v << (8 * i);
+            }
+        }
+        *(uint32_t*)dst = out;
+        return;
+    }
+    const int2* xt = tabs + D.xtabOff;
+    const int2 ty = tabs[D.ytabOff + y];
+    const int sy0 = min(max(ty.x, 0), S.h - 1), sy1 = min(max(ty.x + 1, 0), S.h - 1);
+    const int b0 = (short)(ty.y & 0xffff), b1 = ty.y >> 16;
+    const uint8_t* r0 = src + (long long)sy0 * S.pitch;
+    const uint8_t* r1 = src + (long long)sy1 * S.pitch;
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        const int x = x4 + i;
+        if (x < D.w) {
+            const int2 tx = xt[x];
+            const int sx = tx.x, sx1 = min(sx + 1, S.w - 1);
+            const int a0 = (short)(tx.y & 0xffff), a1 = tx.y >> 16;
+            const int H0 = r0[sx] * a0 + r0[sx1] * a1;
+            const int H1 = r1[sx] * a0 + r1[sx1] * a1;
+            const int v = (((b0 * (H0 >> 4)) >> 16) + ((b1 * (H1 >> 4)) >> 16) + 2) >> 2;
+            out |= (uint32_t)(v & 0xff) << (8 * i);
+        }
+    }
+    *(uint32_t*)dst = out;
+}
+
+// ------------------------------------------------------------------------------------------------ K2 FAST
+// One CTA per (cell, frame). The (wCell+6) x (hCell+6) cell ROI is fetched with ONE 3-D TMA tile load
+// (coordinates x, y, frame on the level's tensor map; out-of-image bytes are zero-filled and never used).
+// Scores are computed once at minThFAST; NMS is cell-local (a neighbour outside this cell's detection area counts 0);
+// the reference's "FAST(ini) else FAST(min)" retry is the block-wide test "any survivor with score >= ini".
+__device__ __forceinline__ bool nine_contiguous(uint32_t m) {
+    m |= m << 16;
+    uint32_t r = m & (m >> 1);
+    r &= r >> 2;
+    r &= r >> 4;
+    r &= m >> 8;
+    return (r & 0xFFFFu) != 0;
+}
+
+__device__ __forceinline__ int fast_score(const int (&d)[16]) {
+    // max over the 16 arcs of 9 of min(d) and of min(-d), minus 1 (OpenCV cornerScore<16>)
+    int mn2[16], mx2[16];
+#pragma unroll
+    for (int k = 0; k < 16; k++) {
+        mn2[k] = min(d[k], d[(k + 1) & 15]);
+        mx2[k] = max(d[k], d[(k + 1) & 15]);
+    }
+    int mn4[16], mx4[16];
+#pragma unroll
+    for (int k = 0; k < 16; k++) {
+        mn4[k] = min(mn2[k], mn2[(k + 2) & 15]);
+        mx4[k] = max(mx2[k], mx2[(k + 2) & 15]);
+    }
+    int best = -256;
+#pragma unroll
+    for (int k = 0; k < 16; k++) {
+        const int mn9 = min(min(mn4[k], mn4[(k + 4) & 15]), d[(k + 8) & 15]);
+        const int mx9 = max(max(mx4[k], mx4[(k + 4) & 15]), d[(k + 8) & 15]);
+        best = max(best, max(mn9, -mx9));
+    }
+    return best - 1;
+}
+
+__global__ void __launch_bounds__(256) k_fast(const __grid_constant__ TmapPack maps, const DevPlan* __restrict__ P,
+                                              u64* __restrict__ cand, int* __restrict__ candCount,
+                                              int* __restrict__ err) {
+    extern __shared__ __align__(128) uint8_t fast_smem[];
+    uint8_t* smem = fast_smem;
+    const int f = blockIdx.y;
+    const int c = blockIdx.x;
+    int level = 0;
+    while (level + 1 < P->nlevels && c >= P->lv[level + 1].cellBase) level++;
+    const LevelGeo& G = P->lv[level];
+    const int ci = (c - G.cellBase) / G.nCols, cj = (c - G.cellBase) % G.nCols;
+    const int e = P->edge;
+    const int ox = e - 3 + cj * G.wCell, oy = e - 3 + ci * G.hCell;  // ROI origin (level pixels)
+    const int dw = min(G.wCell, (G.w - e) - (ox + 3));               // detection area of this cell
+    const int dh = min(G.hCell, (G.h - e) - (oy + 3));
+    if (dw <= 0 || dh <= 0) return;
+
+    const int boxW = G.boxW, boxH = G.boxH;
+    const int SP = G.wCell + 2;  // score pitch (1-px zero ring)
+    uint8_t* tile = smem;
+    const int tileBytes = (boxW * boxH + 127) & ~127;
+    uint8_t* score = smem + tileBytes;
+    const int scoreBytes = (SP * (G.hCell + 2) + 15) & ~15;
+    u64* staging = (u64*)(score + scoreBytes);
+    u64* mbar = staging + G.maxSurv;
+    int* sh = (int*)(mbar + 1);  // [0] survivor count, [1] global base
+
+    const int tid = threadIdx.x;
+    const uint32_t bar = smem_u32(mbar);
+    if (tid == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        sh[0] = 0;
+    }
+    for (int i = tid; i < scoreBytes / 4; i += blockDim.x) ((uint32_t*)score)[i] = 0;
+    __syncthreads();
+    if (tid == 0) {
+        const uint32_t bytes = (uint32_t)(boxW * boxH);
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+        asm volatile(
+            "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+            ::"r"(smem_u32(tile)), "l"(&maps.m[level]), "r"(ox), "r"(oy), "r"(f), "r"(bar)
+            : "memory");
+    }
+    {   // bounded wait on phase 0 (a lost TMA must not hang the GPU: flag the error and bail out)
+        uint32_t done = 0;
+        int spins = 0;
+        while (!done) {
+            asm volatile(
+                "{\n\t.reg .pred p;\n\t"
+                "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+                "selp.u32 %0, 1, 0, p;\n\t}"
+                : "=r"(done)
+                : "r"(bar), "r"(0u)
+                : "memory");
+            if (!done && ++spins > (1 << 22)) {
+                atomicExch(err, 2);
+                break;
+            }
+        }
+    }
+
+    const int th = P->minTh;
+    const int npx = dw * dh;
+    for (int p = tid; p < npx; p += blockDim.x) {
+        const int yin = p / dw, xin = p - yin * dw;
+        const uint8_t* q = tile + (yin + 3) * boxW + (xin + 3);
+        const int v = q[0];
+        // compass pre-test: every arc of 9 contains at least two of the four compass points
+        const int c0 = q[3 * boxW], c4 = q[3], c8 = q[-3 * boxW], c12 = q[-3];
+        const int hi = v + th, lo = v - th;
+        const int nb = (c0 > hi) + (c4 > hi) + (c8 > hi) + (c12 > hi);
+        const int nd = (c0 < lo) + (c4 < lo) + (c8 < lo) + (c12 < lo);
+        if (nb < 2 && nd < 2) continue;
+        int d[16];
+        d[0] = v - c0;
+        d[1] = v - q[3 * boxW + 1];
+        d[2] = v - q[2 * boxW + 2];
+        d[3] = v - q[boxW + 3];
+        d[4] = v - c4;
+        d[5] = v - q[-boxW + 3];
+        d[6] = v - q[-2 * boxW + 2];
+        d[7] = v - q[-3 * boxW + 1];
+        d[8] = v - c8;
+        d[9] = v - q[-3 * boxW - 1];
+        d[10] = v - q[-2 * boxW - 2];
+        d[11] = v - q[-boxW - 3];
+        d[12] = v - c12;
+        d[13] = v - q[boxW - 3];
+        d[14] = v - q[2 * boxW - 2];
+        d[15] = v - q[3 * boxW - 1];
+        uint32_t mb = 0, md = 0;  // circle brighter than centre (d < -th) / darker (d > th)
+#pragma unroll
+        for (int k = 0; k < 16; k++) {
+            mb |= (uint32_t)(d[k] < -th) << k;
+            md |= (uint32_t)(d[k] > th) << k;
+        }
+        if (nine_contiguous(mb) || nine_contiguous(md)) score[(yin + 1) * SP + xin + 1] = (uint8_t)fast_score(d);
+    }
+    __syncthreads();
+
+    // cell-local NMS (strictly greater than all 8 neighbours); remember survivors as a per-thread bit mask
+    uint32_t surv = 0;
+    int anyIni = 0;
+    const int ini = P->iniTh;
+    {
+        int it = 0;
+        for (int p = tid; p < npx; p += blockDim.x, it++) {
+            const int yin = p / dw, xin = p - yin * dw;
+            const uint8_t* s = score + (yin + 1) * SP + xin + 1;
+            const int v = s[0];
+            if (v == 0) continue;
+            if (v > s[-1] && v > s[1] && v > s[-SP - 1] && v > s[-SP] && v > s[-SP + 1] && v > s[SP - 1] && v > s[SP] &&
+                v > s[SP + 1]) {
+                surv |= 1u << it;
+                anyIni |= (v >= ini);
+            }
+        }
+    }
+    const int useIni = __syncthreads_or(anyIni);
+    {
+        int it = 0;
+        for (int p = tid; p < npx; p += blockDim.x, it++) {
+            if (!((surv >> it) & 1u)) continue;
+            const int yin = p / dw, xin = p - yin * dw;
+            const int v = score[(yin + 1) * SP + xin + 1];
+            if (useIni && v < ini) continue;
+            const int slot = atomicAdd(&sh[0], 1);
+            if (slot < G.maxSurv) staging[slot] = cand_pack(v, ci, cj, yin, xin);
+        }
+    }
+    __syncthreads();
+    const int cnt = min(sh[0], G.maxSurv);
+    if (cnt == 0) return;
+    if (tid == 0) sh[1] = atomicAdd(&candCount[f * P->nlevels + level], cnt);
+    __syncthreads();
+    const int base = sh[1];
+    u64* out = cand + G.candOff + (long long)f * G.candCap;
+    for (int i = tid; i < cnt; i += blockDim.x) {
+        if (base + i < G.candCap) out[base + i] = staging[i];
+        else atomicExch(err, 3);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ K3 quadtree
+// DistributeOctTree without lists or pointers. Nodes live in shared memory as rectangles + key counts; every key
+// carries the id of the node it is in. A sweep divides every node with > 1 key ("full" sweep) or, once
+// size + 3*nToExpand > N, the largest nodes first until size >= N ("sorted" sweep: bitonic sort of
+// (count desc, UL.y, UL.x), prefix sum of per-node gains, cut at the first prefix reaching N). The reference's
+// termination rules (size >= N, or a sweep that did not grow the node set) are kept verbatim.
+struct QtSmem {
+    short4* geoA; short4* geoB;
+    int* cntA; int* cntB;
+    int* slotOf; int* remap; int* rankOfSlot; int* orderSlot; int* nodeOfSlot;
+    int* childCnt; int* childNew; int* gain; int* flags;
+    u64* sortbuf;
+    int* ws;
+};
+
+__device__ __forceinline__ int quadrant_of(const short4 g, int x, int y) {
+    const int mx = g.x + ((g.y - g.x + 1) >> 1);  // UL.x + ceil((UR.x-UL.x)/2)
+    const int my = g.z + ((g.w - g.z + 1) >> 1);
+    return (x < mx ? 0 : 1) + (y < my ? 0 : 2);
+}
+
+__global__ void k_quadtree(const DevPlan* __restrict__ P, const u64* __restrict__ cand,
+                           const int* __restrict__ candCount, int* __restrict__ nodeOf, uint2* __restrict__ sel,
+                           int* __restrict__ selCount, int C, int C2, int* __restrict__ err) {
+    extern __shared__ __align__(16) uint8_t qt_smem[];
+    uint8_t* smem = qt_smem;
+    const int level = blockIdx.x, f = blockIdx.y;
+    const LevelGeo& G = P->lv[level];
+    const int nl = P->nlevels;
+    const int tid = threadIdx.x, T = blockDim.x;
+    int n = candCount[f * nl + level];
+    if (n > G.candCap) n = G.candCap;
+    if (n == 0) {
+        if (tid == 0) selCount[f * nl + level] = 0;
+        return;
+    }
+    const u64* keys = cand + G.candOff + (long long)f * G.candCap;
+    int* nod = nodeOf + G.candOff + (long long)f * G.candCap;
+
+    QtSmem S;
+    {
+        uint8_t* p = smem;
+        S.sortbuf = (u64*)p; p += sizeof(u64) * C2;
+        S.geoA = (short4*)p; p += sizeof(short4) * C;
+        S.geoB = (short4*)p; p += sizeof(short4) * C;
+        S.cntA = (int*)p; p += 4 * C;
+        S.cntB = (int*)p; p += 4 * C;
+        S.slotOf = (int*)p; p += 4 * C;
+        S.remap = (int*)p; p += 4 * C;
+        S.rankOfSlot = (int*)p; p += 4 * C;
+        S.orderSlot = (int*)p; p += 4 * C;
+        S.nodeOfSlot = (int*)p; p += 4 * C;
+        S.gain = (int*)p; p += 4 * C;
+        S.flags = (int*)p; p += 4 * C;
+        S.childCnt = (int*)p; p += 16 * C;
+        S.childNew = (int*)p; p += 16 * C;
+        S.ws = (int*)p;  // 40 ints
+    }
+    const int N = G.quota;
+    const float hX = G.hX;
+    int nNodes = G.nIni;
+    for (int i = tid; i < C; i += T) S.cntA[i] = 0;
+    for (int i = tid; i < nNodes; i += T)
+        S.geoA[i] = make_short4((short)(int)__fmul_rn(hX, (float)i), (short)(int)__fmul_rn(hX, (float)(i + 1)), 0,
+                                (short)G.treeH);
+    __syncthreads();
+    for (int k = tid; k < n; k += T) {
+        int x, y, s;
+        cand_unpack(keys[k], G, x, y, s);
+        int idx = (int)__fdiv_rn((float)x, hX);
+        idx = min(idx, nNodes - 1);
+        nod[k] = idx;
+        atomicAdd(&S.cntA[idx], 1);
+    }
+    __syncthreads();
+
+    bool sortedMode = false, first = true;
+    int size = 0, prevSize = 0;
+    {   // alive count
+        for (int i = tid; i < nNodes; i += T) S.flags[i] = S.cntA[i] > 0;
+        __syncthreads();
+        size = block_excl_scan(S.flags, nNodes, S.ws);
+    }
+    for (int sweep = 0; sweep < 64; sweep++) {
+        // expandable nodes -> slots
+        for (int i = tid; i < nNodes; i += T) S.flags[i] = S.cntA[i] > 1;
+        __syncthreads();
+        const int nE = block_excl_scan(S.flags, nNodes, S.ws);
+        if (!first) {
+            if (size >= N || size == prevSize) break;
+            if (!sortedMode && size + 3 * nE > N) sortedMode = true;
+        }
+        first = false;
+        if (nE == 0) break;
+        for (int i = tid; i < nNodes; i += T) {
+            if (S.cntA[i] > 1) {
+                const int s = S.flags[i];
+                S.slotOf[i] = s;
+                S.nodeOfSlot[s] = i;
+            } else
+                S.slotOf[i] = -1;
+        }
+        for (int i = tid; i < 4 * nE; i += T) S.childCnt[i] = 0;
+        __syncthreads();
+        if (sortedMode) {
+            const int P2 = next_pow2(nE);
+            for (int s = tid; s < P2; s += T) {
+                u64 key = ~0ull;
+                if (s < nE) {
+                    const int nd = S.nodeOfSlot[s];
+                    const short4 g = S.geoA[nd];
+                    key = ((u64)(0x3FFFFFu - (unsigned)min(S.cntA[nd], 0x3FFFFF)) << 40) | ((u64)(unsigned short)g.z << 26) |
+                          ((u64)(unsigned short)g.x << 12) | (u64)s;
+                }
+                S.sortbuf[s] = key;
+            }
+            __syncthreads();
+            block_bitonic_sort(S.sortbuf, P2);
+            for (int r = tid; r < nE; r += T) {
+                const int s = (int)(S.sortbuf[r] & 0xFFFull);
+                S.orderSlot[r] = s;
+                S.rankOfSlot[s] = r;
+            }
+        } else {
+            for (int r = tid; r < nE; r += T) {
+                S.orderSlot[r] = r;
+                S.rankOfSlot[r] = r;
+            }
+        }
+        __syncthreads();
+        // child key counts
+        for (int k = tid; k < n; k += T) {
+            const int nd = nod[k];
+            const int s = S.slotOf[nd];
+            if (s >= 0) {
+                int x, y, sc;
+                cand_unpack(keys[k], G, x, y, sc);
+                atomicAdd(&S.childCnt[4 * s + quadrant_of(S.geoA[nd], x, y)], 1);
+            }
+        }
+        __syncthreads();
+        // gains in rank order, prefix sum, cut
+        for (int r = tid; r < nE; r += T) {
+            const int* cc = S.childCnt + 4 * S.orderSlot[r];
+            S.gain[r] = (cc[0] > 0) + (cc[1] > 0) + (cc[2] > 0) + (cc[3] > 0) - 1;
+        }
+        if (tid == 0) S.ws[36] = nE;  // expandCount
+        __syncthreads();
+        block_excl_scan(S.gain, nE, S.ws);
+        if (sortedMode) {
+            for (int r = tid; r < nE; r += T) {
+                const int* cc = S.childCnt + 4 * S.orderSlot[r];
+                const int own = (cc[0] > 0) + (cc[1] > 0) + (cc[2] > 0) + (cc[3] > 0) - 1;
+                if (size + S.gain[r] + own >= N) atomicMin(&S.ws[36], r + 1);
+            }
+        }
+        __syncthreads();
+        const int expandCount = S.ws[36];
+        // survivors (alive, not divided in this sweep)
+        for (int i = tid; i < nNodes; i += T) {
+            const int s = S.slotOf[i];
+            S.flags[i] = (S.cntA[i] > 0) && (s < 0 || S.rankOfSlot[s] >= expandCount);
+        }
+        __syncthreads();
+        const int nSurv = block_excl_scan(S.flags, nNodes, S.ws);
+        for (int j = tid; j < 4 * nE; j += T) {
+            const int r = j >> 2, q = j & 3;
+            S.childNew[j] = (r < expandCount) && (S.childCnt[4 * S.orderSlot[r] + q] > 0);
+        }
+        __syncthreads();
+        const int nCh = block_excl_scan(S.childNew, 4 * nE, S.ws);
+        if (nSurv + nCh > C) {  // cannot happen (node bound); guard against smem overrun
+            if (tid == 0) atomicExch(err, 4);
+            break;
+        }
+        for (int i = tid; i < nNodes; i += T) {
+            const int s = S.slotOf[i];
+            if ((S.cntA[i] > 0) && (s < 0 || S.rankOfSlot[s] >= expandCount)) {
+                const int id = S.flags[i];
+                S.remap[i] = id;
+                S.geoB[id] = S.geoA[i];
+                S.cntB[id] = S.cntA[i];
+            }
+        }
+        for (int j = tid; j < 4 * nE; j += T) {
+            const int r = j >> 2, q = j & 3;
+            if (r >= expandCount) continue;
+            const int s = S.orderSlot[r];
+            const int cc = S.childCnt[4 * s + q];
+            if (cc == 0) continue;
+            const short4 g = S.geoA[S.nodeOfSlot[s]];
+            const short mx = g.x + ((g.y - g.x + 1) >> 1), my = g.z + ((g.w - g.z + 1) >> 1);
+            short4 cg;
+            cg.x = (q & 1) ? mx : g.x;
+            cg.y = (q & 1) ? g.y : mx;
+            cg.z = (q & 2) ? my : g.z;
+            cg.w = (q & 2) ? g.w : my;
+            const int id = nSurv + S.childNew[j];
+            S.geoB[id] = cg;
+            S.cntB[id] = cc;
+        }
+        __syncthreads();
+        for (int k = tid; k < n; k += T) {
+            const int nd = nod[k];
+            const int s = S.slotOf[nd];
+            if (s >= 0 && S.rankOfSlot[s] < expandCount) {
+                int x, y, sc;
+                cand_unpack(keys[k], G, x, y, sc);
+                nod[k] = nSurv + S.childNew[4 * S.rankOfSlot[s] + quadrant_of(S.geoA[nd], x, y)];
+            } else
+                nod[k] = S.remap[nd];
+        }
+        __syncthreads();
+        {
+            short4* tg = S.geoA; S.geoA = S.geoB; S.geoB = tg;
+            int* tc = S.cntA; S.cntA = S.cntB; S.cntB = tc;
+        }
+        prevSize = size;
+        size = nSurv + nCh;
+        nNodes = size;
+    }
+
+    // one keypoint per node: max (score, first in reference order)
+    u64* best = (u64*)S.childCnt;  // 2*C u64 available
+    for (int i = tid; i < nNodes; i += T) best[i] = 0;
+    __syncthreads();
+    for (int k = tid; k < n; k += T) atomicMax(&best[nod[k]], keys[k]);
+    __syncthreads();
+    const int P2 = next_pow2(nNodes);
+    for (int i = tid; i < P2; i += T) {
+        u64 key = ~0ull;
+        if (i < nNodes && S.cntA[i] > 0) {
+            int x, y, sc;
+            cand_unpack(best[i], G, x, y, sc);
+            x += P->edge - 3;
+            y += P->edge - 3;
+            key = ((u64)(unsigned)((y << 16) | x) << 32) | (u64)(unsigned)sc;
+        }
+        S.sortbuf[i] = key;
+    }
+    __syncthreads();
+    block_bitonic_sort(S.sortbuf, P2);
+    const int nOut = min(size, G.selCap);
+    if (size > G.selCap && tid == 0) atomicExch(err, 5);
+    uint2* out = sel + (long long)f * P->selStride + G.selOff;
+    for (int i = tid; i < nOut; i += T) {
+        const u64 k = S.sortbuf[i];
+        out[i] = make_uint2((unsigned)(k >> 32), (unsigned)(k & 0xFFFFFFFFull));
+    }
+    if (tid == 0) selCount[f * nl + level] = nOut;
+}
+
+// ------------------------------------------------------------------------------------------------ K4 blur
+// 7x7 Gaussian, sigma 2, OpenCV 8U fixed point: taps {18,34,48,56,48,34,18}/256 per axis, exact 16/32-bit
+// accumulation, single rounding (sum + 32768) >> 16. BORDER_REFLECT_101 by index reflection on the tile load.
+// One CTA = 64 x 16 output tile of one level of one frame (fused launch over all levels).
+#define BLUR_TW 64
+#define BLUR_TH 16
+__global__ void __launch_bounds__(256) k_blur(const DevPlan* __restrict__ P, const uint8_t* __restrict__ pyr,
+                                              uint8_t* __restrict__ blur) {
+    __shared__ uint8_t raw[BLUR_TH + 6][BLUR_TW + 8];
+    __shared__ uint16_t hb[BLUR_TH + 6][BLUR_TW];
+    const int f = blockIdx.y;
+    int t = blockIdx.x, level = 0;
+    while (level + 1 < P->nlevels && t >= P->lv[level + 1].blurTileBase) level++;
+    const LevelGeo& G = P->lv[level];
+    t -= G.blurTileBase;
+    const int tx = t % G.blurTilesX, ty = t / G.blurTilesX;
+    const int x0 = tx * BLUR_TW, y0 = ty * BLUR_TH;
+    const uint8_t* src = pyr + G.pyrOff + (long long)f * G.frameStride;
+    const int tid = threadIdx.x;
+    for (int i = tid; i < (BLUR_TH + 6) * (BLUR_TW + 6); i += 256) {
+        const int ry = i / (BLUR_TW + 6), rx = i - ry * (BLUR_TW + 6);
+        const int gx = reflect101(min(x0 + rx - 3, G.w + 2), G.w), gy = reflect101(min(y0 + ry - 3, G.h + 2), G.h);
+        raw[ry][rx] = src[(long long)gy * G.pitch + gx];
+    }
+    __syncthreads();
+    for (int i = tid; i < (BLUR_TH + 6) * BLUR_TW; i += 256) {
+        const int ry = i / BLUR_TW, rx = i - ry * BLUR_TW;
+        const uint8_t* r = &raw[ry][rx];
+        hb[ry][rx] = (uint16_t)(18 * (r[0] + r[6]) + 34 * (r[1] + r[5]) + 48 * (r[2] + r[4]) + 56 * r[3]);
+    }
+    __syncthreads();
+    uint8_t* dst = blur + G.pyrOff + (long long)f * G.frameStride;
+    for (int i = tid; i < BLUR_TH * BLUR_TW; i += 256) {
+        const int oy = i / BLUR_TW, ox = i - oy * BLUR_TW;
+        const int gx = x0 + ox, gy = y0 + oy;
+        if (gx < G.w && gy < G.h) {
+            const uint32_t acc = 18u * (hb[oy][ox] + hb[oy + 6][ox]) + 34u * (hb[oy + 1][ox] + hb[oy + 5][ox]) +
+                                 48u * (hb[oy + 2][ox] + hb[oy + 4][ox]) + 56u * hb[oy + 3][ox];
+            dst[(long long)gy * G.pitch + gx] = (uint8_t)((acc + 32768u) >> 16);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ K5 orientation + descriptor
+// One warp per selected keypoint slot. Orientation: lanes = the 31 rows of the circular patch, integer moments,
+// warp-shuffle reduction, OpenCV's fastAtan2 polynomial evaluated without FMA contraction. Descriptor: lane i
+// produces byte i (pairs 8i..8i+7) from the blurred level with the reference's float rotate + round-half-even.
+__device__ __forceinline__ float fast_atan2_deg(float y, float x) {
+    const float scale = (float)(180.0 / 3.141592653589793238462643383279502884);
+    const float p1 = 0.9997878412794807f * scale, p3 = -0.3258083974640975f * scale;
+    const float p5 = 0.1555786518463281f * scale, p7 = -0.04432655554792128f * scale;
+    const float eps = 2.2204460492503131e-16f;  // (float)DBL_EPSILON
+    const float ax = fabsf(x), ay = fabsf(y);
+    float a, c, c2;
+    if (ax >= ay) {
+        c = __fdiv_rn(ay, __fadd_rn(ax, eps));
+        c2 = __fmul_rn(c, c);
+        a = __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(p7, c2), p5), c2), p3), c2), p1), c);
+    } else {
+        c = __fdiv_rn(ax, __fadd_rn(ay, eps));
+        c2 = __fmul_rn(c, c);
+        a = __fsub_rn(90.f,
+                      __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(p7, c2), p5), c2), p3), c2), p1), c));
+    }
+    if (x < 0) a = __fsub_rn(180.f, a);
+    if (y < 0) a = __fsub_rn(360.f, a);
+    return a;
+}
+
+__global__ void __launch_bounds__(256) k_orient_desc(const DevPlan* __restrict__ P, const uint8_t* __restrict__ pyr,
+                                                     const uint8_t* __restrict__ blur, const uint2* __restrict__ sel,
+                                                     const int* __restrict__ selCount, orbx_kp* __restrict__ kps,
+                                                     uint8_t* __restrict__ desc, int* __restrict__ nOut) {
+    const int lane = threadIdx.x & 31;
+    const int slot = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int f = blockIdx.y;
+    if (slot >= P->selStride) return;
+    const int nl = P->nlevels;
+    int level = 0;
+    while (level + 1 < nl && slot >= P->lv[level + 1].selOff) level++;
+    const LevelGeo& G = P->lv[level];
+    const int idx = slot - G.selOff;
+    const int* sc = selCount + f * nl;
+    int before = 0, total = 0;
+    for (int l = 0; l < nl; l++) {
+        const int c = sc[l];
+        if (l < level) before += c;
+        total += c;
+    }
+    if (slot == 0 && lane == 0) nOut[f] = total;
+    if (idx >= sc[level]) return;
+    const uint2 s = sel[(long long)f * P->selStride + slot];
+    const int x = s.x & 0xFFFF, y = s.x >> 16;
+    const uint8_t* img = pyr + G.pyrOff + (long long)f * G.frameStride + (long long)y * G.pitch + x;
+
+    // IC_Angle
+    const int hp = P->halfPatch;
+    int m10 = 0, m01 = 0;
+    for (int v = lane - hp; v <= hp; v += 32) {
+        const int d = P->umax[v < 0 ? -v : v];
+        const uint8_t* r = img + (long long)v * G.pitch;
+        int rs = 0;
+        for (int u = -d; u <= d; u++) {
+            const int val = r[u];
+            m10 += u * val;
+            rs += val;
+        }
+        m01 += v * rs;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        m10 += __shfl_xor_sync(0xffffffffu, m10, o);
+        m01 += __shfl_xor_sync(0xffffffffu, m01, o);
+    }
+    const float angle = fast_atan2_deg((float)m01, (float)m10);
+
+    // steered BRIEF on the blurred level
+    const float factorPI = (float)(3.1415926535897932384626433832795 / 180.f);
+    const float rad = __fmul_rn(angle, factorPI);
+    const float a = (float)cos((double)rad), b = (float)sin((double)rad);
+    const uint8_t* ctr = blur + G.pyrOff + (long long)f * G.frameStride + (long long)y * G.pitch + x;
+    const signed char* pat = c_pattern + lane * 32;
+    int val = 0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+        const float x1 = (float)pat[4 * k], y1 = (float)pat[4 * k + 1], x2 = (float)pat[4 * k + 2], y2 = (float)pat[4 * k + 3];
+        const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, b), __fmul_rn(y1, a)));
+        const int c1 = __float2int_rn(__fsub_rn(__fmul_rn(x1, a), __fmul_rn(y1, b)));
+        const int r2 = __float2int_rn(__fadd_rn(__fmul_rn(x2, b), __fmul_rn(y2, a)));
+        const int c2 = __float2int_rn(__fsub_rn(__fmul_rn(x2, a), __fmul_rn(y2, b)));
+        const int t0 = ctr[(long long)r1 * G.pitch + c1], t1 = ctr[(long long)r2 * G.pitch + c2];
+        val |= (t0 < t1) << k;
+    }
+    const long long o = (long long)f * P->selStride + before + idx;
+    desc[o * 32 + lane] = (uint8_t)val;
+    if (lane == 0) {
+        orbx_kp k;
+        k.x = (level == 0) ? (float)x : __fmul_rn((float)x, G.scale);
+        k.y = (level == 0) ? (float)y : __fmul_rn((float)y, G.scale);
+        k.size = G.sizeField;
+        k.angle = angle;
+        k.response = (float)s.y;
+        k.octave = level;
+        k.class_id = -1;
+        kps[o] = k;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ K6 export
+// Copy one level of one frame into a dense (w+2e) x (h+2e) buffer with the BORDER_REFLECT_101 frame (e may be 0).
+__global__ void k_export(const DevPlan* __restrict__ P, const uint8_t* __restrict__ src, int level, int f, int e,
+                         uint8_t* __restrict__ dst) {
+    const LevelGeo& G = P->lv[level];
+    const int W = G.w + 2 * e, H = G.h + 2 * e;
+    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y * blockDim.y + threadIdx.y;
+    if (x >= W || y >= H) return;
+    const uint8_t* s = src + G.pyrOff + (long long)f * G.frameStride;
+    dst[(long long)y * W + x] = s[(long long)reflect101(y - e, G.h) * G.pitch + reflect101(x - e, G.w)];
+}

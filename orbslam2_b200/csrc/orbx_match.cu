@@ -1,0 +1,638 @@
+// orbx_match.cu — matcher half of the C ABI (include/orbx.h) and the stereo matcher.
+//
+// K7  k_knn2           brute-force 2-NN over a train matrix   (ref: inner scan of ORBmatcher::SearchByFboW,
+//                                                              /root/reference/src/ORBmatcher.cc:195-229)
+// K7m k_knn2_merge     ordered merge of train-split partials (lowest index wins ties, as a sequential scan would)
+// K8  k_window_search  CSR candidate lists, one warp per query (ref: every ORBmatcher search loop)
+// K8d k_distance       batched DescriptorDistance              (ref: src/ORBmatcher.cc:1643-1659)
+// K9  k_stereo_match   row-band Hamming search + 11x11 SAD sweep + parabola (ref: src/Frame.cc:506-625)
+// K10 k_stereo_cut     median outlier cut                      (ref: src/Frame.cc:628-641)
+#include <algorithm>
+#include <vector>
+
+#include "orbx_internal.cuh"
+
+struct orbx_handle;
+struct OrbxView {
+    const DevPlan* hp; DevPlan* dPlan; uint8_t* dPyr; orbx_kp* dKps; uint8_t* dDesc; int* dNOut; int lastBatch;
+    cudaStream_t stream; int device; int outSpace; int* hCounts;
+};
+OrbxView orbx_view(orbx_handle* h);
+void orbx_count_launch(orbx_handle* h, int k);
+
+// ------------------------------------------------------------------------------------------------ K7 knn2
+#define KNN_THREADS 128
+#define KNN_QPT 2        // queries per thread
+#define KNN_TILE 512     // train descriptors per shared-memory tile (16 KB)
+
+struct Best2 {
+    int d1, i1, d2;
+};
+__device__ __forceinline__ void best2_push(Best2& b, int d, int j) {
+    // strict '<' in ascending index order: first (lowest index) wins ties; d2 = second smallest with multiplicity
+    if (d < b.d1) {
+        b.d2 = b.d1;
+        b.d1 = d;
+        b.i1 = j;
+    } else if (d < b.d2)
+        b.d2 = d;
+}
+
+__global__ void __launch_bounds__(KNN_THREADS) k_knn2(const uint4* __restrict__ q, int nq, const uint4* __restrict__ t,
+                                                      int nt, int chunk, int4* __restrict__ partial,
+                                                      int32_t* __restrict__ i1, uint16_t* __restrict__ d1,
+                                                      uint16_t* __restrict__ d2) {
+    __shared__ uint4 tile[KNN_TILE * 2];
+    const int tid = threadIdx.x;
+    const int qbase = blockIdx.x * (KNN_THREADS * KNN_QPT);
+    const int split = blockIdx.y;
+    const int t0 = split * chunk, t1 = min(nt, t0 + chunk);
+    uint4 qa[KNN_QPT][2];
+    Best2 b[KNN_QPT];
+#pragma unroll
+    for (int k = 0; k < KNN_QPT; k++) {
+        const int qi = min(qbase + k * KNN_THREADS + tid, nq - 1);
+        qa[k][0] = q[2 * (size_t)qi];
+        qa[k][1] = q[2 * (size_t)qi + 1];
+        b[k].d1 = 256;
+        b[k].d2 = 256;
+        b[k].i1 = -1;
+    }
+    for (int base = t0; base < t1; base += KNN_TILE) {
+        const int cnt = min(KNN_TILE, t1 - base);
+        __syncthreads();
+        for (int i = tid; i < cnt * 2; i += KNN_THREADS) tile[i] = t[2 * (size_t)base + i];
+        __syncthreads();
+#pragma unroll 4
+        for (int j = 0; j < cnt; j++) {
+            const uint4 x0 = tile[2 * j], x1 = tile[2 * j + 1];
+#pragma unroll
+            for (int k = 0; k < KNN_QPT; k++) best2_push(b[k], hamming256(qa[k][0], qa[k][1], x0, x1), base + j);
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < KNN_QPT; k++) {
+        const int qi = qbase + k * KNN_THREADS + tid;
+        if (qi >= nq) continue;
+        if (partial) partial[(size_t)split * nq + qi] = make_int4(b[k].d1, b[k].i1, b[k].d2, 0);
+        else {
+            i1[qi] = b[k].i1;
+            d1[qi] = (uint16_t)b[k].d1;
+            d2[qi] = (uint16_t)b[k].d2;
+        }
+    }
+}
+
+__global__ void k_knn2_merge(const int4* __restrict__ partial, int nq, int splits, int32_t* __restrict__ i1,
+                             uint16_t* __restrict__ d1, uint16_t* __restrict__ d2) {
+    const int qi = blockIdx.x * blockDim.x + threadIdx.x;
+    if (qi >= nq) return;
+    Best2 b = {256, -1, 256};
+    for (int s = 0; s < splits; s++) {  // ascending train order == the order a sequential scan visits them
+        const int4 p = partial[(size_t)s * nq + qi];
+        if (p.x < b.d1) {
+            b.d2 = min(b.d1, p.z);
+            b.d1 = p.x;
+            b.i1 = p.y;
+        } else
+            b.d2 = min(b.d2, p.x);
+    }
+    i1[qi] = b.i1;
+    d1[qi] = (uint16_t)b.d1;
+    d2[qi] = (uint16_t)b.d2;
+}
+
+// ------------------------------------------------------------------------------------------------ K8 window search
+__device__ __forceinline__ u64 shfl_min_u64(u64 v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const u64 w = __shfl_xor_sync(0xffffffffu, v, o);
+        v = w < v ? w : v;
+    }
+    return v;
+}
+
+__global__ void __launch_bounds__(256) k_window_search(const uint4* __restrict__ q, int nq, const int* __restrict__ off,
+                                                       const int* __restrict__ idx, const uint8_t* __restrict__ skip,
+                                                       const uint4* __restrict__ t, int32_t* __restrict__ bi,
+                                                       uint16_t* __restrict__ bd, uint16_t* __restrict__ sd,
+                                                       int32_t* __restrict__ si) {
+    const int lane = threadIdx.x & 31;
+    const int a = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (a >= nq) return;
+    const uint4 q0 = q[2 * (size_t)a], q1 = q[2 * (size_t)a + 1];
+    const int c0 = off[a], c1 = off[a + 1];
+    const u64 none = ((u64)256 << 32) | 0xFFFFFFFFull;
+    u64 k1 = none, k2 = none;  // two smallest (distance << 32 | list position) seen by this lane
+    for (int c = c0 + lane; c < c1; c += 32) {
+        if (skip && skip[c]) continue;
+        const int j = idx[c];
+        const int d = hamming256(q0, q1, t[2 * (size_t)j], t[2 * (size_t)j + 1]);
+        const u64 k = ((u64)d << 32) | (unsigned)(c - c0);
+        if (k < k1) {
+            k2 = k1;
+            k1 = k;
+        } else if (k < k2)
+            k2 = k;
+    }
+    const u64 best = shfl_min_u64(k1);
+    const u64 second = shfl_min_u64(k1 == best && best != none ? k2 : k1);
+    if (lane == 0) {
+        const int db = (int)(best >> 32), ds = (int)(second >> 32);
+        bd[a] = (uint16_t)db;
+        sd[a] = (uint16_t)ds;
+        bi[a] = (best == none || db >= 256) ? -1 : idx[c0 + (int)(best & 0xFFFFFFFFull)];
+        si[a] = (second == none || ds >= 256) ? -1 : idx[c0 + (int)(second & 0xFFFFFFFFull)];
+    }
+}
+
+__global__ void k_distance(const uint4* __restrict__ a, const uint4* __restrict__ b, int n, uint16_t* __restrict__ d) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    d[i] = (uint16_t)hamming256(a[2 * (size_t)i], a[2 * (size_t)i + 1], b[2 * (size_t)i], b[2 * (size_t)i + 1]);
+}
+
+// ------------------------------------------------------------------------------------------------ K9/K10 stereo
+__device__ __forceinline__ int reflect101_i(int p, int len) {
+    while (p < 0 || p >= len) p = p < 0 ? -p : 2 * len - 2 - p;
+    return p;
+}
+
+// One warp per left keypoint. Candidate scan: every right keypoint whose row band [floor(y-r), ceil(y+r)],
+// r = 2*scale[octave], contains (int)vL, octave within +-1, uR in [uL-maxD, uL-minD]; best = strict '<' from TH_HIGH in
+// ascending right index (packed (dist, iR) minimum). Then the 11-shift SAD sweep on the un-blurred pyramids.
+__global__ void __launch_bounds__(256) k_stereo_match(const DevPlan* __restrict__ P, const orbx_kp* __restrict__ kL,
+                                                      const uint8_t* __restrict__ dL, const int* __restrict__ nL,
+                                                      const uint8_t* __restrict__ pyrL, const orbx_kp* __restrict__ kR,
+                                                      const uint8_t* __restrict__ dR, const int* __restrict__ nR,
+                                                      const uint8_t* __restrict__ pyrR, float mbf, float minD, float maxD,
+                                                      float* __restrict__ uRight, float* __restrict__ depth,
+                                                      int* __restrict__ sad, int outStride) {
+    const int lane = threadIdx.x & 31;
+    const int iL = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int f = blockIdx.y;
+    const int NL = nL[f], NR = nR[f];
+    if (iL >= NL) return;
+    const long long kb = (long long)f * P->selStride;
+    const long long ob = (long long)f * outStride;
+    if (lane == 0) {
+        uRight[ob + iL] = -1.0f;
+        depth[ob + iL] = -1.0f;
+        sad[kb + iL] = -1;
+    }
+    const orbx_kp kp = kL[kb + iL];
+    const int levelL = kp.octave;
+    const float vL = kp.y, uL = kp.x;
+    const int row = (int)vL;
+    const float minU = __fsub_rn(uL, maxD), maxU = __fsub_rn(uL, minD);
+    if (maxU < 0) return;
+    const uint4* qd = (const uint4*)(dL + (kb + iL) * 32);
+    const uint4 q0 = qd[0], q1 = qd[1];
+    u64 best = ((u64)100 << 32) | 0xFFFFFFFFull;  // ORBmatcher::TH_HIGH
+    for (int iR = lane; iR < NR; iR += 32) {
+        const orbx_kp r = kR[kb + iR];
+        if (r.octave < levelL - 1 || r.octave > levelL + 1) continue;
+        const float rad = __fmul_rn(2.0f, P->lv[r.octave].scale);
+        const int maxr = (int)ceilf(__fadd_rn(r.y, rad)), minr = (int)floorf(__fsub_rn(r.y, rad));
+        if (row < minr || row > maxr) continue;
+        if (!(r.x >= minU && r.x <= maxU)) continue;
+        const uint4* td = (const uint4*)(dR + (kb + iR) * 32);
+        const int d = hamming256(q0, q1, td[0], td[1]);
+        const u64 k = ((u64)d << 32) | (unsigned)iR;
+        best = k < best ? k : best;
+    }
+    best = shfl_min_u64(best);
+    const int bestDist = (int)(best >> 32);
+    if (bestDist >= 75 || (best & 0xFFFFFFFFull) == 0xFFFFFFFFull) return;  // thOrbDist = (TH_HIGH+TH_LOW)/2
+    const int bestIdxR = (int)(best & 0xFFFFFFFFull);
+
+    const LevelGeo& G = P->lv[levelL];
+    const float uR0 = kR[kb + bestIdxR].x;
+    const float sfac = __fdiv_rn(1.0f, G.scale);  // mvInvScaleFactors[octave] = 1.0f / mvScaleFactor[octave]
+    const float scaleduL = roundf(__fmul_rn(kp.x, sfac));
+    const float scaledvL = roundf(__fmul_rn(kp.y, sfac));
+    const float scaleduR0 = roundf(__fmul_rn(uR0, sfac));
+    const int w = 5, L = 5;
+    const float iniu = scaleduR0 + L - w, endu = scaleduR0 + L + w + 1;
+    if (iniu < 0 || endu >= (float)G.w) return;
+    const int cy = (int)scaledvL, cxL = (int)scaleduL, cxR = (int)scaleduR0;
+    const uint8_t* IL = pyrL + G.pyrOff + (long long)f * G.frameStride;
+    const uint8_t* IR = pyrR + G.pyrOff + (long long)f * G.frameStride;
+    const int cL = IL[(long long)cy * G.pitch + cxL];
+    int acc[11];
+#pragma unroll
+    for (int s = 0; s < 11; s++) acc[s] = 0;
+    for (int p = lane; p < 121; p += 32) {
+        const int dy = p / 11 - w, dx = p % 11 - w;
+        const int yy = min(max(cy + dy, 0), G.h - 1);
+        const int a = IL[(long long)yy * G.pitch + cxL + dx] - cL;
+        const uint8_t* rrow = IR + (long long)yy * G.pitch;
+        const uint8_t* crow = IR + (long long)cy * G.pitch;
+#pragma unroll
+        for (int s = 0; s < 11; s++) {
+            const int inc = s - L;
+            const int cR = crow[reflect101_i(cxR + inc, G.w)];
+            const int b = rrow[reflect101_i(cxR + inc + dx, G.w)] - cR;
+            acc[s] += abs(a - b);
+        }
+    }
+#pragma unroll
+    for (int s = 0; s < 11; s++)
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) acc[s] += __shfl_xor_sync(0xffffffffu, acc[s], o);
+    if (lane != 0) return;
+    int bestSad = 0x7fffffff, bestinc = 0;
+#pragma unroll
+    for (int s = 0; s < 11; s++)
+        if (acc[s] < bestSad) {
+            bestSad = acc[s];
+            bestinc = s - L;
+        }
+    if (bestinc == -L || bestinc == L) return;
+    float dist1 = 0, dist2 = 0, dist3 = 0;
+#pragma unroll
+    for (int s = 1; s < 10; s++)
+        if (s - L == bestinc) {
+            dist1 = (float)acc[s - 1];
+            dist2 = (float)acc[s];
+            dist3 = (float)acc[s + 1];
+        }
+    const float deltaR = __fdiv_rn(__fsub_rn(dist1, dist3),
+                                   __fmul_rn(2.0f, __fsub_rn(__fadd_rn(dist1, dist3), __fmul_rn(2.0f, dist2))));
+    if (deltaR < -1 || deltaR > 1) return;  // NaN (0/0) passes, as in the reference; rejected below by the disparity test
+    float bestuR = __fmul_rn(G.scale, __fadd_rn(__fadd_rn(scaleduR0, (float)bestinc), deltaR));
+    float disparity = __fsub_rn(uL, bestuR);
+    if (disparity >= minD && disparity < maxD) {
+        if (disparity <= 0) {
+            disparity = 0.01f;
+            bestuR = (float)((double)uL - 0.01);
+        }
+        depth[ob + iL] = __fdiv_rn(mbf, disparity);
+        uRight[ob + iL] = bestuR;
+        sad[kb + iL] = bestSad;
+    }
+}
+
+// One CTA per frame: sort accepted (SAD, iL), median = element size/2, threshold 1.5f*1.4f*median, drop SAD >= it.
+__global__ void __launch_bounds__(1024) k_stereo_cut(const DevPlan* __restrict__ P, const int* __restrict__ nL,
+                                                     const int* __restrict__ sad, float* __restrict__ uRight,
+                                                     float* __restrict__ depth, int outStride, int P2) {
+    extern __shared__ __align__(16) uint8_t cut_smem[];
+    u64* buf = (u64*)cut_smem;
+    __shared__ int cnt;
+    const int f = blockIdx.x, tid = threadIdx.x;
+    const int N = nL[f];
+    const long long kb = (long long)f * P->selStride, ob = (long long)f * outStride;
+    if (tid == 0) cnt = 0;
+    for (int i = tid; i < P2; i += blockDim.x) buf[i] = ~0ull;
+    __syncthreads();
+    for (int i = tid; i < N; i += blockDim.x) {
+        const int s = sad[kb + i];
+        if (s >= 0) buf[atomicAdd(&cnt, 1)] = ((u64)(unsigned)s << 32) | (unsigned)i;
+    }
+    __syncthreads();
+    const int m = cnt;
+    if (m == 0) return;  // the reference indexes an empty vector here (UB); nothing to cut
+    int p2 = 1;
+    while (p2 < m) p2 <<= 1;
+    for (int k = 2; k <= p2; k <<= 1)
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int i = tid; i < p2; i += blockDim.x) {
+                const int ixj = i ^ j;
+                if (ixj > i) {
+                    const bool up = ((i & k) == 0);
+                    const u64 x = buf[i], y = buf[ixj];
+                    if ((x > y) == up) {
+                        buf[i] = y;
+                        buf[ixj] = x;
+                    }
+                }
+            }
+            __syncthreads();
+        }
+    const float median = (float)(int)(buf[m / 2] >> 32);
+    const float thDist = __fmul_rn(__fmul_rn(1.5f, 1.4f), median);
+    for (int i = tid; i < m; i += blockDim.x) {
+        const int s = (int)(buf[i] >> 32), il = (int)(buf[i] & 0xFFFFFFFFull);
+        if (!((float)s < thDist)) {
+            uRight[ob + il] = -1.0f;
+            depth[ob + il] = -1.0f;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ matcher handle
+struct orbm_handle {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    int inSpace = ORBX_MEM_HOST, outSpace = ORBX_MEM_HOST;
+    uint8_t* dTrain = nullptr; size_t trainCap = 0; int nTrain = 0; bool trainAdopted = false;
+    uint8_t* dQ = nullptr; size_t qCap = 0;
+    uint8_t* dB = nullptr; size_t bCap = 0;
+    int4* dPartial = nullptr; size_t partialCap = 0;
+    int32_t* dI1 = nullptr; int32_t* dI2 = nullptr; uint16_t* dD1 = nullptr; uint16_t* dD2 = nullptr; size_t outCap = 0;
+    int* dOff = nullptr; size_t offCap = 0;
+    int* dIdx = nullptr; size_t idxCap = 0;
+    uint8_t* dSkip = nullptr; size_t skipCap = 0;
+    int smCount = 148;
+    int64_t launches = 0;
+};
+
+template <typename T>
+static int ensure(T*& p, size_t& cap, size_t need) {
+    if (need <= cap) return ORBX_OK;
+    cudaFree(p);
+    p = nullptr;
+    cap = 0;
+    CK(cudaMalloc(&p, need * sizeof(T)));
+    cap = need;
+    return ORBX_OK;
+}
+
+extern "C" int orbm_create(int device, orbm_t** out) {
+    if (!out) FAIL(ORBX_EINVAL, "null argument");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        FAIL(ORBX_ECUDA, "no CUDA device: liborbx has no CPU path");
+    }
+    if (device < 0 || device >= ndev) FAIL(ORBX_EINVAL, "device %d out of range", device);
+    CK(cudaSetDevice(device));
+    orbm_handle* m = new orbm_handle();
+    m->device = device;
+    cudaError_t e = cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking);
+    if (e != cudaSuccess) {
+        delete m;
+        FAIL(ORBX_ECUDA, "cudaStreamCreate: %s", cudaGetErrorString(e));
+    }
+    cudaDeviceGetAttribute(&m->smCount, cudaDevAttrMultiProcessorCount, device);
+    *out = m;
+    return ORBX_OK;
+}
+
+extern "C" int orbm_destroy(orbm_t* m) {
+    if (!m) return ORBX_OK;
+    cudaSetDevice(m->device);
+    cudaStreamSynchronize(m->stream);
+    if (!m->trainAdopted) cudaFree(m->dTrain);
+    cudaFree(m->dQ); cudaFree(m->dB); cudaFree(m->dPartial); cudaFree(m->dI1); cudaFree(m->dI2); cudaFree(m->dD1);
+    cudaFree(m->dD2); cudaFree(m->dOff); cudaFree(m->dIdx); cudaFree(m->dSkip);
+    cudaStreamDestroy(m->stream);
+    delete m;
+    return ORBX_OK;
+}
+
+extern "C" int orbm_set_memory_space(orbm_t* m, int in, int out) {
+    if (!m || in < 0 || in > 1 || out < 0 || out > 1) FAIL(ORBX_EINVAL, "bad memory space");
+    m->inSpace = in;
+    m->outSpace = out;
+    return ORBX_OK;
+}
+extern "C" int orbm_stream(orbm_t* m, void** s) {
+    if (!m || !s) FAIL(ORBX_EINVAL, "null argument");
+    *s = (void*)m->stream;
+    return ORBX_OK;
+}
+extern "C" int64_t orbm_launch_count(orbm_t* m) { return m ? m->launches : 0; }
+
+extern "C" int orbm_set_train(orbm_t* m, const uint8_t* t, int nt) {
+    if (!m || !t || nt < 1) FAIL(ORBX_EINVAL, "bad argument");
+    CK(cudaSetDevice(m->device));
+    if (m->inSpace == ORBX_MEM_DEVICE) {
+        if (((uintptr_t)t & 15) != 0) FAIL(ORBX_EINVAL, "device descriptor matrix must be 16-byte aligned");
+        if (!m->trainAdopted) cudaFree(m->dTrain);
+        m->dTrain = (uint8_t*)t;
+        m->trainCap = 0;
+        m->trainAdopted = true;
+    } else {
+        if (m->trainAdopted) {
+            m->dTrain = nullptr;
+            m->trainCap = 0;
+            m->trainAdopted = false;
+        }
+        int rc = ensure(m->dTrain, m->trainCap, (size_t)nt * 32);
+        if (rc) return rc;
+        CK(cudaMemcpyAsync(m->dTrain, t, (size_t)nt * 32, cudaMemcpyHostToDevice, m->stream));
+    }
+    m->nTrain = nt;
+    return ORBX_OK;
+}
+
+// stage a caller array on the device if it is host memory
+template <typename T>
+static int stage_in(orbm_handle* m, const T* src, size_t count, T*& buf, size_t& cap, const T** dev) {
+    if (m->inSpace == ORBX_MEM_DEVICE) {
+        *dev = src;
+        return ORBX_OK;
+    }
+    int rc = ensure(buf, cap, count);
+    if (rc) return rc;
+    CK(cudaMemcpyAsync(buf, src, count * sizeof(T), cudaMemcpyHostToDevice, m->stream));
+    *dev = buf;
+    return ORBX_OK;
+}
+
+static int ensure_out(orbm_handle* m, size_t nq) {
+    if (nq <= m->outCap) return ORBX_OK;
+    cudaFree(m->dI1); cudaFree(m->dI2); cudaFree(m->dD1); cudaFree(m->dD2);
+    m->dI1 = m->dI2 = nullptr; m->dD1 = m->dD2 = nullptr; m->outCap = 0;
+    CK(cudaMalloc(&m->dI1, nq * 4));
+    CK(cudaMalloc(&m->dI2, nq * 4));
+    CK(cudaMalloc(&m->dD1, nq * 2));
+    CK(cudaMalloc(&m->dD2, nq * 2));
+    m->outCap = nq;
+    return ORBX_OK;
+}
+
+extern "C" int orbm_knn2(orbm_t* m, const uint8_t* q, int nq, const uint8_t* t, int nt, int32_t* i1, uint16_t* d1,
+                         uint16_t* d2) {
+    if (!m || !q || nq < 0 || !i1 || !d1 || !d2) FAIL(ORBX_EINVAL, "bad argument");
+    if (nq == 0) return ORBX_OK;
+    CK(cudaSetDevice(m->device));
+    int rc;
+    if (t) {
+        if ((rc = orbm_set_train(m, t, nt))) return rc;
+    } else if (!m->dTrain)
+        FAIL(ORBX_ESTATE, "no train set: pass t or call orbm_set_train first");
+    nt = m->nTrain;
+    const uint8_t* dq = nullptr;
+    if ((rc = stage_in(m, q, (size_t)nq * 32, m->dQ, m->qCap, &dq))) return rc;
+    if (((uintptr_t)dq & 15) != 0) FAIL(ORBX_EINVAL, "device descriptor matrix must be 16-byte aligned");
+    int32_t* o1 = i1; uint16_t* od1 = d1; uint16_t* od2 = d2;
+    if (m->outSpace == ORBX_MEM_HOST) {
+        if ((rc = ensure_out(m, nq))) return rc;
+        o1 = m->dI1; od1 = m->dD1; od2 = m->dD2;
+    }
+    const int qblocks = (nq + KNN_THREADS * KNN_QPT - 1) / (KNN_THREADS * KNN_QPT);
+    // split the train set so that the grid fills the machine for small query counts
+    int splits = 1;
+    const int target = m->smCount * 8;
+    while (qblocks * splits < target && (nt / (splits * 2)) >= 4 * KNN_TILE) splits *= 2;
+    int chunk = (nt + splits - 1) / splits;
+    chunk = (chunk + KNN_TILE - 1) / KNN_TILE * KNN_TILE;
+    splits = (nt + chunk - 1) / chunk;
+    int4* partial = nullptr;
+    if (splits > 1) {
+        if ((rc = ensure(m->dPartial, m->partialCap, (size_t)splits * nq))) return rc;
+        partial = m->dPartial;
+    }
+    k_knn2<<<dim3(qblocks, splits), KNN_THREADS, 0, m->stream>>>((const uint4*)dq, nq, (const uint4*)m->dTrain, nt, chunk,
+                                                                 partial, o1, od1, od2);
+    m->launches++;
+    if (splits > 1) {
+        k_knn2_merge<<<(nq + 255) / 256, 256, 0, m->stream>>>(partial, nq, splits, o1, od1, od2);
+        m->launches++;
+    }
+    CK(cudaGetLastError());
+    if (m->outSpace == ORBX_MEM_HOST) {
+        CK(cudaMemcpyAsync(i1, o1, (size_t)nq * 4, cudaMemcpyDeviceToHost, m->stream));
+        CK(cudaMemcpyAsync(d1, od1, (size_t)nq * 2, cudaMemcpyDeviceToHost, m->stream));
+        CK(cudaMemcpyAsync(d2, od2, (size_t)nq * 2, cudaMemcpyDeviceToHost, m->stream));
+    }
+    CK(cudaStreamSynchronize(m->stream));
+    return ORBX_OK;
+}
+
+extern "C" int orbm_window_search(orbm_t* m, const uint8_t* q, int nq, const int32_t* cand_off, const int32_t* cand_idx,
+                                  const uint8_t* cand_skip, const uint8_t* t, int nt, int32_t* best_idx, uint16_t* best_d,
+                                  uint16_t* second_d, int32_t* second_idx) {
+    if (!m || !q || nq < 0 || !cand_off || !best_idx || !best_d || !second_d || !second_idx) FAIL(ORBX_EINVAL, "bad argument");
+    if (nq == 0) return ORBX_OK;
+    CK(cudaSetDevice(m->device));
+    int rc;
+    if (t) {
+        if ((rc = orbm_set_train(m, t, nt))) return rc;
+    } else if (!m->dTrain)
+        FAIL(ORBX_ESTATE, "no train set");
+    const uint8_t* dq = nullptr;
+    if ((rc = stage_in(m, q, (size_t)nq * 32, m->dQ, m->qCap, &dq))) return rc;
+    const int* doff = nullptr;
+    const int* didx = nullptr;
+    const uint8_t* dskip = nullptr;
+    int ncand = 0;
+    if (m->inSpace == ORBX_MEM_HOST) {
+        ncand = cand_off[nq];
+        for (int a = 0; a < nq; a++)
+            if (cand_off[a] > cand_off[a + 1] || cand_off[a] < 0) FAIL(ORBX_EINVAL, "cand_off must be non-decreasing");
+        if (ncand > 0 && !cand_idx) FAIL(ORBX_EINVAL, "null cand_idx");
+        for (int c = 0; c < ncand; c++)
+            if (cand_idx[c] < 0 || cand_idx[c] >= m->nTrain) FAIL(ORBX_EINVAL, "candidate index %d out of range", cand_idx[c]);
+    } else {
+        CK(cudaMemcpyAsync(&ncand, cand_off + nq, sizeof(int), cudaMemcpyDeviceToHost, m->stream));
+        CK(cudaStreamSynchronize(m->stream));
+    }
+    if ((rc = stage_in(m, cand_off, (size_t)nq + 1, m->dOff, m->offCap, &doff))) return rc;
+    if (ncand > 0) {
+        if ((rc = stage_in(m, cand_idx, (size_t)ncand, m->dIdx, m->idxCap, &didx))) return rc;
+        if (cand_skip && (rc = stage_in(m, cand_skip, (size_t)ncand, m->dSkip, m->skipCap, &dskip))) return rc;
+    }
+    int32_t* o1 = best_idx; int32_t* o2 = second_idx; uint16_t* od1 = best_d; uint16_t* od2 = second_d;
+    if (m->outSpace == ORBX_MEM_HOST) {
+        if ((rc = ensure_out(m, nq))) return rc;
+        o1 = m->dI1; o2 = m->dI2; od1 = m->dD1; od2 = m->dD2;
+    }
+    k_window_search<<<(nq + 7) / 8, 256, 0, m->stream>>>((const uint4*)dq, nq, doff, didx, dskip, (const uint4*)m->dTrain, o1,
+                                                         od1, od2, o2);
+    m->launches++;
+    CK(cudaGetLastError());
+    if (m->outSpace == ORBX_MEM_HOST) {
+        CK(cudaMemcpyAsync(best_idx, o1, (size_t)nq * 4, cudaMemcpyDeviceToHost, m->stream));
+        CK(cudaMemcpyAsync(second_idx, o2, (size_t)nq * 4, cudaMemcpyDeviceToHost, m->stream));
+        CK(cudaMemcpyAsync(best_d, od1, (size_t)nq * 2, cudaMemcpyDeviceToHost, m->stream));
+        CK(cudaMemcpyAsync(second_d, od2, (size_t)nq * 2, cudaMemcpyDeviceToHost, m->stream));
+    }
+    CK(cudaStreamSynchronize(m->stream));
+    return ORBX_OK;
+}
+
+extern "C" int orbm_distance(orbm_t* m, const uint8_t* a, const uint8_t* b, int n, uint16_t* d) {
+    if (!m || !a || !b || n < 0 || !d) FAIL(ORBX_EINVAL, "bad argument");
+    if (n == 0) return ORBX_OK;
+    CK(cudaSetDevice(m->device));
+    int rc;
+    const uint8_t* da = nullptr;
+    const uint8_t* db = nullptr;
+    if ((rc = stage_in(m, a, (size_t)n * 32, m->dQ, m->qCap, &da))) return rc;
+    if ((rc = stage_in(m, b, (size_t)n * 32, m->dB, m->bCap, &db))) return rc;
+    uint16_t* od = d;
+    if (m->outSpace == ORBX_MEM_HOST) {
+        if ((rc = ensure_out(m, n))) return rc;
+        od = m->dD1;
+    }
+    k_distance<<<(n + 255) / 256, 256, 0, m->stream>>>((const uint4*)da, (const uint4*)db, n, od);
+    m->launches++;
+    CK(cudaGetLastError());
+    if (m->outSpace == ORBX_MEM_HOST) CK(cudaMemcpyAsync(d, od, (size_t)n * 2, cudaMemcpyDeviceToHost, m->stream));
+    CK(cudaStreamSynchronize(m->stream));
+    return ORBX_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ stereo ABI
+struct StereoScratch {
+    int* dSad = nullptr; float* dU = nullptr; float* dZ = nullptr; size_t cap = 0; int device = -1;
+};
+static thread_local StereoScratch g_ss;
+
+extern "C" int orbx_stereo_match_batch(orbx_t* left, orbx_t* right, float mbf, float minD, float maxD, float* uRight,
+                                       float* depth, int cap) {
+    if (!left || !right || !uRight || !depth || cap < 1) FAIL(ORBX_EINVAL, "bad argument");
+    OrbxView A = orbx_view((orbx_handle*)left), B = orbx_view((orbx_handle*)right);
+    if (!A.lastBatch || A.lastBatch != B.lastBatch) FAIL(ORBX_ESTATE, "left and right must hold the same extracted batch");
+    if (A.device != B.device) FAIL(ORBX_EINVAL, "left and right extractors must be on the same device");
+    if (A.hp->nlevels != B.hp->nlevels || A.hp->selStride != B.hp->selStride || A.hp->lv[0].w != B.hp->lv[0].w ||
+        A.hp->lv[0].h != B.hp->lv[0].h)
+        FAIL(ORBX_EINVAL, "left and right extractors must share parameters and image shape");
+    CK(cudaSetDevice(A.device));
+    const int batch = A.lastBatch, stride = A.hp->selStride;
+    const size_t need = (size_t)batch * stride;
+    if (g_ss.device != A.device || g_ss.cap < need) {
+        cudaFree(g_ss.dSad); cudaFree(g_ss.dU); cudaFree(g_ss.dZ);
+        g_ss = StereoScratch();
+        CK(cudaMalloc(&g_ss.dSad, need * 4));
+        CK(cudaMalloc(&g_ss.dU, need * 4));
+        CK(cudaMalloc(&g_ss.dZ, need * 4));
+        g_ss.cap = need;
+        g_ss.device = A.device;
+    }
+    cudaStream_t st = A.stream;
+    CK(cudaStreamSynchronize(B.stream));  // right extractor's results must be complete (its extract call already synced)
+    float* oU = A.outSpace == ORBX_MEM_DEVICE ? uRight : g_ss.dU;
+    float* oZ = A.outSpace == ORBX_MEM_DEVICE ? depth : g_ss.dZ;
+    const int oStride = A.outSpace == ORBX_MEM_DEVICE ? cap : stride;
+    int maxN = 0;
+    for (int f = 0; f < batch; f++) maxN = std::max(maxN, A.hCounts[f]);
+    if (maxN > cap) FAIL(ORBX_ECAP, "cap_per_frame %d < %d left keypoints", cap, maxN);
+    if (maxN == 0) maxN = 1;
+    k_stereo_match<<<dim3((maxN + 7) / 8, batch), 256, 0, st>>>(A.dPlan, A.dKps, A.dDesc, A.dNOut, A.dPyr, B.dKps, B.dDesc,
+                                                               B.dNOut, B.dPyr, mbf, minD, maxD, oU, oZ, g_ss.dSad, oStride);
+    int P2 = 1;
+    while (P2 < maxN) P2 <<= 1;
+    k_stereo_cut<<<batch, 1024, (size_t)P2 * 8, st>>>(A.dPlan, A.dNOut, g_ss.dSad, oU, oZ, oStride, P2);
+    orbx_count_launch((orbx_handle*)left, 2);
+    CK(cudaGetLastError());
+    if (A.outSpace == ORBX_MEM_HOST) {
+        const int cols = std::min(cap, stride);
+        CK(cudaMemcpy2DAsync(uRight, (size_t)cap * 4, oU, (size_t)stride * 4, (size_t)cols * 4, batch, cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpy2DAsync(depth, (size_t)cap * 4, oZ, (size_t)stride * 4, (size_t)cols * 4, batch, cudaMemcpyDeviceToHost, st));
+    }
+    CK(cudaStreamSynchronize(st));
+    return ORBX_OK;
+}
+
+extern "C" int orbx_stereo_match(orbx_t* left, orbx_t* right, int frame, float mbf, float minD, float maxD, float* uRight,
+                                 float* depth) {
+    if (!left || !right) FAIL(ORBX_EINVAL, "null handle");
+    OrbxView A = orbx_view((orbx_handle*)left);
+    if (frame < 0 || frame >= A.lastBatch) FAIL(ORBX_ESTATE, "frame %d not in the last extracted batch", frame);
+    if (A.lastBatch == 1) return orbx_stereo_match_batch(left, right, mbf, minD, maxD, uRight, depth, std::max(A.hCounts[0], 1));
+    // general case: run the batch and hand back one row (host outputs only)
+    if (A.outSpace != ORBX_MEM_HOST) FAIL(ORBX_EINVAL, "single-frame stereo on a multi-frame batch needs host outputs");
+    const int stride = A.hp->selStride;
+    std::vector<float> u((size_t)A.lastBatch * stride), z((size_t)A.lastBatch * stride);
+    int rc = orbx_stereo_match_batch(left, right, mbf, minD, maxD, u.data(), z.data(), stride);
+    if (rc) return rc;
+    const int n = A.hCounts[frame];
+    std::copy(u.begin() + (size_t)frame * stride, u.begin() + (size_t)frame * stride + n, uRight);
+    std::copy(z.begin() + (size_t)frame * stride, z.begin() + (size_t)frame * stride + n, depth);
+    return ORBX_OK;
+}

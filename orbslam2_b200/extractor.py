@@ -1,0 +1,206 @@
+"""Host-side mirror of ORB_SLAM2::ORBextractor (/root/reference/include/ORBextractor.h:45-112) over the C ABI.
+
+Same constructor arguments, same call shape (`extractor(image, mask) -> keypoints, descriptors`), same getters and the
+`mvImagePyramid` member; plus a batched call and device-memory I/O for torch CUDA tensors. All compute happens in
+liborbx.so's CUDA kernels — this file only marshals pointers.
+"""
+import ctypes as C
+import numpy as np
+
+from . import _lib
+
+KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"), ("response", "<f4"),
+                     ("octave", "<i4"), ("class_id", "<i4")])
+
+
+def _is_torch(x):
+    return type(x).__module__.startswith("torch")
+
+
+class ORBextractor:
+    HARRIS_SCORE, FAST_SCORE = 0, 1
+
+    def __init__(self, nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST, patchSize=31, halfPatchSize=15,
+                 edgeThreshold=19, device=0):
+        # the reference's yaml defaults: 0 means "use 31/15/19" (src/Tracking.cc:118-123)
+        patchSize = patchSize or 31
+        halfPatchSize = halfPatchSize or 15
+        edgeThreshold = edgeThreshold or 19
+        self._L = _lib.lib()
+        self.params = _lib.OrbxParams(nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST, patchSize, halfPatchSize,
+                                      edgeThreshold)
+        self._h = C.c_void_p()
+        _lib.check(self._L.orbx_create(C.byref(self.params), device, C.byref(self._h)))
+        self.device = device
+        n = nlevels
+        t = [np.zeros(n, np.float32) for _ in range(4)]
+        self.mnFeaturesPerLevel = np.zeros(n, np.int32)
+        self.umax = np.zeros(halfPatchSize + 1, np.int32)
+        _lib.check(self._L.orbx_tables(self._h, *[a.ctypes.data for a in t], self.mnFeaturesPerLevel.ctypes.data,
+                                       self.umax.ctypes.data))
+        self.mvScaleFactor, self.mvInvScaleFactor, self.mvLevelSigma2, self.mvInvLevelSigma2 = t
+        self._in_space = self._out_space = _lib.MEM_HOST
+        self._last = None
+
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            self._L.orbx_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # --- getters of the reference class ---------------------------------------------------------------------------
+    def GetLevels(self):
+        return self.params.nlevels
+
+    def GetScaleFactor(self):
+        return float(np.float64(np.float32(self.params.scaleFactor)))
+
+    def GetScaleFactors(self):
+        return self.mvScaleFactor.copy()
+
+    def GetInverseScaleFactors(self):
+        return self.mvInvScaleFactor.copy()
+
+    def GetScaleSigmaSquares(self):
+        return self.mvLevelSigma2.copy()
+
+    def GetInverseScaleSigmaSquares(self):
+        return self.mvInvLevelSigma2.copy()
+
+    # --- extraction ------------------------------------------------------------------------------------------------
+    def max_keypoints(self, w, h):
+        cap = C.c_int()
+        _lib.check(self._L.orbx_max_keypoints(self._h, w, h, C.byref(cap)))
+        return cap.value
+
+    def _set_space(self, i, o):
+        if (i, o) != (self._in_space, self._out_space):
+            _lib.check(self._L.orbx_set_memory_space(self._h, i, o))
+            self._in_space, self._out_space = i, o
+
+    def __call__(self, image, mask=None):
+        """operator()(image, mask, keypoints, descriptors): mask is ignored, as in the reference
+        (include/ORBextractor.h:57). Returns (keypoints [KP_DTYPE], descriptors [N,32] uint8); empty image -> empty."""
+        image = np.asarray(image)
+        if image.size == 0:
+            return np.zeros(0, KP_DTYPE), np.zeros((0, 32), np.uint8)
+        assert image.dtype == np.uint8 and image.ndim == 2, "CV_8UC1 image required"
+        k, d, n = self.extract_batch(image[None])
+        return k[0, :n[0]].copy(), d[0, :n[0]].copy()
+
+    def extract_batch(self, images, out=None):
+        """images: [B,H,W] uint8 numpy array (host, any row stride) or torch CUDA tensor (device).
+        Returns (kps [B,cap], desc [B,cap,32], n [B]) in the same memory space as the input (n always numpy)."""
+        if _is_torch(images):
+            return self._extract_batch_torch(images, out)
+        assert images.dtype == np.uint8 and images.ndim == 3
+        B, H, W = images.shape
+        if images.strides[2] != 1 or images.strides[1] < W or (B > 1 and images.strides[0] < images.strides[1] * H):
+            images = np.ascontiguousarray(images)
+        cap = self.max_keypoints(W, H)
+        if out is None:
+            out = (np.zeros((B, cap), KP_DTYPE), np.zeros((B, cap, 32), np.uint8))
+        kps, desc = out
+        n = np.zeros(B, np.int32)
+        self._set_space(_lib.MEM_HOST, _lib.MEM_HOST)
+        _lib.check(self._L.orbx_extract_batch(self._h, images.ctypes.data, B, W, H, images.strides[1], images.strides[0],
+                                              kps.ctypes.data, desc.ctypes.data, cap, n.ctypes.data))
+        self._last = (B, W, H)
+        return kps, desc, n
+
+    def _extract_batch_torch(self, images, out=None):
+        import torch
+        assert images.is_cuda and images.dtype == torch.uint8 and images.dim() == 3 and images.is_contiguous()
+        assert images.device.index == self.device
+        B, H, W = images.shape
+        cap = self.max_keypoints(W, H)
+        if out is None:
+            out = (torch.empty((B, cap, 7), dtype=torch.float32, device=images.device),
+                   torch.empty((B, cap, 32), dtype=torch.uint8, device=images.device))
+        kps, desc = out
+        n = np.zeros(B, np.int32)
+        self._set_space(_lib.MEM_DEVICE, _lib.MEM_DEVICE)
+        torch.cuda.current_stream(images.device).synchronize()
+        _lib.check(self._L.orbx_extract_batch(self._h, images.data_ptr(), B, W, H, W, W * H, kps.data_ptr(),
+                                              desc.data_ptr(), cap, n.ctypes.data))
+        self._last = (B, W, H)
+        return kps, desc, n
+
+    # --- mvImagePyramid ---------------------------------------------------------------------------------------------
+    def level_size(self, level):
+        w, h = C.c_int(), C.c_int()
+        _lib.check(self._L.orbx_level_size(self._h, level, C.byref(w), C.byref(h)))
+        return w.value, h.value
+
+    def pyramid_level(self, level, frame=0, with_border=False):
+        w, h = self.level_size(level)
+        e = self.params.edgeThreshold if with_border else 0
+        out = np.zeros((h + 2 * e, w + 2 * e), np.uint8)
+        _lib.check(self._L.orbx_pyramid_level(self._h, frame, level, out.ctypes.data, out.strides[0], int(with_border)))
+        return out
+
+    @property
+    def mvImagePyramid(self):
+        """The reference's public member: one un-blurred image per level (interior ROI of a padded buffer whose
+        19-px frame is BORDER_REFLECT_101, src/ORBextractor.cc:927-942). Fetched from the device on access."""
+        e = self.params.edgeThreshold
+        out = []
+        for l in range(self.params.nlevels):
+            padded = self.pyramid_level(l, 0, True)
+            out.append(padded[e:-e, e:-e])
+        return out
+
+    def GetImagePyramid(self):
+        return self.mvImagePyramid
+
+    def blurred_level(self, level, frame=0):
+        w, h = self.level_size(level)
+        out = np.zeros((h, w), np.uint8)
+        _lib.check(self._L.orbx_blurred_level(self._h, frame, level, out.ctypes.data, out.strides[0]))
+        return out
+
+    def candidates(self, level, frame=0):
+        w, h = self.level_size(level)
+        cap = w * h // 3 + 64
+        out = np.zeros((cap, 3), np.int32)
+        n = C.c_int()
+        _lib.check(self._L.orbx_candidates(self._h, frame, level, out.ctypes.data, cap, C.byref(n)))
+        return out[:n.value].copy()
+
+    # --- instrumentation --------------------------------------------------------------------------------------------
+    def cuda_stream(self):
+        s = C.c_void_p()
+        _lib.check(self._L.orbx_stream(self._h, C.byref(s)))
+        return s.value
+
+    def launch_count(self):
+        return int(self._L.orbx_launch_count(self._h))
+
+    def set_profiling(self, on):
+        _lib.check(self._L.orbx_set_profiling(self._h, int(on)))
+
+    def stage_ms(self):
+        ms = np.zeros(7, np.float32)
+        _lib.check(self._L.orbx_stage_ms(self._h, ms.ctypes.data))
+        return dict(zip(["ingest", "pyramid", "fast", "quadtree", "blur", "orient_desc", "egress"], ms.tolist()))
+
+
+def compute_stereo_matches(left, right, mbf, minD, maxD, frame=None):
+    """Frame::ComputeStereoMatches (src/Frame.cc:464-642) on the state resident in two extractors that have just
+    processed the left/right images. Returns (mvuRight, mvDepth) per left keypoint; frame=None -> all frames [B,cap]."""
+    L = left._L
+    B, W, H = left._last
+    cap = left.max_keypoints(W, H)
+    left._set_space(left._in_space, _lib.MEM_HOST)
+    if frame is None:
+        u = np.zeros((B, cap), np.float32); z = np.zeros((B, cap), np.float32)
+        _lib.check(L.orbx_stereo_match_batch(left._h, right._h, mbf, minD, maxD, u.ctypes.data, z.ctypes.data, cap))
+        return u, z
+    u = np.zeros(cap, np.float32); z = np.zeros(cap, np.float32)
+    _lib.check(L.orbx_stereo_match(left._h, right._h, frame, mbf, minD, maxD, u.ctypes.data, z.ctypes.data))
+    return u, z

@@ -1,0 +1,121 @@
+"""Host-side mirror of ORB_SLAM2::ORBmatcher's descriptor-distance surface (/root/reference/include/ORBmatcher.h:38-102)
+over the C ABI: DescriptorDistance, the brute-force 2-NN + ratio test and the windowed best/second-best scan that every
+ORBmatcher search loop runs. Geometric gating (projection, frustum, epipolar) stays with the caller,
+who passes candidate lists. All compute happens in liborbx.so's CUDA kernels."""
+import ctypes as C
+import numpy as np
+
+from . import _lib
+
+
+def _is_torch(x):
+    return type(x).__module__.startswith("torch")
+
+
+def _ptr(a):
+    return a.data_ptr() if _is_torch(a) else a.ctypes.data
+
+
+class ORBmatcher:
+    TH_LOW = 50       # src/ORBmatcher.cc:35-37
+    TH_HIGH = 100
+    HISTO_LENGTH = 30
+
+    def __init__(self, nnratio=0.6, checkOri=True, device=0):
+        self.mfNNratio = np.float32(nnratio)
+        self.mbCheckOrientation = checkOri
+        self._L = _lib.lib()
+        self._h = C.c_void_p()
+        _lib.check(self._L.orbm_create(device, C.byref(self._h)))
+        self.device = device
+        self._space = (_lib.MEM_HOST, _lib.MEM_HOST)
+
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            self._L.orbm_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _set_space(self, i, o):
+        if (i, o) != self._space:
+            _lib.check(self._L.orbm_set_memory_space(self._h, i, o))
+            self._space = (i, o)
+
+    def DescriptorDistance(self, a, b):
+        """Hamming distance of two 32-byte descriptors (or of N row pairs -> array)."""
+        a = np.ascontiguousarray(a, np.uint8).reshape(-1, 32); b = np.ascontiguousarray(b, np.uint8).reshape(-1, 32)
+        d = np.zeros(len(a), np.uint16)
+        self._set_space(_lib.MEM_HOST, _lib.MEM_HOST)
+        _lib.check(self._L.orbm_distance(self._h, a.ctypes.data, b.ctypes.data, len(a), d.ctypes.data))
+        return int(d[0]) if len(d) == 1 else d.astype(np.int32)
+
+    def set_train(self, t):
+        dev = _is_torch(t)
+        self._set_space(_lib.MEM_DEVICE if dev else _lib.MEM_HOST, self._space[1])
+        if not dev:
+            t = np.ascontiguousarray(t, np.uint8)
+        self._train = t  # keep alive
+        _lib.check(self._L.orbm_set_train(self._h, _ptr(t), int(t.shape[0])))
+
+    def knn2(self, q, t=None):
+        """(i1, d1, d2) per query; lowest train index wins ties; d2 counts multiplicity."""
+        if _is_torch(q):
+            import torch
+            nq = q.shape[0]
+            i1 = torch.empty(nq, dtype=torch.int32, device=q.device)
+            d1 = torch.empty(nq, dtype=torch.int16, device=q.device); d2 = torch.empty(nq, dtype=torch.int16, device=q.device)
+            self._set_space(_lib.MEM_DEVICE, _lib.MEM_DEVICE)
+            torch.cuda.current_stream(q.device).synchronize()
+            if t is not None:
+                self._train = t
+            _lib.check(self._L.orbm_knn2(self._h, q.data_ptr(), nq, 0 if t is None else t.data_ptr(),
+                                         0 if t is None else t.shape[0], i1.data_ptr(), d1.data_ptr(), d2.data_ptr()))
+            return i1, d1, d2
+        q = np.ascontiguousarray(q, np.uint8)
+        nq = len(q)
+        i1 = np.zeros(nq, np.int32); d1 = np.zeros(nq, np.uint16); d2 = np.zeros(nq, np.uint16)
+        self._set_space(_lib.MEM_HOST, _lib.MEM_HOST)
+        if t is not None:
+            t = np.ascontiguousarray(t, np.uint8)
+        _lib.check(self._L.orbm_knn2(self._h, q.ctypes.data, nq, None if t is None else t.ctypes.data,
+                                     0 if t is None else len(t), i1.ctypes.data, d1.ctypes.data, d2.ctypes.data))
+        return i1, d1, d2
+
+    def match_ratio(self, q, t=None, th=None, ratio=None):
+        """The SearchByFboW acceptance rule on a brute-force candidate set (src/ORBmatcher.cc:225-229):
+        match iff d1 <= th and (float)d1 < ratio*(float)d2. Returns (i1 with -1 for rejects, d1, d2)."""
+        th = self.TH_LOW if th is None else th
+        ratio = self.mfNNratio if ratio is None else np.float32(ratio)
+        i1, d1, d2 = self.knn2(q, t)
+        ok = (d1 <= th) & (d1.astype(np.float32) < ratio * d2.astype(np.float32))
+        return np.where(ok, i1, -1).astype(np.int32), d1, d2
+
+    def window_search(self, q, cand_off, cand_idx, t=None, cand_skip=None):
+        """Per query: scan candidates cand_idx[cand_off[a]:cand_off[a+1]] in list order ->
+        (best_idx, best_d, second_d, second_idx); -1 / 256 when absent."""
+        q = np.ascontiguousarray(q, np.uint8)
+        off = np.ascontiguousarray(cand_off, np.int32); idx = np.ascontiguousarray(cand_idx, np.int32)
+        sk = None if cand_skip is None else np.ascontiguousarray(cand_skip, np.uint8)
+        nq = len(q)
+        bi = np.zeros(nq, np.int32); si = np.zeros(nq, np.int32); bd = np.zeros(nq, np.uint16); sd = np.zeros(nq, np.uint16)
+        self._set_space(_lib.MEM_HOST, _lib.MEM_HOST)
+        if t is not None:
+            t = np.ascontiguousarray(t, np.uint8)
+        _lib.check(self._L.orbm_window_search(self._h, q.ctypes.data, nq, off.ctypes.data, idx.ctypes.data if idx.size else None,
+                                              None if sk is None else sk.ctypes.data, None if t is None else t.ctypes.data,
+                                              0 if t is None else len(t), bi.ctypes.data, bd.ctypes.data, sd.ctypes.data,
+                                              si.ctypes.data))
+        return bi, bd, sd, si
+
+    def cuda_stream(self):
+        s = C.c_void_p()
+        _lib.check(self._L.orbm_stream(self._h, C.byref(s)))
+        return s.value
+
+    def launch_count(self):
+        return int(self._L.orbm_launch_count(self._h))

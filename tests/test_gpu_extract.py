@@ -1,0 +1,128 @@
+"""GPU parity: liborbx (through the C ABI / Python mirror) vs the CPU oracle, stage by stage.
+
+Bars (BASELINE.json north_star): pyramid + blurred pixels, FAST candidates/scores and the selected keypoint set
+bit-exact; coordinates within 1e-4 px, angles within 1e-2 deg, >= 99.99 % of descriptors bit-identical."""
+import numpy as np
+import pytest
+
+from oracle_lib import Oracle, canonical, TUM1
+from orbslam2_b200.synth import synth_image
+
+pytestmark = pytest.mark.gpu
+
+SHAPES = [(640, 480, 1000), (752, 480, 1200), (1241, 376, 2000)]
+
+
+@pytest.fixture(scope="module")
+def ob():
+    import orbslam2_b200
+    return orbslam2_b200
+
+
+def _params(nf):
+    p = dict(TUM1); p["nfeatures"] = nf
+    return p
+
+
+def _compare_frame(ex, orc, img, frame=0, desc_stats=None, kps=None, desc=None):
+    p = orc.params
+    ko, do = orc.extract(img, 4 * p["nfeatures"])
+    for l in range(p["nlevels"]):
+        assert ex.level_size(l) == orc.level_size(l)
+        assert np.array_equal(ex.pyramid_level(l, frame, True), orc.level(l, True)), f"pyramid level {l}"
+        assert np.array_equal(ex.blurred_level(l, frame), orc.blurred(l)), f"blurred level {l}"
+        cg = ex.candidates(l, frame); co = orc.candidates(l)
+        cg = cg[np.lexsort((cg[:, 0], cg[:, 1]))]; co = co[np.lexsort((co[:, 0], co[:, 1]))]
+        assert np.array_equal(cg, co), f"FAST candidates level {l}: {len(cg)} vs {len(co)}"
+    ko, do = canonical(ko, do)
+    assert len(kps) == len(ko)
+    # GPU output is already canonical (level, y, x)
+    assert np.array_equal(kps["octave"], ko["octave"])
+    assert np.array_equal(kps["response"], ko["response"]) and np.array_equal(kps["size"], ko["size"])
+    assert np.array_equal(kps["class_id"], ko["class_id"])
+    assert np.abs(kps["x"] - ko["x"]).max() <= 1e-4 and np.abs(kps["y"] - ko["y"]).max() <= 1e-4
+    assert np.abs(kps["angle"] - ko["angle"]).max() <= 1e-2
+    same = (desc == do).all(axis=1)
+    if desc_stats is not None:
+        desc_stats[0] += int(same.sum()); desc_stats[1] += len(same)
+    return same
+
+
+@pytest.mark.parametrize("w,h,nf", SHAPES)
+def test_single_frame_all_stages(ob, w, h, nf):
+    p = _params(nf)
+    ex = ob.ORBextractor(**p); orc = Oracle(**p)
+    stats = [0, 0]
+    for seed in (0, 1):
+        img = synth_image(w, h, seed)
+        kps, desc = ex(img)
+        _compare_frame(ex, orc, img, 0, stats, kps, desc)
+    assert stats[0] >= 0.9999 * stats[1], f"descriptors identical {stats[0]}/{stats[1]}"
+    ex.close()
+
+
+def test_batch_matches_single(ob):
+    p = _params(1000)
+    ex = ob.ORBextractor(**p); orc = Oracle(**p)
+    imgs = np.stack([synth_image(640, 480, s) for s in range(6)])
+    kps, desc, n = ex.extract_batch(imgs)
+    stats = [0, 0]
+    for f in (0, 3, 5):
+        _compare_frame(ex, orc, imgs[f], f, stats, kps[f, :n[f]], desc[f, :n[f]])
+    assert stats[0] >= 0.9999 * stats[1]
+    # the same frames one at a time give identical bytes
+    for f in range(6):
+        k1, d1 = ex(imgs[f])
+        assert np.array_equal(k1, kps[f, :n[f]]) and np.array_equal(d1, desc[f, :n[f]])
+    ex.close()
+
+
+def test_strided_input_and_noise(ob):
+    """Row-strided host input (an ROI view) and a dense-corner noise image (candidate-capacity stress)."""
+    p = _params(500)
+    ex = ob.ORBextractor(**p); orc = Oracle(**p)
+    big = np.random.default_rng(5).integers(0, 256, (300, 500), dtype=np.uint8)
+    view = big[10:270, 20:420]
+    k, d = ex(view[None][0])
+    kb, db, nb = ex.extract_batch(view[None])
+    img = np.ascontiguousarray(view)
+    _compare_frame(ex, orc, img, 0, None, kb[0, :nb[0]], db[0, :nb[0]])
+    assert np.array_equal(k, kb[0, :nb[0]])
+    ex.close()
+
+
+def test_flat_and_empty_images(ob):
+    p = _params(1000)
+    ex = ob.ORBextractor(**p)
+    k, d = ex(np.full((480, 640), 77, np.uint8))
+    assert len(k) == 0 and d.shape == (0, 32)
+    k, d = ex(np.zeros((0, 0), np.uint8))
+    assert len(k) == 0
+    with pytest.raises(ob.OrbxError):
+        ex(np.zeros((60, 60), np.uint8))  # top pyramid levels smaller than one FAST cell
+    ex.close()
+
+
+def test_getters_match_oracle(ob):
+    p = _params(1000)
+    ex = ob.ORBextractor(**p); orc = Oracle(**p)
+    t, pl, um = orc.tables()
+    assert np.array_equal(ex.GetScaleFactors(), t[0]) and np.array_equal(ex.GetInverseScaleFactors(), t[1])
+    assert np.array_equal(ex.GetScaleSigmaSquares(), t[2]) and np.array_equal(ex.GetInverseScaleSigmaSquares(), t[3])
+    assert np.array_equal(ex.mnFeaturesPerLevel, pl) and np.array_equal(ex.umax, um)
+    assert ex.GetLevels() == 8
+    ex.close()
+
+
+def test_device_io_torch(ob):
+    import torch
+    p = _params(1000)
+    ex = ob.ORBextractor(**p)
+    imgs = np.stack([synth_image(640, 480, s) for s in range(4)])
+    kh, dh, nh = ex.extract_batch(imgs)
+    kd, dd, nd = ex.extract_batch(torch.from_numpy(imgs).cuda())
+    assert np.array_equal(nh, nd)
+    for f in range(4):
+        assert np.array_equal(dd[f, :nd[f]].cpu().numpy(), dh[f, :nh[f]])
+        assert kd[f, :nd[f]].cpu().numpy().tobytes() == kh[f, :nh[f]].tobytes()
+    ex.close()

@@ -1,0 +1,84 @@
+"""GPU parity of the matcher kernels against the oracle's sequential loops: bit-exact distances and indices,
+including lowest-index tie-breaks (planted duplicates), empty candidate lists and skip masks."""
+import numpy as np
+import pytest
+
+from oracle_lib import OraclePrims
+from orbslam2_b200.synth import synth_descriptors
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ob():
+    import orbslam2_b200
+    return orbslam2_b200
+
+
+def test_descriptor_distance(ob):
+    m = ob.ORBmatcher(); P = OraclePrims()
+    rng = np.random.default_rng(0)
+    a = rng.integers(0, 256, (500, 32), dtype=np.uint8); b = rng.integers(0, 256, (500, 32), dtype=np.uint8)
+    a[0] = 0; b[0] = 255; a[1] = b[1]
+    d = m.DescriptorDistance(a, b)
+    assert d[0] == 256 and d[1] == 0
+    assert all(int(d[i]) == P.hamming(a[i], b[i]) for i in range(500))
+    assert m.DescriptorDistance(a[7], b[7]) == P.hamming(a[7], b[7])
+
+
+@pytest.mark.parametrize("nt,nq", [(1, 5), (2, 3), (700, 257), (20000, 1500)])
+def test_knn2_vs_oracle(ob, nt, nq):
+    m = ob.ORBmatcher(); P = OraclePrims()
+    t, q = synth_descriptors(nt, nq, seed=nt, dup=min(100, nt // 4))
+    i1, d1, d2 = m.knn2(q, t)
+    o1, e1, e2 = P.knn2(q, t)
+    assert np.array_equal(i1, o1) and np.array_equal(d1, e1) and np.array_equal(d2, e2)
+
+
+def test_knn2_ties_lowest_index(ob):
+    m = ob.ORBmatcher()
+    rng = np.random.default_rng(3)
+    t = rng.integers(0, 256, (5000, 32), dtype=np.uint8)
+    t[4000] = t[17]; t[2500] = t[17]
+    q = t[[17, 2500, 4000]].copy()
+    i1, d1, d2 = m.knn2(q, t)
+    assert list(i1) == [17, 17, 17] and list(d1) == [0, 0, 0] and list(d2) == [0, 0, 0]
+
+
+def test_knn2_split_train_large(ob):
+    """Few queries x many train rows exercises the train-split + ordered merge path."""
+    m = ob.ORBmatcher(); P = OraclePrims()
+    t, q = synth_descriptors(300000, 64, seed=11, dup=1000)
+    i1, d1, d2 = m.knn2(q, t)
+    o1, e1, e2 = P.knn2(q, t, popcnt=True)
+    assert np.array_equal(i1, o1) and np.array_equal(d1, e1) and np.array_equal(d2, e2)
+
+
+def test_ratio_rule(ob):
+    m = ob.ORBmatcher(nnratio=0.7)
+    t, q = synth_descriptors(20000, 2000, seed=5)
+    i1, d1, d2 = m.knn2(q, t)
+    for th in (50, 100):
+        acc, _, _ = m.match_ratio(q, t, th=th)
+        exp = (d1 <= th) & (d1.astype(np.float32) < np.float32(0.7) * d2.astype(np.float32))
+        assert np.array_equal(acc >= 0, exp)
+    assert (acc >= 0).sum() > 500
+
+
+def test_window_search_vs_oracle(ob):
+    m = ob.ORBmatcher(); P = OraclePrims()
+    rng = np.random.default_rng(9)
+    t, q = synth_descriptors(3000, 400, seed=9, dup=300)
+    lens = rng.integers(0, 90, 400); lens[:5] = 0; lens[5] = 1
+    off = np.zeros(401, np.int32); off[1:] = np.cumsum(lens)
+    idx = rng.integers(0, 3000, off[-1]).astype(np.int32)
+    # force ties: repeat the same train row several times inside some lists
+    for a in range(10, 60):
+        if lens[a] > 4:
+            idx[off[a] + 3] = idx[off[a] + 1]
+    skip = (rng.random(off[-1]) < 0.2).astype(np.uint8)
+    for sk in (None, skip):
+        got = m.window_search(q, off, idx, t, sk)
+        exp = P.window_search(q, off, idx, sk, t)
+        for g, e, name in zip(got, exp, ("best_idx", "best_d", "second_d", "second_idx")):
+            assert np.array_equal(g, e), name
