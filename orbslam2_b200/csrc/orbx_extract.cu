@@ -3,6 +3,7 @@
 // Mirrors ORB_SLAM2::ORBextractor (/root/reference/src/ORBextractor.cc:405-464 ctor tables, :858-919 operator()).
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <vector>
@@ -189,7 +190,7 @@ static int build_plan(orbx_handle* h, int w, int hgt, int batch) {
         pyrOff += ((G.frameStride * batch + 255) / 256) * 256;
         G.cellBase = cellBase;
         cellBase += G.nCols * G.nRows;
-        G.boxW = (G.wCell + 6 + 15) & ~15;
+        G.boxW = (G.wCell + 6 + 15 + 15) & ~15;  // + up to 15 px of x-alignment slack (see k_fast)
         G.boxH = G.hCell + 6;
         G.maxSurv = ((G.wCell + 1) / 2) * ((G.hCell + 1) / 2);
         G.quota = h->perLevel[l];
@@ -366,6 +367,21 @@ static inline void stamp(orbx_handle* h, int i) {
     if (h->profiling) cudaEventRecord(h->ev[i], h->stream);
 }
 
+// ORBX_DEBUG_SYNC=1: synchronise after every launch and name the kernel that faulted (development aid).
+static bool debug_sync() {
+    static const bool on = getenv("ORBX_DEBUG_SYNC") != nullptr;
+    return on;
+}
+#define KCHECK(h, name)                                                                              \
+    do {                                                                                             \
+        (h)->launches++;                                                                             \
+        if (debug_sync()) {                                                                          \
+            cudaError_t e_ = cudaStreamSynchronize((h)->stream);                                     \
+            if (e_ == cudaSuccess) e_ = cudaGetLastError();                                          \
+            if (e_ != cudaSuccess) FAIL(ORBX_ECUDA, "kernel %s failed: %s", name, cudaGetErrorString(e_)); \
+        }                                                                                            \
+    } while (0)
+
 extern "C" int orbx_extract_batch(orbx_t* h, const uint8_t* imgs, int batch, int w, int hgt, size_t stride,
                                   size_t img_stride, orbx_kp* kps, uint8_t* desc, int cap, int* n) {
     if (!h || !n) FAIL(ORBX_EINVAL, "null argument");
@@ -400,22 +416,22 @@ extern "C" int orbx_extract_batch(orbx_t* h, const uint8_t* imgs, int batch, int
         const LevelGeo& G = D.lv[l];
         dim3 grid((G.w + 255) / 256, (G.h + 3) / 4, batch), block(64, 4);
         k_resize<<<grid, block, 0, st>>>(h->dPlan, l, h->dPyr, h->dTabs);
-        h->launches++;
+        KCHECK(h, "k_resize");
     }
     stamp(h, 2);
     k_fast<<<dim3(D.totalCells, batch), 256, h->fastSmem, st>>>(h->maps, h->dPlan, h->dCand, h->dCandCount, h->dErr);
-    h->launches++;
+    KCHECK(h, "k_fast");
     stamp(h, 3);
     k_quadtree<<<dim3(nl, batch), h->qtThreads, h->qtSmem, st>>>(h->dPlan, h->dCand, h->dCandCount, h->dNodeOf, h->dSel,
                                                                   h->dSelCount, h->qtC, h->qtC2, h->dErr);
-    h->launches++;
+    KCHECK(h, "k_quadtree");
     stamp(h, 4);
     k_blur<<<dim3(D.totalBlurTiles, batch), 256, 0, st>>>(h->dPlan, h->dPyr, h->dBlur);
-    h->launches++;
+    KCHECK(h, "k_blur");
     stamp(h, 5);
     k_orient_desc<<<dim3((D.selStride + 7) / 8, batch), 256, 0, st>>>(h->dPlan, h->dPyr, h->dBlur, h->dSel, h->dSelCount,
                                                                       h->dKps, h->dDesc, h->dNOut);
-    h->launches++;
+    KCHECK(h, "k_orient_desc");
     stamp(h, 6);
     CK(cudaGetLastError());
     h->lastBatch = batch;

@@ -36,7 +36,7 @@ struct LevelGeo {
     // FAST cell grid (src/ORBextractor.cc:763-781 of the reference)
     int nCols, nRows, wCell, hCell;
     int cellBase;           // first block index of this level in the fused FAST launch
-    int boxW, boxH;         // TMA box: roundup16(wCell+6) x (hCell+6)
+    int boxW, boxH;         // TMA box: roundup16(wCell+6+15) x (hCell+6)
     int maxSurv;            // upper bound of NMS survivors in one cell
     // quadtree
     int quota, nIni, treeW, treeH;

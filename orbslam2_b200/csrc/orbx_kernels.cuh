@@ -133,7 +133,7 @@ __global__ void __launch_bounds__(256) k_resize(const DevPlan* __restrict__ P, i
 }
 
 // ------------------------------------------------------------------------------------------------ K2 FAST
-// One CTA per (cell, frame). The (wCell+6) x (hCell+6) cell ROI is fetched with ONE 3-D TMA tile load
+// One CTA per (cell, frame). The (wCell+6) x (hCell+6) cell ROI (x start rounded down to 16) is fetched with ONE 3-D TMA tile load
 // (coordinates x, y, frame on the level's tensor map; out-of-image bytes are zero-filled and never used).
 // Scores are computed once at minThFAST; NMS is cell-local (a neighbour outside this cell's detection area counts 0);
 // the reference's "FAST(ini) else FAST(min)" retry is the block-wide test "any survivor with score >= ini".
@@ -183,6 +183,9 @@ __global__ void __launch_bounds__(256) k_fast(const __grid_constant__ TmapPack m
     const int ci = (c - G.cellBase) / G.nCols, cj = (c - G.cellBase) % G.nCols;
     const int e = P->edge;
     const int ox = e - 3 + cj * G.wCell, oy = e - 3 + ci * G.hCell;  // ROI origin (level pixels)
+    // TMA tile mode needs the box start 16-byte aligned in the innermost dimension (an unaligned x coordinate
+    // faults with "illegal instruction" on sm_100a): fetch from ox rounded down, address the tile with xoff.
+    const int oxa = ox & ~15, xoff = ox - oxa;
     const int dw = min(G.wCell, (G.w - e) - (ox + 3));               // detection area of this cell
     const int dh = min(G.hCell, (G.h - e) - (oy + 3));
     if (dw <= 0 || dh <= 0) return;
@@ -211,7 +214,7 @@ __global__ void __launch_bounds__(256) k_fast(const __grid_constant__ TmapPack m
         asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
         asm volatile(
             "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
-            ::"r"(smem_u32(tile)), "l"(&maps.m[level]), "r"(ox), "r"(oy), "r"(f), "r"(bar)
+            ::"r"(smem_u32(tile)), "l"(&maps.m[level]), "r"(oxa), "r"(oy), "r"(f), "r"(bar)
             : "memory");
     }
     {   // bounded wait on phase 0 (a lost TMA must not hang the GPU: flag the error and bail out)
@@ -236,7 +239,7 @@ __global__ void __launch_bounds__(256) k_fast(const __grid_constant__ TmapPack m
     const int npx = dw * dh;
     for (int p = tid; p < npx; p += blockDim.x) {
         const int yin = p / dw, xin = p - yin * dw;
-        const uint8_t* q = tile + (yin + 3) * boxW + (xin + 3);
+        const uint8_t* q = tile + (yin + 3) * boxW + (xin + 3 + xoff);
         const int v = q[0];
         // compass pre-test: every arc of 9 contains at least two of the four compass points
         const int c0 = q[3 * boxW], c4 = q[3], c8 = q[-3 * boxW], c12 = q[-3];
