@@ -419,7 +419,8 @@ extern "C" int orbx_extract_batch(orbx_t* h, const uint8_t* imgs, int batch, int
         KCHECK(h, "k_resize");
     }
     stamp(h, 2);
-    k_fast<<<dim3(D.totalCells, batch), 256, h->fastSmem, st>>>(h->maps, h->dPlan, h->dCand, h->dCandCount, h->dErr);
+    k_fast<<<dim3(D.totalCells, batch), 256, h->fastSmem, st>>>(h->maps, h->dPlan, h->dCand, h->dCandCount, h->dErr,
+                                                                      h->dPyr, getenv("ORBX_NO_TMA") != nullptr);
     KCHECK(h, "k_fast");
     stamp(h, 3);
     k_quadtree<<<dim3(nl, batch), h->qtThreads, h->qtSmem, st>>>(h->dPlan, h->dCand, h->dCandCount, h->dNodeOf, h->dSel,

@@ -146,33 +146,30 @@ __device__ __forceinline__ bool nine_contiguous(uint32_t m) {
     return (r & 0xFFFFu) != 0;
 }
 
-__device__ __forceinline__ int fast_score(const int (&d)[16]) {
-    // max over the 16 arcs of 9 of min(d) and of min(-d), minus 1 (OpenCV cornerScore<16>)
-    int mn2[16], mx2[16];
+// FAST score (OpenCV cornerScore<16>): the largest threshold at which the pixel is still a corner =
+// max over the 16 arcs of 9 of min(e) - 1, e = d for a centre-brighter corner, -d for the other
+// polarity. Only the polarity that passed the corner test matters: an arc of the other polarity overlaps the
+// corner arc in >= 2 pixels whose sign is wrong, so its arc-minimum is negative. (Single polarity also avoids a
+// ptxas 12.9 miscompile seen on sm_100a: max(a, -max3(..)) lost the negation when fused into VIMNMX3.)
+__device__ __forceinline__ int fast_score(const int (&d)[16], bool centreBrighter) {
+    int e[16];
 #pragma unroll
-    for (int k = 0; k < 16; k++) {
-        mn2[k] = min(d[k], d[(k + 1) & 15]);
-        mx2[k] = max(d[k], d[(k + 1) & 15]);
-    }
-    int mn4[16], mx4[16];
+    for (int k = 0; k < 16; k++) e[k] = centreBrighter ? d[k] : -d[k];
+    int mn2[16];
 #pragma unroll
-    for (int k = 0; k < 16; k++) {
-        mn4[k] = min(mn2[k], mn2[(k + 2) & 15]);
-        mx4[k] = max(mx2[k], mx2[(k + 2) & 15]);
-    }
+    for (int k = 0; k < 16; k++) mn2[k] = min(e[k], e[(k + 1) & 15]);
+    int mn4[16];
+#pragma unroll
+    for (int k = 0; k < 16; k++) mn4[k] = min(mn2[k], mn2[(k + 2) & 15]);
     int best = -256;
 #pragma unroll
-    for (int k = 0; k < 16; k++) {
-        const int mn9 = min(min(mn4[k], mn4[(k + 4) & 15]), d[(k + 8) & 15]);
-        const int mx9 = max(max(mx4[k], mx4[(k + 4) & 15]), d[(k + 8) & 15]);
-        best = max(best, max(mn9, -mx9));
-    }
+    for (int k = 0; k < 16; k++) best = max(best, min(min(mn4[k], mn4[(k + 4) & 15]), e[(k + 8) & 15]));
     return best - 1;
 }
 
 __global__ void __launch_bounds__(256) k_fast(const __grid_constant__ TmapPack maps, const DevPlan* __restrict__ P,
                                               u64* __restrict__ cand, int* __restrict__ candCount,
-                                              int* __restrict__ err) {
+                                              int* __restrict__ err, const uint8_t* __restrict__ pyr, int noTma) {
     extern __shared__ __align__(128) uint8_t fast_smem[];
     uint8_t* smem = fast_smem;
     const int f = blockIdx.y;
@@ -209,7 +206,14 @@ __global__ void __launch_bounds__(256) k_fast(const __grid_constant__ TmapPack m
     }
     for (int i = tid; i < scoreBytes / 4; i += blockDim.x) ((uint32_t*)score)[i] = 0;
     __syncthreads();
-    if (tid == 0) {
+    if (noTma) {  // development aid (ORBX_NO_TMA=1): same tile through ordinary loads
+        const uint8_t* src = pyr + G.pyrOff + (long long)f * G.frameStride;
+        for (int i = tid; i < boxW * boxH; i += blockDim.x) {
+            const int x = oxa + i % boxW, y = oy + i / boxW;
+            tile[i] = (x < G.w && y < G.h) ? src[(long long)y * G.pitch + x] : 0;
+        }
+        __syncthreads();
+    } else if (tid == 0) {
         const uint32_t bytes = (uint32_t)(boxW * boxH);
         asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
         asm volatile(
@@ -217,7 +221,7 @@ __global__ void __launch_bounds__(256) k_fast(const __grid_constant__ TmapPack m
             ::"r"(smem_u32(tile)), "l"(&maps.m[level]), "r"(oxa), "r"(oy), "r"(f), "r"(bar)
             : "memory");
     }
-    {   // bounded wait on phase 0 (a lost TMA must not hang the GPU: flag the error and bail out)
+    if (!noTma) {   // bounded wait on phase 0 (a lost TMA must not hang the GPU: flag the error and bail out)
         uint32_t done = 0;
         int spins = 0;
         while (!done) {
@@ -270,7 +274,8 @@ __global__ void __launch_bounds__(256) k_fast(const __grid_constant__ TmapPack m
             mb |= (uint32_t)(d[k] < -th) << k;
             md |= (uint32_t)(d[k] > th) << k;
         }
-        if (nine_contiguous(mb) || nine_contiguous(md)) score[(yin + 1) * SP + xin + 1] = (uint8_t)fast_score(d);
+        const bool dark = nine_contiguous(md);
+        if (dark || nine_contiguous(mb)) score[(yin + 1) * SP + xin + 1] = (uint8_t)fast_score(d, dark);
     }
     __syncthreads();
 
