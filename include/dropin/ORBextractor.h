@@ -1,0 +1,146 @@
+// include/dropin/ORBextractor.h — header-only C++ drop-in for ORB_SLAM2::ORBextractor over the liborbx C ABI (orbx.h).
+//
+// Put this directory ahead of the reference's include/ on the include path and link liborbx.so: Frame.cc / Tracking.cc
+// compile unchanged (same constructor, operator(), getters, public mvImagePyramid). Replaces
+// /root/reference/include/ORBextractor.h:45-112 and /root/reference/src/ORBextractor.cc:405-947.
+// All compute runs in the CUDA kernels behind orbx_extract; this file only marshals buffers. There is no CPU path:
+// when the library reports an error the wrapper throws std::runtime_error (the reference would cv::Exception).
+#ifndef ORBX_DROPIN_ORBEXTRACTOR_H
+#define ORBX_DROPIN_ORBEXTRACTOR_H
+
+#include <cassert>
+#include <cstring>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include <opencv2/core/core.hpp>
+
+#include "../orbx.h"
+
+namespace ORB_SLAM2 {
+
+class ORBextractor {
+public:
+    enum { HARRIS_SCORE = 0, FAST_SCORE = 1 };
+
+    // 8-argument form of this fork (include/ORBextractor.h:51); zeros select 31/15/19 like src/Tracking.cc:118-123.
+    ORBextractor(int nfeatures_, float scaleFactor_, int nlevels_, int iniThFAST_, int minThFAST_, int patchSize_,
+                 int halfPatchSize_, int edgeThreshold_, int cudaDevice = 0)
+        : nfeatures(nfeatures_), scaleFactor(scaleFactor_), nlevels(nlevels_), iniThFAST(iniThFAST_),
+          minThFAST(minThFAST_), patchSize(patchSize_ ? patchSize_ : 31),
+          halfPatchSize(halfPatchSize_ ? halfPatchSize_ : 15), edgeThreshold(edgeThreshold_ ? edgeThreshold_ : 19) {
+        orbx_params p = {nfeatures, scaleFactor_, nlevels, iniThFAST, minThFAST, patchSize, halfPatchSize, edgeThreshold};
+        check(orbx_create(&p, cudaDevice, &h_), "orbx_create");
+        mvScaleFactor.resize(nlevels); mvInvScaleFactor.resize(nlevels);
+        mvLevelSigma2.resize(nlevels); mvInvLevelSigma2.resize(nlevels);
+        mnFeaturesPerLevel.resize(nlevels); umax.resize(halfPatchSize + 1);
+        check(orbx_tables(h_, mvScaleFactor.data(), mvInvScaleFactor.data(), mvLevelSigma2.data(),
+                          mvInvLevelSigma2.data(), mnFeaturesPerLevel.data(), umax.data()), "orbx_tables");
+        mvImagePyramid.resize(nlevels);
+    }
+    // upstream ORB-SLAM2 5-argument form (what BASELINE.json's north_star writes)
+    ORBextractor(int nfeatures_, float scaleFactor_, int nlevels_, int iniThFAST_, int minThFAST_)
+        : ORBextractor(nfeatures_, scaleFactor_, nlevels_, iniThFAST_, minThFAST_, 31, 15, 19) {}
+    ~ORBextractor() { orbx_destroy(h_); }
+    ORBextractor(const ORBextractor&) = delete;
+    ORBextractor& operator=(const ORBextractor&) = delete;
+
+    // When false, operator() skips the device->host copy of the pyramid (callers that run stereo matching on the device
+    // through ComputeStereoMatchesDevice do not need it). Default true = exact drop-in behaviour.
+    bool keepHostPyramid = true;
+
+    // src/ORBextractor.cc:858-919. mask is ignored as in the reference.
+    void operator()(cv::InputArray _image, cv::InputArray /*_mask*/, std::vector<cv::KeyPoint>& _keypoints,
+                    cv::OutputArray _descriptors) {
+        if (_image.empty()) return;  // outputs untouched (:861-862)
+        cv::Mat image = _image.getMat();
+        assert(image.type() == CV_8UC1);
+        int cap = 0;
+        check(orbx_max_keypoints(h_, image.cols, image.rows, &cap), "orbx_max_keypoints");
+        static_assert(sizeof(cv::KeyPoint) == sizeof(orbx_kp), "cv::KeyPoint must be 28 bytes");
+        kp_.resize(cap);
+        desc_.resize((size_t)cap * 32);
+        int n = 0;
+        check(orbx_extract(h_, image.data, image.cols, image.rows, image.step, kp_.data(), desc_.data(), cap, &n),
+              "orbx_extract");
+        _keypoints.clear();
+        if (n == 0) {
+            _descriptors.release();
+        } else {
+            _descriptors.create(n, 32, CV_8U);
+            cv::Mat d = _descriptors.getMat();
+            for (int i = 0; i < n; i++) std::memcpy(d.ptr(i), desc_.data() + (size_t)i * 32, 32);
+            _keypoints.resize(n);
+            std::memcpy((void*)_keypoints.data(), kp_.data(), (size_t)n * sizeof(orbx_kp));
+        }
+        if (keepHostPyramid) refreshPyramid();
+    }
+
+    int inline GetLevels() { return nlevels; }
+    float inline GetScaleFactor() { return (float)scaleFactor; }
+    std::vector<float> inline GetScaleFactors() { return mvScaleFactor; }
+    std::vector<float> inline GetInverseScaleFactors() { return mvInvScaleFactor; }
+    std::vector<float> inline GetScaleSigmaSquares() { return mvLevelSigma2; }
+    std::vector<float> inline GetInverseScaleSigmaSquares() { return mvInvLevelSigma2; }
+    // north_star's accessor (not in this fork): the pyramid of the last image
+    const std::vector<cv::Mat>& GetImagePyramid() { return mvImagePyramid; }
+
+    // Public data member read by Frame::ComputeStereoMatches (src/Frame.cc:471,565,577,582): level interiors as ROIs
+    // at (edgeThreshold, edgeThreshold) of padded BORDER_REFLECT_101 buffers, exactly like src/ORBextractor.cc:927-942.
+    std::vector<cv::Mat> mvImagePyramid;
+
+    orbx_t* handle() { return h_; }  // for ComputeStereoMatchesDevice / batch calls on the C ABI
+
+protected:
+    void refreshPyramid() {
+        padded_.resize(nlevels);
+        for (int l = 0; l < nlevels; l++) {
+            int w = 0, hgt = 0;
+            check(orbx_level_size(h_, l, &w, &hgt), "orbx_level_size");
+            const int W = w + 2 * edgeThreshold, H = hgt + 2 * edgeThreshold;
+            padded_[l].create(H, W, CV_8UC1);
+            check(orbx_pyramid_level(h_, 0, l, padded_[l].data, padded_[l].step, 1), "orbx_pyramid_level");
+            mvImagePyramid[l] = padded_[l](cv::Rect(edgeThreshold, edgeThreshold, w, hgt));
+        }
+    }
+    static void check(int rc, const char* what) {
+        if (rc != ORBX_OK) throw std::runtime_error(std::string(what) + ": " + orbx_last_error_string());
+    }
+
+    int nfeatures;
+    double scaleFactor;
+    int nlevels;
+    int iniThFAST;
+    int minThFAST;
+    int patchSize;
+    int halfPatchSize;
+    int edgeThreshold;
+    std::vector<int> mnFeaturesPerLevel;
+    std::vector<int> umax;
+    std::vector<float> mvScaleFactor;
+    std::vector<float> mvInvScaleFactor;
+    std::vector<float> mvLevelSigma2;
+    std::vector<float> mvInvLevelSigma2;
+
+private:
+    orbx_t* h_ = nullptr;
+    std::vector<orbx_kp> kp_;
+    std::vector<uint8_t> desc_;
+    std::vector<cv::Mat> padded_;
+};
+
+// Frame::ComputeStereoMatches (src/Frame.cc:464-642) on the device state of two extractors that have just processed the
+// left and right image. mvuRight / mvDepth are resized to the left keypoint count and filled (-1 = no match).
+inline void ComputeStereoMatchesDevice(ORBextractor& left, ORBextractor& right, int nLeft, float mbf, float minD,
+                                       float maxD, std::vector<float>& mvuRight, std::vector<float>& mvDepth) {
+    mvuRight.assign(nLeft, -1.0f);
+    mvDepth.assign(nLeft, -1.0f);
+    if (nLeft == 0) return;
+    if (orbx_stereo_match(left.handle(), right.handle(), 0, mbf, minD, maxD, mvuRight.data(), mvDepth.data()) != ORBX_OK)
+        throw std::runtime_error(std::string("orbx_stereo_match: ") + orbx_last_error_string());
+}
+
+}  // namespace ORB_SLAM2
+
+#endif

@@ -1,0 +1,52 @@
+// Compiles the reference-signature C++ wrappers (include/dropin) against the cv shim and drives them the way
+// Frame::ExtractORB (/root/reference/src/Frame.cc:248-254) and Frame's stereo constructor (:61-117) do.
+// Usage: dropin_run <w> <h> <left.raw> <right.raw> <out.bin>   (raw 8-bit images); built and run by tests/test_gpu_dropin.py
+#include <cstdio>
+#include <cstdlib>
+#include <vector>
+
+#include "dropin/ORBextractor.h"
+#include "dropin/ORBmatcher.h"
+
+static std::vector<unsigned char> slurp(const char* path, size_t n) {
+    std::vector<unsigned char> b(n);
+    FILE* f = fopen(path, "rb");
+    if (!f || fread(b.data(), 1, n, f) != n) { fprintf(stderr, "cannot read %s\n", path); exit(2); }
+    fclose(f);
+    return b;
+}
+
+int main(int argc, char** argv) {
+    if (argc < 6) return 1;
+    const int w = atoi(argv[1]), h = atoi(argv[2]);
+    std::vector<unsigned char> L = slurp(argv[3], (size_t)w * h), R = slurp(argv[4], (size_t)w * h);
+    cv::Mat imL(h, w, CV_8UC1, L.data(), (size_t)w), imR(h, w, CV_8UC1, R.data(), (size_t)w);
+    ORB_SLAM2::ORBextractor exL(1000, 1.2f, 8, 20, 7, 31, 15, 19), exR(1000, 1.2f, 8, 20, 7);
+    std::vector<cv::KeyPoint> kL, kR;
+    cv::Mat dL, dR;
+    exL(imL, cv::Mat(), kL, dL);
+    exR(imR, cv::Mat(), kR, dR);
+    std::vector<float> uR, depth;
+    ORB_SLAM2::ComputeStereoMatchesDevice(exL, exR, (int)kL.size(), 40.0f, 0.0f, 400.0f, uR, depth);
+    ORB_SLAM2::ORBmatcher matcher(0.7f);
+    std::vector<int32_t> i1; std::vector<uint16_t> d1, d2;
+    ORB_SLAM2::ORBmatcher::Knn2(dL, dR, i1, d1, d2);
+    int accepted = 0;
+    for (size_t i = 0; i < i1.size(); i++) accepted += matcher.AcceptRatio(d1[i], d2[i], ORB_SLAM2::ORBmatcher::TH_LOW);
+    const int d01 = kL.size() > 1 ? ORB_SLAM2::ORBmatcher::DescriptorDistance(dL.rowRange(0, 1), dL.rowRange(1, 2)) : -1;
+    FILE* f = fopen(argv[5], "wb");
+    int hdr[6] = {(int)kL.size(), (int)kR.size(), accepted, d01, exL.GetLevels(), exL.mvImagePyramid[3].cols};
+    fwrite(hdr, sizeof(int), 6, f);
+    fwrite(kL.data(), sizeof(cv::KeyPoint), kL.size(), f);
+    for (int i = 0; i < dL.rows; i++) fwrite(dL.ptr(i), 1, 32, f);
+    fwrite(uR.data(), 4, uR.size(), f);
+    fwrite(depth.data(), 4, depth.size(), f);
+    fwrite(i1.data(), 4, i1.size(), f);
+    // level-3 pyramid interior incl. what the ROI sees of its reflect border (first row above the ROI)
+    const cv::Mat& p3 = exL.mvImagePyramid[3];
+    fwrite(p3.data - p3.step, 1, p3.cols, f);
+    for (int y = 0; y < p3.rows; y++) fwrite(p3.ptr(y), 1, p3.cols, f);
+    fclose(f);
+    printf("dropin ok: %zu/%zu keypoints, %d ratio-accepted\n", kL.size(), kR.size(), accepted);
+    return 0;
+}

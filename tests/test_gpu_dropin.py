@@ -1,0 +1,63 @@
+"""GPU test of the C++ drop-in wrappers (include/dropin/ORBextractor.h, ORBmatcher.h): a C++ program written like the
+reference's callers (Frame::ExtractORB, stereo Frame ctor) is compiled with g++ against the cv shim, linked to
+liborbx.so, run on the device, and its outputs are compared with the Python host mirror and the CPU oracle."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from oracle_lib import Oracle, OraclePrims, canonical, KP_DTYPE, TUM1
+from orbslam2_b200.synth import synth_stereo_pair
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_cpp_dropin_end_to_end(tmp_path):
+    from orbslam2_b200 import build
+    lib = build.build()
+    exe = str(tmp_path / "dropin_run")
+    subprocess.check_call(["g++", "-std=c++14", "-O1", "-I", os.path.join(ROOT, "include"), "-I",
+                           os.path.join(ROOT, "oracle", "shim"), os.path.join(ROOT, "tests", "cpp", "wrapper_compile_check.cpp"),
+                           "-L", os.path.dirname(lib), "-lorbx", "-Wl,-rpath," + os.path.dirname(lib), "-o", exe])
+    w, h = 640, 480
+    left, right = synth_stereo_pair(w, h, 5)
+    left.tofile(tmp_path / "l.raw"); right.tofile(tmp_path / "r.raw")
+    out = tmp_path / "out.bin"
+    r = subprocess.run([exe, str(w), str(h), str(tmp_path / "l.raw"), str(tmp_path / "r.raw"), str(out)],
+                       capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stdout + r.stderr
+    raw = open(out, "rb").read()
+    nL, nR, accepted, d01, levels, p3w = np.frombuffer(raw[:24], np.int32)
+    off = 24
+    kps = np.frombuffer(raw[off:off + 28 * nL], KP_DTYPE); off += 28 * nL
+    desc = np.frombuffer(raw[off:off + 32 * nL], np.uint8).reshape(nL, 32); off += 32 * nL
+    uR = np.frombuffer(raw[off:off + 4 * nL], np.float32); off += 4 * nL
+    depth = np.frombuffer(raw[off:off + 4 * nL], np.float32); off += 4 * nL
+    i1 = np.frombuffer(raw[off:off + 4 * nL], np.int32); off += 4 * nL
+
+    orc = Oracle(**TUM1); P = OraclePrims()
+    ko, do = canonical(*orc.extract(left, 4000))
+    assert levels == 8 and nL == len(ko)
+    assert kps.tobytes() == ko.tobytes() or (np.abs(kps["x"] - ko["x"]).max() <= 1e-4 and np.abs(kps["angle"] - ko["angle"]).max() <= 1e-2)
+    assert (desc == do).all(axis=1).mean() >= 0.9999
+    # mvImagePyramid[3]: ROI inside a padded reflect-101 buffer (the row above the ROI is the reflection of row 1)
+    lw, lh = orc.level_size(3)
+    assert p3w == lw
+    pyr = np.frombuffer(raw[off:off + lw * (lh + 1)], np.uint8).reshape(lh + 1, lw)
+    lvl = orc.level(3)
+    assert np.array_equal(pyr[1:], lvl) and np.array_equal(pyr[0], lvl[1])
+    # stereo + matcher against the oracle on the same inputs
+    orcR = Oracle(**TUM1)
+    kr, dr = canonical(*orcR.extract(right, 4000))
+    assert nR == len(kr)
+    pyrL = [orc.level(l) for l in range(8)]; pyrR = [orcR.level(l) for l in range(8)]
+    t, _, _ = orc.tables()
+    eu, ez, _, _ = P.stereo_match(ko, do, kr, dr, pyrL, pyrR, t[0], t[1], 40.0, 0.0, 400.0)
+    assert np.array_equal(uR, eu) and np.array_equal(depth, ez)
+    o1, e1, e2 = P.knn2(do, dr)
+    assert np.array_equal(i1, o1)
+    exp_acc = int(((e1 <= 50) & (e1.astype(np.float32) < np.float32(0.7) * e2.astype(np.float32))).sum())
+    assert accepted == exp_acc
+    assert d01 == P.hamming(do[0], do[1])
