@@ -188,10 +188,14 @@ static int build_plan(orbx_handle* h, int w, int hgt, int batch) {
         G.frameStride = (long long)G.pitch * G.h;
         G.pyrOff = pyrOff;
         pyrOff += ((G.frameStride * batch + 255) / 256) * 256;
-        G.cellBase = cellBase;
-        cellBase += G.nCols * G.nRows;
-        G.boxW = (G.wCell + 6 + 15 + 15) & ~15;  // + up to 15 px of x-alignment slack (see k_fast)
-        G.boxH = G.hCell + 6;
+        G.stCX = std::max(1, std::min(4, (256 - 28) / G.wCell));
+        G.stCY = 2;
+        G.nStX = (G.nCols + G.stCX - 1) / G.stCX;
+        G.nStY = (G.nRows + G.stCY - 1) / G.stCY;
+        G.stBase = cellBase;
+        cellBase += G.nStX * G.nStY;
+        G.boxW = (G.stCX * G.wCell + 28 + 15) & ~15;  // 3-px circle rim + word/16-byte alignment slack (see k_fast)
+        G.boxH = G.stCY * G.hCell + 6;
         G.maxSurv = ((G.wCell + 1) / 2) * ((G.hCell + 1) / 2);
         G.quota = h->perLevel[l];
         G.treeW = maxBX - minB;
@@ -218,11 +222,9 @@ static int build_plan(orbx_handle* h, int w, int hgt, int batch) {
             G.ytabOff = (int)tabs.size();
             linear_table(D.lv[l - 1].h, G.h, false, tabs);
         }
-        size_t sm = ((size_t)(G.boxW * G.boxH + 127) & ~(size_t)127) + (((G.wCell + 2) * (G.hCell + 2) + 15) & ~15) +
-                    (size_t)G.maxSurv * 8 + 8 + 16;
-        fastSmem = std::max(fastSmem, sm);
+        fastSmem = std::max(fastSmem, (size_t)2 * G.boxW * G.boxH + sizeof(FastSmemHdr));
     }
-    D.totalCells = cellBase;
+    D.totalSt = cellBase;
     D.totalBlurTiles = blurBase;
     D.selStride = selOff;
     h->fastSmem = fastSmem;
@@ -419,8 +421,7 @@ extern "C" int orbx_extract_batch(orbx_t* h, const uint8_t* imgs, int batch, int
         KCHECK(h, "k_resize");
     }
     stamp(h, 2);
-    k_fast<<<dim3(D.totalCells, batch), 256, h->fastSmem, st>>>(h->maps, h->dPlan, h->dCand, h->dCandCount, h->dErr,
-                                                                      h->dPyr, getenv("ORBX_NO_TMA") != nullptr);
+    k_fast<<<dim3(D.totalSt, batch), FAST_THREADS, h->fastSmem, st>>>(h->maps, h->dPlan, h->dCand, h->dCandCount, h->dErr);
     KCHECK(h, "k_fast");
     stamp(h, 3);
     k_quadtree<<<dim3(nl, batch), h->qtThreads, h->qtSmem, st>>>(h->dPlan, h->dCand, h->dCandCount, h->dNodeOf, h->dSel,

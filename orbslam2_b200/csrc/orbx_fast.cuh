@@ -1,0 +1,307 @@
+// orbx_fast.cuh — K2 k_fast: per-cell FAST-9/16 + cell-local NMS + ini/min threshold rule.
+// Reference: ORBextractor::ComputeKeyPointsOctTree first half, /root/reference/src/ORBextractor.cc:759-823, and the
+// external cv::FAST(img, kps, th, true) (TYPE_9_16) it calls per 30-px cell.
+//
+// Formulation (threshold independent, so the reference's "FAST(ini) else FAST(min)" retry needs no second pass):
+//   for a centre v and its 16-pixel Bresenham circle c_0..c_15
+//     M = max over the 16 arcs of 9 of min(c over the arc)      m = min over the arcs of max(c over the arc)
+//     score = max(M - v, v - m) - 1   = the largest t at which the pixel is still a FAST corner (OpenCV cornerScore)
+//   the pixel is a corner at threshold t  <=>  score >= t.
+// The arc minima / maxima are computed for TWO pixels per instruction with the packed 16-bit DPX min/max
+// (VIMNMX3.U16x2): min3 over 3 neighbours, then min3 of three of those = min over 9; 40 instructions per polarity and
+// pixel pair. One thread scores 4 horizontally adjacent pixels (one 32-bit word of the tile).
+//
+// One CTA = a "supertile" of stCX x stCY cells of one level of one frame:
+//   TMA 3-D tile load (x start rounded down to 16 bytes — an unaligned innermost coordinate faults on sm_100a)
+//   phase 1  score map  (u8, value = score - (minTh-1), 0 = not a corner at minTh), same coordinates as the tile
+//   phase 2  SWAR non-maximum suppression, strictly greater than the 8 neighbours; a neighbour in another cell
+//            counts 0 (the reference runs cv::FAST per cell ROI), per-cell survivor counts (all / >= iniTh)
+//   phase 3  per cell: keep survivors >= iniTh if any exist, else all; one global atomic per CTA; emit records.
+#pragma once
+#include "orbx_internal.cuh"
+
+#define FAST_THREADS 256
+#define FAST_MAX_ST_CELLS 16  // cells per supertile (stCX * stCY)
+
+// bytes (x+dx .. x+dx+3) of a row given the three words around word x
+__device__ __forceinline__ unsigned fast_align(unsigned wm, unsigned w0, unsigned wp, int dx) {
+    switch (dx) {
+        case -3: return __byte_perm(wm, w0, 0x4321);
+        case -2: return __byte_perm(wm, w0, 0x5432);
+        case -1: return __byte_perm(wm, w0, 0x6543);
+        case 1: return __byte_perm(w0, wp, 0x4321);
+        case 2: return __byte_perm(w0, wp, 0x5432);
+        case 3: return __byte_perm(w0, wp, 0x6543);
+        default: return w0;
+    }
+}
+
+// Packed score of two pixels (16-bit lanes): c[k] = circle values, v = centres; returns max(score - (minTh-1), 0).
+__device__ __forceinline__ unsigned fast_score2(const unsigned (&c)[16], unsigned v, unsigned negThm1) {
+    unsigned a3[16], b3[16];
+#pragma unroll
+    for (int k = 0; k < 16; k++) {
+        a3[k] = __vimin3_u16x2(c[k], c[(k + 1) & 15], c[(k + 2) & 15]);
+        b3[k] = __vimax3_u16x2(c[k], c[(k + 1) & 15], c[(k + 2) & 15]);
+    }
+    unsigned M = 0u, m = 0xFFFFFFFFu;
+#pragma unroll
+    for (int k = 0; k < 16; k += 2) {
+        const unsigned a9 = __vimin3_u16x2(a3[k], a3[(k + 3) & 15], a3[(k + 6) & 15]);
+        const unsigned a9b = __vimin3_u16x2(a3[k + 1], a3[(k + 4) & 15], a3[(k + 7) & 15]);
+        M = __vimax3_u16x2(M, a9, a9b);
+        const unsigned b9 = __vimax3_u16x2(b3[k], b3[(k + 3) & 15], b3[(k + 6) & 15]);
+        const unsigned b9b = __vimax3_u16x2(b3[k + 1], b3[(k + 4) & 15], b3[(k + 7) & 15]);
+        m = __vimin3_u16x2(m, b9, b9b);
+    }
+    // per 16-bit lane ~x == -x-1, so M + ~v = (M - v) - 1 and v + ~m = (v - m) - 1
+    const unsigned sb = __viaddmax_s16x2(M, ~v, 0u);
+    const unsigned sd = __viaddmax_s16x2(v, ~m, 0u);
+    return __viaddmax_s16x2(__vmaxu2(sb, sd), negThm1, 0u);
+}
+
+// flag (bit 7 of each byte) = (a > b) for unsigned bytes; a7 = a & 0x7f7f7f7f
+__device__ __forceinline__ unsigned bytes_gt(unsigned a, unsigned a7, unsigned b) {
+    const unsigned nb = ~b;
+    const unsigned t = a7 + (nb & 0x7f7f7f7fu);      // carries out of the low 7 bits land in bit 7
+    return (a & nb) | (a & t) | (nb & t);            // majority = carry out of bit 7 of a + ~b  <=>  a > b
+}
+
+struct FastSmemHdr {
+    unsigned long long mbar;
+    int nAll[FAST_MAX_ST_CELLS];
+    int nIni[FAST_MAX_ST_CELLS];
+    int emitBase[FAST_MAX_ST_CELLS];
+    int total, gbase, slot, pad;
+    unsigned firstCol[64], lastCol[64];  // per word column: bytes that are the first / last column of a cell
+    unsigned char rowFlag[128];          // per detection row: bit0 first row of a cell, bit1 last row
+};
+
+__global__ void __launch_bounds__(FAST_THREADS) k_fast(const __grid_constant__ TmapPack maps,
+                                                       const DevPlan* __restrict__ P, u64* __restrict__ cand,
+                                                       int* __restrict__ candCount, int* __restrict__ err) {
+    extern __shared__ __align__(128) uint8_t fast_smem[];
+    const int tid = threadIdx.x;
+    const int f = blockIdx.y;
+    int level = 0;
+    while (level + 1 < P->nlevels && (int)blockIdx.x >= P->lv[level + 1].stBase) level++;
+    const LevelGeo& G = P->lv[level];
+    const int st = blockIdx.x - G.stBase;
+    const int sy = st / G.nStX, sx = st - sy * G.nStX;
+    const int e = P->edge;
+    const int cj0 = sx * G.stCX, ci0 = sy * G.stCY;
+    const int ncx = min(G.stCX, G.nCols - cj0), ncy = min(G.stCY, G.nRows - ci0);
+    const int xFirst = e + cj0 * G.wCell, xEnd = min(e + (cj0 + ncx) * G.wCell, G.w - e);
+    const int yFirst = e + ci0 * G.hCell, yEnd = min(e + (ci0 + ncy) * G.hCell, G.h - e);
+    if (xEnd <= xFirst || yEnd <= yFirst) return;
+
+    const int boxW = G.boxW, boxH = G.boxH;
+    const int pitchW = boxW >> 2;  // tile pitch in words
+    const int tileBytes = boxW * boxH;
+    unsigned* tile = (unsigned*)fast_smem;
+    unsigned* sc = (unsigned*)(fast_smem + tileBytes);
+    FastSmemHdr* H = (FastSmemHdr*)(fast_smem + 2 * tileBytes);
+    const int oxa = (xFirst - 6) & ~15, oy = yFirst - 3;
+    const int wx0 = (xFirst - oxa) >> 2, wx1 = (xEnd - 1 - oxa) >> 2;
+    const int nW = wx1 - wx0 + 1, nR = yEnd - yFirst;
+
+    const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&H->mbar);
+    if (tid == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        H->total = 0;
+        H->slot = 0;
+    }
+    if (tid < FAST_MAX_ST_CELLS) {
+        H->nAll[tid] = 0;
+        H->nIni[tid] = 0;
+    }
+    // column / row lookup tables (which bytes sit on a cell edge)
+    for (int i = tid; i < nW; i += FAST_THREADS) {
+        unsigned fc = 0, lc = 0;
+#pragma unroll
+        for (int b = 0; b < 4; b++) {
+            const int x = oxa + ((wx0 + i) << 2) + b;
+            if (x >= xFirst && x < xEnd) {
+                const int r = (x - xFirst) % G.wCell;
+                if (r == 0) fc |= 0xFFu << (8 * b);
+                if (r == G.wCell - 1 || x == xEnd - 1) lc |= 0xFFu << (8 * b);
+            }
+        }
+        H->firstCol[i] = fc;
+        H->lastCol[i] = lc;
+    }
+    for (int i = tid; i < nR; i += FAST_THREADS) {
+        const int r = i % G.hCell;
+        H->rowFlag[i] = (unsigned char)((r == 0 ? 1 : 0) | ((r == G.hCell - 1 || i == nR - 1) ? 2 : 0));
+    }
+    {   // zero the score map (its unused rim is what NMS reads as "no corner")
+        uint4* z = (uint4*)sc;
+        for (int i = tid; i < (tileBytes >> 4); i += FAST_THREADS) z[i] = make_uint4(0, 0, 0, 0);
+    }
+    __syncthreads();
+    if (tid == 0) {
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"((uint32_t)tileBytes) : "memory");
+        asm volatile(
+            "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+            ::"r"((uint32_t)__cvta_generic_to_shared(tile)), "l"(&maps.m[level]), "r"(oxa), "r"(oy), "r"(f), "r"(bar)
+            : "memory");
+    }
+    {   // bounded wait on phase 0 (a lost TMA must not hang the GPU: flag the error and bail out)
+        uint32_t done = 0;
+        int spins = 0;
+        while (!done) {
+            asm volatile(
+                "{\n\t.reg .pred p;\n\t"
+                "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+                "selp.u32 %0, 1, 0, p;\n\t}"
+                : "=r"(done)
+                : "r"(bar), "r"(0u)
+                : "memory");
+            if (!done && ++spins > (1 << 22)) {
+                atomicExch(err, 2);
+                break;
+            }
+        }
+    }
+
+    const int minTh = P->minTh, iniTh = P->iniTh;
+    const unsigned negThm1 = (unsigned)((-(minTh - 1)) & 0xFFFF) * 0x10001u;
+    const int nUnits = nW * nR;
+
+    // ---- phase 1: scores
+    for (int u = tid; u < nUnits; u += FAST_THREADS) {
+        const int wy = u / nW, wi = u - wy * nW;
+        const int wx = wx0 + wi;
+        const unsigned* r0 = tile + (wy + 3) * pitchW + wx;  // centre row
+        unsigned cw[16];  // aligned circle words, Bresenham order (dx,dy): (0,3)(1,3)(2,2)(3,1)(3,0)(3,-1)(2,-2)(1,-3)(0,-3)...
+        {
+            const unsigned* r = r0 + 3 * pitchW;
+            const unsigned a = r[-1], b = r[0], c = r[1];
+            cw[15] = fast_align(a, b, c, -1); cw[0] = b; cw[1] = fast_align(a, b, c, 1);
+        }
+        {
+            const unsigned* r = r0 + 2 * pitchW;
+            const unsigned a = r[-1], b = r[0], c = r[1];
+            cw[14] = fast_align(a, b, c, -2); cw[2] = fast_align(a, b, c, 2);
+        }
+        {
+            const unsigned* r = r0 + pitchW;
+            const unsigned a = r[-1], b = r[0], c = r[1];
+            cw[13] = fast_align(a, b, c, -3); cw[3] = fast_align(a, b, c, 3);
+        }
+        unsigned vw;
+        {
+            const unsigned a = r0[-1], b = r0[0], c = r0[1];
+            cw[12] = fast_align(a, b, c, -3); cw[4] = fast_align(a, b, c, 3);
+            vw = b;
+        }
+        {
+            const unsigned* r = r0 - pitchW;
+            const unsigned a = r[-1], b = r[0], c = r[1];
+            cw[11] = fast_align(a, b, c, -3); cw[5] = fast_align(a, b, c, 3);
+        }
+        {
+            const unsigned* r = r0 - 2 * pitchW;
+            const unsigned a = r[-1], b = r[0], c = r[1];
+            cw[10] = fast_align(a, b, c, -2); cw[6] = fast_align(a, b, c, 2);
+        }
+        {
+            const unsigned* r = r0 - 3 * pitchW;
+            const unsigned a = r[-1], b = r[0], c = r[1];
+            cw[9] = fast_align(a, b, c, -1); cw[8] = b; cw[7] = fast_align(a, b, c, 1);
+        }
+        unsigned ce[16], co[16];
+#pragma unroll
+        for (int k = 0; k < 16; k++) {
+            ce[k] = cw[k] & 0x00FF00FFu;              // pixels 0 and 2
+            co[k] = __byte_perm(cw[k], 0u, 0x4341);   // pixels 1 and 3
+        }
+        const unsigned se = fast_score2(ce, vw & 0x00FF00FFu, negThm1);
+        const unsigned so = fast_score2(co, __byte_perm(vw, 0u, 0x4341), negThm1);
+        unsigned s = se | (so << 8);
+        if (wi == 0 || wi == nW - 1) {  // bytes outside the detection columns
+            const int xb = oxa + (wx << 2);
+#pragma unroll
+            for (int b = 0; b < 4; b++)
+                if (xb + b < xFirst || xb + b >= xEnd) s &= ~(0xFFu << (8 * b));
+        }
+        sc[(wy + 3) * pitchW + wx] = s;
+    }
+    __syncthreads();
+
+    // ---- phase 2: NMS (strictly greater than all 8 neighbours of the same cell); survivors go to `tile`
+    for (int u = tid; u < nUnits; u += FAST_THREADS) {
+        const int wy = u / nW, wi = u - wy * nW;
+        const int wx = wx0 + wi;
+        const unsigned* q = sc + (wy + 3) * pitchW + wx;
+        const unsigned s = q[0];
+        unsigned surv = 0;
+        if (s) {
+            const unsigned s7 = s & 0x7f7f7f7fu;
+            const unsigned nfc = ~H->firstCol[wi], nlc = ~H->lastCol[wi];
+            const unsigned rf = H->rowFlag[wy];
+            unsigned ok = bytes_gt(s, s7, __byte_perm(q[-1], s, 0x6543) & nfc) & bytes_gt(s, s7, __byte_perm(s, q[1], 0x4321) & nlc);
+            if (!(rf & 1)) {
+                const unsigned* r = q - pitchW;
+                const unsigned a = r[-1], b = r[0], c = r[1];
+                ok &= bytes_gt(s, s7, __byte_perm(a, b, 0x6543) & nfc) & bytes_gt(s, s7, b) &
+                      bytes_gt(s, s7, __byte_perm(b, c, 0x4321) & nlc);
+            }
+            if (!(rf & 2)) {
+                const unsigned* r = q + pitchW;
+                const unsigned a = r[-1], b = r[0], c = r[1];
+                ok &= bytes_gt(s, s7, __byte_perm(a, b, 0x6543) & nfc) & bytes_gt(s, s7, b) &
+                      bytes_gt(s, s7, __byte_perm(b, c, 0x4321) & nlc);
+            }
+            ok &= 0x80808080u;  // a zero byte never beats its own "neighbour" comparisons' carry: s > n fails for s = 0
+            if (ok) {
+                const int cyl = wy / G.hCell;
+                const int xb = oxa + (wx << 2) - xFirst;
+#pragma unroll
+                for (int b = 0; b < 4; b++) {
+                    if (ok & (0x80u << (8 * b))) {
+                        const int v = (s >> (8 * b)) & 0xFF;
+                        const int cell = cyl * G.stCX + (xb + b) / G.wCell;
+                        atomicAdd(&H->nAll[cell], 1);
+                        if (v + minTh - 1 >= iniTh) atomicAdd(&H->nIni[cell], 1);
+                        surv |= (unsigned)v << (8 * b);
+                    }
+                }
+            }
+        }
+        tile[(wy + 3) * pitchW + wx] = surv;
+    }
+    __syncthreads();
+
+    // ---- phase 3: per-cell rule, one global reservation per CTA
+    if (tid == 0) {
+        int tot = 0;
+        for (int c = 0; c < G.stCX * G.stCY; c++) tot += H->nIni[c] > 0 ? H->nIni[c] : H->nAll[c];
+        H->total = tot;
+        H->gbase = tot ? atomicAdd(&candCount[f * P->nlevels + level], tot) : 0;
+    }
+    __syncthreads();
+    if (H->total == 0) return;
+    const int gbase = H->gbase;
+    u64* out = cand + G.candOff + (long long)f * G.candCap;
+    for (int u = tid; u < nUnits; u += FAST_THREADS) {
+        const int wy = u / nW, wi = u - wy * nW;
+        const int wx = wx0 + wi;
+        const unsigned s = tile[(wy + 3) * pitchW + wx];
+        if (!s) continue;
+        const int cyl = wy / G.hCell, yin = wy - cyl * G.hCell;
+        const int xb = oxa + (wx << 2) - xFirst;
+#pragma unroll
+        for (int b = 0; b < 4; b++) {
+            const int v = (s >> (8 * b)) & 0xFF;
+            if (!v) continue;
+            const int cxl = (xb + b) / G.wCell, xin = (xb + b) - cxl * G.wCell;
+            const int score = v + minTh - 1;
+            if (H->nIni[cyl * G.stCX + cxl] > 0 && score < iniTh) continue;
+            const int slot = gbase + atomicAdd(&H->slot, 1);
+            if (slot < G.candCap) out[slot] = cand_pack(score, ci0 + cyl, cj0 + cxl, yin, xin);
+            else atomicExch(err, 3);
+        }
+    }
+}

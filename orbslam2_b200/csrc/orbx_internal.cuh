@@ -35,8 +35,9 @@ struct LevelGeo {
     long long pyrOff;       // byte offset of this level's block inside the pyramid (and the blurred) allocation
     // FAST cell grid (src/ORBextractor.cc:763-781 of the reference)
     int nCols, nRows, wCell, hCell;
-    int cellBase;           // first block index of this level in the fused FAST launch
-    int boxW, boxH;         // TMA box: roundup16(wCell+6+15) x (hCell+6)
+    int stCX, stCY;         // FAST supertile = stCX x stCY cells (one CTA)
+    int nStX, nStY, stBase; // supertile grid of this level; first block index in the fused FAST launch
+    int boxW, boxH;         // TMA box of a supertile: roundup16(stCX*wCell + 28) x (stCY*hCell + 6)
     int maxSurv;            // upper bound of NMS survivors in one cell
     // quadtree
     int quota, nIni, treeW, treeH;
@@ -53,7 +54,7 @@ struct LevelGeo {
 struct DevPlan {
     int nlevels, batch;
     int iniTh, minTh, halfPatch, edge;
-    int totalCells, totalBlurTiles;
+    int totalSt, totalBlurTiles;
     int selStride;  // selected-keypoint slots per frame (sum of selCap)
     int umax[32];
     LevelGeo lv[ORBX_MAX_LEVELS];

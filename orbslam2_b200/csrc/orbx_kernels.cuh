@@ -1,7 +1,7 @@
 // orbx_kernels.cuh — extraction kernels (sm_100a). Included once by orbx_extract.cu.
 //
 // K1 k_resize      bilinear 8U pyramid level from the previous level       (ref: src/ORBextractor.cc:921-946 + cv::resize)
-// K2 k_fast        per-cell FAST-9/16 score + cell-local NMS + ini/min retry (ref: :759-823 + cv::FAST); tile via TMA
+// K2 k_fast        per-cell FAST-9/16 score + cell-local NMS + ini/min retry (ref: :759-823 + cv::FAST); orbx_fast.cuh
 // K3 k_quadtree    DistributeOctTree as a level-synchronous CTA algorithm    (ref: :475-757)
 // K4 k_blur        7x7 sigma-2 fixed-point Gaussian                          (ref: :899-900 + cv::GaussianBlur)
 // K5 k_orient_desc IC_Angle + steered BRIEF + keypoint assembly              (ref: :72-142, :835-841, :909-917)
@@ -133,194 +133,7 @@ __global__ void __launch_bounds__(256) k_resize(const DevPlan* __restrict__ P, i
 }
 
 // ------------------------------------------------------------------------------------------------ K2 FAST
-// One CTA per (cell, frame). The (wCell+6) x (hCell+6) cell ROI (x start rounded down to 16) is fetched with ONE 3-D TMA tile load
-// (coordinates x, y, frame on the level's tensor map; out-of-image bytes are zero-filled and never used).
-// Scores are computed once at minThFAST; NMS is cell-local (a neighbour outside this cell's detection area counts 0);
-// the reference's "FAST(ini) else FAST(min)" retry is the block-wide test "any survivor with score >= ini".
-__device__ __forceinline__ bool nine_contiguous(uint32_t m) {
-    m |= m << 16;
-    uint32_t r = m & (m >> 1);
-    r &= r >> 2;
-    r &= r >> 4;
-    r &= m >> 8;
-    return (r & 0xFFFFu) != 0;
-}
-
-// FAST score (OpenCV cornerScore<16>): the largest threshold at which the pixel is still a corner =
-// max over the 16 arcs of 9 of min(e) - 1, e = d for a centre-brighter corner, -d for the other
-// polarity. Only the polarity that passed the corner test matters: an arc of the other polarity overlaps the
-// corner arc in >= 2 pixels whose sign is wrong, so its arc-minimum is negative. (Single polarity also avoids a
-// ptxas 12.9 miscompile seen on sm_100a: max(a, -max3(..)) lost the negation when fused into VIMNMX3.)
-__device__ __forceinline__ int fast_score(const int (&d)[16], bool centreBrighter) {
-    int e[16];
-#pragma unroll
-    for (int k = 0; k < 16; k++) e[k] = centreBrighter ? d[k] : -d[k];
-    int mn2[16];
-#pragma unroll
-    for (int k = 0; k < 16; k++) mn2[k] = min(e[k], e[(k + 1) & 15]);
-    int mn4[16];
-#pragma unroll
-    for (int k = 0; k < 16; k++) mn4[k] = min(mn2[k], mn2[(k + 2) & 15]);
-    int best = -256;
-#pragma unroll
-    for (int k = 0; k < 16; k++) best = max(best, min(min(mn4[k], mn4[(k + 4) & 15]), e[(k + 8) & 15]));
-    return best - 1;
-}
-
-__global__ void __launch_bounds__(256) k_fast(const __grid_constant__ TmapPack maps, const DevPlan* __restrict__ P,
-                                              u64* __restrict__ cand, int* __restrict__ candCount,
-                                              int* __restrict__ err, const uint8_t* __restrict__ pyr, int noTma) {
-    extern __shared__ __align__(128) uint8_t fast_smem[];
-    uint8_t* smem = fast_smem;
-    const int f = blockIdx.y;
-    const int c = blockIdx.x;
-    int level = 0;
-    while (level + 1 < P->nlevels && c >= P->lv[level + 1].cellBase) level++;
-    const LevelGeo& G = P->lv[level];
-    const int ci = (c - G.cellBase) / G.nCols, cj = (c - G.cellBase) % G.nCols;
-    const int e = P->edge;
-    const int ox = e - 3 + cj * G.wCell, oy = e - 3 + ci * G.hCell;  // ROI origin (level pixels)
-    // TMA tile mode needs the box start 16-byte aligned in the innermost dimension (an unaligned x coordinate
-    // faults with "illegal instruction" on sm_100a): fetch from ox rounded down, address the tile with xoff.
-    const int oxa = ox & ~15, xoff = ox - oxa;
-    const int dw = min(G.wCell, (G.w - e) - (ox + 3));               // detection area of this cell
-    const int dh = min(G.hCell, (G.h - e) - (oy + 3));
-    if (dw <= 0 || dh <= 0) return;
-
-    const int boxW = G.boxW, boxH = G.boxH;
-    const int SP = G.wCell + 2;  // score pitch (1-px zero ring)
-    uint8_t* tile = smem;
-    const int tileBytes = (boxW * boxH + 127) & ~127;
-    uint8_t* score = smem + tileBytes;
-    const int scoreBytes = (SP * (G.hCell + 2) + 15) & ~15;
-    u64* staging = (u64*)(score + scoreBytes);
-    u64* mbar = staging + G.maxSurv;
-    int* sh = (int*)(mbar + 1);  // [0] survivor count, [1] global base
-
-    const int tid = threadIdx.x;
-    const uint32_t bar = smem_u32(mbar);
-    if (tid == 0) {
-        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        sh[0] = 0;
-    }
-    for (int i = tid; i < scoreBytes / 4; i += blockDim.x) ((uint32_t*)score)[i] = 0;
-    __syncthreads();
-    if (noTma) {  // development aid (ORBX_NO_TMA=1): same tile through ordinary loads
-        const uint8_t* src = pyr + G.pyrOff + (long long)f * G.frameStride;
-        for (int i = tid; i < boxW * boxH; i += blockDim.x) {
-            const int x = oxa + i % boxW, y = oy + i / boxW;
-            tile[i] = (x < G.w && y < G.h) ? src[(long long)y * G.pitch + x] : 0;
-        }
-        __syncthreads();
-    } else if (tid == 0) {
-        const uint32_t bytes = (uint32_t)(boxW * boxH);
-        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-        asm volatile(
-            "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
-            ::"r"(smem_u32(tile)), "l"(&maps.m[level]), "r"(oxa), "r"(oy), "r"(f), "r"(bar)
-            : "memory");
-    }
-    if (!noTma) {   // bounded wait on phase 0 (a lost TMA must not hang the GPU: flag the error and bail out)
-        uint32_t done = 0;
-        int spins = 0;
-        while (!done) {
-            asm volatile(
-                "{\n\t.reg .pred p;\n\t"
-                "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-                "selp.u32 %0, 1, 0, p;\n\t}"
-                : "=r"(done)
-                : "r"(bar), "r"(0u)
-                : "memory");
-            if (!done && ++spins > (1 << 22)) {
-                atomicExch(err, 2);
-                break;
-            }
-        }
-    }
-
-    const int th = P->minTh;
-    const int npx = dw * dh;
-    for (int p = tid; p < npx; p += blockDim.x) {
-        const int yin = p / dw, xin = p - yin * dw;
-        const uint8_t* q = tile + (yin + 3) * boxW + (xin + 3 + xoff);
-        const int v = q[0];
-        // compass pre-test: every arc of 9 contains at least two of the four compass points
-        const int c0 = q[3 * boxW], c4 = q[3], c8 = q[-3 * boxW], c12 = q[-3];
-        const int hi = v + th, lo = v - th;
-        const int nb = (c0 > hi) + (c4 > hi) + (c8 > hi) + (c12 > hi);
-        const int nd = (c0 < lo) + (c4 < lo) + (c8 < lo) + (c12 < lo);
-        if (nb < 2 && nd < 2) continue;
-        int d[16];
-        d[0] = v - c0;
-        d[1] = v - q[3 * boxW + 1];
-        d[2] = v - q[2 * boxW + 2];
-        d[3] = v - q[boxW + 3];
-        d[4] = v - c4;
-        d[5] = v - q[-boxW + 3];
-        d[6] = v - q[-2 * boxW + 2];
-        d[7] = v - q[-3 * boxW + 1];
-        d[8] = v - c8;
-        d[9] = v - q[-3 * boxW - 1];
-        d[10] = v - q[-2 * boxW - 2];
-        d[11] = v - q[-boxW - 3];
-        d[12] = v - c12;
-        d[13] = v - q[boxW - 3];
-        d[14] = v - q[2 * boxW - 2];
-        d[15] = v - q[3 * boxW - 1];
-        uint32_t mb = 0, md = 0;  // circle brighter than centre (d < -th) / darker (d > th)
-#pragma unroll
-        for (int k = 0; k < 16; k++) {
-            mb |= (uint32_t)(d[k] < -th) << k;
-            md |= (uint32_t)(d[k] > th) << k;
-        }
-        const bool dark = nine_contiguous(md);
-        if (dark || nine_contiguous(mb)) score[(yin + 1) * SP + xin + 1] = (uint8_t)fast_score(d, dark);
-    }
-    __syncthreads();
-
-    // cell-local NMS (strictly greater than all 8 neighbours); remember survivors as a per-thread bit mask
-    uint32_t surv = 0;
-    int anyIni = 0;
-    const int ini = P->iniTh;
-    {
-        int it = 0;
-        for (int p = tid; p < npx; p += blockDim.x, it++) {
-            const int yin = p / dw, xin = p - yin * dw;
-            const uint8_t* s = score + (yin + 1) * SP + xin + 1;
-            const int v = s[0];
-            if (v == 0) continue;
-            if (v > s[-1] && v > s[1] && v > s[-SP - 1] && v > s[-SP] && v > s[-SP + 1] && v > s[SP - 1] && v > s[SP] &&
-                v > s[SP + 1]) {
-                surv |= 1u << it;
-                anyIni |= (v >= ini);
-            }
-        }
-    }
-    const int useIni = __syncthreads_or(anyIni);
-    {
-        int it = 0;
-        for (int p = tid; p < npx; p += blockDim.x, it++) {
-            if (!((surv >> it) & 1u)) continue;
-            const int yin = p / dw, xin = p - yin * dw;
-            const int v = score[(yin + 1) * SP + xin + 1];
-            if (useIni && v < ini) continue;
-            const int slot = atomicAdd(&sh[0], 1);
-            if (slot < G.maxSurv) staging[slot] = cand_pack(v, ci, cj, yin, xin);
-        }
-    }
-    __syncthreads();
-    const int cnt = min(sh[0], G.maxSurv);
-    if (cnt == 0) return;
-    if (tid == 0) sh[1] = atomicAdd(&candCount[f * P->nlevels + level], cnt);
-    __syncthreads();
-    const int base = sh[1];
-    u64* out = cand + G.candOff + (long long)f * G.candCap;
-    for (int i = tid; i < cnt; i += blockDim.x) {
-        if (base + i < G.candCap) out[base + i] = staging[i];
-        else atomicExch(err, 3);
-    }
-}
+#include "orbx_fast.cuh"
 
 // ------------------------------------------------------------------------------------------------ K3 quadtree
 // DistributeOctTree without lists or pointers. Nodes live in shared memory as rectangles + key counts; every key
