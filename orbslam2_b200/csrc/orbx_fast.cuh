@@ -15,7 +15,7 @@
 //   TMA 3-D tile load (x start rounded down to 16 bytes — an unaligned innermost coordinate faults on sm_100a)
 //   phase 1  score map  (u8, value = score - (minTh-1), 0 = not a corner at minTh), same coordinates as the tile
 //   phase 2  SWAR non-maximum suppression, strictly greater than the 8 neighbours; a neighbour in another cell
-//            counts 0 (the reference runs cv::FAST per cell ROI), per-cell survivor counts (all / >= iniTh)
+//            counts 0 (the reference runs cv::FAST per cell ROI); survivors compacted into a shared-memory list
 //   phase 3  per cell: keep survivors >= iniTh if any exist, else all; one global atomic per CTA; emit records.
 #pragma once
 #include "orbx_internal.cuh"
@@ -72,7 +72,7 @@ struct FastSmemHdr {
     int nAll[FAST_MAX_ST_CELLS];
     int nIni[FAST_MAX_ST_CELLS];
     int emitBase[FAST_MAX_ST_CELLS];
-    int total, gbase, slot, pad;
+    int total, gbase, slot, nList;
     unsigned firstCol[64], lastCol[64];  // per word column: bytes that are the first / last column of a cell
     unsigned char rowFlag[128];          // per detection row: bit0 first row of a cell, bit1 last row
 };
@@ -111,6 +111,7 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast(const __grid_constant__ T
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         H->total = 0;
         H->slot = 0;
+        H->nList = 0;
     }
     if (tid < FAST_MAX_ST_CELLS) {
         H->nAll[tid] = 0;
@@ -168,10 +169,11 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast(const __grid_constant__ T
     const int minTh = P->minTh, iniTh = P->iniTh;
     const unsigned negThm1 = (unsigned)((-(minTh - 1)) & 0xFFFF) * 0x10001u;
     const int nUnits = nW * nR;
+    const unsigned divW = (1048576u + nW - 1) / nW;  // u / nW == (u * divW) >> 20 for u < 16384
 
     // ---- phase 1: scores
     for (int u = tid; u < nUnits; u += FAST_THREADS) {
-        const int wy = u / nW, wi = u - wy * nW;
+        const int wy = (int)(((unsigned)u * divW) >> 20), wi = u - wy * nW;
         const int wx = wx0 + wi;
         const unsigned* r0 = tile + (wy + 3) * pitchW + wx;  // centre row
         unsigned cw[16];  // aligned circle words, Bresenham order (dx,dy): (0,3)(1,3)(2,2)(3,1)(3,0)(3,-1)(2,-2)(1,-3)(0,-3)...
@@ -230,51 +232,58 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast(const __grid_constant__ T
     }
     __syncthreads();
 
-    // ---- phase 2: NMS (strictly greater than all 8 neighbours of the same cell); survivors go to `tile`
+    // ---- phase 2: NMS (strictly greater than all 8 neighbours of the same cell); survivors are compacted into a
+    // list (packed wy<<16 | x<<8 | value) that overlays the no-longer-needed pixel tile
+    unsigned* list = tile;
+    const int listCap = tileBytes >> 2;
     for (int u = tid; u < nUnits; u += FAST_THREADS) {
-        const int wy = u / nW, wi = u - wy * nW;
+        const int wy = (int)(((unsigned)u * divW) >> 20), wi = u - wy * nW;
         const int wx = wx0 + wi;
         const unsigned* q = sc + (wy + 3) * pitchW + wx;
         const unsigned s = q[0];
-        unsigned surv = 0;
-        if (s) {
-            const unsigned s7 = s & 0x7f7f7f7fu;
-            const unsigned nfc = ~H->firstCol[wi], nlc = ~H->lastCol[wi];
-            const unsigned rf = H->rowFlag[wy];
-            unsigned ok = bytes_gt(s, s7, __byte_perm(q[-1], s, 0x6543) & nfc) & bytes_gt(s, s7, __byte_perm(s, q[1], 0x4321) & nlc);
-            if (!(rf & 1)) {
-                const unsigned* r = q - pitchW;
-                const unsigned a = r[-1], b = r[0], c = r[1];
-                ok &= bytes_gt(s, s7, __byte_perm(a, b, 0x6543) & nfc) & bytes_gt(s, s7, b) &
-                      bytes_gt(s, s7, __byte_perm(b, c, 0x4321) & nlc);
-            }
-            if (!(rf & 2)) {
-                const unsigned* r = q + pitchW;
-                const unsigned a = r[-1], b = r[0], c = r[1];
-                ok &= bytes_gt(s, s7, __byte_perm(a, b, 0x6543) & nfc) & bytes_gt(s, s7, b) &
-                      bytes_gt(s, s7, __byte_perm(b, c, 0x4321) & nlc);
-            }
-            ok &= 0x80808080u;  // a zero byte never beats its own "neighbour" comparisons' carry: s > n fails for s = 0
-            if (ok) {
-                const int cyl = wy / G.hCell;
-                const int xb = oxa + (wx << 2) - xFirst;
-#pragma unroll
-                for (int b = 0; b < 4; b++) {
-                    if (ok & (0x80u << (8 * b))) {
-                        const int v = (s >> (8 * b)) & 0xFF;
-                        const int cell = cyl * G.stCX + (xb + b) / G.wCell;
-                        atomicAdd(&H->nAll[cell], 1);
-                        if (v + minTh - 1 >= iniTh) atomicAdd(&H->nIni[cell], 1);
-                        surv |= (unsigned)v << (8 * b);
-                    }
-                }
-            }
+        if (!s) continue;
+        const unsigned s7 = s & 0x7f7f7f7fu;
+        const unsigned nfc = ~H->firstCol[wi], nlc = ~H->lastCol[wi];
+        const unsigned rf = H->rowFlag[wy];
+        unsigned ok = bytes_gt(s, s7, __byte_perm(q[-1], s, 0x6543) & nfc) & bytes_gt(s, s7, __byte_perm(s, q[1], 0x4321) & nlc);
+        if (!(rf & 1)) {
+            const unsigned* r = q - pitchW;
+            const unsigned a = r[-1], b = r[0], c = r[1];
+            ok &= bytes_gt(s, s7, __byte_perm(a, b, 0x6543) & nfc) & bytes_gt(s, s7, b) &
+                  bytes_gt(s, s7, __byte_perm(b, c, 0x4321) & nlc);
         }
-        tile[(wy + 3) * pitchW + wx] = surv;
+        if (!(rf & 2)) {
+            const unsigned* r = q + pitchW;
+            const unsigned a = r[-1], b = r[0], c = r[1];
+            ok &= bytes_gt(s, s7, __byte_perm(a, b, 0x6543) & nfc) & bytes_gt(s, s7, b) &
+                  bytes_gt(s, s7, __byte_perm(b, c, 0x4321) & nlc);
+        }
+        ok &= 0x80808080u;  // (a zero byte is never greater than anything, so non-corners drop out here)
+        if (ok) {
+            const int n = __popc(ok);
+            int pos = atomicAdd(&H->nList, n);
+            const int base = (wy << 16) + (((wx << 2) + oxa - xFirst) << 8);  // x of byte 0 may be < 0 (masked bytes)
+#pragma unroll
+            for (int b = 0; b < 4; b++)
+                if ((ok >> (8 * b + 7)) & 1u) {
+                    if (pos < listCap) list[pos] = (unsigned)(base + (b << 8) + (int)((s >> (8 * b)) & 0xFFu));
+                    pos++;
+                }
+        }
+    }
+    __syncthreads();
+    // per-cell counts (all survivors / survivors >= iniTh)
+    const int nList = min(H->nList, listCap);
+    for (int i = tid; i < nList; i += FAST_THREADS) {
+        const unsigned r = list[i];
+        const int wy = r >> 16, x = (r >> 8) & 0xFF, v = r & 0xFF;
+        const int cell = (wy / G.hCell) * G.stCX + x / G.wCell;
+        atomicAdd(&H->nAll[cell], 1);
+        if (v + minTh - 1 >= iniTh) atomicAdd(&H->nIni[cell], 1);
     }
     __syncthreads();
 
-    // ---- phase 3: per-cell rule, one global reservation per CTA
+    // ---- phase 3: per-cell rule, one global reservation per CTA, emit
     if (tid == 0) {
         int tot = 0;
         for (int c = 0; c < G.stCX * G.stCY; c++) tot += H->nIni[c] > 0 ? H->nIni[c] : H->nAll[c];
@@ -285,23 +294,15 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast(const __grid_constant__ T
     if (H->total == 0) return;
     const int gbase = H->gbase;
     u64* out = cand + G.candOff + (long long)f * G.candCap;
-    for (int u = tid; u < nUnits; u += FAST_THREADS) {
-        const int wy = u / nW, wi = u - wy * nW;
-        const int wx = wx0 + wi;
-        const unsigned s = tile[(wy + 3) * pitchW + wx];
-        if (!s) continue;
+    for (int i = tid; i < nList; i += FAST_THREADS) {
+        const unsigned r = list[i];
+        const int wy = r >> 16, x = (r >> 8) & 0xFF, v = r & 0xFF;
         const int cyl = wy / G.hCell, yin = wy - cyl * G.hCell;
-        const int xb = oxa + (wx << 2) - xFirst;
-#pragma unroll
-        for (int b = 0; b < 4; b++) {
-            const int v = (s >> (8 * b)) & 0xFF;
-            if (!v) continue;
-            const int cxl = (xb + b) / G.wCell, xin = (xb + b) - cxl * G.wCell;
-            const int score = v + minTh - 1;
-            if (H->nIni[cyl * G.stCX + cxl] > 0 && score < iniTh) continue;
-            const int slot = gbase + atomicAdd(&H->slot, 1);
-            if (slot < G.candCap) out[slot] = cand_pack(score, ci0 + cyl, cj0 + cxl, yin, xin);
-            else atomicExch(err, 3);
-        }
+        const int cxl = x / G.wCell, xin = x - cxl * G.wCell;
+        const int score = v + minTh - 1;
+        if (H->nIni[cyl * G.stCX + cxl] > 0 && score < iniTh) continue;
+        const int slot = gbase + atomicAdd(&H->slot, 1);
+        if (slot < G.candCap) out[slot] = cand_pack(score, ci0 + cyl, cj0 + cxl, yin, xin);
+        else atomicExch(err, 3);
     }
 }
