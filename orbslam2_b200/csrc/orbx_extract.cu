@@ -212,8 +212,8 @@ static int build_plan(orbx_handle* h, int w, int hgt, int batch) {
         maxSel = std::max(maxSel, G.selCap);
         G.scale = h->sf[l];
         G.sizeField = (float)(int)(p.patchSize * h->sf[l]);  // src/ORBextractor.cc:831
-        G.blurTilesX = (G.w + BLUR_TW - 1) / BLUR_TW;
-        G.blurTilesY = (G.h + BLUR_TH - 1) / BLUR_TH;
+        G.blurTilesX = (G.w + 127) / 128;
+        G.blurTilesY = (G.h + BLUR_ROWS - 1) / BLUR_ROWS;
         G.blurTileBase = blurBase;
         blurBase += G.blurTilesX * G.blurTilesY;
         if (l > 0) {
@@ -286,7 +286,7 @@ extern "C" int orbx_create(const orbx_params* p, int device, orbx_t** out) {
     if (p->nfeatures < 1 || !(p->scaleFactor > 1.0f)) FAIL(ORBX_EINVAL, "nfeatures >= 1 and scaleFactor > 1 required");
     if (p->minThFAST < 1 || p->iniThFAST < p->minThFAST || p->iniThFAST > 254)
         FAIL(ORBX_EINVAL, "need 1 <= minThFAST <= iniThFAST <= 254");
-    if (p->halfPatchSize < 1 || p->halfPatchSize > 31 || p->patchSize < 1) FAIL(ORBX_EINVAL, "halfPatchSize in [1,31]");
+    if (p->halfPatchSize < 1 || p->halfPatchSize > 15 || p->patchSize < 1) FAIL(ORBX_EINVAL, "halfPatchSize in [1,15]");
     if (p->edgeThreshold < 19 || p->edgeThreshold < p->halfPatchSize + 4)
         FAIL(ORBX_EINVAL, "edgeThreshold must cover the descriptor reach (>= 19) and the orientation patch");
     int ndev = 0;
@@ -308,7 +308,7 @@ extern "C" int orbx_create(const orbx_params* p, int device, orbx_t** out) {
     for (int i = 0; i < 8; i++) cudaEventCreate(&h->ev[i]);
     cudaMalloc(&h->dErr, sizeof(int));
     cudaMemset(h->dErr, 0, sizeof(int));
-    cudaMemcpyToSymbol(c_pattern, kOrbPattern, 1024);
+    cudaMemcpyToSymbol(d_pattern, kOrbPattern, 1024);
     *out = h;
     return ORBX_OK;
 }
@@ -428,10 +428,10 @@ extern "C" int orbx_extract_batch(orbx_t* h, const uint8_t* imgs, int batch, int
                                                                   h->dSelCount, h->qtC, h->qtC2, h->dErr);
     KCHECK(h, "k_quadtree");
     stamp(h, 4);
-    k_blur<<<dim3(D.totalBlurTiles, batch), 256, 0, st>>>(h->dPlan, h->dPyr, h->dBlur);
+    k_blur<<<dim3((D.totalBlurTiles + BLUR_WARPS - 1) / BLUR_WARPS, batch), 32 * BLUR_WARPS, 0, st>>>(h->dPlan, h->dPyr, h->dBlur);
     KCHECK(h, "k_blur");
     stamp(h, 5);
-    k_orient_desc<<<dim3((D.selStride + 7) / 8, batch), 256, 0, st>>>(h->dPlan, h->dPyr, h->dBlur, h->dSel, h->dSelCount,
+    k_orient_desc<<<dim3((D.selStride + 8 * DESC_KPW - 1) / (8 * DESC_KPW), batch), 256, 0, st>>>(h->dPlan, h->dPyr, h->dBlur, h->dSel, h->dSelCount,
                                                                       h->dKps, h->dDesc, h->dNOut);
     KCHECK(h, "k_orient_desc");
     stamp(h, 6);

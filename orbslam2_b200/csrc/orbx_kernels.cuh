@@ -10,7 +10,6 @@
 #include "orbx_internal.cuh"
 #include "../../include/orbx_pattern.inc"
 
-__device__ __constant__ signed char c_pattern[1024];
 
 // ------------------------------------------------------------------------------------------------ helpers
 __device__ __forceinline__ int reflect101(int p, int len) {
@@ -388,152 +387,10 @@ __global__ void k_quadtree(const DevPlan* __restrict__ P, const u64* __restrict_
 }
 
 // ------------------------------------------------------------------------------------------------ K4 blur
-// 7x7 Gaussian, sigma 2, OpenCV 8U fixed point: taps {18,34,48,56,48,34,18}/256 per axis, exact 16/32-bit
-// accumulation, single rounding (sum + 32768) >> 16. BORDER_REFLECT_101 by index reflection on the tile load.
-// One CTA = 64 x 16 output tile of one level of one frame (fused launch over all levels).
-#define BLUR_TW 64
-#define BLUR_TH 16
-__global__ void __launch_bounds__(256) k_blur(const DevPlan* __restrict__ P, const uint8_t* __restrict__ pyr,
-                                              uint8_t* __restrict__ blur) {
-    __shared__ uint8_t raw[BLUR_TH + 6][BLUR_TW + 8];
-    __shared__ uint16_t hb[BLUR_TH + 6][BLUR_TW];
-    const int f = blockIdx.y;
-    int t = blockIdx.x, level = 0;
-    while (level + 1 < P->nlevels && t >= P->lv[level + 1].blurTileBase) level++;
-    const LevelGeo& G = P->lv[level];
-    t -= G.blurTileBase;
-    const int tx = t % G.blurTilesX, ty = t / G.blurTilesX;
-    const int x0 = tx * BLUR_TW, y0 = ty * BLUR_TH;
-    const uint8_t* src = pyr + G.pyrOff + (long long)f * G.frameStride;
-    const int tid = threadIdx.x;
-    for (int i = tid; i < (BLUR_TH + 6) * (BLUR_TW + 6); i += 256) {
-        const int ry = i / (BLUR_TW + 6), rx = i - ry * (BLUR_TW + 6);
-        const int gx = reflect101(min(x0 + rx - 3, G.w + 2), G.w), gy = reflect101(min(y0 + ry - 3, G.h + 2), G.h);
-        raw[ry][rx] = src[(long long)gy * G.pitch + gx];
-    }
-    __syncthreads();
-    for (int i = tid; i < (BLUR_TH + 6) * BLUR_TW; i += 256) {
-        const int ry = i / BLUR_TW, rx = i - ry * BLUR_TW;
-        const uint8_t* r = &raw[ry][rx];
-        hb[ry][rx] = (uint16_t)(18 * (r[0] + r[6]) + 34 * (r[1] + r[5]) + 48 * (r[2] + r[4]) + 56 * r[3]);
-    }
-    __syncthreads();
-    uint8_t* dst = blur + G.pyrOff + (long long)f * G.frameStride;
-    for (int i = tid; i < BLUR_TH * BLUR_TW; i += 256) {
-        const int oy = i / BLUR_TW, ox = i - oy * BLUR_TW;
-        const int gx = x0 + ox, gy = y0 + oy;
-        if (gx < G.w && gy < G.h) {
-            const uint32_t acc = 18u * (hb[oy][ox] + hb[oy + 6][ox]) + 34u * (hb[oy + 1][ox] + hb[oy + 5][ox]) +
-                                 48u * (hb[oy + 2][ox] + hb[oy + 4][ox]) + 56u * hb[oy + 3][ox];
-            dst[(long long)gy * G.pitch + gx] = (uint8_t)((acc + 32768u) >> 16);
-        }
-    }
-}
+#include "orbx_blur.cuh"
 
 // ------------------------------------------------------------------------------------------------ K5 orientation + descriptor
-// One warp per selected keypoint slot. Orientation: lanes = the 31 rows of the circular patch, integer moments,
-// warp-shuffle reduction, OpenCV's fastAtan2 polynomial evaluated without FMA contraction. Descriptor: lane i
-// produces byte i (pairs 8i..8i+7) from the blurred level with the reference's float rotate + round-half-even.
-__device__ __forceinline__ float fast_atan2_deg(float y, float x) {
-    const float scale = (float)(180.0 / 3.141592653589793238462643383279502884);
-    const float p1 = 0.9997878412794807f * scale, p3 = -0.3258083974640975f * scale;
-    const float p5 = 0.1555786518463281f * scale, p7 = -0.04432655554792128f * scale;
-    const float eps = 2.2204460492503131e-16f;  // (float)DBL_EPSILON
-    const float ax = fabsf(x), ay = fabsf(y);
-    float a, c, c2;
-    if (ax >= ay) {
-        c = __fdiv_rn(ay, __fadd_rn(ax, eps));
-        c2 = __fmul_rn(c, c);
-        a = __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(p7, c2), p5), c2), p3), c2), p1), c);
-    } else {
-        c = __fdiv_rn(ax, __fadd_rn(ay, eps));
-        c2 = __fmul_rn(c, c);
-        a = __fsub_rn(90.f,
-                      __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(p7, c2), p5), c2), p3), c2), p1), c));
-    }
-    if (x < 0) a = __fsub_rn(180.f, a);
-    if (y < 0) a = __fsub_rn(360.f, a);
-    return a;
-}
-
-__global__ void __launch_bounds__(256) k_orient_desc(const DevPlan* __restrict__ P, const uint8_t* __restrict__ pyr,
-                                                     const uint8_t* __restrict__ blur, const uint2* __restrict__ sel,
-                                                     const int* __restrict__ selCount, orbx_kp* __restrict__ kps,
-                                                     uint8_t* __restrict__ desc, int* __restrict__ nOut) {
-    const int lane = threadIdx.x & 31;
-    const int slot = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    const int f = blockIdx.y;
-    if (slot >= P->selStride) return;
-    const int nl = P->nlevels;
-    int level = 0;
-    while (level + 1 < nl && slot >= P->lv[level + 1].selOff) level++;
-    const LevelGeo& G = P->lv[level];
-    const int idx = slot - G.selOff;
-    const int* sc = selCount + f * nl;
-    int before = 0, total = 0;
-    for (int l = 0; l < nl; l++) {
-        const int c = sc[l];
-        if (l < level) before += c;
-        total += c;
-    }
-    if (slot == 0 && lane == 0) nOut[f] = total;
-    if (idx >= sc[level]) return;
-    const uint2 s = sel[(long long)f * P->selStride + slot];
-    const int x = s.x & 0xFFFF, y = s.x >> 16;
-    const uint8_t* img = pyr + G.pyrOff + (long long)f * G.frameStride + (long long)y * G.pitch + x;
-
-    // IC_Angle
-    const int hp = P->halfPatch;
-    int m10 = 0, m01 = 0;
-    for (int v = lane - hp; v <= hp; v += 32) {
-        const int d = P->umax[v < 0 ? -v : v];
-        const uint8_t* r = img + (long long)v * G.pitch;
-        int rs = 0;
-        for (int u = -d; u <= d; u++) {
-            const int val = r[u];
-            m10 += u * val;
-            rs += val;
-        }
-        m01 += v * rs;
-    }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        m10 += __shfl_xor_sync(0xffffffffu, m10, o);
-        m01 += __shfl_xor_sync(0xffffffffu, m01, o);
-    }
-    const float angle = fast_atan2_deg((float)m01, (float)m10);
-
-    // steered BRIEF on the blurred level
-    const float factorPI = (float)(3.1415926535897932384626433832795 / 180.f);
-    const float rad = __fmul_rn(angle, factorPI);
-    const float a = (float)cos((double)rad), b = (float)sin((double)rad);
-    const uint8_t* ctr = blur + G.pyrOff + (long long)f * G.frameStride + (long long)y * G.pitch + x;
-    const signed char* pat = c_pattern + lane * 32;
-    int val = 0;
-#pragma unroll
-    for (int k = 0; k < 8; k++) {
-        const float x1 = (float)pat[4 * k], y1 = (float)pat[4 * k + 1], x2 = (float)pat[4 * k + 2], y2 = (float)pat[4 * k + 3];
-        const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, b), __fmul_rn(y1, a)));
-        const int c1 = __float2int_rn(__fsub_rn(__fmul_rn(x1, a), __fmul_rn(y1, b)));
-        const int r2 = __float2int_rn(__fadd_rn(__fmul_rn(x2, b), __fmul_rn(y2, a)));
-        const int c2 = __float2int_rn(__fsub_rn(__fmul_rn(x2, a), __fmul_rn(y2, b)));
-        const int t0 = ctr[(long long)r1 * G.pitch + c1], t1 = ctr[(long long)r2 * G.pitch + c2];
-        val |= (t0 < t1) << k;
-    }
-    const long long o = (long long)f * P->selStride + before + idx;
-    desc[o * 32 + lane] = (uint8_t)val;
-    if (lane == 0) {
-        orbx_kp k;
-        k.x = (level == 0) ? (float)x : __fmul_rn((float)x, G.scale);
-        k.y = (level == 0) ? (float)y : __fmul_rn((float)y, G.scale);
-        k.size = G.sizeField;
-        k.angle = angle;
-        k.response = (float)s.y;
-        k.octave = level;
-        k.class_id = -1;
-        kps[o] = k;
-    }
-}
+#include "orbx_desc.cuh"
 
 // ------------------------------------------------------------------------------------------------ K6 export
 // Copy one level of one frame into a dense (w+2e) x (h+2e) buffer with the BORDER_REFLECT_101 frame (e may be 0).
