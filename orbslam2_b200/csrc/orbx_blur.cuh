@@ -5,12 +5,12 @@
 // One warp = 128 px x BLUR_ROWS output rows of one level of one frame; a thread owns 4 adjacent pixels (one aligned
 // 32-bit word) and slides down the rows, so every input row is loaded and filtered horizontally once per strip:
 //   horizontal: two pixels per register in 16-bit lanes (a row sum is <= 255*256 = 65280, it fits), taps by IMAD;
-//   vertical:   32-bit per pixel over a 7-row register window (loop fully unrolled, so the window is renamed, not moved);
+//   vertical:   32-bit per pixel over a 7-row register window (loop unrolled by the window period 7, so the window is renamed, not moved);
 //   reflect-101: row index reflection for y; left edge by byte permutation, right edge by an 8-byte gather (last lanes only).
 #pragma once
 #include "orbx_internal.cuh"
 
-#define BLUR_ROWS 32
+#define BLUR_ROWS 36  // + 6 halo rows = 42 = 6 x 7: the 7-row window unrolls exactly (small code, no i-cache misses)
 #define BLUR_WARPS 4
 
 __device__ __forceinline__ int blur_reflect(int p, int len) {
@@ -44,9 +44,11 @@ __global__ void __launch_bounds__(32 * BLUR_WARPS) k_blur(const DevPlan* __restr
     for (int j = 0; j < 8; j++) ridx[j] = redge ? blur_reflect(x0 + j, w) - x0 : j;
 
     unsigned hw[7][4];  // horizontal sums of the last 7 input rows, one 32-bit value per pixel
+    static_assert((BLUR_ROWS + 6) % 7 == 0, "row loop is unrolled by the window period");
+    for (int ib = 0; ib < BLUR_ROWS + 6; ib += 7)
 #pragma unroll
-    for (int i = 0; i < BLUR_ROWS + 6; i++) {
-        const int yin = y0 + i - 3;
+    for (int i = 0; i < 7; i++) {   // i = row phase inside the 7-row window; absolute input row = ib + i
+        const int yin = y0 + ib + i - 3;
         if (yin - 3 < h) {  // rows whose outputs all lie below the image are not needed
             const uint8_t* row = src + (long long)blur_reflect(yin, h) * G.pitch;
             const uint8_t* rp = row + x0;
@@ -76,9 +78,9 @@ __global__ void __launch_bounds__(32 * BLUR_WARPS) k_blur(const DevPlan* __restr
             hw[i % 7][2] = he >> 16;
             hw[i % 7][3] = ho >> 16;
         }
-        if (i >= 6) {
-            const int yout = y0 + i - 6;
-            if (yout < h) {
+        {
+            const int yout = y0 + ib + i - 6;
+            if (ib + i >= 6 && yout < h) {
                 // window rows: oldest = (i+1)%7 ... newest = i%7
                 unsigned out = 0;
 #pragma unroll

@@ -217,8 +217,13 @@ static int build_plan(orbx_handle* h, int w, int hgt, int batch) {
         G.blurTileBase = blurBase;
         blurBase += G.blurTilesX * G.blurTilesY;
         if (l > 0) {
+            if (tabs.size() & 1) tabs.push_back(make_int2(0, 0));  // 16-byte alignment of the x table
             G.xtabOff = (int)tabs.size();
             linear_table(D.lv[l - 1].w, G.w, true, tabs);
+            while ((tabs.size() - G.xtabOff) & 3) tabs.push_back(tabs.back());
+            G.resizeFast = !(D.lv[l - 1].w == 2 * G.w && D.lv[l - 1].h == 2 * G.h);
+            for (size_t i = G.xtabOff; i + 3 < tabs.size(); i += 4)
+                if (tabs[i + 3].x - tabs[i].x > 6 || tabs[i + 3].x < tabs[i].x) G.resizeFast = 0;
             G.ytabOff = (int)tabs.size();
             linear_table(D.lv[l - 1].h, G.h, false, tabs);
         }
@@ -417,7 +422,8 @@ extern "C" int orbx_extract_batch(orbx_t* h, const uint8_t* imgs, int batch, int
     for (int l = 1; l < nl; l++) {
         const LevelGeo& G = D.lv[l];
         dim3 grid((G.w + 255) / 256, (G.h + 3) / 4, batch), block(64, 4);
-        k_resize<<<grid, block, 0, st>>>(h->dPlan, l, h->dPyr, h->dTabs);
+        if (G.resizeFast) k_resize_fast<<<grid, block, 0, st>>>(h->dPlan, l, h->dPyr, h->dTabs);
+        else k_resize<<<grid, block, 0, st>>>(h->dPlan, l, h->dPyr, h->dTabs);
         KCHECK(h, "k_resize");
     }
     stamp(h, 2);

@@ -47,7 +47,8 @@ struct LevelGeo {
     int selCap, selOff;     // selected-keypoint capacity, offset inside a frame's selection row
     float scale;            // mvScaleFactor[level]
     float sizeField;        // (int)(patchSize*scale)
-    int xtabOff, ytabOff;   // offsets (in int2) of the bilinear tables
+    int xtabOff, ytabOff;   // offsets (in int2) of the bilinear tables (x table padded to a multiple of 4 entries)
+    int resizeFast;         // 1: k_resize_fast applies (4 output pixels read <= 8 source bytes)
     int blurTileBase, blurTilesX, blurTilesY;
 };
 

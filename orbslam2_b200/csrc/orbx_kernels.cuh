@@ -131,6 +131,8 @@ __global__ void __launch_bounds__(256) k_resize(const DevPlan* __restrict__ P, i
     *(uint32_t*)dst = out;
 }
 
+#include "orbx_resize.cuh"
+
 // ------------------------------------------------------------------------------------------------ K2 FAST
 #include "orbx_fast.cuh"
 

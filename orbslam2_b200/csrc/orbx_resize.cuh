@@ -1,0 +1,58 @@
+// orbx_resize.cuh — K1 k_resize_fast: one pyramid level from the previous one, cv::resize INTER_LINEAR on 8-bit data.
+// Reference: ORBextractor::ComputePyramid, /root/reference/src/ORBextractor.cc:921-946 (resize at :934).
+// OpenCV's 8U bilinear is fixed point (11-bit coefficients):
+//     H(row, d) = S[row][s_d] * a0_d + S[row][s_d + 1] * a1_d
+//     dst = (((b0 * (H(y0, d) >> 4)) >> 16) + ((b1 * (H(y1, d) >> 4)) >> 16) + 2) >> 2
+// with {s_d, a0_d, a1_d} / {y0, b0, b1} from tables built on the host with OpenCV's own float expressions.
+//
+// One thread = 4 adjacent output pixels of one row. For down-scaling factors <= 2 their source pixels span at most 8
+// bytes, so each of the two source rows is read as 3 aligned words, funnel-shifted to the first source pixel, and a
+// pixel's (S[s], S[s+1]) pair is one PRMT; the horizontal blend is one DP2A against the table's packed (a0, a1).
+// Down-scaling factors > 2 and OpenCV's exact-2x INTER_AREA shortcut use the generic k_resize.
+#pragma once
+#include "orbx_internal.cuh"
+
+__device__ __forceinline__ unsigned dp2a_lo_u32(unsigned a16x2, unsigned b8x4, unsigned c) {
+    unsigned d;
+    asm("dp2a.lo.u32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a16x2), "r"(b8x4), "r"(c));
+    return d;
+}
+
+__global__ void __launch_bounds__(256) k_resize_fast(const DevPlan* __restrict__ P, int level, uint8_t* __restrict__ pyr,
+                                                     const int2* __restrict__ tabs) {
+    const LevelGeo& D = P->lv[level];
+    const LevelGeo& S = P->lv[level - 1];
+    const int x4 = (blockIdx.x * 64 + threadIdx.x) * 4;
+    const int y = blockIdx.y * 4 + threadIdx.y;
+    const int f = blockIdx.z;
+    if (x4 >= D.w || y >= D.h) return;
+    const uint8_t* src = pyr + S.pyrOff + (long long)f * S.frameStride;
+    const int2 ty = tabs[D.ytabOff + y];
+    const int sy0 = min(max(ty.x, 0), S.h - 1), sy1 = min(max(ty.x + 1, 0), S.h - 1);
+    const unsigned b0s = (unsigned)(ty.y & 0xffff) << 16, b1s = (unsigned)ty.y & 0xffff0000u;  // b << 16: (b*x)>>16 == umulhi
+    // x table: 4 entries {s, a0 | a1 << 16} (the table is padded to a multiple of 4 entries)
+    const uint4* xt = (const uint4*)(tabs + D.xtabOff + x4);
+    const uint4 t01 = xt[0], t23 = xt[1];
+    const int sx0 = (int)t01.x;
+    const int a0 = sx0 & ~3, sh = (sx0 & 3) * 8;
+    const unsigned* r0 = (const unsigned*)(src + (long long)sy0 * S.pitch + a0);
+    const unsigned* r1 = (const unsigned*)(src + (long long)sy1 * S.pitch + a0);
+    const unsigned u0 = r0[0], u1 = r0[1], u2 = r0[2];
+    const unsigned v0 = r1[0], v1 = r1[1], v2 = r1[2];
+    const unsigned ulo = __funnelshift_r(u0, u1, sh), uhi = __funnelshift_r(u1, u2, sh);  // source bytes sx0 .. sx0+7
+    const unsigned vlo = __funnelshift_r(v0, v1, sh), vhi = __funnelshift_r(v1, v2, sh);
+    const unsigned sx[4] = {t01.x, t01.z, t23.x, t23.z};
+    const unsigned cf[4] = {t01.y, t01.w, t23.y, t23.w};
+    unsigned out = 0;
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        const unsigned rel = min(sx[i] - (unsigned)sx0, 6u);   // <= 6 by construction; the clamp only guards the padding entries
+        const unsigned sel = rel * 0x11u + 0x10u;              // PRMT picks bytes (rel, rel+1) into byte 0, 1
+        const unsigned H0 = dp2a_lo_u32(cf[i], __byte_perm(ulo, uhi, sel), 0u);
+        const unsigned H1 = dp2a_lo_u32(cf[i], __byte_perm(vlo, vhi, sel), 0u);
+        const unsigned v = (__umulhi(b0s, H0 >> 4) + __umulhi(b1s, H1 >> 4) + 2u) >> 2;
+        out |= (v & 0xffu) << (8 * i);
+    }
+    if (x4 + 4 > D.w) out &= 0xffffffffu >> (8 * (x4 + 4 - D.w));  // keep the row padding zero
+    *(unsigned*)(pyr + D.pyrOff + (long long)f * D.frameStride + (long long)y * D.pitch + x4) = out;
+}
