@@ -49,6 +49,7 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=384, help="frames per step per GPU")
+    ap.add_argument("--chunk", type=int, default=0, help="frames per pipeline chunk of the host-buffer path (0 = default)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-match", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline leg")
@@ -92,12 +93,16 @@ class ClockSampler:
     def __init__(self, index):
         self.index = index
         self.proc = None
-        self.lines = []
+        self.lines = []      # (arrival time, csv line)
+        self.windows = []    # timed regions [t0, t1] (host clock); samples outside them are warm-up / idle
+
+    def mark(self, t0, t1):
+        self.windows.append((t0, t1))
 
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "200"], stdout=subprocess.PIPE,
+                                          "--format=csv,noheader,nounits", "-lms", "50"], stdout=subprocess.PIPE,
                                          stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
@@ -106,7 +111,7 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.lines.append(line.strip())
+            self.lines.append((time.perf_counter(), line.strip()))
 
     def stop(self):
         if not self.proc:
@@ -118,7 +123,8 @@ class ClockSampler:
             self.proc.kill()
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ln in self.lines:
+        inside = [ln for t, ln in self.lines if any(a <= t <= b + 0.05 for a, b in self.windows)]
+        for ln in (inside if len(inside) >= 3 or not self.lines else [ln for _, ln in self.lines]):
             c = [x.strip() for x in ln.split(",")]
             if len(c) < 9:
                 continue
@@ -130,7 +136,7 @@ class ClockSampler:
                 if v.lower().startswith("active"):
                     reasons.add(nm)
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+                "reasons": sorted(reasons), "samples": len(sm), "samples_in_timed_regions": len(inside)}
 
 
 # ------------------------------------------------------------------------------------------------ CPU arm
@@ -275,24 +281,27 @@ def run_ours(args):
             fn()
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        th0 = time.perf_counter()
         e0.record(stream)
         for _ in range(steps):
             n = fn()
         e1.record(stream)
         barrier()
+        sampler.mark(th0, time.perf_counter())
         return e0.elapsed_time(e1) * 1e-3, n
 
     # ---- device-resident throughput (value) with per-stage CUDA events for the roofline of the dominant kernel
     ex.set_profiling(True)
-    for _ in range(args.warmup):
-        step_device()
-    barrier()
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
+    for _ in range(args.warmup):
+        step_device()
+    barrier()
     launches0 = ex.launch_count()
     stage_sum = {}
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    th0 = time.perf_counter()
     e0.record(stream)
     for _ in range(args.steps):
         n = step_device()
@@ -300,17 +309,20 @@ def run_ours(args):
             stage_sum[k] = stage_sum.get(k, 0.0) + v
     e1.record(stream)
     barrier()
+    sampler.mark(th0, time.perf_counter())
     t_dev = e0.elapsed_time(e1) * 1e-3
     launches = ex.launch_count() - launches0
-    clocks = sampler.stop() if rank == 0 else None
     n_out_mean = float(np.mean(n))
     t_dev = max_over_ranks(t_dev)
     value = world * B * args.steps / t_dev
     ex.set_profiling(False)
 
     # ---- end to end through the C ABI with host buffers
+    if args.chunk:
+        ex.set_chunk(args.chunk)
     t_e2e, _ = timed(step_host, args.steps, args.warmup)
     t_e2e = max_over_ranks(t_e2e)
+    clocks = sampler.stop() if rank == 0 else None
     e2e = world * B * args.steps / t_e2e
     h2d = B * W * H
     d2h = B * cap * (28 + 32) + B * 4 + 4

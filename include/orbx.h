@@ -75,6 +75,9 @@ int orbx_extract_batch(orbx_t* h, const uint8_t* imgs, int batch, int w, int hgt
                        orbx_kp* kps, uint8_t* desc, int cap_per_frame, int* n);
 /* Smallest cap_per_frame that can never return ORBX_ECAP for this shape (sum over levels of quota + slack). */
 int orbx_max_keypoints(orbx_t* h, int w, int hgt, int* cap);
+/* With host buffers a batch is split into chunks of `frames` frames that are software-pipelined: the PCIe copy-in of
+ * chunk c+1 and the copy-out of chunk c-1 overlap the kernels of chunk c. 0 = library default (48). */
+int orbx_set_chunk(orbx_t* h, int frames);
 
 /* Replaces the getters GetLevels / GetScaleFactors / GetInverseScaleFactors / GetScaleSigmaSquares /
  * GetInverseScaleSigmaSquares (include/ORBextractor.h:62-82) and exposes mnFeaturesPerLevel / umax

@@ -20,9 +20,9 @@ __device__ __forceinline__ int blur_reflect(int p, int len) {
 }
 
 __global__ void __launch_bounds__(32 * BLUR_WARPS) k_blur(const DevPlan* __restrict__ P, const uint8_t* __restrict__ pyr,
-                                                          uint8_t* __restrict__ blur) {
+                                                          uint8_t* __restrict__ blur, int f0) {
     const int lane = threadIdx.x & 31;
-    const int f = blockIdx.y;
+    const int f = f0 + blockIdx.y;
     int unit = blockIdx.x * BLUR_WARPS + (threadIdx.x >> 5);
     if (unit >= P->totalBlurTiles) return;
     int level = 0;

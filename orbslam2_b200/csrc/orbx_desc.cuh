@@ -57,9 +57,9 @@ __host__ __device__ constexpr int desc_uweights(int j) {
 __global__ void __launch_bounds__(256) k_orient_desc(const DevPlan* __restrict__ P, const uint8_t* __restrict__ pyr,
                                                      const uint8_t* __restrict__ blur, const uint2* __restrict__ sel,
                                                      const int* __restrict__ selCount, orbx_kp* __restrict__ kps,
-                                                     uint8_t* __restrict__ desc, int* __restrict__ nOut) {
+                                                     uint8_t* __restrict__ desc, int* __restrict__ nOut, int f0) {
     const int lane = threadIdx.x & 31;
-    const int f = blockIdx.y;
+    const int f = f0 + blockIdx.y;
     const int nl = P->nlevels;
     // per-frame level prefix (lane l holds the end offset of level l in the compact output)
     int cnt = (lane < nl) ? selCount[f * nl + lane] : 0;

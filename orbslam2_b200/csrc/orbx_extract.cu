@@ -58,6 +58,11 @@ struct orbx_handle {
     int64_t launches = 0;
     bool profiling = false;
     cudaEvent_t ev[8] = {};
+    // host-IO pipeline (orbx_extract_batch): copy-in, two compute and copy-out streams, one event pair per chunk
+    int chunk = 0;
+    cudaStream_t sIn = nullptr, sOut = nullptr, sComp[2] = {nullptr, nullptr};
+    cudaEvent_t evStart = nullptr, evDone = nullptr;
+    std::vector<cudaEvent_t> evIn, evComp;
     float stageMs[7] = {};
 };
 
@@ -325,6 +330,16 @@ extern "C" int orbx_destroy(orbx_t* h) {
     free_plan(h);
     cudaFree(h->dErr);
     for (int i = 0; i < 8; i++) cudaEventDestroy(h->ev[i]);
+    for (cudaEvent_t e : h->evIn) cudaEventDestroy(e);
+    for (cudaEvent_t e : h->evComp) cudaEventDestroy(e);
+    if (h->sIn) {
+        cudaEventDestroy(h->evStart);
+        cudaEventDestroy(h->evDone);
+        cudaStreamDestroy(h->sIn);
+        cudaStreamDestroy(h->sOut);
+        cudaStreamDestroy(h->sComp[0]);
+        cudaStreamDestroy(h->sComp[1]);
+    }
     cudaStreamDestroy(h->stream);
     delete h;
     return ORBX_OK;
@@ -389,6 +404,84 @@ static bool debug_sync() {
         }                                                                                            \
     } while (0)
 
+// One chunk of frames [f0, f0 + nb) through the whole kernel chain on stream `cs`. Every arena is indexed by the
+// absolute frame number, so chunks of one batch never touch each other's memory.
+static int launch_chain(orbx_handle* h, cudaStream_t cs, int f0, int nb, bool stamps) {
+    const DevPlan& D = h->hp;
+    const int nl = D.nlevels;
+    for (int l = 1; l < nl; l++) {
+        const LevelGeo& G = D.lv[l];
+        dim3 grid((G.w + 255) / 256, (G.h + 3) / 4, nb), block(64, 4);
+        if (G.resizeFast) k_resize_fast<<<grid, block, 0, cs>>>(h->dPlan, l, h->dPyr, h->dTabs, f0);
+        else k_resize<<<grid, block, 0, cs>>>(h->dPlan, l, h->dPyr, h->dTabs, f0);
+        KCHECK(h, "k_resize");
+    }
+    if (stamps) stamp(h, 2);
+    k_fast<<<dim3(D.totalSt, nb), FAST_THREADS, h->fastSmem, cs>>>(h->maps, h->dPlan, h->dCand, h->dCandCount, h->dErr, f0);
+    KCHECK(h, "k_fast");
+    if (stamps) stamp(h, 3);
+    k_quadtree<<<dim3(nl, nb), h->qtThreads, h->qtSmem, cs>>>(h->dPlan, h->dCand, h->dCandCount, h->dNodeOf, h->dSel,
+                                                             h->dSelCount, h->qtC, h->qtC2, h->dErr, f0);
+    KCHECK(h, "k_quadtree");
+    if (stamps) stamp(h, 4);
+    k_blur<<<dim3((D.totalBlurTiles + BLUR_WARPS - 1) / BLUR_WARPS, nb), 32 * BLUR_WARPS, 0, cs>>>(h->dPlan, h->dPyr, h->dBlur, f0);
+    KCHECK(h, "k_blur");
+    if (stamps) stamp(h, 5);
+    k_orient_desc<<<dim3((D.selStride + 8 * DESC_KPW - 1) / (8 * DESC_KPW), nb), 256, 0, cs>>>(
+        h->dPlan, h->dPyr, h->dBlur, h->dSel, h->dSelCount, h->dKps, h->dDesc, h->dNOut, f0);
+    KCHECK(h, "k_orient_desc");
+    if (stamps) stamp(h, 6);
+    return ORBX_OK;
+}
+
+static int copy_in(orbx_handle* h, cudaStream_t cs, const uint8_t* imgs, int f0, int nb, int w, int hgt, size_t stride,
+                   size_t img_stride) {
+    // ingest: level 0 of the pyramid IS the input image (src/ORBextractor.cc:939-943); one strided copy
+    const cudaMemcpyKind kin = h->inSpace == ORBX_MEM_HOST ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToDevice;
+    const LevelGeo& L0 = h->hp.lv[0];
+    uint8_t* dst = h->dPyr + L0.pyrOff + (long long)f0 * L0.frameStride;
+    const uint8_t* src = imgs + (size_t)f0 * img_stride;
+    if (nb == 1 || img_stride == stride * (size_t)hgt) {
+        CK(cudaMemcpy2DAsync(dst, L0.pitch, src, stride, w, (size_t)hgt * nb, kin, cs));
+    } else {
+        for (int f = 0; f < nb; f++)
+            CK(cudaMemcpy2DAsync(dst + f * L0.frameStride, L0.pitch, src + f * img_stride, stride, w, hgt, kin, cs));
+    }
+    return ORBX_OK;
+}
+
+static int copy_out(orbx_handle* h, cudaStream_t cs, orbx_kp* kps, uint8_t* desc, int cap, int f0, int nb) {
+    const DevPlan& D = h->hp;
+    const cudaMemcpyKind kout = h->outSpace == ORBX_MEM_HOST ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice;
+    const int rows = std::min(cap, D.selStride);
+    if (rows > 0) {
+        CK(cudaMemcpy2DAsync(kps + (size_t)f0 * cap, (size_t)cap * sizeof(orbx_kp), h->dKps + (size_t)f0 * D.selStride,
+                             (size_t)D.selStride * sizeof(orbx_kp), (size_t)rows * sizeof(orbx_kp), nb, kout, cs));
+        CK(cudaMemcpy2DAsync(desc + (size_t)f0 * cap * 32, (size_t)cap * 32, h->dDesc + (size_t)f0 * D.selStride * 32,
+                             (size_t)D.selStride * 32, (size_t)rows * 32, nb, kout, cs));
+    }
+    return ORBX_OK;
+}
+
+static int ensure_pipeline(orbx_handle* h, int nChunks) {
+    if (!h->sIn) {
+        CK(cudaStreamCreateWithFlags(&h->sIn, cudaStreamNonBlocking));
+        CK(cudaStreamCreateWithFlags(&h->sOut, cudaStreamNonBlocking));
+        CK(cudaStreamCreateWithFlags(&h->sComp[0], cudaStreamNonBlocking));
+        CK(cudaStreamCreateWithFlags(&h->sComp[1], cudaStreamNonBlocking));
+        CK(cudaEventCreateWithFlags(&h->evStart, cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&h->evDone, cudaEventDisableTiming));
+    }
+    while ((int)h->evIn.size() < nChunks) {
+        cudaEvent_t a, b;
+        CK(cudaEventCreateWithFlags(&a, cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&b, cudaEventDisableTiming));
+        h->evIn.push_back(a);
+        h->evComp.push_back(b);
+    }
+    return ORBX_OK;
+}
+
 extern "C" int orbx_extract_batch(orbx_t* h, const uint8_t* imgs, int batch, int w, int hgt, size_t stride,
                                   size_t img_stride, orbx_kp* kps, uint8_t* desc, int cap, int* n) {
     if (!h || !n) FAIL(ORBX_EINVAL, "null argument");
@@ -406,55 +499,55 @@ extern "C" int orbx_extract_batch(orbx_t* h, const uint8_t* imgs, int batch, int
     cudaStream_t st = h->stream;
     const int nl = D.nlevels;
 
+    // Host buffers on either side: split the batch into chunks and software-pipeline them — chunk c+1 crosses PCIe
+    // on the copy-in stream while chunk c computes (two compute streams, so one chunk's tail overlaps the next one's
+    // head) and chunk c-1 leaves on the copy-out stream. Device buffers: one launch sequence for the whole batch.
+    const bool hostIO = h->inSpace == ORBX_MEM_HOST || h->outSpace == ORBX_MEM_HOST;
+    int chunk = batch;
+    if (hostIO && !h->profiling) {
+        chunk = h->chunk > 0 ? h->chunk : 48;
+        if (batch < 2 * chunk) chunk = batch;
+    }
+    const int nChunks = (batch + chunk - 1) / chunk;
+
     stamp(h, 0);
-    // ingest: level 0 of the pyramid IS the input image (src/ORBextractor.cc:939-943); one strided copy
-    const cudaMemcpyKind kin = h->inSpace == ORBX_MEM_HOST ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToDevice;
-    const LevelGeo& L0 = D.lv[0];
-    if (batch == 1 || img_stride == stride * (size_t)hgt) {
-        CK(cudaMemcpy2DAsync(h->dPyr + L0.pyrOff, L0.pitch, imgs, stride, w, (size_t)hgt * batch, kin, st));
-    } else {
-        for (int f = 0; f < batch; f++)
-            CK(cudaMemcpy2DAsync(h->dPyr + L0.pyrOff + f * L0.frameStride, L0.pitch, imgs + f * img_stride, stride, w, hgt,
-                                 kin, st));
-    }
     CK(cudaMemsetAsync(h->dCandCount, 0, (size_t)batch * nl * sizeof(int), st));
-    stamp(h, 1);
-    for (int l = 1; l < nl; l++) {
-        const LevelGeo& G = D.lv[l];
-        dim3 grid((G.w + 255) / 256, (G.h + 3) / 4, batch), block(64, 4);
-        if (G.resizeFast) k_resize_fast<<<grid, block, 0, st>>>(h->dPlan, l, h->dPyr, h->dTabs);
-        else k_resize<<<grid, block, 0, st>>>(h->dPlan, l, h->dPyr, h->dTabs);
-        KCHECK(h, "k_resize");
+    if (nChunks == 1) {
+        rc = copy_in(h, st, imgs, 0, batch, w, hgt, stride, img_stride);
+        if (rc != ORBX_OK) return rc;
+        stamp(h, 1);
+        rc = launch_chain(h, st, 0, batch, true);
+        if (rc != ORBX_OK) return rc;
+        CK(cudaGetLastError());
+        rc = copy_out(h, st, kps, desc, cap, 0, batch);
+        if (rc != ORBX_OK) return rc;
+    } else {
+        rc = ensure_pipeline(h, nChunks);
+        if (rc != ORBX_OK) return rc;
+        CK(cudaEventRecord(h->evStart, st));
+        CK(cudaStreamWaitEvent(h->sIn, h->evStart, 0));
+        for (int c = 0; c < nChunks; c++) {
+            const int f0 = c * chunk, nb = std::min(chunk, batch - f0);
+            cudaStream_t cs = h->sComp[c & 1];
+            rc = copy_in(h, h->sIn, imgs, f0, nb, w, hgt, stride, img_stride);
+            if (rc != ORBX_OK) return rc;
+            CK(cudaEventRecord(h->evIn[c], h->sIn));
+            CK(cudaStreamWaitEvent(cs, h->evIn[c], 0));
+            rc = launch_chain(h, cs, f0, nb, false);
+            if (rc != ORBX_OK) return rc;
+            CK(cudaGetLastError());
+            CK(cudaEventRecord(h->evComp[c], cs));
+            CK(cudaStreamWaitEvent(h->sOut, h->evComp[c], 0));
+            rc = copy_out(h, h->sOut, kps, desc, cap, f0, nb);
+            if (rc != ORBX_OK) return rc;
+        }
+        CK(cudaEventRecord(h->evDone, h->sOut));  // sOut is ordered after every compute chunk, hence after every copy-in
+        CK(cudaStreamWaitEvent(st, h->evDone, 0));
     }
-    stamp(h, 2);
-    k_fast<<<dim3(D.totalSt, batch), FAST_THREADS, h->fastSmem, st>>>(h->maps, h->dPlan, h->dCand, h->dCandCount, h->dErr);
-    KCHECK(h, "k_fast");
-    stamp(h, 3);
-    k_quadtree<<<dim3(nl, batch), h->qtThreads, h->qtSmem, st>>>(h->dPlan, h->dCand, h->dCandCount, h->dNodeOf, h->dSel,
-                                                                  h->dSelCount, h->qtC, h->qtC2, h->dErr);
-    KCHECK(h, "k_quadtree");
-    stamp(h, 4);
-    k_blur<<<dim3((D.totalBlurTiles + BLUR_WARPS - 1) / BLUR_WARPS, batch), 32 * BLUR_WARPS, 0, st>>>(h->dPlan, h->dPyr, h->dBlur);
-    KCHECK(h, "k_blur");
-    stamp(h, 5);
-    k_orient_desc<<<dim3((D.selStride + 8 * DESC_KPW - 1) / (8 * DESC_KPW), batch), 256, 0, st>>>(h->dPlan, h->dPyr, h->dBlur, h->dSel, h->dSelCount,
-                                                                      h->dKps, h->dDesc, h->dNOut);
-    KCHECK(h, "k_orient_desc");
-    stamp(h, 6);
-    CK(cudaGetLastError());
     h->lastBatch = batch;
     h->blurValid = true;
-
-    // results: counts first (they gate the error code), then one strided copy per array
     CK(cudaMemcpyAsync(h->hCounts, h->dNOut, (size_t)batch * sizeof(int), cudaMemcpyDeviceToHost, st));
     CK(cudaMemcpyAsync(h->hCounts + batch, h->dErr, sizeof(int), cudaMemcpyDeviceToHost, st));
-    const cudaMemcpyKind kout = h->outSpace == ORBX_MEM_HOST ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice;
-    const int rows = std::min(cap, D.selStride);
-    if (rows > 0) {
-        CK(cudaMemcpy2DAsync(kps, (size_t)cap * sizeof(orbx_kp), h->dKps, (size_t)D.selStride * sizeof(orbx_kp),
-                             (size_t)rows * sizeof(orbx_kp), batch, kout, st));
-        CK(cudaMemcpy2DAsync(desc, (size_t)cap * 32, h->dDesc, (size_t)D.selStride * 32, (size_t)rows * 32, batch, kout, st));
-    }
     stamp(h, 7);
     CK(cudaStreamSynchronize(st));
     if (h->profiling)
@@ -466,10 +559,17 @@ extern "C" int orbx_extract_batch(orbx_t* h, const uint8_t* imgs, int batch, int
     }
     int worst = 0;
     for (int f = 0; f < batch; f++) {
-        if (h->outSpace == ORBX_MEM_HOST || n) n[f] = h->hCounts[f];
+        n[f] = h->hCounts[f];
         worst = std::max(worst, h->hCounts[f]);
     }
     if (worst > cap) FAIL(ORBX_ECAP, "cap_per_frame %d < %d keypoints found", cap, worst);
+    return ORBX_OK;
+}
+
+/* Frames per pipeline chunk when a buffer lives in host memory (0 = default). */
+extern "C" int orbx_set_chunk(orbx_t* h, int frames) {
+    if (!h || frames < 0) FAIL(ORBX_EINVAL, "bad chunk");
+    h->chunk = frames;
     return ORBX_OK;
 }
 

@@ -79,10 +79,10 @@ struct FastSmemHdr {
 
 __global__ void __launch_bounds__(FAST_THREADS) k_fast(const __grid_constant__ TmapPack maps,
                                                        const DevPlan* __restrict__ P, u64* __restrict__ cand,
-                                                       int* __restrict__ candCount, int* __restrict__ err) {
+                                                       int* __restrict__ candCount, int* __restrict__ err, int f0) {
     extern __shared__ __align__(128) uint8_t fast_smem[];
     const int tid = threadIdx.x;
-    const int f = blockIdx.y;
+    const int f = f0 + blockIdx.y;
     int level = 0;
     while (level + 1 < P->nlevels && (int)blockIdx.x >= P->lv[level + 1].stBase) level++;
     const LevelGeo& G = P->lv[level];

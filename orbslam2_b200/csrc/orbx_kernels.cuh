@@ -85,12 +85,12 @@ __device__ __forceinline__ int next_pow2(int v) {
 // Tables (host-computed with OpenCV's float/double expressions): int2 {source index, a0 | a1<<16}.
 // One thread = 4 consecutive output pixels (one aligned 32-bit store).
 __global__ void __launch_bounds__(256) k_resize(const DevPlan* __restrict__ P, int level, uint8_t* __restrict__ pyr,
-                                                const int2* __restrict__ tabs) {
+                                                const int2* __restrict__ tabs, int f0) {
     const LevelGeo& D = P->lv[level];
     const LevelGeo& S = P->lv[level - 1];
     const int x4 = (blockIdx.x * 64 + threadIdx.x) * 4;
     const int y = blockIdx.y * 4 + threadIdx.y;
-    const int f = blockIdx.z;
+    const int f = f0 + blockIdx.z;
     if (x4 >= D.w || y >= D.h) return;
     const uint8_t* src = pyr + S.pyrOff + (long long)f * S.frameStride;
     uint8_t* dst = pyr + D.pyrOff + (long long)f * D.frameStride + (long long)y * D.pitch + x4;
@@ -159,10 +159,10 @@ __device__ __forceinline__ int quadrant_of(const short4 g, int x, int y) {
 
 __global__ void k_quadtree(const DevPlan* __restrict__ P, const u64* __restrict__ cand,
                            const int* __restrict__ candCount, int* __restrict__ nodeOf, uint2* __restrict__ sel,
-                           int* __restrict__ selCount, int C, int C2, int* __restrict__ err) {
+                           int* __restrict__ selCount, int C, int C2, int* __restrict__ err, int f0) {
     extern __shared__ __align__(16) uint8_t qt_smem[];
     uint8_t* smem = qt_smem;
-    const int level = blockIdx.x, f = blockIdx.y;
+    const int level = blockIdx.x, f = f0 + blockIdx.y;
     const LevelGeo& G = P->lv[level];
     const int nl = P->nlevels;
     const int tid = threadIdx.x, T = blockDim.x;

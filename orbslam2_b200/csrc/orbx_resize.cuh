@@ -19,12 +19,12 @@ __device__ __forceinline__ unsigned dp2a_lo_u32(unsigned a16x2, unsigned b8x4, u
 }
 
 __global__ void __launch_bounds__(256) k_resize_fast(const DevPlan* __restrict__ P, int level, uint8_t* __restrict__ pyr,
-                                                     const int2* __restrict__ tabs) {
+                                                     const int2* __restrict__ tabs, int f0) {
     const LevelGeo& D = P->lv[level];
     const LevelGeo& S = P->lv[level - 1];
     const int x4 = (blockIdx.x * 64 + threadIdx.x) * 4;
     const int y = blockIdx.y * 4 + threadIdx.y;
-    const int f = blockIdx.z;
+    const int f = f0 + blockIdx.z;
     if (x4 >= D.w || y >= D.h) return;
     const uint8_t* src = pyr + S.pyrOff + (long long)f * S.frameStride;
     const int2 ty = tabs[D.ytabOff + y];

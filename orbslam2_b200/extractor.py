@@ -78,6 +78,10 @@ class ORBextractor:
         _lib.check(self._L.orbx_max_keypoints(self._h, w, h, C.byref(cap)))
         return cap.value
 
+    def set_chunk(self, frames):
+        """Frames per pipeline chunk of the host-buffer path (0 = library default)."""
+        _lib.check(self._L.orbx_set_chunk(self._h, int(frames)))
+
     def _set_space(self, i, o):
         if (i, o) != (self._in_space, self._out_space):
             _lib.check(self._L.orbx_set_memory_space(self._h, i, o))

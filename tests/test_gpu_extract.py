@@ -126,3 +126,24 @@ def test_device_io_torch(ob):
         assert np.array_equal(dd[f, :nd[f]].cpu().numpy(), dh[f, :nh[f]])
         assert kd[f, :nd[f]].cpu().numpy().tobytes() == kh[f, :nh[f]].tobytes()
     ex.close()
+
+
+def test_host_pipeline_chunks_match_single_launch(ob):
+    """Host buffers are processed in software-pipelined chunks (copy-in / compute / copy-out overlap): every chunking,
+    including a ragged last chunk, gives the bytes of the one-launch path."""
+    p = _params(1000)
+    ex = ob.ORBextractor(**p)
+    imgs = np.stack([synth_image(640, 480, s % 5) for s in range(23)])
+    ex.set_chunk(64)                      # 23 < 2*64 -> one launch sequence
+    k0, d0, n0 = ex.extract_batch(imgs)
+    for chunk in (1, 4, 7, 11):
+        ex.set_chunk(chunk)
+        k, d, n = ex.extract_batch(imgs)
+        assert np.array_equal(n, n0)
+        for f in range(len(imgs)):
+            assert k[f, :n[f]].tobytes() == k0[f, :n0[f]].tobytes() and np.array_equal(d[f, :n[f]], d0[f, :n0[f]])
+    # resident state (pyramid of a frame from a late chunk) is still addressable by absolute frame index
+    lvl = ex.pyramid_level(3, 22)
+    k1, d1 = ex(imgs[22])
+    assert k1.tobytes() == k0[22, :n0[22]].tobytes() and np.array_equal(ex.pyramid_level(3, 0), lvl)
+    ex.close()
