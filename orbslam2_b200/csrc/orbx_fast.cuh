@@ -8,8 +8,9 @@
 //     score = max(M - v, v - m) - 1   = the largest t at which the pixel is still a FAST corner (OpenCV cornerScore)
 //   the pixel is a corner at threshold t  <=>  score >= t.
 // The arc minima / maxima are computed for TWO pixels per instruction with the packed 16-bit DPX min/max
-// (VIMNMX3.U16x2): min3 over 3 neighbours, then min3 of three of those = min over 9; 40 instructions per polarity and
-// pixel pair. One thread scores 4 horizontally adjacent pixels (one 32-bit word of the tile).
+// (VIMNMX.U16x2 / VIMNMX3.U16x2; measured on B200: the 2-input form issues at 4 warp-inst/clk/SM, the 3-input form and
+// PRMT at 2 — scripts/pipe_probe.cu), in the paired-arc formulation of fast_score2 (47 two-input min/max per polarity
+// and pixel pair). One thread scores 4 horizontally adjacent pixels (one 32-bit word of the tile).
 //
 // One CTA = a "supertile" of stCX x stCY cells of one level of one frame:
 //   TMA 3-D tile load (x start rounded down to 16 bytes — an unaligned innermost coordinate faults on sm_100a)
@@ -36,24 +37,36 @@ __device__ __forceinline__ unsigned fast_align(unsigned wm, unsigned w0, unsigne
     }
 }
 
-// Packed score of two pixels (16-bit lanes): c[k] = circle values, v = centres; returns max(score - (minTh-1), 0).
-__device__ __forceinline__ unsigned fast_score2(const unsigned (&c)[16], unsigned v, unsigned negThm1) {
-    unsigned a3[16], b3[16];
+// Packed score of two pixels (16-bit lanes, pixel value in the HIGH byte, don't-care low byte): c[k] = circle values,
+// vh = centres; returns max(score - (minTh-1), 0) as plain 16-bit lanes.
+// The 16 arcs of 9 pair up around the 8 even-aligned runs of 8: with A8[k] = min(c[k..k+7]) (k even, by doubling),
+//   arc9(k) = min(A8[k], c[k+8])   arc9(k-1) = min(c[k-1], A8[k])   =>   max of the two = min(A8[k], max(c[k+8], c[k-1]))
+// so M = max over the 8 even k of min(A8[k], max(c[k+8], c[k-1])): 47 two-input min/max per polarity instead of 80.
+__device__ __forceinline__ unsigned fast_score2(const unsigned (&c)[16], unsigned vh, unsigned negThm1) {
+    unsigned a2[8], b2[8], a4[8], b4[8];
 #pragma unroll
-    for (int k = 0; k < 16; k++) {
-        a3[k] = __vimin3_u16x2(c[k], c[(k + 1) & 15], c[(k + 2) & 15]);
-        b3[k] = __vimax3_u16x2(c[k], c[(k + 1) & 15], c[(k + 2) & 15]);
+    for (int j = 0; j < 8; j++) {
+        a2[j] = __vminu2(c[2 * j], c[2 * j + 1]);
+        b2[j] = __vmaxu2(c[2 * j], c[2 * j + 1]);
     }
-    unsigned M = 0u, m = 0xFFFFFFFFu;
 #pragma unroll
-    for (int k = 0; k < 16; k += 2) {
-        const unsigned a9 = __vimin3_u16x2(a3[k], a3[(k + 3) & 15], a3[(k + 6) & 15]);
-        const unsigned a9b = __vimin3_u16x2(a3[k + 1], a3[(k + 4) & 15], a3[(k + 7) & 15]);
-        M = __vimax3_u16x2(M, a9, a9b);
-        const unsigned b9 = __vimax3_u16x2(b3[k], b3[(k + 3) & 15], b3[(k + 6) & 15]);
-        const unsigned b9b = __vimax3_u16x2(b3[k + 1], b3[(k + 4) & 15], b3[(k + 7) & 15]);
-        m = __vimin3_u16x2(m, b9, b9b);
+    for (int j = 0; j < 8; j++) {
+        a4[j] = __vminu2(a2[j], a2[(j + 1) & 7]);
+        b4[j] = __vmaxu2(b2[j], b2[(j + 1) & 7]);
     }
+    unsigned r[8], q[8];
+#pragma unroll
+    for (int j = 0; j < 8; j++) {
+        const int k = 2 * j;
+        const unsigned dmax = __vmaxu2(c[(k + 8) & 15], c[(k + 15) & 15]);
+        const unsigned dmin = __vminu2(c[(k + 8) & 15], c[(k + 15) & 15]);
+        r[j] = __vimin3_u16x2(a4[j], a4[(j + 2) & 7], dmax);
+        q[j] = __vimax3_u16x2(b4[j], b4[(j + 2) & 7], dmin);
+    }
+    const unsigned Mh = __vimax3_u16x2(__vimax3_u16x2(r[0], r[1], r[2]), __vimax3_u16x2(r[3], r[4], r[5]), __vmaxu2(r[6], r[7]));
+    const unsigned mh = __vimin3_u16x2(__vimin3_u16x2(q[0], q[1], q[2]), __vimin3_u16x2(q[3], q[4], q[5]), __vminu2(q[6], q[7]));
+    // the pixel values are the high bytes of the lanes (see k_fast): bring them down before the signed 16-bit arithmetic
+    const unsigned M = __byte_perm(Mh, 0u, 0x4341), m = __byte_perm(mh, 0u, 0x4341), v = __byte_perm(vh, 0u, 0x4341);
     // per 16-bit lane ~x == -x-1, so M + ~v = (M - v) - 1 and v + ~m = (v - m) - 1
     const unsigned sb = __viaddmax_s16x2(M, ~v, 0u);
     const unsigned sd = __viaddmax_s16x2(v, ~m, 0u);
@@ -176,51 +189,57 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast(const __grid_constant__ T
         const int wy = (int)(((unsigned)u * divW) >> 20), wi = u - wy * nW;
         const int wx = wx0 + wi;
         const unsigned* r0 = tile + (wy + 3) * pitchW + wx;  // centre row
-        unsigned cw[16];  // aligned circle words, Bresenham order (dx,dy): (0,3)(1,3)(2,2)(3,1)(3,0)(3,-1)(2,-2)(1,-3)(0,-3)...
+        // Operands stay 16-bit lanes with the PIXEL IN THE HIGH BYTE and a neighbouring pixel as junk in the low byte:
+        // the high byte of any min/max tree over such lanes is the same tree over the high bytes (lexicographic
+        // order), so no masking is needed. With A(d) = bytes x+d .. x+d+3 of a row, the operand for pixels (1,3) at
+        // circle offset dx is A(dx) itself and the one for pixels (0,2) is A(dx-1).
+        // Bresenham order (dx,dy): (0,3)(1,3)(2,2)(3,1)(3,0)(3,-1)(2,-2)(1,-3)(0,-3)(-1,-3)(-2,-2)(-3,-1)(-3,0)(-3,1)(-2,2)(-1,3)
+        unsigned ce[16], co[16];
         {
             const unsigned* r = r0 + 3 * pitchW;
             const unsigned a = r[-1], b = r[0], c = r[1];
-            cw[15] = fast_align(a, b, c, -1); cw[0] = b; cw[1] = fast_align(a, b, c, 1);
+            const unsigned m2 = fast_align(a, b, c, -2), m1 = fast_align(a, b, c, -1), p1 = fast_align(a, b, c, 1);
+            ce[15] = m2; co[15] = m1; ce[0] = m1; co[0] = b; ce[1] = b; co[1] = p1;
         }
         {
             const unsigned* r = r0 + 2 * pitchW;
             const unsigned a = r[-1], b = r[0], c = r[1];
-            cw[14] = fast_align(a, b, c, -2); cw[2] = fast_align(a, b, c, 2);
+            ce[14] = fast_align(a, b, c, -3); co[14] = fast_align(a, b, c, -2);
+            ce[2] = fast_align(a, b, c, 1); co[2] = fast_align(a, b, c, 2);
         }
         {
             const unsigned* r = r0 + pitchW;
             const unsigned a = r[-1], b = r[0], c = r[1];
-            cw[13] = fast_align(a, b, c, -3); cw[3] = fast_align(a, b, c, 3);
+            ce[13] = a; co[13] = fast_align(a, b, c, -3);
+            ce[3] = fast_align(a, b, c, 2); co[3] = fast_align(a, b, c, 3);
         }
-        unsigned vw;
+        unsigned ve, vo;
         {
             const unsigned a = r0[-1], b = r0[0], c = r0[1];
-            cw[12] = fast_align(a, b, c, -3); cw[4] = fast_align(a, b, c, 3);
-            vw = b;
+            ce[12] = a; co[12] = fast_align(a, b, c, -3);
+            ce[4] = fast_align(a, b, c, 2); co[4] = fast_align(a, b, c, 3);
+            ve = fast_align(a, b, c, -1); vo = b;
         }
         {
             const unsigned* r = r0 - pitchW;
             const unsigned a = r[-1], b = r[0], c = r[1];
-            cw[11] = fast_align(a, b, c, -3); cw[5] = fast_align(a, b, c, 3);
+            ce[11] = a; co[11] = fast_align(a, b, c, -3);
+            ce[5] = fast_align(a, b, c, 2); co[5] = fast_align(a, b, c, 3);
         }
         {
             const unsigned* r = r0 - 2 * pitchW;
             const unsigned a = r[-1], b = r[0], c = r[1];
-            cw[10] = fast_align(a, b, c, -2); cw[6] = fast_align(a, b, c, 2);
+            ce[10] = fast_align(a, b, c, -3); co[10] = fast_align(a, b, c, -2);
+            ce[6] = fast_align(a, b, c, 1); co[6] = fast_align(a, b, c, 2);
         }
         {
             const unsigned* r = r0 - 3 * pitchW;
             const unsigned a = r[-1], b = r[0], c = r[1];
-            cw[9] = fast_align(a, b, c, -1); cw[8] = b; cw[7] = fast_align(a, b, c, 1);
+            const unsigned m2 = fast_align(a, b, c, -2), m1 = fast_align(a, b, c, -1), p1 = fast_align(a, b, c, 1);
+            ce[9] = m2; co[9] = m1; ce[8] = m1; co[8] = b; ce[7] = b; co[7] = p1;
         }
-        unsigned ce[16], co[16];
-#pragma unroll
-        for (int k = 0; k < 16; k++) {
-            ce[k] = cw[k] & 0x00FF00FFu;              // pixels 0 and 2
-            co[k] = __byte_perm(cw[k], 0u, 0x4341);   // pixels 1 and 3
-        }
-        const unsigned se = fast_score2(ce, vw & 0x00FF00FFu, negThm1);
-        const unsigned so = fast_score2(co, __byte_perm(vw, 0u, 0x4341), negThm1);
+        const unsigned se = fast_score2(ce, ve, negThm1);
+        const unsigned so = fast_score2(co, vo, negThm1);
         unsigned s = se | (so << 8);
         if (wi == 0 || wi == nW - 1) {  // bytes outside the detection columns
             const int xb = oxa + (wx << 2);
