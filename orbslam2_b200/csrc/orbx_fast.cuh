@@ -122,6 +122,12 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast(const __grid_constant__ T
     if (tid == 0) {
         asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        // the tile is requested before anything else so its latency overlaps the table set-up below
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"((uint32_t)tileBytes) : "memory");
+        asm volatile(
+            "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+            ::"r"((uint32_t)__cvta_generic_to_shared(tile)), "l"(&maps.m[level]), "r"(oxa), "r"(oy), "r"(f), "r"(bar)
+            : "memory");
         H->total = 0;
         H->slot = 0;
         H->nList = 0;
@@ -131,13 +137,16 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast(const __grid_constant__ T
         H->nIni[tid] = 0;
     }
     // column / row lookup tables (which bytes sit on a cell edge)
+    const unsigned divCw = (65536u + G.wCell - 1) / G.wCell;  // v / wCell == (v * divCw) >> 16 for v < 1024
+    const unsigned divCh = (65536u + G.hCell - 1) / G.hCell;
     for (int i = tid; i < nW; i += FAST_THREADS) {
         unsigned fc = 0, lc = 0;
 #pragma unroll
         for (int b = 0; b < 4; b++) {
             const int x = oxa + ((wx0 + i) << 2) + b;
             if (x >= xFirst && x < xEnd) {
-                const int r = (x - xFirst) % G.wCell;
+                const int v = x - xFirst;
+                const int r = v - (int)(((unsigned)v * divCw) >> 16) * G.wCell;
                 if (r == 0) fc |= 0xFFu << (8 * b);
                 if (r == G.wCell - 1 || x == xEnd - 1) lc |= 0xFFu << (8 * b);
             }
@@ -146,7 +155,7 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast(const __grid_constant__ T
         H->lastCol[i] = lc;
     }
     for (int i = tid; i < nR; i += FAST_THREADS) {
-        const int r = i % G.hCell;
+        const int r = i - (int)(((unsigned)i * divCh) >> 16) * G.hCell;
         H->rowFlag[i] = (unsigned char)((r == 0 ? 1 : 0) | ((r == G.hCell - 1 || i == nR - 1) ? 2 : 0));
     }
     {   // zero the score map (its unused rim is what NMS reads as "no corner")
@@ -154,13 +163,6 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast(const __grid_constant__ T
         for (int i = tid; i < (tileBytes >> 4); i += FAST_THREADS) z[i] = make_uint4(0, 0, 0, 0);
     }
     __syncthreads();
-    if (tid == 0) {
-        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"((uint32_t)tileBytes) : "memory");
-        asm volatile(
-            "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
-            ::"r"((uint32_t)__cvta_generic_to_shared(tile)), "l"(&maps.m[level]), "r"(oxa), "r"(oy), "r"(f), "r"(bar)
-            : "memory");
-    }
     {   // bounded wait on phase 0 (a lost TMA must not hang the GPU: flag the error and bail out)
         uint32_t done = 0;
         int spins = 0;
@@ -192,13 +194,14 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast(const __grid_constant__ T
         // Operands stay 16-bit lanes with the PIXEL IN THE HIGH BYTE and a neighbouring pixel as junk in the low byte:
         // the high byte of any min/max tree over such lanes is the same tree over the high bytes (lexicographic
         // order), so no masking is needed. With A(d) = bytes x+d .. x+d+3 of a row, the operand for pixels (1,3) at
-        // circle offset dx is A(dx) itself and the one for pixels (0,2) is A(dx-1).
+        // circle offset dx is A(dx) itself and the one for pixels (0,2) is A(dx-1). Where only the high bytes matter a
+        // plain shift of one word does (A(-1) ~ b << 8, A(3) ~ c << 8): IMAD.SHL runs on the idle FMA pipe.
         // Bresenham order (dx,dy): (0,3)(1,3)(2,2)(3,1)(3,0)(3,-1)(2,-2)(1,-3)(0,-3)(-1,-3)(-2,-2)(-3,-1)(-3,0)(-3,1)(-2,2)(-1,3)
         unsigned ce[16], co[16];
         {
             const unsigned* r = r0 + 3 * pitchW;
             const unsigned a = r[-1], b = r[0], c = r[1];
-            const unsigned m2 = fast_align(a, b, c, -2), m1 = fast_align(a, b, c, -1), p1 = fast_align(a, b, c, 1);
+            const unsigned m2 = fast_align(a, b, c, -2), m1 = b << 8, p1 = fast_align(a, b, c, 1);
             ce[15] = m2; co[15] = m1; ce[0] = m1; co[0] = b; ce[1] = b; co[1] = p1;
         }
         {
@@ -211,20 +214,20 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast(const __grid_constant__ T
             const unsigned* r = r0 + pitchW;
             const unsigned a = r[-1], b = r[0], c = r[1];
             ce[13] = a; co[13] = fast_align(a, b, c, -3);
-            ce[3] = fast_align(a, b, c, 2); co[3] = fast_align(a, b, c, 3);
+            ce[3] = fast_align(a, b, c, 2); co[3] = c << 8;
         }
         unsigned ve, vo;
         {
             const unsigned a = r0[-1], b = r0[0], c = r0[1];
             ce[12] = a; co[12] = fast_align(a, b, c, -3);
-            ce[4] = fast_align(a, b, c, 2); co[4] = fast_align(a, b, c, 3);
-            ve = fast_align(a, b, c, -1); vo = b;
+            ce[4] = fast_align(a, b, c, 2); co[4] = c << 8;
+            ve = b << 8; vo = b;
         }
         {
             const unsigned* r = r0 - pitchW;
             const unsigned a = r[-1], b = r[0], c = r[1];
             ce[11] = a; co[11] = fast_align(a, b, c, -3);
-            ce[5] = fast_align(a, b, c, 2); co[5] = fast_align(a, b, c, 3);
+            ce[5] = fast_align(a, b, c, 2); co[5] = c << 8;
         }
         {
             const unsigned* r = r0 - 2 * pitchW;
@@ -235,7 +238,7 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast(const __grid_constant__ T
         {
             const unsigned* r = r0 - 3 * pitchW;
             const unsigned a = r[-1], b = r[0], c = r[1];
-            const unsigned m2 = fast_align(a, b, c, -2), m1 = fast_align(a, b, c, -1), p1 = fast_align(a, b, c, 1);
+            const unsigned m2 = fast_align(a, b, c, -2), m1 = b << 8, p1 = fast_align(a, b, c, 1);
             ce[9] = m2; co[9] = m1; ce[8] = m1; co[8] = b; ce[7] = b; co[7] = p1;
         }
         const unsigned se = fast_score2(ce, ve, negThm1);
@@ -295,10 +298,10 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast(const __grid_constant__ T
     const int nList = min(H->nList, listCap);
     for (int i = tid; i < nList; i += FAST_THREADS) {
         const unsigned r = list[i];
-        const int wy = r >> 16, x = (r >> 8) & 0xFF, v = r & 0xFF;
-        const int cell = (wy / G.hCell) * G.stCX + x / G.wCell;
+        const unsigned wy = r >> 16, x = (r >> 8) & 0xFF, v = r & 0xFF;
+        const int cell = (int)((wy * divCh) >> 16) * G.stCX + (int)((x * divCw) >> 16);
         atomicAdd(&H->nAll[cell], 1);
-        if (v + minTh - 1 >= iniTh) atomicAdd(&H->nIni[cell], 1);
+        if ((int)v + minTh - 1 >= iniTh) atomicAdd(&H->nIni[cell], 1);
     }
     __syncthreads();
 
@@ -315,10 +318,10 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast(const __grid_constant__ T
     u64* out = cand + G.candOff + (long long)f * G.candCap;
     for (int i = tid; i < nList; i += FAST_THREADS) {
         const unsigned r = list[i];
-        const int wy = r >> 16, x = (r >> 8) & 0xFF, v = r & 0xFF;
-        const int cyl = wy / G.hCell, yin = wy - cyl * G.hCell;
-        const int cxl = x / G.wCell, xin = x - cxl * G.wCell;
-        const int score = v + minTh - 1;
+        const unsigned wy = r >> 16, x = (r >> 8) & 0xFF, v = r & 0xFF;
+        const int cyl = (int)((wy * divCh) >> 16), yin = (int)wy - cyl * G.hCell;
+        const int cxl = (int)((x * divCw) >> 16), xin = (int)x - cxl * G.wCell;
+        const int score = (int)v + minTh - 1;
         if (H->nIni[cyl * G.stCX + cxl] > 0 && score < iniTh) continue;
         const int slot = gbase + atomicAdd(&H->slot, 1);
         if (slot < G.candCap) out[slot] = cand_pack(score, ci0 + cyl, cj0 + cxl, yin, xin);
