@@ -5,7 +5,9 @@
 // One warp per keypoint, each warp walks KPW consecutive keypoints of one frame so that everything that depends only
 // on the lane is computed once: the circular-patch byte masks (lane = patch row v = lane-15, |u| <= umax[|v|]) and the
 // lane's 8 BRIEF pairs as floats (lane i produces descriptor byte i = pairs 8i..8i+7, LSB first).
-//   orientation: 9 aligned 32-bit loads per row, funnel-shift to the patch start, mask, two DP4A per word
+//   staging:     the 31x31 un-blurred patch and the 37x37 blurred patch (pattern reach +-18) are copied to shared memory
+//                with flat, row-crossing warp loads (~4 rows per load instead of one row per lane: 8x fewer L1 wavefronts)
+//   orientation: 9 words per row from shared memory, funnel-shift to the patch start, mask, two DP4A per word
 //                (m10 += sum u*I with constant s8 weights, row sum for m01 = v * sum I), warp-shuffle reduction,
 //                OpenCV's fastAtan2 polynomial op for op in fp32 without FMA contraction.
 //   descriptor:  a = cos(angle), b = sin(angle); sample (round(x*b + y*a), round(x*a - y*b)) from the blurred level;
@@ -14,6 +16,8 @@
 #include "orbx_internal.cuh"
 
 #define DESC_KPW 4  // keypoints per warp
+#define DESC_RAW_WORDS 288  // 31 rows x 9 words, rounded up to a multiple of 32
+#define DESC_BLR_WORDS 384  // 37 rows x 10 words, rounded up to a multiple of 32
 
 __device__ signed char d_pattern[1024];  // 256 x (x1, y1, x2, y2), the reference's bit_pattern_31_
 
@@ -54,7 +58,7 @@ __host__ __device__ constexpr int desc_uweights(int j) {
                  ((unsigned)((4 * j - 13) & 0xFF) << 16) | ((unsigned)((4 * j - 12) & 0xFF) << 24));
 }
 
-__global__ void __launch_bounds__(256) k_orient_desc(const DevPlan* __restrict__ P, const uint8_t* __restrict__ pyr,
+__global__ void __launch_bounds__(256, 3) k_orient_desc(const DevPlan* __restrict__ P, const uint8_t* __restrict__ pyr,
                                                      const uint8_t* __restrict__ blur, const uint2* __restrict__ sel,
                                                      const int* __restrict__ selCount, orbx_kp* __restrict__ kps,
                                                      uint8_t* __restrict__ desc, int* __restrict__ nOut, int f0) {
@@ -107,6 +111,13 @@ __global__ void __launch_bounds__(256) k_orient_desc(const DevPlan* __restrict__
         }
     }
 
+    // per-warp staging buffers: the un-blurred 31-row patch (9 words per row) and the blurred 37-row patch (10 words per
+    // row). Both are fetched with flat lane -> (row, word) indexing, so one warp-load touches ~4 rows instead of 32.
+    __shared__ unsigned sh_raw[256 / 32][DESC_RAW_WORDS];
+    __shared__ unsigned sh_blr[256 / 32][DESC_BLR_WORDS];
+    unsigned* raw = sh_raw[threadIdx.x >> 5];
+    unsigned* blr = sh_blr[threadIdx.x >> 5];
+
     for (int o = o0; o < min(o0 + DESC_KPW, total); o++) {
         // level of output index o
         const unsigned ge = __ballot_sync(0xffffffffu, lane < nl && o >= endOff);
@@ -116,13 +127,39 @@ __global__ void __launch_bounds__(256) k_orient_desc(const DevPlan* __restrict__
         const uint2 s = sel[(long long)f * P->selStride + G.selOff + (o - before)];
         const int x = s.x & 0xFFFF, y = s.x >> 16;
         const long long lvlOff = G.pyrOff + (long long)f * G.frameStride;
+        const int pitch = G.pitch;
+
+        // ---- stage both patches (all loads of the keypoint are in flight together)
+        const int xs = x - 15, a0 = xs & ~3, sh = (xs & 3) * 8;
+        const int xb = x - 18, b0 = xb & ~3, shB = xb & 3;
+        {
+            const uint8_t* rbase = pyr + lvlOff + (long long)(y - 15) * pitch + a0;
+            const uint8_t* bbase = blur + lvlOff + (long long)(y - 18) * pitch + b0;
+            unsigned rv[DESC_RAW_WORDS / 32], bv[DESC_BLR_WORDS / 32];
+#pragma unroll
+            for (int i = 0; i < DESC_RAW_WORDS / 32; i++) {
+                const int idx = lane + 32 * i;
+                const int row = (idx * 7282) >> 16;  // idx / 9 for idx < 288
+                rv[i] = (idx < 31 * 9) ? *(const unsigned*)(rbase + row * pitch + 4 * (idx - row * 9)) : 0u;
+            }
+#pragma unroll
+            for (int i = 0; i < DESC_BLR_WORDS / 32; i++) {
+                const int idx = lane + 32 * i;
+                const int row = (idx * 6554) >> 16;  // idx / 10 for idx < 384
+                bv[i] = (idx < 37 * 10) ? *(const unsigned*)(bbase + row * pitch + 4 * (idx - row * 10)) : 0u;
+            }
+            __syncwarp();  // the previous keypoint's readers are done with the buffers
+#pragma unroll
+            for (int i = 0; i < DESC_RAW_WORDS / 32; i++) raw[lane + 32 * i] = rv[i];
+#pragma unroll
+            for (int i = 0; i < DESC_BLR_WORDS / 32; i++) blr[lane + 32 * i] = bv[i];
+            __syncwarp();
+        }
 
         // ---- IC_Angle
         int m10 = 0, rs = 0;
         if (rowOn) {
-            const int xs = x - 15;
-            const int a0 = xs & ~3, sh = (xs & 3) * 8;
-            const unsigned* rowp = (const unsigned*)(pyr + lvlOff + (long long)(y + v) * G.pitch + a0);
+            const unsigned* rowp = raw + lane * 9;  // bank = (9 * lane + j) % 32: conflict free
             unsigned w[9];
 #pragma unroll
             for (int j = 0; j < 9; j++) w[j] = rowp[j];
@@ -145,13 +182,13 @@ __global__ void __launch_bounds__(256) k_orient_desc(const DevPlan* __restrict__
         const float factorPI = (float)(3.1415926535897932384626433832795 / 180.f);
         const float rad = __fmul_rn(angle, factorPI);
         const float a = (float)cos((double)rad), b = (float)sin((double)rad);
-        const uint8_t* ctr = blur + lvlOff + (long long)y * G.pitch + x;
+        const uint8_t* ctr = (const uint8_t*)blr + 18 * 40 + 18 + shB;  // (row, col) of the keypoint inside the staged patch
         int t[16];
 #pragma unroll
         for (int k = 0; k < 16; k++) {
             const int r = round_half_even(__fadd_rn(__fmul_rn(px[k], b), __fmul_rn(py[k], a)));
             const int c = round_half_even(__fsub_rn(__fmul_rn(px[k], a), __fmul_rn(py[k], b)));
-            t[k] = ctr[r * G.pitch + c];
+            t[k] = ctr[r * 40 + c];
         }
         int val = 0;
 #pragma unroll
