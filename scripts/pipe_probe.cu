@@ -27,6 +27,11 @@ __device__ __forceinline__ unsigned op(unsigned a, unsigned b, unsigned c) {
     if (OP == 8) return __viaddmax_s16x2(a, b, c);
     if (OP == 9) return __umulhi(a, b) + c;    // IMAD.HI
     if (OP == 10) return __popc(a) + b;
+    if (OP == 11) return (unsigned)__dp4a(a, b, c);
+    if (OP == 12) { unsigned d; asm("dp2a.lo.u32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c)); return d; }
+    if (OP == 13) return a + b + c;            // IADD3
+    if (OP == 14) return (a > b) ? c : a;      // ISETP + SEL
+    if (OP == 15) return (a << 8);             // shift (IMAD.SHL or SHF)
     return a;
 }
 
@@ -103,6 +108,13 @@ int main() {
     run("VIADDMNMX.S16x2", probe<8>, n);
     run("IMAD.HI", probe<9>, n);
     run("POPC+IADD", probe<10>, n);
+    run("DP4A", probe<11>, n);
+    run("DP2A", probe<12>, n);
+    run("IADD3", probe<13>, n);
+    run("ISETP+SEL (2 inst)", probe<14>, 2 * n);
+    run("SHL", probe<15>, n);
+    run("mix DP4A 4 : PRMT 4", probe_mix<11, 3, 4, 4>, (double)ITERS * 8);
+    run("mix DP4A 4 : IMAD 4", probe_mix<11, 5, 4, 4>, (double)ITERS * 8);
     run("mix VIMNMX3 4 : HMNMX2 4", probe_mix<0, 2, 4, 4>, (double)ITERS * 8);
     run("mix VIMNMX3 4 : IMAD 4", probe_mix<0, 5, 4, 4>, (double)ITERS * 8);
     run("mix PRMT 4 : IMAD 4", probe_mix<3, 5, 4, 4>, (double)ITERS * 8);
