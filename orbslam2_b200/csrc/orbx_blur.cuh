@@ -8,7 +8,10 @@
 //   vertical:   row sums of adjacent rows packed in 16-bit pairs, three DP2A + one IMAD per pixel over a 6-pair register
 //               window (loop unrolled by the window period 6, so the window is renamed, not moved);
 //   pipes (B200, scripts/pipe_probe.cu): DP4A/DP2A/IMAD issue on the FMA pipe, PRMT on the ALU pipe, and they overlap;
-//   reflect-101: row index reflection for y; left edge by byte permutation, right edge by an 8-byte gather (last lanes only).
+//   loads:      the 18 word loads of a 6-row group are issued together and nothing on the load path reads loaded data
+//               (a predicated-off instruction still waits for its source registers — that serialised every warp);
+//   reflect-101: row index reflection for y; the x reflection only exists in the EDGE instantiation, taken by the
+//               first and last warp of a row (left edge: byte permutation; right edge: 8-byte gather of the last lanes).
 #pragma once
 #include "orbx_internal.cuh"
 
@@ -21,10 +24,105 @@ __device__ __forceinline__ unsigned blur_dp2a(unsigned a16x2, unsigned b8x4, uns
     return d;
 }
 
+// BORDER_REFLECT_101 of an index at most one period outside [0, len) (the blur reaches 3 past either end; len >= 30)
 __device__ __forceinline__ int blur_reflect(int p, int len) {
-    if (len == 1) return 0;
-    while (p < 0 || p >= len) p = p < 0 ? -p : 2 * len - 2 - p;
-    return p;
+    p = abs(p);
+    return min(p, 2 * len - 2 - p);
+}
+
+struct BlurRows {
+    unsigned m[6], z[6], q[6];  // words at x0-4, x0, x0+4 of six consecutive input rows
+};
+
+template <bool EDGE>
+__device__ __forceinline__ void blur_strip(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, int pitch, int w,
+                                           int h, int x0, int y0) {
+    const unsigned K1 = 18u | (34u << 8) | (48u << 16) | (56u << 24);  // taps of x-3 .. x
+    const unsigned K2 = 48u | (34u << 8) | (18u << 16);                // taps of x+1 .. x+3 (x+4 weighs 0)
+    const unsigned V01 = 18u | (34u << 8), V23 = 48u | (56u << 8), V45 = 48u | (34u << 8);
+    const bool redge = EDGE && x0 + 8 > w;
+    const bool ledge = EDGE && x0 == 0;
+    int ridx[8];
+#pragma unroll
+    for (int j = 0; j < 8; j++) ridx[j] = redge ? blur_reflect(x0 + j, w) - x0 : j;
+    const int lback = ledge ? 0 : 4;
+    const uint8_t* col = src + x0;
+
+    auto load_group = [&](int n0, BlurRows& R) {  // input rows n0 .. n0+5 of the strip (absolute row y0 + n - 3)
+#pragma unroll
+        for (int i = 0; i < 6; i++) {
+            const int off = blur_reflect(min(y0 + n0 + i - 3, h + 2), h) * pitch;
+            R.z[i] = *(const unsigned*)(col + off);
+            R.q[i] = *(const unsigned*)(col + off + 4);  // may run into the row padding / next row: addressable
+            R.m[i] = *(const unsigned*)(col + off - lback);
+        }
+    };
+    // row sums H[0..3] of input row i of a loaded group
+    auto hsum = [&](const BlurRows& R, int n, int i, unsigned (&H)[4]) {
+        unsigned w0 = R.z[i], wp = R.q[i], wm = R.m[i];
+        if (EDGE) {
+            if (redge) {  // gather the reflected bytes (the lines are in L1 by now)
+                const uint8_t* rp = col + blur_reflect(min(y0 + n - 3, h + 2), h) * pitch;
+                w0 = rp[ridx[0]] | (rp[ridx[1]] << 8) | (rp[ridx[2]] << 16) | (rp[ridx[3]] << 24);
+                wp = rp[ridx[4]] | (rp[ridx[5]] << 8) | (rp[ridx[6]] << 16) | (rp[ridx[7]] << 24);
+            }
+            if (ledge) wm = __byte_perm(w0, wp, 0x1234);  // x = -4..-1 -> pixels 4, 3, 2, 1
+        }
+        H[0] = __dp4a(__byte_perm(w0, wp, 0x4321), K2, __dp4a(__byte_perm(wm, w0, 0x4321), K1, 0u));
+        H[1] = __dp4a(__byte_perm(w0, wp, 0x5432), K2, __dp4a(__byte_perm(wm, w0, 0x5432), K1, 0u));
+        H[2] = __dp4a(__byte_perm(w0, wp, 0x6543), K2, __dp4a(__byte_perm(wm, w0, 0x6543), K1, 0u));
+        H[3] = __dp4a(wp, K2, __dp4a(w0, K1, 0u));
+    };
+
+    // Vertical pass state: PW[j % 6][p] = H_j | H_j+1 << 16 for pixel p, hp = H of the previous row.
+    // Output row n-6 = 18*H_n-6 + 34*H_n-5 | 48*H_n-4 + 56*H_n-3 | 48*H_n-2 + 34*H_n-1 | 18*H_n: three DP2A + one IMAD.
+    unsigned PW[6][4], hp[4];
+    BlurRows R;
+    load_group(0, R);
+    {   // prologue: rows 0..5 only fill the window
+        unsigned H[4];
+        hsum(R, 0, 0, hp);
+#pragma unroll
+        for (int i = 1; i < 6; i++) {
+            hsum(R, i, i, H);
+#pragma unroll
+            for (int p = 0; p < 4; p++) {
+                PW[i - 1][p] = __byte_perm(hp[p], H[p], 0x5410);
+                hp[p] = H[p];
+            }
+        }
+    }
+    static_assert(BLUR_ROWS % 6 == 0, "row loop is unrolled by the window period");
+    for (int n0 = 6; n0 < BLUR_ROWS + 6; n0 += 6) {
+        if (y0 + n0 - 6 >= h) break;  // every remaining output lies below the image
+        load_group(n0, R);
+        uint8_t* orow = dst + (y0 + n0 - 6) * pitch + x0;
+#pragma unroll
+        for (int i = 0; i < 6; i++) {  // input row n = n0 + i, output row n - 6
+            unsigned H[4];
+            hsum(R, n0 + i, i, H);
+            unsigned sum[4];
+#pragma unroll
+            for (int p = 0; p < 4; p++) {
+                PW[(i + 5) % 6][p] = __byte_perm(hp[p], H[p], 0x5410);  // P_n-1
+                hp[p] = H[p];
+                unsigned acc = 18u * H[p] + 32768u;
+                acc = blur_dp2a(PW[i][p], V01, acc);            // P_n-6
+                acc = blur_dp2a(PW[(i + 2) % 6][p], V23, acc);  // P_n-4
+                acc = blur_dp2a(PW[(i + 4) % 6][p], V45, acc);  // P_n-2
+                sum[p] = acc;
+            }
+            // result byte p = bits 16..23 of sum[p]
+            const unsigned out = __byte_perm(__byte_perm(sum[0], sum[1], 0x0062), __byte_perm(sum[2], sum[3], 0x0062), 0x5410);
+            if (y0 + n0 + i - 6 < h) {
+                if (!EDGE || x0 + 4 <= w) {
+                    *(unsigned*)(orow + i * pitch) = out;
+                } else {
+                    for (int p = 0; p < w - x0; p++) orow[i * pitch + p] = (uint8_t)(out >> (8 * p));
+                }
+            }
+        }
+    }
 }
 
 __global__ void __launch_bounds__(32 * BLUR_WARPS) k_blur(const DevPlan* __restrict__ P, const uint8_t* __restrict__ pyr,
@@ -42,83 +140,7 @@ __global__ void __launch_bounds__(32 * BLUR_WARPS) k_blur(const DevPlan* __restr
     const int w = G.w, h = G.h;
     if (x0 >= w) return;
     const long long lvlOff = G.pyrOff + (long long)f * G.frameStride;
-    const uint8_t* src = pyr + lvlOff;
-    uint8_t* dst = blur + lvlOff;
-    // x reflect-101: the left edge is a byte permutation of the first two words; at the right edge the 8 bytes at
-    // x0..x0+7 are gathered through offsets computed once (only the last one or two lanes of a row take that path)
-    const bool redge = x0 + 8 > w;
-    int ridx[8];
-#pragma unroll
-    for (int j = 0; j < 8; j++) ridx[j] = redge ? blur_reflect(x0 + j, w) - x0 : j;
-
-    // Horizontal pass: one DP4A pair per pixel on byte windows cut out of (wm, w0, wp) by PRMT.
-    // Vertical pass: the 16-bit row sums of vertically adjacent rows are packed in pairs P_j = (H_j, H_j+1), so an
-    // output is three DP2A and one IMAD: 18*H_n-6 + 34*H_n-5 | 48*H_n-4 + 56*H_n-3 | 48*H_n-2 + 34*H_n-1 | 18*H_n.
-    const unsigned K1 = 18u | (34u << 8) | (48u << 16) | (56u << 24);  // taps of x-3 .. x
-    const unsigned K2 = 48u | (34u << 8) | (18u << 16);                // taps of x+1 .. x+3 (x+4 weighs 0)
-    const unsigned V01 = 18u | (34u << 8), V23 = 48u | (56u << 8), V45 = 48u | (34u << 8);
-    unsigned PW[6][4];  // PW[j % 6][p] = H_j | H_j+1 << 16 for pixel p; the loop is unrolled by the window period 6
-    unsigned hp[4];     // H of the previous input row
-    static_assert((BLUR_ROWS + 6) % 6 == 0, "row loop is unrolled by the window period");
-    for (int ib = 0; ib < BLUR_ROWS + 6; ib += 6) {
-    if (y0 + ib - 6 >= h) break;  // every output of this and the following groups lies below the image
-    // all loads of the 6-row group are issued before any is used: the kernel is bound by memory latency, not by
-    // instruction issue, so what matters is how many rows each warp has in flight
-    unsigned Wm[6], W0[6], Wp[6];
-#pragma unroll
-    for (int i = 0; i < 6; i++) {
-        const int yin = y0 + ib + i - 3;
-        const uint8_t* rp = src + (long long)blur_reflect(min(yin, h + 2), h) * G.pitch + x0;
-        if (redge) {
-            W0[i] = rp[ridx[0]] | (rp[ridx[1]] << 8) | (rp[ridx[2]] << 16) | (rp[ridx[3]] << 24);
-            Wp[i] = rp[ridx[4]] | (rp[ridx[5]] << 8) | (rp[ridx[6]] << 16) | (rp[ridx[7]] << 24);
-        } else {
-            W0[i] = *(const unsigned*)rp;
-            Wp[i] = *(const unsigned*)(rp + 4);
-        }
-        // (no use of loaded data in this loop — a predicated-off instruction still waits for its source registers, so
-        // the left-edge reflection is applied in the compute loop; here the first column just re-reads its own word)
-        Wm[i] = *(const unsigned*)(rp - (x0 > 0 ? 4 : 0));
-    }
-#pragma unroll
-    for (int i = 0; i < 6; i++) {   // input row n = ib + i of the strip (absolute row y0 + n - 3)
-        unsigned H[4];
-        {
-            const unsigned w0 = W0[i], wp = Wp[i];
-            const unsigned wm = (x0 > 0) ? Wm[i] : __byte_perm(w0, wp, 0x1234);  // x = -4..-1 -> pixels 4, 3, 2, 1
-            H[0] = __dp4a(__byte_perm(w0, wp, 0x4321), K2, __dp4a(__byte_perm(wm, w0, 0x4321), K1, 0u));
-            H[1] = __dp4a(__byte_perm(w0, wp, 0x5432), K2, __dp4a(__byte_perm(wm, w0, 0x5432), K1, 0u));
-            H[2] = __dp4a(__byte_perm(w0, wp, 0x6543), K2, __dp4a(__byte_perm(wm, w0, 0x6543), K1, 0u));
-            H[3] = __dp4a(wp, K2, __dp4a(w0, K1, 0u));
-        }
-        if (ib + i >= 1) {
-#pragma unroll
-            for (int p = 0; p < 4; p++) PW[(i + 5) % 6][p] = __byte_perm(hp[p], H[p], 0x5410);  // P_n-1
-        }
-        if (ib + i >= 6) {
-            const int yout = y0 + ib + i - 6;
-            if (yout < h) {
-                unsigned sum[4];
-#pragma unroll
-                for (int p = 0; p < 4; p++) {
-                    unsigned acc = 18u * H[p] + 32768u;
-                    acc = blur_dp2a(PW[i % 6][p], V01, acc);        // P_n-6
-                    acc = blur_dp2a(PW[(i + 2) % 6][p], V23, acc);  // P_n-4
-                    acc = blur_dp2a(PW[(i + 4) % 6][p], V45, acc);  // P_n-2
-                    sum[p] = acc;
-                }
-                // result byte p = bits 16..23 of sum[p]
-                const unsigned out = __byte_perm(__byte_perm(sum[0], sum[1], 0x0062), __byte_perm(sum[2], sum[3], 0x0062), 0x5410);
-                if (x0 + 4 <= w) {
-                    *(unsigned*)(dst + (long long)yout * G.pitch + x0) = out;
-                } else {
-                    for (int p = 0; p < w - x0; p++) dst[(long long)yout * G.pitch + x0 + p] = (uint8_t)(out >> (8 * p));
-                }
-            }
-        }
-#pragma unroll
-        for (int p = 0; p < 4; p++) hp[p] = H[p];
-    }
-    }
+    // warp-uniform: does this warp hold the first column or a lane whose 8-byte window crosses the right border?
+    if (tx == 0 || tx * 128 + 132 > w) blur_strip<true>(pyr + lvlOff, blur + lvlOff, G.pitch, w, h, x0, y0);
+    else blur_strip<false>(pyr + lvlOff, blur + lvlOff, G.pitch, w, h, x0, y0);
 }
-
