@@ -125,7 +125,7 @@ __device__ __forceinline__ void blur_strip(const uint8_t* __restrict__ src, uint
     }
 }
 
-__global__ void __launch_bounds__(32 * BLUR_WARPS) k_blur(const DevPlan* __restrict__ P, const uint8_t* __restrict__ pyr,
+__global__ void __launch_bounds__(32 * BLUR_WARPS, 6) k_blur(const DevPlan* __restrict__ P, const uint8_t* __restrict__ pyr,
                                                           uint8_t* __restrict__ blur, int f0) {
     const int lane = threadIdx.x & 31;
     const int f = f0 + blockIdx.y;
