@@ -412,7 +412,8 @@ static int launch_chain(orbx_handle* h, cudaStream_t cs, int f0, int nb, bool st
     for (int l = 1; l < nl; l++) {
         const LevelGeo& G = D.lv[l];
         dim3 grid((G.w + 255) / 256, (G.h + 3) / 4, nb), block(64, 4);
-        if (G.resizeFast) k_resize_fast<<<grid, block, 0, cs>>>(h->dPlan, l, h->dPyr, h->dTabs, f0);
+        dim3 gridFast((G.w + 255) / 256, (G.h + 4 * RESIZE_ROWS - 1) / (4 * RESIZE_ROWS), nb);
+        if (G.resizeFast) k_resize_fast<<<gridFast, block, 0, cs>>>(h->dPlan, l, h->dPyr, h->dTabs, f0);
         else k_resize<<<grid, block, 0, cs>>>(h->dPlan, l, h->dPyr, h->dTabs, f0);
         KCHECK(h, "k_resize");
     }
