@@ -232,7 +232,7 @@ static int build_plan(orbx_handle* h, int w, int hgt, int batch) {
             G.ytabOff = (int)tabs.size();
             linear_table(D.lv[l - 1].h, G.h, false, tabs);
         }
-        fastSmem = std::max(fastSmem, (size_t)2 * G.boxW * G.boxH + sizeof(FastSmemHdr));
+        fastSmem = std::max(fastSmem, (size_t)2 * G.boxW * G.boxH + ((G.boxW * G.boxH / 2 + 15) & ~15) + sizeof(FastSmemHdr));
     }
     D.totalSt = cellBase;
     D.totalBlurTiles = blurBase;
@@ -509,7 +509,24 @@ extern "C" int orbx_extract_batch(orbx_t* h, const uint8_t* imgs, int batch, int
         chunk = h->chunk > 0 ? h->chunk : 48;
         if (batch < 2 * chunk) chunk = batch;
     }
-    const int nChunks = (batch + chunk - 1) / chunk;
+    // chunk boundaries: the first two chunks are short (1/3 and 2/3 of a chunk) so the pipeline fills quickly — the
+    // first copy-in is the only one nothing overlaps
+    std::vector<int> cuts;
+    if (chunk >= batch) {
+        cuts = {0, batch};
+    } else {
+        cuts.push_back(0);
+        int at = 0;
+        if (chunk >= 12 && batch >= 3 * chunk) {
+            at += chunk / 3; cuts.push_back(at);
+            at += (2 * chunk) / 3; cuts.push_back(at);
+        }
+        while (at < batch) {
+            at = std::min(batch, at + chunk);
+            cuts.push_back(at);
+        }
+    }
+    const int nChunks = (int)cuts.size() - 1;
 
     stamp(h, 0);
     CK(cudaMemsetAsync(h->dCandCount, 0, (size_t)batch * nl * sizeof(int), st));
@@ -528,7 +545,7 @@ extern "C" int orbx_extract_batch(orbx_t* h, const uint8_t* imgs, int batch, int
         CK(cudaEventRecord(h->evStart, st));
         CK(cudaStreamWaitEvent(h->sIn, h->evStart, 0));
         for (int c = 0; c < nChunks; c++) {
-            const int f0 = c * chunk, nb = std::min(chunk, batch - f0);
+            const int f0 = cuts[c], nb = cuts[c + 1] - cuts[c];
             cudaStream_t cs = h->sComp[c & 1];
             rc = copy_in(h, h->sIn, imgs, f0, nb, w, hgt, stride, img_stride);
             if (rc != ORBX_OK) return rc;

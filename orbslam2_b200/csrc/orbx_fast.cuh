@@ -85,12 +85,13 @@ struct FastSmemHdr {
     int nAll[FAST_MAX_ST_CELLS];
     int nIni[FAST_MAX_ST_CELLS];
     int emitBase[FAST_MAX_ST_CELLS];
-    int total, gbase, slot, nList;
+    int total, gbase, slot, nList, nAct;
     unsigned firstCol[64], lastCol[64];  // per word column: bytes that are the first / last column of a cell
+    unsigned valid[64];                  // per word column: bytes inside the detection columns
     unsigned char rowFlag[128];          // per detection row: bit0 first row of a cell, bit1 last row
 };
 
-__global__ void __launch_bounds__(FAST_THREADS) k_fast(const __grid_constant__ TmapPack maps,
+__global__ void __launch_bounds__(FAST_THREADS, 3) k_fast(const __grid_constant__ TmapPack maps,
                                                        const DevPlan* __restrict__ P, u64* __restrict__ cand,
                                                        int* __restrict__ candCount, int* __restrict__ err, int f0) {
     extern __shared__ __align__(128) uint8_t fast_smem[];
@@ -113,7 +114,8 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast(const __grid_constant__ T
     const int tileBytes = boxW * boxH;
     unsigned* tile = (unsigned*)fast_smem;
     unsigned* sc = (unsigned*)(fast_smem + tileBytes);
-    FastSmemHdr* H = (FastSmemHdr*)(fast_smem + 2 * tileBytes);
+    unsigned short* act = (unsigned short*)(fast_smem + 2 * tileBytes);  // units (words) with a corner, <= tileBytes/4 entries
+    FastSmemHdr* H = (FastSmemHdr*)(fast_smem + 2 * tileBytes + (((tileBytes >> 1) + 15) & ~15));
     const int oxa = (xFirst - 6) & ~15, oy = yFirst - 3;
     const int wx0 = (xFirst - oxa) >> 2, wx1 = (xEnd - 1 - oxa) >> 2;
     const int nW = wx1 - wx0 + 1, nR = yEnd - yFirst;
@@ -131,6 +133,7 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast(const __grid_constant__ T
         H->total = 0;
         H->slot = 0;
         H->nList = 0;
+        H->nAct = 0;
     }
     if (tid < FAST_MAX_ST_CELLS) {
         H->nAll[tid] = 0;
@@ -140,11 +143,12 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast(const __grid_constant__ T
     const unsigned divCw = (65536u + G.wCell - 1) / G.wCell;  // v / wCell == (v * divCw) >> 16 for v < 1024
     const unsigned divCh = (65536u + G.hCell - 1) / G.hCell;
     for (int i = tid; i < nW; i += FAST_THREADS) {
-        unsigned fc = 0, lc = 0;
+        unsigned fc = 0, lc = 0, vm = 0;
 #pragma unroll
         for (int b = 0; b < 4; b++) {
             const int x = oxa + ((wx0 + i) << 2) + b;
             if (x >= xFirst && x < xEnd) {
+                vm |= 0xFFu << (8 * b);
                 const int v = x - xFirst;
                 const int r = v - (int)(((unsigned)v * divCw) >> 16) * G.wCell;
                 if (r == 0) fc |= 0xFFu << (8 * b);
@@ -153,6 +157,7 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast(const __grid_constant__ T
         }
         H->firstCol[i] = fc;
         H->lastCol[i] = lc;
+        H->valid[i] = vm;
     }
     for (int i = tid; i < nR; i += FAST_THREADS) {
         const int r = i - (int)(((unsigned)i * divCh) >> 16) * G.hCell;
@@ -243,14 +248,16 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast(const __grid_constant__ T
         }
         const unsigned se = fast_score2(ce, ve, negThm1);
         const unsigned so = fast_score2(co, vo, negThm1);
-        unsigned s = se | (so << 8);
-        if (wi == 0 || wi == nW - 1) {  // bytes outside the detection columns
-            const int xb = oxa + (wx << 2);
-#pragma unroll
-            for (int b = 0; b < 4; b++)
-                if (xb + b < xFirst || xb + b >= xEnd) s &= ~(0xFFu << (8 * b));
-        }
+        const unsigned s = (se | (so << 8)) & H->valid[wi];  // drop bytes outside the detection columns
         sc[(wy + 3) * pitchW + wx] = s;
+        if (s) {  // remember the words that hold a corner: phase 2 visits only those (warp-aggregated append)
+            const unsigned m = __activemask();
+            const int lane = tid & 31, leader = __ffs(m) - 1;
+            int base = 0;
+            if (lane == leader) base = atomicAdd(&H->nAct, __popc(m));
+            base = __shfl_sync(m, base, leader);
+            act[base + __popc(m & ((1u << lane) - 1u))] = (unsigned short)u;
+        }
     }
     __syncthreads();
 
@@ -258,12 +265,13 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast(const __grid_constant__ T
     // list (packed wy<<16 | x<<8 | value) that overlays the no-longer-needed pixel tile
     unsigned* list = tile;
     const int listCap = tileBytes >> 2;
-    for (int u = tid; u < nUnits; u += FAST_THREADS) {
+    const int nAct = H->nAct;
+    for (int ia = tid; ia < nAct; ia += FAST_THREADS) {
+        const int u = act[ia];
         const int wy = (int)(((unsigned)u * divW) >> 20), wi = u - wy * nW;
         const int wx = wx0 + wi;
         const unsigned* q = sc + (wy + 3) * pitchW + wx;
         const unsigned s = q[0];
-        if (!s) continue;
         const unsigned s7 = s & 0x7f7f7f7fu;
         const unsigned nfc = ~H->firstCol[wi], nlc = ~H->lastCol[wi];
         const unsigned rf = H->rowFlag[wy];
