@@ -91,7 +91,7 @@ struct FastSmemHdr {
     unsigned char rowFlag[128];          // per detection row: bit0 first row of a cell, bit1 last row
 };
 
-__global__ void __launch_bounds__(FAST_THREADS, 3) k_fast(const __grid_constant__ TmapPack maps,
+__global__ void __launch_bounds__(FAST_THREADS, 4) k_fast(const __grid_constant__ TmapPack maps,
                                                        const DevPlan* __restrict__ P, u64* __restrict__ cand,
                                                        int* __restrict__ candCount, int* __restrict__ err, int f0) {
     extern __shared__ __align__(128) uint8_t fast_smem[];
