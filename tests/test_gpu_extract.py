@@ -147,3 +147,19 @@ def test_host_pipeline_chunks_match_single_launch(ob):
     k1, d1 = ex(imgs[22])
     assert k1.tobytes() == k0[22, :n0[22]].tobytes() and np.array_equal(ex.pyramid_level(3, 0), lvl)
     ex.close()
+
+
+def test_4k_frame_all_stages(ob):
+    """BASELINE config 5: 3840x2160, 8000 keypoints — every stage bit-exact at the largest shape (26 925 FAST cells,
+    per-level quotas up to 1737, TMA tiles at the widest cell size)."""
+    p = _params(8000)
+    ex = ob.ORBextractor(**p); orc = Oracle(**p)
+    img = synth_image(3840, 2160, 0)
+    kps, desc = ex(img)
+    same = _compare_frame(ex, orc, img, 0, None, kps, desc)
+    assert same.all(), f"descriptors identical {int(same.sum())}/{len(same)}"
+    # a batch of two 4K frames through the chunked host path gives the same bytes
+    ex.set_chunk(1)
+    kb, db, nb = ex.extract_batch(np.stack([img, img[::-1].copy()]))
+    assert kb[0, :nb[0]].tobytes() == kps.tobytes() and np.array_equal(db[0, :nb[0]], desc)
+    ex.close()
