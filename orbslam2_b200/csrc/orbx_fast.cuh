@@ -8,9 +8,10 @@
 //     score = max(M - v, v - m) - 1   = the largest t at which the pixel is still a FAST corner (OpenCV cornerScore)
 //   the pixel is a corner at threshold t  <=>  score >= t.
 // The arc minima / maxima are computed for TWO pixels per instruction with the packed 16-bit DPX min/max
-// (VIMNMX.U16x2 / VIMNMX3.U16x2; measured on B200: the 2-input form issues at 4 warp-inst/clk/SM, the 3-input form and
-// PRMT at 2 — scripts/pipe_probe.cu), in the paired-arc formulation of fast_score2 (47 two-input min/max per polarity
-// and pixel pair). One thread scores 4 horizontally adjacent pixels (one 32-bit word of the tile).
+// (VIMNMX.U16x2 / VIMNMX3.U16x2) in the paired-arc formulation of fast_score2: 36 instructions per polarity and pixel
+// pair. Measured on B200 (scripts/pipe_probe.cu): every ALU-pipe instruction — VIMNMX 2- or 3-input, HMNMX2, PRMT, LOP3,
+// IADD3 — issues at 2 warp-inst/clk/SM, so this kernel is bound by its ALU-pipe instruction count; IMAD/DP4A go to the
+// FMA pipe (also 2/clk/SM) and overlap. One thread scores 4 horizontally adjacent pixels (one 32-bit word of the tile).
 //
 // One CTA = a "supertile" of stCX x stCY cells of one level of one frame:
 //   TMA 3-D tile load (x start rounded down to 16 bytes — an unaligned innermost coordinate faults on sm_100a)
@@ -41,7 +42,7 @@ __device__ __forceinline__ unsigned fast_align(unsigned wm, unsigned w0, unsigne
 // vh = centres; returns max(score - (minTh-1), 0) as plain 16-bit lanes.
 // The 16 arcs of 9 pair up around the 8 even-aligned runs of 8: with A8[k] = min(c[k..k+7]) (k even, by doubling),
 //   arc9(k) = min(A8[k], c[k+8])   arc9(k-1) = min(c[k-1], A8[k])   =>   max of the two = min(A8[k], max(c[k+8], c[k-1]))
-// so M = max over the 8 even k of min(A8[k], max(c[k+8], c[k-1])): 47 two-input min/max per polarity instead of 80.
+// so M = max over the 8 even k of min(A8[k], max(c[k+8], c[k-1])): 36 instructions per polarity instead of 40.
 __device__ __forceinline__ unsigned fast_score2(const unsigned (&c)[16], unsigned vh, unsigned negThm1) {
     unsigned a2[8], b2[8], a4[8], b4[8];
 #pragma unroll

@@ -51,6 +51,46 @@ __global__ void probe(unsigned* out, unsigned seed) {
     if (s == 0x12345678u) out[0] = s;
 }
 
+// cross-chain variant: operand b is the neighbouring chain, so nothing is loop invariant or idempotent
+template <int OP>
+__global__ void probe_x(unsigned* out, unsigned seed) {
+    unsigned r[CHAINS];
+#pragma unroll
+    for (int i = 0; i < CHAINS; i++) r[i] = seed * (threadIdx.x + 1) + i * 0x9E3779B9u;
+    unsigned c = seed | 1u;
+    for (int it = 0; it < ITERS; it++) {
+#pragma unroll
+        for (int i = 0; i < CHAINS; i++) {
+            if (OP == 0) asm("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(r[i]) : "r"(r[(i + 1) % CHAINS]), "r"(c));
+            if (OP == 1) asm("lop3.b32 %0, %0, %1, %2, 0xE8;" : "+r"(r[i]) : "r"(r[(i + 1) % CHAINS]), "r"(c));
+            if (OP == 2) r[i] = __vminu2(r[i], r[(i + 1) % CHAINS]) + 0u;
+            if (OP == 3) r[i] = r[i] + r[(i + 1) % CHAINS] + c;
+            if (OP == 4) r[i] = __popc(r[i] ^ r[(i + 1) % CHAINS]);
+            if (OP == 5) {
+                __half2 x = *(__half2*)&r[i], y = *(__half2*)&r[(i + 1) % CHAINS];
+                __half2 z = __hmin2(x, y);
+                r[i] = *(unsigned*)&z + 0u;
+            }
+            if (OP == 6) {  // half the chains VIMNMX3, half HMNMX2
+                if (i & 1) {
+                    __half2 x = *(__half2*)&r[i], y = *(__half2*)&r[(i + 2) % CHAINS];
+                    __half2 z = __hmax2(x, y);
+                    r[i] = *(unsigned*)&z;
+                } else
+                    r[i] = __vimin3_u16x2(r[i], r[(i + 2) % CHAINS], c);
+            }
+            if (OP == 7) {  // half VIMNMX3, half IMAD
+                if (i & 1) r[i] = r[i] * r[(i + 2) % CHAINS] + c;
+                else r[i] = __vimin3_u16x2(r[i], r[(i + 2) % CHAINS], c);
+            }
+        }
+    }
+    unsigned s = 0;
+#pragma unroll
+    for (int i = 0; i < CHAINS; i++) s ^= r[i];
+    if (s == 0x12345678u) out[0] = s;
+}
+
 // mix: A of op X then B of op Y per iteration, independent chains
 template <int X, int Y, int NX, int NY>
 __global__ void probe_mix(unsigned* out, unsigned seed) {
@@ -113,6 +153,14 @@ int main() {
     run("IADD3", probe<13>, n);
     run("ISETP+SEL (2 inst)", probe<14>, 2 * n);
     run("SHL", probe<15>, n);
+    run("x LOP3 xor3", probe_x<0>, n);
+    run("x LOP3 maj", probe_x<1>, n);
+    run("x VIMNMX.U16x2 2-in", probe_x<2>, n);
+    run("x IADD3", probe_x<3>, n);
+    run("x XOR+POPC (2 inst)", probe_x<4>, 2 * n);
+    run("x HMNMX2", probe_x<5>, n);
+    run("x VIMNMX3 : HMNMX2 1:1", probe_x<6>, n);
+    run("x VIMNMX3 : IMAD 1:1", probe_x<7>, n);
     run("mix DP4A 4 : PRMT 4", probe_mix<11, 3, 4, 4>, (double)ITERS * 8);
     run("mix DP4A 4 : IMAD 4", probe_mix<11, 5, 4, 4>, (double)ITERS * 8);
     run("mix VIMNMX3 4 : HMNMX2 4", probe_mix<0, 2, 4, 4>, (double)ITERS * 8);
