@@ -64,6 +64,18 @@ def peaks():
         return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def ncu_traffic(kernel, batch):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one launch of the dominant kernel, from the committed
+    `ncu --set full` capture of this same command (profiles/traffic.json: {"batch": B, "<stage>": bytes}); None when
+    the capture was taken at another batch size."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            t = json.load(f)
+        return float(t[kernel]) if int(t.get("batch", -1)) == batch and kernel in t else None
+    except Exception:
+        return None
+
+
 def level_area_sum(w, h):
     """Sum of pyramid level areas, same rounding as the extractor (src/ORBextractor.cc:925-926)."""
     total, sf = 0, np.float32(1.0)
@@ -335,7 +347,9 @@ def run_ours(args):
     achieved = alg / (kern[dom] * 1e-3) / 1e9
     step_ms = sum(kern.values())
     roofline = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                "frac": achieved / peak, "traffic": ncu_traffic(dom, B), "peak_source": peak_src,
+                "limiter": "ALU-pipe issue (packed 16-bit min/max, 2 warp-inst/clk/SM; profiles/ r01f ncu: pipe_alu "
+                           "active ~80 %, DRAM < 5 % of peak) - the HBM fraction is reported as the contract asks",
                 "algorithmic_bytes_per_launch": alg, "kernel_ms": kern[dom],
                 "stage_ms": {k: round(v, 4) for k, v in kern.items()},
                 "whole_step_achieved": alg / (step_ms * 1e-3) / 1e9, "whole_step_frac": alg / (step_ms * 1e-3) / 1e9 / peak}
