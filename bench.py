@@ -50,6 +50,7 @@ def parse_args():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=384, help="frames per step per GPU")
     ap.add_argument("--chunk", type=int, default=0, help="frames per pipeline chunk of the host-buffer path (0 = default)")
+    ap.add_argument("--dev-chunk", type=int, default=0, help="frames per chunk of the device-buffer path (0 = one launch sequence)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-match", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline leg")
@@ -292,6 +293,7 @@ def run_ours(args):
         for _ in range(warmup):
             fn()
         barrier()
+        l0 = ex.launch_count()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         th0 = time.perf_counter()
         e0.record(stream)
@@ -300,39 +302,32 @@ def run_ours(args):
         e1.record(stream)
         barrier()
         sampler.mark(th0, time.perf_counter())
-        return e0.elapsed_time(e1) * 1e-3, n
+        return e0.elapsed_time(e1) * 1e-3, n, ex.launch_count() - l0
 
-    # ---- device-resident throughput (value) with per-stage CUDA events for the roofline of the dominant kernel
-    ex.set_profiling(True)
+    # ---- device-resident throughput (value)
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    for _ in range(args.warmup):
-        step_device()
-    barrier()
-    launches0 = ex.launch_count()
+    ex.set_chunk(args.dev_chunk)
+    t_dev, n, launches = timed(step_device, args.steps, args.warmup)
+    # ---- per-stage CUDA events (on the launching stream) for the roofline of the dominant kernel: same steps, whole-batch launches
+    ex.set_chunk(0)
+    ex.set_profiling(True)
+    step_device()
     stage_sum = {}
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    th0 = time.perf_counter()
-    e0.record(stream)
     for _ in range(args.steps):
-        n = step_device()
+        step_device()
         for k, v in ex.stage_ms().items():
             stage_sum[k] = stage_sum.get(k, 0.0) + v
-    e1.record(stream)
     barrier()
-    sampler.mark(th0, time.perf_counter())
-    t_dev = e0.elapsed_time(e1) * 1e-3
-    launches = ex.launch_count() - launches0
     n_out_mean = float(np.mean(n))
     t_dev = max_over_ranks(t_dev)
     value = world * B * args.steps / t_dev
     ex.set_profiling(False)
 
     # ---- end to end through the C ABI with host buffers
-    if args.chunk:
-        ex.set_chunk(args.chunk)
-    t_e2e, _ = timed(step_host, args.steps, args.warmup)
+    ex.set_chunk(args.chunk)
+    t_e2e, _, launches_e2e = timed(step_host, args.steps, args.warmup)
     t_e2e = max_over_ranks(t_e2e)
     clocks = sampler.stop() if rank == 0 else None
     e2e = world * B * args.steps / t_e2e

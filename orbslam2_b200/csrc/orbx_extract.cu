@@ -505,7 +505,7 @@ extern "C" int orbx_extract_batch(orbx_t* h, const uint8_t* imgs, int batch, int
     // head) and chunk c-1 leaves on the copy-out stream. Device buffers: one launch sequence for the whole batch.
     const bool hostIO = h->inSpace == ORBX_MEM_HOST || h->outSpace == ORBX_MEM_HOST;
     int chunk = batch;
-    if (hostIO && !h->profiling) {
+    if (!h->profiling && (hostIO || h->chunk > 0)) {  // device buffers are chunked only on request (orbx_set_chunk)
         chunk = h->chunk > 0 ? h->chunk : 48;
         if (batch < 2 * chunk) chunk = batch;
     }
