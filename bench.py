@@ -204,6 +204,32 @@ def cpu_baseline(frames, seconds):
                       f"{dt:.1f} s wall; {nk / count:.0f} keypoints/frame"}
 
 
+def cpu_match_baseline(nt=1000000, q_per_thread=32):
+    """The reference's DescriptorDistance loop (SWAR popcount on 8 x int32, src/ORBmatcher.cc:1643-1659) scanning the
+    whole train matrix with the best / second-best rule, one block of queries per host thread (oracle port: ORBmatcher.cc
+    cannot be compiled here). A bounded sample: threads x q_per_thread queries x 1M train rows."""
+    import oracle_lib
+    from orbslam2_b200.synth import synth_descriptors
+    threads = cpu_cores()
+    t, q = synth_descriptors(nt, threads * q_per_thread, seed=7, dup=1000)
+    P = [oracle_lib.OraclePrims() for _ in range(threads)]
+
+    def work(k):
+        P[k].knn2(q[k * q_per_thread:(k + 1) * q_per_thread], t)
+
+    th = [threading.Thread(target=work, args=(k,)) for k in range(threads)]
+    t0 = time.perf_counter()
+    for x in th:
+        x.start()
+    for x in th:
+        x.join()
+    dt = time.perf_counter() - t0
+    pairs = threads * q_per_thread * nt
+    return {"value": pairs / dt / 1e9, "unit": "Gpairs/s", "cores": threads, "kind": "port",
+            "sample": f"{threads * q_per_thread} queries x {nt} train rows, {threads} threads, {dt:.1f} s wall; "
+                      "reference SWAR DescriptorDistance + best/second-best scan"}
+
+
 def run_reference(args):
     """--impl reference: the reference's own CPU implementation on the host cores, same metric/config/unit."""
     rank = int(os.environ.get("RANK", "0"))
@@ -350,6 +376,8 @@ def run_ours(args):
                 "whole_step_achieved": alg / (step_ms * 1e-3) / 1e9, "whole_step_frac": alg / (step_ms * 1e-3) / 1e9 / peak}
 
     match = None if args.no_match else bench_match(ob, torch, dev, rank, world, barrier, max_over_ranks)
+    if match is not None and rank == 0 and not args.no_cpu_baseline:
+        match["cpu_baseline"] = cpu_match_baseline()
     cpu = None
     if rank == 0 and not args.no_cpu_baseline:
         cpu = cpu_baseline(frames, args.cpu_seconds)
