@@ -127,6 +127,52 @@ int orbm_window_search(orbm_t* m, const uint8_t* q, int nq, const int32_t* cand_
 /* Batched DescriptorDistance: d[i] = hamming(a[i], b[i]). */
 int orbm_distance(orbm_t* m, const uint8_t* a, const uint8_t* b, int n, uint16_t* d);
 
+/* ---- device-resident windowed search: replaces ORBmatcher::SearchByProjection(Frame& CurrentFrame, const Frame&
+ * LastFrame, float th, bool bMono) (src/ORBmatcher.cc:1324-1466) together with what it calls on the current frame:
+ * Frame::AssignFeaturesToGrid / PosInGrid (src/Frame.cc:231-246, 383-393), Frame::GetFeaturesInArea (src/Frame.cc:328-381),
+ * DescriptorDistance and ComputeThreeMaxima (src/ORBmatcher.cc:1597-1638). Queries (last-frame map points) claim
+ * current-frame keypoints greedily in index order exactly as the sequential loop does; the device reaches the same
+ * result by a fixed-point iteration. All pointers live in the matcher's input / output memory space. ------ */
+typedef struct {
+    float fx, fy, cx, cy, bf;      /* Frame::fx, fy, cx, cy, mbf */
+    float minX, maxX, minY, maxY;  /* Frame::mnMinX .. mnMaxY (src/Frame.cc:98-113) */
+    float grid_w_inv, grid_h_inv;  /* Frame::mfGridElementWidthInv / HeightInv (src/Frame.cc:101-102); 64 x 48 cells */
+    int nlevels;
+    float scale[ORBX_MAX_LEVELS];  /* CurrentFrame.mvScaleFactors */
+    float Rcw[9], tcw[3];          /* CurrentFrame.mTcw, row major */
+    int forward, backward;         /* bForward / bBackward as computed at src/ORBmatcher.cc:1343-1344 */
+    float th;                      /* window factor */
+    int th_high;                   /* ORBmatcher::TH_HIGH (100) */
+    int check_orientation;         /* mbCheckOrientation */
+} orbm_proj_params;
+
+typedef struct {              /* LastFrame: n keypoints */
+    int n;
+    const float* world_pos;   /* n x 3, pMP->GetWorldPos() (ignored where flags bit0 is clear) */
+    const uint8_t* flags;     /* bit0: mvpMapPoints[i] != NULL && !mvbOutlier[i]; bit1: pMP->Observations() > 0 */
+    const int32_t* octave;    /* mvKeys[i].octave */
+    const float* angle;       /* mvKeysUn[i].angle */
+    const uint8_t* desc;      /* n x 32, pMP->GetDescriptor() */
+} orbm_last_frame;
+
+typedef struct {              /* CurrentFrame: n keypoints */
+    int n;
+    const orbx_kp* keys_un;   /* mvKeysUn (pt, octave, angle are read) */
+    const float* u_right;     /* mvuRight, or NULL for monocular frames (treated as -1) */
+    const uint8_t* desc;      /* mDescriptors, n x 32 */
+    const uint8_t* taken;     /* 1 where mvpMapPoints[i] is set with Observations() > 0 on entry; may be NULL */
+} orbm_cur_frame;
+
+/* cur_match[i2]  (cur->n)  index into LastFrame of the map point left in CurrentFrame.mvpMapPoints[i2], -1 = none
+ * last_match[i]  (last->n) keypoint i2 claimed by last-frame point i before the rotation filter, -1 = none
+ * last_keep[i]   (last->n) 1 if that claim survived the rotation-consistency filter
+ * nmatches       the function's return value (host pointer) */
+int orbm_search_by_projection(orbm_t* m, const orbm_proj_params* p, const orbm_last_frame* last,
+                              const orbm_cur_frame* cur, int32_t* cur_match, int32_t* last_match, uint8_t* last_keep,
+                              int* nmatches);
+/* Diagnostics of the last orbm_search_by_projection call: fixed-point rounds and candidate pairs evaluated. */
+int orbm_search_stats(orbm_t* m, int* rounds, int64_t* candidates);
+
 /* ---- instrumentation ---------------------------------------------------------------------------------------------- */
 /* CUDA stream (cudaStream_t) the handle launches on — for timing with events on the launching stream. */
 int orbx_stream(orbx_t* h, void** stream);

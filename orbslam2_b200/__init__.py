@@ -4,3 +4,4 @@ Python host mirror of include/orbx.h; all compute runs in hand-written sm_100a C
 from .extractor import ORBextractor, KP_DTYPE, compute_stereo_matches  # noqa: F401
 from .matcher import ORBmatcher  # noqa: F401
 from ._lib import OrbxError  # noqa: F401
+from .frame import Frame  # noqa: F401

@@ -28,8 +28,29 @@ SYMBOLS = ["orbx_create", "orbx_destroy", "orbx_set_memory_space", "orbx_extract
            "orbx_max_keypoints", "orbx_set_chunk", "orbx_level_count", "orbx_tables", "orbx_level_size", "orbx_pyramid_level",
            "orbx_blurred_level", "orbx_candidates", "orbx_stereo_match", "orbx_stereo_match_batch", "orbm_create",
            "orbm_destroy", "orbm_set_memory_space", "orbm_set_train", "orbm_knn2", "orbm_window_search", "orbm_distance",
+           "orbm_search_by_projection", "orbm_search_stats",
            "orbx_stream", "orbm_stream", "orbx_launch_count", "orbm_launch_count", "orbx_stage_ms", "orbx_set_profiling",
            "orbx_last_error_string", "orbx_version"]
+
+
+class ProjParams(C.Structure):
+    """orbm_proj_params (include/orbx.h)."""
+    _fields_ = [("fx", C.c_float), ("fy", C.c_float), ("cx", C.c_float), ("cy", C.c_float), ("bf", C.c_float),
+                ("minX", C.c_float), ("maxX", C.c_float), ("minY", C.c_float), ("maxY", C.c_float),
+                ("grid_w_inv", C.c_float), ("grid_h_inv", C.c_float), ("nlevels", C.c_int),
+                ("scale", C.c_float * 16), ("Rcw", C.c_float * 9), ("tcw", C.c_float * 3),
+                ("forward", C.c_int), ("backward", C.c_int), ("th", C.c_float), ("th_high", C.c_int),
+                ("check_orientation", C.c_int)]
+
+
+class LastFrameArgs(C.Structure):
+    _fields_ = [("n", C.c_int), ("world_pos", C.c_void_p), ("flags", C.c_void_p), ("octave", C.c_void_p),
+                ("angle", C.c_void_p), ("desc", C.c_void_p)]
+
+
+class CurFrameArgs(C.Structure):
+    _fields_ = [("n", C.c_int), ("keys_un", C.c_void_p), ("u_right", C.c_void_p), ("desc", C.c_void_p),
+                ("taken", C.c_void_p)]
 
 
 def lib():
@@ -63,6 +84,9 @@ def lib():
     L.orbm_knn2.argtypes = [vp, vp, ci, vp, ci, vp, vp, vp]
     L.orbm_window_search.argtypes = [vp, vp, ci, vp, vp, vp, vp, ci, vp, vp, vp, vp]
     L.orbm_distance.argtypes = [vp, vp, vp, ci, vp]
+    L.orbm_search_by_projection.argtypes = [vp, C.POINTER(ProjParams), C.POINTER(LastFrameArgs), C.POINTER(CurFrameArgs),
+                                            vp, vp, vp, C.POINTER(ci)]
+    L.orbm_search_stats.argtypes = [vp, C.POINTER(ci), C.POINTER(C.c_int64)]
     L.orbx_stream.argtypes = [vp, C.POINTER(vp)]
     L.orbm_stream.argtypes = [vp, C.POINTER(vp)]
     L.orbx_launch_count.argtypes = [vp]; L.orbx_launch_count.restype = C.c_int64

@@ -334,8 +334,12 @@ struct orbm_handle {
     int* dOff = nullptr; size_t offCap = 0;
     int* dIdx = nullptr; size_t idxCap = 0;
     uint8_t* dSkip = nullptr; size_t skipCap = 0;
+    uint8_t* dWs = nullptr; size_t wsCap = 0;      // orbm_search_by_projection: staged inputs + grid + outputs
+    uint8_t* dCand = nullptr; size_t candCap = 0;  // candidate (keypoint, distance) lists
+    int* hRes = nullptr;                           // pinned: [0] nmatches, [1] rounds, [2] total candidates
     int smCount = 148;
     int64_t launches = 0;
+    int lastRounds = 0; int64_t lastCandidates = 0;
 };
 
 template <typename T>
@@ -376,7 +380,7 @@ extern "C" int orbm_destroy(orbm_t* m) {
     cudaStreamSynchronize(m->stream);
     if (!m->trainAdopted) cudaFree(m->dTrain);
     cudaFree(m->dQ); cudaFree(m->dB); cudaFree(m->dPartial); cudaFree(m->dI1); cudaFree(m->dI2); cudaFree(m->dD1);
-    cudaFree(m->dD2); cudaFree(m->dOff); cudaFree(m->dIdx); cudaFree(m->dSkip);
+    cudaFree(m->dD2); cudaFree(m->dOff); cudaFree(m->dIdx); cudaFree(m->dSkip); cudaFree(m->dWs); cudaFree(m->dCand); if (m->hRes) cudaFreeHost(m->hRes);
     cudaStreamDestroy(m->stream);
     delete m;
     return ORBX_OK;
@@ -634,5 +638,131 @@ extern "C" int orbx_stereo_match(orbx_t* left, orbx_t* right, int frame, float m
     const int n = A.hCounts[frame];
     std::copy(u.begin() + (size_t)frame * stride, u.begin() + (size_t)frame * stride + n, uRight);
     std::copy(z.begin() + (size_t)frame * stride, z.begin() + (size_t)frame * stride + n, depth);
+    return ORBX_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ windowed search ABI
+#include "orbx_search.cuh"
+
+namespace {
+struct WsCursor {  // bump allocator over the handle's workspace (256-byte aligned pieces)
+    uint8_t* base; size_t off;
+    template <typename T> T* take(size_t count) {
+        T* p = (T*)(base + off);
+        off += (count * sizeof(T) + 255) & ~(size_t)255;
+        return p;
+    }
+};
+}  // namespace
+
+extern "C" int orbm_search_by_projection(orbm_t* m, const orbm_proj_params* p, const orbm_last_frame* last,
+                                         const orbm_cur_frame* cur, int32_t* cur_match, int32_t* last_match,
+                                         uint8_t* last_keep, int* nmatches) {
+    if (!m || !p || !last || !cur || !nmatches) FAIL(ORBX_EINVAL, "null argument");
+    const int nL = last->n, nC = cur->n;
+    if (nL < 0 || nC < 0) FAIL(ORBX_EINVAL, "negative count");
+    if ((nL && (!last->world_pos || !last->flags || !last->octave || !last->angle || !last->desc || !last_match || !last_keep)) ||
+        (nC && (!cur->keys_un || !cur->desc || !cur_match)))
+        FAIL(ORBX_EINVAL, "null array");
+    if (p->nlevels < 1 || p->nlevels > ORBX_MAX_LEVELS) FAIL(ORBX_EINVAL, "nlevels out of range");
+    if (nL > (1 << 20) || nC > (1 << 20)) FAIL(ORBX_EINVAL, "frame too large");
+    *nmatches = 0;
+    CK(cudaSetDevice(m->device));
+    cudaStream_t st = m->stream;
+    const bool hin = m->inSpace == ORBX_MEM_HOST, hout = m->outSpace == ORBX_MEM_HOST;
+    if (nL == 0 || nC == 0) {  // nothing can match: outputs are all "none"
+        if (hout) {
+            for (int i = 0; i < nC; i++) cur_match[i] = -1;
+            for (int i = 0; i < nL; i++) { last_match[i] = -1; last_keep[i] = 0; }
+        } else {
+            if (nC) CK(cudaMemsetAsync(cur_match, 0xFF, (size_t)nC * 4, st));
+            if (nL) { CK(cudaMemsetAsync(last_match, 0xFF, (size_t)nL * 4, st)); CK(cudaMemsetAsync(last_keep, 0, nL, st)); }
+            CK(cudaStreamSynchronize(st));
+        }
+        return ORBX_OK;
+    }
+    // workspace: staged inputs (host mode), grid, per-query state, outputs (host mode)
+    const size_t need = ((size_t)nL * (12 + 1 + 4 + 4 + 32 + 4 + 4 + 4 + 4 + 1) + (size_t)nC * (28 + 4 + 32 + 1 + 4 + 4 + 4) +
+                         (size_t)SP_CELLS * 12 + 64) + 256 * 32;
+    int rc;
+    if ((rc = ensure(m->dWs, m->wsCap, need))) return rc;
+    if (!m->hRes) CK(cudaMallocHost(&m->hRes, 4 * sizeof(int)));
+    WsCursor W{m->dWs, 0};
+    SpDev S;
+    S.p = *p;
+    S.nLast = nL;
+    S.nCur = nC;
+    auto in = [&](const void* src, size_t bytes) -> const void* {  // stage a caller array if it is host memory
+        if (!src) return nullptr;
+        if (!hin) return src;
+        uint8_t* d = W.take<uint8_t>(bytes);
+        cudaMemcpyAsync(d, src, bytes, cudaMemcpyHostToDevice, st);
+        return d;
+    };
+    S.worldPos = (const float*)in(last->world_pos, (size_t)nL * 12);
+    S.lflags = (const uint8_t*)in(last->flags, nL);
+    S.loct = (const int32_t*)in(last->octave, (size_t)nL * 4);
+    S.langle = (const float*)in(last->angle, (size_t)nL * 4);
+    S.ldesc = (const uint4*)in(last->desc, (size_t)nL * 32);
+    S.keys = (const orbx_kp*)in(cur->keys_un, (size_t)nC * sizeof(orbx_kp));
+    S.uRight = (const float*)in(cur->u_right, (size_t)nC * 4);
+    S.cdesc = (const uint4*)in(cur->desc, (size_t)nC * 32);
+    S.taken = (const uint8_t*)in(cur->taken, nC);
+    if ((((uintptr_t)S.ldesc) | ((uintptr_t)S.cdesc)) & 15) FAIL(ORBX_EINVAL, "device descriptor matrices must be 16-byte aligned");
+    int* cellCount = W.take<int>(SP_CELLS);
+    int* cellStart = W.take<int>(SP_CELLS + 1);
+    int* cursor = W.take<int>(SP_CELLS);
+    int* items = W.take<int>(nC);
+    int* candCount = W.take<int>(nL);
+    int* candOff = W.take<int>(nL + 1);
+    int* choice = W.take<int>(nL);
+    int* owner = W.take<int>(nC);
+    int* dRes = W.take<int>(4);
+    int32_t* oCur = hout ? W.take<int32_t>(nC) : cur_match;
+    int32_t* oLast = hout ? W.take<int32_t>(nL) : last_match;
+    uint8_t* oKeep = hout ? W.take<uint8_t>(nL) : last_keep;
+    if (W.off > m->wsCap) FAIL(ORBX_ECUDA, "internal: workspace estimate too small (%zu > %zu)", W.off, m->wsCap);
+
+    // S1 grid
+    CK(cudaMemsetAsync(cellCount, 0, SP_CELLS * sizeof(int), st));
+    k_sp_grid_count<<<(nC + 255) / 256, 256, 0, st>>>(S, cellCount);
+    k_sp_grid_scan<<<1, 1024, 0, st>>>(cellCount, cellStart, cursor);
+    k_sp_grid_fill<<<(nC + 255) / 256, 256, 0, st>>>(S, cursor, items);
+    k_sp_grid_sort<<<(SP_CELLS + 255) / 256, 256, 0, st>>>(cellStart, items);
+    // S2 candidates: count, scan, fill
+    const int qBlocks = (nL + 7) / 8;
+    k_sp_candidates<false><<<qBlocks, 256, 0, st>>>(S, cellStart, items, candCount, nullptr, nullptr, nullptr);
+    k_sp_scan<<<1, 1024, 0, st>>>(candCount, nL, candOff);
+    m->launches += 6;
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(m->hRes + 2, candOff + nL, sizeof(int), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    const size_t total = (size_t)m->hRes[2];
+    if ((rc = ensure(m->dCand, m->candCap, (total + 64) * 6))) return rc;
+    int* candIdx = (int*)m->dCand;
+    unsigned short* candDist = (unsigned short*)(m->dCand + ((total + 63) & ~(size_t)63) * 4);
+    k_sp_candidates<true><<<qBlocks, 256, 0, st>>>(S, cellStart, items, nullptr, candOff, candIdx, candDist);
+    // S3 greedy resolve + rotation filter
+    k_sp_resolve<<<1, 1024, 0, st>>>(S, candOff, candIdx, candDist, choice, owner, oCur, oLast, oKeep, dRes);
+    m->launches += 2;
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(m->hRes, dRes, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
+    if (hout) {
+        CK(cudaMemcpyAsync(cur_match, oCur, (size_t)nC * 4, cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(last_match, oLast, (size_t)nL * 4, cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(last_keep, oKeep, nL, cudaMemcpyDeviceToHost, st));
+    }
+    CK(cudaStreamSynchronize(st));
+    *nmatches = m->hRes[0];
+    m->lastRounds = m->hRes[1];
+    m->lastCandidates = (int64_t)total;
+    return ORBX_OK;
+}
+
+/* Diagnostics of the last orbm_search_by_projection call: fixed-point rounds and candidate pairs evaluated. */
+extern "C" int orbm_search_stats(orbm_t* m, int* rounds, int64_t* candidates) {
+    if (!m) FAIL(ORBX_EINVAL, "null handle");
+    if (rounds) *rounds = m->lastRounds;
+    if (candidates) *candidates = m->lastCandidates;
     return ORBX_OK;
 }

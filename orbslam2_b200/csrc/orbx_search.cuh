@@ -1,0 +1,339 @@
+// orbx_search.cuh — device-resident windowed search (included by orbx_match.cu).
+// Replaces ORBmatcher::SearchByProjection(Frame&, const Frame&, th, bMono), /root/reference/src/ORBmatcher.cc:1324-1466,
+// and the Frame functions it calls on the current frame: AssignFeaturesToGrid / PosInGrid (src/Frame.cc:231-246,
+// 383-393) and GetFeaturesInArea (src/Frame.cc:328-381); rotation histogram + ComputeThreeMaxima (:1597-1638).
+//
+//   S1 k_sp_grid_count / k_sp_grid_fill   keypoints -> 64 x 48 cell lists in keypoint-index order (counting sort:
+//                                          atomics place, a per-cell insertion sort restores the push_back order)
+//   S2 k_sp_candidates<FILL>              one warp per last-frame map point: project, window, walk the cells in the
+//                                          reference's order (ix outer, iy inner, items in insertion order), apply the
+//                                          level / window / stereo gates, Hamming distance per surviving candidate.
+//                                          Run twice: count, (scan), fill — the CSR lists keep the reference's order,
+//                                          which is what breaks distance ties.
+//   S3 k_sp_resolve                        one CTA: the sequential loop's greedy claims ("skip a keypoint that an
+//                                          earlier query already took") as a fixed point: every query picks its best
+//                                          candidate among those not claimed by a lower-index query of the previous
+//                                          round; rounds repeat until nothing changes. By induction on the query index
+//                                          the fixed point is the sequential result (query 0 is right after round 1,
+//                                          query k once 0..k-1 are). Then the rotation histogram, ComputeThreeMaxima,
+//                                          the filter, and the final mvpMapPoints image.
+#pragma once
+
+#define SP_COLS 64  // FRAME_GRID_COLS, include/Frame.h:37
+#define SP_ROWS 48  // FRAME_GRID_ROWS
+#define SP_CELLS (SP_COLS * SP_ROWS)
+#define SP_HISTO 30
+
+struct SpDev {  // device copies of the call's arrays
+    orbm_proj_params p;
+    int nLast, nCur;
+    const float* worldPos; const uint8_t* lflags; const int32_t* loct; const float* langle; const uint4* ldesc;
+    const orbx_kp* keys; const float* uRight; const uint4* cdesc; const uint8_t* taken;
+};
+
+// Frame::PosInGrid (src/Frame.cc:383-393): round() = half away from zero, on the float product
+__device__ __forceinline__ int sp_cell_of(const SpDev& S, int i) {
+    const orbx_kp k = S.keys[i];
+    const int posX = (int)round((double)__fmul_rn(__fsub_rn(k.x, S.p.minX), S.p.grid_w_inv));
+    const int posY = (int)round((double)__fmul_rn(__fsub_rn(k.y, S.p.minY), S.p.grid_h_inv));
+    if (posX < 0 || posX >= SP_COLS || posY < 0 || posY >= SP_ROWS) return -1;
+    return posX * SP_ROWS + posY;
+}
+
+__global__ void k_sp_grid_count(SpDev S, int* __restrict__ cellCount) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= S.nCur) return;
+    const int c = sp_cell_of(S, i);
+    if (c >= 0) atomicAdd(&cellCount[c], 1);
+}
+
+// one CTA: exclusive scan of the 3072 cell counts -> cellStart[0..3072]; fill cursors reset
+__global__ void k_sp_grid_scan(const int* __restrict__ cellCount, int* __restrict__ cellStart, int* __restrict__ cursor) {
+    __shared__ int part[1024];
+    const int tid = threadIdx.x;  // 1024 threads, 3 cells each
+    int c[3], s = 0;
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        c[k] = cellCount[tid * 3 + k];
+        s += c[k];
+    }
+    part[tid] = s;
+    __syncthreads();
+    for (int o = 1; o < 1024; o <<= 1) {
+        const int v = tid >= o ? part[tid - o] : 0;
+        __syncthreads();
+        part[tid] += v;
+        __syncthreads();
+    }
+    int base = part[tid] - s;
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        cellStart[tid * 3 + k] = base;
+        cursor[tid * 3 + k] = base;
+        base += c[k];
+    }
+    if (tid == 1023) cellStart[SP_CELLS] = base;
+}
+
+__global__ void k_sp_grid_fill(SpDev S, int* __restrict__ cursor, int* __restrict__ items) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= S.nCur) return;
+    const int c = sp_cell_of(S, i);
+    if (c >= 0) items[atomicAdd(&cursor[c], 1)] = i;
+}
+
+// thread per cell: restore keypoint-index order inside the cell (cells hold a handful of items)
+__global__ void k_sp_grid_sort(const int* __restrict__ cellStart, int* __restrict__ items) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= SP_CELLS) return;
+    const int s = cellStart[c], e = cellStart[c + 1];
+    for (int a = s + 1; a < e; a++) {
+        const int v = items[a];
+        int b = a - 1;
+        while (b >= s && items[b] > v) {
+            items[b + 1] = items[b];
+            b--;
+        }
+        items[b + 1] = v;
+    }
+}
+
+// Projection of last-frame point i into the current frame and its search window (src/ORBmatcher.cc:1353-1386).
+struct SpQuery {
+    float u, v, invzc, radius;
+    int minLevel, maxLevel;  // GetFeaturesInArea level arguments
+    int x0, x1, y0, y1;      // cell range
+    bool valid;
+};
+
+__device__ __forceinline__ SpQuery sp_query(const SpDev& S, int i) {
+    SpQuery q;
+    q.valid = false;
+    if (!(S.lflags[i] & 1)) return q;
+    const float X = S.worldPos[3 * i], Y = S.worldPos[3 * i + 1], Z = S.worldPos[3 * i + 2];
+    float c3[3];
+#pragma unroll
+    for (int r = 0; r < 3; r++) {  // CV_32F matrix product: double accumulation, one rounding, then + tcw in float
+        const double acc = __dadd_rn(__dadd_rn(__dmul_rn((double)S.p.Rcw[3 * r], (double)X),
+                                               __dmul_rn((double)S.p.Rcw[3 * r + 1], (double)Y)),
+                                     __dmul_rn((double)S.p.Rcw[3 * r + 2], (double)Z));
+        c3[r] = __fadd_rn((float)acc, S.p.tcw[r]);
+    }
+    q.invzc = (float)(1.0 / (double)c3[2]);
+    if (q.invzc < 0) return q;
+    q.u = __fadd_rn(__fmul_rn(__fmul_rn(S.p.fx, c3[0]), q.invzc), S.p.cx);
+    q.v = __fadd_rn(__fmul_rn(__fmul_rn(S.p.fy, c3[1]), q.invzc), S.p.cy);
+    if (q.u < S.p.minX || q.u > S.p.maxX) return q;
+    if (q.v < S.p.minY || q.v > S.p.maxY) return q;
+    const int oct = S.loct[i];
+    q.radius = __fmul_rn(S.p.th, S.p.scale[oct]);
+    if (S.p.forward) { q.minLevel = oct; q.maxLevel = -1; }
+    else if (S.p.backward) { q.minLevel = 0; q.maxLevel = oct; }
+    else { q.minLevel = oct - 1; q.maxLevel = oct + 1; }
+    // Frame::GetFeaturesInArea cell range (src/Frame.cc:333-347)
+    q.x0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(q.u, S.p.minX), q.radius), S.p.grid_w_inv)));
+    if (q.x0 >= SP_COLS) return q;
+    q.x1 = min(SP_COLS - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(q.u, S.p.minX), q.radius), S.p.grid_w_inv)));
+    if (q.x1 < 0) return q;
+    q.y0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(q.v, S.p.minY), q.radius), S.p.grid_h_inv)));
+    if (q.y0 >= SP_ROWS) return q;
+    q.y1 = min(SP_ROWS - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(q.v, S.p.minY), q.radius), S.p.grid_h_inv)));
+    if (q.y1 < 0) return q;
+    q.valid = true;
+    return q;
+}
+
+// One warp per query. FILL = false: candCount[i] = number of candidates. FILL = true: the (keypoint, distance) pairs
+// are written at candOff[i] in the reference's visiting order.
+template <bool FILL>
+__global__ void __launch_bounds__(256) k_sp_candidates(SpDev S, const int* __restrict__ cellStart,
+                                                       const int* __restrict__ items, int* __restrict__ candCount,
+                                                       const int* __restrict__ candOff, int* __restrict__ candIdx,
+                                                       unsigned short* __restrict__ candDist) {
+    const int lane = threadIdx.x & 31;
+    const int i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (i >= S.nLast) return;
+    const SpQuery q = sp_query(S, i);  // uniform across the warp
+    int n = 0;
+    if (q.valid) {
+        const bool bCheckLevels = (q.minLevel > 0) || (q.maxLevel >= 0);
+        uint4 d0, d1;
+        int base = 0;
+        if (FILL) {
+            d0 = S.ldesc[2 * i];
+            d1 = S.ldesc[2 * i + 1];
+            base = candOff[i];
+        }
+        const float ur = __fsub_rn(q.u, __fmul_rn(S.p.bf, q.invzc));
+        for (int ix = q.x0; ix <= q.x1; ix++) {
+            // the cells (ix, y0..y1) are consecutive in the cell index, so their items are one contiguous run that is
+            // already in the reference's order (iy ascending, then insertion order)
+            const int s = cellStart[ix * SP_ROWS + q.y0], e = cellStart[ix * SP_ROWS + q.y1 + 1];
+            for (int b = s; b < e; b += 32) {
+                const int k = b + lane;
+                bool pass = false;
+                int i2 = -1;
+                if (k < e) {
+                    i2 = items[k];
+                    const orbx_kp kp = S.keys[i2];
+                    pass = true;
+                    if (bCheckLevels) {
+                        if (kp.octave < q.minLevel) pass = false;
+                        if (q.maxLevel >= 0 && kp.octave > q.maxLevel) pass = false;
+                    }
+                    const float distx = __fsub_rn(kp.x, q.u), disty = __fsub_rn(kp.y, q.v);
+                    if (!(fabsf(distx) < q.radius && fabsf(disty) < q.radius)) pass = false;
+                    // static part of the skip test at src/ORBmatcher.cc:1399-1401 (points present on entry)
+                    if (S.taken && S.taken[i2]) pass = false;
+                    if (pass && S.uRight) {  // src/ORBmatcher.cc:1403-1409
+                        const float uR = S.uRight[i2];
+                        if (uR > 0) {
+                            const float er = fabsf(__fsub_rn(ur, uR));
+                            if (er > q.radius) pass = false;
+                        }
+                    }
+                }
+                const unsigned m = __ballot_sync(0xffffffffu, pass);
+                if (FILL && pass) {
+                    const int pos = base + n + __popc(m & ((1u << lane) - 1u));
+                    const uint4 c0 = S.cdesc[2 * i2], c1 = S.cdesc[2 * i2 + 1];
+                    candIdx[pos] = i2;
+                    candDist[pos] = (unsigned short)hamming256(d0, d1, c0, c1);
+                }
+                n += __popc(m);
+            }
+        }
+    }
+    if (!FILL && lane == 0) candCount[i] = n;
+}
+
+// single CTA exclusive scan of n counts (n <= 1 << 20): off[0..n], returns total in off[n]
+__global__ void k_sp_scan(const int* __restrict__ cnt, int n, int* __restrict__ off) {
+    __shared__ int part[1024];
+    __shared__ int carry;
+    const int tid = threadIdx.x;
+    if (tid == 0) carry = 0;
+    __syncthreads();
+    for (int base = 0; base < n; base += 1024) {
+        const int i = base + tid;
+        const int v = i < n ? cnt[i] : 0;
+        part[tid] = v;
+        __syncthreads();
+        for (int o = 1; o < 1024; o <<= 1) {
+            const int a = tid >= o ? part[tid - o] : 0;
+            __syncthreads();
+            part[tid] += a;
+            __syncthreads();
+        }
+        if (i < n) off[i] = carry + part[tid] - v;
+        __syncthreads();
+        if (tid == 1023) carry += part[1023];
+        __syncthreads();
+    }
+    if (tid == 0) off[n] = carry;
+}
+
+__global__ void __launch_bounds__(1024) k_sp_resolve(SpDev S, const int* __restrict__ candOff,
+                                                     const int* __restrict__ candIdx,
+                                                     const unsigned short* __restrict__ candDist, int* __restrict__ choice,
+                                                     int* __restrict__ owner, int32_t* __restrict__ curMatch,
+                                                     int32_t* __restrict__ lastMatch, uint8_t* __restrict__ lastKeep,
+                                                     int* __restrict__ result /* [0] nmatches, [1] rounds */) {
+    __shared__ int hist[SP_HISTO];
+    __shared__ int keepBin[SP_HISTO];
+    __shared__ int nKeep;
+    const int tid = threadIdx.x, T = blockDim.x;
+    const int nL = S.nLast, nC = S.nCur;
+    for (int i = tid; i < nL; i += T) choice[i] = -1;
+    int rounds = 0;
+    for (;;) {
+        // owner[i2] = lowest-index query that claimed i2 in the previous round with a point that blocks later queries
+        // (CurrentFrame.mvpMapPoints[i2]->Observations() > 0, src/ORBmatcher.cc:1399-1401)
+        for (int k = tid; k < nC; k += T) owner[k] = 0x7fffffff;
+        __syncthreads();
+        for (int i = tid; i < nL; i += T) {
+            const int c = choice[i];
+            if (c >= 0 && (S.lflags[i] & 2)) atomicMin(&owner[c], i);
+        }
+        __syncthreads();
+        int changed = 0;
+        for (int i = tid; i < nL; i += T) {
+            int best = 256, bi = -1;
+            for (int c = candOff[i], e = candOff[i + 1]; c < e; c++) {
+                const int i2 = candIdx[c];
+                if (owner[i2] < i) continue;  // taken by an earlier query
+                const int d = candDist[c];
+                if (d < best) {  // strict '<': the first candidate in the reference's order wins ties
+                    best = d;
+                    bi = i2;
+                }
+            }
+            const int nc = best <= S.p.th_high ? bi : -1;
+            if (nc != choice[i]) {
+                choice[i] = nc;
+                changed = 1;
+            }
+        }
+        rounds++;
+        if (!__syncthreads_or(changed)) break;
+    }
+    // rotation histogram (src/ORBmatcher.cc:1427-1437) and ComputeThreeMaxima (:1597-1638)
+    if (tid < SP_HISTO) {
+        hist[tid] = 0;
+        keepBin[tid] = 1;
+    }
+    if (tid == 0) nKeep = 0;
+    for (int k = tid; k < nC; k += T) curMatch[k] = -1;
+    __syncthreads();
+    const float factor = 1.0f / SP_HISTO;
+    for (int i = tid; i < nL; i += T) {
+        const int c = choice[i];
+        lastMatch[i] = c;
+        if (c >= 0) {
+            atomicMax(&curMatch[c], i);  // a later claim overwrites an earlier one
+            if (S.p.check_orientation) {
+                float rot = __fsub_rn(S.langle[i], S.keys[c].angle);
+                if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
+                int bin = (int)roundf(__fmul_rn(rot, factor));
+                if (bin == SP_HISTO) bin = 0;
+                atomicAdd(&hist[bin], 1);
+            }
+        }
+    }
+    __syncthreads();
+    if (tid == 0 && S.p.check_orientation) {
+        int max1 = 0, max2 = 0, max3 = 0, ind1 = -1, ind2 = -1, ind3 = -1;
+        for (int i = 0; i < SP_HISTO; i++) {
+            const int s = hist[i];
+            if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = i; }
+            else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = i; }
+            else if (s > max3) { max3 = s; ind3 = i; }
+        }
+        if ((float)max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
+        else if ((float)max3 < 0.1f * (float)max1) { ind3 = -1; }
+        for (int i = 0; i < SP_HISTO; i++) keepBin[i] = (i == ind1 || i == ind2 || i == ind3);
+    }
+    __syncthreads();
+    for (int i = tid; i < nL; i += T) {
+        const int c = choice[i];
+        int keep = 0;
+        if (c >= 0) {
+            keep = 1;
+            if (S.p.check_orientation) {
+                float rot = __fsub_rn(S.langle[i], S.keys[c].angle);
+                if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
+                int bin = (int)roundf(__fmul_rn(rot, factor));
+                if (bin == SP_HISTO) bin = 0;
+                keep = keepBin[bin];
+            }
+            if (keep) atomicAdd(&nKeep, 1);
+            else curMatch[c] = -1;  // mvpMapPoints[i2] = NULL for every entry of a rejected bin
+        }
+        lastKeep[i] = (uint8_t)keep;
+    }
+    __syncthreads();
+    if (tid == 0) {
+        result[0] = nKeep;
+        result[1] = rounds;
+    }
+}

@@ -112,6 +112,52 @@ class ORBmatcher:
                                               si.ctypes.data))
         return bi, bd, sd, si
 
+    def _proj_params(self, cur, last, th, bMono):
+        from .frame import forward_backward
+        P = _lib.ProjParams()
+        P.fx, P.fy, P.cx, P.cy, P.bf = float(cur.fx), float(cur.fy), float(cur.cx), float(cur.cy), float(cur.mbf)
+        P.minX, P.maxX, P.minY, P.maxY = float(cur.mnMinX), float(cur.mnMaxX), float(cur.mnMinY), float(cur.mnMaxY)
+        P.grid_w_inv, P.grid_h_inv = float(cur.mfGridElementWidthInv), float(cur.mfGridElementHeightInv)
+        P.nlevels = len(cur.mvScaleFactors)
+        for i, v in enumerate(cur.mvScaleFactors):
+            P.scale[i] = float(v)
+        for i, v in enumerate(cur.mTcw[:3, :3].reshape(-1)):
+            P.Rcw[i] = float(v)
+        for i, v in enumerate(cur.mTcw[:3, 3]):
+            P.tcw[i] = float(v)
+        fwd, bwd = forward_backward(cur, last, bMono)
+        P.forward, P.backward = int(fwd), int(bwd)
+        P.th, P.th_high, P.check_orientation = float(th), self.TH_HIGH, int(bool(self.mbCheckOrientation))
+        return P
+
+    def SearchByProjection(self, CurrentFrame, LastFrame, th, bMono, taken=None):
+        """ORBmatcher::SearchByProjection(Frame &CurrentFrame, const Frame &LastFrame, th, bMono)
+        (src/ORBmatcher.cc:1324-1466) entirely on the device: grid build, window candidates, Hamming scan, greedy claims
+        in query order, rotation filter. Returns (nmatches, cur_match, last_match, last_keep); cur_match[i2] is the
+        LastFrame index whose map point now sits in CurrentFrame.mvpMapPoints[i2] (-1 = none)."""
+        cur, last = CurrentFrame, LastFrame
+        P = self._proj_params(cur, last, th, bMono)
+        flags = ((last.mp_valid != 0) & (last.mvbOutlier == 0)).astype(np.uint8) | ((last.mp_observed != 0).astype(np.uint8) << 1)
+        keep = {"flags": flags, "oct": np.ascontiguousarray(last.mvKeysUn["octave"], np.int32),
+                "ang": np.ascontiguousarray(last.mvKeysUn["angle"], np.float32),
+                "wp": np.ascontiguousarray(last.mp_world, np.float32), "ld": np.ascontiguousarray(last.mp_desc, np.uint8),
+                "tk": None if taken is None else np.ascontiguousarray(taken, np.uint8)}
+        LA = _lib.LastFrameArgs(last.N, keep["wp"].ctypes.data, keep["flags"].ctypes.data, keep["oct"].ctypes.data,
+                                keep["ang"].ctypes.data, keep["ld"].ctypes.data)
+        CA = _lib.CurFrameArgs(cur.N, cur.mvKeysUn.ctypes.data, None if cur.mvuRight is None else cur.mvuRight.ctypes.data,
+                               cur.mDescriptors.ctypes.data, None if keep["tk"] is None else keep["tk"].ctypes.data)
+        cm = np.zeros(cur.N, np.int32); lm = np.zeros(last.N, np.int32); lk = np.zeros(last.N, np.uint8)
+        n = C.c_int()
+        self._set_space(_lib.MEM_HOST, _lib.MEM_HOST)
+        _lib.check(self._L.orbm_search_by_projection(self._h, C.byref(P), C.byref(LA), C.byref(CA), cm.ctypes.data,
+                                                     lm.ctypes.data, lk.ctypes.data, C.byref(n)))
+        return n.value, cm, lm, lk
+
+    def search_stats(self):
+        r, c = C.c_int(), C.c_int64()
+        _lib.check(self._L.orbm_search_stats(self._h, C.byref(r), C.byref(c)))
+        return r.value, c.value
+
     def cuda_stream(self):
         s = C.c_void_p()
         _lib.check(self._L.orbm_stream(self._h, C.byref(s)))

@@ -79,3 +79,84 @@ def synth_descriptors(n_train, n_query, seed=7, dup=1000, flip_p=0.08, matched_f
     q[:nm] = train[rows] ^ np.packbits(flips, axis=1, bitorder="little")
     perm = rng.permutation(n_query)
     return train, np.ascontiguousarray(q[perm])
+
+
+def synth_tracking_pair(n_points=1200, seed=0, width=640, height=480, stereo=True, motion=(0.05, -0.02, 0.12),
+                        conflicts=150, nlevels=8, scale=1.2):
+    """A (LastFrame, CurrentFrame) pair for ORBmatcher::SearchByProjection(Frame, Frame): random 3-D points seen by two
+    nearby camera poses. Current keypoints = projections + pixel noise + distractors (shuffled, so grid order differs from
+    query order); descriptors = the map point's descriptor with a few bits flipped. `conflicts` last-frame points are
+    near-duplicates of others (same place, similar descriptor) so that several queries compete for one keypoint and
+    the greedy claim order matters; ~15 % of the map points have no observations (temporal points that do not block)."""
+    from .frame import Frame
+    from .extractor import KP_DTYPE
+    rng = np.random.default_rng(seed)
+    fx = fy = np.float32(520.0); cx, cy = np.float32(width / 2 - 0.5), np.float32(height / 2 + 0.25)
+    bf = np.float32(40.0)
+    sf = np.ones(nlevels, np.float32)
+    for i in range(1, nlevels):
+        sf[i] = np.float32(np.float64(sf[i - 1]) * np.float64(np.float32(scale)))
+    # world points in front of the last camera (identity pose)
+    z = rng.uniform(2.0, 12.0, n_points).astype(np.float32)
+    u = rng.uniform(20, width - 20, n_points).astype(np.float32); v = rng.uniform(20, height - 20, n_points).astype(np.float32)
+    X = np.stack([(u - cx) / fx * z, (v - cy) / fy * z, z], 1).astype(np.float32)
+    desc = rng.integers(0, 256, (n_points, 32), dtype=np.uint8)
+    octave = rng.integers(0, nlevels, n_points).astype(np.int32)
+    angle = rng.uniform(0, 360, n_points).astype(np.float32)
+    # near-duplicate map points
+    dup = rng.choice(n_points, conflicts, replace=False)
+    src = rng.choice(np.setdiff1d(np.arange(n_points), dup), conflicts)
+    X[dup] = X[src] + rng.normal(0, 0.002, (conflicts, 3)).astype(np.float32)
+    desc[dup] = desc[src]
+    flip = rng.integers(0, 256, (conflicts, 2))
+    for k, d in enumerate(dup):
+        for b in flip[k]:
+            desc[d, b >> 3] ^= np.uint8(1 << (b & 7))
+    octave[dup] = octave[src]; angle[dup] = angle[src] + rng.normal(0, 2, conflicts).astype(np.float32)
+    angle = np.mod(angle, 360).astype(np.float32)
+
+    def kps(x, y, o, a):
+        k = np.zeros(len(x), KP_DTYPE)
+        k["x"], k["y"], k["octave"], k["angle"] = x, y, o, a
+        k["size"] = 31 * sf[o]; k["class_id"] = -1
+        return k
+
+    last = Frame(kps(u, v, octave, angle), desc, sf, fx, fy, cx, cy, bf, width, height,
+                 u_right=(u - bf / z).astype(np.float32) if stereo else None)
+    last.mp_valid[:] = 1
+    last.mp_valid[rng.random(n_points) < 0.05] = 0
+    last.mvbOutlier[rng.random(n_points) < 0.03] = 1
+    last.mp_observed[:] = (rng.random(n_points) > 0.15).astype(np.uint8)
+    last.mp_world[:] = X
+    last.mp_desc[:] = desc
+    # current pose: small rotation about y + translation
+    th = 0.02
+    R = np.array([[np.cos(th), 0, np.sin(th)], [0, 1, 0], [-np.sin(th), 0, np.cos(th)]], np.float32)
+    T = np.eye(4, dtype=np.float32); T[:3, :3] = R; T[:3, 3] = np.asarray(motion, np.float32)
+    Xc = (R.astype(np.float64) @ X.T.astype(np.float64)).T + np.asarray(motion, np.float64)
+    uc = (fx * Xc[:, 0] / Xc[:, 2] + cx + rng.normal(0, 1.5, n_points)).astype(np.float32)
+    vc = (fy * Xc[:, 1] / Xc[:, 2] + cy + rng.normal(0, 1.5, n_points)).astype(np.float32)
+    keep = np.setdiff1d(np.arange(n_points), dup)              # one keypoint per physical point
+    keep = keep[rng.random(len(keep)) > 0.1]                   # some points are not re-detected
+    nd = n_points // 3                                         # distractors
+    cu = np.concatenate([uc[keep], rng.uniform(0, width, nd).astype(np.float32)])
+    cv = np.concatenate([vc[keep], rng.uniform(0, height, nd).astype(np.float32)])
+    cd = np.concatenate([desc[keep], rng.integers(0, 256, (nd, 32), dtype=np.uint8)])
+    nbits = rng.binomial(256, 0.06, len(keep))
+    for k in range(len(keep)):
+        for b in rng.integers(0, 256, nbits[k]):
+            cd[k, b >> 3] ^= np.uint8(1 << (b & 7))
+    co = np.concatenate([np.clip(octave[keep] + rng.integers(-1, 2, len(keep)), 0, nlevels - 1),
+                         rng.integers(0, nlevels, nd)]).astype(np.int32)
+    ca = np.concatenate([np.mod(angle[keep] + rng.normal(0, 4, len(keep)), 360),
+                         rng.uniform(0, 360, nd)]).astype(np.float32)
+    wild = rng.random(len(keep)) < 0.08                        # matches the rotation-consistency filter must reject
+    ca[:len(keep)][wild] = rng.uniform(0, 360, int(wild.sum())).astype(np.float32)
+    cz = np.concatenate([Xc[keep, 2], rng.uniform(2, 12, nd)])
+    cur_ur = (cu - bf / cz).astype(np.float32)
+    cur_ur[rng.random(len(cu)) < 0.2] = -1                     # keypoints without a stereo match
+    perm = rng.permutation(len(cu))
+    cur = Frame(kps(cu[perm], cv[perm], co[perm], ca[perm]), cd[perm], sf, fx, fy, cx, cy, bf, width, height,
+                u_right=cur_ur[perm] if stereo else None)
+    cur.SetPose(T)
+    return last, cur

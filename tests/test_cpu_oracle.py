@@ -159,3 +159,46 @@ def test_window_search_rules(P):
     skip = np.zeros(12, np.uint8); skip[0] = 1
     bi2, bd2, _, _ = P.window_search(q, off, idx, skip, t)
     assert bi2[1] == -1 and bd2[1] == 256
+
+
+def test_search_by_projection_oracle_micro_cases():
+    """Hand-derived cases pin the oracle's SearchByProjection(Frame, Frame) restatement (the reference ships no test):
+    two map points at the same place compete for one keypoint — the first (with observations) claims it and blocks the
+    second, which falls back to the farther keypoint; without observations the first does not block and is overwritten."""
+    import ctypes as C
+    from oracle_lib import OraclePrims
+    from orbslam2_b200 import _lib
+    from orbslam2_b200.frame import Frame, forward_backward
+    from orbslam2_b200.extractor import KP_DTYPE
+    sf = (np.float32(1.2) ** np.arange(8, dtype=np.float32)).astype(np.float32)
+    kc = np.zeros(2, KP_DTYPE); kc["x"] = (320, 323); kc["y"] = 240
+    dc = np.zeros((2, 32), np.uint8); dc[1, 0] = 0x0F            # keypoint 1 is 4 bits away from the query descriptor
+    cur = Frame(kc, dc, sf, 500, 500, 320, 240, 40, 640, 480)
+    kl = np.zeros(2, KP_DTYPE); kl["x"] = 320; kl["y"] = 240
+    last = Frame(kl, np.zeros((2, 32), np.uint8), sf, 500, 500, 320, 240, 40, 640, 480)
+    last.mp_valid[:] = 1; last.mp_world[:] = (0.0, 0.0, 4.0)
+
+    def params(th):
+        P = _lib.ProjParams()
+        P.fx = P.fy = 500; P.cx, P.cy, P.bf = 320, 240, 40
+        P.minX, P.maxX, P.minY, P.maxY = 0, 640, 0, 480
+        P.grid_w_inv, P.grid_h_inv = 64 / 640, 48 / 480
+        P.nlevels = 8
+        for i in range(8):
+            P.scale[i] = float(sf[i])
+        for i, v in enumerate(np.eye(3, dtype=np.float32).reshape(-1)):
+            P.Rcw[i] = float(v)
+        P.th, P.th_high, P.check_orientation = th, 100, 0
+        return P
+
+    O = OraclePrims()
+    last.mp_observed[:] = 1
+    n, cm, lm, lk = O.search_by_projection(params(7.0), cur, last)
+    assert n == 2 and list(lm) == [0, 1] and list(cm) == [0, 1] and list(lk) == [1, 1]
+    last.mp_observed[:] = 0                                         # no observations: no blocking, the later claim wins
+    n, cm, lm, lk = O.search_by_projection(params(7.0), cur, last)
+    assert n == 2 and list(lm) == [0, 0] and list(cm) == [1, -1]
+    last.mp_observed[:] = 1
+    n, cm, lm, lk = O.search_by_projection(params(2.0), cur, last)  # window 2 px: keypoint 1 (3 px away) is out of reach
+    assert n == 1 and list(lm) == [0, -1] and list(cm) == [0, -1]
+    assert forward_backward(cur, last, True) == (False, False)

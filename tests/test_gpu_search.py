@@ -1,0 +1,83 @@
+"""GPU parity of the device-resident ORBmatcher::SearchByProjection(Frame, Frame) (grid build + GetFeaturesInArea +
+Hamming scan + greedy claims + rotation filter) against the oracle's line-by-line sequential restatement.
+Bit-exact bar: nmatches, the final mvpMapPoints image, every query's claim and its rotation-filter fate."""
+import numpy as np
+import pytest
+
+from oracle_lib import OraclePrims
+from orbslam2_b200.synth import synth_tracking_pair
+
+pytestmark = pytest.mark.gpu
+
+
+def _run(m, P, last, cur, th, bMono, taken=None):
+    prm = m._proj_params(cur, last, th, bMono)
+    got = m.SearchByProjection(cur, last, th, bMono, taken=taken)
+    exp = P.search_by_projection(prm, cur, last, taken=taken)
+    assert got[0] == exp[0], f"nmatches {got[0]} vs {exp[0]}"
+    for g, e, name in zip(got[1:], exp[1:], ("cur_match", "last_match", "last_keep")):
+        assert np.array_equal(g, e), f"{name}: {(g != e).sum()} differ"
+    return got, prm
+
+
+@pytest.mark.parametrize("seed,stereo,th,bMono,motion", [
+    (0, True, 15.0, False, (0.05, -0.02, 0.12)),     # backward (stereo)
+    (1, True, 7.0, False, (0.03, 0.01, -0.15)),      # forward (stereo)
+    (2, True, 15.0, False, (0.02, 0.01, 0.01)),      # neither: octave window [o-1, o+1]
+    (3, False, 15.0, True, (0.05, -0.02, 0.12)),     # monocular
+    (4, False, 30.0, True, (0.08, 0.03, 0.10)),      # the doubled-window retry of TrackWithMotionModel
+])
+def test_search_by_projection_vs_oracle(seed, stereo, th, bMono, motion):
+    import orbslam2_b200 as ob
+    m = ob.ORBmatcher(0.9, True); P = OraclePrims()
+    last, cur = synth_tracking_pair(1500, seed, stereo=stereo, motion=motion)
+    got, prm = _run(m, P, last, cur, th, bMono)
+    assert got[0] > 300, "synthetic pair should track"
+    assert (got[2] >= 0).sum() > got[3].sum(), "the rotation filter should reject something"
+    rounds, cands = m.search_stats()
+    assert rounds >= 2 and cands > 1000, "conflicting claims must exercise the fixed point"
+    if seed == 0:
+        assert (prm.forward, prm.backward) == (0, 1)
+    if seed == 1:
+        assert (prm.forward, prm.backward) == (1, 0)
+    if seed == 2:
+        assert (prm.forward, prm.backward) == (0, 0)
+
+
+def test_taken_mask_no_orientation_and_empty():
+    import orbslam2_b200 as ob
+    P = OraclePrims()
+    last, cur = synth_tracking_pair(900, 7, width=752, height=480)
+    m = ob.ORBmatcher(0.9, False)  # mbCheckOrientation = false
+    taken = (np.random.default_rng(1).random(cur.N) < 0.3).astype(np.uint8)
+    got, _ = _run(m, P, last, cur, 15.0, False, taken=taken)
+    assert not (got[1][taken != 0] >= 0).any(), "keypoints occupied on entry are never claimed"
+    assert np.array_equal(got[3], (got[2] >= 0).astype(np.uint8))
+    # every map point invalid -> no match; empty current frame
+    last.mp_valid[:] = 0
+    got, _ = _run(m, P, last, cur, 15.0, False)
+    assert got[0] == 0 and (got[1] < 0).all()
+
+
+def test_chain_of_claims():
+    """A worst case for the fixed point: K queries with identical descriptors all prefer keypoint 0, then 1, ... —
+    query k must end on keypoint k (K rounds), exactly as the sequential loop."""
+    import orbslam2_b200 as ob
+    from orbslam2_b200.frame import Frame
+    from orbslam2_b200.extractor import KP_DTYPE
+    K = 12
+    sf = np.float32(1.2) ** np.arange(8, dtype=np.float32)
+    kc = np.zeros(K, KP_DTYPE); kc["x"] = 320 + np.arange(K) * 0.5; kc["y"] = 240; kc["octave"] = 0
+    dc = np.zeros((K, 32), np.uint8)
+    for k in range(K):  # keypoint k differs from the query descriptor in k bits -> strictly increasing distance
+        for b in range(k):
+            dc[k, b >> 3] |= np.uint8(1 << (b & 7))
+    cur = Frame(kc, dc, sf, 500, 500, 320, 240, 40, 640, 480)
+    kl = np.zeros(K, KP_DTYPE); kl["x"] = 320; kl["y"] = 240
+    last = Frame(kl, np.zeros((K, 32), np.uint8), sf, 500, 500, 320, 240, 40, 640, 480)
+    last.mp_valid[:] = 1; last.mp_observed[:] = 1
+    last.mp_world[:] = (0.0, 0.0, 5.0)
+    m = ob.ORBmatcher(0.9, False); P = OraclePrims()
+    got, _ = _run(m, P, last, cur, 15.0, True)
+    assert list(got[2]) == list(range(K)) and got[0] == K
+    assert m.search_stats()[0] >= K
