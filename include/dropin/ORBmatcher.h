@@ -5,7 +5,8 @@
 // (src/ORBmatcher.cc:1643-1659) and the "scan candidates -> best / second best with strict '<'" loop that all twelve
 // searches share. The geometric gating around it (projection, frustum, epipolar tests, greedy
 // bookkeeping) stays in the caller, which hands candidate lists in CSR form to ScanCandidates and applies its own
-// accept rule with the helpers below. The per-thread matcher handle makes the class re-entrant like the reference's
+// accept rule with the helpers below — except for SearchByProjection(Frame, Frame), the per-frame tracking search,
+// which runs end to end on the device (grid, windows, scan, greedy claims, rotation filter). The per-thread matcher handle makes the class re-entrant like the reference's
 // stack-allocated ORBmatcher objects (src/Tracking.cc:862, src/LocalMapping.cc:215, src/LoopClosing.cc:275).
 #ifndef ORBX_DROPIN_ORBMATCHER_H
 #define ORBX_DROPIN_ORBMATCHER_H
@@ -82,6 +83,78 @@ public:
         }
         if (max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
         else if (max3 < 0.1f * (float)max1) { ind3 = -1; }
+    }
+
+    // ORBmatcher::SearchByProjection(Frame &CurrentFrame, const Frame &LastFrame, const float th, const bool bMono)
+    // (src/ORBmatcher.cc:1324-1466, called by Tracking::TrackWithMotionModel, src/Tracking.cc:985,991) on the device:
+    // the current frame's grid, GetFeaturesInArea, the Hamming scan, the greedy claims and the rotation filter all run
+    // in orbm_search_by_projection; this wrapper only flattens the Frame / MapPoint objects into arrays and writes the
+    // resulting mvpMapPoints back. FrameT is ORB_SLAM2::Frame (a template so this header needs none of its includes).
+    template <class FrameT>
+    int SearchByProjection(FrameT& CurrentFrame, const FrameT& LastFrame, const float th, const bool bMono) {
+        orbm_proj_params P;
+        P.fx = CurrentFrame.fx; P.fy = CurrentFrame.fy; P.cx = CurrentFrame.cx; P.cy = CurrentFrame.cy;
+        P.bf = CurrentFrame.mbf;
+        P.minX = CurrentFrame.mnMinX; P.maxX = CurrentFrame.mnMaxX; P.minY = CurrentFrame.mnMinY; P.maxY = CurrentFrame.mnMaxY;
+        P.grid_w_inv = CurrentFrame.mfGridElementWidthInv; P.grid_h_inv = CurrentFrame.mfGridElementHeightInv;
+        P.nlevels = (int)CurrentFrame.mvScaleFactors.size();
+        for (int i = 0; i < P.nlevels && i < ORBX_MAX_LEVELS; i++) P.scale[i] = CurrentFrame.mvScaleFactors[i];
+        const cv::Mat& Tcw = CurrentFrame.mTcw;
+        const cv::Mat& Tlw = LastFrame.mTcw;
+        for (int r = 0; r < 3; r++) {
+            for (int c = 0; c < 3; c++) P.Rcw[3 * r + c] = Tcw.template at<float>(r, c);
+            P.tcw[r] = Tcw.template at<float>(r, 3);
+        }
+        // twc = -Rcw.t()*tcw; tlc = Rlw*twc + tlw (src/ORBmatcher.cc:1334-1341; CV_32F products accumulate in double)
+        float twc[3], tlcz;
+        for (int r = 0; r < 3; r++) {
+            double a = 0;
+            for (int k = 0; k < 3; k++) a += (double)(-Tcw.template at<float>(k, r)) * (double)P.tcw[k];
+            twc[r] = (float)a;
+        }
+        {
+            double a = 0;
+            for (int k = 0; k < 3; k++) a += (double)Tlw.template at<float>(2, k) * (double)twc[k];
+            tlcz = (float)a + Tlw.template at<float>(2, 3);
+        }
+        P.forward = (tlcz > CurrentFrame.mb && !bMono) ? 1 : 0;
+        P.backward = (-tlcz > CurrentFrame.mb && !bMono) ? 1 : 0;
+        P.th = th; P.th_high = TH_HIGH; P.check_orientation = mbCheckOrientation ? 1 : 0;
+
+        const int nL = LastFrame.N, nC = CurrentFrame.N;
+        std::vector<float> wp((size_t)nL * 3, 0.f), ang(nL, 0.f);
+        std::vector<uint8_t> flags(nL, 0), ld((size_t)nL * 32, 0), taken(nC, 0);
+        std::vector<int32_t> oct(nL, 0);
+        for (int i = 0; i < nL; i++) {
+            auto* pMP = LastFrame.mvpMapPoints[i];
+            oct[i] = LastFrame.mvKeys[i].octave;
+            ang[i] = LastFrame.mvKeysUn[i].angle;
+            if (!pMP || LastFrame.mvbOutlier[i]) continue;
+            flags[i] = (uint8_t)(1 | (pMP->Observations() > 0 ? 2 : 0));
+            const cv::Mat x3Dw = pMP->GetWorldPos();
+            for (int k = 0; k < 3; k++) wp[3 * i + k] = x3Dw.template at<float>(k, 0);
+            const cv::Mat d = pMP->GetDescriptor();
+            for (int k = 0; k < 32; k++) ld[(size_t)i * 32 + k] = d.ptr()[k];
+        }
+        for (int i = 0; i < nC; i++)
+            if (CurrentFrame.mvpMapPoints[i] && CurrentFrame.mvpMapPoints[i]->Observations() > 0) taken[i] = 1;
+        static_assert(sizeof(cv::KeyPoint) == sizeof(orbx_kp), "cv::KeyPoint layout");
+        orbm_last_frame L = {nL, wp.data(), flags.data(), oct.data(), ang.data(), ld.data()};
+        orbm_cur_frame Cf = {nC, (const orbx_kp*)CurrentFrame.mvKeysUn.data(),
+                             CurrentFrame.mvuRight.empty() ? nullptr : CurrentFrame.mvuRight.data(),
+                             CurrentFrame.mDescriptors.ptr(), taken.data()};
+        std::vector<int32_t> curMatch(nC), lastMatch(nL);
+        std::vector<uint8_t> lastKeep(nL);
+        int nmatches = 0;
+        check(orbm_search_by_projection(tls(), &P, &L, &Cf, curMatch.data(), lastMatch.data(), lastKeep.data(), &nmatches),
+              "orbm_search_by_projection");
+        // write-back: claims first (a later claim overwrites), then the rotation filter's NULLs — cur_match already
+        // holds the net effect per keypoint, except that a filtered claim also clears a pointer that was there on entry
+        for (int i = 0; i < nL; i++)
+            if (lastMatch[i] >= 0 && !lastKeep[i]) CurrentFrame.mvpMapPoints[lastMatch[i]] = nullptr;
+        for (int i2 = 0; i2 < nC; i2++)
+            if (curMatch[i2] >= 0) CurrentFrame.mvpMapPoints[i2] = LastFrame.mvpMapPoints[curMatch[i2]];
+        return nmatches;
     }
 
 protected:

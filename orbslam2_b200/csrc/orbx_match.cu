@@ -336,7 +336,8 @@ struct orbm_handle {
     uint8_t* dSkip = nullptr; size_t skipCap = 0;
     uint8_t* dWs = nullptr; size_t wsCap = 0;      // orbm_search_by_projection: staged inputs + grid + outputs
     uint8_t* dCand = nullptr; size_t candCap = 0;  // candidate (keypoint, distance) lists
-    int* hRes = nullptr;                           // pinned: [0] nmatches, [1] rounds, [2] total candidates
+    int* hRes = nullptr;                           // pinned: [0] nmatches, [2] total candidates
+    int* hFlags = nullptr; size_t hFlagsCap = 0;   // pinned copy of the per-round change flags
     int smCount = 148;
     int64_t launches = 0;
     int lastRounds = 0; int64_t lastCandidates = 0;
@@ -380,7 +381,7 @@ extern "C" int orbm_destroy(orbm_t* m) {
     cudaStreamSynchronize(m->stream);
     if (!m->trainAdopted) cudaFree(m->dTrain);
     cudaFree(m->dQ); cudaFree(m->dB); cudaFree(m->dPartial); cudaFree(m->dI1); cudaFree(m->dI2); cudaFree(m->dD1);
-    cudaFree(m->dD2); cudaFree(m->dOff); cudaFree(m->dIdx); cudaFree(m->dSkip); cudaFree(m->dWs); cudaFree(m->dCand); if (m->hRes) cudaFreeHost(m->hRes);
+    cudaFree(m->dD2); cudaFree(m->dOff); cudaFree(m->dIdx); cudaFree(m->dSkip); cudaFree(m->dWs); cudaFree(m->dCand); if (m->hRes) cudaFreeHost(m->hRes); if (m->hFlags) cudaFreeHost(m->hFlags);
     cudaStreamDestroy(m->stream);
     delete m;
     return ORBX_OK;
@@ -682,11 +683,17 @@ extern "C" int orbm_search_by_projection(orbm_t* m, const orbm_proj_params* p, c
         return ORBX_OK;
     }
     // workspace: staged inputs (host mode), grid, per-query state, outputs (host mode)
-    const size_t need = ((size_t)nL * (12 + 1 + 4 + 4 + 32 + 4 + 4 + 4 + 4 + 1) + (size_t)nC * (28 + 4 + 32 + 1 + 4 + 4 + 4) +
+    const size_t need = ((size_t)nL * (12 + 1 + 4 + 4 + 32 + 4 + 4 + 4 + 4 + 1 + 4) + (size_t)nC * (28 + 4 + 32 + 1 + 4 + 4 + 4) +
                          (size_t)SP_CELLS * 12 + 64) + 256 * 32;
     int rc;
     if ((rc = ensure(m->dWs, m->wsCap, need))) return rc;
     if (!m->hRes) CK(cudaMallocHost(&m->hRes, 4 * sizeof(int)));
+    if (m->hFlagsCap < (size_t)nL + 8) {
+        if (m->hFlags) cudaFreeHost(m->hFlags);
+        m->hFlags = nullptr;
+        CK(cudaMallocHost(&m->hFlags, ((size_t)nL + 8) * sizeof(int)));
+        m->hFlagsCap = (size_t)nL + 8;
+    }
     WsCursor W{m->dWs, 0};
     SpDev S;
     S.p = *p;
@@ -718,6 +725,8 @@ extern "C" int orbm_search_by_projection(orbm_t* m, const orbm_proj_params* p, c
     int* choice = W.take<int>(nL);
     int* owner = W.take<int>(nC);
     int* dRes = W.take<int>(4);
+    const int maxRounds = nL + 8;
+    int* flags = W.take<int>(maxRounds);
     int32_t* oCur = hout ? W.take<int32_t>(nC) : cur_match;
     int32_t* oLast = hout ? W.take<int32_t>(nL) : last_match;
     uint8_t* oKeep = hout ? W.take<uint8_t>(nL) : last_keep;
@@ -742,11 +751,32 @@ extern "C" int orbm_search_by_projection(orbm_t* m, const orbm_proj_params* p, c
     int* candIdx = (int*)m->dCand;
     unsigned short* candDist = (unsigned short*)(m->dCand + ((total + 63) & ~(size_t)63) * 4);
     k_sp_candidates<true><<<qBlocks, 256, 0, st>>>(S, cellStart, items, nullptr, candOff, candIdx, candDist);
-    // S3 greedy resolve + rotation filter
-    k_sp_resolve<<<1, 1024, 0, st>>>(S, candOff, candIdx, candDist, choice, owner, oCur, oLast, oKeep, dRes);
+    // S3 greedy claims as a fixed point: a few rounds are enqueued speculatively (converged rounds return at once),
+    // then the flags are read; more rounds follow only if the last one still changed something
+    CK(cudaMemsetAsync(choice, 0xFF, (size_t)nL * sizeof(int), st));
+    CK(cudaMemsetAsync(flags, 0, (size_t)maxRounds * sizeof(int), st));
+    int round = 0, rounds = 0;
+    for (;;) {
+        const int R = 4;
+        if (round + R > maxRounds) FAIL(ORBX_ECUDA, "internal: greedy resolution did not converge in %d rounds", maxRounds);
+        for (int r = 0; r < R; r++, round++) {
+            CK(cudaMemsetAsync(owner, 0x7F, (size_t)nC * sizeof(int), st));
+            k_sp_claim<<<(nL + 255) / 256, 256, 0, st>>>(S, choice, owner, flags, round);
+            k_sp_choose<<<qBlocks, 256, 0, st>>>(S, candOff, candIdx, candDist, choice, owner, flags, round);
+            m->launches += 2;
+        }
+        CK(cudaGetLastError());
+        CK(cudaMemcpyAsync(m->hFlags, flags, (size_t)round * sizeof(int), cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        rounds = 0;
+        while (rounds < round && m->hFlags[rounds]) rounds++;
+        if (rounds < round) break;  // round `rounds` changed nothing: fixed point reached
+    }
+    rounds++;  // the confirming round
+    k_sp_finish<<<1, 1024, 0, st>>>(S, choice, oCur, oLast, oKeep, dRes);
     m->launches += 2;
     CK(cudaGetLastError());
-    CK(cudaMemcpyAsync(m->hRes, dRes, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(m->hRes, dRes, sizeof(int), cudaMemcpyDeviceToHost, st));
     if (hout) {
         CK(cudaMemcpyAsync(cur_match, oCur, (size_t)nC * 4, cudaMemcpyDeviceToHost, st));
         CK(cudaMemcpyAsync(last_match, oLast, (size_t)nL * 4, cudaMemcpyDeviceToHost, st));
@@ -754,7 +784,7 @@ extern "C" int orbm_search_by_projection(orbm_t* m, const orbm_proj_params* p, c
     }
     CK(cudaStreamSynchronize(st));
     *nmatches = m->hRes[0];
-    m->lastRounds = m->hRes[1];
+    m->lastRounds = rounds;
     m->lastCandidates = (int64_t)total;
     return ORBX_OK;
 }

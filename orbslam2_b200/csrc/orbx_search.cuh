@@ -10,7 +10,7 @@
 //                                          level / window / stereo gates, Hamming distance per surviving candidate.
 //                                          Run twice: count, (scan), fill — the CSR lists keep the reference's order,
 //                                          which is what breaks distance ties.
-//   S3 k_sp_resolve                        one CTA: the sequential loop's greedy claims ("skip a keypoint that an
+//   S3 k_sp_claim / k_sp_choose / k_sp_finish  the sequential loop's greedy claims ("skip a keypoint that an
 //                                          earlier query already took") as a fixed point: every query picks its best
 //                                          candidate among those not claimed by a lower-index query of the previous
 //                                          round; rounds repeat until nothing changes. By induction on the query index
@@ -233,50 +233,56 @@ __global__ void k_sp_scan(const int* __restrict__ cnt, int n, int* __restrict__ 
     if (tid == 0) off[n] = carry;
 }
 
-__global__ void __launch_bounds__(1024) k_sp_resolve(SpDev S, const int* __restrict__ candOff,
-                                                     const int* __restrict__ candIdx,
-                                                     const unsigned short* __restrict__ candDist, int* __restrict__ choice,
-                                                     int* __restrict__ owner, int32_t* __restrict__ curMatch,
-                                                     int32_t* __restrict__ lastMatch, uint8_t* __restrict__ lastKeep,
-                                                     int* __restrict__ result /* [0] nmatches, [1] rounds */) {
+// One round of the fixed point is two grid-wide kernels (the candidate lists of a dense frame are ~100 entries per
+// query, too much for one CTA): k_sp_claim rebuilds owner[] from the previous round's choices, k_sp_choose re-picks.
+// flag[r] = "round r changed something"; the kernels of round r + 1 return at once when flag[r] == 0 (converged), so
+// the host can enqueue a few rounds speculatively and look at the flags once.
+__global__ void k_sp_claim(SpDev S, const int* __restrict__ choice, int* __restrict__ owner, const int* __restrict__ flag,
+                           int round) {
+    if (round > 0 && flag[round - 1] == 0) return;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= S.nLast) return;
+    // owner[i2] = lowest-index query that claimed i2 in the previous round with a point that blocks later queries
+    // (CurrentFrame.mvpMapPoints[i2]->Observations() > 0, src/ORBmatcher.cc:1399-1401)
+    const int c = choice[i];
+    if (c >= 0 && (S.lflags[i] & 2)) atomicMin(&owner[c], i);
+}
+
+__global__ void __launch_bounds__(256) k_sp_choose(SpDev S, const int* __restrict__ candOff, const int* __restrict__ candIdx,
+                                                   const unsigned short* __restrict__ candDist, int* __restrict__ choice,
+                                                   const int* __restrict__ owner, int* __restrict__ flag, int round) {
+    if (round > 0 && flag[round - 1] == 0) return;
+    const int lane = threadIdx.x & 31;
+    const int i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (i >= S.nLast) return;
+    const int s = candOff[i], e = candOff[i + 1];
+    unsigned best = 0xFFFFFFFFu;  // (distance << 22) | position: the minimum is the smallest distance, first in list order
+    for (int c = s + lane; c < e; c += 32) {
+        const int i2 = candIdx[c];
+        if (owner[i2] < i) continue;  // taken by an earlier query
+        const unsigned key = ((unsigned)candDist[c] << 22) | (unsigned)(c - s);
+        best = min(best, key);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, o));
+    if (lane == 0) {
+        int nc = -1;
+        if (best != 0xFFFFFFFFu && (int)(best >> 22) <= S.p.th_high) nc = candIdx[s + (int)(best & 0x3FFFFFu)];
+        if (nc != choice[i]) {
+            choice[i] = nc;
+            flag[round] = 1;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(1024) k_sp_finish(SpDev S, const int* __restrict__ choice, int32_t* __restrict__ curMatch,
+                                                    int32_t* __restrict__ lastMatch, uint8_t* __restrict__ lastKeep,
+                                                    int* __restrict__ result /* [0] nmatches */) {
     __shared__ int hist[SP_HISTO];
     __shared__ int keepBin[SP_HISTO];
     __shared__ int nKeep;
     const int tid = threadIdx.x, T = blockDim.x;
     const int nL = S.nLast, nC = S.nCur;
-    for (int i = tid; i < nL; i += T) choice[i] = -1;
-    int rounds = 0;
-    for (;;) {
-        // owner[i2] = lowest-index query that claimed i2 in the previous round with a point that blocks later queries
-        // (CurrentFrame.mvpMapPoints[i2]->Observations() > 0, src/ORBmatcher.cc:1399-1401)
-        for (int k = tid; k < nC; k += T) owner[k] = 0x7fffffff;
-        __syncthreads();
-        for (int i = tid; i < nL; i += T) {
-            const int c = choice[i];
-            if (c >= 0 && (S.lflags[i] & 2)) atomicMin(&owner[c], i);
-        }
-        __syncthreads();
-        int changed = 0;
-        for (int i = tid; i < nL; i += T) {
-            int best = 256, bi = -1;
-            for (int c = candOff[i], e = candOff[i + 1]; c < e; c++) {
-                const int i2 = candIdx[c];
-                if (owner[i2] < i) continue;  // taken by an earlier query
-                const int d = candDist[c];
-                if (d < best) {  // strict '<': the first candidate in the reference's order wins ties
-                    best = d;
-                    bi = i2;
-                }
-            }
-            const int nc = best <= S.p.th_high ? bi : -1;
-            if (nc != choice[i]) {
-                choice[i] = nc;
-                changed = 1;
-            }
-        }
-        rounds++;
-        if (!__syncthreads_or(changed)) break;
-    }
     // rotation histogram (src/ORBmatcher.cc:1427-1437) and ComputeThreeMaxima (:1597-1638)
     if (tid < SP_HISTO) {
         hist[tid] = 0;
@@ -332,8 +338,5 @@ __global__ void __launch_bounds__(1024) k_sp_resolve(SpDev S, const int* __restr
         lastKeep[i] = (uint8_t)keep;
     }
     __syncthreads();
-    if (tid == 0) {
-        result[0] = nKeep;
-        result[1] = rounds;
-    }
+    if (tid == 0) result[0] = nKeep;
 }

@@ -1,0 +1,44 @@
+#!/usr/bin/env python
+"""Latency of the device-resident ORBmatcher::SearchByProjection(Frame, Frame) (orbm_search_by_projection, host arrays
+in and out, staging copies included) beside the oracle's sequential CPU restatement, on synthetic tracking pairs."""
+import json
+import os
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+import numpy as np  # noqa: E402
+
+
+def main():
+    import orbslam2_b200 as ob
+    from orbslam2_b200.synth import synth_tracking_pair
+    from oracle_lib import OraclePrims
+    P = OraclePrims()
+    m = ob.ORBmatcher(0.9, True)
+    for n, th in ((1000, 15.0), (2000, 15.0), (8000, 15.0)):
+        last, cur = synth_tracking_pair(n, 5, conflicts=n // 8)
+        prm = m._proj_params(cur, last, th, False)
+        for _ in range(3):
+            got = m.SearchByProjection(cur, last, th, False)
+        t0 = time.perf_counter()
+        reps = 20
+        for _ in range(reps):
+            got = m.SearchByProjection(cur, last, th, False)
+        gpu_ms = (time.perf_counter() - t0) / reps * 1e3
+        t0 = time.perf_counter()
+        for _ in range(5):
+            exp = P.search_by_projection(prm, cur, last)
+        cpu_ms = (time.perf_counter() - t0) / 5 * 1e3
+        rounds, cands = m.search_stats()
+        same = got[0] == exp[0] and all(np.array_equal(a, b) for a, b in zip(got[1:], exp[1:]))
+        print(json.dumps({"metric": "search_by_projection_ms_per_frame_pair", "map_points": last.N, "keypoints": cur.N,
+                          "th": th, "gpu_ms_host_call": gpu_ms, "cpu_oracle_ms_1_thread": cpu_ms, "nmatches": got[0],
+                          "candidate_pairs": cands, "fixed_point_rounds": rounds, "identical_to_oracle": bool(same)}))
+
+
+if __name__ == "__main__":
+    main()

@@ -50,3 +50,26 @@ int main(int argc, char** argv) {
     printf("dropin ok: %zu/%zu keypoints, %d ratio-accepted\n", kL.size(), kR.size(), accepted);
     return 0;
 }
+
+// Compile-only instantiation of the device-resident SearchByProjection(Frame, Frame) wrapper against a stand-in with
+// the members of ORB_SLAM2::Frame / MapPoint it reads (include/Frame.h:110-190, include/MapPoint.h:43-80).
+namespace dropin_check {
+struct MapPoint {
+    cv::Mat pos, desc;
+    int nObs = 0;
+    cv::Mat GetWorldPos() { return pos; }
+    cv::Mat GetDescriptor() { return desc; }
+    int Observations() { return nObs; }
+};
+struct Frame {
+    float fx = 0, fy = 0, cx = 0, cy = 0, mbf = 0, mb = 0;
+    float mnMinX = 0, mnMaxX = 0, mnMinY = 0, mnMaxY = 0, mfGridElementWidthInv = 0, mfGridElementHeightInv = 0;
+    int N = 0;
+    cv::Mat mTcw, mDescriptors;
+    std::vector<float> mvScaleFactors, mvuRight;
+    std::vector<cv::KeyPoint> mvKeys, mvKeysUn;
+    std::vector<MapPoint*> mvpMapPoints;
+    std::vector<bool> mvbOutlier;
+};
+int instantiate(ORB_SLAM2::ORBmatcher& m, Frame& cur, const Frame& last) { return m.SearchByProjection(cur, last, 15.f, false); }
+}  // namespace dropin_check
