@@ -157,6 +157,43 @@ public:
         return nmatches;
     }
 
+    // ORBmatcher::SearchByProjection(Frame &F, const std::vector<MapPoint*> &vpMapPoints, const float th = 3)
+    // (src/ORBmatcher.cc:43-127, Tracking::SearchLocalPoints, src/Tracking.cc:1290) on the device.
+    template <class FrameT, class MapPointT>
+    int SearchByProjection(FrameT& F, const std::vector<MapPointT*>& vpMapPoints, const float th = 3) {
+        orbm_proj_params P = orbm_proj_params();
+        P.minX = F.mnMinX; P.maxX = F.mnMaxX; P.minY = F.mnMinY; P.maxY = F.mnMaxY;
+        P.grid_w_inv = F.mfGridElementWidthInv; P.grid_h_inv = F.mfGridElementHeightInv;
+        P.nlevels = (int)F.mvScaleFactors.size();
+        for (int i = 0; i < P.nlevels && i < ORBX_MAX_LEVELS; i++) P.scale[i] = F.mvScaleFactors[i];
+        P.th = th; P.th_high = TH_HIGH;
+        const int n = (int)vpMapPoints.size(), nC = F.N;
+        std::vector<float> px(n, 0.f), py(n, 0.f), pxr(n, 0.f), vc(n, 0.f);
+        std::vector<int32_t> lvl(n, 0);
+        std::vector<uint8_t> flags(n, 0), desc((size_t)n * 32, 0), taken(nC, 0);
+        for (int i = 0; i < n; i++) {
+            MapPointT* pMP = vpMapPoints[i];
+            if (!pMP->mbTrackInView || pMP->isBad()) continue;
+            flags[i] = (uint8_t)(1 | (pMP->Observations() > 0 ? 2 : 0));
+            px[i] = pMP->mTrackProjX; py[i] = pMP->mTrackProjY; pxr[i] = pMP->mTrackProjXR;
+            lvl[i] = pMP->mnTrackScaleLevel; vc[i] = pMP->mTrackViewCos;
+            const cv::Mat d = pMP->GetDescriptor();
+            for (int k = 0; k < 32; k++) desc[(size_t)i * 32 + k] = d.ptr()[k];
+        }
+        for (int i = 0; i < nC; i++)
+            if (F.mvpMapPoints[i] && F.mvpMapPoints[i]->Observations() > 0) taken[i] = 1;
+        orbm_map_points M = {n, px.data(), py.data(), pxr.data(), lvl.data(), vc.data(), flags.data(), desc.data()};
+        orbm_cur_frame Cf = {nC, (const orbx_kp*)F.mvKeysUn.data(), F.mvuRight.empty() ? nullptr : F.mvuRight.data(),
+                             F.mDescriptors.ptr(), taken.data()};
+        std::vector<int32_t> curMatch(nC), mpMatch(n);
+        int nmatches = 0;
+        check(orbm_search_local_points(tls(), &P, mfNNratio, &M, &Cf, curMatch.data(), mpMatch.data(), &nmatches),
+              "orbm_search_local_points");
+        for (int i2 = 0; i2 < nC; i2++)
+            if (curMatch[i2] >= 0) F.mvpMapPoints[i2] = vpMapPoints[curMatch[i2]];
+        return nmatches;
+    }
+
 protected:
     float mfNNratio;
     bool mbCheckOrientation;

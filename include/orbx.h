@@ -170,6 +170,24 @@ typedef struct {              /* CurrentFrame: n keypoints */
 int orbm_search_by_projection(orbm_t* m, const orbm_proj_params* p, const orbm_last_frame* last,
                               const orbm_cur_frame* cur, int32_t* cur_match, int32_t* last_match, uint8_t* last_keep,
                               int* nmatches);
+/* Replaces ORBmatcher::SearchByProjection(Frame &F, const std::vector<MapPoint*> &vpMapPoints, const float th)
+ * (src/ORBmatcher.cc:43-127, called by Tracking::SearchLocalPoints, src/Tracking.cc:1290) on the device, with the same
+ * grid / GetFeaturesInArea kernels. Of `p` the grid constants, scale[], th and th_high are read (no pose: the map
+ * points carry the projection Frame::isInFrustum stored in them, src/Frame.cc:256-326). */
+typedef struct {              /* vpMapPoints: n entries */
+    int n;
+    const float* proj_x;      /* pMP->mTrackProjX */
+    const float* proj_y;      /* pMP->mTrackProjY */
+    const float* proj_xr;     /* pMP->mTrackProjXR */
+    const int32_t* level;     /* pMP->mnTrackScaleLevel */
+    const float* view_cos;    /* pMP->mTrackViewCos */
+    const uint8_t* flags;     /* bit0: pMP->mbTrackInView && !pMP->isBad(); bit1: pMP->Observations() > 0 */
+    const uint8_t* desc;      /* n x 32, pMP->GetDescriptor() */
+} orbm_map_points;
+/* cur_match[idx] (cur->n): index into vpMapPoints of the point now in F.mvpMapPoints[idx], -1 = none;
+ * mp_match[i] (mps->n): keypoint claimed by map point i, -1 = none; nn_ratio = ORBmatcher::mfNNratio. */
+int orbm_search_local_points(orbm_t* m, const orbm_proj_params* p, float nn_ratio, const orbm_map_points* mps,
+                             const orbm_cur_frame* cur, int32_t* cur_match, int32_t* mp_match, int* nmatches);
 /* Diagnostics of the last orbm_search_by_projection call: fixed-point rounds and candidate pairs evaluated. */
 int orbm_search_stats(orbm_t* m, int* rounds, int64_t* candidates);
 

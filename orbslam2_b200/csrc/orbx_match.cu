@@ -656,15 +656,21 @@ struct WsCursor {  // bump allocator over the handle's workspace (256-byte align
 };
 }  // namespace
 
-extern "C" int orbm_search_by_projection(orbm_t* m, const orbm_proj_params* p, const orbm_last_frame* last,
-                                         const orbm_cur_frame* cur, int32_t* cur_match, int32_t* last_match,
-                                         uint8_t* last_keep, int* nmatches) {
-    if (!m || !p || !last || !cur || !nmatches) FAIL(ORBX_EINVAL, "null argument");
+// Queries of either search (mode 0: last-frame map points, mode 1: local map points with their tracking projection).
+struct SpHostQueries {
+    int n;
+    const float* world_pos; const uint8_t* flags; const int32_t* octave; const float* angle; const uint8_t* desc;
+    const float* proj_x; const float* proj_y; const float* proj_xr; const float* view_cos;
+};
+
+static int sp_run(orbm_handle* m, int mode, const orbm_proj_params* p, float nnRatio, const SpHostQueries* last,
+                  const orbm_cur_frame* cur, int32_t* cur_match, int32_t* last_match, uint8_t* last_keep, int* nmatches) {
     const int nL = last->n, nC = cur->n;
     if (nL < 0 || nC < 0) FAIL(ORBX_EINVAL, "negative count");
-    if ((nL && (!last->world_pos || !last->flags || !last->octave || !last->angle || !last->desc || !last_match || !last_keep)) ||
-        (nC && (!cur->keys_un || !cur->desc || !cur_match)))
+    if ((nL && (!last->flags || !last->octave || !last->desc || !last_match)) || (nC && (!cur->keys_un || !cur->desc || !cur_match)))
         FAIL(ORBX_EINVAL, "null array");
+    if (nL && mode == 0 && (!last->world_pos || !last->angle || !last_keep)) FAIL(ORBX_EINVAL, "null array");
+    if (nL && mode == 1 && (!last->proj_x || !last->proj_y || !last->proj_xr || !last->view_cos)) FAIL(ORBX_EINVAL, "null array");
     if (p->nlevels < 1 || p->nlevels > ORBX_MAX_LEVELS) FAIL(ORBX_EINVAL, "nlevels out of range");
     if (nL > (1 << 20) || nC > (1 << 20)) FAIL(ORBX_EINVAL, "frame too large");
     *nmatches = 0;
@@ -674,17 +680,17 @@ extern "C" int orbm_search_by_projection(orbm_t* m, const orbm_proj_params* p, c
     if (nL == 0 || nC == 0) {  // nothing can match: outputs are all "none"
         if (hout) {
             for (int i = 0; i < nC; i++) cur_match[i] = -1;
-            for (int i = 0; i < nL; i++) { last_match[i] = -1; last_keep[i] = 0; }
+            for (int i = 0; i < nL; i++) { last_match[i] = -1; if (last_keep) last_keep[i] = 0; }
         } else {
             if (nC) CK(cudaMemsetAsync(cur_match, 0xFF, (size_t)nC * 4, st));
-            if (nL) { CK(cudaMemsetAsync(last_match, 0xFF, (size_t)nL * 4, st)); CK(cudaMemsetAsync(last_keep, 0, nL, st)); }
+            if (nL) { CK(cudaMemsetAsync(last_match, 0xFF, (size_t)nL * 4, st)); if (last_keep) CK(cudaMemsetAsync(last_keep, 0, nL, st)); }
             CK(cudaStreamSynchronize(st));
         }
         return ORBX_OK;
     }
     // workspace: staged inputs (host mode), grid, per-query state, outputs (host mode)
-    const size_t need = ((size_t)nL * (12 + 1 + 4 + 4 + 32 + 4 + 4 + 4 + 4 + 1 + 4) + (size_t)nC * (28 + 4 + 32 + 1 + 4 + 4 + 4) +
-                         (size_t)SP_CELLS * 12 + 64) + 256 * 32;
+    const size_t need = ((size_t)nL * (12 + 1 + 4 + 4 + 32 + 4 + 4 + 4 + 4 + 1 + 4 + 16) + (size_t)nC * (28 + 4 + 32 + 1 + 4 + 4 + 4) +
+                         (size_t)SP_CELLS * 12 + 64) + 256 * 40;
     int rc;
     if ((rc = ensure(m->dWs, m->wsCap, need))) return rc;
     if (!m->hRes) CK(cudaMallocHost(&m->hRes, 4 * sizeof(int)));
@@ -699,6 +705,8 @@ extern "C" int orbm_search_by_projection(orbm_t* m, const orbm_proj_params* p, c
     S.p = *p;
     S.nLast = nL;
     S.nCur = nC;
+    S.mode = mode;
+    S.nnRatio = nnRatio;
     auto in = [&](const void* src, size_t bytes) -> const void* {  // stage a caller array if it is host memory
         if (!src) return nullptr;
         if (!hin) return src;
@@ -711,6 +719,10 @@ extern "C" int orbm_search_by_projection(orbm_t* m, const orbm_proj_params* p, c
     S.loct = (const int32_t*)in(last->octave, (size_t)nL * 4);
     S.langle = (const float*)in(last->angle, (size_t)nL * 4);
     S.ldesc = (const uint4*)in(last->desc, (size_t)nL * 32);
+    S.projX = (const float*)in(last->proj_x, (size_t)nL * 4);
+    S.projY = (const float*)in(last->proj_y, (size_t)nL * 4);
+    S.projXR = (const float*)in(last->proj_xr, (size_t)nL * 4);
+    S.viewCos = (const float*)in(last->view_cos, (size_t)nL * 4);
     S.keys = (const orbx_kp*)in(cur->keys_un, (size_t)nC * sizeof(orbx_kp));
     S.uRight = (const float*)in(cur->u_right, (size_t)nC * 4);
     S.cdesc = (const uint4*)in(cur->desc, (size_t)nC * 32);
@@ -729,7 +741,7 @@ extern "C" int orbm_search_by_projection(orbm_t* m, const orbm_proj_params* p, c
     int* flags = W.take<int>(maxRounds);
     int32_t* oCur = hout ? W.take<int32_t>(nC) : cur_match;
     int32_t* oLast = hout ? W.take<int32_t>(nL) : last_match;
-    uint8_t* oKeep = hout ? W.take<uint8_t>(nL) : last_keep;
+    uint8_t* oKeep = (hout && last_keep) ? W.take<uint8_t>(nL) : last_keep;
     if (W.off > m->wsCap) FAIL(ORBX_ECUDA, "internal: workspace estimate too small (%zu > %zu)", W.off, m->wsCap);
 
     // S1 grid
@@ -762,7 +774,8 @@ extern "C" int orbm_search_by_projection(orbm_t* m, const orbm_proj_params* p, c
         for (int r = 0; r < R; r++, round++) {
             CK(cudaMemsetAsync(owner, 0x7F, (size_t)nC * sizeof(int), st));
             k_sp_claim<<<(nL + 255) / 256, 256, 0, st>>>(S, choice, owner, flags, round);
-            k_sp_choose<<<qBlocks, 256, 0, st>>>(S, candOff, candIdx, candDist, choice, owner, flags, round);
+            if (mode == 0) k_sp_choose<<<qBlocks, 256, 0, st>>>(S, candOff, candIdx, candDist, choice, owner, flags, round);
+            else k_sp_choose_mp<<<(nL + 255) / 256, 256, 0, st>>>(S, candOff, candIdx, candDist, choice, owner, flags, round);
             m->launches += 2;
         }
         CK(cudaGetLastError());
@@ -773,20 +786,36 @@ extern "C" int orbm_search_by_projection(orbm_t* m, const orbm_proj_params* p, c
         if (rounds < round) break;  // round `rounds` changed nothing: fixed point reached
     }
     rounds++;  // the confirming round
-    k_sp_finish<<<1, 1024, 0, st>>>(S, choice, oCur, oLast, oKeep, dRes);
+    if (mode == 0) k_sp_finish<<<1, 1024, 0, st>>>(S, choice, oCur, oLast, oKeep, dRes);
+    else k_sp_finish_mp<<<1, 1024, 0, st>>>(S, choice, oCur, oLast, dRes);
     m->launches += 2;
     CK(cudaGetLastError());
     CK(cudaMemcpyAsync(m->hRes, dRes, sizeof(int), cudaMemcpyDeviceToHost, st));
     if (hout) {
         CK(cudaMemcpyAsync(cur_match, oCur, (size_t)nC * 4, cudaMemcpyDeviceToHost, st));
         CK(cudaMemcpyAsync(last_match, oLast, (size_t)nL * 4, cudaMemcpyDeviceToHost, st));
-        CK(cudaMemcpyAsync(last_keep, oKeep, nL, cudaMemcpyDeviceToHost, st));
+        if (last_keep) CK(cudaMemcpyAsync(last_keep, oKeep, nL, cudaMemcpyDeviceToHost, st));
     }
     CK(cudaStreamSynchronize(st));
     *nmatches = m->hRes[0];
     m->lastRounds = rounds;
     m->lastCandidates = (int64_t)total;
     return ORBX_OK;
+}
+
+extern "C" int orbm_search_by_projection(orbm_t* m, const orbm_proj_params* p, const orbm_last_frame* last,
+                                         const orbm_cur_frame* cur, int32_t* cur_match, int32_t* last_match,
+                                         uint8_t* last_keep, int* nmatches) {
+    if (!m || !p || !last || !cur || !nmatches) FAIL(ORBX_EINVAL, "null argument");
+    SpHostQueries Q = {last->n, last->world_pos, last->flags, last->octave, last->angle, last->desc, nullptr, nullptr, nullptr, nullptr};
+    return sp_run(m, 0, p, 0.f, &Q, cur, cur_match, last_match, last_keep, nmatches);
+}
+
+extern "C" int orbm_search_local_points(orbm_t* m, const orbm_proj_params* p, float nn_ratio, const orbm_map_points* mps,
+                                        const orbm_cur_frame* cur, int32_t* cur_match, int32_t* mp_match, int* nmatches) {
+    if (!m || !p || !mps || !cur || !nmatches) FAIL(ORBX_EINVAL, "null argument");
+    SpHostQueries Q = {mps->n, nullptr, mps->flags, mps->level, nullptr, mps->desc, mps->proj_x, mps->proj_y, mps->proj_xr, mps->view_cos};
+    return sp_run(m, 1, p, nn_ratio, &Q, cur, cur_match, mp_match, nullptr, nmatches);
 }
 
 /* Diagnostics of the last orbm_search_by_projection call: fixed-point rounds and candidate pairs evaluated. */

@@ -29,6 +29,11 @@ struct SpDev {  // device copies of the call's arrays
     int nLast, nCur;
     const float* worldPos; const uint8_t* lflags; const int32_t* loct; const float* langle; const uint4* ldesc;
     const orbx_kp* keys; const float* uRight; const uint4* cdesc; const uint8_t* taken;
+    // mode 1 = SearchByProjection(Frame&, vector<MapPoint*>, th): the queries come with their tracking projection
+    // (MapPoint::mTrackProjX/Y/XR, mnTrackScaleLevel, mTrackViewCos set by Frame::isInFrustum, src/Frame.cc:256-326)
+    int mode;
+    const float* projX; const float* projY; const float* projXR; const float* viewCos;
+    float nnRatio;
 };
 
 // Frame::PosInGrid (src/Frame.cc:383-393): round() = half away from zero, on the float product
@@ -100,7 +105,7 @@ __global__ void k_sp_grid_sort(const int* __restrict__ cellStart, int* __restric
 
 // Projection of last-frame point i into the current frame and its search window (src/ORBmatcher.cc:1353-1386).
 struct SpQuery {
-    float u, v, invzc, radius;
+    float u, v, invzc, radius, ur;  // ur = expected right-image coordinate for the stereo gate
     int minLevel, maxLevel;  // GetFeaturesInArea level arguments
     int x0, x1, y0, y1;      // cell range
     bool valid;
@@ -110,6 +115,18 @@ __device__ __forceinline__ SpQuery sp_query(const SpDev& S, int i) {
     SpQuery q;
     q.valid = false;
     if (!(S.lflags[i] & 1)) return q;
+    if (S.mode == 1) {  // src/ORBmatcher.cc:58-68
+        const int lvl = S.loct[i];
+        float r = (double)S.viewCos[i] > 0.998 ? 2.5f : 4.0f;  // RadiusByViewingCos, :129-135 (compares in double)
+        if (S.p.th != 1.0f) r = __fmul_rn(r, S.p.th);
+        q.radius = __fmul_rn(r, S.p.scale[lvl]);
+        q.u = S.projX[i];
+        q.v = S.projY[i];
+        q.ur = S.projXR[i];
+        q.invzc = 0.f;
+        q.minLevel = lvl - 1;
+        q.maxLevel = lvl;
+    } else {
     const float X = S.worldPos[3 * i], Y = S.worldPos[3 * i + 1], Z = S.worldPos[3 * i + 2];
     float c3[3];
 #pragma unroll
@@ -130,6 +147,8 @@ __device__ __forceinline__ SpQuery sp_query(const SpDev& S, int i) {
     if (S.p.forward) { q.minLevel = oct; q.maxLevel = -1; }
     else if (S.p.backward) { q.minLevel = 0; q.maxLevel = oct; }
     else { q.minLevel = oct - 1; q.maxLevel = oct + 1; }
+    q.ur = __fsub_rn(q.u, __fmul_rn(S.p.bf, q.invzc));
+    }
     // Frame::GetFeaturesInArea cell range (src/Frame.cc:333-347)
     q.x0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(q.u, S.p.minX), q.radius), S.p.grid_w_inv)));
     if (q.x0 >= SP_COLS) return q;
@@ -164,7 +183,7 @@ __global__ void __launch_bounds__(256) k_sp_candidates(SpDev S, const int* __res
             d1 = S.ldesc[2 * i + 1];
             base = candOff[i];
         }
-        const float ur = __fsub_rn(q.u, __fmul_rn(S.p.bf, q.invzc));
+        const float ur = q.ur;
         for (int ix = q.x0; ix <= q.x1; ix++) {
             // the cells (ix, y0..y1) are consecutive in the cell index, so their items are one contiguous run that is
             // already in the reference's order (iy ascending, then insertion order)
@@ -339,4 +358,62 @@ __global__ void __launch_bounds__(1024) k_sp_finish(SpDev S, const int* __restri
     }
     __syncthreads();
     if (tid == 0) result[0] = nKeep;
+}
+
+// ---- mode 1: ORBmatcher::SearchByProjection(Frame &F, const vector<MapPoint*>&, th), src/ORBmatcher.cc:43-127 --------
+// The accept rule needs the best and the second-best candidate and the pyramid level of each, where "second" follows
+// the reference's update order (a demoted best replaces the current second even on equal distance), so each query
+// replays the reference's scan over its short candidate list sequentially — one thread per query.
+__global__ void __launch_bounds__(256) k_sp_choose_mp(SpDev S, const int* __restrict__ candOff,
+                                                      const int* __restrict__ candIdx,
+                                                      const unsigned short* __restrict__ candDist, int* __restrict__ choice,
+                                                      const int* __restrict__ owner, int* __restrict__ flag, int round) {
+    if (round > 0 && flag[round - 1] == 0) return;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= S.nLast) return;
+    int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1;
+    for (int c = candOff[i], e = candOff[i + 1]; c < e; c++) {
+        const int idx = candIdx[c];
+        if (owner[idx] < i) continue;  // F.mvpMapPoints[idx] was set by an earlier map point with observations
+        const int dist = candDist[c];
+        if (dist < bestDist) {
+            bestDist2 = bestDist;
+            bestDist = dist;
+            bestLevel2 = bestLevel;
+            bestLevel = S.keys[idx].octave;
+            bestIdx = idx;
+        } else if (dist < bestDist2) {
+            bestLevel2 = S.keys[idx].octave;
+            bestDist2 = dist;
+        }
+    }
+    int nc = -1;
+    if (bestDist <= S.p.th_high) {
+        if (!(bestLevel == bestLevel2 && (float)bestDist > __fmul_rn(S.nnRatio, (float)bestDist2))) nc = bestIdx;
+    }
+    if (nc != choice[i]) {
+        choice[i] = nc;
+        flag[round] = 1;
+    }
+}
+
+__global__ void __launch_bounds__(1024) k_sp_finish_mp(SpDev S, const int* __restrict__ choice, int32_t* __restrict__ curMatch,
+                                                       int32_t* __restrict__ mpMatch, int* __restrict__ result) {
+    __shared__ int nAcc;
+    const int tid = threadIdx.x, T = blockDim.x;
+    if (tid == 0) nAcc = 0;
+    for (int k = tid; k < S.nCur; k += T) curMatch[k] = -1;
+    __syncthreads();
+    int mine = 0;
+    for (int i = tid; i < S.nLast; i += T) {
+        const int c = choice[i];
+        mpMatch[i] = c;
+        if (c >= 0) {
+            atomicMax(&curMatch[c], i);  // a later claim overwrites an earlier one
+            mine++;
+        }
+    }
+    if (mine) atomicAdd(&nAcc, mine);
+    __syncthreads();
+    if (tid == 0) result[0] = nAcc;
 }

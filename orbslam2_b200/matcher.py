@@ -153,6 +153,38 @@ class ORBmatcher:
                                                      lm.ctypes.data, lk.ctypes.data, C.byref(n)))
         return n.value, cm, lm, lk
 
+    def SearchLocalPoints(self, F, mps, th=1.0, taken=None):
+        """ORBmatcher::SearchByProjection(Frame &F, const vector<MapPoint*> &vpMapPoints, th) (src/ORBmatcher.cc:43-127)
+        on the device. `mps` is a dict of arrays: proj_x, proj_y, proj_xr, level, view_cos, in_view (mbTrackInView &&
+        !isBad()), observed (Observations() > 0), desc [n,32]. Returns (nmatches, cur_match, mp_match)."""
+        P = _lib.ProjParams()
+        P.minX, P.maxX, P.minY, P.maxY = float(F.mnMinX), float(F.mnMaxX), float(F.mnMinY), float(F.mnMaxY)
+        P.grid_w_inv, P.grid_h_inv = float(F.mfGridElementWidthInv), float(F.mfGridElementHeightInv)
+        P.nlevels = len(F.mvScaleFactors)
+        for i, v in enumerate(F.mvScaleFactors):
+            P.scale[i] = float(v)
+        P.th, P.th_high = float(th), self.TH_HIGH
+        a = self._mp_arrays(mps)
+        tk = None if taken is None else np.ascontiguousarray(taken, np.uint8)
+        MA = _lib.MapPointsArgs(len(a["flags"]), a["px"].ctypes.data, a["py"].ctypes.data, a["pxr"].ctypes.data,
+                                a["lvl"].ctypes.data, a["vc"].ctypes.data, a["flags"].ctypes.data, a["desc"].ctypes.data)
+        CA = _lib.CurFrameArgs(F.N, F.mvKeysUn.ctypes.data, None if F.mvuRight is None else F.mvuRight.ctypes.data,
+                               F.mDescriptors.ctypes.data, None if tk is None else tk.ctypes.data)
+        cm = np.zeros(F.N, np.int32); mm = np.zeros(len(a["flags"]), np.int32)
+        n = C.c_int()
+        self._set_space(_lib.MEM_HOST, _lib.MEM_HOST)
+        _lib.check(self._L.orbm_search_local_points(self._h, C.byref(P), float(self.mfNNratio), C.byref(MA), C.byref(CA),
+                                                    cm.ctypes.data, mm.ctypes.data, C.byref(n)))
+        return n.value, cm, mm, P
+
+    @staticmethod
+    def _mp_arrays(mps):
+        f32 = lambda k: np.ascontiguousarray(mps[k], np.float32)
+        flags = (np.asarray(mps["in_view"]) != 0).astype(np.uint8) | ((np.asarray(mps["observed"]) != 0).astype(np.uint8) << 1)
+        return {"px": f32("proj_x"), "py": f32("proj_y"), "pxr": f32("proj_xr"), "vc": f32("view_cos"),
+                "lvl": np.ascontiguousarray(mps["level"], np.int32), "flags": flags,
+                "desc": np.ascontiguousarray(mps["desc"], np.uint8)}
+
     def search_stats(self):
         r, c = C.c_int(), C.c_int64()
         _lib.check(self._L.orbm_search_stats(self._h, C.byref(r), C.byref(c)))

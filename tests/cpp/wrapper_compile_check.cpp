@@ -57,6 +57,10 @@ namespace dropin_check {
 struct MapPoint {
     cv::Mat pos, desc;
     int nObs = 0;
+    bool mbTrackInView = false;
+    float mTrackProjX = 0, mTrackProjY = 0, mTrackProjXR = 0, mTrackViewCos = 0;
+    int mnTrackScaleLevel = 0;
+    bool isBad() { return false; }
     cv::Mat GetWorldPos() { return pos; }
     cv::Mat GetDescriptor() { return desc; }
     int Observations() { return nObs; }
@@ -72,4 +76,5 @@ struct Frame {
     std::vector<bool> mvbOutlier;
 };
 int instantiate(ORB_SLAM2::ORBmatcher& m, Frame& cur, const Frame& last) { return m.SearchByProjection(cur, last, 15.f, false); }
+int instantiate2(ORB_SLAM2::ORBmatcher& m, Frame& F, const std::vector<MapPoint*>& v) { return m.SearchByProjection(F, v, 3.f); }
 }  // namespace dropin_check

@@ -174,6 +174,23 @@ class OraclePrims:
                                        None if tk is None else _p(tk), _p(cm), _p(lm), _p(lk))
         return n, cm, lm, lk
 
+    def search_local_points(self, P, nn_ratio, F, a, taken=None):
+        """Oracle of ORBmatcher::SearchByProjection(Frame&, vector<MapPoint*>, th); `a` = ORBmatcher._mp_arrays(mps)."""
+        L = self.lib
+        L.orc_search_local_points.restype = C.c_int
+        L.orc_search_local_points.argtypes = [C.c_void_p, C.c_float, C.c_int] + [C.c_void_p] * 7 + [C.c_int] + [C.c_void_p] * 8
+        kx = np.ascontiguousarray(F.mvKeysUn["x"], np.float32); ky = np.ascontiguousarray(F.mvKeysUn["y"], np.float32)
+        koct = np.ascontiguousarray(F.mvKeysUn["octave"], np.int32)
+        ur = None if F.mvuRight is None else np.ascontiguousarray(F.mvuRight, np.float32)
+        tk = None if taken is None else np.ascontiguousarray(taken, np.uint8)
+        n_mp = len(a["flags"])
+        cm = np.zeros(F.N, np.int32); mm = np.zeros(n_mp, np.int32)
+        n = L.orc_search_local_points(C.addressof(P), float(nn_ratio), n_mp, _p(a["px"]), _p(a["py"]), _p(a["pxr"]),
+                                      _p(a["lvl"]), _p(a["vc"]), _p(a["flags"]), _p(a["desc"]), F.N, _p(kx), _p(ky), _p(koct),
+                                      None if ur is None else _p(ur), _p(F.mDescriptors), None if tk is None else _p(tk),
+                                      _p(cm), _p(mm))
+        return n, cm, mm
+
     def resize(self, src, dw, dh):
         src = np.ascontiguousarray(src, np.uint8); out = np.zeros((dh, dw), np.uint8)
         self.lib.orc_resize(_p(src), src.shape[1], src.shape[0], _p(out), dw, dh)

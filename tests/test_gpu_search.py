@@ -81,3 +81,32 @@ def test_chain_of_claims():
     got, _ = _run(m, P, last, cur, 15.0, True)
     assert list(got[2]) == list(range(K)) and got[0] == K
     assert m.search_stats()[0] >= K
+
+
+def _local_points(last, cur, seed):
+    """Local map points for SearchLocalPoints: the pair's map points projected with the current pose (what
+    Frame::isInFrustum stores in each MapPoint), a predicted level and a viewing cosine."""
+    rng = np.random.default_rng(seed)
+    T = cur.mTcw.astype(np.float64)
+    Xc = (T[:3, :3] @ last.mp_world.T.astype(np.float64)).T + T[:3, 3]
+    u = (float(cur.fx) * Xc[:, 0] / Xc[:, 2] + float(cur.cx)).astype(np.float32)
+    v = (float(cur.fy) * Xc[:, 1] / Xc[:, 2] + float(cur.cy)).astype(np.float32)
+    return {"proj_x": u, "proj_y": v, "proj_xr": (u - float(cur.mbf) / Xc[:, 2]).astype(np.float32),
+            "level": np.clip(last.mvKeysUn["octave"] + rng.integers(0, 2, last.N), 0, 7).astype(np.int32),
+            "view_cos": rng.choice(np.array([0.9, 0.998, 0.9995], np.float32), last.N),
+            "in_view": (rng.random(last.N) > 0.1) & (u > 0) & (u < 640) & (v > 0) & (v < 480),
+            "observed": rng.random(last.N) > 0.1, "desc": last.mp_desc}
+
+
+@pytest.mark.parametrize("seed,stereo,th,ratio", [(0, True, 1.0, 0.8), (1, True, 3.0, 0.8), (2, False, 5.0, 0.9), (3, True, 1.0, 0.6)])
+def test_search_local_points_vs_oracle(seed, stereo, th, ratio):
+    import orbslam2_b200 as ob
+    m = ob.ORBmatcher(ratio, True); P = OraclePrims()
+    last, cur = synth_tracking_pair(1500, 10 + seed, stereo=stereo, conflicts=300)
+    mps = _local_points(last, cur, seed)
+    taken = (np.random.default_rng(seed).random(cur.N) < 0.1).astype(np.uint8)
+    n, cm, mm, prm = m.SearchLocalPoints(cur, mps, th, taken=taken)
+    en, ecm, emm = P.search_local_points(prm, m.mfNNratio, cur, m._mp_arrays(mps), taken=taken)
+    assert n == en and np.array_equal(cm, ecm) and np.array_equal(mm, emm)
+    assert n > 200, "local points should be found"
+    assert m.search_stats()[0] >= 2
