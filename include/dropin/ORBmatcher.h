@@ -66,6 +66,21 @@ public:
         if (nq) check(orbm_knn2(tls(), queries.ptr(), nq, train.ptr(), train.rows, i1.data(), d1.data(), d2.data()), "orbm_knn2");
     }
 
+    // Batched MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:242-307): vDescriptors of many map points back to
+    // back (point p owns rows off[p] .. off[p+1]-1, 1x32 CV_8U each, in the reference's iteration order);
+    // bestIdx[p] = the row (relative to off[p]) whose clone becomes pMP->mDescriptor, -1 if the point has no rows.
+    static void ComputeDistinctiveDescriptors(const std::vector<cv::Mat>& vDescriptors, const std::vector<int32_t>& off,
+                                              std::vector<int32_t>& bestIdx) {
+        const int np = (int)off.size() - 1;
+        bestIdx.assign(np > 0 ? np : 0, -1);
+        if (np <= 0) return;
+        std::vector<uint8_t> flat(vDescriptors.size() * 32);
+        for (size_t r = 0; r < vDescriptors.size(); r++)
+            for (int k = 0; k < 32; k++) flat[r * 32 + k] = vDescriptors[r].ptr()[k];
+        check(orbm_distinctive_descriptors(tls(), flat.data(), off.data(), np, bestIdx.data(), nullptr),
+              "orbm_distinctive_descriptors");
+    }
+
     // Accept rules of the reference, evaluated in fp32 like mfNNratio (include/ORBmatcher.h:100).
     bool AcceptRatio(int best, int second, int th) const {  // SearchByFboW(KF,F): src/ORBmatcher.cc:225-229
         return best <= th && (float)best < mfNNratio * (float)second;

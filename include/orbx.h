@@ -188,6 +188,13 @@ typedef struct {              /* vpMapPoints: n entries */
  * mp_match[i] (mps->n): keypoint claimed by map point i, -1 = none; nn_ratio = ORBmatcher::mfNNratio. */
 int orbm_search_local_points(orbm_t* m, const orbm_proj_params* p, float nn_ratio, const orbm_map_points* mps,
                              const orbm_cur_frame* cur, int32_t* cur_match, int32_t* mp_match, int* nmatches);
+/* Batched MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:242-307; called for every new or updated map point by
+ * LocalMapping / Fuse): map point p owns the descriptor rows off[p] .. off[p+1]-1 of `desc` (its observations, in the
+ * reference's iteration order). best_idx[p] = row (relative to off[p]) with the least median distance to the others —
+ * the median is sorted_row[0.5*(N-1)], self distance included; the first such row wins — or -1 for a point without
+ * observations. best_median may be NULL. At most 1024 observations per point. */
+int orbm_distinctive_descriptors(orbm_t* m, const uint8_t* desc, const int32_t* off, int npoints, int32_t* best_idx,
+                                 int32_t* best_median);
 /* Diagnostics of the last orbm_search_by_projection call: fixed-point rounds and candidate pairs evaluated. */
 int orbm_search_stats(orbm_t* m, int* rounds, int64_t* candidates);
 

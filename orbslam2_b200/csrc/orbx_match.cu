@@ -818,6 +818,60 @@ extern "C" int orbm_search_local_points(orbm_t* m, const orbm_proj_params* p, fl
     return sp_run(m, 1, p, nn_ratio, &Q, cur, cur_match, mp_match, nullptr, nmatches);
 }
 
+extern "C" int orbm_distinctive_descriptors(orbm_t* m, const uint8_t* desc, const int32_t* off, int npoints,
+                                            int32_t* best_idx, int32_t* best_median) {
+    if (!m || !off || npoints < 0 || !best_idx) FAIL(ORBX_EINVAL, "bad argument");
+    if (npoints == 0) return ORBX_OK;
+    CK(cudaSetDevice(m->device));
+    cudaStream_t st = m->stream;
+    const bool hin = m->inSpace == ORBX_MEM_HOST, hout = m->outSpace == ORBX_MEM_HOST;
+    // the offsets are needed on the host for the size checks (max observations -> shared memory)
+    std::vector<int32_t> hoff;
+    const int32_t* ho = off;
+    if (!hin) {
+        hoff.resize((size_t)npoints + 1);
+        CK(cudaMemcpyAsync(hoff.data(), off, ((size_t)npoints + 1) * 4, cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        ho = hoff.data();
+    }
+    int maxN = 0;
+    for (int p = 0; p < npoints; p++) {
+        if (ho[p + 1] < ho[p]) FAIL(ORBX_EINVAL, "offsets must be non-decreasing");
+        maxN = std::max(maxN, ho[p + 1] - ho[p]);
+    }
+    if (maxN > DD_MAX_OBS) FAIL(ORBX_ESHAPE, "a map point has %d observations (limit %d)", maxN, DD_MAX_OBS);
+    const size_t total = (size_t)ho[npoints] - (size_t)ho[0];
+    if (total && !desc) FAIL(ORBX_EINVAL, "null descriptors");
+    const size_t need = total * 32 + ((size_t)npoints + 1) * 4 + (size_t)npoints * 8 + 1024;
+    int rc;
+    if ((rc = ensure(m->dWs, m->wsCap, need))) return rc;
+    WsCursor W{m->dWs, 0};
+    const uint4* dDesc = (const uint4*)desc;
+    const int* dOff = off;
+    if (hin) {
+        uint8_t* d = W.take<uint8_t>(std::max<size_t>(total * 32, 16));
+        if (total) CK(cudaMemcpyAsync(d, desc + (size_t)ho[0] * 32, total * 32, cudaMemcpyHostToDevice, st));
+        dDesc = (const uint4*)d - 2 * (size_t)ho[0];  // so that row off[p] is addressed as given
+        int* o = W.take<int>((size_t)npoints + 1);
+        CK(cudaMemcpyAsync(o, off, ((size_t)npoints + 1) * 4, cudaMemcpyHostToDevice, st));
+        dOff = o;
+    } else if ((uintptr_t)desc & 15)
+        FAIL(ORBX_EINVAL, "device descriptor matrix must be 16-byte aligned");
+    int32_t* oIdx = hout ? W.take<int32_t>(npoints) : best_idx;
+    int32_t* oMed = (hout || !best_median) ? W.take<int32_t>(npoints) : best_median;
+    const size_t smem = (size_t)std::max(maxN, 1) * 32;
+    if (smem > 48 * 1024) CK(cudaFuncSetAttribute(k_distinctive, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_distinctive<<<npoints, DD_THREADS, smem, st>>>(dDesc, dOff, npoints, oIdx, oMed);
+    m->launches++;
+    CK(cudaGetLastError());
+    if (hout) {
+        CK(cudaMemcpyAsync(best_idx, oIdx, (size_t)npoints * 4, cudaMemcpyDeviceToHost, st));
+        if (best_median) CK(cudaMemcpyAsync(best_median, oMed, (size_t)npoints * 4, cudaMemcpyDeviceToHost, st));
+    }
+    CK(cudaStreamSynchronize(st));
+    return ORBX_OK;
+}
+
 /* Diagnostics of the last orbm_search_by_projection call: fixed-point rounds and candidate pairs evaluated. */
 extern "C" int orbm_search_stats(orbm_t* m, int* rounds, int64_t* candidates) {
     if (!m) FAIL(ORBX_EINVAL, "null handle");

@@ -417,3 +417,53 @@ __global__ void __launch_bounds__(1024) k_sp_finish_mp(SpDev S, const int* __res
     __syncthreads();
     if (tid == 0) result[0] = nAcc;
 }
+
+// ---- batched MapPoint::ComputeDistinctiveDescriptors, /root/reference/src/MapPoint.cc:242-307 -------------------------
+// Per map point: all-pairs Hamming distances of its observations' descriptors, per row the median
+// vDists[0.5*(N-1)] of the sorted row (self distance 0 included), result = first row with the least median.
+// One CTA per map point; its descriptors sit in shared memory; a thread owns a row and finds the k-th smallest
+// distance by bisection on the value (distances are 0..256: 9 counting passes over broadcast reads, no sort, no N x N
+// matrix).
+#define DD_THREADS 64
+#define DD_MAX_OBS 1024
+
+__global__ void __launch_bounds__(DD_THREADS) k_distinctive(const uint4* __restrict__ desc, const int* __restrict__ off,
+                                                            int npoints, int32_t* __restrict__ bestIdx,
+                                                            int32_t* __restrict__ bestMedian) {
+    extern __shared__ uint4 dd_rows[];  // 2 x N
+    __shared__ unsigned red[DD_THREADS / 32];
+    const int p = blockIdx.x, tid = threadIdx.x;
+    const int s = off[p], N = off[p + 1] - s;
+    if (N <= 0) {
+        if (tid == 0) {
+            bestIdx[p] = -1;
+            bestMedian[p] = 0x7fffffff;
+        }
+        return;
+    }
+    for (int i = tid; i < 2 * N; i += DD_THREADS) dd_rows[i] = desc[2 * (size_t)s + i];
+    __syncthreads();
+    const int k = (int)(0.5 * (N - 1));  // index into the sorted row, as the reference computes it
+    unsigned best = 0xFFFFFFFFu;         // (median << 16) | row: the minimum is the least median, first row on ties
+    for (int i = tid; i < N; i += DD_THREADS) {
+        const uint4 a0 = dd_rows[2 * i], a1 = dd_rows[2 * i + 1];
+        int lo = 0, hi = 256;  // smallest v with #{j : d(i,j) <= v} >= k + 1
+        while (lo < hi) {
+            const int mid = (lo + hi) >> 1;
+            int cnt = 0;
+            for (int j = 0; j < N; j++) cnt += hamming256(a0, a1, dd_rows[2 * j], dd_rows[2 * j + 1]) <= mid;
+            if (cnt >= k + 1) hi = mid;
+            else lo = mid + 1;
+        }
+        best = min(best, ((unsigned)lo << 16) | (unsigned)i);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, o));
+    if ((tid & 31) == 0) red[tid >> 5] = best;
+    __syncthreads();
+    if (tid == 0) {
+        for (int w = 1; w < DD_THREADS / 32; w++) best = min(best, red[w]);
+        bestIdx[p] = (int)(best & 0xFFFFu);
+        bestMedian[p] = (int)(best >> 16);
+    }
+}

@@ -185,6 +185,17 @@ class ORBmatcher:
                 "lvl": np.ascontiguousarray(mps["level"], np.int32), "flags": flags,
                 "desc": np.ascontiguousarray(mps["desc"], np.uint8)}
 
+    def ComputeDistinctiveDescriptors(self, desc, off):
+        """Batched MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:242-307): map point p owns descriptor rows
+        off[p]:off[p+1]. Returns (best_idx, best_median) per point (best_idx = -1 without observations)."""
+        desc = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32); off = np.ascontiguousarray(off, np.int32)
+        n = len(off) - 1
+        bi = np.zeros(n, np.int32); bm = np.zeros(n, np.int32)
+        self._set_space(_lib.MEM_HOST, _lib.MEM_HOST)
+        _lib.check(self._L.orbm_distinctive_descriptors(self._h, desc.ctypes.data if desc.size else None, off.ctypes.data, n,
+                                                        bi.ctypes.data, bm.ctypes.data))
+        return bi, bm
+
     def search_stats(self):
         r, c = C.c_int(), C.c_int64()
         _lib.check(self._L.orbm_search_stats(self._h, C.byref(r), C.byref(c)))

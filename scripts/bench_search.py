@@ -39,6 +39,23 @@ def main():
                           "th": th, "gpu_ms_host_call": gpu_ms, "cpu_oracle_ms_1_thread": cpu_ms, "nmatches": got[0],
                           "candidate_pairs": cands, "fixed_point_rounds": rounds, "identical_to_oracle": bool(same)}))
 
+    # batched MapPoint::ComputeDistinctiveDescriptors: 20 000 map points with 3..40 observations
+    rng = np.random.default_rng(1)
+    counts = rng.integers(3, 41, 20000).astype(np.int32)
+    off = np.zeros(len(counts) + 1, np.int32); off[1:] = np.cumsum(counts)
+    desc = rng.integers(0, 256, (off[-1], 32), dtype=np.uint8)
+    m.ComputeDistinctiveDescriptors(desc, off)
+    t0 = time.perf_counter()
+    for _ in range(5):
+        bi, bm = m.ComputeDistinctiveDescriptors(desc, off)
+    gpu_ms = (time.perf_counter() - t0) / 5 * 1e3
+    t0 = time.perf_counter()
+    ei, em = P.distinctive_descriptors(desc, off)
+    cpu_ms = (time.perf_counter() - t0) * 1e3
+    print(json.dumps({"metric": "distinctive_descriptors_ms_per_20000_map_points", "observations": int(off[-1]),
+                      "gpu_ms_host_call": gpu_ms, "cpu_oracle_ms_1_thread": cpu_ms,
+                      "identical_to_oracle": bool(np.array_equal(bi, ei) and np.array_equal(bm, em))}))
+
 
 if __name__ == "__main__":
     main()

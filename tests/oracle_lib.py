@@ -191,6 +191,14 @@ class OraclePrims:
                                       _p(cm), _p(mm))
         return n, cm, mm
 
+    def distinctive_descriptors(self, desc, off):
+        desc = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32); off = np.ascontiguousarray(off, np.int32)
+        n = len(off) - 1
+        bi = np.zeros(n, np.int32); bm = np.zeros(n, np.int32)
+        self.lib.orc_distinctive_descriptors.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
+        self.lib.orc_distinctive_descriptors(_p(desc) if desc.size else None, _p(off), n, _p(bi), _p(bm))
+        return bi, bm
+
     def resize(self, src, dw, dh):
         src = np.ascontiguousarray(src, np.uint8); out = np.zeros((dh, dw), np.uint8)
         self.lib.orc_resize(_p(src), src.shape[1], src.shape[0], _p(out), dw, dh)

@@ -202,3 +202,13 @@ def test_search_by_projection_oracle_micro_cases():
     n, cm, lm, lk = O.search_by_projection(params(2.0), cur, last)  # window 2 px: keypoint 1 (3 px away) is out of reach
     assert n == 1 and list(lm) == [0, -1] and list(cm) == [0, -1]
     assert forward_backward(cur, last, True) == (False, False)
+
+
+def test_distinctive_descriptors_oracle_micro_case():
+    """Three views: rows 0 and 1 identical, row 2 eight bits away. Sorted rows: [0,0,8], [0,0,8], [0,8,8]; the median is
+    element int(0.5*(3-1)) = 1 -> medians 0, 0, 8 -> the first row wins. Two views: k = int(0.5) = 0 -> every median is the
+    self distance 0 -> row 0."""
+    from oracle_lib import OraclePrims
+    d = np.zeros((5, 32), np.uint8); d[2, 0] = 0xFF; d[4, :] = 0xFF
+    bi, bm = OraclePrims().distinctive_descriptors(d, np.array([0, 3, 5, 5], np.int32))
+    assert list(bi) == [0, 0, -1] and list(bm[:2]) == [0, 0]

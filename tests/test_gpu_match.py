@@ -82,3 +82,24 @@ def test_window_search_vs_oracle(ob):
         exp = P.window_search(q, off, idx, sk, t)
         for g, e, name in zip(got, exp, ("best_idx", "best_d", "second_d", "second_idx")):
             assert np.array_equal(g, e), name
+
+
+def test_distinctive_descriptors_vs_oracle(ob):
+    """Batched MapPoint::ComputeDistinctiveDescriptors: ragged observation counts (0, 1, 2, even/odd, large), ties."""
+    m = ob.ORBmatcher(); P = OraclePrims()
+    rng = np.random.default_rng(4)
+    counts = np.concatenate([[0, 1, 2, 3, 4, 300, 0, 65], rng.integers(1, 40, 2000)]).astype(np.int32)
+    off = np.zeros(len(counts) + 1, np.int32); off[1:] = np.cumsum(counts)
+    desc = np.zeros((off[-1], 32), np.uint8)
+    for p in range(len(counts)):  # observations of one point: a common descriptor with a few bits flipped per view
+        base = rng.integers(0, 256, 32, dtype=np.uint8)
+        for r in range(off[p], off[p + 1]):
+            d = base.copy()
+            for b in rng.integers(0, 256, rng.integers(0, 30)):
+                d[b >> 3] ^= np.uint8(1 << (b & 7))
+            desc[r] = d
+    desc[off[8]:off[9]] = desc[off[8]]  # a point whose views are all identical: every median ties, first row wins
+    bi, bm = m.ComputeDistinctiveDescriptors(desc, off)
+    ei, em = P.distinctive_descriptors(desc, off)
+    assert np.array_equal(bi, ei) and np.array_equal(bm[counts > 0], em[counts > 0])
+    assert bi[0] == -1 and bi[1] == 0 and bi[8] == 0
