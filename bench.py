@@ -398,12 +398,18 @@ def run_ours(args):
 
     # what the host link alone sustains with every rank copying at once (explains e2e at N > 1: the ranks share the
     # host's PCIe / memory fabric, so per-GPU copy bandwidth drops as N grows while the kernels scale linearly)
-    def copy_only():
-        d_imgs.copy_(host, non_blocking=True)
-        return None
-    with torch.cuda.stream(stream):
-        t_copy, _, _ = timed(copy_only, 10, 2)
-    h2d_gbs = B * W * H * 10 / max_over_ranks(t_copy) / 1e9
+    cs = torch.cuda.Stream(device=dev)  # a torch-owned stream: the pinned-memory allocator keeps events on it
+    with torch.cuda.stream(cs):
+        for _ in range(2):
+            d_imgs.copy_(host, non_blocking=True)
+        barrier()
+        c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        c0.record(cs)
+        for _ in range(10):
+            d_imgs.copy_(host, non_blocking=True)
+        c1.record(cs)
+        barrier()
+    h2d_gbs = B * W * H * 10 / max_over_ranks(c0.elapsed_time(c1) * 1e-3) / 1e9
     h2d = B * W * H
     d2h = B * cap * (28 + 32) + B * 4 + 4
 
