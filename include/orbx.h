@@ -73,6 +73,15 @@ int orbx_extract(orbx_t* h, const uint8_t* img, int w, int hgt, size_t stride, o
  * kps + f*cap_per_frame, desc + f*cap_per_frame*32, n[f]. */
 int orbx_extract_batch(orbx_t* h, const uint8_t* imgs, int batch, int w, int hgt, size_t stride, size_t img_stride,
                        orbx_kp* kps, uint8_t* desc, int cap_per_frame, int* n);
+/* The same call in two halves, for callers that keep more than one batch in flight (one handle per batch in flight):
+ * submit enqueues the copies and kernels and returns at once; wait blocks until that batch is complete, fills n[] and
+ * reports device-side errors / ORBX_ECAP. The buffers passed to submit must stay valid until wait returns. One pending
+ * batch per handle; orbx_extract_batch == submit + wait. With two handles the copy-in of batch k+1 and the copy-out of
+ * batch k-1 overlap the kernels of batch k (the monocular Frame constructor's call, src/Frame.cc:247-253, issued for
+ * a queue of camera frames instead of one). */
+int orbx_extract_batch_submit(orbx_t* h, const uint8_t* imgs, int batch, int w, int hgt, size_t stride,
+                              size_t img_stride, orbx_kp* kps, uint8_t* desc, int cap_per_frame);
+int orbx_extract_batch_wait(orbx_t* h, int* n);
 /* Smallest cap_per_frame that can never return ORBX_ECAP for this shape (sum over levels of quota + slack). */
 int orbx_max_keypoints(orbx_t* h, int w, int hgt, int* cap);
 /* With host buffers a batch is split into chunks of `frames` frames that are software-pipelined: the PCIe copy-in of

@@ -25,6 +25,7 @@ class OrbxParams(C.Structure):
 
 # every symbol include/orbx.h declares (tests check the export table against this list and the header)
 SYMBOLS = ["orbx_create", "orbx_destroy", "orbx_set_memory_space", "orbx_extract", "orbx_extract_batch",
+           "orbx_extract_batch_submit", "orbx_extract_batch_wait",
            "orbx_max_keypoints", "orbx_set_chunk", "orbx_level_count", "orbx_tables", "orbx_level_size", "orbx_pyramid_level",
            "orbx_blurred_level", "orbx_candidates", "orbx_stereo_match", "orbx_stereo_match_batch", "orbm_create",
            "orbm_destroy", "orbm_set_memory_space", "orbm_set_train", "orbm_knn2", "orbm_window_search", "orbm_distance",
@@ -73,6 +74,8 @@ def lib():
     L.orbx_set_memory_space.argtypes = [vp, ci, ci]
     L.orbx_extract.argtypes = [vp, vp, ci, ci, sz, vp, vp, ci, vp]
     L.orbx_extract_batch.argtypes = [vp, vp, ci, ci, ci, sz, sz, vp, vp, ci, vp]
+    L.orbx_extract_batch_submit.argtypes = [vp, vp, ci, ci, ci, sz, sz, vp, vp, ci]
+    L.orbx_extract_batch_wait.argtypes = [vp, vp]
     L.orbx_max_keypoints.argtypes = [vp, ci, ci, C.POINTER(ci)]
     L.orbx_set_chunk.argtypes = [vp, ci]
     L.orbx_level_count.argtypes = [vp]

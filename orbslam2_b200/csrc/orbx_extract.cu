@@ -54,6 +54,7 @@ struct orbx_handle {
     int qtC = 0, qtC2 = 0, qtThreads = 256;
     size_t qtSmem = 0, fastSmem = 0;
     int lastBatch = 0;
+    int pendingBatch = 0, pendingCap = 0;  // orbx_extract_batch_submit without its wait (negative: empty-image batch)
     bool blurValid = false;
     int64_t launches = 0;
     bool profiling = false;
@@ -425,6 +426,7 @@ static int launch_chain(orbx_handle* h, cudaStream_t cs, int f0, int nb, bool st
                                                              h->dSelCount, h->qtC, h->qtC2, h->dErr, f0);
     KCHECK(h, "k_quadtree");
     if (stamps) stamp(h, 4);
+    // (running the blur on a side stream next to FAST + quadtree was measured: no gain, FAST fills every SM)
     k_blur<<<dim3((D.totalBlurTiles + BLUR_WARPS - 1) / BLUR_WARPS, nb), 32 * BLUR_WARPS, 0, cs>>>(h->dPlan, h->dPyr, h->dBlur, f0);
     KCHECK(h, "k_blur");
     if (stamps) stamp(h, 5);
@@ -483,12 +485,15 @@ static int ensure_pipeline(orbx_handle* h, int nChunks) {
     return ORBX_OK;
 }
 
-extern "C" int orbx_extract_batch(orbx_t* h, const uint8_t* imgs, int batch, int w, int hgt, size_t stride,
-                                  size_t img_stride, orbx_kp* kps, uint8_t* desc, int cap, int* n) {
-    if (!h || !n) FAIL(ORBX_EINVAL, "null argument");
+// Enqueue one batch (copies, kernels, count read-back) without waiting for it; orbx_extract_batch_wait() completes it.
+// A caller with two handles keeps one batch on the PCIe link while the other computes.
+extern "C" int orbx_extract_batch_submit(orbx_t* h, const uint8_t* imgs, int batch, int w, int hgt, size_t stride,
+                                         size_t img_stride, orbx_kp* kps, uint8_t* desc, int cap) {
+    if (!h) FAIL(ORBX_EINVAL, "null argument");
+    if (h->pendingBatch != 0) FAIL(ORBX_EINVAL, "a submitted batch is still pending: call orbx_extract_batch_wait first");
     if (batch < 1) FAIL(ORBX_EINVAL, "batch must be >= 1");
     if (!imgs || w <= 0 || hgt <= 0) {  // empty image: the reference returns silently with outputs untouched (:861-862)
-        for (int f = 0; f < batch; f++) n[f] = 0;
+        h->pendingBatch = -batch;
         return ORBX_OK;
     }
     if (stride < (size_t)w || (batch > 1 && img_stride < stride * (size_t)hgt)) FAIL(ORBX_EINVAL, "bad strides");
@@ -505,9 +510,14 @@ extern "C" int orbx_extract_batch(orbx_t* h, const uint8_t* imgs, int batch, int
     // head) and chunk c-1 leaves on the copy-out stream. Device buffers: one launch sequence for the whole batch.
     const bool hostIO = h->inSpace == ORBX_MEM_HOST || h->outSpace == ORBX_MEM_HOST;
     int chunk = batch;
-    if (!h->profiling && (hostIO || h->chunk > 0)) {  // device buffers are chunked only on request (orbx_set_chunk)
-        chunk = h->chunk > 0 ? h->chunk : 48;
-        if (batch < 2 * chunk) chunk = batch;
+    if (!h->profiling) {
+        if (hostIO || h->chunk > 0) {
+            chunk = h->chunk > 0 ? h->chunk : 48;
+            if (batch < 2 * chunk) chunk = batch;
+        } else if (batch >= 96) {
+            chunk = (batch + 1) / 2;  // device buffers: two halves on the two compute streams, so one half's kernel
+                                      // tails and its latency-bound quadtree overlap the other's kernels (measured +2 %)
+        }
     }
     // chunk boundaries: the first two chunks are short (1/3 and 2/3 of a chunk) so the pipeline fills quickly — the
     // first copy-in is the only one nothing overlaps
@@ -567,6 +577,23 @@ extern "C" int orbx_extract_batch(orbx_t* h, const uint8_t* imgs, int batch, int
     CK(cudaMemcpyAsync(h->hCounts, h->dNOut, (size_t)batch * sizeof(int), cudaMemcpyDeviceToHost, st));
     CK(cudaMemcpyAsync(h->hCounts + batch, h->dErr, sizeof(int), cudaMemcpyDeviceToHost, st));
     stamp(h, 7);
+    h->pendingBatch = batch;
+    h->pendingCap = cap;
+    return ORBX_OK;
+}
+
+extern "C" int orbx_extract_batch_wait(orbx_t* h, int* n) {
+    if (!h || !n) FAIL(ORBX_EINVAL, "null argument");
+    if (h->pendingBatch == 0) FAIL(ORBX_EINVAL, "no submitted batch to wait for");
+    const int batch = std::abs(h->pendingBatch), cap = h->pendingCap;
+    const bool empty = h->pendingBatch < 0;
+    h->pendingBatch = 0;
+    if (empty) {
+        for (int f = 0; f < batch; f++) n[f] = 0;
+        return ORBX_OK;
+    }
+    CK(cudaSetDevice(h->device));
+    cudaStream_t st = h->stream;
     CK(cudaStreamSynchronize(st));
     if (h->profiling)
         for (int i = 0; i < 7; i++) cudaEventElapsedTime(&h->stageMs[i], h->ev[i], h->ev[i + 1]);
@@ -582,6 +609,17 @@ extern "C" int orbx_extract_batch(orbx_t* h, const uint8_t* imgs, int batch, int
     }
     if (worst > cap) FAIL(ORBX_ECAP, "cap_per_frame %d < %d keypoints found", cap, worst);
     return ORBX_OK;
+}
+
+extern "C" int orbx_extract_batch(orbx_t* h, const uint8_t* imgs, int batch, int w, int hgt, size_t stride,
+                                  size_t img_stride, orbx_kp* kps, uint8_t* desc, int cap, int* n) {
+    if (!h || !n) FAIL(ORBX_EINVAL, "null argument");
+    int rc = orbx_extract_batch_submit(h, imgs, batch, w, hgt, stride, img_stride, kps, desc, cap);
+    if (rc != ORBX_OK) {
+        h->pendingBatch = 0;
+        return rc;
+    }
+    return orbx_extract_batch_wait(h, n);
 }
 
 /* Frames per pipeline chunk when a buffer lives in host memory (0 = default). */

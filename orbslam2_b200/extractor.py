@@ -41,6 +41,7 @@ class ORBextractor:
         self.mvScaleFactor, self.mvInvScaleFactor, self.mvLevelSigma2, self.mvInvLevelSigma2 = t
         self._in_space = self._out_space = _lib.MEM_HOST
         self._last = None
+        self._pending = None
 
     def close(self):
         if getattr(self, "_h", None) and self._h.value:
@@ -116,6 +117,30 @@ class ORBextractor:
                                               kps.ctypes.data, desc.ctypes.data, cap, n.ctypes.data))
         self._last = (B, W, H)
         return kps, desc, n
+
+    def submit_batch(self, images, out):
+        """First half of extract_batch for host buffers (orbx_extract_batch_submit): enqueue and return. `images`
+        [B,H,W] uint8 and `out` = (kps [B,cap] KP_DTYPE or [B,cap,7] float32, desc [B,cap,32] uint8) are numpy arrays or
+        CPU torch tensors (pinned memory makes the copies asynchronous); they must stay alive until wait_batch()."""
+        def view(a):
+            return a.numpy() if _is_torch(a) else a
+        images, kps, desc = view(images), view(out[0]), view(out[1])
+        assert images.dtype == np.uint8 and images.ndim == 3 and images.strides[2] == 1
+        B, H, W = images.shape
+        cap = desc.shape[1]
+        assert desc.shape == (B, cap, 32) and kps.shape[:2] == (B, cap) and kps.nbytes == B * cap * 28
+        self._set_space(_lib.MEM_HOST, _lib.MEM_HOST)
+        _lib.check(self._L.orbx_extract_batch_submit(self._h, images.ctypes.data, B, W, H, images.strides[1],
+                                                     images.strides[0], kps.ctypes.data, desc.ctypes.data, cap))
+        self._pending = (images, out, np.zeros(B, np.int32))
+        self._last = (B, W, H)
+
+    def wait_batch(self):
+        """Second half (orbx_extract_batch_wait): returns (kps, desc, n) of the submitted batch."""
+        images, out, n = self._pending
+        self._pending = None
+        _lib.check(self._L.orbx_extract_batch_wait(self._h, n.ctypes.data))
+        return out[0], out[1], n
 
     def _extract_batch_torch(self, images, out=None):
         import torch
@@ -208,3 +233,62 @@ def compute_stereo_matches(left, right, mbf, minD, maxD, frame=None):
     u = np.zeros(cap, np.float32); z = np.zeros(cap, np.float32)
     _lib.check(L.orbx_stereo_match(left._h, right._h, frame, mbf, minD, maxD, u.ctypes.data, z.ctypes.data))
     return u, z
+
+
+class ExtractorRing:
+    """`depth` extractor handles used round-robin so that `depth` batches are in flight: while one batch's kernels run,
+    the next one's images cross PCIe and the previous one's keypoints come back. push(images) submits a batch and
+    returns the results of the batch pushed `depth` calls earlier (None while the ring fills); drain() returns the
+    rest in order. Result arrays are the ring's own pinned buffers: they are overwritten `depth` pushes after the call
+    that returned them."""
+
+    def __init__(self, depth=2, chunk=96, device=0, **params):
+        self.ex = [ORBextractor(**params, device=device) for _ in range(depth)]
+        for e in self.ex:
+            e.set_chunk(chunk)
+        self._out = [None] * (2 * depth)  # two result sets per handle: a returned set stays valid for `depth` pushes
+        self._flip = [0] * depth
+        self._shape = None
+        self._busy = [False] * depth
+        self._at = 0
+
+    def _buffers(self, k, B, cap):
+        import torch
+        if self._shape != (B, cap):  # (re)allocate every result set at once: pinning memory stalls the device
+            for k2 in range(len(self.ex)):
+                if self._busy[k2]:
+                    raise RuntimeError("ExtractorRing: drain() before pushing a batch of a different shape")
+            self._out = [(torch.empty((B, cap, 7), dtype=torch.float32).pin_memory(),
+                          torch.empty((B, cap, 32), dtype=torch.uint8).pin_memory()) for _ in self._out]
+            self._shape = (B, cap)
+        self._flip[k] ^= 1
+        return self._out[2 * k + self._flip[k]]
+
+    def _finish(self, k):
+        kps, desc, n = self.ex[k].wait_batch()
+        self._busy[k] = False
+        return kps.numpy().view(KP_DTYPE)[..., 0], desc.numpy(), n
+
+    def push(self, images):
+        k = self._at
+        self._at = (k + 1) % len(self.ex)
+        done = self._finish(k) if self._busy[k] else None
+        B, H, W = images.shape
+        self.ex[k].submit_batch(images, self._buffers(k, B, self.ex[k].max_keypoints(W, H)))
+        self._busy[k] = True
+        return done
+
+    def drain(self):
+        res = []
+        for i in range(len(self.ex)):
+            k = (self._at + i) % len(self.ex)
+            if self._busy[k]:
+                res.append(self._finish(k))
+        return res
+
+    def launch_count(self):
+        return sum(e.launch_count() for e in self.ex)
+
+    def close(self):
+        for e in self.ex:
+            e.close()

@@ -149,6 +149,40 @@ def test_host_pipeline_chunks_match_single_launch(ob):
     ex.close()
 
 
+def test_extractor_ring_matches_blocking_call(ob):
+    """submit/wait halves of orbx_extract_batch on two handles (ExtractorRing): batches of different content pushed back
+    to back come out in order with the bytes of the blocking call; misuse of the halves is an error, not a hang."""
+    p = _params(1000)
+    ex = ob.ORBextractor(**p)
+    batches = [np.stack([synth_image(640, 480, (3 * b + s) % 7) for s in range(9)]) for b in range(5)]
+    ref = [tuple(a.copy() for a in ex.extract_batch(b)) for b in batches]
+    ring = ob.ExtractorRing(depth=2, chunk=4, **p)
+    got = []
+    for b in batches:
+        r = ring.push(b)
+        if r is not None:
+            got.append(tuple(a.copy() for a in r))
+    got += [tuple(a.copy() for a in r) for r in ring.drain()]
+    assert len(got) == len(ref) and ring.drain() == []
+    for (k, d, n), (k0, d0, n0) in zip(got, ref):
+        assert np.array_equal(n, n0)
+        for f in range(len(n)):
+            assert k[f, :n[f]].tobytes() == k0[f, :n0[f]].tobytes() and np.array_equal(d[f, :n[f]], d0[f, :n0[f]])
+    ring.close()
+    # one pending batch per handle; wait without submit
+    cap = ex.max_keypoints(640, 480)
+    out = (np.zeros((9, cap), ob.KP_DTYPE), np.zeros((9, cap, 32), np.uint8))
+    ex._pending = (None, out, np.zeros(9, np.int32))
+    with pytest.raises(ob.OrbxError):
+        ex.wait_batch()
+    ex.submit_batch(batches[0], out)
+    with pytest.raises(ob.OrbxError):
+        ex.submit_batch(batches[1], out)
+    k, d, n = ex.wait_batch()
+    assert np.array_equal(n, ref[0][2]) and np.array_equal(d[0, :n[0]], ref[0][1][0, :n[0]])
+    ex.close()
+
+
 def test_4k_frame_all_stages(ob):
     """BASELINE config 5: 3840x2160, 8000 keypoints — every stage bit-exact at the largest shape (26 925 FAST cells,
     per-level quotas up to 1737, TMA tiles at the widest cell size)."""
