@@ -221,6 +221,36 @@ int orbx_set_profiling(orbx_t* h, int on);
 const char* orbx_last_error_string(void);
 const char* orbx_version(void);
 
+/* ---- vocabulary tree (bag of words): replaces fbow::Vocabulary as the reference uses it -------------------------------
+ * (Thirdparty/fbow/src/fbow.h:51-125, fbow.cpp; called from Frame::ComputeFboW src/Frame.cc:395-400 and
+ * KeyFrame::ComputeFboW src/KeyFrame.cc:62). */
+typedef struct orbv_handle orbv_t;
+/* Vocabulary::readFromFile / fromStream (fbow.cpp:156-183): blob = the bytes of a .fbow file. Only ORB vocabularies
+ * (CV_8UC1, 32 bytes) are accepted; anything else is ORBX_EINVAL. */
+int orbv_create(const void* blob, size_t size, int device, orbv_t** out);
+int orbv_destroy(orbv_t* v);
+/* getK / size / getDescSize / getTotalWords (fbow.h:100-108). Any output pointer may be NULL. */
+int orbv_info(orbv_t* v, uint32_t* k, uint32_t* nblocks, uint32_t* desc_size, uint64_t* total_words);
+int orbv_set_memory_space(orbv_t* v, int input_space, int output_space);
+/* Vocabulary::transform(features, level, fBow&, fBow2&) (fbow.cpp:52-93; level >= 0) and Vocabulary::transform(features)
+ * (fbow.cpp:95-153; level < 0 with normalize = 1) for `batch` descriptor matrices laid out as orbx_extract_batch
+ * writes them: frame f = desc + f*stride*32 with n[f] rows. Per frame f the results start at index f*stride
+ * (node_off: f*(stride+1)):
+ *   fBow   word_id[0..n_words[f])  ascending ids, word_w = the summed leaf weights (float sum in feature order)
+ *   fBow2  node_id[0..n_nodes[f])  ascending node ids; the features of node j are
+ *          node_feat[node_off[j] .. node_off[j+1]) in ascending feature order
+ * n, n_words, n_nodes are host arrays; the other pointers live in the handle's memory spaces. An empty frame gives
+ * empty results (the reference throws on an empty matrix and its callers never pass one, src/Frame.cc:398). */
+int orbv_transform_batch(orbv_t* v, const uint8_t* desc, const int* n, int batch, int stride, int level, int normalize,
+                         uint32_t* word_id, float* word_w, int* n_words, uint32_t* node_id, int* node_off,
+                         uint32_t* node_feat, int* n_nodes);
+/* fBow::score(q, db[i]) (fbow.cpp:208-254) for m id-sorted vectors in CSR form (db_off: m+1 entries), as
+ * KeyFrameDatabase evaluates it per candidate keyframe (src/KeyFrameDatabase.cc:130,247). Host pointers. */
+int orbv_score_batch(orbv_t* v, const uint32_t* q_id, const float* q_w, int nq, const uint32_t* db_id, const float* db_w,
+                     const int* db_off, int m, double* score);
+int orbv_stream(orbv_t* v, void** stream);
+int64_t orbv_launch_count(orbv_t* v);
+
 #ifdef __cplusplus
 }
 #endif

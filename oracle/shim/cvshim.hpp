@@ -11,6 +11,7 @@
 #include <cmath>
 #include <cstdint>
 #include <cstring>
+#include <limits>
 #include <memory>
 #include <vector>
 
@@ -19,6 +20,7 @@
 #define CV_PI 3.1415926535897932384626433832795
 #define CV_8U 0
 #define CV_8UC1 0
+#define CV_32FC1 5
 
 typedef unsigned char uchar;
 
@@ -109,6 +111,8 @@ public:
     bool empty() const { return data == nullptr || rows == 0 || cols == 0; }
     int type() const { return CV_8UC1; }
     size_t step1() const { return step; }
+    size_t elemSize() const { return 1; }   // used by Thirdparty/fbow (descriptor rows are CV_8UC1)
+    size_t elemSize1() const { return 1; }
 
     Mat operator()(const Rect& r) const {
         Mat m = *this;

@@ -5,3 +5,4 @@ from .extractor import ORBextractor, ExtractorRing, KP_DTYPE, compute_stereo_mat
 from .matcher import ORBmatcher  # noqa: F401
 from ._lib import OrbxError  # noqa: F401
 from .frame import Frame  # noqa: F401
+from .vocabulary import Vocabulary  # noqa: F401,E402

@@ -31,7 +31,8 @@ SYMBOLS = ["orbx_create", "orbx_destroy", "orbx_set_memory_space", "orbx_extract
            "orbm_destroy", "orbm_set_memory_space", "orbm_set_train", "orbm_knn2", "orbm_window_search", "orbm_distance",
            "orbm_search_by_projection", "orbm_search_local_points", "orbm_search_stats", "orbm_distinctive_descriptors",
            "orbx_stream", "orbm_stream", "orbx_launch_count", "orbm_launch_count", "orbx_stage_ms", "orbx_set_profiling",
-           "orbx_last_error_string", "orbx_version"]
+           "orbv_create", "orbv_destroy", "orbv_info", "orbv_set_memory_space", "orbv_transform_batch", "orbv_score_batch",
+           "orbv_stream", "orbv_launch_count", "orbx_last_error_string", "orbx_version"]
 
 
 class ProjParams(C.Structure):
@@ -103,6 +104,14 @@ def lib():
     L.orbm_stream.argtypes = [vp, C.POINTER(vp)]
     L.orbx_launch_count.argtypes = [vp]; L.orbx_launch_count.restype = C.c_int64
     L.orbm_launch_count.argtypes = [vp]; L.orbm_launch_count.restype = C.c_int64
+    L.orbv_create.argtypes = [C.c_char_p, sz, ci, C.POINTER(vp)]
+    L.orbv_destroy.argtypes = [vp]
+    L.orbv_info.argtypes = [vp, vp, vp, vp, vp]
+    L.orbv_set_memory_space.argtypes = [vp, ci, ci]
+    L.orbv_transform_batch.argtypes = [vp, vp, vp, ci, ci, ci, ci] + [vp] * 7
+    L.orbv_score_batch.argtypes = [vp, vp, vp, ci, vp, vp, vp, ci, vp]
+    L.orbv_stream.argtypes = [vp, C.POINTER(vp)]
+    L.orbv_launch_count.argtypes = [vp]; L.orbv_launch_count.restype = C.c_int64
     L.orbx_stage_ms.argtypes = [vp, vp]
     L.orbx_set_profiling.argtypes = [vp, ci]
     L.orbx_last_error_string.restype = C.c_char_p

@@ -6,7 +6,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "liborbx.so")
-SOURCES = ["orbx_extract.cu", "orbx_match.cu"]
+SOURCES = ["orbx_extract.cu", "orbx_match.cu", "orbx_fbow.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "--fmad=false",
               "-Xcompiler", "-fPIC,-O2,-ffp-contract=off", "-shared", "-cudart", "shared"]
 

@@ -160,3 +160,100 @@ def synth_tracking_pair(n_points=1200, seed=0, width=640, height=480, stereo=Tru
                 u_right=cur_ur[perm] if stereo else None)
     cur.SetPose(T)
     return last, cur
+
+
+FBOW_SIG = 55824124          # Thirdparty/fbow/src/fbow.cpp:166
+FBOW_PARAMS_BYTES = 120      # sizeof(fbow::Vocabulary::params), Thirdparty/fbow/src/fbow.h:115-125 (x86-64 layout)
+
+
+def _roundup(x, a):
+    return (x + a - 1) // a * a
+
+
+def synth_vocabulary(k=10, levels=3, seed=0, align=8, ragged=False, leaf_prob=0.0, name="orb"):
+    """Bytes of a synthetic vocabulary in the reference's `.fbow` wire format (Vocabulary::toStream,
+    Thirdparty/fbow/src/fbow.cpp:164-171; block layout fbow.h:160-190; sizes as setParams computes them,
+    fbow.cpp:10-49). `Vocabulary/orb_mur.fbow` itself is not in the reference tree, so tests and benches use this.
+
+    A k-ary tree of `levels` levels: a node's descriptor is its parent's with a level-dependent number of random bit
+    flips (so the descent is a meaningful nearest-centre search). ragged: blocks hold 1..k nodes; leaf_prob: inner
+    nodes that are leaves before the last level (words at mixed depths). Word ids run in creation order; weights are
+    random positive floats."""
+    rng = np.random.default_rng(seed)
+    desc_wp = _roundup(32, align)
+    feat_off = _roundup(8, align)
+    child_off = feat_off + k * desc_wp
+    block_size = _roundup(feat_off + k * (desc_wp + 8), align)
+    parents = rng.integers(0, 256, (1, 32), dtype=np.uint8)   # the (virtual) root descriptor
+    parent_block = np.zeros(1, np.uint32)
+    base, word = 0, 0
+    chunks = []
+    for d in range(levels):
+        nb = len(parents)
+        n = rng.integers(1, k + 1, nb) if ragged else np.full(nb, k)
+        if d == 0:
+            n[0] = k
+        mask = rng.integers(0, 256, (nb, k, 32), dtype=np.uint8)
+        for _ in range(d + 1):                                  # bit density 2^-(d+2)
+            mask &= rng.integers(0, 256, (nb, k, 32), dtype=np.uint8)
+        desc = parents[:, None, :] ^ mask
+        valid = np.arange(k)[None, :] < n[:, None]
+        leaf = np.ones((nb, k), bool) if d == levels - 1 else rng.random((nb, k)) < leaf_prob
+        inner = valid & ~leaf
+        leafv = valid & leaf
+        info = np.zeros((nb, k, 2), np.uint32)
+        n_inner, n_leaf = int(inner.sum()), int(leafv.sum())
+        info[..., 0][inner] = base + nb + np.arange(n_inner, dtype=np.uint32)
+        info[..., 0][leafv] = (word + np.arange(n_leaf, dtype=np.uint32)) | np.uint32(0x80000000)
+        info[..., 1][leafv] = (0.25 + 8.0 * rng.random(n_leaf)).astype(np.float32).view(np.uint32)
+        blk = np.zeros((nb, block_size), np.uint8)
+        blk[:, 0:2] = n.astype(np.uint16)[:, None].view(np.uint8)
+        blk[:, 2:4] = (~inner.any(axis=1)).astype(np.uint16)[:, None].view(np.uint8)
+        blk[:, 4:8] = parent_block.astype(np.uint32)[:, None].view(np.uint8)
+        feats = np.zeros((nb, k, desc_wp), np.uint8)
+        feats[:, :, :32] = desc * valid[:, :, None]
+        blk[:, feat_off:child_off] = feats.reshape(nb, k * desc_wp)
+        blk[:, child_off:child_off + 8 * k] = info.reshape(nb, 2 * k).view(np.uint8)
+        chunks.append(blk)
+        bi, _ = np.nonzero(inner)
+        parents = desc[inner]
+        parent_block = (base + bi).astype(np.uint32)
+        base += nb
+        word += n_leaf
+        if n_inner == 0:
+            break
+    data = np.concatenate(chunks)
+    nblocks = len(data)
+    hdr = np.zeros(FBOW_PARAMS_BYTES, np.uint8)
+    nm = name.encode()[:49]
+    hdr[:len(nm)] = np.frombuffer(nm, np.uint8)
+    hdr[52:60] = np.array([align, nblocks], np.uint32).view(np.uint8)
+    hdr[64:104] = np.array([desc_wp, block_size, feat_off, child_off, nblocks * block_size], np.uint64).view(np.uint8)
+    hdr[104:112] = np.array([0, 32], np.int32).view(np.uint8)   # CV_8UC1, 32 bytes
+    hdr[112:116] = np.array([k], np.uint32).view(np.uint8)
+    return np.array([FBOW_SIG], np.uint64).tobytes() + hdr.tobytes() + data.tobytes()
+
+
+def synth_vocabulary_features(blob, n, seed=0, flips=12, random_frac=0.1):
+    """n descriptors that resemble a vocabulary's words: a random leaf descriptor with `flips` random bits toggled
+    (a fraction random_frac is uniform noise). Reads the wire format only (layout as in synth_vocabulary)."""
+    rng = np.random.default_rng(seed)
+    raw = np.frombuffer(blob, np.uint8)
+    hdr = raw[8:8 + FBOW_PARAMS_BYTES]
+    nblocks = int(hdr[56:60].view(np.uint32)[0])
+    desc_wp, block_size, feat_off, child_off = (int(v) for v in hdr[64:96].view(np.uint64))
+    k = int(hdr[112:116].view(np.uint32)[0])
+    data = raw[8 + FBOW_PARAMS_BYTES:8 + FBOW_PARAMS_BYTES + nblocks * block_size].reshape(nblocks, block_size)
+    cnt = data[:, 0:2].copy().view(np.uint16)[:, 0]
+    info = data[:, child_off:child_off + 8 * k].copy().view(np.uint32).reshape(nblocks, k, 2)
+    leaf = ((info[..., 0] & np.uint32(0x80000000)) != 0) & (np.arange(k)[None, :] < cnt[:, None])
+    bi, ci = np.nonzero(leaf)
+    pick = rng.integers(0, len(bi), n)
+    feats = data[:, feat_off:feat_off + k * desc_wp].reshape(nblocks, k, desc_wp)[bi[pick], ci[pick], :32].copy()
+    bits = np.unpackbits(feats, axis=1)
+    for _ in range(flips):
+        bits[np.arange(n), rng.integers(0, 256, n)] ^= 1
+    feats = np.packbits(bits, axis=1)
+    noise = rng.random(n) < random_frac
+    feats[noise] = rng.integers(0, 256, (int(noise.sum()), 32), dtype=np.uint8)
+    return feats

@@ -268,3 +268,98 @@ def canonical(kps, desc):
     """Sort (level, y, x) — the order-free comparison key of SURVEY.md §7 H8."""
     order = np.lexsort((kps["x"], kps["y"], kps["octave"]))
     return kps[order], desc[order]
+
+
+REF_FBOW_SO = os.path.join(ROOT, "oracle", "_ref", "libref_fbow.so")
+
+
+def have_ref_fbow():
+    build_oracle()
+    return os.path.exists(REF_FBOW_SO)
+
+
+def _bow_buffers(n):
+    return (np.zeros(n, np.uint32), np.zeros(n, np.float32), np.zeros(n, np.uint32), np.zeros(n + 1, np.int32),
+            np.zeros(n, np.uint32))
+
+
+def _bow_pack(wid, ww, nw, nid, noff, feat, nn):
+    """(fBow as (ids, weights), fBow2 as {node: feature indices})"""
+    return (wid[:nw].copy(), ww[:nw].copy()), {int(nid[i]): feat[noff[i]:noff[i + 1]].copy() for i in range(nn)}
+
+
+class OracleVocabulary:
+    """Restatement of fbow::Vocabulary::transform (oracle/orb_oracle.cpp orc_fbow_*) over the bytes of a .fbow file."""
+
+    def __init__(self, blob):
+        build_oracle()
+        self.L = L = _load(ORACLE_SO)
+        self.blob = bytes(blob)
+        L.orc_fbow_transform.argtypes = [C.c_char_p, C.c_size_t, C.c_void_p, C.c_int, C.c_int] + [C.c_void_p] * 7
+        L.orc_fbow_normalize.argtypes = [C.c_void_p, C.c_int]
+        L.orc_fbow_score.restype = C.c_double
+        L.orc_fbow_score.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int]
+
+    def transform(self, desc, level=None):
+        """level given: Vocabulary::transform(features, level, fBow&, fBow2&) -> ((ids, weights), {node: features});
+        level None: Vocabulary::transform(features) -> L2-normalised (ids, weights)."""
+        desc = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+        n = len(desc)
+        wid, ww, nid, noff, feat = _bow_buffers(n)
+        nw, nn = C.c_int(), C.c_int()
+        rc = self.L.orc_fbow_transform(self.blob, len(self.blob), _p(desc), n, -1 if level is None else level, _p(wid),
+                                       _p(ww), C.byref(nw), _p(nid), _p(noff), _p(feat), C.byref(nn))
+        assert rc == 0, "bad vocabulary blob"
+        bow, fv = _bow_pack(wid, ww, nw.value, nid, noff, feat, nn.value)
+        if level is None:
+            self.L.orc_fbow_normalize(_p(bow[1]), len(bow[1]))
+            return bow
+        return bow, fv
+
+    def score(self, a, b):
+        return self.L.orc_fbow_score(_p(a[0]), _p(a[1]), len(a[0]), _p(b[0]), _p(b[1]), len(b[0]))
+
+
+class RefVocabulary:
+    """The unmodified reference fbow::Vocabulary (oracle/_ref/libref_fbow.so), loaded through fromStream."""
+
+    def __init__(self, blob):
+        build_oracle()
+        self.L = L = _load(REF_FBOW_SO)
+        L.ref_fbow_load.restype = C.c_void_p
+        L.ref_fbow_load.argtypes = [C.c_char_p, C.c_size_t]
+        L.ref_fbow_free.argtypes = [C.c_void_p]
+        L.ref_fbow_info.argtypes = [C.c_void_p] * 5
+        L.ref_fbow_transform2.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int] + [C.c_void_p] * 7
+        L.ref_fbow_transform.argtypes = [C.c_void_p, C.c_void_p, C.c_int] + [C.c_void_p] * 3
+        L.ref_fbow_score.restype = C.c_double
+        L.ref_fbow_score.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int]
+        self.h = L.ref_fbow_load(bytes(blob), len(blob))
+        assert self.h, "reference fromStream rejected the blob"
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.L.ref_fbow_free(self.h)
+            self.h = None
+
+    def info(self):
+        k, nb, ds, tw = C.c_uint32(), C.c_uint64(), C.c_uint32(), C.c_uint64()
+        self.L.ref_fbow_info(self.h, C.byref(k), C.byref(nb), C.byref(ds), C.byref(tw))
+        return dict(k=k.value, nblocks=nb.value, desc_size=ds.value, total_words=tw.value)
+
+    def transform(self, desc, level=None):
+        desc = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+        n = len(desc)
+        wid, ww, nid, noff, feat = _bow_buffers(n)
+        nw, nn = C.c_int(), C.c_int()
+        if level is None:
+            rc = self.L.ref_fbow_transform(self.h, _p(desc), n, _p(wid), _p(ww), C.byref(nw))
+            assert rc == 0
+            return wid[:nw.value].copy(), ww[:nw.value].copy()
+        rc = self.L.ref_fbow_transform2(self.h, _p(desc), n, level, _p(wid), _p(ww), C.byref(nw), _p(nid), _p(noff),
+                                        _p(feat), C.byref(nn))
+        assert rc == 0
+        return _bow_pack(wid, ww, nw.value, nid, noff, feat, nn.value)
+
+    def score(self, a, b):
+        return self.L.ref_fbow_score(_p(a[0]), _p(a[1]), len(a[0]), _p(b[0]), _p(b[1]), len(b[0]))

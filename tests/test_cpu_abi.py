@@ -20,7 +20,7 @@ def lib_path():
 def _header_symbols():
     src = open(os.path.join(ROOT, "include", "orbx.h")).read()
     src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
-    return sorted(set(re.findall(r"\b(orb[xm]_[a-z0-9_]+)\s*\(", src)))
+    return sorted(set(re.findall(r"\b(orb[xmv]_[a-z0-9_]+)\s*\(", src)))
 
 
 def test_header_and_python_symbol_lists_agree():
