@@ -245,7 +245,8 @@ int orbv_transform_batch(orbv_t* v, const uint8_t* desc, const int* n, int batch
                          uint32_t* word_id, float* word_w, int* n_words, uint32_t* node_id, int* node_off,
                          uint32_t* node_feat, int* n_nodes);
 /* fBow::score(q, db[i]) (fbow.cpp:208-254) for m id-sorted vectors in CSR form (db_off: m+1 entries), as
- * KeyFrameDatabase evaluates it per candidate keyframe (src/KeyFrameDatabase.cc:130,247). Host pointers. */
+ * KeyFrameDatabase evaluates it per candidate keyframe (src/KeyFrameDatabase.cc:130,247). Host pointers. v may be NULL
+ * (fBow::score is static in the reference): the current device is used. */
 int orbv_score_batch(orbv_t* v, const uint32_t* q_id, const float* q_w, int nq, const uint32_t* db_id, const float* db_w,
                      const int* db_off, int m, double* score);
 int orbv_stream(orbv_t* v, void** stream);

@@ -212,11 +212,11 @@ extern "C" int orbv_transform_batch(orbv_t* v, const uint8_t* desc, const int* n
 // (src/KeyFrameDatabase.cc:130,247). All pointers are host pointers.
 extern "C" int orbv_score_batch(orbv_t* v, const uint32_t* q_id, const float* q_w, int nq, const uint32_t* db_id,
                                 const float* db_w, const int* db_off, int m, double* score) {
-    if (!v || !db_off || !score || nq < 0 || m < 0) FAIL(ORBX_EINVAL, "bad argument");
+    if (!db_off || !score || nq < 0 || m < 0) FAIL(ORBX_EINVAL, "bad argument");
     if (m == 0) return ORBX_OK;
-    CK(cudaSetDevice(v->device));
+    if (v) CK(cudaSetDevice(v->device));
     const int total = db_off[m];
-    cudaStream_t st = v->stream;
+    cudaStream_t st = v ? v->stream : cudaStreamPerThread;  // fBow::score is static: no vocabulary needed
     uint8_t* buf = nullptr;
     const size_t bq = (size_t)std::max(nq, 1) * 4, bd = (size_t)std::max(total, 1) * 4, bo = (size_t)(m + 1) * 4;
     auto up = [](size_t x) { return (x + 255) & ~(size_t)255; };
@@ -238,7 +238,7 @@ extern "C" int orbv_score_batch(orbv_t* v, const uint32_t* q_id, const float* q_
     }
     CK(cudaMemcpyAsync(doff, db_off, bo, cudaMemcpyHostToDevice, st));
     k_fbow_score<<<(m + 127) / 128, 128, 0, st>>>(dq, dqw, nq, dd, ddw, doff, m, ds);
-    v->launches++;
+    if (v) v->launches++;
     CK(cudaGetLastError());
     CK(cudaMemcpyAsync(score, ds, (size_t)m * 8, cudaMemcpyDeviceToHost, st));
     CK(cudaFreeAsync(buf, st));

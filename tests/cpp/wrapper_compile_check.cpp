@@ -7,6 +7,7 @@
 
 #include "dropin/ORBextractor.h"
 #include "dropin/ORBmatcher.h"
+#include "dropin/fbow.h"
 
 static std::vector<unsigned char> slurp(const char* path, size_t n) {
     std::vector<unsigned char> b(n);
@@ -48,6 +49,27 @@ int main(int argc, char** argv) {
     for (int y = 0; y < p3.rows; y++) fwrite(p3.ptr(y), 1, p3.cols, f);
     fclose(f);
     printf("dropin ok: %zu/%zu keypoints, %d ratio-accepted\n", kL.size(), kR.size(), accepted);
+    if (argc >= 8) {  // Frame::ComputeFboW (src/Frame.cc:395-400) + a KeyFrameDatabase-style score: <vocab.fbow> <out2.bin>
+        fbow::Vocabulary voc;
+        voc.readFromFile(argv[6]);
+        fbow::fBow bL, bR;
+        fbow::fBow2 fL, fR;
+        voc.transform(dL, 4, bL, fL);
+        voc.transform(dR, 4, bR, fR);
+        fbow::fBow nL = voc.transform(dL), nR = voc.transform(dR);
+        const double sc[2] = {fbow::fBow::score(nL, nR), fbow::fBow::score(nL, nL)};
+        FILE* g = fopen(argv[7], "wb");
+        int h2[4] = {(int)bL.size(), (int)fL.size(), (int)voc.getK(), (int)voc.getTotalWords()};
+        fwrite(h2, sizeof(int), 4, g);
+        for (const auto& e : bL) { float w = e.second; fwrite(&e.first, 4, 1, g); fwrite(&w, 4, 1, g); }
+        for (const auto& e : fL) {
+            int c = (int)e.second.size();
+            fwrite(&e.first, 4, 1, g); fwrite(&c, 4, 1, g); fwrite(e.second.data(), 4, e.second.size(), g);
+        }
+        fwrite(sc, 8, 2, g);
+        fclose(g);
+        printf("fbow ok: %zu words, %zu nodes, score %.6f\n", bL.size(), fL.size(), sc[0]);
+    }
     return 0;
 }
 

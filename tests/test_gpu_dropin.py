@@ -7,8 +7,8 @@ import subprocess
 import numpy as np
 import pytest
 
-from oracle_lib import Oracle, OraclePrims, canonical, KP_DTYPE, TUM1
-from orbslam2_b200.synth import synth_stereo_pair
+from oracle_lib import Oracle, OraclePrims, OracleVocabulary, canonical, KP_DTYPE, TUM1
+from orbslam2_b200.synth import synth_stereo_pair, synth_vocabulary
 
 pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -24,9 +24,11 @@ def test_cpp_dropin_end_to_end(tmp_path):
     w, h = 640, 480
     left, right = synth_stereo_pair(w, h, 5)
     left.tofile(tmp_path / "l.raw"); right.tofile(tmp_path / "r.raw")
-    out = tmp_path / "out.bin"
-    r = subprocess.run([exe, str(w), str(h), str(tmp_path / "l.raw"), str(tmp_path / "r.raw"), str(out)],
-                       capture_output=True, text=True, timeout=120)
+    out, out2, vfile = tmp_path / "out.bin", tmp_path / "out2.bin", tmp_path / "synthetic.fbow"
+    blob = synth_vocabulary(k=10, levels=4, seed=21)
+    vfile.write_bytes(blob)
+    r = subprocess.run([exe, str(w), str(h), str(tmp_path / "l.raw"), str(tmp_path / "r.raw"), str(out), str(vfile),
+                        str(out2)], capture_output=True, text=True, timeout=120)
     assert r.returncode == 0, r.stdout + r.stderr
     raw = open(out, "rb").read()
     nL, nR, accepted, d01, levels, p3w = np.frombuffer(raw[:24], np.int32)
@@ -61,3 +63,21 @@ def test_cpp_dropin_end_to_end(tmp_path):
     exp_acc = int(((e1 <= 50) & (e1.astype(np.float32) < np.float32(0.7) * e2.astype(np.float32))).sum())
     assert accepted == exp_acc
     assert d01 == P.hamming(do[0], do[1])
+    # fbow drop-in: Vocabulary::transform(features, 4, fBow, fBow2), transform(features) and fBow::score
+    raw2 = open(out2, "rb").read()
+    nw, nn, k, words = np.frombuffer(raw2[:16], np.int32)
+    assert k == 10 and words == 10000
+    voc = OracleVocabulary(blob)
+    (ewid, eww), efv = voc.transform(desc, 4)
+    pairs = np.frombuffer(raw2[16:16 + 8 * nw], np.uint32).reshape(nw, 2)
+    assert np.array_equal(pairs[:, 0], ewid) and pairs[:, 1].tobytes() == eww.tobytes()
+    at = 16 + 8 * nw
+    assert nn == len(efv)
+    for key in sorted(efv):
+        nid, c = np.frombuffer(raw2[at:at + 8], np.uint32)
+        lst = np.frombuffer(raw2[at + 8:at + 8 + 4 * c], np.uint32)
+        assert nid == key and np.array_equal(lst, efv[key])
+        at += 8 + 4 * c
+    sc = np.frombuffer(raw2[at:at + 16], np.float64)
+    a, bR = voc.transform(desc), voc.transform(dr)  # (right descriptors: the oracle's own extraction, identical above)
+    assert sc[0] == voc.score(a, bR) and sc[1] == voc.score(a, a)
