@@ -363,3 +363,36 @@ class RefVocabulary:
 
     def score(self, a, b):
         return self.L.ref_fbow_score(_p(a[0]), _p(a[1]), len(a[0]), _p(b[0]), _p(b[1]), len(b[0]))
+
+
+class OraclePrep:
+    """Upstream image prep restatements (oracle/cvprim.hpp): cvtColor X2GRAY, remap INTER_LINEAR, undistortPoints."""
+
+    def __init__(self):
+        build_oracle()
+        self.L = L = _load(ORACLE_SO)
+        L.orc_cvt_gray.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_size_t, C.c_int, C.c_int, C.c_void_p]
+        L.orc_remap.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+        L.orc_undistort_points.argtypes = [C.c_void_p, C.c_int] + [C.c_float] * 4 + [C.c_void_p, C.c_int, C.c_void_p]
+
+    def cvt_gray(self, img, blue_first):
+        img = np.ascontiguousarray(img, np.uint8)
+        h, w, ch = img.shape
+        out = np.zeros((h, w), np.uint8)
+        self.L.orc_cvt_gray(_p(img), w, h, w * ch, ch, int(blue_first), _p(out))
+        return out
+
+    def remap(self, src, mapx, mapy):
+        src = np.ascontiguousarray(src, np.uint8)
+        mapx, mapy = np.ascontiguousarray(mapx, np.float32), np.ascontiguousarray(mapy, np.float32)
+        dh, dw = mapx.shape
+        out = np.zeros((dh, dw), np.uint8)
+        self.L.orc_remap(_p(src), src.shape[1], src.shape[0], _p(mapx), _p(mapy), dw, dh, _p(out))
+        return out
+
+    def undistort_points(self, pts, fx, fy, cx, cy, dist):
+        pts = np.ascontiguousarray(pts, np.float32).reshape(-1, 2)
+        dist = np.ascontiguousarray(dist, np.float32).ravel()
+        out = np.zeros_like(pts)
+        self.L.orc_undistort_points(_p(pts), len(pts), fx, fy, cx, cy, _p(dist), len(dist), _p(out))
+        return out

@@ -212,3 +212,40 @@ def test_distinctive_descriptors_oracle_micro_case():
     d = np.zeros((5, 32), np.uint8); d[2, 0] = 0xFF; d[4, :] = 0xFF
     bi, bm = OraclePrims().distinctive_descriptors(d, np.array([0, 3, 5, 5], np.int32))
     assert list(bi) == [0, 0, -1] and list(bm[:2]) == [0, 0]
+
+
+# ---- upstream image prep: restatements vs cv2 golden vectors ------------------------------------
+def _prep_golden():
+    return np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "cv2_prep.npz"))
+
+
+def colour_cube():
+    r, g, b = np.meshgrid(np.arange(256), np.arange(256), np.arange(0, 256, 51), indexing="ij")
+    return np.stack([r, g, b], -1).astype(np.uint8).reshape(256, -1, 3)
+
+
+def test_prep_cvtcolor_matches_cv2():
+    from oracle_lib import OraclePrep
+    G, P = _prep_golden(), OraclePrep()
+    assert np.array_equal(P.cvt_gray(G["cvt_rgb"], False), G["gray_rgb"])
+    assert np.array_equal(P.cvt_gray(G["cvt_rgb"], True), G["gray_bgr"])
+    assert np.array_equal(P.cvt_gray(G["cvt_rgba"], False), G["gray_rgba"])
+    assert np.array_equal(P.cvt_gray(G["cvt_rgba"], True), G["gray_bgra"])
+    assert np.array_equal(P.cvt_gray(colour_cube(), False), G["gray_cube_rgb"])
+
+
+def test_prep_remap_matches_cv2():
+    from oracle_lib import OraclePrep
+    G, P = _prep_golden(), OraclePrep()
+    for name in ("rect", "noisy", "wild"):
+        got = P.remap(G["remap_src"], G[f"remap_{name}_x"], G[f"remap_{name}_y"])
+        assert np.array_equal(got, G[f"remap_{name}"]), name
+
+
+def test_prep_undistort_points_matches_cv2():
+    from oracle_lib import OraclePrep
+    G, P = _prep_golden(), OraclePrep()
+    for name in ("tum1", "euroc4"):
+        K = G[f"und_{name}_K"]
+        got = P.undistort_points(G["und_pts"], K[0], K[1], K[2], K[3], G[f"und_{name}_D"])
+        assert got.tobytes() == G[f"und_{name}"].tobytes(), name
