@@ -82,6 +82,21 @@ int orbx_extract_batch(orbx_t* h, const uint8_t* imgs, int batch, int w, int hgt
 int orbx_extract_batch_submit(orbx_t* h, const uint8_t* imgs, int batch, int w, int hgt, size_t stride,
                               size_t img_stride, orbx_kp* kps, uint8_t* desc, int cap_per_frame);
 int orbx_extract_batch_wait(orbx_t* h, int* n);
+/* ---- upstream image prep fused into the ingest (the calls the reference makes before the extractor) -----------------
+ * Pixel format of the images handed to orbx_extract*: colour input is converted exactly as
+ * cv::cvtColor(.., COLOR_{RGB,BGR,RGBA,BGRA}2GRAY) (src/Tracking.cc:269-294, 308-321, 337-350) while it is written into
+ * pyramid level 0. `stride` of the extract calls is then the row stride in bytes of the interleaved image. */
+enum { ORBX_FMT_GRAY8 = 0, ORBX_FMT_RGB8 = 1, ORBX_FMT_BGR8 = 2, ORBX_FMT_RGBA8 = 3, ORBX_FMT_BGRA8 = 4 };
+int orbx_set_input_format(orbx_t* h, int fmt);
+/* Rectification maps as cv::initUndistortRectifyMap(.., CV_32F, M1, M2) returns them (host pointers, out_w*out_h floats
+ * each). Every following extract call remaps its source images as cv::remap(src, dst, M1, M2, cv::INTER_LINEAR) does
+ * (Test/Replay/Stereo/stereo_euroc.cc:98-99, 136-137; BORDER_CONSTANT 0) into pyramid level 0: (w, hgt) of the extract
+ * call describe the source, the pyramid has the maps' size. NULL, NULL switches rectification off. */
+int orbx_set_rectify_maps(orbx_t* h, const float* map_x, const float* map_y, int out_w, int out_h);
+/* Frame::UndistortKeyPoints (src/Frame.cc:402-432) for every frame of the last batch: kps_un[f*cap + i] = keypoint i of
+ * frame f with pt replaced by cv::undistortPoints(pt, K, D, Mat(), K). K4 = fx, fy, cx, cy; dist = k1 k2 p1 p2 [k3 [k4
+ * k5 k6]] (host pointers); dist[0] == 0 copies the keypoints (src/Frame.cc:404-408). kps_un lives in the output space. */
+int orbx_undistort_keypoints(orbx_t* h, const float* K4, const float* dist, int ndist, orbx_kp* kps_un, int cap);
 /* Smallest cap_per_frame that can never return ORBX_ECAP for this shape (sum over levels of quota + slack). */
 int orbx_max_keypoints(orbx_t* h, int w, int hgt, int* cap);
 /* With host buffers a batch is split into chunks of `frames` frames that are software-pipelined: the PCIe copy-in of

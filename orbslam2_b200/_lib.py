@@ -9,6 +9,7 @@ _LIB = None
 
 ORBX_OK, ORBX_EINVAL, ORBX_ESHAPE, ORBX_ECAP, ORBX_ECUDA, ORBX_ESTATE = range(6)
 MEM_HOST, MEM_DEVICE = 0, 1
+FMT_GRAY8, FMT_RGB8, FMT_BGR8, FMT_RGBA8, FMT_BGRA8 = range(5)
 _NAMES = {1: "ORBX_EINVAL", 2: "ORBX_ESHAPE", 3: "ORBX_ECAP", 4: "ORBX_ECUDA", 5: "ORBX_ESTATE"}
 
 
@@ -25,7 +26,8 @@ class OrbxParams(C.Structure):
 
 # every symbol include/orbx.h declares (tests check the export table against this list and the header)
 SYMBOLS = ["orbx_create", "orbx_destroy", "orbx_set_memory_space", "orbx_extract", "orbx_extract_batch",
-           "orbx_extract_batch_submit", "orbx_extract_batch_wait",
+           "orbx_extract_batch_submit", "orbx_extract_batch_wait", "orbx_set_input_format", "orbx_set_rectify_maps",
+           "orbx_undistort_keypoints",
            "orbx_max_keypoints", "orbx_set_chunk", "orbx_level_count", "orbx_tables", "orbx_level_size", "orbx_pyramid_level",
            "orbx_blurred_level", "orbx_candidates", "orbx_stereo_match", "orbx_stereo_match_batch", "orbm_create",
            "orbm_destroy", "orbm_set_memory_space", "orbm_set_train", "orbm_knn2", "orbm_window_search", "orbm_distance",
@@ -77,6 +79,9 @@ def lib():
     L.orbx_extract_batch.argtypes = [vp, vp, ci, ci, ci, sz, sz, vp, vp, ci, vp]
     L.orbx_extract_batch_submit.argtypes = [vp, vp, ci, ci, ci, sz, sz, vp, vp, ci]
     L.orbx_extract_batch_wait.argtypes = [vp, vp]
+    L.orbx_set_input_format.argtypes = [vp, ci]
+    L.orbx_set_rectify_maps.argtypes = [vp, vp, vp, ci, ci]
+    L.orbx_undistort_keypoints.argtypes = [vp, vp, vp, ci, vp, ci]
     L.orbx_max_keypoints.argtypes = [vp, ci, ci, C.POINTER(ci)]
     L.orbx_set_chunk.argtypes = [vp, ci]
     L.orbx_level_count.argtypes = [vp]

@@ -65,6 +65,14 @@ struct orbx_handle {
     cudaEvent_t evStart = nullptr, evDone = nullptr;
     std::vector<cudaEvent_t> evIn, evComp;
     float stageMs[7] = {};
+    // upstream image prep fused into the ingest (orbx_prep.cuh)
+    int inFmt = ORBX_FMT_GRAY8;
+    float *dMapX = nullptr, *dMapY = nullptr;  // rectification maps (output size mapW x mapH)
+    int mapW = 0, mapH = 0;
+    uint8_t *dRaw = nullptr, *dGray = nullptr;  // staged source images / grey source of the remap
+    size_t rawCap = 0, grayCap = 0;
+    orbx_kp* dKpsUn = nullptr;
+    size_t kpsUnCap = 0;
 };
 
 static inline int round_half_even_f(float v) { return (int)lrintf(v); }
@@ -341,6 +349,7 @@ extern "C" int orbx_destroy(orbx_t* h) {
         cudaStreamDestroy(h->sComp[0]);
         cudaStreamDestroy(h->sComp[1]);
     }
+    cudaFree(h->dMapX); cudaFree(h->dMapY); cudaFree(h->dRaw); cudaFree(h->dGray); cudaFree(h->dKpsUn);
     cudaStreamDestroy(h->stream);
     delete h;
     return ORBX_OK;
@@ -437,6 +446,28 @@ static int launch_chain(orbx_handle* h, cudaStream_t cs, int f0, int nb, bool st
     return ORBX_OK;
 }
 
+static inline int fmt_channels(int fmt) { return fmt == ORBX_FMT_GRAY8 ? 1 : (fmt == ORBX_FMT_RGB8 || fmt == ORBX_FMT_BGR8 ? 3 : 4); }
+
+// staging for colour / rectified input: the raw source images (host input only) and the grey source of the remap
+static int ensure_ingest(orbx_handle* h, int batch, int w, int hgt) {
+    const int ch = fmt_channels(h->inFmt);
+    if (ch == 1 && !h->dMapX) return ORBX_OK;
+    const size_t raw = (size_t)batch * hgt * w * ch, gray = (size_t)batch * hgt * w;
+    if (h->inSpace == ORBX_MEM_HOST && raw > h->rawCap) {
+        cudaFree(h->dRaw);
+        h->dRaw = nullptr;
+        CK(cudaMalloc(&h->dRaw, raw));
+        h->rawCap = raw;
+    }
+    if (ch > 1 && h->dMapX && gray > h->grayCap) {
+        cudaFree(h->dGray);
+        h->dGray = nullptr;
+        CK(cudaMalloc(&h->dGray, gray));
+        h->grayCap = gray;
+    }
+    return ORBX_OK;
+}
+
 static int copy_in(orbx_handle* h, cudaStream_t cs, const uint8_t* imgs, int f0, int nb, int w, int hgt, size_t stride,
                    size_t img_stride) {
     // ingest: level 0 of the pyramid IS the input image (src/ORBextractor.cc:939-943); one strided copy
@@ -444,6 +475,43 @@ static int copy_in(orbx_handle* h, cudaStream_t cs, const uint8_t* imgs, int f0,
     const LevelGeo& L0 = h->hp.lv[0];
     uint8_t* dst = h->dPyr + L0.pyrOff + (long long)f0 * L0.frameStride;
     const uint8_t* src = imgs + (size_t)f0 * img_stride;
+    const int ch = fmt_channels(h->inFmt);
+    if (ch > 1 || h->dMapX) {
+        // colour and/or unrectified input: the source is staged (host input) or read in place (device input), then
+        // converted / remapped straight into level 0
+        const size_t rowBytes = (size_t)w * ch;
+        size_t sStride = stride, sImg = img_stride;
+        if (h->inSpace == ORBX_MEM_HOST) {
+            uint8_t* raw = h->dRaw + (size_t)f0 * hgt * rowBytes;
+            if (nb == 1 || img_stride == stride * (size_t)hgt) {
+                CK(cudaMemcpy2DAsync(raw, rowBytes, src, stride, rowBytes, (size_t)hgt * nb, kin, cs));
+            } else {
+                for (int f = 0; f < nb; f++)
+                    CK(cudaMemcpy2DAsync(raw + (size_t)f * hgt * rowBytes, rowBytes, src + f * img_stride, stride, rowBytes, hgt, kin, cs));
+            }
+            src = raw;
+            sStride = rowBytes;
+            sImg = rowBytes * hgt;
+        }
+        if (ch > 1) {
+            uint8_t* g = h->dMapX ? h->dGray + (size_t)f0 * hgt * w : dst;
+            const int gPitch = h->dMapX ? w : L0.pitch;
+            const long long gFrame = h->dMapX ? (long long)hgt * w : L0.frameStride;
+            k_cvt_gray<<<dim3((w + 255) / 256, hgt, nb), 64, 0, cs>>>(src, sStride, sImg, ch,
+                                                                      h->inFmt == ORBX_FMT_BGR8 || h->inFmt == ORBX_FMT_BGRA8,
+                                                                      w, g, gPitch, gFrame);
+            KCHECK(h, "k_cvt_gray");
+            src = g;
+            sStride = (size_t)w;
+            sImg = (size_t)hgt * w;
+        }
+        if (h->dMapX) {
+            k_remap<<<dim3((L0.w + 127) / 128, L0.h, nb), 128, 0, cs>>>(src, sStride, sImg, w, hgt, h->dMapX, h->dMapY, L0.w,
+                                                                        dst, L0.pitch, L0.frameStride);
+            KCHECK(h, "k_remap");
+        }
+        return ORBX_OK;
+    }
     if (nb == 1 || img_stride == stride * (size_t)hgt) {
         CK(cudaMemcpy2DAsync(dst, L0.pitch, src, stride, w, (size_t)hgt * nb, kin, cs));
     } else {
@@ -496,10 +564,14 @@ extern "C" int orbx_extract_batch_submit(orbx_t* h, const uint8_t* imgs, int bat
         h->pendingBatch = -batch;
         return ORBX_OK;
     }
-    if (stride < (size_t)w || (batch > 1 && img_stride < stride * (size_t)hgt)) FAIL(ORBX_EINVAL, "bad strides");
+    if (stride < (size_t)w * fmt_channels(h->inFmt) || (batch > 1 && img_stride < stride * (size_t)hgt))
+        FAIL(ORBX_EINVAL, "bad strides");
     if (cap < 0 || (cap > 0 && (!kps || !desc))) FAIL(ORBX_EINVAL, "null output");
     CK(cudaSetDevice(h->device));
-    int rc = build_plan(h, w, hgt, batch);
+    // with rectification maps the pyramid has the maps' size; (w, hgt) describe the source images
+    int rc = build_plan(h, h->dMapX ? h->mapW : w, h->dMapX ? h->mapH : hgt, batch);
+    if (rc != ORBX_OK) return rc;
+    rc = ensure_ingest(h, batch, w, hgt);
     if (rc != ORBX_OK) return rc;
     const DevPlan& D = h->hp;
     cudaStream_t st = h->stream;
@@ -620,6 +692,70 @@ extern "C" int orbx_extract_batch(orbx_t* h, const uint8_t* imgs, int batch, int
         return rc;
     }
     return orbx_extract_batch_wait(h, n);
+}
+
+/* Pixel format of the images handed to orbx_extract*: colour input is converted as cv::cvtColor(.., COLOR_x2GRAY) does
+ * (src/Tracking.cc:269-294) while it is written into pyramid level 0. Strides are in bytes. */
+extern "C" int orbx_set_input_format(orbx_t* h, int fmt) {
+    if (!h || fmt < ORBX_FMT_GRAY8 || fmt > ORBX_FMT_BGRA8) FAIL(ORBX_EINVAL, "bad input format");
+    h->inFmt = fmt;
+    return ORBX_OK;
+}
+
+/* Rectification maps as cv::initUndistortRectifyMap(.., CV_32F, M1, M2) returns them (host pointers, out_w x out_h
+ * floats each): every following extract call remaps its source images like cv::remap(src, dst, M1, M2, INTER_LINEAR)
+ * (Test/Replay/Stereo/stereo_euroc.cc:98-99,136-137) into pyramid level 0. NULL maps switch it off. */
+extern "C" int orbx_set_rectify_maps(orbx_t* h, const float* map_x, const float* map_y, int out_w, int out_h) {
+    if (!h) FAIL(ORBX_EINVAL, "null handle");
+    CK(cudaSetDevice(h->device));
+    CK(cudaStreamSynchronize(h->stream));
+    cudaFree(h->dMapX); cudaFree(h->dMapY);
+    h->dMapX = h->dMapY = nullptr;
+    h->mapW = h->mapH = 0;
+    if (!map_x && !map_y) return ORBX_OK;
+    if (!map_x || !map_y || out_w <= 0 || out_h <= 0) FAIL(ORBX_EINVAL, "bad maps");
+    const size_t bytes = (size_t)out_w * out_h * sizeof(float);
+    CK(cudaMalloc(&h->dMapX, bytes));
+    CK(cudaMalloc(&h->dMapY, bytes));
+    CK(cudaMemcpy(h->dMapX, map_x, bytes, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(h->dMapY, map_y, bytes, cudaMemcpyHostToDevice));
+    h->mapW = out_w;
+    h->mapH = out_h;
+    return ORBX_OK;
+}
+
+/* Frame::UndistortKeyPoints (src/Frame.cc:402-432) for every frame of the last batch: kps_un[f*cap + i] is keypoint i
+ * of frame f with pt replaced by cv::undistortPoints(pt, K, D, Mat(), K); K4 = fx, fy, cx, cy; dist = k1 k2 p1 p2 [k3
+ * [k4 k5 k6]] (host pointers). dist[0] == 0 (or ndist == 0) copies the keypoints unchanged, as the reference does. */
+extern "C" int orbx_undistort_keypoints(orbx_t* h, const float* K4, const float* dist, int ndist, orbx_kp* kps_un, int cap) {
+    if (!h || !K4 || !kps_un || ndist < 0 || ndist > 8 || (ndist > 0 && !dist)) FAIL(ORBX_EINVAL, "bad argument");
+    if (!h->lastBatch) FAIL(ORBX_ESTATE, "no extracted batch to undistort");
+    CK(cudaSetDevice(h->device));
+    const DevPlan& D = h->hp;
+    const int batch = h->lastBatch;
+    const size_t need = (size_t)batch * D.selStride;
+    if (need > h->kpsUnCap) {
+        cudaFree(h->dKpsUn);
+        h->dKpsUn = nullptr;
+        CK(cudaMalloc(&h->dKpsUn, need * sizeof(orbx_kp)));
+        h->kpsUnCap = need;
+    }
+    UndistortParams P;
+    memset(&P, 0, sizeof(P));
+    P.fx = K4[0]; P.fy = K4[1]; P.cx = K4[2]; P.cy = K4[3];
+    for (int i = 0; i < ndist; i++) P.k[i] = dist[i];
+    P.identity = ndist == 0 || dist[0] == 0.0f;
+    cudaStream_t st = h->stream;
+    k_undistort<<<dim3((D.selStride + 127) / 128, batch), 128, 0, st>>>(h->dKps, h->dNOut, D.selStride, P, h->dKpsUn);
+    KCHECK(h, "k_undistort");
+    CK(cudaGetLastError());
+    const cudaMemcpyKind kout = h->outSpace == ORBX_MEM_HOST ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice;
+    const int rows = std::min(cap, D.selStride);
+    if (rows > 0)
+        CK(cudaMemcpy2DAsync(kps_un, (size_t)cap * sizeof(orbx_kp), h->dKpsUn, (size_t)D.selStride * sizeof(orbx_kp),
+                             (size_t)rows * sizeof(orbx_kp), batch, kout, st));
+    CK(cudaStreamSynchronize(st));
+    return ORBX_OK;
 }
 
 /* Frames per pipeline chunk when a buffer lives in host memory (0 = default). */

@@ -393,6 +393,7 @@ __global__ void k_quadtree(const DevPlan* __restrict__ P, const u64* __restrict_
 
 // ------------------------------------------------------------------------------------------------ K5 orientation + descriptor
 #include "orbx_desc.cuh"
+#include "orbx_prep.cuh"
 
 // ------------------------------------------------------------------------------------------------ K6 export
 // Copy one level of one frame into a dense (w+2e) x (h+2e) buffer with the BORDER_REFLECT_101 frame (e may be 0).

@@ -42,6 +42,8 @@ class ORBextractor:
         self._in_space = self._out_space = _lib.MEM_HOST
         self._last = None
         self._pending = None
+        self._channels = 1
+        self._out_size = None
 
     def close(self):
         if getattr(self, "_h", None) and self._h.value:
@@ -83,6 +85,40 @@ class ORBextractor:
         """Frames per pipeline chunk of the host-buffer path (0 = library default)."""
         _lib.check(self._L.orbx_set_chunk(self._h, int(frames)))
 
+    # --- upstream image prep fused into the ingest (cvtColor, remap; src/Tracking.cc:269-294, stereo_euroc.cc:136) -----
+    _FORMATS = {"gray": _lib.FMT_GRAY8, "rgb": _lib.FMT_RGB8, "bgr": _lib.FMT_BGR8, "rgba": _lib.FMT_RGBA8,
+                "bgra": _lib.FMT_BGRA8}
+
+    def set_input_format(self, fmt):
+        """'gray' (default), 'rgb', 'bgr', 'rgba', 'bgra': images are then [.., H, W, C] and are converted like
+        cv::cvtColor(.., COLOR_x2GRAY) on the device."""
+        _lib.check(self._L.orbx_set_input_format(self._h, self._FORMATS[fmt]))
+        self._channels = 1 if fmt == "gray" else (3 if fmt in ("rgb", "bgr") else 4)
+
+    def set_rectify_maps(self, map_x, map_y):
+        """Maps of cv::initUndistortRectifyMap(.., CV_32F): every image is remapped (INTER_LINEAR) on the device before
+        extraction; None, None switches it off."""
+        if map_x is None:
+            _lib.check(self._L.orbx_set_rectify_maps(self._h, None, None, 0, 0))
+            self._out_size = None
+            return
+        mx, my = np.ascontiguousarray(map_x, np.float32), np.ascontiguousarray(map_y, np.float32)
+        assert mx.ndim == 2 and mx.shape == my.shape
+        _lib.check(self._L.orbx_set_rectify_maps(self._h, mx.ctypes.data, my.ctypes.data, mx.shape[1], mx.shape[0]))
+        self._out_size = (mx.shape[1], mx.shape[0])
+
+    def undistort_keypoints(self, K4, dist, cap=None):
+        """Frame::UndistortKeyPoints for the last batch: returns mvKeysUn as [B, cap] KP_DTYPE (host)."""
+        B, W, H = self._last
+        cap = cap or self.max_keypoints(W, H)
+        K4 = np.ascontiguousarray(K4, np.float32)
+        dist = np.ascontiguousarray(dist, np.float32).ravel()
+        out = np.zeros((B, cap), KP_DTYPE)
+        self._set_space(self._in_space, _lib.MEM_HOST)
+        _lib.check(self._L.orbx_undistort_keypoints(self._h, K4.ctypes.data, dist.ctypes.data if len(dist) else None,
+                                                    len(dist), out.ctypes.data, cap))
+        return out
+
     def _set_space(self, i, o):
         if (i, o) != (self._in_space, self._out_space):
             _lib.check(self._L.orbx_set_memory_space(self._h, i, o))
@@ -94,28 +130,38 @@ class ORBextractor:
         image = np.asarray(image)
         if image.size == 0:
             return np.zeros(0, KP_DTYPE), np.zeros((0, 32), np.uint8)
-        assert image.dtype == np.uint8 and image.ndim == 2, "CV_8UC1 image required"
+        assert image.dtype == np.uint8 and image.ndim == (2 if self._channels == 1 else 3), "CV_8UC1 image required"
         k, d, n = self.extract_batch(image[None])
         return k[0, :n[0]].copy(), d[0, :n[0]].copy()
 
     def extract_batch(self, images, out=None):
-        """images: [B,H,W] uint8 numpy array (host, any row stride) or torch CUDA tensor (device).
-        Returns (kps [B,cap], desc [B,cap,32], n [B]) in the same memory space as the input (n always numpy)."""
+        """images: [B,H,W] uint8 ([B,H,W,C] with a colour input format) numpy array (host, any row stride) or torch CUDA
+        tensor (device). Returns (kps [B,cap], desc [B,cap,32], n [B]) in the same memory space as the input (n always
+        numpy)."""
         if _is_torch(images):
             return self._extract_batch_torch(images, out)
-        assert images.dtype == np.uint8 and images.ndim == 3
-        B, H, W = images.shape
-        if images.strides[2] != 1 or images.strides[1] < W or (B > 1 and images.strides[0] < images.strides[1] * H):
+        C_ = self._channels
+        assert images.dtype == np.uint8 and images.ndim == (3 if C_ == 1 else 4)
+        if C_ > 1:
+            assert images.shape[3] == C_
             images = np.ascontiguousarray(images)
-        cap = self.max_keypoints(W, H)
+            B, H, W = images.shape[:3]
+            row, frame = W * C_, H * W * C_
+        else:
+            B, H, W = images.shape
+            if images.strides[2] != 1 or images.strides[1] < W or (B > 1 and images.strides[0] < images.strides[1] * H):
+                images = np.ascontiguousarray(images)
+            row, frame = images.strides[1], images.strides[0]
+        oW, oH = self._out_size or (W, H)
+        cap = self.max_keypoints(oW, oH)
         if out is None:
             out = (np.zeros((B, cap), KP_DTYPE), np.zeros((B, cap, 32), np.uint8))
         kps, desc = out
         n = np.zeros(B, np.int32)
         self._set_space(_lib.MEM_HOST, _lib.MEM_HOST)
-        _lib.check(self._L.orbx_extract_batch(self._h, images.ctypes.data, B, W, H, images.strides[1], images.strides[0],
+        _lib.check(self._L.orbx_extract_batch(self._h, images.ctypes.data, B, W, H, row, frame,
                                               kps.ctypes.data, desc.ctypes.data, cap, n.ctypes.data))
-        self._last = (B, W, H)
+        self._last = (B, oW, oH)
         return kps, desc, n
 
     def submit_batch(self, images, out):
@@ -144,10 +190,12 @@ class ORBextractor:
 
     def _extract_batch_torch(self, images, out=None):
         import torch
-        assert images.is_cuda and images.dtype == torch.uint8 and images.dim() == 3 and images.is_contiguous()
+        C_ = self._channels
+        assert images.is_cuda and images.dtype == torch.uint8 and images.dim() == (3 if C_ == 1 else 4) and images.is_contiguous()
         assert images.device.index == self.device
-        B, H, W = images.shape
-        cap = self.max_keypoints(W, H)
+        B, H, W = images.shape[:3]
+        oW, oH = self._out_size or (W, H)
+        cap = self.max_keypoints(oW, oH)
         if out is None:
             out = (torch.empty((B, cap, 7), dtype=torch.float32, device=images.device),
                    torch.empty((B, cap, 32), dtype=torch.uint8, device=images.device))
@@ -155,9 +203,9 @@ class ORBextractor:
         n = np.zeros(B, np.int32)
         self._set_space(_lib.MEM_DEVICE, _lib.MEM_DEVICE)
         torch.cuda.current_stream(images.device).synchronize()
-        _lib.check(self._L.orbx_extract_batch(self._h, images.data_ptr(), B, W, H, W, W * H, kps.data_ptr(),
+        _lib.check(self._L.orbx_extract_batch(self._h, images.data_ptr(), B, W, H, W * C_, W * H * C_, kps.data_ptr(),
                                               desc.data_ptr(), cap, n.ctypes.data))
-        self._last = (B, W, H)
+        self._last = (B, oW, oH)
         return kps, desc, n
 
     # --- mvImagePyramid ---------------------------------------------------------------------------------------------
