@@ -8,6 +8,7 @@
 #ifndef ORBX_DROPIN_ORBEXTRACTOR_H
 #define ORBX_DROPIN_ORBEXTRACTOR_H
 
+#include <algorithm>
 #include <cassert>
 #include <cstring>
 #include <stdexcept>
@@ -55,15 +56,16 @@ public:
                     cv::OutputArray _descriptors) {
         if (_image.empty()) return;  // outputs untouched (:861-862)
         cv::Mat image = _image.getMat();
-        assert(image.type() == CV_8UC1);
+        assert(inputFormat_ != ORBX_FMT_GRAY8 || image.type() == CV_8UC1);
         int cap = 0;
-        check(orbx_max_keypoints(h_, image.cols, image.rows, &cap), "orbx_max_keypoints");
+        check(orbx_max_keypoints(h_, outW_ ? outW_ : image.cols, outW_ ? outH_ : image.rows, &cap), "orbx_max_keypoints");
         static_assert(sizeof(cv::KeyPoint) == sizeof(orbx_kp), "cv::KeyPoint must be 28 bytes");
         kp_.resize(cap);
         desc_.resize((size_t)cap * 32);
         int n = 0;
         check(orbx_extract(h_, image.data, image.cols, image.rows, image.step, kp_.data(), desc_.data(), cap, &n),
               "orbx_extract");
+        lastN_ = n;
         _keypoints.clear();
         if (n == 0) {
             _descriptors.release();
@@ -75,6 +77,38 @@ public:
             std::memcpy((void*)_keypoints.data(), kp_.data(), (size_t)n * sizeof(orbx_kp));
         }
         if (keepHostPyramid) refreshPyramid();
+    }
+
+    // ---- upstream image prep on the device (what Tracking::GrabImage* and the EuRoC replay do before this call) ----
+    // Colour images: pass the CV_8UC3 / CV_8UC4 frame to operator() instead of calling cv::cvtColor first
+    // (src/Tracking.cc:269-294, 308-321, 337-350); fmt = ORBX_FMT_{RGB8,BGR8,RGBA8,BGRA8} chosen from mbRGB / channels().
+    void SetInputFormat(int fmt) {
+        check(orbx_set_input_format(h_, fmt), "orbx_set_input_format");
+        inputFormat_ = fmt;
+    }
+    // Unrectified images: hand over M1, M2 of cv::initUndistortRectifyMap(.., CV_32F, M1, M2) once and pass the raw
+    // frames; replaces cv::remap(im, imRect, M1, M2, cv::INTER_LINEAR) (Test/Replay/Stereo/stereo_euroc.cc:136-137).
+    void SetRectifyMaps(const cv::Mat& M1, const cv::Mat& M2) {
+        if (M1.empty()) {
+            check(orbx_set_rectify_maps(h_, nullptr, nullptr, 0, 0), "orbx_set_rectify_maps");
+            outW_ = outH_ = 0;
+            return;
+        }
+        cv::Mat a = M1.clone(), b = M2.clone();  // continuous rows
+        check(orbx_set_rectify_maps(h_, (const float*)a.data, (const float*)b.data, M1.cols, M1.rows), "orbx_set_rectify_maps");
+        outW_ = M1.cols;
+        outH_ = M1.rows;
+    }
+    // Frame::UndistortKeyPoints (src/Frame.cc:402-432) for the keypoints of the last operator() call.
+    void UndistortKeyPoints(const cv::Mat& K, const cv::Mat& distCoef, std::vector<cv::KeyPoint>& keysUn) {
+        const float K4[4] = {K.at<float>(0, 0), K.at<float>(1, 1), K.at<float>(0, 2), K.at<float>(1, 2)};
+        float d[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        const int nd = std::min(8, distCoef.rows * distCoef.cols);
+        for (int i = 0; i < nd; i++) d[i] = distCoef.rows > 1 ? distCoef.at<float>(i, 0) : distCoef.at<float>(0, i);
+        std::vector<orbx_kp> un(kp_.size());
+        check(orbx_undistort_keypoints(h_, K4, d, nd, un.data(), (int)un.size()), "orbx_undistort_keypoints");
+        keysUn.resize(lastN_);
+        if (lastN_) std::memcpy((void*)keysUn.data(), un.data(), (size_t)lastN_ * sizeof(orbx_kp));
     }
 
     int inline GetLevels() { return nlevels; }
@@ -108,6 +142,7 @@ protected:
         if (rc != ORBX_OK) throw std::runtime_error(std::string(what) + ": " + orbx_last_error_string());
     }
 
+    int inputFormat_ = ORBX_FMT_GRAY8, outW_ = 0, outH_ = 0, lastN_ = 0;
     int nfeatures;
     double scaleFactor;
     int nlevels;

@@ -497,17 +497,18 @@ static int copy_in(orbx_handle* h, cudaStream_t cs, const uint8_t* imgs, int f0,
             uint8_t* g = h->dMapX ? h->dGray + (size_t)f0 * hgt * w : dst;
             const int gPitch = h->dMapX ? w : L0.pitch;
             const long long gFrame = h->dMapX ? (long long)hgt * w : L0.frameStride;
-            k_cvt_gray<<<dim3((w + 255) / 256, hgt, nb), 64, 0, cs>>>(src, sStride, sImg, ch,
-                                                                      h->inFmt == ORBX_FMT_BGR8 || h->inFmt == ORBX_FMT_BGRA8,
-                                                                      w, g, gPitch, gFrame);
+            const size_t al = ch == 3 ? 3 : 15;
+            const int wide = (((size_t)src | sStride | sImg) & al) == 0;
+            k_cvt_gray<<<dim3((w + 255) / 256, (hgt + 3) / 4, nb), dim3(64, 4), 0, cs>>>(
+                src, sStride, sImg, ch, h->inFmt == ORBX_FMT_BGR8 || h->inFmt == ORBX_FMT_BGRA8, wide, w, hgt, g, gPitch, gFrame);
             KCHECK(h, "k_cvt_gray");
             src = g;
             sStride = (size_t)w;
             sImg = (size_t)hgt * w;
         }
         if (h->dMapX) {
-            k_remap<<<dim3((L0.w + 127) / 128, L0.h, nb), 128, 0, cs>>>(src, sStride, sImg, w, hgt, h->dMapX, h->dMapY, L0.w,
-                                                                        dst, L0.pitch, L0.frameStride);
+            k_remap<<<dim3((L0.w + 127) / 128, (L0.h + 1) / 2, (nb + REMAP_FRAMES - 1) / REMAP_FRAMES), dim3(128, 2), 0, cs>>>(
+                src, sStride, sImg, w, hgt, h->dMapX, h->dMapY, L0.w, L0.h, nb, dst, L0.pitch, L0.frameStride);
             KCHECK(h, "k_remap");
         }
         return ORBX_OK;

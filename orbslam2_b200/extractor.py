@@ -171,15 +171,17 @@ class ORBextractor:
         def view(a):
             return a.numpy() if _is_torch(a) else a
         images, kps, desc = view(images), view(out[0]), view(out[1])
-        assert images.dtype == np.uint8 and images.ndim == 3 and images.strides[2] == 1
-        B, H, W = images.shape
+        C_ = self._channels
+        assert images.dtype == np.uint8 and images.ndim == (3 if C_ == 1 else 4) and images.strides[-1] == 1
+        assert C_ == 1 or (images.shape[3] == C_ and images.strides[2] == C_)
+        B, H, W = images.shape[:3]
         cap = desc.shape[1]
         assert desc.shape == (B, cap, 32) and kps.shape[:2] == (B, cap) and kps.nbytes == B * cap * 28
         self._set_space(_lib.MEM_HOST, _lib.MEM_HOST)
         _lib.check(self._L.orbx_extract_batch_submit(self._h, images.ctypes.data, B, W, H, images.strides[1],
                                                      images.strides[0], kps.ctypes.data, desc.ctypes.data, cap))
         self._pending = (images, out, np.zeros(B, np.int32))
-        self._last = (B, W, H)
+        self._last = (B,) + (self._out_size or (W, H))
 
     def wait_batch(self):
         """Second half (orbx_extract_batch_wait): returns (kps, desc, n) of the submitted batch."""
@@ -321,8 +323,9 @@ class ExtractorRing:
         k = self._at
         self._at = (k + 1) % len(self.ex)
         done = self._finish(k) if self._busy[k] else None
-        B, H, W = images.shape
-        self.ex[k].submit_batch(images, self._buffers(k, B, self.ex[k].max_keypoints(W, H)))
+        B, H, W = images.shape[:3]
+        oW, oH = self.ex[k]._out_size or (W, H)
+        self.ex[k].submit_batch(images, self._buffers(k, B, self.ex[k].max_keypoints(oW, oH)))
         self._busy[k] = True
         return done
 

@@ -98,5 +98,11 @@ struct Frame {
     std::vector<bool> mvbOutlier;
 };
 int instantiate(ORB_SLAM2::ORBmatcher& m, Frame& cur, const Frame& last) { return m.SearchByProjection(cur, last, 15.f, false); }
+void instantiate_prep(ORB_SLAM2::ORBextractor& e, const cv::Mat& M1, const cv::Mat& M2, const cv::Mat& K, const cv::Mat& D,
+                      std::vector<cv::KeyPoint>& un) {
+    e.SetInputFormat(ORBX_FMT_BGR8);
+    e.SetRectifyMaps(M1, M2);
+    e.UndistortKeyPoints(K, D, un);
+}
 int instantiate2(ORB_SLAM2::ORBmatcher& m, Frame& F, const std::vector<MapPoint*>& v) { return m.SearchByProjection(F, v, 3.f); }
 }  // namespace dropin_check
