@@ -209,7 +209,71 @@ public:
         return nmatches;
     }
 
+    // ORBmatcher::SearchByFboW(KeyFrame* pKF, Frame& F, std::vector<MapPoint*>& vpMapPointMatches)
+    // (src/ORBmatcher.cc:157-283; TrackReferenceKeyFrame src/Tracking.cc:867, Relocalization :1476) on the device.
+    // FeatVecT is fbow::fBow2 (std::map<uint32_t, std::vector<uint32_t>>).
+    template <class KeyFrameT, class FrameT, class MapPointT>
+    int SearchByFboW(KeyFrameT* pKF, FrameT& F, std::vector<MapPointT*>& vpMapPointMatches) {
+        const std::vector<MapPointT*> vpMapPointsKF = pKF->GetMapPointMatches();
+        vpMapPointMatches = std::vector<MapPointT*>(F.N, static_cast<MapPointT*>(NULL));
+        const int nA = (int)vpMapPointsKF.size(), nB = F.N;
+        std::vector<uint8_t> elig(nA, 0);
+        std::vector<float> angA(nA), angB(nB);
+        for (int i = 0; i < nA; i++) {
+            elig[i] = vpMapPointsKF[i] && !vpMapPointsKF[i]->isBad();
+            angA[i] = pKF->mvKeysUn[i].angle;
+        }
+        for (int i = 0; i < nB; i++) angB[i] = F.mvKeys[i].angle;
+        BowCsr a(pKF->mFbowFeatVec), b(F.mFbowFeatVec);
+        orbm_bow_side A = {nA, elig.data(), angA.data(), pKF->mDescriptors.ptr(), (int)a.id.size(), a.id.data(), a.off.data(), a.feat.data()};
+        orbm_bow_side B = {nB, nullptr, angB.data(), F.mDescriptors.ptr(), (int)b.id.size(), b.id.data(), b.off.data(), b.feat.data()};
+        std::vector<int32_t> match(nA, -1);
+        int nmatches = 0;
+        check(orbm_search_by_bow(tls(), &A, &B, a.off.back(), b.off.back(), mfNNratio, TH_LOW, 0, mbCheckOrientation ? 1 : 0,
+                                 match.data(), &nmatches), "orbm_search_by_bow");
+        for (int i = 0; i < nA; i++)
+            if (match[i] >= 0) vpMapPointMatches[match[i]] = vpMapPointsKF[i];
+        return nmatches;
+    }
+
+    // ORBmatcher::SearchByFboW(KeyFrame* pKF1, KeyFrame* pKF2, std::vector<MapPoint*>& vpMatches12)
+    // (src/ORBmatcher.cc:517-650; LoopClosing::ComputeSim3 src/LoopClosing.cc:301) on the device.
+    template <class KeyFrameT, class MapPointT>
+    int SearchByFboW(KeyFrameT* pKF1, KeyFrameT* pKF2, std::vector<MapPointT*>& vpMatches12) {
+        const std::vector<MapPointT*> mp1 = pKF1->GetMapPointMatches(), mp2 = pKF2->GetMapPointMatches();
+        vpMatches12 = std::vector<MapPointT*>(mp1.size(), static_cast<MapPointT*>(NULL));
+        const int nA = (int)mp1.size(), nB = (int)mp2.size();
+        std::vector<uint8_t> e1(nA, 0), e2(nB, 0);
+        std::vector<float> angA(nA), angB(nB);
+        for (int i = 0; i < nA; i++) { e1[i] = mp1[i] && !mp1[i]->isBad(); angA[i] = pKF1->mvKeysUn[i].angle; }
+        for (int i = 0; i < nB; i++) { e2[i] = mp2[i] && !mp2[i]->isBad(); angB[i] = pKF2->mvKeysUn[i].angle; }
+        BowCsr a(pKF1->mFbowFeatVec), b(pKF2->mFbowFeatVec);
+        orbm_bow_side A = {nA, e1.data(), angA.data(), pKF1->mDescriptors.ptr(), (int)a.id.size(), a.id.data(), a.off.data(), a.feat.data()};
+        orbm_bow_side B = {nB, e2.data(), angB.data(), pKF2->mDescriptors.ptr(), (int)b.id.size(), b.id.data(), b.off.data(), b.feat.data()};
+        std::vector<int32_t> match(nA, -1);
+        int nmatches = 0;
+        check(orbm_search_by_bow(tls(), &A, &B, a.off.back(), b.off.back(), mfNNratio, TH_LOW, 1, mbCheckOrientation ? 1 : 0,
+                                 match.data(), &nmatches), "orbm_search_by_bow");
+        for (int i = 0; i < nA; i++)
+            if (match[i] >= 0) vpMatches12[i] = mp2[match[i]];
+        return nmatches;
+    }
+
 protected:
+    // std::map<node, vector<feature>> (fbow::fBow2) flattened to the CSR form of the C ABI
+    struct BowCsr {
+        std::vector<uint32_t> id, feat;
+        std::vector<int> off;
+        template <class FeatVecT>
+        explicit BowCsr(const FeatVecT& fv) {
+            off.push_back(0);
+            for (const auto& e : fv) {
+                id.push_back(e.first);
+                feat.insert(feat.end(), e.second.begin(), e.second.end());
+                off.push_back((int)feat.size());
+            }
+        }
+    };
     float mfNNratio;
     bool mbCheckOrientation;
 

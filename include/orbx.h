@@ -236,6 +236,29 @@ int orbx_set_profiling(orbx_t* h, int on);
 const char* orbx_last_error_string(void);
 const char* orbx_version(void);
 
+/* ORBmatcher::SearchByFboW, both overloads (include/ORBmatcher.h:54-55, 71): KeyFrame vs Frame
+ * (src/ORBmatcher.cc:157-283; Tracking::TrackReferenceKeyFrame / Relocalization) with strict = 0, th = TH_LOW, and
+ * KeyFrame vs KeyFrame (src/ORBmatcher.cc:517-650; LoopClosing) with strict = 1. A side is a frame's descriptors,
+ * keypoint angles and its feature vector mFbowFeatVec in the CSR form orbv_transform_batch returns (node ids ascending).
+ *   a (queries, KF / KF1): eligible[i] = vpMapPoints[i] && !isBad();   b: eligible = NULL (Frame: every feature is a
+ *   candidate) or vpMapPoints2[i] && !isBad() (KF2).
+ * match_a[i] = index in b matched to feature i of a after the rotation-histogram filter, else -1; the wrapper turns it
+ * into vpMapPointMatches[match_a[i]] = vpMapPointsKF[i] (KF,F) or vpMatches12[i] = vpMapPoints2[match_a[i]] (KF,KF).
+ * The "skip features already matched by an earlier query" rule is reproduced exactly (fixed point, see
+ * orbm_search_by_projection). n_pos_a / n_pos_b = node_off[n_nodes] of each side. */
+typedef struct {
+    int n;
+    const uint8_t* eligible; /* [n] */
+    const float* angle;      /* [n] mvKeysUn[i].angle (KF) / mvKeys[i].angle (Frame) */
+    const uint8_t* desc;     /* [n][32] */
+    int n_nodes;
+    const uint32_t* node_id; /* [n_nodes] ascending */
+    const int* node_off;     /* [n_nodes + 1] */
+    const uint32_t* node_feat;
+} orbm_bow_side;
+int orbm_search_by_bow(orbm_t* m, const orbm_bow_side* a, const orbm_bow_side* b, int n_pos_a, int n_pos_b, float nn_ratio,
+                       int th, int strict, int check_orientation, int32_t* match_a, int* nmatches);
+
 /* ---- vocabulary tree (bag of words): replaces fbow::Vocabulary as the reference uses it -------------------------------
  * (Thirdparty/fbow/src/fbow.h:51-125, fbow.cpp; called from Frame::ComputeFboW src/Frame.cc:395-400 and
  * KeyFrame::ComputeFboW src/KeyFrame.cc:62). */

@@ -1,0 +1,233 @@
+// orbx_bowsearch.cuh — device-resident ORBmatcher::SearchByFboW (included at the end of orbx_match.cu).
+//
+// Replaces /root/reference/src/ORBmatcher.cc:157-283 (KeyFrame vs Frame: TrackReferenceKeyFrame, Relocalization) and
+// :517-650 (KeyFrame vs KeyFrame: LoopClosing). Both walk the two feature vectors (fBow2: node -> feature indices) in
+// node order; for every eligible feature of side A in a common node they scan side B's features of the same node with
+// the best / second-best rule, skip B features already matched by an EARLIER A feature, accept on
+// `best <= th` (`<` for KF-KF) and `(float)best < ratio * (float)second`, then filter by the rotation histogram.
+//
+// The sequential "already matched" dependence is resolved as in orbx_search.cuh: a fixed point over rounds in which
+// every query replays its scan while skipping candidates claimed in the previous round by a query of lower rank
+// (rank = position in A's feature vector = the reference's visiting order). By induction on the rank the fixed point is
+// the sequential result. Node lists are short, so a thread per query computes its Hamming distances on the fly.
+#pragma once
+
+struct BowDev {
+    int nA, nB, nPosA;                // features; entries of A's feature vector
+    const uint8_t *eligA, *eligB;     // eligB may be NULL (every B feature is a candidate)
+    const float *angA, *angB;
+    const uint4 *descA, *descB;
+    int nNodesA, nNodesB;
+    const uint32_t *nodeIdA, *nodeIdB, *featA, *featB;
+    const int *offA, *offB;
+    float nnRatio;
+    int th, strict, checkOri;
+};
+
+// per entry p of A's feature vector: the matching node of B (or -1), found once
+__global__ void k_bow_pair_nodes(BowDev S, int* __restrict__ posNodeB) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;  // node of A
+    if (j >= S.nNodesA) return;
+    const uint32_t id = S.nodeIdA[j];
+    int lo = 0, hi = S.nNodesB - 1, hit = -1;
+    while (lo <= hi) {
+        const int mid = (lo + hi) >> 1;
+        const uint32_t v = S.nodeIdB[mid];
+        if (v == id) { hit = mid; break; }
+        if (v < id) lo = mid + 1; else hi = mid - 1;
+    }
+    for (int p = S.offA[j]; p < S.offA[j + 1]; p++) posNodeB[p] = hit;
+}
+
+__global__ void k_bow_claim(BowDev S, const int* __restrict__ choice, int* __restrict__ owner, const int* __restrict__ flag,
+                            int round) {
+    if (round > 0 && flag[round - 1] == 0) return;
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= S.nPosA) return;
+    const int c = choice[p];
+    if (c >= 0) atomicMin(&owner[c], p);
+}
+
+__global__ void __launch_bounds__(128) k_bow_choose(BowDev S, const int* __restrict__ posNodeB, int* __restrict__ choice,
+                                                    const int* __restrict__ owner, int* __restrict__ flag, int round) {
+    if (round > 0 && flag[round - 1] == 0) return;
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= S.nPosA) return;
+    int nc = -1;
+    const int jb = posNodeB[p];
+    const uint32_t ia = S.featA[p];
+    if (jb >= 0 && S.eligA[ia]) {
+        const uint4 a0 = S.descA[2 * (size_t)ia], a1 = S.descA[2 * (size_t)ia + 1];
+        int best1 = 256, best2 = 256, bestIdx = -1;
+        for (int c = S.offB[jb], e = S.offB[jb + 1]; c < e; c++) {
+            const uint32_t ib = S.featB[c];
+            if (owner[ib] < p) continue;                 // vpMapPointMatches[realIdxF] / vbMatched2[idx2] set earlier
+            if (S.eligB && !S.eligB[ib]) continue;       // !pMP2 || pMP2->isBad()
+            const int d = hamming256(a0, a1, S.descB[2 * (size_t)ib], S.descB[2 * (size_t)ib + 1]);
+            if (d < best1) { best2 = best1; best1 = d; bestIdx = (int)ib; }
+            else if (d < best2) best2 = d;
+        }
+        const bool in = S.strict ? best1 < S.th : best1 <= S.th;
+        if (in && (float)best1 < __fmul_rn(S.nnRatio, (float)best2)) nc = bestIdx;
+    }
+    if (nc != choice[p]) {
+        choice[p] = nc;
+        flag[round] = 1;
+    }
+}
+
+__global__ void __launch_bounds__(1024) k_bow_finish(BowDev S, const int* __restrict__ choice, int32_t* __restrict__ matchA,
+                                                     int* __restrict__ result) {
+    __shared__ int hist[SP_HISTO];
+    __shared__ int keepBin[SP_HISTO];
+    __shared__ int nKeep;
+    const int tid = threadIdx.x, T = blockDim.x;
+    if (tid < SP_HISTO) { hist[tid] = 0; keepBin[tid] = 1; }
+    if (tid == 0) nKeep = 0;
+    for (int i = tid; i < S.nA; i += T) matchA[i] = -1;
+    __syncthreads();
+    const float factor = 1.0f / SP_HISTO;
+    if (S.checkOri) {
+        for (int p = tid; p < S.nPosA; p += T) {
+            const int c = choice[p];
+            if (c < 0) continue;
+            float rot = __fsub_rn(S.angA[S.featA[p]], S.angB[c]);
+            if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
+            int bin = (int)roundf(__fmul_rn(rot, factor));
+            if (bin == SP_HISTO) bin = 0;
+            atomicAdd(&hist[bin], 1);
+        }
+        __syncthreads();
+        if (tid == 0) {  // ComputeThreeMaxima, src/ORBmatcher.cc:1597-1638
+            int max1 = 0, max2 = 0, max3 = 0, ind1 = -1, ind2 = -1, ind3 = -1;
+            for (int i = 0; i < SP_HISTO; i++) {
+                const int s = hist[i];
+                if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = i; }
+                else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = i; }
+                else if (s > max3) { max3 = s; ind3 = i; }
+            }
+            if ((float)max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
+            else if ((float)max3 < 0.1f * (float)max1) { ind3 = -1; }
+            for (int i = 0; i < SP_HISTO; i++) keepBin[i] = (i == ind1 || i == ind2 || i == ind3);
+        }
+        __syncthreads();
+    }
+    int mine = 0;
+    for (int p = tid; p < S.nPosA; p += T) {
+        const int c = choice[p];
+        if (c < 0) continue;
+        int keep = 1;
+        if (S.checkOri) {
+            float rot = __fsub_rn(S.angA[S.featA[p]], S.angB[c]);
+            if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
+            int bin = (int)roundf(__fmul_rn(rot, factor));
+            if (bin == SP_HISTO) bin = 0;
+            keep = keepBin[bin];
+        }
+        if (keep) { matchA[S.featA[p]] = c; mine++; }
+    }
+    if (mine) atomicAdd(&nKeep, mine);
+    __syncthreads();
+    if (tid == 0) result[0] = nKeep;
+}
+
+static int bow_side_ok(const orbm_bow_side* s) {
+    if (s->n < 0 || s->n_nodes < 0) return 0;
+    if (s->n && (!s->angle || !s->desc)) return 0;
+    if (s->n_nodes && (!s->node_id || !s->node_off || !s->node_feat)) return 0;
+    return 1;
+}
+
+extern "C" int orbm_search_by_bow(orbm_t* m, const orbm_bow_side* a, const orbm_bow_side* b, int n_pos_a, int n_pos_b,
+                                  float nn_ratio, int th, int strict, int check_orientation, int32_t* match_a,
+                                  int* nmatches) {
+    if (!m || !a || !b || !nmatches || (a->n && !match_a)) FAIL(ORBX_EINVAL, "null argument");
+    if (!bow_side_ok(a) || !bow_side_ok(b) || (a->n && !a->eligible) || n_pos_a < 0 || n_pos_b < 0) FAIL(ORBX_EINVAL, "bad feature-vector arrays");
+    *nmatches = 0;
+    CK(cudaSetDevice(m->device));
+    cudaStream_t st = m->stream;
+    const bool hin = m->inSpace == ORBX_MEM_HOST, hout = m->outSpace == ORBX_MEM_HOST;
+    const int nA = a->n, nB = b->n;
+    if (nA == 0) return ORBX_OK;
+    if (nB == 0 || a->n_nodes == 0 || b->n_nodes == 0 || n_pos_a == 0) {
+        if (hout) for (int i = 0; i < nA; i++) match_a[i] = -1;
+        else { CK(cudaMemsetAsync(match_a, 0xFF, (size_t)nA * 4, st)); CK(cudaStreamSynchronize(st)); }
+        return ORBX_OK;
+    }
+    const int maxRounds = n_pos_a + 8;
+    const size_t need = (size_t)nA * (1 + 4 + 32 + 4) + (size_t)nB * (1 + 4 + 32 + 4) + (size_t)(a->n_nodes + b->n_nodes) * 8 +
+                        (size_t)(n_pos_a + n_pos_b) * 4 + (size_t)n_pos_a * 8 + (size_t)maxRounds * 4 + 256 * 24;
+    int rc;
+    if ((rc = ensure(m->dWs, m->wsCap, need))) return rc;
+    if (!m->hRes) CK(cudaMallocHost(&m->hRes, 4 * sizeof(int)));
+    if (m->hFlagsCap < (size_t)maxRounds) {
+        if (m->hFlags) cudaFreeHost(m->hFlags);
+        m->hFlags = nullptr;
+        CK(cudaMallocHost(&m->hFlags, (size_t)maxRounds * sizeof(int)));
+        m->hFlagsCap = (size_t)maxRounds;
+    }
+    WsCursor W{m->dWs, 0};
+    auto in = [&](const void* src, size_t bytes) -> const void* {
+        if (!src) return nullptr;
+        if (!hin) return src;
+        uint8_t* d = W.take<uint8_t>(bytes);
+        cudaMemcpyAsync(d, src, bytes, cudaMemcpyHostToDevice, st);
+        return d;
+    };
+    BowDev S;
+    S.nA = nA; S.nB = nB; S.nPosA = n_pos_a;
+    S.eligA = (const uint8_t*)in(a->eligible, nA);
+    S.eligB = (const uint8_t*)in(b->eligible, nB);
+    S.angA = (const float*)in(a->angle, (size_t)nA * 4);
+    S.angB = (const float*)in(b->angle, (size_t)nB * 4);
+    S.descA = (const uint4*)in(a->desc, (size_t)nA * 32);
+    S.descB = (const uint4*)in(b->desc, (size_t)nB * 32);
+    S.nNodesA = a->n_nodes; S.nNodesB = b->n_nodes;
+    S.nodeIdA = (const uint32_t*)in(a->node_id, (size_t)a->n_nodes * 4);
+    S.nodeIdB = (const uint32_t*)in(b->node_id, (size_t)b->n_nodes * 4);
+    S.offA = (const int*)in(a->node_off, (size_t)(a->n_nodes + 1) * 4);
+    S.offB = (const int*)in(b->node_off, (size_t)(b->n_nodes + 1) * 4);
+    S.featA = (const uint32_t*)in(a->node_feat, (size_t)n_pos_a * 4);
+    S.featB = (const uint32_t*)in(b->node_feat, (size_t)n_pos_b * 4);
+    S.nnRatio = nn_ratio; S.th = th; S.strict = strict; S.checkOri = check_orientation;
+    if ((((uintptr_t)S.descA) | ((uintptr_t)S.descB)) & 15) FAIL(ORBX_EINVAL, "device descriptor matrices must be 16-byte aligned");
+    int* posNodeB = W.take<int>(n_pos_a);
+    int* choice = W.take<int>(n_pos_a);
+    int* owner = W.take<int>(nB);
+    int* flags = W.take<int>(maxRounds);
+    int* dRes = W.take<int>(4);
+    int32_t* oMatch = hout ? W.take<int32_t>(nA) : match_a;
+    if (W.off > m->wsCap) FAIL(ORBX_ECUDA, "internal: workspace estimate too small (%zu > %zu)", W.off, m->wsCap);
+
+    k_bow_pair_nodes<<<(a->n_nodes + 127) / 128, 128, 0, st>>>(S, posNodeB);
+    m->launches++;
+    CK(cudaMemsetAsync(choice, 0xFF, (size_t)n_pos_a * sizeof(int), st));
+    CK(cudaMemsetAsync(flags, 0, (size_t)maxRounds * sizeof(int), st));
+    int round = 0, rounds = 0;
+    for (;;) {
+        const int R = 4;
+        if (round + R > maxRounds) FAIL(ORBX_ECUDA, "internal: greedy resolution did not converge in %d rounds", maxRounds);
+        for (int r = 0; r < R; r++, round++) {
+            CK(cudaMemsetAsync(owner, 0x7F, (size_t)nB * sizeof(int), st));
+            k_bow_claim<<<(n_pos_a + 255) / 256, 256, 0, st>>>(S, choice, owner, flags, round);
+            k_bow_choose<<<(n_pos_a + 127) / 128, 128, 0, st>>>(S, posNodeB, choice, owner, flags, round);
+            m->launches += 2;
+        }
+        CK(cudaGetLastError());
+        CK(cudaMemcpyAsync(m->hFlags, flags, (size_t)round * sizeof(int), cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        rounds = 0;
+        while (rounds < round && m->hFlags[rounds]) rounds++;
+        if (rounds < round) break;
+    }
+    k_bow_finish<<<1, 1024, 0, st>>>(S, choice, oMatch, dRes);
+    m->launches++;
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(m->hRes, dRes, sizeof(int), cudaMemcpyDeviceToHost, st));
+    if (hout) CK(cudaMemcpyAsync(match_a, oMatch, (size_t)nA * 4, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    *nmatches = m->hRes[0];
+    m->lastRounds = rounds + 1;
+    m->lastCandidates = 0;
+    return ORBX_OK;
+}

@@ -873,6 +873,8 @@ extern "C" int orbm_distinctive_descriptors(orbm_t* m, const uint8_t* desc, cons
 }
 
 /* Diagnostics of the last orbm_search_by_projection call: fixed-point rounds and candidate pairs evaluated. */
+#include "orbx_bowsearch.cuh"
+
 extern "C" int orbm_search_stats(orbm_t* m, int* rounds, int64_t* candidates) {
     if (!m) FAIL(ORBX_EINVAL, "null handle");
     if (rounds) *rounds = m->lastRounds;

@@ -177,6 +177,43 @@ class ORBmatcher:
                                                     cm.ctypes.data, mm.ctypes.data, C.byref(n)))
         return n.value, cm, mm, P
 
+    # --- SearchByFboW (src/ORBmatcher.cc:157-283 KeyFrame vs Frame, :517-650 KeyFrame vs KeyFrame) -----------------------
+    @staticmethod
+    def bow_side(desc, angle, feat_vec, eligible=None):
+        """One frame for SearchByFboW: descriptors [n,32], keypoint angles [n], mFbowFeatVec as Vocabulary.transform returns
+        it ({node: feature indices}), and the per-feature "has a good map point" mask (None: every feature)."""
+        desc = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+        keys = sorted(feat_vec)
+        off = np.zeros(len(keys) + 1, np.int32)
+        off[1:] = np.cumsum([len(feat_vec[k]) for k in keys])
+        feat = (np.concatenate([np.asarray(feat_vec[k], np.uint32) for k in keys]) if keys else np.zeros(0, np.uint32))
+        return dict(n=len(desc), desc=desc, angle=np.ascontiguousarray(angle, np.float32),
+                    eligible=None if eligible is None else np.ascontiguousarray(eligible, np.uint8),
+                    node_id=np.array(keys, np.uint32), node_off=off, node_feat=np.ascontiguousarray(feat, np.uint32))
+
+    def SearchByFboW(self, a, b, strict=False, th=None):
+        """a: KeyFrame (queries; eligible = map point present and not bad), b: Frame (strict False) or second KeyFrame
+        (strict True, eligible = map point present and not bad). Returns (nmatches, match_a [a.n] int32: index in b or -1)."""
+        self._set_space(_lib.MEM_HOST, _lib.MEM_HOST)
+        keep = []
+
+        def side(d, need_elig):
+            elig = d["eligible"]
+            if elig is None and need_elig:
+                elig = np.ones(d["n"], np.uint8)
+            keep.append(elig)
+            return _lib.BowSide(d["n"], None if elig is None else elig.ctypes.data, d["angle"].ctypes.data,
+                                d["desc"].ctypes.data, len(d["node_id"]), d["node_id"].ctypes.data,
+                                d["node_off"].ctypes.data, d["node_feat"].ctypes.data)
+
+        A, B = side(a, True), side(b, False)
+        match = np.full(a["n"], -1, np.int32)
+        n = C.c_int()
+        _lib.check(self._L.orbm_search_by_bow(self._h, C.byref(A), C.byref(B), int(a["node_off"][-1]), int(b["node_off"][-1]),
+                                              float(self.mfNNratio), int(self.TH_LOW if th is None else th), int(strict),
+                                              int(self.mbCheckOrientation), match.ctypes.data, C.byref(n)))
+        return n.value, match
+
     @staticmethod
     def _mp_arrays(mps):
         f32 = lambda k: np.ascontiguousarray(mps[k], np.float32)

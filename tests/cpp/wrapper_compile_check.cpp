@@ -104,5 +104,15 @@ void instantiate_prep(ORB_SLAM2::ORBextractor& e, const cv::Mat& M1, const cv::M
     e.SetRectifyMaps(M1, M2);
     e.UndistortKeyPoints(K, D, un);
 }
+struct KeyFrame {
+    std::vector<cv::KeyPoint> mvKeysUn;
+    cv::Mat mDescriptors;
+    fbow::fBow2 mFbowFeatVec;
+    std::vector<MapPoint*> mps;
+    std::vector<MapPoint*> GetMapPointMatches() { return mps; }
+};
+struct BowFrame : Frame { fbow::fBow2 mFbowFeatVec; };
+int instantiate3(ORB_SLAM2::ORBmatcher& m, KeyFrame* kf, BowFrame& F, std::vector<MapPoint*>& out) { return m.SearchByFboW(kf, F, out); }
+int instantiate4(ORB_SLAM2::ORBmatcher& m, KeyFrame* a, KeyFrame* b, std::vector<MapPoint*>& out) { return m.SearchByFboW(a, b, out); }
 int instantiate2(ORB_SLAM2::ORBmatcher& m, Frame& F, const std::vector<MapPoint*>& v) { return m.SearchByProjection(F, v, 3.f); }
 }  // namespace dropin_check

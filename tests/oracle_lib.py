@@ -396,3 +396,25 @@ class OraclePrep:
         out = np.zeros_like(pts)
         self.L.orc_undistort_points(_p(pts), len(pts), fx, fy, cx, cy, _p(dist), len(dist), _p(out))
         return out
+
+
+def oracle_search_by_bow(a, b, nn_ratio, th, strict, check_ori):
+    """orc_search_by_bow over two ORBmatcher.bow_side dicts."""
+    build_oracle()
+    L = _load(ORACLE_SO)
+    L.orc_search_by_bow.restype = C.c_int
+    side = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.orc_search_by_bow.argtypes = side + side + [C.c_float, C.c_int, C.c_int, C.c_int, C.c_void_p]
+
+    def args(d, need):
+        e = d["eligible"]
+        if e is None and need:
+            e = np.ones(d["n"], np.uint8)
+        return [d["n"], None if e is None else _p(e), _p(d["angle"]), _p(d["desc"]), len(d["node_id"]), _p(d["node_id"]),
+                _p(d["node_off"]), _p(d["node_feat"])], e
+
+    aa, ka = args(a, True)
+    bb, kb = args(b, False)
+    match = np.full(a["n"], -1, np.int32)
+    n = L.orc_search_by_bow(*aa, *bb, np.float32(nn_ratio), th, int(strict), int(check_ori), _p(match))
+    return n, match

@@ -94,3 +94,55 @@ def test_vocabulary_blob_validation_needs_no_gpu():
     assert create(bad) == _lib.ORBX_EINVAL
     if not torch.cuda.is_available():
         assert create(blob) == _lib.ORBX_ECUDA
+
+
+# ---- oracle of ORBmatcher::SearchByFboW on hand-made cases with known answers ------------------------------------------
+def _side(desc, fv, elig=None, angle=None):
+    desc = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+    keys = sorted(fv)
+    off = np.zeros(len(keys) + 1, np.int32)
+    off[1:] = np.cumsum([len(fv[k]) for k in keys])
+    feat = np.concatenate([np.asarray(fv[k], np.uint32) for k in keys]) if keys else np.zeros(0, np.uint32)
+    return dict(n=len(desc), desc=desc, angle=np.zeros(len(desc), np.float32) if angle is None else np.asarray(angle, np.float32),
+                eligible=None if elig is None else np.asarray(elig, np.uint8), node_id=np.array(keys, np.uint32),
+                node_off=off, node_feat=np.ascontiguousarray(feat, np.uint32))
+
+
+def _with_bits(n):
+    d = np.zeros(32, np.uint8)
+    d[:n // 8] = 255
+    if n % 8:
+        d[n // 8] = (1 << (n % 8)) - 1
+    return d
+
+
+def test_search_by_bow_oracle_known_answers():
+    from oracle_lib import oracle_search_by_bow
+    z = _with_bits(0)
+    # B: distances 0, 10, 40 from the zero descriptor, one far away (200)
+    B = _side([_with_bits(0), _with_bits(10), _with_bits(40), _with_bits(200)], {3: [0, 1, 2], 5: [3]})
+    # A: two zero descriptors in node 3 (the 2nd finds B0 taken and falls back to B1: 10 < 0.7*40), one in node 4 (no
+    # such node in B), one ineligible
+    A = _side([z, z, z, z], {3: [0, 1, 3], 4: [2]}, elig=[1, 1, 1, 0])
+    n, m = oracle_search_by_bow(A, B, 0.7, 50, False, False)
+    assert n == 2 and m.tolist() == [0, 1, -1, -1]
+    # ratio test: best 10, second 12 -> rejected at 0.7, accepted at 0.9
+    B2 = _side([_with_bits(10), _with_bits(12)], {3: [0, 1]})
+    A2 = _side([z], {3: [0]}, elig=[1])
+    assert oracle_search_by_bow(A2, B2, 0.7, 50, False, False)[0] == 0
+    assert oracle_search_by_bow(A2, B2, 0.9, 50, False, False)[1].tolist() == [0]
+    # threshold: best == 50 passes `<=` (KF, F) and fails `<` (KF, KF)
+    B3 = _side([_with_bits(50)], {3: [0]})
+    assert oracle_search_by_bow(A2, B3, 0.9, 50, False, False)[0] == 1
+    assert oracle_search_by_bow(A2, _side([_with_bits(50)], {3: [0]}, elig=[1]), 0.9, 50, True, False)[0] == 0
+    # KF, KF: a candidate without a map point is invisible (neither best nor second)
+    B4 = _side([_with_bits(2), _with_bits(3)], {3: [0, 1]}, elig=[0, 1])
+    assert oracle_search_by_bow(A2, B4, 0.7, 50, True, False)[1].tolist() == [1]
+    # rotation filter: 12 matches at a 30 degree offset, one at 200 -> the lone bin is dropped (< 10 % of the peak)
+    nA = 13
+    dA = np.stack([_with_bits(8 * i) for i in range(nA)])          # mutually far apart (>= 8 bits)
+    ang_a = np.full(nA, 100, np.float32)
+    ang_b = np.full(nA, 70, np.float32); ang_b[12] = 260
+    fv = {i: [i] for i in range(nA)}
+    n, m = oracle_search_by_bow(_side(dA, fv, elig=np.ones(nA), angle=ang_a), _side(dA, fv, angle=ang_b), 0.9, 50, False, True)
+    assert n == 12 and m[12] == -1 and m[:12].tolist() == list(range(12))

@@ -104,3 +104,86 @@ def test_device_descriptors_from_extractor(ob):
     assert same(voc.transform(dh[1, :n[1]], 4), res[1])
     assert voc.launch_count() > 0
     ex.close(); voc.close()
+
+
+# ---- ORBmatcher::SearchByFboW on the device ---------------------------------------------------------------------------
+def _bow_frames(ob, voc, blob, n_a, n_b, seed, level=4, shared=0.7):
+    """two frames that see partly the same words: B's descriptors are A's with a few bits flipped (shuffled), plus
+    unrelated ones; keypoint angles consistent up to a common rotation + noise (so the rotation filter has a peak)."""
+    rng = np.random.default_rng(seed)
+    da = _features(blob, n_a, seed)
+    ns = int(min(n_a, n_b) * shared)
+    pick = rng.permutation(n_a)[:ns]
+    db = np.concatenate([da[pick], _features(blob, n_b - ns, seed + 1)])
+    bits = np.unpackbits(db[:ns], axis=1)
+    for _ in range(6):
+        bits[np.arange(ns), rng.integers(0, 256, ns)] ^= 1
+    db[:ns] = np.packbits(bits, axis=1)
+    perm = rng.permutation(n_b)
+    db = np.ascontiguousarray(db[perm])
+    ang_a = (rng.random(n_a) * 360).astype(np.float32)
+    ang_b = (rng.random(n_b) * 360).astype(np.float32)
+    src = np.full(n_b, -1); src[:ns] = pick; src = src[perm]
+    has = src >= 0
+    ang_b[has] = np.mod(ang_a[src[has]] - np.float32(25.0) + rng.normal(0, 3, has.sum()).astype(np.float32), 360).astype(np.float32)
+    wrong = rng.random(n_b) < 0.15
+    ang_b[wrong] = (rng.random(wrong.sum()) * 360).astype(np.float32)
+    return da, ang_a, None, db, ang_b, None
+
+
+@pytest.mark.parametrize("strict", [False, True])
+@pytest.mark.parametrize("level", [4, 2])
+def test_search_by_bow_vs_oracle(ob, strict, level):
+    from oracle_lib import oracle_search_by_bow
+    blob = synth_vocabulary(k=10, levels=5, seed=31)
+    voc = ob.Vocabulary(); voc.fromStream(blob)
+    rng = np.random.default_rng(7)
+    total = 0
+    for seed, (na, nb) in enumerate([(1000, 1100), (1500, 700), (300, 2000), (5, 5)]):
+        da, ang_a, _, db, ang_b, _ = _bow_frames(ob, voc, blob, na, nb, 40 + seed, level)
+        fa, fb = voc.transform(da, level)[1], voc.transform(db, level)[1]
+        elig_a = (rng.random(na) < 0.8).astype(np.uint8)
+        elig_b = (rng.random(nb) < 0.85).astype(np.uint8) if strict else None
+        A = ob.ORBmatcher.bow_side(da, ang_a, fa, elig_a)
+        B = ob.ORBmatcher.bow_side(db, ang_b, fb, elig_b)
+        for ratio, ori in ((0.7, True), (0.9, True), (0.75, False)):
+            m = ob.ORBmatcher(ratio, ori)
+            n, match = m.SearchByFboW(A, B, strict=strict)
+            en, ematch = oracle_search_by_bow(A, B, ratio, 50, strict, ori)
+            assert n == en and np.array_equal(match, ematch), (seed, ratio, ori)
+            total += n
+            m.close()
+    assert total > 500, "the synthetic frames must actually match"
+    voc.close()
+
+
+def test_search_by_bow_greedy_chain_and_empty(ob):
+    """Adversarial order dependence: every A feature's best candidate is the same B feature, so each query's result
+    depends on all earlier ones (the fixed point needs many rounds); and the empty / disjoint cases."""
+    from oracle_lib import oracle_search_by_bow
+    rng = np.random.default_rng(3)
+    n = 40
+    base = rng.integers(0, 256, 32, dtype=np.uint8)
+    # B: features at Hamming distance 0, 2, 4, ... from base (distinct); A: all equal to base, so query r takes B[r]
+    db = np.repeat(base[None], n, 0)
+    bits = np.unpackbits(db, axis=1)
+    for r in range(n):
+        bits[r, :2 * r] ^= 1
+    db = np.packbits(bits, axis=1)
+    da = np.repeat(base[None], n, 0)
+    fv_a = {7: np.arange(n, dtype=np.uint32)}
+    fv_b = {7: rng.permutation(n).astype(np.uint32)}
+    A = ob.ORBmatcher.bow_side(da, np.zeros(n, np.float32), fv_a, np.ones(n, np.uint8))
+    B = ob.ORBmatcher.bow_side(db, np.zeros(n, np.float32), fv_b, None)
+    m = ob.ORBmatcher(0.99, False)
+    got = m.SearchByFboW(A, B)
+    exp = oracle_search_by_bow(A, B, 0.99, 50, False, False)
+    assert got[0] == exp[0] and np.array_equal(got[1], exp[1]) and got[0] >= 10
+    rounds, _ = m.search_stats()
+    assert rounds > 4
+    # disjoint node sets and empty sides
+    B2 = ob.ORBmatcher.bow_side(db, np.zeros(n, np.float32), {9: np.arange(n, dtype=np.uint32)}, None)
+    assert m.SearchByFboW(A, B2)[0] == 0
+    E = ob.ORBmatcher.bow_side(np.zeros((0, 32), np.uint8), np.zeros(0, np.float32), {}, None)
+    assert m.SearchByFboW(A, E)[0] == 0 and m.SearchByFboW(E, B)[0] == 0
+    m.close()
