@@ -314,7 +314,7 @@ def run_ours(args):
     dev = torch.device("cuda", local)
     numa = bind_to_gpu_numa_node(local)  # before any pinned allocation: first touch places the staging buffers
     if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
+        dist.init_process_group("nccl", device_id=dev, timeout=__import__("datetime").timedelta(seconds=300))  # a stuck rank fails in minutes
 
     def barrier():
         if world > 1:
@@ -462,6 +462,7 @@ def run_ours(args):
     if rank == 0 and not args.no_cpu_baseline:
         cpu = cpu_baseline(frames, args.cpu_seconds)
     total_launches = int(sum_over_ranks(launches))
+    total_launches_ring = int(sum_over_ranks(launches_ring))  # collectives on every rank, never inside `if rank == 0`
     if rank == 0:
         out.emit(json.dumps({
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -476,7 +477,7 @@ def run_ours(args):
                     "api": "ExtractorRing.push: orbx_extract_batch_submit/_wait on %d handles (%d batches in flight), "
                            "host buffers, chunk %d" % (args.ring_depth, args.ring_depth, args.ring_chunk),
                     "single_call_value": e2e, "single_call_ms_per_step": t_e2e / args.steps * 1e3,
-                    "gpu_launches": int(sum_over_ranks(launches_ring)),
+                    "gpu_launches": total_launches_ring,
                     "h2d_copy_only_gbs_per_gpu": h2d_gbs,
                     "h2d_copy_only_frames_per_s": world * h2d_gbs * 1e9 / (W * H)},
             "gpu_launches": total_launches, "clocks": clocks, "host_affinity": numa, "roofline": roofline, "cpu_baseline": cpu,
