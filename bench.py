@@ -463,6 +463,7 @@ def run_ours(args):
         cpu = cpu_baseline(frames, args.cpu_seconds)
     total_launches = int(sum_over_ranks(launches))
     total_launches_ring = int(sum_over_ranks(launches_ring))  # collectives on every rank, never inside `if rank == 0`
+    total_launches_e2e = int(sum_over_ranks(launches_e2e))
     if rank == 0:
         out.emit(json.dumps({
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -472,12 +473,15 @@ def run_ours(args):
                        "levels": 8, "scale": 1.2, "fast": [20, 7], "keypoints_per_frame": n_out_mean,
                        "l2": "inputs larger than L2 (batch images + pyramids ~ %d MB per step)" %
                              ((B * (W * H + 2 * level_area_sum(W, H))) >> 20)},
-            "e2e": {"value": e2e_ring, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "ms_per_step": t_ring / args.steps * 1e3,
-                    "api": "ExtractorRing.push: orbx_extract_batch_submit/_wait on %d handles (%d batches in flight), "
-                           "host buffers, chunk %d" % (args.ring_depth, args.ring_depth, args.ring_chunk),
-                    "single_call_value": e2e, "single_call_ms_per_step": t_e2e / args.steps * 1e3,
-                    "gpu_launches": total_launches_ring,
+            # both ways of driving the C ABI with host buffers are measured; the headline is the faster one (on a box
+            # whose host link is the limit, e.g. 8 ranks behind one PCIe root, the ring cannot add anything)
+            "e2e": {"value": max(e2e_ring, e2e), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "ms_per_step": min(t_ring, t_e2e) / args.steps * 1e3,
+                    "api": ("ExtractorRing.push: orbx_extract_batch_submit/_wait on %d handles (%d batches in flight), "
+                            "host buffers, chunk %d" % (args.ring_depth, args.ring_depth, args.ring_chunk))
+                           if e2e_ring >= e2e else "one blocking orbx_extract_batch per step, host buffers",
+                    "ring_value": e2e_ring, "single_call_value": e2e,
+                    "gpu_launches": total_launches_ring if e2e_ring >= e2e else total_launches_e2e,
                     "h2d_copy_only_gbs_per_gpu": h2d_gbs,
                     "h2d_copy_only_frames_per_s": world * h2d_gbs * 1e9 / (W * H)},
             "gpu_launches": total_launches, "clocks": clocks, "host_affinity": numa, "roofline": roofline, "cpu_baseline": cpu,
