@@ -51,9 +51,17 @@ struct orbx_handle {
     uint8_t* dExport = nullptr;
     size_t exportBytes = 0;
     int* hCounts = nullptr;  // pinned: [batch] nOut + [1] err
+    uint8_t* dOutBlock = nullptr;  // [dKps | dDesc | dNOut | dErr]
+    size_t outBlockBytes = 0;
+    uint8_t* hStage = nullptr;     // pinned mirror of the block (plans with batch == 1)
     int qtC = 0, qtC2 = 0, qtThreads = 256;
     size_t qtSmem = 0, fastSmem = 0;
     int lastBatch = 0;
+    cudaStream_t sSide = nullptr;  // small batches: blur beside FAST + quadtree
+    cudaEvent_t evFork = nullptr, evJoin = nullptr;
+    bool pendingOneCopy = false;
+    orbx_kp* pendingKps = nullptr;
+    uint8_t* pendingDesc = nullptr;
     int pendingBatch = 0, pendingCap = 0;  // orbx_extract_batch_submit without its wait (negative: empty-image batch)
     bool blurValid = false;
     int64_t launches = 0;
@@ -153,9 +161,11 @@ static PFN_encodeTiled get_encode() {
 
 static void free_plan(orbx_handle* h) {
     cudaFree(h->dPlan); cudaFree(h->dPyr); cudaFree(h->dBlur); cudaFree(h->dTabs); cudaFree(h->dCand);
-    cudaFree(h->dNodeOf); cudaFree(h->dCandCount); cudaFree(h->dSel); cudaFree(h->dSelCount); cudaFree(h->dKps);
-    cudaFree(h->dDesc); cudaFree(h->dNOut); cudaFree(h->dExport);
+    cudaFree(h->dNodeOf); cudaFree(h->dCandCount); cudaFree(h->dSel); cudaFree(h->dSelCount); cudaFree(h->dOutBlock);
+    cudaFree(h->dExport);
     if (h->hCounts) cudaFreeHost(h->hCounts);
+    if (h->hStage) cudaFreeHost(h->hStage);
+    h->hStage = nullptr; h->dOutBlock = nullptr; h->dErr = nullptr;
     h->dPlan = nullptr; h->dPyr = h->dBlur = nullptr; h->dTabs = nullptr; h->dCand = nullptr; h->dNodeOf = nullptr;
     h->dCandCount = nullptr; h->dSel = nullptr; h->dSelCount = nullptr; h->dKps = nullptr; h->dDesc = nullptr;
     h->dNOut = nullptr; h->dExport = nullptr; h->exportBytes = 0; h->hCounts = nullptr;
@@ -264,10 +274,18 @@ static int build_plan(orbx_handle* h, int w, int hgt, int batch) {
     CK(cudaMalloc(&h->dCandCount, (size_t)batch * p.nlevels * sizeof(int)));
     CK(cudaMalloc(&h->dSelCount, (size_t)batch * p.nlevels * sizeof(int)));
     CK(cudaMalloc(&h->dSel, (size_t)batch * D.selStride * sizeof(uint2)));
-    CK(cudaMalloc(&h->dKps, (size_t)batch * D.selStride * sizeof(orbx_kp)));
-    CK(cudaMalloc(&h->dDesc, (size_t)batch * D.selStride * 32));
-    CK(cudaMalloc(&h->dNOut, (size_t)batch * sizeof(int)));
+    // results live in ONE block [keypoints | descriptors | nOut[batch] | error flag] so that counts + flag are one
+    // device->host copy and a single frame's whole result is one copy (single-frame latency)
+    const size_t kpBytes = (size_t)batch * D.selStride * sizeof(orbx_kp), dsBytes = (size_t)batch * D.selStride * 32;
+    h->outBlockBytes = kpBytes + dsBytes + (size_t)(batch + 1) * sizeof(int);
+    CK(cudaMalloc(&h->dOutBlock, h->outBlockBytes));
+    h->dKps = (orbx_kp*)h->dOutBlock;
+    h->dDesc = h->dOutBlock + kpBytes;
+    h->dNOut = (int*)(h->dOutBlock + kpBytes + dsBytes);
+    h->dErr = h->dNOut + batch;
+    CK(cudaMemsetAsync(h->dErr, 0, sizeof(int), h->stream));
     CK(cudaMallocHost(&h->hCounts, (size_t)(batch + 1) * sizeof(int)));
+    if (batch == 1) CK(cudaMallocHost(&h->hStage, h->outBlockBytes));
     CK(cudaMemcpyAsync(h->dPlan, &D, sizeof(DevPlan), cudaMemcpyHostToDevice, h->stream));
     if (!tabs.empty())
         CK(cudaMemcpyAsync(h->dTabs, tabs.data(), tabs.size() * sizeof(int2), cudaMemcpyHostToDevice, h->stream));
@@ -325,8 +343,6 @@ extern "C" int orbx_create(const orbx_params* p, int device, orbx_t** out) {
         FAIL(ORBX_ECUDA, "cudaStreamCreate: %s", cudaGetErrorString(e));
     }
     for (int i = 0; i < 8; i++) cudaEventCreate(&h->ev[i]);
-    cudaMalloc(&h->dErr, sizeof(int));
-    cudaMemset(h->dErr, 0, sizeof(int));
     cudaMemcpyToSymbol(d_pattern, kOrbPattern, 1024);
     *out = h;
     return ORBX_OK;
@@ -337,7 +353,6 @@ extern "C" int orbx_destroy(orbx_t* h) {
     cudaSetDevice(h->device);
     cudaStreamSynchronize(h->stream);
     free_plan(h);
-    cudaFree(h->dErr);
     for (int i = 0; i < 8; i++) cudaEventDestroy(h->ev[i]);
     for (cudaEvent_t e : h->evIn) cudaEventDestroy(e);
     for (cudaEvent_t e : h->evComp) cudaEventDestroy(e);
@@ -350,6 +365,11 @@ extern "C" int orbx_destroy(orbx_t* h) {
         cudaStreamDestroy(h->sComp[1]);
     }
     cudaFree(h->dMapX); cudaFree(h->dMapY); cudaFree(h->dRaw); cudaFree(h->dGray); cudaFree(h->dKpsUn);
+    if (h->sSide) {
+        cudaEventDestroy(h->evFork);
+        cudaEventDestroy(h->evJoin);
+        cudaStreamDestroy(h->sSide);
+    }
     cudaStreamDestroy(h->stream);
     delete h;
     return ORBX_OK;
@@ -428,16 +448,36 @@ static int launch_chain(orbx_handle* h, cudaStream_t cs, int f0, int nb, bool st
         KCHECK(h, "k_resize");
     }
     if (stamps) stamp(h, 2);
+    // a few frames do not fill the GPU: the blur (it reads only the pyramid) then runs on a side stream next to FAST and
+    // the quadtree and joins before the descriptors. (For large batches this was measured: no gain, FAST fills every SM.)
+    const bool fork = nb <= 4 && !stamps && cs == h->stream;
+    if (fork) {
+        if (!h->sSide) {
+            CK(cudaStreamCreateWithFlags(&h->sSide, cudaStreamNonBlocking));
+            CK(cudaEventCreateWithFlags(&h->evFork, cudaEventDisableTiming));
+            CK(cudaEventCreateWithFlags(&h->evJoin, cudaEventDisableTiming));
+        }
+        CK(cudaEventRecord(h->evFork, cs));
+        CK(cudaStreamWaitEvent(h->sSide, h->evFork, 0));
+        k_blur<<<dim3((D.totalBlurTiles + BLUR_WARPS - 1) / BLUR_WARPS, nb), 32 * BLUR_WARPS, 0, h->sSide>>>(h->dPlan, h->dPyr, h->dBlur, f0);
+        KCHECK(h, "k_blur");
+        CK(cudaEventRecord(h->evJoin, h->sSide));
+    }
     k_fast<<<dim3(D.totalSt, nb), FAST_THREADS, h->fastSmem, cs>>>(h->maps, h->dPlan, h->dCand, h->dCandCount, h->dErr, f0);
     KCHECK(h, "k_fast");
     if (stamps) stamp(h, 3);
-    k_quadtree<<<dim3(nl, nb), h->qtThreads, h->qtSmem, cs>>>(h->dPlan, h->dCand, h->dCandCount, h->dNodeOf, h->dSel,
+    // a few frames: one CTA per level is all the parallelism there is, so give it the widest CTA
+    // (measured, single 640x480 / 1241x376 frame: 256 thr 160 / 278 us per call, 512 thr 155 / 220, 1024 thr 160 / 215)
+    k_quadtree<<<dim3(nl, nb), nb <= 4 ? std::max(512, h->qtThreads) : h->qtThreads, h->qtSmem, cs>>>(h->dPlan, h->dCand, h->dCandCount, h->dNodeOf, h->dSel,
                                                              h->dSelCount, h->qtC, h->qtC2, h->dErr, f0);
     KCHECK(h, "k_quadtree");
     if (stamps) stamp(h, 4);
-    // (running the blur on a side stream next to FAST + quadtree was measured: no gain, FAST fills every SM)
-    k_blur<<<dim3((D.totalBlurTiles + BLUR_WARPS - 1) / BLUR_WARPS, nb), 32 * BLUR_WARPS, 0, cs>>>(h->dPlan, h->dPyr, h->dBlur, f0);
-    KCHECK(h, "k_blur");
+    if (fork) {
+        CK(cudaStreamWaitEvent(cs, h->evJoin, 0));
+    } else {
+        k_blur<<<dim3((D.totalBlurTiles + BLUR_WARPS - 1) / BLUR_WARPS, nb), 32 * BLUR_WARPS, 0, cs>>>(h->dPlan, h->dPyr, h->dBlur, f0);
+        KCHECK(h, "k_blur");
+    }
     if (stamps) stamp(h, 5);
     k_orient_desc<<<dim3((D.selStride + 8 * DESC_KPW - 1) / (8 * DESC_KPW), nb), 256, 0, cs>>>(
         h->dPlan, h->dPyr, h->dBlur, h->dSel, h->dSelCount, h->dKps, h->dDesc, h->dNOut, f0);
@@ -613,6 +653,12 @@ extern "C" int orbx_extract_batch_submit(orbx_t* h, const uint8_t* imgs, int bat
 
     stamp(h, 0);
     CK(cudaMemsetAsync(h->dCandCount, 0, (size_t)batch * nl * sizeof(int), st));
+    // single frame to host memory: the whole result block (keypoints, descriptors, count, error flag) leaves in one
+    // copy into a pinned mirror; orbx_extract_batch_wait hands the rows to the caller
+    const bool oneCopy = batch == 1 && h->planBatch == 1 && h->hStage && h->outSpace == ORBX_MEM_HOST && !h->profiling;
+    h->pendingOneCopy = oneCopy;
+    h->pendingKps = kps;
+    h->pendingDesc = desc;
     if (nChunks == 1) {
         rc = copy_in(h, st, imgs, 0, batch, w, hgt, stride, img_stride);
         if (rc != ORBX_OK) return rc;
@@ -620,8 +666,12 @@ extern "C" int orbx_extract_batch_submit(orbx_t* h, const uint8_t* imgs, int bat
         rc = launch_chain(h, st, 0, batch, true);
         if (rc != ORBX_OK) return rc;
         CK(cudaGetLastError());
-        rc = copy_out(h, st, kps, desc, cap, 0, batch);
-        if (rc != ORBX_OK) return rc;
+        if (oneCopy) {
+            CK(cudaMemcpyAsync(h->hStage, h->dOutBlock, h->outBlockBytes, cudaMemcpyDeviceToHost, st));
+        } else {
+            rc = copy_out(h, st, kps, desc, cap, 0, batch);
+            if (rc != ORBX_OK) return rc;
+        }
     } else {
         rc = ensure_pipeline(h, nChunks);
         if (rc != ORBX_OK) return rc;
@@ -647,8 +697,14 @@ extern "C" int orbx_extract_batch_submit(orbx_t* h, const uint8_t* imgs, int bat
     }
     h->lastBatch = batch;
     h->blurValid = true;
-    CK(cudaMemcpyAsync(h->hCounts, h->dNOut, (size_t)batch * sizeof(int), cudaMemcpyDeviceToHost, st));
-    CK(cudaMemcpyAsync(h->hCounts + batch, h->dErr, sizeof(int), cudaMemcpyDeviceToHost, st));
+    if (oneCopy) {
+        // counts and flag are the tail of the block already on its way
+    } else if (batch == h->planBatch) {
+        CK(cudaMemcpyAsync(h->hCounts, h->dNOut, (size_t)(batch + 1) * sizeof(int), cudaMemcpyDeviceToHost, st));  // nOut + flag
+    } else {
+        CK(cudaMemcpyAsync(h->hCounts, h->dNOut, (size_t)batch * sizeof(int), cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(h->hCounts + batch, h->dErr, sizeof(int), cudaMemcpyDeviceToHost, st));
+    }
     stamp(h, 7);
     h->pendingBatch = batch;
     h->pendingCap = cap;
@@ -670,6 +726,16 @@ extern "C" int orbx_extract_batch_wait(orbx_t* h, int* n) {
     CK(cudaStreamSynchronize(st));
     if (h->profiling)
         for (int i = 0; i < 7; i++) cudaEventElapsedTime(&h->stageMs[i], h->ev[i], h->ev[i + 1]);
+    if (h->pendingOneCopy) {
+        const DevPlan& D = h->hp;
+        const size_t kpBytes = (size_t)D.selStride * sizeof(orbx_kp), dsBytes = (size_t)D.selStride * 32;
+        memcpy(h->hCounts, h->hStage + kpBytes + dsBytes, 2 * sizeof(int));
+        const int rows = std::min(std::min(cap, D.selStride), std::max(h->hCounts[0], 0));
+        if (rows > 0 && h->hCounts[1] == 0) {
+            memcpy(h->pendingKps, h->hStage, (size_t)rows * sizeof(orbx_kp));
+            memcpy(h->pendingDesc, h->hStage + kpBytes, (size_t)rows * 32);
+        }
+    }
     if (h->hCounts[batch] != 0) {
         const int code = h->hCounts[batch];
         cudaMemsetAsync(h->dErr, 0, sizeof(int), st);
