@@ -259,6 +259,64 @@ public:
         return nmatches;
     }
 
+    // ORBmatcher::SearchForTriangulation(KeyFrame* pKF1, KeyFrame* pKF2, cv::Mat F12,
+    //                                    std::vector<std::pair<size_t, size_t>>& vMatchedPairs, const bool bOnlyStereo)
+    // (src/ORBmatcher.cc:652-819; LocalMapping::CreateNewMapPoints src/LocalMapping.cc:268) on the device.
+    template <class KeyFrameT>
+    int SearchForTriangulation(KeyFrameT* pKF1, KeyFrameT* pKF2, cv::Mat F12,
+                               std::vector<std::pair<size_t, size_t> >& vMatchedPairs, const bool bOnlyStereo) {
+        // epipole of KF1's centre in KF2 (:657-664), CV_32F algebra as cv::Mat evaluates it
+        // (R2w*Cw: double accumulation rounded once to float, then the float add of t2w)
+        const cv::Mat Cw = pKF1->GetCameraCenter(), R2w = pKF2->GetRotation(), t2w = pKF2->GetTranslation();
+        float C2[3];
+        for (int r = 0; r < 3; r++) {
+            double acc = 0;
+            for (int c = 0; c < 3; c++) acc += (double)R2w.template at<float>(r, c) * (double)Cw.template at<float>(c, 0);
+            C2[r] = (float)acc + t2w.template at<float>(r, 0);
+        }
+        const float invz = 1.0f / C2[2];
+        orbm_triangulation T = orbm_triangulation();
+        T.ex = pKF2->fx * C2[0] * invz + pKF2->cx;
+        T.ey = pKF2->fy * C2[1] * invz + pKF2->cy;
+        for (int r = 0; r < 3; r++)
+            for (int c = 0; c < 3; c++) T.F12[3 * r + c] = F12.at<float>(r, c);
+        T.nlevels = (int)pKF2->mvScaleFactors.size();
+        for (int i = 0; i < T.nlevels && i < ORBX_MAX_LEVELS; i++) {
+            T.scale_factors[i] = pKF2->mvScaleFactors[i];
+            T.level_sigma2[i] = pKF2->mvLevelSigma2[i];
+        }
+        const int nA = pKF1->N, nB = pKF2->N;
+        std::vector<uint8_t> eA(nA), eB(nB), sA(nA), sB(nB);
+        std::vector<float> angA(nA), angB(nB), ptA(2 * (size_t)nA), ptB(2 * (size_t)nB);
+        std::vector<int32_t> octB(nB);
+        for (int i = 0; i < nA; i++) {
+            sA[i] = pKF1->mvuRight[i] >= 0;
+            eA[i] = !pKF1->GetMapPoint(i) && (!bOnlyStereo || sA[i]);
+            angA[i] = pKF1->mvKeysUn[i].angle;
+            ptA[2 * i] = pKF1->mvKeysUn[i].pt.x; ptA[2 * i + 1] = pKF1->mvKeysUn[i].pt.y;
+        }
+        for (int i = 0; i < nB; i++) {
+            sB[i] = pKF2->mvuRight[i] >= 0;
+            eB[i] = !pKF2->GetMapPoint(i) && (!bOnlyStereo || sB[i]);
+            angB[i] = pKF2->mvKeysUn[i].angle;
+            ptB[2 * i] = pKF2->mvKeysUn[i].pt.x; ptB[2 * i + 1] = pKF2->mvKeysUn[i].pt.y;
+            octB[i] = pKF2->mvKeysUn[i].octave;
+        }
+        T.pt_a = ptA.data(); T.pt_b = ptB.data(); T.octave_b = octB.data(); T.stereo_a = sA.data(); T.stereo_b = sB.data();
+        BowCsr a(pKF1->mFbowFeatVec), b(pKF2->mFbowFeatVec);
+        orbm_bow_side A = {nA, eA.data(), angA.data(), pKF1->mDescriptors.ptr(), (int)a.id.size(), a.id.data(), a.off.data(), a.feat.data()};
+        orbm_bow_side B = {nB, eB.data(), angB.data(), pKF2->mDescriptors.ptr(), (int)b.id.size(), b.id.data(), b.off.data(), b.feat.data()};
+        std::vector<int32_t> match(nA, -1);
+        int nmatches = 0;
+        check(orbm_search_for_triangulation(tls(), &A, &B, a.off.back(), b.off.back(), &T, TH_LOW, mbCheckOrientation ? 1 : 0,
+                                            match.data(), &nmatches), "orbm_search_for_triangulation");
+        vMatchedPairs.clear();
+        vMatchedPairs.reserve(nmatches);
+        for (int i = 0; i < nA; i++)
+            if (match[i] >= 0) vMatchedPairs.push_back(std::make_pair((size_t)i, (size_t)match[i]));
+        return nmatches;
+    }
+
 protected:
     // std::map<node, vector<feature>> (fbow::fBow2) flattened to the CSR form of the C ABI
     struct BowCsr {

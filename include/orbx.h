@@ -259,6 +259,27 @@ typedef struct {
 int orbm_search_by_bow(orbm_t* m, const orbm_bow_side* a, const orbm_bow_side* b, int n_pos_a, int n_pos_b, float nn_ratio,
                        int th, int strict, int check_orientation, int32_t* match_a, int* nmatches);
 
+/* ORBmatcher::SearchForTriangulation (include/ORBmatcher.h:76-77, src/ORBmatcher.cc:652-819; LocalMapping::
+ * CreateNewMapPoints src/LocalMapping.cc:268) on the same machinery: sides as above with
+ *   a.eligible[i] = !pKF1->GetMapPoint(i) && (!bOnlyStereo || mvuRight1[i] >= 0), b.eligible likewise for pKF2;
+ * a candidate replaces the best when dist <= TH_LOW, dist <= best, it is not within 100*scale of the epipole (mono-mono
+ * pairs only) and CheckDistEpipolarLine (src/ORBmatcher.cc:138-155) passes. match_a[i] = vMatches12[i]. */
+typedef struct {
+    const float* pt_a;        /* [a.n][2] mvKeysUn[i].pt of KF1 */
+    const float* pt_b;        /* [b.n][2] mvKeysUn[i].pt of KF2 */
+    const int32_t* octave_b;  /* [b.n]    mvKeysUn[i].octave of KF2 */
+    const uint8_t* stereo_a;  /* [a.n]    mvuRight[i] >= 0 */
+    const uint8_t* stereo_b;  /* [b.n] */
+    float F12[9];             /* row major */
+    float ex, ey;             /* epipole of KF1's centre in KF2 (src/ORBmatcher.cc:657-664) */
+    int nlevels;
+    float scale_factors[ORBX_MAX_LEVELS]; /* pKF2->mvScaleFactors */
+    float level_sigma2[ORBX_MAX_LEVELS];  /* pKF2->mvLevelSigma2 */
+} orbm_triangulation;
+int orbm_search_for_triangulation(orbm_t* m, const orbm_bow_side* a, const orbm_bow_side* b, int n_pos_a, int n_pos_b,
+                                  const orbm_triangulation* t, int th, int check_orientation, int32_t* match_a,
+                                  int* nmatches);
+
 /* ---- vocabulary tree (bag of words): replaces fbow::Vocabulary as the reference uses it -------------------------------
  * (Thirdparty/fbow/src/fbow.h:51-125, fbow.cpp; called from Frame::ComputeFboW src/Frame.cc:395-400 and
  * KeyFrame::ComputeFboW src/KeyFrame.cc:62). */

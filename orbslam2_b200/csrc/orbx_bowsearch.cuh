@@ -22,6 +22,12 @@ struct BowDev {
     const int *offA, *offB;
     float nnRatio;
     int th, strict, checkOri;
+    // SearchForTriangulation only (tri = 1): undistorted keypoint positions, octaves of B, stereo flags, F12, epipole
+    int tri;
+    const float2 *ptA, *ptB;
+    const int32_t* octB;
+    const uint8_t *stereoA, *stereoB;
+    float F[9], ex, ey, scale[ORBX_MAX_LEVELS], sigma2[ORBX_MAX_LEVELS];
 };
 
 // per entry p of A's feature vector: the matching node of B (or -1), found once
@@ -69,6 +75,51 @@ __global__ void __launch_bounds__(128) k_bow_choose(BowDev S, const int* __restr
         }
         const bool in = S.strict ? best1 < S.th : best1 <= S.th;
         if (in && (float)best1 < __fmul_rn(S.nnRatio, (float)best2)) nc = bestIdx;
+    }
+    if (nc != choice[p]) {
+        choice[p] = nc;
+        flag[round] = 1;
+    }
+}
+
+// ORBmatcher::SearchForTriangulation's scan (src/ORBmatcher.cc:697-749): best = TH_LOW; a candidate replaces the best
+// when dist <= best (equal distance: the LAST one wins) and it passes the epipole and epipolar-line gates
+// (CheckDistEpipolarLine, :138-155; float arithmetic in the reference's order, no FMA contraction).
+__global__ void __launch_bounds__(128) k_tri_choose(BowDev S, const int* __restrict__ posNodeB, int* __restrict__ choice,
+                                                    const int* __restrict__ owner, int* __restrict__ flag, int round) {
+    if (round > 0 && flag[round - 1] == 0) return;
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= S.nPosA) return;
+    int nc = -1;
+    const int jb = posNodeB[p];
+    const uint32_t ia = S.featA[p];
+    if (jb >= 0 && S.eligA[ia]) {
+        const uint4 a0 = S.descA[2 * (size_t)ia], a1 = S.descA[2 * (size_t)ia + 1];
+        const float2 k1 = S.ptA[ia];
+        const bool st1 = S.stereoA[ia] != 0;
+        // epipolar line in the second image l = x1' F12 = [a b c]
+        const float la = __fadd_rn(__fadd_rn(__fmul_rn(k1.x, S.F[0]), __fmul_rn(k1.y, S.F[3])), S.F[6]);
+        const float lb = __fadd_rn(__fadd_rn(__fmul_rn(k1.x, S.F[1]), __fmul_rn(k1.y, S.F[4])), S.F[7]);
+        const float lc = __fadd_rn(__fadd_rn(__fmul_rn(k1.x, S.F[2]), __fmul_rn(k1.y, S.F[5])), S.F[8]);
+        const float den = __fadd_rn(__fmul_rn(la, la), __fmul_rn(lb, lb));
+        int best = S.th;
+        for (int c = S.offB[jb], e = S.offB[jb + 1]; c < e; c++) {
+            const uint32_t ib = S.featB[c];
+            if (owner[ib] < p) continue;     // vbMatched2[idx2]
+            if (!S.eligB[ib]) continue;      // pMP2 (and the bOnlyStereo gate, folded in by the caller)
+            const int d = hamming256(a0, a1, S.descB[2 * (size_t)ib], S.descB[2 * (size_t)ib + 1]);
+            if (d > S.th || d > best) continue;
+            const float2 k2 = S.ptB[ib];
+            const int oct = S.octB[ib];
+            if (!st1 && !S.stereoB[ib]) {
+                const float dx = __fsub_rn(S.ex, k2.x), dy = __fsub_rn(S.ey, k2.y);
+                if (__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)) < __fmul_rn(100.f, S.scale[oct])) continue;
+            }
+            const float num = __fadd_rn(__fadd_rn(__fmul_rn(la, k2.x), __fmul_rn(lb, k2.y)), lc);
+            if (den == 0.f) continue;
+            const float dsqr = __fdiv_rn(__fmul_rn(num, num), den);
+            if ((double)dsqr < 3.84 * (double)S.sigma2[oct]) { nc = (int)ib; best = d; }
+        }
     }
     if (nc != choice[p]) {
         choice[p] = nc;
@@ -138,9 +189,9 @@ static int bow_side_ok(const orbm_bow_side* s) {
     return 1;
 }
 
-extern "C" int orbm_search_by_bow(orbm_t* m, const orbm_bow_side* a, const orbm_bow_side* b, int n_pos_a, int n_pos_b,
-                                  float nn_ratio, int th, int strict, int check_orientation, int32_t* match_a,
-                                  int* nmatches) {
+static int bow_run(orbm_t* m, const orbm_bow_side* a, const orbm_bow_side* b, int n_pos_a, int n_pos_b, float nn_ratio,
+                   int th, int strict, int check_orientation, const orbm_triangulation* T, int32_t* match_a,
+                   int* nmatches) {
     if (!m || !a || !b || !nmatches || (a->n && !match_a)) FAIL(ORBX_EINVAL, "null argument");
     if (!bow_side_ok(a) || !bow_side_ok(b) || (a->n && !a->eligible) || n_pos_a < 0 || n_pos_b < 0) FAIL(ORBX_EINVAL, "bad feature-vector arrays");
     *nmatches = 0;
@@ -155,7 +206,10 @@ extern "C" int orbm_search_by_bow(orbm_t* m, const orbm_bow_side* a, const orbm_
         return ORBX_OK;
     }
     const int maxRounds = n_pos_a + 8;
-    const size_t need = (size_t)nA * (1 + 4 + 32 + 4) + (size_t)nB * (1 + 4 + 32 + 4) + (size_t)(a->n_nodes + b->n_nodes) * 8 +
+    if (T && (!T->pt_a || !T->pt_b || !T->octave_b || !T->stereo_a || !T->stereo_b || !b->eligible || T->nlevels < 1 ||
+              T->nlevels > ORBX_MAX_LEVELS))
+        FAIL(ORBX_EINVAL, "bad triangulation arguments");
+    const size_t need = (size_t)nA * (1 + 4 + 32 + 4 + 8 + 1) + (size_t)nB * (1 + 4 + 32 + 4 + 8 + 4 + 1) + (size_t)(a->n_nodes + b->n_nodes) * 8 +
                         (size_t)(n_pos_a + n_pos_b) * 4 + (size_t)n_pos_a * 8 + (size_t)maxRounds * 4 + 256 * 24;
     int rc;
     if ((rc = ensure(m->dWs, m->wsCap, need))) return rc;
@@ -190,6 +244,17 @@ extern "C" int orbm_search_by_bow(orbm_t* m, const orbm_bow_side* a, const orbm_
     S.featA = (const uint32_t*)in(a->node_feat, (size_t)n_pos_a * 4);
     S.featB = (const uint32_t*)in(b->node_feat, (size_t)n_pos_b * 4);
     S.nnRatio = nn_ratio; S.th = th; S.strict = strict; S.checkOri = check_orientation;
+    S.tri = T != nullptr;
+    if (T) {
+        S.ptA = (const float2*)in(T->pt_a, (size_t)nA * 8);
+        S.ptB = (const float2*)in(T->pt_b, (size_t)nB * 8);
+        S.octB = (const int32_t*)in(T->octave_b, (size_t)nB * 4);
+        S.stereoA = (const uint8_t*)in(T->stereo_a, nA);
+        S.stereoB = (const uint8_t*)in(T->stereo_b, nB);
+        for (int i = 0; i < 9; i++) S.F[i] = T->F12[i];
+        S.ex = T->ex; S.ey = T->ey;
+        for (int i = 0; i < T->nlevels; i++) { S.scale[i] = T->scale_factors[i]; S.sigma2[i] = T->level_sigma2[i]; }
+    }
     if ((((uintptr_t)S.descA) | ((uintptr_t)S.descB)) & 15) FAIL(ORBX_EINVAL, "device descriptor matrices must be 16-byte aligned");
     int* posNodeB = W.take<int>(n_pos_a);
     int* choice = W.take<int>(n_pos_a);
@@ -210,7 +275,8 @@ extern "C" int orbm_search_by_bow(orbm_t* m, const orbm_bow_side* a, const orbm_
         for (int r = 0; r < R; r++, round++) {
             CK(cudaMemsetAsync(owner, 0x7F, (size_t)nB * sizeof(int), st));
             k_bow_claim<<<(n_pos_a + 255) / 256, 256, 0, st>>>(S, choice, owner, flags, round);
-            k_bow_choose<<<(n_pos_a + 127) / 128, 128, 0, st>>>(S, posNodeB, choice, owner, flags, round);
+            if (T) k_tri_choose<<<(n_pos_a + 127) / 128, 128, 0, st>>>(S, posNodeB, choice, owner, flags, round);
+            else k_bow_choose<<<(n_pos_a + 127) / 128, 128, 0, st>>>(S, posNodeB, choice, owner, flags, round);
             m->launches += 2;
         }
         CK(cudaGetLastError());
@@ -230,4 +296,17 @@ extern "C" int orbm_search_by_bow(orbm_t* m, const orbm_bow_side* a, const orbm_
     m->lastRounds = rounds + 1;
     m->lastCandidates = 0;
     return ORBX_OK;
+}
+
+extern "C" int orbm_search_by_bow(orbm_t* m, const orbm_bow_side* a, const orbm_bow_side* b, int n_pos_a, int n_pos_b,
+                                  float nn_ratio, int th, int strict, int check_orientation, int32_t* match_a,
+                                  int* nmatches) {
+    return bow_run(m, a, b, n_pos_a, n_pos_b, nn_ratio, th, strict, check_orientation, nullptr, match_a, nmatches);
+}
+
+extern "C" int orbm_search_for_triangulation(orbm_t* m, const orbm_bow_side* a, const orbm_bow_side* b, int n_pos_a,
+                                             int n_pos_b, const orbm_triangulation* T, int th, int check_orientation,
+                                             int32_t* match_a, int* nmatches) {
+    if (!T) FAIL(ORBX_EINVAL, "null argument");
+    return bow_run(m, a, b, n_pos_a, n_pos_b, 0.f, th, 0, check_orientation, T, match_a, nmatches);
 }

@@ -214,6 +214,40 @@ class ORBmatcher:
                                               int(self.mbCheckOrientation), match.ctypes.data, C.byref(n)))
         return n.value, match
 
+    def SearchForTriangulation(self, a, b, geo, th=None):
+        """SearchForTriangulation(pKF1, pKF2, F12, vMatchedPairs, bOnlyStereo) (src/ORBmatcher.cc:652-819). a, b: bow_side
+        dicts with eligible = "no map point (and stereo when bOnlyStereo)"; geo: dict(pt_a [nA,2], pt_b [nB,2], octave_b,
+        stereo_a, stereo_b, F12 [3,3], ex, ey, scale_factors, level_sigma2). Returns (nmatches, vMatches12)."""
+        self._set_space(_lib.MEM_HOST, _lib.MEM_HOST)
+        ea = a["eligible"] if a["eligible"] is not None else np.ones(a["n"], np.uint8)
+        eb = b["eligible"] if b["eligible"] is not None else np.ones(b["n"], np.uint8)
+
+        def side(d, e):
+            return _lib.BowSide(d["n"], e.ctypes.data, d["angle"].ctypes.data, d["desc"].ctypes.data, len(d["node_id"]),
+                                d["node_id"].ctypes.data, d["node_off"].ctypes.data, d["node_feat"].ctypes.data)
+
+        A, B = side(a, ea), side(b, eb)
+        g = {k: np.ascontiguousarray(geo[k], t) for k, t in (("pt_a", np.float32), ("pt_b", np.float32), ("octave_b", np.int32),
+                                                              ("stereo_a", np.uint8), ("stereo_b", np.uint8))}
+        T = _lib.Triangulation()
+        T.pt_a, T.pt_b, T.octave_b = g["pt_a"].ctypes.data, g["pt_b"].ctypes.data, g["octave_b"].ctypes.data
+        T.stereo_a, T.stereo_b = g["stereo_a"].ctypes.data, g["stereo_b"].ctypes.data
+        F = np.ascontiguousarray(geo["F12"], np.float32).ravel()
+        for i in range(9):
+            T.F12[i] = F[i]
+        T.ex, T.ey = float(np.float32(geo["ex"])), float(np.float32(geo["ey"]))
+        sf, s2 = np.asarray(geo["scale_factors"], np.float32), np.asarray(geo["level_sigma2"], np.float32)
+        T.nlevels = len(sf)
+        for i in range(len(sf)):
+            T.scale_factors[i], T.level_sigma2[i] = sf[i], s2[i]
+        match = np.full(a["n"], -1, np.int32)
+        n = C.c_int()
+        _lib.check(self._L.orbm_search_for_triangulation(self._h, C.byref(A), C.byref(B), int(a["node_off"][-1]),
+                                                         int(b["node_off"][-1]), C.byref(T),
+                                                         int(self.TH_LOW if th is None else th),
+                                                         int(self.mbCheckOrientation), match.ctypes.data, C.byref(n)))
+        return n.value, match
+
     @staticmethod
     def _mp_arrays(mps):
         f32 = lambda k: np.ascontiguousarray(mps[k], np.float32)

@@ -111,6 +111,19 @@ struct KeyFrame {
     std::vector<MapPoint*> mps;
     std::vector<MapPoint*> GetMapPointMatches() { return mps; }
 };
+struct TriKeyFrame : KeyFrame {
+    int N = 0;
+    float fx = 0, fy = 0, cx = 0, cy = 0;
+    std::vector<float> mvuRight, mvScaleFactors, mvLevelSigma2;
+    cv::Mat Ow, R, t;
+    cv::Mat GetCameraCenter() { return Ow; }
+    cv::Mat GetRotation() { return R; }
+    cv::Mat GetTranslation() { return t; }
+    MapPoint* GetMapPoint(int i) { return mps[i]; }
+};
+int instantiate5(ORB_SLAM2::ORBmatcher& m, TriKeyFrame* a, TriKeyFrame* b, cv::Mat F12, std::vector<std::pair<size_t, size_t> >& out) {
+    return m.SearchForTriangulation(a, b, F12, out, false);
+}
 struct BowFrame : Frame { fbow::fBow2 mFbowFeatVec; };
 int instantiate3(ORB_SLAM2::ORBmatcher& m, KeyFrame* kf, BowFrame& F, std::vector<MapPoint*>& out) { return m.SearchByFboW(kf, F, out); }
 int instantiate4(ORB_SLAM2::ORBmatcher& m, KeyFrame* a, KeyFrame* b, std::vector<MapPoint*>& out) { return m.SearchByFboW(a, b, out); }

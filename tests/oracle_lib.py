@@ -418,3 +418,29 @@ def oracle_search_by_bow(a, b, nn_ratio, th, strict, check_ori):
     match = np.full(a["n"], -1, np.int32)
     n = L.orc_search_by_bow(*aa, *bb, np.float32(nn_ratio), th, int(strict), int(check_ori), _p(match))
     return n, match
+
+
+def oracle_search_for_triangulation(a, b, geo, th, check_ori):
+    """orc_search_for_triangulation over two bow_side dicts and the geometry dict of ORBmatcher.SearchForTriangulation."""
+    build_oracle()
+    L = _load(ORACLE_SO)
+    L.orc_search_for_triangulation.restype = C.c_int
+    side = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.orc_search_for_triangulation.argtypes = side + side + [C.c_void_p] * 6 + [C.c_float, C.c_float, C.c_void_p, C.c_void_p,
+                                                                                C.c_int, C.c_int, C.c_void_p]
+    keep = []
+
+    def args(d):
+        e = d["eligible"] if d["eligible"] is not None else np.ones(d["n"], np.uint8)
+        keep.append(e)
+        return [d["n"], _p(e), _p(d["angle"]), _p(d["desc"]), len(d["node_id"]), _p(d["node_id"]), _p(d["node_off"]),
+                _p(d["node_feat"])]
+
+    g = {k: np.ascontiguousarray(geo[k], t) for k, t in (("pt_a", np.float32), ("pt_b", np.float32), ("octave_b", np.int32),
+                                                          ("stereo_a", np.uint8), ("stereo_b", np.uint8), ("F12", np.float32),
+                                                          ("scale_factors", np.float32), ("level_sigma2", np.float32))}
+    match = np.full(a["n"], -1, np.int32)
+    n = L.orc_search_for_triangulation(*args(a), *args(b), _p(g["pt_a"]), _p(g["pt_b"]), _p(g["octave_b"]), _p(g["stereo_a"]),
+                                       _p(g["stereo_b"]), _p(g["F12"]), np.float32(geo["ex"]), np.float32(geo["ey"]),
+                                       _p(g["scale_factors"]), _p(g["level_sigma2"]), th, int(check_ori), _p(match))
+    return n, match

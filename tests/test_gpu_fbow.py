@@ -187,3 +187,72 @@ def test_search_by_bow_greedy_chain_and_empty(ob):
     E = ob.ORBmatcher.bow_side(np.zeros((0, 32), np.uint8), np.zeros(0, np.float32), {}, None)
     assert m.SearchByFboW(A, E)[0] == 0 and m.SearchByFboW(E, B)[0] == 0
     m.close()
+
+
+def _two_view_geometry(n_a, n_b, src_of_b, seed):
+    """keypoints of two views of random 3-D points (B's feature j sees the point of A's feature src_of_b[j] when >= 0),
+    with the fundamental matrix F12 and KF1's epipole in KF2, all float32 as the reference holds them."""
+    rng = np.random.default_rng(seed)
+    fx = fy = np.float32(520.0); cx, cy = np.float32(320.0), np.float32(240.0)
+    K = np.array([[fx, 0, cx], [0, fy, cy], [0, 0, 1]], np.float64)
+    ang = 0.05
+    R21 = np.array([[np.cos(ang), 0, np.sin(ang)], [0, 1, 0], [-np.sin(ang), 0, np.cos(ang)]])
+    t21 = np.array([0.25, 0.02, 0.05])
+    X = np.stack([rng.uniform(-2, 2, n_a), rng.uniform(-1.5, 1.5, n_a), rng.uniform(3, 9, n_a)], 1)
+    pa = (K @ X.T).T; pa = pa[:, :2] / pa[:, 2:]
+    pt_b = np.stack([rng.uniform(0, 640, n_b), rng.uniform(0, 480, n_b)], 1)
+    has = src_of_b >= 0
+    Xb = (R21 @ X[src_of_b[has]].T).T + t21
+    pb = (K @ Xb.T).T; pb = pb[:, :2] / pb[:, 2:]
+    pt_b[has] = pb + rng.normal(0, 0.6, pb.shape)
+    tx = np.array([[0, -t21[2], t21[1]], [t21[2], 0, -t21[0]], [-t21[1], t21[0], 0]])
+    E = tx @ R21
+    F21 = np.linalg.inv(K).T @ E @ np.linalg.inv(K)      # x2' F21 x1 = 0
+    F12 = F21.T                                          # line in image 2: l = x1' F12
+    C2 = t21                                             # KF1's centre in KF2's frame
+    ex, ey = fx * np.float32(C2[0]) / np.float32(C2[2]) + cx, fy * np.float32(C2[1]) / np.float32(C2[2]) + cy
+    sf = (np.float32(1.2) ** np.arange(8)).astype(np.float32)
+    return dict(pt_a=pa.astype(np.float32), pt_b=pt_b.astype(np.float32), octave_b=rng.integers(0, 8, n_b).astype(np.int32),
+                stereo_a=(rng.random(n_a) < 0.4).astype(np.uint8), stereo_b=(rng.random(n_b) < 0.4).astype(np.uint8),
+                F12=F12.astype(np.float32), ex=ex, ey=ey, scale_factors=sf, level_sigma2=(sf * sf).astype(np.float32))
+
+
+@pytest.mark.parametrize("only_stereo", [False, True])
+def test_search_for_triangulation_vs_oracle(ob, only_stereo):
+    from oracle_lib import oracle_search_for_triangulation
+    blob = synth_vocabulary(k=10, levels=5, seed=33)
+    voc = ob.Vocabulary(); voc.fromStream(blob)
+    total = 0
+    for seed, (na, nb) in enumerate([(1200, 1300), (800, 2000), (40, 30)]):
+        rng = np.random.default_rng(60 + seed)
+        da = _features(blob, na, 70 + seed)
+        ns = int(min(na, nb) * 0.7)
+        pick = rng.permutation(na)[:ns]
+        db = np.concatenate([da[pick], _features(blob, nb - ns, 80 + seed)])
+        bits = np.unpackbits(db[:ns], axis=1)
+        for _ in range(5):
+            bits[np.arange(ns), rng.integers(0, 256, ns)] ^= 1
+        db[:ns] = np.packbits(bits, axis=1)
+        perm = rng.permutation(nb)
+        db = np.ascontiguousarray(db[perm])
+        src = np.full(nb, -1); src[:ns] = pick; src = src[perm]
+        geo = _two_view_geometry(na, nb, src, seed)
+        ang_a = (rng.random(na) * 360).astype(np.float32)
+        ang_b = (rng.random(nb) * 360).astype(np.float32)
+        ang_b[src >= 0] = np.mod(ang_a[src[src >= 0]] + np.float32(12.0) + rng.normal(0, 3, (src >= 0).sum()), 360).astype(np.float32)
+        fa, fb = voc.transform(da, 4)[1], voc.transform(db, 4)[1]
+        ea = (rng.random(na) < 0.7).astype(np.uint8)      # features without a map point
+        eb = (rng.random(nb) < 0.7).astype(np.uint8)
+        if only_stereo:
+            ea &= geo["stereo_a"]; eb &= geo["stereo_b"]
+        A = ob.ORBmatcher.bow_side(da, ang_a, fa, ea)
+        B = ob.ORBmatcher.bow_side(db, ang_b, fb, eb)
+        for ori in (True, False):
+            m = ob.ORBmatcher(0.6, ori)
+            n, match = m.SearchForTriangulation(A, B, geo)
+            en, ematch = oracle_search_for_triangulation(A, B, geo, 50, ori)
+            assert n == en and np.array_equal(match, ematch), (seed, ori)
+            total += n
+            m.close()
+    assert total > (100 if only_stereo else 400)
+    voc.close()
