@@ -39,6 +39,44 @@ def main():
                           "th": th, "gpu_ms_host_call": gpu_ms, "cpu_oracle_ms_1_thread": cpu_ms, "nmatches": got[0],
                           "candidate_pairs": cands, "fixed_point_rounds": rounds, "identical_to_oracle": bool(same)}))
 
+    # SearchByFboW(KF, F) and SearchForTriangulation on a synthetic vocabulary (k = 10, 5 levels), 2000 features per side
+    from orbslam2_b200.synth import synth_vocabulary, synth_vocabulary_features
+    from oracle_lib import oracle_search_by_bow
+    blob = synth_vocabulary(k=10, levels=5, seed=31)
+    voc = ob.Vocabulary(); voc.fromStream(blob)
+    rng = np.random.default_rng(2)
+    for n in (1000, 2000, 8000):
+        da = synth_vocabulary_features(blob, n, seed=5)
+        pick = rng.permutation(n)[: int(0.7 * n)]
+        db = np.concatenate([da[pick], synth_vocabulary_features(blob, n - len(pick), seed=6)])
+        bits = np.unpackbits(db[:len(pick)], axis=1)
+        for _ in range(6):
+            bits[np.arange(len(pick)), rng.integers(0, 256, len(pick))] ^= 1
+        db[:len(pick)] = np.packbits(bits, axis=1)
+        db = np.ascontiguousarray(db[rng.permutation(n)])
+        t0 = time.perf_counter()
+        fa, fb = voc.transform(da, 4)[1], voc.transform(db, 4)[1]
+        t_bow = (time.perf_counter() - t0) / 2 * 1e3
+        A = ob.ORBmatcher.bow_side(da, (rng.random(n) * 360).astype(np.float32), fa, np.ones(n, np.uint8))
+        B = ob.ORBmatcher.bow_side(db, (rng.random(n) * 360).astype(np.float32), fb, None)
+        mb = ob.ORBmatcher(0.7, False)
+        for _ in range(3):
+            got = mb.SearchByFboW(A, B)
+        t0 = time.perf_counter()
+        for _ in range(20):
+            got = mb.SearchByFboW(A, B)
+        gpu_ms = (time.perf_counter() - t0) / 20 * 1e3
+        t0 = time.perf_counter()
+        for _ in range(5):
+            exp = oracle_search_by_bow(A, B, 0.7, 50, False, False)
+        cpu_ms = (time.perf_counter() - t0) / 5 * 1e3
+        print(json.dumps({"metric": "search_by_bow_ms_per_keyframe_frame_pair", "features_per_side": n,
+                          "gpu_ms_host_call": gpu_ms, "cpu_oracle_ms_1_thread": cpu_ms, "nmatches": got[0],
+                          "fixed_point_rounds": mb.search_stats()[0], "transform_ms_per_frame_python_call": t_bow,
+                          "identical_to_oracle": bool(got[0] == exp[0] and np.array_equal(got[1], exp[1]))}))
+        mb.close()
+    voc.close()
+
     # batched MapPoint::ComputeDistinctiveDescriptors: 20 000 map points with 3..40 observations
     rng = np.random.default_rng(1)
     counts = rng.integers(3, 41, 20000).astype(np.int32)
