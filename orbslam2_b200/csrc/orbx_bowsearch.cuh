@@ -221,13 +221,9 @@ static int bow_run(orbm_t* m, const orbm_bow_side* a, const orbm_bow_side* b, in
         m->hFlagsCap = (size_t)maxRounds;
     }
     WsCursor W{m->dWs, 0};
-    auto in = [&](const void* src, size_t bytes) -> const void* {
-        if (!src) return nullptr;
-        if (!hin) return src;
-        uint8_t* d = W.take<uint8_t>(bytes);
-        cudaMemcpyAsync(d, src, bytes, cudaMemcpyHostToDevice, st);
-        return d;
-    };
+    if (hin && (rc = ensure_host_in(m, need))) return rc;
+    Stager stg{m, &W, hin, (size_t)-1};
+    auto in = [&](const void* src, size_t bytes) -> const void* { return stg.in(src, bytes); };
     BowDev S;
     S.nA = nA; S.nB = nB; S.nPosA = n_pos_a;
     S.eligA = (const uint8_t*)in(a->eligible, nA);
@@ -256,6 +252,7 @@ static int bow_run(orbm_t* m, const orbm_bow_side* a, const orbm_bow_side* b, in
         for (int i = 0; i < T->nlevels; i++) { S.scale[i] = T->scale_factors[i]; S.sigma2[i] = T->level_sigma2[i]; }
     }
     if ((((uintptr_t)S.descA) | ((uintptr_t)S.descB)) & 15) FAIL(ORBX_EINVAL, "device descriptor matrices must be 16-byte aligned");
+    if ((rc = stg.flush(st))) return rc;
     int* posNodeB = W.take<int>(n_pos_a);
     int* choice = W.take<int>(n_pos_a);
     int* owner = W.take<int>(nB);

@@ -338,6 +338,7 @@ struct orbm_handle {
     uint8_t* dCand = nullptr; size_t candCap = 0;  // candidate (keypoint, distance) lists
     int* hRes = nullptr;                           // pinned: [0] nmatches, [2] total candidates
     int* hFlags = nullptr; size_t hFlagsCap = 0;   // pinned copy of the per-round change flags
+    uint8_t* hIn = nullptr; size_t hInCap = 0;     // pinned mirror of the staged inputs: many small arrays, one copy
     int smCount = 148;
     int64_t launches = 0;
     int lastRounds = 0; int64_t lastCandidates = 0;
@@ -381,7 +382,7 @@ extern "C" int orbm_destroy(orbm_t* m) {
     cudaStreamSynchronize(m->stream);
     if (!m->trainAdopted) cudaFree(m->dTrain);
     cudaFree(m->dQ); cudaFree(m->dB); cudaFree(m->dPartial); cudaFree(m->dI1); cudaFree(m->dI2); cudaFree(m->dD1);
-    cudaFree(m->dD2); cudaFree(m->dOff); cudaFree(m->dIdx); cudaFree(m->dSkip); cudaFree(m->dWs); cudaFree(m->dCand); if (m->hRes) cudaFreeHost(m->hRes); if (m->hFlags) cudaFreeHost(m->hFlags);
+    cudaFree(m->dD2); cudaFree(m->dOff); cudaFree(m->dIdx); cudaFree(m->dSkip); cudaFree(m->dWs); cudaFree(m->dCand); if (m->hRes) cudaFreeHost(m->hRes); if (m->hFlags) cudaFreeHost(m->hFlags); if (m->hIn) cudaFreeHost(m->hIn);
     cudaStreamDestroy(m->stream);
     delete m;
     return ORBX_OK;
@@ -656,6 +657,35 @@ struct WsCursor {  // bump allocator over the handle's workspace (256-byte align
 };
 }  // namespace
 
+// Host-input staging: the caller's arrays (a dozen small ones per search) are gathered into a pinned mirror of the
+// workspace prefix and cross PCIe as ONE copy; with device input the pointers are used in place.
+struct Stager {
+    orbm_handle* m; WsCursor* W; bool host; size_t begin;
+    const void* in(const void* src, size_t bytes) {
+        if (!src) return nullptr;
+        if (!host) return src;
+        uint8_t* d = W->take<uint8_t>(bytes);
+        const size_t off = (size_t)(d - W->base);
+        if (begin == (size_t)-1) begin = off;
+        memcpy(m->hIn + (off - begin), src, bytes);
+        return d;
+    }
+    int flush(cudaStream_t st) {
+        if (!host || begin == (size_t)-1) return ORBX_OK;
+        CK(cudaMemcpyAsync(W->base + begin, m->hIn, W->off - begin, cudaMemcpyHostToDevice, st));
+        return ORBX_OK;
+    }
+};
+static int ensure_host_in(orbm_handle* m, size_t bytes) {
+    if (bytes <= m->hInCap) return ORBX_OK;
+    if (m->hIn) cudaFreeHost(m->hIn);
+    m->hIn = nullptr;
+    m->hInCap = 0;
+    CK(cudaMallocHost(&m->hIn, bytes));
+    m->hInCap = bytes;
+    return ORBX_OK;
+}
+
 // Queries of either search (mode 0: last-frame map points, mode 1: local map points with their tracking projection).
 struct SpHostQueries {
     int n;
@@ -707,13 +737,9 @@ static int sp_run(orbm_handle* m, int mode, const orbm_proj_params* p, float nnR
     S.nCur = nC;
     S.mode = mode;
     S.nnRatio = nnRatio;
-    auto in = [&](const void* src, size_t bytes) -> const void* {  // stage a caller array if it is host memory
-        if (!src) return nullptr;
-        if (!hin) return src;
-        uint8_t* d = W.take<uint8_t>(bytes);
-        cudaMemcpyAsync(d, src, bytes, cudaMemcpyHostToDevice, st);
-        return d;
-    };
+    if (hin && (rc = ensure_host_in(m, need))) return rc;
+    Stager stg{m, &W, hin, (size_t)-1};
+    auto in = [&](const void* src, size_t bytes) -> const void* { return stg.in(src, bytes); };
     S.worldPos = (const float*)in(last->world_pos, (size_t)nL * 12);
     S.lflags = (const uint8_t*)in(last->flags, nL);
     S.loct = (const int32_t*)in(last->octave, (size_t)nL * 4);
@@ -728,6 +754,7 @@ static int sp_run(orbm_handle* m, int mode, const orbm_proj_params* p, float nnR
     S.cdesc = (const uint4*)in(cur->desc, (size_t)nC * 32);
     S.taken = (const uint8_t*)in(cur->taken, nC);
     if ((((uintptr_t)S.ldesc) | ((uintptr_t)S.cdesc)) & 15) FAIL(ORBX_EINVAL, "device descriptor matrices must be 16-byte aligned");
+    if ((rc = stg.flush(st))) return rc;
     int* cellCount = W.take<int>(SP_CELLS);
     int* cellStart = W.take<int>(SP_CELLS + 1);
     int* cursor = W.take<int>(SP_CELLS);
