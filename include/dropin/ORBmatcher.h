@@ -209,6 +209,66 @@ public:
         return nmatches;
     }
 
+    // ORBmatcher::SearchByProjection(Frame& CurrentFrame, KeyFrame* pKF, const std::set<MapPoint*>& sAlreadyFound,
+    //                                const float th, const int ORBdist)
+    // (src/ORBmatcher.cc:1468-1595; Tracking::Relocalization src/Tracking.cc:1552,1566) on the device. The per-point
+    // gates that need MapPoint internals (scale-invariance range, PredictScale) stay on the host; projection, window
+    // search, greedy claims and the rotation filter run in orbm_search_by_projection.
+    template <class FrameT, class KeyFrameT, class SetT>
+    int SearchByProjection(FrameT& CurrentFrame, KeyFrameT* pKF, const SetT& sAlreadyFound, const float th, const int ORBdist) {
+        orbm_proj_params P = orbm_proj_params();
+        P.fx = CurrentFrame.fx; P.fy = CurrentFrame.fy; P.cx = CurrentFrame.cx; P.cy = CurrentFrame.cy; P.bf = CurrentFrame.mbf;
+        P.minX = CurrentFrame.mnMinX; P.maxX = CurrentFrame.mnMaxX; P.minY = CurrentFrame.mnMinY; P.maxY = CurrentFrame.mnMaxY;
+        P.grid_w_inv = CurrentFrame.mfGridElementWidthInv; P.grid_h_inv = CurrentFrame.mfGridElementHeightInv;
+        P.nlevels = (int)CurrentFrame.mvScaleFactors.size();
+        for (int i = 0; i < P.nlevels && i < ORBX_MAX_LEVELS; i++) P.scale[i] = CurrentFrame.mvScaleFactors[i];
+        for (int r = 0; r < 3; r++) {
+            for (int c = 0; c < 3; c++) P.Rcw[3 * r + c] = CurrentFrame.mTcw.template at<float>(r, c);
+            P.tcw[r] = CurrentFrame.mTcw.template at<float>(r, 3);
+        }
+        P.th = th; P.th_high = ORBdist; P.check_orientation = mbCheckOrientation ? 1 : 0; P.skip_depth_test = 1;
+        float Ow[3];  // -Rcw.t()*tcw: CV_32F product = double accumulation rounded once
+        for (int r = 0; r < 3; r++) {
+            double acc = 0;
+            for (int c = 0; c < 3; c++) acc += (double)P.Rcw[3 * c + r] * (double)P.tcw[c];
+            Ow[r] = -(float)acc;
+        }
+        const auto vpMPs = pKF->GetMapPointMatches();
+        const int n = (int)vpMPs.size(), nC = CurrentFrame.N;
+        std::vector<float> wp((size_t)n * 3, 0.f), ang(n, 0.f);
+        std::vector<int32_t> lvl(n, 0);
+        std::vector<uint8_t> flags(n, 0), desc((size_t)n * 32, 0), taken(nC, 0);
+        for (int i = 0; i < n; i++) {
+            auto* pMP = vpMPs[i];
+            if (!pMP || pMP->isBad() || sAlreadyFound.count(pMP)) continue;
+            const cv::Mat x = pMP->GetWorldPos();
+            double s = 0;
+            for (int k = 0; k < 3; k++) {
+                wp[3 * i + k] = x.template at<float>(k, 0);
+                const float po = wp[3 * i + k] - Ow[k];
+                s += (double)po * (double)po;
+            }
+            const float dist3D = (float)std::sqrt(s);  // cv::norm(PO)
+            if (dist3D < pMP->GetMinDistanceInvariance() || dist3D > pMP->GetMaxDistanceInvariance()) continue;
+            lvl[i] = pMP->PredictScale(dist3D, &CurrentFrame);
+            flags[i] = 3;
+            ang[i] = pKF->mvKeysUn[i].angle;
+            const cv::Mat d = pMP->GetDescriptor();
+            for (int k = 0; k < 32; k++) desc[(size_t)i * 32 + k] = d.ptr()[k];
+        }
+        for (int i = 0; i < nC; i++) taken[i] = CurrentFrame.mvpMapPoints[i] != NULL;
+        orbm_last_frame L = {n, wp.data(), flags.data(), lvl.data(), ang.data(), desc.data()};
+        orbm_cur_frame Cf = {nC, (const orbx_kp*)CurrentFrame.mvKeysUn.data(), nullptr, CurrentFrame.mDescriptors.ptr(), taken.data()};
+        std::vector<int32_t> curMatch(nC), kfMatch(n);
+        std::vector<uint8_t> keep(n);
+        int nmatches = 0;
+        check(orbm_search_by_projection(tls(), &P, &L, &Cf, curMatch.data(), kfMatch.data(), keep.data(), &nmatches),
+              "orbm_search_by_projection");
+        for (int i2 = 0; i2 < nC; i2++)
+            if (curMatch[i2] >= 0) CurrentFrame.mvpMapPoints[i2] = vpMPs[curMatch[i2]];
+        return nmatches;
+    }
+
     // ORBmatcher::SearchByFboW(KeyFrame* pKF, Frame& F, std::vector<MapPoint*>& vpMapPointMatches)
     // (src/ORBmatcher.cc:157-283; TrackReferenceKeyFrame src/Tracking.cc:867, Relocalization :1476) on the device.
     // FeatVecT is fbow::fBow2 (std::map<uint32_t, std::vector<uint32_t>>).

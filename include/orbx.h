@@ -168,6 +168,8 @@ typedef struct {
     float th;                      /* window factor */
     int th_high;                   /* ORBmatcher::TH_HIGH (100) */
     int check_orientation;         /* mbCheckOrientation */
+    int skip_depth_test;           /* 0: `if(invzc<0) continue` (src/ORBmatcher.cc:1360-1361); 1: the KeyFrame overload
+                                      used by Relocalization has no such test (src/ORBmatcher.cc:1494-1505) */
 } orbm_proj_params;
 
 typedef struct {              /* LastFrame: n keypoints */
@@ -191,6 +193,12 @@ typedef struct {              /* CurrentFrame: n keypoints */
  * last_match[i]  (last->n) keypoint i2 claimed by last-frame point i before the rotation filter, -1 = none
  * last_keep[i]   (last->n) 1 if that claim survived the rotation-consistency filter
  * nmatches       the function's return value (host pointer) */
+/* The same entry point serves ORBmatcher::SearchByProjection(Frame& CurrentFrame, KeyFrame* pKF, const set<MapPoint*>&
+ * sAlreadyFound, float th, int ORBdist) (src/ORBmatcher.cc:1468-1595; Tracking::Relocalization src/Tracking.cc:1552,
+ * 1566): `last` holds pKF's map points with flags bit 0 = usable (not bad, not in sAlreadyFound, dist3D inside the
+ * point's scale-invariance range) and bit 1 set, octave[i] = pMP->PredictScale(dist3D, &CurrentFrame) (host: it is a
+ * logarithm per point), angle[i] = pKF->mvKeysUn[i].angle; forward = backward = 0, th_high = ORBdist,
+ * skip_depth_test = 1, u_right = NULL, taken[i2] = CurrentFrame.mvpMapPoints[i2] != NULL. */
 int orbm_search_by_projection(orbm_t* m, const orbm_proj_params* p, const orbm_last_frame* last,
                               const orbm_cur_frame* cur, int32_t* cur_match, int32_t* last_match, uint8_t* last_keep,
                               int* nmatches);

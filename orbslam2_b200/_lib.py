@@ -44,7 +44,7 @@ class ProjParams(C.Structure):
                 ("grid_w_inv", C.c_float), ("grid_h_inv", C.c_float), ("nlevels", C.c_int),
                 ("scale", C.c_float * 16), ("Rcw", C.c_float * 9), ("tcw", C.c_float * 3),
                 ("forward", C.c_int), ("backward", C.c_int), ("th", C.c_float), ("th_high", C.c_int),
-                ("check_orientation", C.c_int)]
+                ("check_orientation", C.c_int), ("skip_depth_test", C.c_int)]
 
 
 class LastFrameArgs(C.Structure):

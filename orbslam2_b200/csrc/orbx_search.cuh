@@ -137,7 +137,7 @@ __device__ __forceinline__ SpQuery sp_query(const SpDev& S, int i) {
         c3[r] = __fadd_rn((float)acc, S.p.tcw[r]);
     }
     q.invzc = (float)(1.0 / (double)c3[2]);
-    if (q.invzc < 0) return q;
+    if (q.invzc < 0 && !S.p.skip_depth_test) return q;
     q.u = __fadd_rn(__fmul_rn(__fmul_rn(S.p.fx, c3[0]), q.invzc), S.p.cx);
     q.v = __fadd_rn(__fmul_rn(__fmul_rn(S.p.fy, c3[1]), q.invzc), S.p.cy);
     if (q.u < S.p.minX || q.u > S.p.maxX) return q;

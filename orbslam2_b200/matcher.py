@@ -153,6 +153,33 @@ class ORBmatcher:
                                                      lm.ctypes.data, lk.ctypes.data, C.byref(n)))
         return n.value, cm, lm, lk
 
+    def SearchByProjectionKF(self, CurrentFrame, kf, usable, predicted_level, th, ORBdist, taken=None):
+        """ORBmatcher::SearchByProjection(Frame &CurrentFrame, KeyFrame *pKF, const set<MapPoint*> &sAlreadyFound, th,
+        ORBdist) (src/ORBmatcher.cc:1468-1595, Tracking::Relocalization) on the device. `kf` is a Frame mirror of pKF
+        (map-point positions, descriptors, mvKeysUn angles); usable[i] = map point present, not bad, not in sAlreadyFound
+        and dist3D inside its scale-invariance range; predicted_level[i] = pMP->PredictScale(dist3D, &CurrentFrame)
+        (both host side: a norm and a logarithm per point); taken[i2] = CurrentFrame.mvpMapPoints[i2] != NULL.
+        Returns (nmatches, cur_match, kf_match, kf_keep) as SearchByProjection does."""
+        cur = CurrentFrame
+        P = self._proj_params(cur, kf, th, True)
+        P.forward = P.backward = 0
+        P.th_high, P.skip_depth_test = int(ORBdist), 1
+        keep = {"flags": (np.ascontiguousarray(usable, np.uint8) != 0).astype(np.uint8) | np.uint8(2),
+                "oct": np.ascontiguousarray(predicted_level, np.int32),
+                "ang": np.ascontiguousarray(kf.mvKeysUn["angle"], np.float32),
+                "wp": np.ascontiguousarray(kf.mp_world, np.float32), "ld": np.ascontiguousarray(kf.mp_desc, np.uint8),
+                "tk": None if taken is None else np.ascontiguousarray(taken, np.uint8)}
+        LA = _lib.LastFrameArgs(kf.N, keep["wp"].ctypes.data, keep["flags"].ctypes.data, keep["oct"].ctypes.data,
+                                keep["ang"].ctypes.data, keep["ld"].ctypes.data)
+        CA = _lib.CurFrameArgs(cur.N, cur.mvKeysUn.ctypes.data, None, cur.mDescriptors.ctypes.data,
+                               None if keep["tk"] is None else keep["tk"].ctypes.data)
+        cm = np.zeros(cur.N, np.int32); lm = np.zeros(kf.N, np.int32); lk = np.zeros(kf.N, np.uint8)
+        n = C.c_int()
+        self._set_space(_lib.MEM_HOST, _lib.MEM_HOST)
+        _lib.check(self._L.orbm_search_by_projection(self._h, C.byref(P), C.byref(LA), C.byref(CA), cm.ctypes.data,
+                                                     lm.ctypes.data, lk.ctypes.data, C.byref(n)))
+        return n.value, cm, lm, lk
+
     def SearchLocalPoints(self, F, mps, th=1.0, taken=None):
         """ORBmatcher::SearchByProjection(Frame &F, const vector<MapPoint*> &vpMapPoints, th) (src/ORBmatcher.cc:43-127)
         on the device. `mps` is a dict of arrays: proj_x, proj_y, proj_xr, level, view_cos, in_view (mbTrackInView &&

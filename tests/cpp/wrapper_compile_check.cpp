@@ -3,6 +3,7 @@
 // Usage: dropin_run <w> <h> <left.raw> <right.raw> <out.bin>   (raw 8-bit images); built and run by tests/test_gpu_dropin.py
 #include <cstdio>
 #include <cstdlib>
+#include <set>
 #include <vector>
 
 #include "dropin/ORBextractor.h"
@@ -123,6 +124,20 @@ struct TriKeyFrame : KeyFrame {
 };
 int instantiate5(ORB_SLAM2::ORBmatcher& m, TriKeyFrame* a, TriKeyFrame* b, cv::Mat F12, std::vector<std::pair<size_t, size_t> >& out) {
     return m.SearchForTriangulation(a, b, F12, out, false);
+}
+struct RelocMapPoint : MapPoint {
+    float GetMinDistanceInvariance() { return 0.f; }
+    float GetMaxDistanceInvariance() { return 1e9f; }
+    template <class F> int PredictScale(float, F*) { return 0; }
+};
+struct RelocFrame : Frame { std::vector<RelocMapPoint*> mvpMapPoints; };
+struct RelocKeyFrame {
+    std::vector<cv::KeyPoint> mvKeysUn;
+    std::vector<RelocMapPoint*> mps;
+    std::vector<RelocMapPoint*> GetMapPointMatches() { return mps; }
+};
+int instantiate6(ORB_SLAM2::ORBmatcher& m, RelocFrame& F, RelocKeyFrame* kf, const std::set<RelocMapPoint*>& found) {
+    return m.SearchByProjection(F, kf, found, 10.f, 100);
 }
 struct BowFrame : Frame { fbow::fBow2 mFbowFeatVec; };
 int instantiate3(ORB_SLAM2::ORBmatcher& m, KeyFrame* kf, BowFrame& F, std::vector<MapPoint*>& out) { return m.SearchByFboW(kf, F, out); }

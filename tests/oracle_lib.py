@@ -155,18 +155,21 @@ class OraclePrims:
                                        C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_float,
                                        C.c_void_p, C.c_void_p, C.c_void_p]
 
-    def search_by_projection(self, P, cur, last, taken=None):
+    def search_by_projection(self, P, cur, last, taken=None, flags=None, octave=None, no_uright=False):
         """Oracle of ORBmatcher::SearchByProjection(Frame&, const Frame&, th, bMono); P is the same ProjParams struct
         the C ABI takes (layout-identical to the oracle's OrcProj)."""
         L = self.lib
         L.orc_search_by_projection.restype = C.c_int
         L.orc_search_by_projection.argtypes = [C.c_void_p, C.c_int] + [C.c_void_p] * 5 + [C.c_int] + [C.c_void_p] * 10
-        flags = ((last.mp_valid != 0) & (last.mvbOutlier == 0)).astype(np.uint8) | ((last.mp_observed != 0).astype(np.uint8) << 1)
-        wp = np.ascontiguousarray(last.mp_world, np.float32); loct = np.ascontiguousarray(last.mvKeysUn["octave"], np.int32)
+        if flags is None:
+            flags = ((last.mp_valid != 0) & (last.mvbOutlier == 0)).astype(np.uint8) | ((last.mp_observed != 0).astype(np.uint8) << 1)
+        flags = np.ascontiguousarray(flags, np.uint8)
+        wp = np.ascontiguousarray(last.mp_world, np.float32)
+        loct = np.ascontiguousarray(last.mvKeysUn["octave"] if octave is None else octave, np.int32)
         lang = np.ascontiguousarray(last.mvKeysUn["angle"], np.float32); ld = np.ascontiguousarray(last.mp_desc, np.uint8)
         kx = np.ascontiguousarray(cur.mvKeysUn["x"], np.float32); ky = np.ascontiguousarray(cur.mvKeysUn["y"], np.float32)
         koct = np.ascontiguousarray(cur.mvKeysUn["octave"], np.int32); kang = np.ascontiguousarray(cur.mvKeysUn["angle"], np.float32)
-        ur = None if cur.mvuRight is None else np.ascontiguousarray(cur.mvuRight, np.float32)
+        ur = None if (cur.mvuRight is None or no_uright) else np.ascontiguousarray(cur.mvuRight, np.float32)
         tk = None if taken is None else np.ascontiguousarray(taken, np.uint8)
         cm = np.zeros(cur.N, np.int32); lm = np.zeros(last.N, np.int32); lk = np.zeros(last.N, np.uint8)
         n = L.orc_search_by_projection(C.addressof(P), last.N, _p(wp), _p(flags), _p(loct), _p(lang), _p(ld), cur.N, _p(kx),

@@ -110,3 +110,33 @@ def test_search_local_points_vs_oracle(seed, stereo, th, ratio):
     assert n == en and np.array_equal(cm, ecm) and np.array_equal(mm, emm)
     assert n > 200, "local points should be found"
     assert m.search_stats()[0] >= 2
+
+
+@pytest.mark.parametrize("seed,th,orbdist", [(0, 10.0, 100), (1, 3.0, 64), (2, 10.0, 100)])
+def test_relocalization_search_vs_oracle(seed, th, orbdist):
+    """ORBmatcher::SearchByProjection(Frame&, KeyFrame*, sAlreadyFound, th, ORBdist) (src/ORBmatcher.cc:1468-1595) through
+    the same entry point: host-predicted levels, window [l-1, l+1], no depth test, no stereo gate, any existing map
+    point blocks a keypoint, accept at ORBdist."""
+    import orbslam2_b200 as ob
+    rng = np.random.default_rng(100 + seed)
+    m = ob.ORBmatcher(0.9, True); P = OraclePrims()
+    kf, cur = synth_tracking_pair(1500, 20 + seed, stereo=True, motion=(0.04, 0.02, 0.06))
+    # PredictScale is the caller's job: here the keypoint's own octave jittered by -1..+1
+    lvl = np.clip(kf.mvKeysUn["octave"] + rng.integers(-1, 2, kf.N), 0, 7).astype(np.int32)
+    usable = ((kf.mp_valid != 0) & (rng.random(kf.N) < 0.85)).astype(np.uint8)   # bad / already found / out of range
+    taken = (rng.random(cur.N) < 0.2).astype(np.uint8)                            # CurrentFrame.mvpMapPoints[i2] set
+    if seed == 2:                                                                  # a pose that puts points behind the camera
+        T = cur.mTcw.copy(); T[2, 3] -= np.float32(4.0); cur.SetPose(T)
+    got = m.SearchByProjectionKF(cur, kf, usable, lvl, th, orbdist, taken=taken)
+    prm = m._proj_params(cur, kf, th, True)
+    prm.forward = prm.backward = 0
+    prm.th_high, prm.skip_depth_test = orbdist, 1
+    exp = P.search_by_projection(prm, cur, kf, taken=taken, flags=(usable != 0).astype(np.uint8) | np.uint8(2), octave=lvl,
+                                 no_uright=True)
+    assert got[0] == exp[0], f"nmatches {got[0]} vs {exp[0]}"
+    for g, e, name in zip(got[1:], exp[1:], ("cur_match", "kf_match", "kf_keep")):
+        assert np.array_equal(g, e), f"{name}: {(g != e).sum()} differ"
+    if seed < 2:
+        assert got[0] > 150
+    assert not (taken[got[1] >= 0]).any(), "keypoints that already had a map point must stay untouched"
+    m.close()
