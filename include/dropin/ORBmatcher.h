@@ -269,6 +269,83 @@ public:
         return nmatches;
     }
 
+    // ORBmatcher::Fuse(KeyFrame* pKF, const std::vector<MapPoint*>& vpMapPoints, const float th = 3.0)
+    // (src/ORBmatcher.cc:821-971; LocalMapping::SearchInNeighbors src/LocalMapping.cc:487,512). Projection and the gates
+    // that need MapPoint internals run on the host in the reference's arithmetic, the window search (grid,
+    // GetFeaturesInArea, octave and chi-square gates, Hamming scan) in orbm_fuse_search, the map mutations on the host
+    // in point order. (The Sim3 overload, :973-1096, uses the same entry point with check_chi2 = 0.)
+    template <class KeyFrameT, class MapPointT>
+    int Fuse(KeyFrameT* pKF, const std::vector<MapPointT*>& vpMapPoints, const float th = 3.0) {
+        const cv::Mat Rcw = pKF->GetRotation(), tcw = pKF->GetTranslation(), Ow = pKF->GetCameraCenter();
+        const float fx = pKF->fx, fy = pKF->fy, cx = pKF->cx, cy = pKF->cy, bf = pKF->mbf;
+        const int nMPs = (int)vpMapPoints.size(), nK = pKF->N;
+        std::vector<float> pu(nMPs, 0.f), pv(nMPs, 0.f), pur(nMPs, 0.f);
+        std::vector<int32_t> lvl(nMPs, 0);
+        std::vector<uint8_t> valid(nMPs, 0), desc((size_t)nMPs * 32, 0);
+        for (int i = 0; i < nMPs; i++) {
+            MapPointT* pMP = vpMapPoints[i];
+            if (!pMP || pMP->isBad()) continue;  // IsInKeyFrame is re-checked below: earlier fusions can change it
+            const cv::Mat p3Dw = pMP->GetWorldPos();
+            float pc[3], w[3];
+            for (int k = 0; k < 3; k++) w[k] = p3Dw.template at<float>(k, 0);
+            for (int r = 0; r < 3; r++) {  // Rcw*p3Dw + tcw: CV_32F product = double accumulation rounded once
+                double acc = 0;
+                for (int c = 0; c < 3; c++) acc += (double)Rcw.template at<float>(r, c) * (double)w[c];
+                pc[r] = (float)acc + tcw.template at<float>(r, 0);
+            }
+            if (pc[2] < 0.0f) continue;
+            const float invz = 1 / pc[2];
+            const float u = fx * (pc[0] * invz) + cx, v = fy * (pc[1] * invz) + cy;
+            if (!pKF->IsInImage(u, v)) continue;
+            double n2 = 0, dot = 0;
+            const cv::Mat Pn = pMP->GetNormal();
+            for (int k = 0; k < 3; k++) {
+                const float po = w[k] - Ow.template at<float>(k, 0);
+                n2 += (double)po * (double)po;
+                dot += (double)po * (double)Pn.template at<float>(k, 0);
+            }
+            const float dist3D = (float)std::sqrt(n2);
+            if (dist3D < pMP->GetMinDistanceInvariance() || dist3D > pMP->GetMaxDistanceInvariance()) continue;
+            if (dot < 0.5 * dist3D) continue;
+            lvl[i] = pMP->PredictScale(dist3D, pKF);
+            pu[i] = u; pv[i] = v; pur[i] = u - bf * invz;
+            valid[i] = 1;
+            const cv::Mat d = pMP->GetDescriptor();
+            for (int k = 0; k < 32; k++) desc[(size_t)i * 32 + k] = d.ptr()[k];
+        }
+        orbm_proj_params P = orbm_proj_params();
+        P.minX = pKF->mnMinX; P.maxX = pKF->mnMaxX; P.minY = pKF->mnMinY; P.maxY = pKF->mnMaxY;
+        P.grid_w_inv = pKF->mfGridElementWidthInv; P.grid_h_inv = pKF->mfGridElementHeightInv;
+        P.nlevels = (int)pKF->mvScaleFactors.size();
+        for (int i = 0; i < P.nlevels && i < ORBX_MAX_LEVELS; i++) P.scale[i] = pKF->mvScaleFactors[i];
+        P.th = th;
+        orbm_fuse_points pts = {nMPs, pu.data(), pv.data(), pur.data(), lvl.data(), valid.data(), desc.data()};
+        orbm_cur_frame kf = {nK, (const orbx_kp*)pKF->mvKeysUn.data(), pKF->mvuRight.empty() ? nullptr : pKF->mvuRight.data(),
+                             pKF->mDescriptors.ptr(), nullptr};
+        std::vector<int32_t> bestIdx(nMPs, -1);
+        std::vector<uint16_t> bestDist(nMPs, 256);
+        check(orbm_fuse_search(tls(), &P, pKF->mvInvLevelSigma2.data(), 1, &pts, &kf, bestIdx.data(), bestDist.data()),
+              "orbm_fuse_search");
+        int nFused = 0;
+        for (int i = 0; i < nMPs; i++) {
+            MapPointT* pMP = vpMapPoints[i];
+            if (!valid[i] || pMP->isBad() || pMP->IsInKeyFrame(pKF)) continue;
+            if (bestIdx[i] < 0 || bestDist[i] > TH_LOW) continue;
+            MapPointT* pMPinKF = pKF->GetMapPoint(bestIdx[i]);
+            if (pMPinKF) {
+                if (!pMPinKF->isBad()) {
+                    if (pMPinKF->Observations() > pMP->Observations()) pMP->Replace(pMPinKF);
+                    else pMPinKF->Replace(pMP);
+                }
+            } else {
+                pMP->AddObservation(pKF, bestIdx[i]);
+                pKF->AddMapPoint(pMP, bestIdx[i]);
+            }
+            nFused++;
+        }
+        return nFused;
+    }
+
     // ORBmatcher::SearchByFboW(KeyFrame* pKF, Frame& F, std::vector<MapPoint*>& vpMapPointMatches)
     // (src/ORBmatcher.cc:157-283; TrackReferenceKeyFrame src/Tracking.cc:867, Relocalization :1476) on the device.
     // FeatVecT is fbow::fBow2 (std::map<uint32_t, std::vector<uint32_t>>).

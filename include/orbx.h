@@ -244,6 +244,28 @@ int orbx_set_profiling(orbx_t* h, int on);
 const char* orbx_last_error_string(void);
 const char* orbx_version(void);
 
+/* The search half of ORBmatcher::Fuse(KeyFrame*, const vector<MapPoint*>&, th) (include/ORBmatcher.h:82,
+ * src/ORBmatcher.cc:821-971; LocalMapping::SearchInNeighbors src/LocalMapping.cc:487,512) and of
+ * Fuse(KeyFrame*, cv::Mat Scw, const vector<MapPoint*>&, th, vector<MapPoint*>&) (include/ORBmatcher.h:85,
+ * src/ORBmatcher.cc:973-1096; LoopClosing::SearchAndFuse src/LoopClosing.cc:633). The caller projects the points
+ * (positive depth, IsInImage, distance range, viewing angle, PredictScale need MapPoint internals) and passes
+ * valid / u / v / ur / level; the device builds the KeyFrame's grid, walks KeyFrame::GetFeaturesInArea(u, v,
+ * th*scale[level]) (src/KeyFrame.cc:563-602) in the reference's order, applies the octave gate [level-1, level], with
+ * check_chi2 the reprojection gates (stereo 7.8 / mono 5.99 on e2*inv_level_sigma2[octave]) and returns per point the
+ * best keypoint (first one on ties; -1 / 256 = none). The caller then applies `bestDist <= TH_LOW` and the map
+ * mutations in point order. p supplies minX..grid_h_inv, nlevels, scale[], th. */
+typedef struct {
+    int n;
+    const float* proj_x;  /* u */
+    const float* proj_y;  /* v */
+    const float* proj_xr; /* ur = u - bf*invz (first overload; ignored without check_chi2) */
+    const int32_t* level; /* nPredictedLevel */
+    const uint8_t* valid; /* every gate before GetFeaturesInArea passed */
+    const uint8_t* desc;  /* [n][32] pMP->GetDescriptor() */
+} orbm_fuse_points;
+int orbm_fuse_search(orbm_t* m, const orbm_proj_params* p, const float* inv_level_sigma2, int check_chi2,
+                     const orbm_fuse_points* pts, const orbm_cur_frame* kf, int32_t* best_idx, uint16_t* best_dist);
+
 /* ORBmatcher::SearchByFboW, both overloads (include/ORBmatcher.h:54-55, 71): KeyFrame vs Frame
  * (src/ORBmatcher.cc:157-283; Tracking::TrackReferenceKeyFrame / Relocalization) with strict = 0, th = TH_LOW, and
  * KeyFrame vs KeyFrame (src/ORBmatcher.cc:517-650; LoopClosing) with strict = 1. A side is a frame's descriptors,

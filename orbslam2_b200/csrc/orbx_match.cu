@@ -900,6 +900,68 @@ extern "C" int orbm_distinctive_descriptors(orbm_t* m, const uint8_t* desc, cons
 }
 
 /* Diagnostics of the last orbm_search_by_projection call: fixed-point rounds and candidate pairs evaluated. */
+extern "C" int orbm_fuse_search(orbm_t* m, const orbm_proj_params* p, const float* inv_level_sigma2, int check_chi2,
+                                const orbm_fuse_points* pts, const orbm_cur_frame* kf, int32_t* best_idx,
+                                uint16_t* best_dist) {
+    if (!m || !p || !pts || !kf || !inv_level_sigma2) FAIL(ORBX_EINVAL, "null argument");
+    const int n = pts->n, nC = kf->n;
+    if (n < 0 || nC < 0) FAIL(ORBX_EINVAL, "negative count");
+    if (n == 0) return ORBX_OK;
+    if (!pts->proj_x || !pts->proj_y || !pts->proj_xr || !pts->level || !pts->valid || !pts->desc || !best_idx || !best_dist ||
+        (nC && (!kf->keys_un || !kf->desc)))
+        FAIL(ORBX_EINVAL, "null array");
+    if (p->nlevels < 1 || p->nlevels > ORBX_MAX_LEVELS) FAIL(ORBX_EINVAL, "nlevels out of range");
+    CK(cudaSetDevice(m->device));
+    cudaStream_t st = m->stream;
+    const bool hin = m->inSpace == ORBX_MEM_HOST, hout = m->outSpace == ORBX_MEM_HOST;
+    const size_t need = (size_t)n * (4 * 4 + 1 + 32 + 4 + 2) + (size_t)nC * (28 + 4 + 32 + 4) + (size_t)SP_CELLS * 12 + 256 * 24;
+    int rc;
+    if ((rc = ensure(m->dWs, m->wsCap, need))) return rc;
+    if (hin && (rc = ensure_host_in(m, need))) return rc;
+    WsCursor W{m->dWs, 0};
+    Stager stg{m, &W, hin, (size_t)-1};
+    SpDev S;
+    memset(&S, 0, sizeof(S));
+    S.p = *p;
+    S.nCur = nC;
+    FuseDev F;
+    F.n = n;
+    F.u = (const float*)stg.in(pts->proj_x, (size_t)n * 4);
+    F.v = (const float*)stg.in(pts->proj_y, (size_t)n * 4);
+    F.ur = (const float*)stg.in(pts->proj_xr, (size_t)n * 4);
+    F.level = (const int32_t*)stg.in(pts->level, (size_t)n * 4);
+    F.valid = (const uint8_t*)stg.in(pts->valid, n);
+    F.desc = (const uint4*)stg.in(pts->desc, (size_t)n * 32);
+    S.keys = (const orbx_kp*)stg.in(kf->keys_un, (size_t)nC * sizeof(orbx_kp));
+    S.uRight = (const float*)stg.in(kf->u_right, (size_t)nC * 4);
+    S.cdesc = (const uint4*)stg.in(kf->desc, (size_t)nC * 32);
+    for (int i = 0; i < ORBX_MAX_LEVELS; i++) F.invSigma2[i] = i < p->nlevels ? inv_level_sigma2[i] : 0.f;
+    F.chi2 = check_chi2;
+    if ((((uintptr_t)F.desc) | ((uintptr_t)S.cdesc)) & 15) FAIL(ORBX_EINVAL, "device descriptor matrices must be 16-byte aligned");
+    if ((rc = stg.flush(st))) return rc;
+    int* cellCount = W.take<int>(SP_CELLS);
+    int* cellStart = W.take<int>(SP_CELLS + 1);
+    int* cursor = W.take<int>(SP_CELLS);
+    int* items = W.take<int>(std::max(nC, 1));
+    int32_t* oIdx = hout ? W.take<int32_t>(n) : best_idx;
+    unsigned short* oDist = hout ? W.take<unsigned short>(n) : best_dist;
+    if (W.off > m->wsCap) FAIL(ORBX_ECUDA, "internal: workspace estimate too small (%zu > %zu)", W.off, m->wsCap);
+    CK(cudaMemsetAsync(cellCount, 0, SP_CELLS * sizeof(int), st));
+    if (nC) k_sp_grid_count<<<(nC + 255) / 256, 256, 0, st>>>(S, cellCount);
+    k_sp_grid_scan<<<1, 1024, 0, st>>>(cellCount, cellStart, cursor);
+    if (nC) k_sp_grid_fill<<<(nC + 255) / 256, 256, 0, st>>>(S, cursor, items);
+    k_sp_grid_sort<<<(SP_CELLS + 255) / 256, 256, 0, st>>>(cellStart, items);
+    k_fuse_search<<<(n + 7) / 8, 256, 0, st>>>(S, F, cellStart, items, oIdx, oDist);
+    m->launches += 5;
+    CK(cudaGetLastError());
+    if (hout) {
+        CK(cudaMemcpyAsync(best_idx, oIdx, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(best_dist, oDist, (size_t)n * 2, cudaMemcpyDeviceToHost, st));
+    }
+    CK(cudaStreamSynchronize(st));
+    return ORBX_OK;
+}
+
 #include "orbx_bowsearch.cuh"
 
 extern "C" int orbm_search_stats(orbm_t* m, int* rounds, int64_t* candidates) {

@@ -418,6 +418,82 @@ __global__ void __launch_bounds__(1024) k_sp_finish_mp(SpDev S, const int* __res
     if (tid == 0) result[0] = nAcc;
 }
 
+// ---- ORBmatcher::Fuse: the search half (src/ORBmatcher.cc:821-971 and :973-1096) --------------------------------------
+// Per map point (projected on the host, where the MapPoint-internal gates live): KeyFrame::GetFeaturesInArea(u, v,
+// th*scale[level]) (src/KeyFrame.cc:563-602), octave in [level-1, level], the chi-square reprojection gates of the
+// first overload (stereo 7.8 / mono 5.99 on e2 * invSigma2[octave]; chi2 = 0 for the Sim3 overload), best Hamming
+// distance with the first candidate winning ties. No query depends on another one: the map mutations (Replace /
+// AddObservation) are applied by the caller in point order from (best_idx, best_dist).
+struct FuseDev {
+    int n;
+    const float *u, *v, *ur;
+    const int32_t* level;
+    const uint8_t* valid;
+    const uint4* desc;
+    float invSigma2[ORBX_MAX_LEVELS];
+    int chi2;
+};
+
+__global__ void __launch_bounds__(256) k_fuse_search(SpDev S, FuseDev F, const int* __restrict__ cellStart,
+                                                     const int* __restrict__ items, int32_t* __restrict__ bestIdx,
+                                                     unsigned short* __restrict__ bestDist) {
+    const int lane = threadIdx.x & 31;
+    const int i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (i >= F.n) return;
+    unsigned best = 0xFFFFFFFFu;  // (distance << 22) | visiting position
+    int bestI = -1;
+    if (F.valid[i]) {
+        const float u = F.u[i], v = F.v[i], ur = F.ur[i];
+        const int lvl = F.level[i];
+        const float r = __fmul_rn(S.p.th, S.p.scale[lvl]);
+        const int x0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(u, S.p.minX), r), S.p.grid_w_inv)));
+        const int x1 = min(SP_COLS - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(u, S.p.minX), r), S.p.grid_w_inv)));
+        const int y0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(v, S.p.minY), r), S.p.grid_h_inv)));
+        const int y1 = min(SP_ROWS - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(v, S.p.minY), r), S.p.grid_h_inv)));
+        if (x0 < SP_COLS && x1 >= 0 && y0 < SP_ROWS && y1 >= 0) {
+            const uint4 d0 = F.desc[2 * (size_t)i], d1 = F.desc[2 * (size_t)i + 1];
+            int pos = 0;
+            for (int ix = x0; ix <= x1; ix++) {
+                const int s = cellStart[ix * SP_ROWS + y0], e = cellStart[ix * SP_ROWS + y1 + 1];
+                for (int b = s; b < e; b += 32, pos += 32) {
+                    const int k = b + lane;
+                    if (k >= e) continue;
+                    const int i2 = items[k];
+                    const orbx_kp kp = S.keys[i2];
+                    if (!(fabsf(__fsub_rn(kp.x, u)) < r && fabsf(__fsub_rn(kp.y, v)) < r)) continue;
+                    if (kp.octave < lvl - 1 || kp.octave > lvl) continue;
+                    if (F.chi2) {
+                        const float ex = __fsub_rn(u, kp.x), ey = __fsub_rn(v, kp.y);
+                        const float kr = S.uRight ? S.uRight[i2] : -1.f;
+                        if (kr >= 0) {
+                            const float er = __fsub_rn(ur, kr);
+                            const float e2 = __fadd_rn(__fadd_rn(__fmul_rn(ex, ex), __fmul_rn(ey, ey)), __fmul_rn(er, er));
+                            if ((double)__fmul_rn(e2, F.invSigma2[kp.octave]) > 7.8) continue;
+                        } else {
+                            const float e2 = __fadd_rn(__fmul_rn(ex, ex), __fmul_rn(ey, ey));
+                            if ((double)__fmul_rn(e2, F.invSigma2[kp.octave]) > 5.99) continue;
+                        }
+                    }
+                    const unsigned d = (unsigned)hamming256(d0, d1, S.cdesc[2 * (size_t)i2], S.cdesc[2 * (size_t)i2 + 1]);
+                    const unsigned key = (d << 22) | (unsigned)(pos + lane);
+                    if (key < best) { best = key; bestI = i2; }
+                }
+            }
+        }
+    }
+    // warp arg-min: smallest distance, first in visiting order
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const unsigned ob = __shfl_xor_sync(0xffffffffu, best, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, bestI, o);
+        if (ob < best) { best = ob; bestI = oi; }
+    }
+    if (lane == 0) {
+        bestIdx[i] = bestI;
+        bestDist[i] = bestI >= 0 ? (unsigned short)(best >> 22) : (unsigned short)256;
+    }
+}
+
 // ---- batched MapPoint::ComputeDistinctiveDescriptors, /root/reference/src/MapPoint.cc:242-307 -------------------------
 // Per map point: all-pairs Hamming distances of its observations' descriptors, per row the median
 // vDists[0.5*(N-1)] of the sorted row (self distance 0 included), result = first row with the least median.

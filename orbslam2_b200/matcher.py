@@ -180,6 +180,32 @@ class ORBmatcher:
                                                      lm.ctypes.data, lk.ctypes.data, C.byref(n)))
         return n.value, cm, lm, lk
 
+    def FuseSearch(self, kf, pts, th=3.0, check_chi2=True):
+        """Search half of ORBmatcher::Fuse (src/ORBmatcher.cc:821-971; check_chi2 False: the Sim3 overload :973-1096).
+        kf: Frame mirror of the KeyFrame (mvKeysUn, mvuRight, mDescriptors, grid constants, mvScaleFactors); pts: dict
+        of arrays u, v, ur, level, valid, desc for the map points the caller projected. Returns (best_idx, best_dist);
+        the caller fuses where best_dist <= TH_LOW, in point order."""
+        P = _lib.ProjParams()
+        P.minX, P.maxX, P.minY, P.maxY = float(kf.mnMinX), float(kf.mnMaxX), float(kf.mnMinY), float(kf.mnMaxY)
+        P.grid_w_inv, P.grid_h_inv = float(kf.mfGridElementWidthInv), float(kf.mfGridElementHeightInv)
+        P.nlevels = len(kf.mvScaleFactors)
+        for i, v in enumerate(kf.mvScaleFactors):
+            P.scale[i] = float(v)
+        P.th = float(th)
+        inv_sigma2 = (np.float32(1.0) / (kf.mvScaleFactors * kf.mvScaleFactors)).astype(np.float32)
+        a = {k: np.ascontiguousarray(pts[k], t) for k, t in (("u", np.float32), ("v", np.float32), ("ur", np.float32),
+                                                              ("level", np.int32), ("valid", np.uint8), ("desc", np.uint8))}
+        n = len(a["u"])
+        FP = _lib.FusePoints(n, a["u"].ctypes.data, a["v"].ctypes.data, a["ur"].ctypes.data, a["level"].ctypes.data,
+                             a["valid"].ctypes.data, a["desc"].ctypes.data)
+        CA = _lib.CurFrameArgs(kf.N, kf.mvKeysUn.ctypes.data, None if kf.mvuRight is None else kf.mvuRight.ctypes.data,
+                               kf.mDescriptors.ctypes.data, None)
+        bi, bd = np.full(n, -1, np.int32), np.full(n, 256, np.uint16)
+        self._set_space(_lib.MEM_HOST, _lib.MEM_HOST)
+        _lib.check(self._L.orbm_fuse_search(self._h, C.byref(P), inv_sigma2.ctypes.data, int(check_chi2), C.byref(FP),
+                                            C.byref(CA), bi.ctypes.data, bd.ctypes.data))
+        return bi, bd, P, inv_sigma2
+
     def SearchLocalPoints(self, F, mps, th=1.0, taken=None):
         """ORBmatcher::SearchByProjection(Frame &F, const vector<MapPoint*> &vpMapPoints, th) (src/ORBmatcher.cc:43-127)
         on the device. `mps` is a dict of arrays: proj_x, proj_y, proj_xr, level, view_cos, in_view (mbTrackInView &&

@@ -139,6 +139,30 @@ struct RelocKeyFrame {
 int instantiate6(ORB_SLAM2::ORBmatcher& m, RelocFrame& F, RelocKeyFrame* kf, const std::set<RelocMapPoint*>& found) {
     return m.SearchByProjection(F, kf, found, 10.f, 100);
 }
+struct FuseKeyFrame;
+struct FuseMapPoint : RelocMapPoint {
+    cv::Mat normal;
+    cv::Mat GetNormal() { return normal; }
+    bool IsInKeyFrame(FuseKeyFrame*) { return false; }
+    void Replace(FuseMapPoint*) {}
+    void AddObservation(FuseKeyFrame*, int) {}
+};
+struct FuseKeyFrame {
+    int N = 0;
+    float fx = 0, fy = 0, cx = 0, cy = 0, mbf = 0, mnMinX = 0, mnMaxX = 0, mnMinY = 0, mnMaxY = 0;
+    float mfGridElementWidthInv = 0, mfGridElementHeightInv = 0;
+    std::vector<float> mvScaleFactors, mvInvLevelSigma2, mvuRight;
+    std::vector<cv::KeyPoint> mvKeysUn;
+    cv::Mat mDescriptors, R, t, Ow;
+    std::vector<FuseMapPoint*> mps;
+    cv::Mat GetRotation() { return R; }
+    cv::Mat GetTranslation() { return t; }
+    cv::Mat GetCameraCenter() { return Ow; }
+    bool IsInImage(float x, float y) { return x >= mnMinX && x < mnMaxX && y >= mnMinY && y < mnMaxY; }
+    FuseMapPoint* GetMapPoint(int i) { return mps[i]; }
+    void AddMapPoint(FuseMapPoint* p, int i) { mps[i] = p; }
+};
+int instantiate7(ORB_SLAM2::ORBmatcher& m, FuseKeyFrame* kf, const std::vector<FuseMapPoint*>& v) { return m.Fuse(kf, v, 3.0f); }
 struct BowFrame : Frame { fbow::fBow2 mFbowFeatVec; };
 int instantiate3(ORB_SLAM2::ORBmatcher& m, KeyFrame* kf, BowFrame& F, std::vector<MapPoint*>& out) { return m.SearchByFboW(kf, F, out); }
 int instantiate4(ORB_SLAM2::ORBmatcher& m, KeyFrame* a, KeyFrame* b, std::vector<MapPoint*>& out) { return m.SearchByFboW(a, b, out); }

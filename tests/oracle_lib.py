@@ -447,3 +447,21 @@ def oracle_search_for_triangulation(a, b, geo, th, check_ori):
                                        _p(g["stereo_b"]), _p(g["F12"]), np.float32(geo["ex"]), np.float32(geo["ey"]),
                                        _p(g["scale_factors"]), _p(g["level_sigma2"]), th, int(check_ori), _p(match))
     return n, match
+
+
+def oracle_fuse_search(P, inv_sigma2, chi2, pts, kf):
+    """orc_fuse_search; P = the ProjParams the C ABI took (layout-identical to OrcProj)."""
+    build_oracle()
+    L = _load(ORACLE_SO)
+    L.orc_fuse_search.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int] + [C.c_void_p] * 6 + [C.c_int] + [C.c_void_p] * 7
+    a = {k: np.ascontiguousarray(pts[k], t) for k, t in (("u", np.float32), ("v", np.float32), ("ur", np.float32),
+                                                          ("level", np.int32), ("valid", np.uint8), ("desc", np.uint8))}
+    n = len(a["u"])
+    kx = np.ascontiguousarray(kf.mvKeysUn["x"], np.float32); ky = np.ascontiguousarray(kf.mvKeysUn["y"], np.float32)
+    ko = np.ascontiguousarray(kf.mvKeysUn["octave"], np.int32)
+    ur = None if kf.mvuRight is None else np.ascontiguousarray(kf.mvuRight, np.float32)
+    bi, bd = np.full(n, -1, np.int32), np.full(n, 256, np.uint16)
+    L.orc_fuse_search(C.addressof(P), _p(inv_sigma2), int(chi2), n, _p(a["u"]), _p(a["v"]), _p(a["ur"]), _p(a["level"]),
+                      _p(a["valid"]), _p(a["desc"]), kf.N, _p(kx), _p(ky), _p(ko), None if ur is None else _p(ur),
+                      _p(kf.mDescriptors), _p(bi), _p(bd))
+    return bi, bd

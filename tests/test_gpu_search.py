@@ -140,3 +140,42 @@ def test_relocalization_search_vs_oracle(seed, th, orbdist):
         assert got[0] > 150
     assert not (taken[got[1] >= 0]).any(), "keypoints that already had a map point must stay untouched"
     m.close()
+
+
+@pytest.mark.parametrize("seed,stereo,th,chi2", [(0, True, 3.0, True), (1, False, 3.0, True), (2, True, 4.0, False), (3, True, 9.0, True)])
+def test_fuse_search_vs_oracle(seed, stereo, th, chi2):
+    """Search half of ORBmatcher::Fuse (both overloads): KeyFrame grid window, octave gate, chi-square gates, best
+    keypoint per map point (first wins ties) — bit-identical to the sequential restatement."""
+    import orbslam2_b200 as ob
+    from oracle_lib import oracle_fuse_search
+    rng = np.random.default_rng(300 + seed)
+    m = ob.ORBmatcher(0.6, True)
+    kf, other = synth_tracking_pair(1500, 30 + seed, stereo=stereo, motion=(0.03, 0.01, 0.05))
+    # map points seen from the other frame, "projected" near their true keypoints in kf (+ noise, + some far off)
+    n = other.N
+    src = rng.integers(0, kf.N, n)
+    u = kf.mvKeysUn["x"][src] + rng.normal(0, 1.2, n).astype(np.float32)
+    v = kf.mvKeysUn["y"][src] + rng.normal(0, 1.2, n).astype(np.float32)
+    far = rng.random(n) < 0.15
+    u[far] = rng.uniform(-30, 700, far.sum()); v[far] = rng.uniform(-30, 520, far.sum())
+    if stereo:
+        ur = (np.where(kf.mvuRight[src] >= 0, kf.mvuRight[src], u - 10) + rng.normal(0, 1.0, n)).astype(np.float32)
+    else:
+        ur = (u - rng.uniform(2, 40, n)).astype(np.float32)
+    desc = kf.mDescriptors[src].copy()
+    bits = np.unpackbits(desc, axis=1)
+    for _ in range(8):
+        bits[np.arange(n), rng.integers(0, 256, n)] ^= 1
+    desc = np.packbits(bits, axis=1)
+    pts = dict(u=u.astype(np.float32), v=v.astype(np.float32), ur=ur,
+               level=np.clip(kf.mvKeysUn["octave"][src] + rng.integers(0, 2, n), 0, 7).astype(np.int32),
+               valid=(rng.random(n) < 0.9).astype(np.uint8), desc=desc)
+    bi, bd, P, inv_s2 = m.FuseSearch(kf, pts, th=th, check_chi2=chi2)
+    ei, ed = oracle_fuse_search(P, inv_s2, chi2, pts, kf)
+    assert np.array_equal(bi, ei) and np.array_equal(bd, ed), f"{(bi != ei).sum()} best indices differ"
+    assert ((bd <= 50) & (bi >= 0)).sum() > 300, "most projected points must find their keypoint"
+    assert (bi[pts["valid"] == 0] == -1).all()
+    # empty sides
+    e = dict(u=np.zeros(0), v=np.zeros(0), ur=np.zeros(0), level=np.zeros(0), valid=np.zeros(0), desc=np.zeros((0, 32)))
+    assert len(m.FuseSearch(kf, e)[0]) == 0
+    m.close()
