@@ -925,10 +925,10 @@ extern "C" int orbx_stage_ms(orbx_t* h, float* ms7) {
 // accessors used by orbx_match.cu (stereo works on the extractor's resident state)
 struct OrbxView {
     const DevPlan* hp; DevPlan* dPlan; uint8_t* dPyr; orbx_kp* dKps; uint8_t* dDesc; int* dNOut; int lastBatch;
-    cudaStream_t stream; int device; int outSpace; int* hCounts;
+    cudaStream_t stream; int device; int outSpace; int* hCounts; const int* dSelCount;
 };
 OrbxView orbx_view(orbx_handle* h) {
     return OrbxView{&h->hp, h->dPlan, h->dPyr, h->dKps, h->dDesc, h->dNOut, h->lastBatch, h->stream, h->device, h->outSpace,
-                    h->hCounts};
+                    h->hCounts, h->dSelCount};
 }
 void orbx_count_launch(orbx_handle* h, int k) { h->launches += k; }

@@ -15,7 +15,7 @@
 struct orbx_handle;
 struct OrbxView {
     const DevPlan* hp; DevPlan* dPlan; uint8_t* dPyr; orbx_kp* dKps; uint8_t* dDesc; int* dNOut; int lastBatch;
-    cudaStream_t stream; int device; int outSpace; int* hCounts;
+    cudaStream_t stream; int device; int outSpace; int* hCounts; const int* dSelCount;
 };
 OrbxView orbx_view(orbx_handle* h);
 void orbx_count_launch(orbx_handle* h, int k);
@@ -161,10 +161,15 @@ __device__ __forceinline__ int reflect101_i(int p, int len) {
 // One warp per left keypoint. Candidate scan: every right keypoint whose row band [floor(y-r), ceil(y+r)],
 // r = 2*scale[octave], contains (int)vL, octave within +-1, uR in [uL-maxD, uL-minD]; best = strict '<' from TH_HIGH in
 // ascending right index (packed (dist, iR) minimum). Then the 11-shift SAD sweep on the un-blurred pyramids.
+// The right keypoints are stored level-major and, inside a level, by ascending y (the extractor's canonical order), and
+// the band radius is constant inside a level: so per octave the candidates are ONE contiguous run found by two binary
+// searches on y (a superset, (row - r - 1, row + r + 1); the exact band test is still applied) instead of a scan of all
+// right keypoints — the role of vRowIndices in the reference (src/Frame.cc:476-492).
 __global__ void __launch_bounds__(256) k_stereo_match(const DevPlan* __restrict__ P, const orbx_kp* __restrict__ kL,
                                                       const uint8_t* __restrict__ dL, const int* __restrict__ nL,
                                                       const uint8_t* __restrict__ pyrL, const orbx_kp* __restrict__ kR,
                                                       const uint8_t* __restrict__ dR, const int* __restrict__ nR,
+                                                      const int* __restrict__ selCountR,
                                                       const uint8_t* __restrict__ pyrR, float mbf, float minD, float maxD,
                                                       float* __restrict__ uRight, float* __restrict__ depth,
                                                       int* __restrict__ sad, int outStride) {
@@ -189,17 +194,48 @@ __global__ void __launch_bounds__(256) k_stereo_match(const DevPlan* __restrict_
     const uint4* qd = (const uint4*)(dL + (kb + iL) * 32);
     const uint4 q0 = qd[0], q1 = qd[1];
     u64 best = ((u64)100 << 32) | 0xFFFFFFFFull;  // ORBmatcher::TH_HIGH
-    for (int iR = lane; iR < NR; iR += 32) {
-        const orbx_kp r = kR[kb + iR];
-        if (r.octave < levelL - 1 || r.octave > levelL + 1) continue;
-        const float rad = __fmul_rn(2.0f, P->lv[r.octave].scale);
-        const int maxr = (int)ceilf(__fadd_rn(r.y, rad)), minr = (int)floorf(__fsub_rn(r.y, rad));
-        if (row < minr || row > maxr) continue;
-        if (!(r.x >= minU && r.x <= maxU)) continue;
-        const uint4* td = (const uint4*)(dR + (kb + iR) * 32);
-        const int d = hamming256(q0, q1, td[0], td[1]);
-        const u64 k = ((u64)d << 32) | (unsigned)iR;
-        best = k < best ? k : best;
+    const int nl = P->nlevels;
+    int segStart = 0;
+    for (int l = 0; l < nl; l++) {
+        const int segEnd = min(NR, segStart + selCountR[f * nl + l]);
+        if (l >= levelL - 1 && l <= levelL + 1 && segEnd > segStart) {
+            const float rad = __fmul_rn(2.0f, P->lv[l].scale);
+            const float yLo = (float)row - rad - 1.001f, yHi = (float)row + rad + 1.001f;
+            // first index of the segment with y > yLo: 32-ary search, the lanes probe 32 evenly spaced keypoints per
+            // round (two dependent loads for a segment of <= 1024 keypoints instead of ten for a binary search)
+            int lo = segStart, len = segEnd - segStart;
+            while (len > 0) {
+                const int step = (len + 31) >> 5;
+                const int idx = lo + lane * step;
+                const bool pred = idx < lo + len ? (kR[kb + idx].y > yLo) : true;
+                const unsigned m = __ballot_sync(0xffffffffu, pred);
+                const int fl = m ? __ffs(m) - 1 : 32;
+                if (fl == 0) break;                       // the first probe already qualifies: answer = lo
+                const int end = lo + len;
+                lo = lo + (fl - 1) * step + 1;            // just after the last probe that failed
+                len = min(lo + step - 1, end) - lo;       // up to (not including) the first probe that passed
+            }
+            // the run is short (band of a few rows): walk it 32 keypoints at a time until y leaves the band
+            for (int base = lo; base < segEnd; base += 32) {
+                const int iR = base + lane;
+                const bool in = iR < segEnd;
+                orbx_kp r;
+                if (in) r = kR[kb + iR];
+                const bool beyond = in && r.y >= yHi;
+                if (in && !beyond && r.octave >= levelL - 1 && r.octave <= levelL + 1) {
+                    const float radr = __fmul_rn(2.0f, P->lv[r.octave].scale);
+                    const int maxr = (int)ceilf(__fadd_rn(r.y, radr)), minr = (int)floorf(__fsub_rn(r.y, radr));
+                    if (row >= minr && row <= maxr && r.x >= minU && r.x <= maxU) {
+                        const uint4* td = (const uint4*)(dR + (kb + iR) * 32);
+                        const int d = hamming256(q0, q1, td[0], td[1]);
+                        const u64 k = ((u64)d << 32) | (unsigned)iR;
+                        best = k < best ? k : best;
+                    }
+                }
+                if (__any_sync(0xffffffffu, beyond)) break;
+            }
+        }
+        segStart = segEnd;
     }
     best = shfl_min_u64(best);
     const int bestDist = (int)(best >> 32);
@@ -219,21 +255,28 @@ __global__ void __launch_bounds__(256) k_stereo_match(const DevPlan* __restrict_
     const uint8_t* IL = pyrL + G.pyrOff + (long long)f * G.frameStride;
     const uint8_t* IR = pyrR + G.pyrOff + (long long)f * G.frameStride;
     const int cL = IL[(long long)cy * G.pitch + cxL];
-    int acc[11];
+    int acc[11], cR[11];
+    // the 21 right-image columns cxR-10 .. cxR+10 lie inside the level for every keypoint the extractor can produce
+    // (keypoints keep 16 px from the border at their own level); the reflected path covers anything else
+    const bool inner = cxR - 2 * w >= 0 && cxR + 2 * w < G.w;
+    const uint8_t* crow = IR + (long long)cy * G.pitch;
 #pragma unroll
-    for (int s = 0; s < 11; s++) acc[s] = 0;
+    for (int s = 0; s < 11; s++) {
+        acc[s] = 0;
+        cR[s] = inner ? crow[cxR + s - L] : crow[reflect101_i(cxR + s - L, G.w)];  // centre of the window shifted by s-L
+    }
     for (int p = lane; p < 121; p += 32) {
         const int dy = p / 11 - w, dx = p % 11 - w;
         const int yy = min(max(cy + dy, 0), G.h - 1);
         const int a = IL[(long long)yy * G.pitch + cxL + dx] - cL;
         const uint8_t* rrow = IR + (long long)yy * G.pitch;
-        const uint8_t* crow = IR + (long long)cy * G.pitch;
+        if (inner) {
+            const uint8_t* rr = rrow + cxR + dx - L;  // 11 consecutive bytes: one per shift
 #pragma unroll
-        for (int s = 0; s < 11; s++) {
-            const int inc = s - L;
-            const int cR = crow[reflect101_i(cxR + inc, G.w)];
-            const int b = rrow[reflect101_i(cxR + inc + dx, G.w)] - cR;
-            acc[s] += abs(a - b);
+            for (int s = 0; s < 11; s++) acc[s] += abs(a - ((int)rr[s] - cR[s]));
+        } else {
+#pragma unroll
+            for (int s = 0; s < 11; s++) acc[s] += abs(a - ((int)rrow[reflect101_i(cxR + s - L + dx, G.w)] - cR[s]));
         }
     }
 #pragma unroll
@@ -610,7 +653,8 @@ extern "C" int orbx_stereo_match_batch(orbx_t* left, orbx_t* right, float mbf, f
     if (maxN > cap) FAIL(ORBX_ECAP, "cap_per_frame %d < %d left keypoints", cap, maxN);
     if (maxN == 0) maxN = 1;
     k_stereo_match<<<dim3((maxN + 7) / 8, batch), 256, 0, st>>>(A.dPlan, A.dKps, A.dDesc, A.dNOut, A.dPyr, B.dKps, B.dDesc,
-                                                               B.dNOut, B.dPyr, mbf, minD, maxD, oU, oZ, g_ss.dSad, oStride);
+                                                               B.dNOut, B.dSelCount, B.dPyr, mbf, minD, maxD, oU, oZ,
+                                                               g_ss.dSad, oStride);
     int P2 = 1;
     while (P2 < maxN) P2 <<= 1;
     k_stereo_cut<<<batch, 1024, (size_t)P2 * 8, st>>>(A.dPlan, A.dNOut, g_ss.dSad, oU, oZ, oStride, P2);
