@@ -165,13 +165,28 @@ class ORBextractor:
         return kps, desc, n
 
     def submit_batch(self, images, out):
-        """First half of extract_batch for host buffers (orbx_extract_batch_submit): enqueue and return. `images`
-        [B,H,W] uint8 and `out` = (kps [B,cap] KP_DTYPE or [B,cap,7] float32, desc [B,cap,32] uint8) are numpy arrays or
-        CPU torch tensors (pinned memory makes the copies asynchronous); they must stay alive until wait_batch()."""
+        """First half of extract_batch (orbx_extract_batch_submit): enqueue and return. `images` [B,H,W] uint8 and
+        `out` = (kps [B,cap] KP_DTYPE or [B,cap,7] float32, desc [B,cap,32] uint8) are numpy arrays or CPU torch tensors
+        (pinned memory makes the copies asynchronous), or all torch CUDA tensors; they must stay alive until wait_batch().
+        Two extractors submitted back to back run together on the device (left and right image of a stereo frame)."""
+        C_ = self._channels
+        if _is_torch(images) and images.is_cuda:  # device-resident batch: the same two halves with device pointers
+            import torch
+            kps, desc = out
+            assert images.dtype == torch.uint8 and images.is_contiguous() and kps.is_cuda and desc.is_cuda
+            B, H, W = images.shape[:3]
+            cap = desc.shape[1]
+            self._set_space(_lib.MEM_DEVICE, _lib.MEM_DEVICE)
+            torch.cuda.current_stream(images.device).synchronize()
+            _lib.check(self._L.orbx_extract_batch_submit(self._h, images.data_ptr(), B, W, H, W * C_, W * H * C_,
+                                                         kps.data_ptr(), desc.data_ptr(), cap))
+            self._pending = (images, out, np.zeros(B, np.int32))
+            self._last = (B,) + (self._out_size or (W, H))
+            return
+
         def view(a):
             return a.numpy() if _is_torch(a) else a
         images, kps, desc = view(images), view(out[0]), view(out[1])
-        C_ = self._channels
         assert images.dtype == np.uint8 and images.ndim == (3 if C_ == 1 else 4) and images.strides[-1] == 1
         assert C_ == 1 or (images.shape[3] == C_ and images.strides[2] == C_)
         B, H, W = images.shape[:3]

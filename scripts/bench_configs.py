@@ -89,8 +89,10 @@ def main():
         stream = torch.cuda.ExternalStream(exL.cuda_stream(), device=dev)
 
         def step():
-            _, _, nL = exL.extract_batch(dL, out=outL)
-            exR.extract_batch(dR, out=outR)
+            exL.submit_batch(dL, outL)   # both extractions in flight: the two handles' kernels interleave
+            exR.submit_batch(dR, outR)
+            _, _, nL = exL.wait_batch()
+            exR.wait_batch()
             u, z = ob.compute_stereo_matches(exL, exR, bf, 0.0, fx)
             return nL, u
 

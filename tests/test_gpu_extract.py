@@ -183,6 +183,31 @@ def test_extractor_ring_matches_blocking_call(ob):
     ex.close()
 
 
+def test_device_submit_wait_on_two_handles(ob):
+    """The halves with DEVICE buffers (torch CUDA tensors): left and right extractors of a stereo frame in flight
+    together (the reference runs them on two host threads, src/Frame.cc:75-78) return the bytes of the blocking call."""
+    import torch
+    p = _params(1000)
+    exL, exR = ob.ORBextractor(**p), ob.ORBextractor(**p)
+    L = np.stack([synth_image(640, 480, s) for s in range(6)])
+    R = np.stack([synth_image(640, 480, 10 + s) for s in range(6)])
+    refL, refR = exL.extract_batch(L), exR.extract_batch(R)
+    cap = exL.max_keypoints(640, 480)
+    dL, dR = torch.from_numpy(L).cuda(), torch.from_numpy(R).cuda()
+    outs = [(torch.zeros((6, cap, 7), dtype=torch.float32, device="cuda"),
+             torch.zeros((6, cap, 32), dtype=torch.uint8, device="cuda")) for _ in range(2)]
+    for _ in range(2):  # twice: the second round reuses every buffer
+        exL.submit_batch(dL, outs[0])
+        exR.submit_batch(dR, outs[1])
+        gotL, gotR = exL.wait_batch(), exR.wait_batch()
+        for (k, d, n), (k0, d0, n0) in ((gotL, refL), (gotR, refR)):
+            assert np.array_equal(n, n0)
+            k, d = k.cpu().numpy(), d.cpu().numpy()
+            for f in range(6):
+                assert k[f, :n[f]].tobytes() == k0[f, :n0[f]].tobytes() and np.array_equal(d[f, :n[f]], d0[f, :n0[f]])
+    exL.close(); exR.close()
+
+
 def test_4k_frame_all_stages(ob):
     """BASELINE config 5: 3840x2160, 8000 keypoints — every stage bit-exact at the largest shape (26 925 FAST cells,
     per-level quotas up to 1737, TMA tiles at the widest cell size)."""
