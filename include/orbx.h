@@ -266,6 +266,18 @@ typedef struct {
 int orbm_fuse_search(orbm_t* m, const orbm_proj_params* p, const float* inv_level_sigma2, int check_chi2,
                      const orbm_fuse_points* pts, const orbm_cur_frame* kf, int32_t* best_idx, uint16_t* best_dist);
 
+/* Replaces the search of ORBmatcher::SearchByProjection(KeyFrame* pKF, cv::Mat Scw, const vector<MapPoint*>& vpPoints,
+ * vector<MapPoint*>& vpMatched, int th) (include/ORBmatcher.h:64, src/ORBmatcher.cc:285-398; LoopClosing::ComputeSim3
+ * src/LoopClosing.cc:411, th = 10). As for Fuse the caller projects the points with Scw (pts->valid / proj_x / proj_y /
+ * level = nPredictedLevel; proj_xr is not read); the device builds pKF's grid, walks KeyFrame::GetFeaturesInArea(u, v,
+ * th*scale[level]), applies the octave gate [level-1, level] and the rule "skip keypoints with vpMatched[idx] set":
+ * kf->taken[idx] = vpMatched[idx] != NULL on entry, and every accepted point (bestDist <= p->th_high, pass TH_LOW)
+ * blocks its keypoint for the later points, exactly as the sequential loop does (fixed point, see
+ * orbm_search_by_projection). kf_match[idx] (kf->n) = index of the point newly written to vpMatched[idx], -1 = none;
+ * pt_match[i] (pts->n) = keypoint taken by point i, -1 = none; *nmatches = the function's return value. */
+int orbm_search_kf_projection(orbm_t* m, const orbm_proj_params* p, const orbm_fuse_points* pts, const orbm_cur_frame* kf,
+                              int32_t* kf_match, int32_t* pt_match, int* nmatches);
+
 /* ORBmatcher::SearchByFboW, both overloads (include/ORBmatcher.h:54-55, 71): KeyFrame vs Frame
  * (src/ORBmatcher.cc:157-283; Tracking::TrackReferenceKeyFrame / Relocalization) with strict = 0, th = TH_LOW, and
  * KeyFrame vs KeyFrame (src/ORBmatcher.cc:517-650; LoopClosing) with strict = 1. A side is a frame's descriptors,

@@ -745,6 +745,7 @@ static int sp_run(orbm_handle* m, int mode, const orbm_proj_params* p, float nnR
         FAIL(ORBX_EINVAL, "null array");
     if (nL && mode == 0 && (!last->world_pos || !last->angle || !last_keep)) FAIL(ORBX_EINVAL, "null array");
     if (nL && mode == 1 && (!last->proj_x || !last->proj_y || !last->proj_xr || !last->view_cos)) FAIL(ORBX_EINVAL, "null array");
+    if (nL && mode == 2 && (!last->proj_x || !last->proj_y)) FAIL(ORBX_EINVAL, "null array");
     if (p->nlevels < 1 || p->nlevels > ORBX_MAX_LEVELS) FAIL(ORBX_EINVAL, "nlevels out of range");
     if (nL > (1 << 20) || nC > (1 << 20)) FAIL(ORBX_EINVAL, "frame too large");
     *nmatches = 0;
@@ -812,7 +813,7 @@ static int sp_run(orbm_handle* m, int mode, const orbm_proj_params* p, float nnR
     int* flags = W.take<int>(maxRounds);
     int32_t* oCur = hout ? W.take<int32_t>(nC) : cur_match;
     int32_t* oLast = hout ? W.take<int32_t>(nL) : last_match;
-    uint8_t* oKeep = (hout && last_keep) ? W.take<uint8_t>(nL) : last_keep;
+    uint8_t* oKeep = ((hout && last_keep) || (mode == 2 && !last_keep)) ? W.take<uint8_t>(nL) : last_keep;
     if (W.off > m->wsCap) FAIL(ORBX_ECUDA, "internal: workspace estimate too small (%zu > %zu)", W.off, m->wsCap);
 
     // S1 grid
@@ -845,7 +846,7 @@ static int sp_run(orbm_handle* m, int mode, const orbm_proj_params* p, float nnR
         for (int r = 0; r < R; r++, round++) {
             CK(cudaMemsetAsync(owner, 0x7F, (size_t)nC * sizeof(int), st));
             k_sp_claim<<<(nL + 255) / 256, 256, 0, st>>>(S, choice, owner, flags, round);
-            if (mode == 0) k_sp_choose<<<qBlocks, 256, 0, st>>>(S, candOff, candIdx, candDist, choice, owner, flags, round);
+            if (mode != 1) k_sp_choose<<<qBlocks, 256, 0, st>>>(S, candOff, candIdx, candDist, choice, owner, flags, round);
             else k_sp_choose_mp<<<(nL + 255) / 256, 256, 0, st>>>(S, candOff, candIdx, candDist, choice, owner, flags, round);
             m->launches += 2;
         }
@@ -857,7 +858,7 @@ static int sp_run(orbm_handle* m, int mode, const orbm_proj_params* p, float nnR
         if (rounds < round) break;  // round `rounds` changed nothing: fixed point reached
     }
     rounds++;  // the confirming round
-    if (mode == 0) k_sp_finish<<<1, 1024, 0, st>>>(S, choice, oCur, oLast, oKeep, dRes);
+    if (mode != 1) k_sp_finish<<<1, 1024, 0, st>>>(S, choice, oCur, oLast, oKeep, dRes);
     else k_sp_finish_mp<<<1, 1024, 0, st>>>(S, choice, oCur, oLast, dRes);
     m->launches += 2;
     CK(cudaGetLastError());
@@ -887,6 +888,17 @@ extern "C" int orbm_search_local_points(orbm_t* m, const orbm_proj_params* p, fl
     if (!m || !p || !mps || !cur || !nmatches) FAIL(ORBX_EINVAL, "null argument");
     SpHostQueries Q = {mps->n, nullptr, mps->flags, mps->level, nullptr, mps->desc, mps->proj_x, mps->proj_y, mps->proj_xr, mps->view_cos};
     return sp_run(m, 1, p, nn_ratio, &Q, cur, cur_match, mp_match, nullptr, nmatches);
+}
+
+extern "C" int orbm_search_kf_projection(orbm_t* m, const orbm_proj_params* p, const orbm_fuse_points* pts,
+                                        const orbm_cur_frame* kf, int32_t* kf_match, int32_t* pt_match, int* nmatches) {
+    if (!m || !p || !pts || !kf || !nmatches) FAIL(ORBX_EINVAL, "null argument");
+    orbm_proj_params P = *p;
+    P.check_orientation = 0;  // the reference applies no rotation filter here
+    SpHostQueries Q = {pts->n, nullptr, pts->valid, pts->level, nullptr, pts->desc, pts->proj_x, pts->proj_y, nullptr, nullptr};
+    orbm_cur_frame K = *kf;
+    K.u_right = nullptr;  // no stereo gate in this search
+    return sp_run(m, 2, &P, 0.f, &Q, &K, kf_match, pt_match, nullptr, nmatches);
 }
 
 extern "C" int orbm_distinctive_descriptors(orbm_t* m, const uint8_t* desc, const int32_t* off, int npoints,

@@ -29,6 +29,8 @@ struct SpDev {  // device copies of the call's arrays
     int nLast, nCur;
     const float* worldPos; const uint8_t* lflags; const int32_t* loct; const float* langle; const uint4* ldesc;
     const orbx_kp* keys; const float* uRight; const uint4* cdesc; const uint8_t* taken;
+    // mode 2 = SearchByProjection(KeyFrame*, Scw, vpPoints, vpMatched, th): host-projected points (projX/projY, loct =
+    // nPredictedLevel), radius th*scale[level], octave gate [level-1, level], every claim blocks later points
     // mode 1 = SearchByProjection(Frame&, vector<MapPoint*>, th): the queries come with their tracking projection
     // (MapPoint::mTrackProjX/Y/XR, mnTrackScaleLevel, mTrackViewCos set by Frame::isInFrustum, src/Frame.cc:256-326)
     int mode;
@@ -115,7 +117,16 @@ __device__ __forceinline__ SpQuery sp_query(const SpDev& S, int i) {
     SpQuery q;
     q.valid = false;
     if (!(S.lflags[i] & 1)) return q;
-    if (S.mode == 1) {  // src/ORBmatcher.cc:58-68
+    if (S.mode == 2) {  // SearchByProjection(KeyFrame*, Scw, vpPoints, vpMatched, th): src/ORBmatcher.cc:349-352, 375
+        const int lvl = S.loct[i];
+        q.radius = __fmul_rn(S.p.th, S.p.scale[lvl]);
+        q.u = S.projX[i];
+        q.v = S.projY[i];
+        q.ur = 0.f;
+        q.invzc = 0.f;
+        q.minLevel = lvl - 1;
+        q.maxLevel = lvl;
+    } else if (S.mode == 1) {  // src/ORBmatcher.cc:58-68
         const int lvl = S.loct[i];
         float r = (double)S.viewCos[i] > 0.998 ? 2.5f : 4.0f;  // RadiusByViewingCos, :129-135 (compares in double)
         if (S.p.th != 1.0f) r = __fmul_rn(r, S.p.th);
@@ -264,7 +275,8 @@ __global__ void k_sp_claim(SpDev S, const int* __restrict__ choice, int* __restr
     // owner[i2] = lowest-index query that claimed i2 in the previous round with a point that blocks later queries
     // (CurrentFrame.mvpMapPoints[i2]->Observations() > 0, src/ORBmatcher.cc:1399-1401)
     const int c = choice[i];
-    if (c >= 0 && (S.lflags[i] & 2)) atomicMin(&owner[c], i);
+    // (mode 2: vpMatched[bestIdx] = pMP blocks every later point, src/ORBmatcher.cc:370, 391)
+    if (c >= 0 && ((S.lflags[i] & 2) || S.mode == 2)) atomicMin(&owner[c], i);
 }
 
 __global__ void __launch_bounds__(256) k_sp_choose(SpDev S, const int* __restrict__ candOff, const int* __restrict__ candIdx,

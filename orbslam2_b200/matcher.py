@@ -206,6 +206,55 @@ class ORBmatcher:
                                             C.byref(CA), bi.ctypes.data, bd.ctypes.data))
         return bi, bd, P, inv_sigma2
 
+    def _kf_grid_params(self, kf, th):
+        P = _lib.ProjParams()
+        P.minX, P.maxX, P.minY, P.maxY = float(kf.mnMinX), float(kf.mnMaxX), float(kf.mnMinY), float(kf.mnMaxY)
+        P.grid_w_inv, P.grid_h_inv = float(kf.mfGridElementWidthInv), float(kf.mfGridElementHeightInv)
+        P.nlevels = len(kf.mvScaleFactors)
+        for i, v in enumerate(kf.mvScaleFactors):
+            P.scale[i] = float(v)
+        P.th = float(th)
+        return P
+
+    def SearchByProjectionSim3(self, kf, pts, th=10, taken=None):
+        """ORBmatcher::SearchByProjection(KeyFrame* pKF, cv::Mat Scw, vpPoints, vpMatched, int th)
+        (src/ORBmatcher.cc:285-398; LoopClosing::ComputeSim3) on the device. kf: Frame mirror of pKF; pts: dict of arrays
+        u, v, level, valid, desc for the points the caller projected with Scw; taken[idx] = vpMatched[idx] != NULL on
+        entry. Returns (nmatches, kf_match, pt_match, P): kf_match[idx] = point now in vpMatched[idx], -1 = unchanged."""
+        P = self._kf_grid_params(kf, th)
+        P.th_high = self.TH_LOW
+        a = {k: np.ascontiguousarray(pts[k], t) for k, t in (("u", np.float32), ("v", np.float32), ("level", np.int32),
+                                                              ("valid", np.uint8), ("desc", np.uint8))}
+        n = len(a["u"])
+        tk = None if taken is None else np.ascontiguousarray(taken, np.uint8)
+        FP = _lib.FusePoints(n, a["u"].ctypes.data, a["v"].ctypes.data, None, a["level"].ctypes.data,
+                             a["valid"].ctypes.data, a["desc"].ctypes.data)
+        CA = _lib.CurFrameArgs(kf.N, kf.mvKeysUn.ctypes.data, None, kf.mDescriptors.ctypes.data,
+                               None if tk is None else tk.ctypes.data)
+        km, pm = np.full(kf.N, -1, np.int32), np.full(n, -1, np.int32)
+        nm = C.c_int()
+        self._set_space(_lib.MEM_HOST, _lib.MEM_HOST)
+        _lib.check(self._L.orbm_search_kf_projection(self._h, C.byref(P), C.byref(FP), C.byref(CA), km.ctypes.data,
+                                                     pm.ctypes.data, C.byref(nm)))
+        return nm.value, km, pm, P
+
+    def SearchBySim3(self, kf1, kf2, pts1_in_2, pts2_in_1, th=7.5):
+        """The two window searches of ORBmatcher::SearchBySim3 (src/ORBmatcher.cc:1098-1322) and the mutual-agreement
+        step (:1303-1319). pts1_in_2: KF1's map points projected into KF2 with the Sim3 (dict u, v, level, valid, desc;
+        entry i belongs to keypoint i of KF1, valid = has a point, not bad, not already matched, gates passed);
+        pts2_in_1 likewise. Returns (nFound, match12) with match12[i1] = keypoint of KF2 agreed by both directions."""
+        def one(kf, pts):
+            p = dict(pts)
+            p["ur"] = np.zeros(len(p["u"]), np.float32)
+            bi, bd, _, _ = self.FuseSearch(kf, p, th=th, check_chi2=False)
+            return np.where(bd <= self.TH_HIGH, bi, -1)
+        m1 = one(kf2, pts1_in_2)
+        m2 = one(kf1, pts2_in_1)
+        i1 = np.arange(len(m1))
+        ok = (m1 >= 0) & (m2[np.clip(m1, 0, max(len(m2) - 1, 0))] == i1) if len(m2) else np.zeros(len(m1), bool)
+        match12 = np.where(ok, m1, -1).astype(np.int32)
+        return int(ok.sum()), match12
+
     def SearchLocalPoints(self, F, mps, th=1.0, taken=None):
         """ORBmatcher::SearchByProjection(Frame &F, const vector<MapPoint*> &vpMapPoints, th) (src/ORBmatcher.cc:43-127)
         on the device. `mps` is a dict of arrays: proj_x, proj_y, proj_xr, level, view_cos, in_view (mbTrackInView &&

@@ -465,3 +465,22 @@ def oracle_fuse_search(P, inv_sigma2, chi2, pts, kf):
                       _p(a["valid"]), _p(a["desc"]), kf.N, _p(kx), _p(ky), _p(ko), None if ur is None else _p(ur),
                       _p(kf.mDescriptors), _p(bi), _p(bd))
     return bi, bd
+
+
+def oracle_search_kf_projection(P, pts, kf, taken, th_low=50):
+    """orc_search_kf_projection; P = the ProjParams the C ABI took (layout-identical to OrcProj)."""
+    build_oracle()
+    L = _load(ORACLE_SO)
+    L.orc_search_kf_projection.argtypes = [C.c_void_p, C.c_int] + [C.c_void_p] * 5 + [C.c_int] + [C.c_void_p] * 5 + [C.c_int] + [C.c_void_p] * 2
+    L.orc_search_kf_projection.restype = C.c_int
+    a = {k: np.ascontiguousarray(pts[k], t) for k, t in (("u", np.float32), ("v", np.float32), ("level", np.int32),
+                                                          ("valid", np.uint8), ("desc", np.uint8))}
+    n = len(a["u"])
+    kx = np.ascontiguousarray(kf.mvKeysUn["x"], np.float32); ky = np.ascontiguousarray(kf.mvKeysUn["y"], np.float32)
+    ko = np.ascontiguousarray(kf.mvKeysUn["octave"], np.int32)
+    tk = None if taken is None else np.ascontiguousarray(taken, np.uint8)
+    km, pm = np.full(kf.N, -1, np.int32), np.full(n, -1, np.int32)
+    r = L.orc_search_kf_projection(C.addressof(P), n, _p(a["u"]), _p(a["v"]), _p(a["level"]), _p(a["valid"]), _p(a["desc"]),
+                                   kf.N, _p(kx), _p(ky), _p(ko), _p(kf.mDescriptors), None if tk is None else _p(tk),
+                                   int(th_low), _p(km), _p(pm))
+    return r, km, pm

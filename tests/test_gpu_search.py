@@ -179,3 +179,86 @@ def test_fuse_search_vs_oracle(seed, stereo, th, chi2):
     e = dict(u=np.zeros(0), v=np.zeros(0), ur=np.zeros(0), level=np.zeros(0), valid=np.zeros(0), desc=np.zeros((0, 32)))
     assert len(m.FuseSearch(kf, e)[0]) == 0
     m.close()
+
+
+def _projected_points(kf, n, rng, noise=1.2, flips=8, far_frac=0.15, dup_frac=0.0):
+    """Map points 'projected' near keypoints of kf: position noise, descriptor bit flips, some far off; with dup_frac
+    several points aim at the same keypoint (they compete for it in index order)."""
+    src = rng.integers(0, kf.N, n)
+    if dup_frac > 0:
+        d = rng.random(n) < dup_frac
+        src[d] = src[rng.integers(0, max(n // 8, 1), d.sum())]
+    u = kf.mvKeysUn["x"][src] + rng.normal(0, noise, n).astype(np.float32)
+    v = kf.mvKeysUn["y"][src] + rng.normal(0, noise, n).astype(np.float32)
+    far = rng.random(n) < far_frac
+    u[far] = rng.uniform(-30, 700, far.sum()); v[far] = rng.uniform(-30, 520, far.sum())
+    bits = np.unpackbits(kf.mDescriptors[src], axis=1)
+    for _ in range(flips):
+        bits[np.arange(n), rng.integers(0, 256, n)] ^= 1
+    return dict(u=u.astype(np.float32), v=v.astype(np.float32),
+                level=np.clip(kf.mvKeysUn["octave"][src] + rng.integers(0, 2, n), 0, 7).astype(np.int32),
+                valid=(rng.random(n) < 0.9).astype(np.uint8), desc=np.packbits(bits, axis=1)), src
+
+
+@pytest.mark.parametrize("seed,th,dup,with_taken", [(0, 10, 0.0, True), (1, 10, 0.6, False), (2, 4, 0.3, True), (3, 25, 0.8, True)])
+def test_search_kf_projection_vs_oracle(seed, th, dup, with_taken):
+    """ORBmatcher::SearchByProjection(KeyFrame*, Scw, vpPoints, vpMatched, th) (LoopClosing::ComputeSim3): KeyFrame grid
+    window, octave gate, 'skip vpMatched[idx]' with the claims of earlier points — bit-identical to the sequential loop,
+    also when most points compete for the same keypoints."""
+    import orbslam2_b200 as ob
+    from oracle_lib import oracle_search_kf_projection
+    rng = np.random.default_rng(500 + seed)
+    m = ob.ORBmatcher(0.75, True)
+    kf, _ = synth_tracking_pair(1500, 40 + seed, stereo=bool(seed & 1), motion=(0.03, 0.01, 0.05))
+    pts, _ = _projected_points(kf, 2500, rng, dup_frac=dup)
+    taken = (rng.random(kf.N) < 0.2).astype(np.uint8) if with_taken else None
+    n, km, pm, P = m.SearchByProjectionSim3(kf, pts, th=th, taken=taken)
+    en, ekm, epm = oracle_search_kf_projection(P, pts, kf, taken)
+    assert n == en and np.array_equal(km, ekm) and np.array_equal(pm, epm), f"{(pm != epm).sum()} point matches differ"
+    assert n > 400
+    if taken is not None:
+        assert not taken[km >= 0].any() and not taken[pm[pm >= 0]].any()
+    got = pm[pm >= 0]
+    assert len(np.unique(got)) == len(got), "a keypoint is claimed at most once"
+    # empty sides
+    e = dict(u=np.zeros(0), v=np.zeros(0), level=np.zeros(0), valid=np.zeros(0), desc=np.zeros((0, 32)))
+    assert m.SearchByProjectionSim3(kf, e)[0] == 0
+    m.close()
+
+
+@pytest.mark.parametrize("seed", [0, 1])
+def test_search_by_sim3_vs_oracle(seed):
+    """ORBmatcher::SearchBySim3: both window searches (octave gate, best <= TH_HIGH) and the mutual-agreement step."""
+    import orbslam2_b200 as ob
+    from oracle_lib import oracle_fuse_search
+    rng = np.random.default_rng(600 + seed)
+    m = ob.ORBmatcher(0.75, True)
+    kf1, kf2 = synth_tracking_pair(1200, 60 + seed, stereo=True, motion=(0.02, 0.01, 0.03))
+    # KF1's point i projected into KF2 (entry i <-> keypoint i of KF1) and the reverse; descriptors are the keypoints' own
+    def side(src_kf, dst_kf):
+        n = src_kf.N
+        p, src = _projected_points(dst_kf, n, rng, noise=1.0, flips=0, far_frac=0.1)
+        p["desc"] = np.ascontiguousarray(src_kf.mDescriptors)
+        # make about half of the pairs consistent: keypoint i of src really looks like keypoint src[i] of dst
+        return p, src
+    p12, s12 = side(kf1, kf2)
+    d1 = kf1.mDescriptors.copy(); half = rng.random(kf1.N) < 0.6
+    d1[half] = kf2.mDescriptors[s12[half]]
+    kf1.mDescriptors = np.ascontiguousarray(d1); p12["desc"] = kf1.mDescriptors
+    p21, s21 = side(kf2, kf1)
+    # the reverse projections of the consistent pairs land on their partner
+    inv = np.full(kf2.N, -1); inv[s12[half]] = np.nonzero(half)[0]
+    hit = inv >= 0
+    p21["u"][hit] = kf1.mvKeysUn["x"][inv[hit]]; p21["v"][hit] = kf1.mvKeysUn["y"][inv[hit]]
+    p21["level"][hit] = kf1.mvKeysUn["octave"][inv[hit]]
+    nf, m12 = m.SearchBySim3(kf1, kf2, p12, p21, th=7.5)
+    def orc(kf, pts):
+        P = m._kf_grid_params(kf, 7.5)
+        q = dict(pts); q["ur"] = np.zeros(len(q["u"]), np.float32)
+        bi, bd = oracle_fuse_search(P, np.ones(8, np.float32), 0, q, kf)
+        return np.where(bd <= 100, bi, -1)
+    e1, e2 = orc(kf2, p12), orc(kf1, p21)
+    exp = np.array([e1[i] if e1[i] >= 0 and e2[e1[i]] == i else -1 for i in range(kf1.N)], np.int32)
+    assert np.array_equal(m12, exp) and nf == int((exp >= 0).sum())
+    assert nf > 100
+    m.close()
