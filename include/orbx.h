@@ -278,6 +278,21 @@ int orbm_fuse_search(orbm_t* m, const orbm_proj_params* p, const float* inv_leve
 int orbm_search_kf_projection(orbm_t* m, const orbm_proj_params* p, const orbm_fuse_points* pts, const orbm_cur_frame* kf,
                               int32_t* kf_match, int32_t* pt_match, int* nmatches);
 
+/* Replaces ORBmatcher::SearchForInitialization(Frame& F1, Frame& F2, vector<cv::Point2f>& vbPrevMatched,
+ * vector<int>& vnMatches12, int windowSize) (include/ORBmatcher.h:68, src/ORBmatcher.cc:400-515;
+ * Tracking::MonocularInitialization src/Tracking.cc:699, windowSize = 100, ORBmatcher(0.9, true)). keys1 / desc1 =
+ * F1.mvKeysUn / F1.mDescriptors (n1 rows; only octave-0 keypoints query, :417); prev_matched = vbPrevMatched as n1 x 2
+ * floats, read as the window centres and UPDATED in place with F2.mvKeysUn[vnMatches12[i1]].pt for the final matches
+ * (:508-510); f2 = F2 (keys_un, desc; u_right / taken are not read). The device builds F2's grid, walks
+ * Frame::GetFeaturesInArea(x, y, windowSize, 0, 0) in the reference's order, and replays the claim loop in query order
+ * including `vMatchedDistance[i2] <= dist` (:439), the best / second-best ratio rule (:454-456, th_low = TH_LOW,
+ * nn_ratio = mfNNratio), the stealing of a keypoint from an earlier worse match (:458-466) and the rotation filter whose
+ * histogram also counts the stolen accepts (:468-505). p supplies minX..grid_h_inv and check_orientation.
+ * matches12[i1] (n1) = vnMatches12; *nmatches = the return value. */
+int orbm_search_for_initialization(orbm_t* m, const orbm_proj_params* p, float nn_ratio, int th_low, int window_size,
+                                   int n1, const orbx_kp* keys1, const uint8_t* desc1, float* prev_matched,
+                                   const orbm_cur_frame* f2, int32_t* matches12, int* nmatches);
+
 /* ORBmatcher::SearchByFboW, both overloads (include/ORBmatcher.h:54-55, 71): KeyFrame vs Frame
  * (src/ORBmatcher.cc:157-283; Tracking::TrackReferenceKeyFrame / Relocalization) with strict = 0, th = TH_LOW, and
  * KeyFrame vs KeyFrame (src/ORBmatcher.cc:517-650; LoopClosing) with strict = 1. A side is a frame's descriptors,

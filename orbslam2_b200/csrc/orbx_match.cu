@@ -8,6 +8,7 @@
 // K9  k_stereo_match   row-band Hamming search + 11x11 SAD sweep + parabola (ref: src/Frame.cc:506-625)
 // K10 k_stereo_cut     median outlier cut                      (ref: src/Frame.cc:628-641)
 #include <algorithm>
+#include <climits>
 #include <vector>
 
 #include "orbx_internal.cuh"
@@ -899,6 +900,98 @@ extern "C" int orbm_search_kf_projection(orbm_t* m, const orbm_proj_params* p, c
     orbm_cur_frame K = *kf;
     K.u_right = nullptr;  // no stereo gate in this search
     return sp_run(m, 2, &P, 0.f, &Q, &K, kf_match, pt_match, nullptr, nmatches);
+}
+
+extern "C" int orbm_search_for_initialization(orbm_t* m, const orbm_proj_params* p, float nn_ratio, int th_low,
+                                              int window_size, int n1, const orbx_kp* keys1, const uint8_t* desc1,
+                                              float* prev_matched, const orbm_cur_frame* f2, int32_t* matches12,
+                                              int* nmatches) {
+    if (!m || !p || !f2 || !nmatches) FAIL(ORBX_EINVAL, "null argument");
+    const int nL = n1, nC = f2->n;
+    if (nL < 0 || nC < 0) FAIL(ORBX_EINVAL, "negative count");
+    if ((nL && (!keys1 || !desc1 || !prev_matched || !matches12)) || (nC && (!f2->keys_un || !f2->desc)))
+        FAIL(ORBX_EINVAL, "null array");
+    if (nL > (1 << 20) || nC > (1 << 20)) FAIL(ORBX_EINVAL, "frame too large");
+    *nmatches = 0;
+    CK(cudaSetDevice(m->device));
+    cudaStream_t st = m->stream;
+    const bool hin = m->inSpace == ORBX_MEM_HOST, hout = m->outSpace == ORBX_MEM_HOST;
+    if (nL == 0) return ORBX_OK;
+    if (nC == 0) {  // vnMatches12 = all -1, vbPrevMatched untouched
+        if (hout) for (int i = 0; i < nL; i++) matches12[i] = -1;
+        else { CK(cudaMemsetAsync(matches12, 0xFF, (size_t)nL * 4, st)); CK(cudaStreamSynchronize(st)); }
+        return ORBX_OK;
+    }
+    const size_t need = (size_t)nL * (28 + 32 + 8 + 4 + 4 + 4 + 4 + 4 + 8) + (size_t)nC * (28 + 32 + 4 + 4 + 4) +
+                        (size_t)SP_CELLS * 12 + 256 * 32;
+    int rc;
+    if ((rc = ensure(m->dWs, m->wsCap, need))) return rc;
+    if (!m->hRes) CK(cudaMallocHost(&m->hRes, 4 * sizeof(int)));
+    if (hin && (rc = ensure_host_in(m, need))) return rc;
+    WsCursor W{m->dWs, 0};
+    Stager stg{m, &W, hin, (size_t)-1};
+    SpDev S;
+    memset(&S, 0, sizeof(S));
+    S.p = *p;
+    S.p.th = (float)window_size;  // GetFeaturesInArea(x, y, windowSize, 0, 0): the int becomes the float radius
+    S.nLast = nL;
+    S.nCur = nC;
+    S.mode = 3;
+    S.nnRatio = nn_ratio;
+    S.qkeys = (const orbx_kp*)stg.in(keys1, (size_t)nL * sizeof(orbx_kp));
+    S.ldesc = (const uint4*)stg.in(desc1, (size_t)nL * 32);
+    S.projX = (const float*)stg.in(prev_matched, (size_t)nL * 8);
+    S.keys = (const orbx_kp*)stg.in(f2->keys_un, (size_t)nC * sizeof(orbx_kp));
+    S.cdesc = (const uint4*)stg.in(f2->desc, (size_t)nC * 32);
+    if ((((uintptr_t)S.ldesc) | ((uintptr_t)S.cdesc)) & 15) FAIL(ORBX_EINVAL, "device descriptor matrices must be 16-byte aligned");
+    if ((rc = stg.flush(st))) return rc;
+    int* cellCount = W.take<int>(SP_CELLS);
+    int* cellStart = W.take<int>(SP_CELLS + 1);
+    int* cursor = W.take<int>(SP_CELLS);
+    int* items = W.take<int>(nC);
+    int* candCount = W.take<int>(nL);
+    int* candOff = W.take<int>(nL + 1);
+    int* matchedDist = W.take<int>(nC);
+    int* match21 = W.take<int>(nC);
+    int* bin12 = W.take<int>(nL);
+    int* dRes = W.take<int>(4);
+    int32_t* o12 = hout ? W.take<int32_t>(nL) : matches12;
+    float* oPrev = hout ? W.take<float>((size_t)nL * 2) : prev_matched;
+    if (W.off > m->wsCap) FAIL(ORBX_ECUDA, "internal: workspace estimate too small (%zu > %zu)", W.off, m->wsCap);
+
+    CK(cudaMemsetAsync(cellCount, 0, SP_CELLS * sizeof(int), st));
+    k_sp_grid_count<<<(nC + 255) / 256, 256, 0, st>>>(S, cellCount);
+    k_sp_grid_scan<<<1, 1024, 0, st>>>(cellCount, cellStart, cursor);
+    k_sp_grid_fill<<<(nC + 255) / 256, 256, 0, st>>>(S, cursor, items);
+    k_sp_grid_sort<<<(SP_CELLS + 255) / 256, 256, 0, st>>>(cellStart, items);
+    const int qBlocks = (nL + 7) / 8;
+    k_sp_candidates<false><<<qBlocks, 256, 0, st>>>(S, cellStart, items, candCount, nullptr, nullptr, nullptr);
+    k_sp_scan<<<1, 1024, 0, st>>>(candCount, nL, candOff);
+    m->launches += 6;
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(m->hRes + 2, candOff + nL, sizeof(int), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    const size_t total = (size_t)m->hRes[2];
+    if ((rc = ensure(m->dCand, m->candCap, (total + 64) * 6))) return rc;
+    int* candIdx = (int*)m->dCand;
+    unsigned short* candDist = (unsigned short*)(m->dCand + ((total + 63) & ~(size_t)63) * 4);
+    k_sp_candidates<true><<<qBlocks, 256, 0, st>>>(S, cellStart, items, nullptr, candOff, candIdx, candDist);
+    CK(cudaMemsetAsync(matchedDist, 0x7F, (size_t)nC * sizeof(int), st));  // 0x7F7F7F7F: above every distance
+    CK(cudaMemsetAsync(match21, 0xFF, (size_t)nC * sizeof(int), st));
+    CK(cudaMemsetAsync(o12, 0xFF, (size_t)nL * sizeof(int), st));
+    k_init_greedy<<<1, 32, 0, st>>>(S, candOff, candIdx, candDist, th_low, matchedDist, match21, o12, bin12, oPrev, dRes);
+    m->launches += 2;
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(m->hRes, dRes, sizeof(int), cudaMemcpyDeviceToHost, st));
+    if (hout) {
+        CK(cudaMemcpyAsync(matches12, o12, (size_t)nL * 4, cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(prev_matched, oPrev, (size_t)nL * 8, cudaMemcpyDeviceToHost, st));
+    }
+    CK(cudaStreamSynchronize(st));
+    *nmatches = m->hRes[0];
+    m->lastRounds = 1;
+    m->lastCandidates = (int64_t)total;
+    return ORBX_OK;
 }
 
 extern "C" int orbm_distinctive_descriptors(orbm_t* m, const uint8_t* desc, const int32_t* off, int npoints,

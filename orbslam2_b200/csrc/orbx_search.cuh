@@ -33,9 +33,13 @@ struct SpDev {  // device copies of the call's arrays
     // nPredictedLevel), radius th*scale[level], octave gate [level-1, level], every claim blocks later points
     // mode 1 = SearchByProjection(Frame&, vector<MapPoint*>, th): the queries come with their tracking projection
     // (MapPoint::mTrackProjX/Y/XR, mnTrackScaleLevel, mTrackViewCos set by Frame::isInFrustum, src/Frame.cc:256-326)
+    // mode 3 = SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize): the queries are F1's level-0
+    // keypoints (qkeys), window centre vbPrevMatched[i] (projX = the interleaved n x 2 array), radius th = windowSize,
+    // level gate [0, 0]
     int mode;
     const float* projX; const float* projY; const float* projXR; const float* viewCos;
     float nnRatio;
+    const orbx_kp* qkeys;
 };
 
 // Frame::PosInGrid (src/Frame.cc:383-393): round() = half away from zero, on the float product
@@ -116,8 +120,19 @@ struct SpQuery {
 __device__ __forceinline__ SpQuery sp_query(const SpDev& S, int i) {
     SpQuery q;
     q.valid = false;
-    if (!(S.lflags[i] & 1)) return q;
-    if (S.mode == 2) {  // SearchByProjection(KeyFrame*, Scw, vpPoints, vpMatched, th): src/ORBmatcher.cc:349-352, 375
+    if (S.mode == 3) {  // src/ORBmatcher.cc:415-420
+        const int level1 = S.qkeys[i].octave;
+        if (level1 > 0) return q;
+        q.radius = S.p.th;
+        q.u = S.projX[2 * i];
+        q.v = S.projX[2 * i + 1];
+        q.ur = 0.f;
+        q.invzc = 0.f;
+        q.minLevel = level1;
+        q.maxLevel = level1;
+    } else if (!(S.lflags[i] & 1)) {
+        return q;
+    } else if (S.mode == 2) {  // SearchByProjection(KeyFrame*, Scw, vpPoints, vpMatched, th): src/ORBmatcher.cc:349-352, 375
         const int lvl = S.loct[i];
         q.radius = __fmul_rn(S.p.th, S.p.scale[lvl]);
         q.u = S.projX[i];
@@ -429,6 +444,103 @@ __global__ void __launch_bounds__(1024) k_sp_finish_mp(SpDev S, const int* __res
     __syncthreads();
     if (tid == 0) result[0] = nAcc;
 }
+
+// ---- mode 3: ORBmatcher::SearchForInitialization, src/ORBmatcher.cc:400-515 ---------------------------------------------
+// Here a later query can STEAL a keypoint from an earlier one (vMatchedDistance / vnMatches21, :439, :458-466), so what a
+// query sees is the running minimum over the earlier accepted claims and not a first-claimer mark. The candidate lists
+// and distances come from the parallel kernels above; the claim loop itself is replayed in query order by ONE warp whose
+// lanes share each query's candidate list (best / second best with multiplicity, first position on ties, merged by
+// shuffles). Only level-0 keypoints query (a few hundred), so the replay is short. The rotation histogram counts every
+// accept, stolen or not, as the reference's rotHist does (:468-478).
+__global__ void __launch_bounds__(32) k_init_greedy(SpDev S, const int* __restrict__ candOff, const int* __restrict__ candIdx,
+                                                    const unsigned short* __restrict__ candDist, int thLow,
+                                                    int* matchedDist /* [nCur] preset >= INT_MAX/2 */,
+                                                    int* match21 /* [nCur] preset -1 */, int32_t* match12 /* [nLast] preset -1 */,
+                                                    int* bin12 /* [nLast] */, float* prevOut /* [nLast][2] */,
+                                                    int* __restrict__ result) {
+    __shared__ int hist[SP_HISTO];
+    __shared__ int keepBin[SP_HISTO];
+    __shared__ int nm;
+    const int lane = threadIdx.x;
+    if (lane < SP_HISTO) { hist[lane] = 0; keepBin[lane] = 1; }
+    if (lane == 0) nm = 0;
+    __syncwarp();
+    volatile int* vMatchedDistance = matchedDist;
+    const float factor = 1.0f / SP_HISTO;
+    const int nL = S.nLast;
+    for (int i = 0; i < nL; i++) {
+        const int s = candOff[i], e = candOff[i + 1];
+        if (s == e) continue;
+        int b = INT_MAX, b2 = INT_MAX, bp = INT_MAX;
+        for (int c = s + lane; c < e; c += 32) {
+            const int dist = candDist[c];
+            if (vMatchedDistance[candIdx[c]] <= dist) continue;
+            if (dist < b) { b2 = b; b = dist; bp = c; }
+            else if (dist < b2) b2 = dist;
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const int ob = __shfl_xor_sync(0xffffffffu, b, o), ob2 = __shfl_xor_sync(0xffffffffu, b2, o),
+                      obp = __shfl_xor_sync(0xffffffffu, bp, o);
+            if (ob < b || (ob == b && obp < bp)) { b2 = min(ob2, b); b = ob; bp = obp; }
+            else b2 = min(b2, ob);
+        }
+        if (b <= thLow && (float)b < __fmul_rn((float)b2, S.nnRatio)) {
+            if (lane == 0) {
+                const int bestIdx2 = candIdx[bp];
+                const int prev = match21[bestIdx2];
+                int d = 1;
+                if (prev >= 0) { match12[prev] = -1; d = 0; }
+                match12[i] = bestIdx2;
+                match21[bestIdx2] = i;
+                vMatchedDistance[bestIdx2] = b;
+                nm += d;
+                if (S.p.check_orientation) {
+                    float rot = __fsub_rn(S.qkeys[i].angle, S.keys[bestIdx2].angle);
+                    if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
+                    int bin = (int)roundf(__fmul_rn(rot, factor));
+                    if (bin == SP_HISTO) bin = 0;
+                    hist[bin]++;
+                    bin12[i] = bin;
+                }
+            }
+            __syncwarp();
+        }
+    }
+    __syncwarp();
+    if (lane == 0 && S.p.check_orientation) {  // ComputeThreeMaxima, :1597-1638
+        int max1 = 0, max2 = 0, max3 = 0, ind1 = -1, ind2 = -1, ind3 = -1;
+        for (int i = 0; i < SP_HISTO; i++) {
+            const int s = hist[i];
+            if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = i; }
+            else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = i; }
+            else if (s > max3) { max3 = s; ind3 = i; }
+        }
+        if ((float)max2 < 0.1f * (float)max1) { ind2 = -1; ind3 = -1; }
+        else if ((float)max3 < 0.1f * (float)max1) { ind3 = -1; }
+        for (int i = 0; i < SP_HISTO; i++) keepBin[i] = (i == ind1 || i == ind2 || i == ind3);
+    }
+    __syncwarp();
+    int dropped = 0;
+    for (int i = lane; i < nL; i += 32) {
+        int c = match12[i];
+        if (c >= 0 && S.p.check_orientation && !keepBin[bin12[i]]) {
+            match12[i] = c = -1;
+            dropped++;
+        }
+        float x = S.projX[2 * i], y = S.projX[2 * i + 1];
+        if (c >= 0) {  // vbPrevMatched[i1] = F2.mvKeysUn[vnMatches12[i1]].pt, :508-510
+            x = S.keys[c].x;
+            y = S.keys[c].y;
+        }
+        prevOut[2 * i] = x;
+        prevOut[2 * i + 1] = y;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) dropped += __shfl_xor_sync(0xffffffffu, dropped, o);
+    if (lane == 0) result[0] = nm - dropped;
+}
+
 
 // ---- ORBmatcher::Fuse: the search half (src/ORBmatcher.cc:821-971 and :973-1096) --------------------------------------
 // Per map point (projected on the host, where the MapPoint-internal gates live): KeyFrame::GetFeaturesInArea(u, v,

@@ -255,6 +255,24 @@ class ORBmatcher:
         match12 = np.where(ok, m1, -1).astype(np.int32)
         return int(ok.sum()), match12
 
+    def SearchForInitialization(self, F1, F2, vbPrevMatched, windowSize=10):
+        """ORBmatcher::SearchForInitialization(Frame& F1, Frame& F2, vbPrevMatched, vnMatches12, windowSize)
+        (src/ORBmatcher.cc:400-515; Tracking::MonocularInitialization) on the device. vbPrevMatched: (F1.N, 2) float32,
+        updated IN PLACE as the reference does. Returns (nmatches, vnMatches12, P)."""
+        P = self._kf_grid_params(F2, float(windowSize))
+        P.check_orientation = int(self.mbCheckOrientation)
+        prev = vbPrevMatched
+        assert prev.dtype == np.float32 and prev.shape == (F1.N, 2) and prev.flags.c_contiguous
+        CA = _lib.CurFrameArgs(F2.N, F2.mvKeysUn.ctypes.data, None, F2.mDescriptors.ctypes.data, None)
+        m12 = np.full(F1.N, -1, np.int32)
+        nm = C.c_int()
+        self._set_space(_lib.MEM_HOST, _lib.MEM_HOST)
+        _lib.check(self._L.orbm_search_for_initialization(self._h, C.byref(P), float(self.mfNNratio), int(self.TH_LOW),
+                                                          int(windowSize), F1.N, F1.mvKeysUn.ctypes.data,
+                                                          F1.mDescriptors.ctypes.data, prev.ctypes.data, C.byref(CA),
+                                                          m12.ctypes.data, C.byref(nm)))
+        return nm.value, m12, P
+
     def SearchLocalPoints(self, F, mps, th=1.0, taken=None):
         """ORBmatcher::SearchByProjection(Frame &F, const vector<MapPoint*> &vpMapPoints, th) (src/ORBmatcher.cc:43-127)
         on the device. `mps` is a dict of arrays: proj_x, proj_y, proj_xr, level, view_cos, in_view (mbTrackInView &&

@@ -484,3 +484,21 @@ def oracle_search_kf_projection(P, pts, kf, taken, th_low=50):
                                    kf.N, _p(kx), _p(ky), _p(ko), _p(kf.mDescriptors), None if tk is None else _p(tk),
                                    int(th_low), _p(km), _p(pm))
     return r, km, pm
+
+
+def oracle_search_for_initialization(P, nn_ratio, F1, F2, prev, window_size, th_low=50):
+    """orc_search_for_initialization; prev (F1.N, 2) float32 is updated in place like vbPrevMatched."""
+    build_oracle()
+    L = _load(ORACLE_SO)
+    L.orc_search_for_initialization.argtypes = ([C.c_void_p, C.c_float, C.c_int, C.c_int, C.c_int] + [C.c_void_p] * 4 +
+                                                [C.c_int] + [C.c_void_p] * 6)
+    L.orc_search_for_initialization.restype = C.c_int
+    o1 = np.ascontiguousarray(F1.mvKeysUn["octave"], np.int32); a1 = np.ascontiguousarray(F1.mvKeysUn["angle"], np.float32)
+    kx = np.ascontiguousarray(F2.mvKeysUn["x"], np.float32); ky = np.ascontiguousarray(F2.mvKeysUn["y"], np.float32)
+    ko = np.ascontiguousarray(F2.mvKeysUn["octave"], np.int32); ka = np.ascontiguousarray(F2.mvKeysUn["angle"], np.float32)
+    assert prev.dtype == np.float32 and prev.flags.c_contiguous
+    m12 = np.full(F1.N, -1, np.int32)
+    r = L.orc_search_for_initialization(C.addressof(P), float(nn_ratio), int(th_low), int(window_size), F1.N, _p(o1), _p(a1),
+                                        _p(F1.mDescriptors), _p(prev), F2.N, _p(kx), _p(ky), _p(ko), _p(ka),
+                                        _p(F2.mDescriptors), _p(m12))
+    return r, m12

@@ -249,3 +249,95 @@ def test_prep_undistort_points_matches_cv2():
         K = G[f"und_{name}_K"]
         got = P.undistort_points(G["und_pts"], K[0], K[1], K[2], K[3], G[f"und_{name}_D"])
         assert got.tobytes() == G[f"und_{name}"].tobytes(), name
+
+
+def test_search_for_initialization_oracle_vs_python_replay():
+    """orc_search_for_initialization against a plain-Python replay of src/ORBmatcher.cc:400-515 written independently
+    (dict grid, Python ints, math.floor/ceil), on a pair built so that keypoints get stolen and late queries are refused."""
+    import math
+    import importlib.util, os
+    from oracle_lib import oracle_search_for_initialization
+    from orbslam2_b200 import _lib
+    spec = importlib.util.spec_from_file_location("tgs", os.path.join(os.path.dirname(__file__), "test_gpu_search.py"))
+    tgs = importlib.util.module_from_spec(spec); spec.loader.exec_module(tgs)
+    F1, F2 = tgs._init_pair(11, n=400, groups=40)
+    window, ratio = 100, np.float32(0.9)
+    P = _lib.ProjParams()
+    P.minX, P.maxX, P.minY, P.maxY = 0, 640, 0, 480
+    P.grid_w_inv, P.grid_h_inv = float(F2.mfGridElementWidthInv), float(F2.mfGridElementHeightInv)
+    P.nlevels, P.check_orientation = 8, 1
+    prev = np.ascontiguousarray(np.stack([F1.mvKeysUn["x"], F1.mvKeysUn["y"]], 1), np.float32)
+    eprev = prev.copy()
+    n, m12 = oracle_search_for_initialization(P, ratio, F1, F2, prev, window)
+
+    f32 = np.float32
+    gwi, ghi = f32(P.grid_w_inv), f32(P.grid_h_inv)
+    grid = {}
+    for i, k in enumerate(F2.mvKeysUn):
+        px = int(math.floor(float(f32(k["x"]) * gwi) + 0.5))  # round(): half away from zero, values are >= 0 here
+        py = int(math.floor(float(f32(k["y"]) * ghi) + 0.5))
+        if 0 <= px < 64 and 0 <= py < 48:
+            grid.setdefault((px, py), []).append(i)
+    bits2 = np.unpackbits(F2.mDescriptors, axis=1).astype(np.int32)
+    bits1 = np.unpackbits(F1.mDescriptors, axis=1).astype(np.int32)
+    INF = 2**31 - 1
+    md, m21, e12 = [INF] * F2.N, [-1] * F2.N, [-1] * F1.N
+    hist = [[] for _ in range(30)]
+    steals = refused = nm = 0
+    r = f32(window)
+    for i1 in range(F1.N):
+        if F1.mvKeysUn["octave"][i1] > 0:
+            continue
+        x, y = f32(eprev[i1, 0]), f32(eprev[i1, 1])
+        x0 = max(0, math.floor(float(f32(x - r) * gwi))); x1 = min(63, math.ceil(float(f32(x + r) * gwi)))
+        y0 = max(0, math.floor(float(f32(y - r) * ghi))); y1 = min(47, math.ceil(float(f32(y + r) * ghi)))
+        if x0 >= 64 or x1 < 0 or y0 >= 48 or y1 < 0:
+            continue
+        best = best2 = INF; bi = -1
+        for ix in range(x0, x1 + 1):
+            for iy in range(y0, y1 + 1):
+                for i2 in grid.get((ix, iy), []):
+                    k = F2.mvKeysUn[i2]
+                    if k["octave"] != 0 or not (abs(f32(k["x"]) - x) < r and abs(f32(k["y"]) - y) < r):
+                        continue
+                    d = int(np.abs(bits1[i1] - bits2[i2]).sum())
+                    if md[i2] <= d:
+                        refused += 1
+                        continue
+                    if d < best:
+                        best2, best, bi = best, d, i2
+                    elif d < best2:
+                        best2 = d
+        if best <= 50 and f32(best) < f32(f32(best2) * ratio):
+            if m21[bi] >= 0:
+                e12[m21[bi]] = -1; nm -= 1; steals += 1
+            e12[i1] = bi; m21[bi] = i1; md[bi] = best; nm += 1
+            rot = f32(F1.mvKeysUn["angle"][i1]) - f32(F2.mvKeysUn["angle"][bi])
+            if rot < 0:
+                rot = f32(rot + f32(360))
+            b = int(math.floor(float(f32(rot * f32(1.0 / 30))) + 0.5))
+            hist[0 if b == 30 else b].append(i1)
+    sizes = [len(h) for h in hist]
+    max1 = max2 = max3 = 0; i1_ = i2_ = i3_ = -1
+    for i, s in enumerate(sizes):
+        if s > max1:
+            max3, max2, max1, i3_, i2_, i1_ = max2, max1, s, i2_, i1_, i
+        elif s > max2:
+            max3, max2, i3_, i2_ = max2, s, i2_, i
+        elif s > max3:
+            max3, i3_ = s, i
+    if max2 < f32(0.1) * f32(max1):
+        i2_ = i3_ = -1
+    elif max3 < f32(0.1) * f32(max1):
+        i3_ = -1
+    for i, h in enumerate(hist):
+        if i in (i1_, i2_, i3_):
+            continue
+        for q in h:
+            if e12[q] >= 0:
+                e12[q] = -1; nm -= 1
+    assert steals >= 5 and refused >= 5, (steals, refused)
+    assert n == nm and list(m12) == e12
+    for q in range(F1.N):
+        exp = (F2.mvKeysUn["x"][e12[q]], F2.mvKeysUn["y"][e12[q]]) if e12[q] >= 0 else tuple(eprev[q])
+        assert tuple(prev[q]) == exp

@@ -262,3 +262,104 @@ def test_search_by_sim3_vs_oracle(seed):
     assert np.array_equal(m12, exp) and nf == int((exp >= 0).sum())
     assert nf > 100
     m.close()
+
+
+def _init_pair(seed, n=1500, groups=60, width=640, height=480):
+    """Two monocular frames for SearchForInitialization: F2 = F1's keypoints moved by a small flow + noise, descriptors
+    with a few flipped bits, shuffled. `groups` clusters of F1 keypoints (3-5 each, all level 0, within the window of one
+    another) carry near-copies of ONE F2 descriptor with a random number of flipped bits, so later queries steal the
+    keypoint from earlier, worse ones and some arrive too late (vMatchedDistance <= dist)."""
+    from orbslam2_b200.frame import Frame
+    from orbslam2_b200.extractor import KP_DTYPE
+    rng = np.random.default_rng(900 + seed)
+    sf = np.float32(1.2) ** np.arange(8, dtype=np.float32)
+
+    def kps(x, y, o, a):
+        k = np.zeros(len(x), KP_DTYPE)
+        k["x"], k["y"], k["octave"], k["angle"] = x, y, o, a
+        k["size"] = 31 * sf[o]; k["class_id"] = -1
+        return k
+
+    x1 = rng.uniform(20, width - 20, n).astype(np.float32); y1 = rng.uniform(20, height - 20, n).astype(np.float32)
+    o1 = np.where(rng.random(n) < 0.55, 0, rng.integers(1, 8, n)).astype(np.int32)
+    a1 = rng.uniform(0, 360, n).astype(np.float32)
+    d1 = rng.integers(0, 256, (n, 32), dtype=np.uint8)
+    perm = rng.permutation(n)
+    x2 = (x1 + 6 + rng.normal(0, 3, n)).astype(np.float32)[perm]; y2 = (y1 - 4 + rng.normal(0, 3, n)).astype(np.float32)[perm]
+    o2 = np.where(rng.random(n) < 0.9, o1, rng.integers(0, 8, n)).astype(np.int32)[perm]
+    rot = np.where(rng.random(n) < 0.85, 12.0, rng.uniform(0, 360, n))
+    a2 = np.mod(a1 - rot + rng.normal(0, 3, n), 360).astype(np.float32)[perm]
+    bits = np.unpackbits(d1, axis=1)
+    for _ in range(14):
+        bits[np.arange(n), rng.integers(0, 256, n)] ^= 1
+    d2 = np.packbits(bits, axis=1)[perm]
+    inv = np.empty(n, np.int64); inv[perm] = np.arange(n)
+    # competing clusters
+    heads = rng.choice(np.flatnonzero(o1 == 0), groups, replace=False)
+    free = np.setdiff1d(np.arange(n), heads)
+    rng.shuffle(free)
+    used = 0
+    for h in heads:
+        k = int(rng.integers(2, 5))
+        members = free[used:used + k]; used += k
+        tgt = inv[h]
+        o2[tgt] = 0
+        for mb in members:
+            x1[mb] = x1[h] + rng.normal(0, 8); y1[mb] = y1[h] + rng.normal(0, 8)
+            o1[mb] = 0
+            a1[mb] = a1[h]
+            b = np.unpackbits(d2[tgt])
+            b[rng.integers(0, 256, int(rng.integers(0, 30)))] ^= 1
+            d1[mb] = np.packbits(b)
+    F1 = Frame(kps(x1, y1, o1, a1), d1, sf, 520, 520, 320, 240, 0, width, height)
+    F2 = Frame(kps(x2, y2, o2, a2), d2, sf, 520, 520, 320, 240, 0, width, height)
+    return F1, F2
+
+
+@pytest.mark.parametrize("seed,window,ratio,ori", [(0, 100, 0.9, True), (1, 100, 0.9, False), (2, 30, 0.7, True), (3, 250, 1.0, True)])
+def test_search_for_initialization_vs_oracle(seed, window, ratio, ori):
+    """ORBmatcher::SearchForInitialization (Tracking::MonocularInitialization): level-0 queries, the window over F2's
+    grid, vMatchedDistance skip, ratio rule, stolen matches, rotation filter over every accept, vbPrevMatched update —
+    bit-identical to the sequential loop; a second call with the updated vbPrevMatched (what the tracker does frame after
+    frame) stays identical too."""
+    import orbslam2_b200 as ob
+    from oracle_lib import oracle_search_for_initialization
+    m = ob.ORBmatcher(ratio, ori)
+    F1, F2 = _init_pair(seed)
+    prev = np.ascontiguousarray(np.stack([F1.mvKeysUn["x"], F1.mvKeysUn["y"]], 1), np.float32)
+    eprev = prev.copy()
+    stolen_seen = False
+    for it in range(2):
+        n, m12, P = m.SearchForInitialization(F1, F2, prev, window)
+        en, em12 = oracle_search_for_initialization(P, np.float32(ratio), F1, F2, eprev, window)
+        assert n == en, f"nmatches {n} vs {en}"
+        assert np.array_equal(m12, em12), f"{(m12 != em12).sum()} matches differ"
+        assert prev.tobytes() == eprev.tobytes(), "vbPrevMatched differs"
+        assert n == (m12 >= 0).sum()
+        assert (F1.mvKeysUn["octave"][m12 >= 0] == 0).all() and (F2.mvKeysUn["octave"][m12[m12 >= 0]] == 0).all()
+        got = m12[m12 >= 0]
+        assert len(np.unique(got)) == len(got), "a keypoint of F2 belongs to at most one match"
+        assert n > 200
+    m.close()
+
+
+def test_search_for_initialization_edges():
+    import orbslam2_b200 as ob
+    from oracle_lib import oracle_search_for_initialization
+    from orbslam2_b200.frame import Frame
+    m = ob.ORBmatcher(0.9, True)
+    F1, F2 = _init_pair(7, n=300, groups=10)
+    E = Frame(F2.mvKeysUn[:0], F2.mDescriptors[:0], F2.mvScaleFactors, 520, 520, 320, 240, 0, 640, 480)
+    prev = np.ascontiguousarray(np.stack([F1.mvKeysUn["x"], F1.mvKeysUn["y"]], 1), np.float32)
+    keep = prev.copy()
+    n, m12, _ = m.SearchForInitialization(F1, E, prev, 100)      # empty F2
+    assert n == 0 and (m12 == -1).all() and np.array_equal(prev, keep)
+    n, m12, _ = m.SearchForInitialization(E, F2, np.zeros((0, 2), np.float32), 100)  # empty F1
+    assert n == 0 and len(m12) == 0
+    # windows far outside the image: no candidates at all
+    far = (prev + np.float32(5000)).astype(np.float32)
+    efar = far.copy()
+    n, m12, P = m.SearchForInitialization(F1, F2, far, 100)
+    en, em12 = oracle_search_for_initialization(P, np.float32(0.9), F1, F2, efar, 100)
+    assert n == en == 0 and np.array_equal(m12, em12) and np.array_equal(far, efar)
+    m.close()
