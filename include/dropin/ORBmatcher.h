@@ -11,6 +11,9 @@
 #ifndef ORBX_DROPIN_ORBMATCHER_H
 #define ORBX_DROPIN_ORBMATCHER_H
 
+#include <cmath>
+#include <cstdint>
+#include <set>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -346,6 +349,142 @@ public:
         return nFused;
     }
 
+    // ORBmatcher::SearchForInitialization(Frame& F1, Frame& F2, std::vector<cv::Point2f>& vbPrevMatched,
+    //                                     std::vector<int>& vnMatches12, int windowSize = 10)
+    // (include/ORBmatcher.h:68, src/ORBmatcher.cc:400-515; Tracking::MonocularInitialization src/Tracking.cc:699)
+    // entirely on the device: grid of F2, level-0 windows, the claim loop with stealing, rotation filter and the
+    // vbPrevMatched update (orbm_search_for_initialization).
+    template <class FrameT>
+    int SearchForInitialization(FrameT& F1, FrameT& F2, std::vector<cv::Point2f>& vbPrevMatched, std::vector<int>& vnMatches12,
+                                int windowSize = 10) {
+        static_assert(sizeof(cv::Point2f) == 8 && sizeof(int) == 4, "vbPrevMatched / vnMatches12 cross the ABI in place");
+        const int n1 = (int)F1.mvKeysUn.size(), n2 = (int)F2.mvKeysUn.size();
+        vnMatches12 = std::vector<int>(n1, -1);
+        orbm_proj_params P = orbm_proj_params();
+        P.minX = F2.mnMinX; P.maxX = F2.mnMaxX; P.minY = F2.mnMinY; P.maxY = F2.mnMaxY;
+        P.grid_w_inv = F2.mfGridElementWidthInv; P.grid_h_inv = F2.mfGridElementHeightInv;
+        P.nlevels = (int)F2.mvScaleFactors.size();
+        for (int i = 0; i < P.nlevels && i < ORBX_MAX_LEVELS; i++) P.scale[i] = F2.mvScaleFactors[i];
+        P.check_orientation = mbCheckOrientation ? 1 : 0;
+        orbm_cur_frame f2 = {n2, (const orbx_kp*)F2.mvKeysUn.data(), nullptr, F2.mDescriptors.ptr(), nullptr};
+        int nmatches = 0;
+        check(orbm_search_for_initialization(tls(), &P, mfNNratio, TH_LOW, windowSize, n1, (const orbx_kp*)F1.mvKeysUn.data(),
+                                             F1.mDescriptors.ptr(), n1 ? &vbPrevMatched[0].x : nullptr, &f2,
+                                             (int32_t*)vnMatches12.data(), &nmatches),
+              "orbm_search_for_initialization");
+        return nmatches;
+    }
+
+    // ORBmatcher::SearchByProjection(KeyFrame* pKF, cv::Mat Scw, const std::vector<MapPoint*>& vpPoints,
+    //                                std::vector<MapPoint*>& vpMatched, int th)
+    // (include/ORBmatcher.h:64, src/ORBmatcher.cc:285-398; LoopClosing::ComputeSim3 src/LoopClosing.cc:411). The Sim3
+    // projection and the MapPoint gates run on the host (project_sim3 below), the window search with the vpMatched
+    // claims in orbm_search_kf_projection.
+    template <class KeyFrameT, class MapPointT>
+    int SearchByProjection(KeyFrameT* pKF, cv::Mat Scw, const std::vector<MapPointT*>& vpPoints,
+                           std::vector<MapPointT*>& vpMatched, int th) {
+        const std::set<MapPointT*> spAlreadyFound(vpMatched.begin(), vpMatched.end());  // a NULL entry never matches a point
+        Sim3Points S;
+        project_sim3(pKF, Scw, vpPoints, spAlreadyFound, S);
+        const int n = (int)vpPoints.size(), nK = (int)pKF->mvKeysUn.size();
+        std::vector<uint8_t> taken(nK, 0);
+        for (int i = 0; i < nK && i < (int)vpMatched.size(); i++) taken[i] = vpMatched[i] != NULL;
+        orbm_proj_params P = kf_grid_params(pKF, (float)th);
+        P.th_high = TH_LOW;
+        orbm_fuse_points pts = {n, S.u.data(), S.v.data(), nullptr, S.lvl.data(), S.valid.data(), S.desc.data()};
+        orbm_cur_frame kf = {nK, (const orbx_kp*)pKF->mvKeysUn.data(), nullptr, pKF->mDescriptors.ptr(), taken.data()};
+        std::vector<int32_t> kfMatch(nK, -1), ptMatch(n, -1);
+        int nmatches = 0;
+        check(orbm_search_kf_projection(tls(), &P, &pts, &kf, kfMatch.data(), ptMatch.data(), &nmatches),
+              "orbm_search_kf_projection");
+        for (int idx = 0; idx < nK; idx++)
+            if (kfMatch[idx] >= 0) vpMatched[idx] = vpPoints[kfMatch[idx]];
+        return nmatches;
+    }
+
+    // ORBmatcher::Fuse(KeyFrame* pKF, cv::Mat Scw, const std::vector<MapPoint*>& vpPoints, float th,
+    //                  std::vector<MapPoint*>& vpReplacePoint)
+    // (include/ORBmatcher.h:85, src/ORBmatcher.cc:973-1096; LoopClosing::SearchAndFuse src/LoopClosing.cc:633): no point
+    // depends on another one's outcome here (spAlreadyFound is taken once, :989), so one orbm_fuse_search pass serves
+    // all points; the map mutations follow on the host in point order.
+    template <class KeyFrameT, class MapPointT>
+    int Fuse(KeyFrameT* pKF, cv::Mat Scw, const std::vector<MapPointT*>& vpPoints, float th,
+             std::vector<MapPointT*>& vpReplacePoint) {
+        const std::set<MapPointT*> spAlreadyFound = pKF->GetMapPoints();
+        Sim3Points S;
+        project_sim3(pKF, Scw, vpPoints, spAlreadyFound, S);
+        const int n = (int)vpPoints.size(), nK = (int)pKF->mvKeysUn.size();
+        orbm_proj_params P = kf_grid_params(pKF, th);
+        std::vector<float> ur(n, 0.f), invSigma2(ORBX_MAX_LEVELS, 0.f);
+        orbm_fuse_points pts = {n, S.u.data(), S.v.data(), ur.data(), S.lvl.data(), S.valid.data(), S.desc.data()};
+        orbm_cur_frame kf = {nK, (const orbx_kp*)pKF->mvKeysUn.data(), nullptr, pKF->mDescriptors.ptr(), nullptr};
+        std::vector<int32_t> bestIdx(n, -1);
+        std::vector<uint16_t> bestDist(n, 256);
+        check(orbm_fuse_search(tls(), &P, invSigma2.data(), 0, &pts, &kf, bestIdx.data(), bestDist.data()), "orbm_fuse_search");
+        int nFused = 0;
+        for (int i = 0; i < n; i++) {
+            if (!S.valid[i] || bestIdx[i] < 0 || bestDist[i] > TH_LOW) continue;
+            MapPointT* pMP = vpPoints[i];
+            MapPointT* pMPinKF = pKF->GetMapPoint(bestIdx[i]);
+            if (pMPinKF) {
+                if (!pMPinKF->isBad()) vpReplacePoint[i] = pMPinKF;
+            } else {
+                pMP->AddObservation(pKF, bestIdx[i]);
+                pKF->AddMapPoint(pMP, bestIdx[i]);
+            }
+            nFused++;
+        }
+        return nFused;
+    }
+
+    // ORBmatcher::SearchBySim3(KeyFrame* pKF1, KeyFrame* pKF2, std::vector<MapPoint*>& vpMatches12, const float& s12,
+    //                          const cv::Mat& R12, const cv::Mat& t12, const float th)
+    // (include/ORBmatcher.h:78, src/ORBmatcher.cc:1098-1322; LoopClosing::ComputeSim3 src/LoopClosing.cc:359): the two
+    // directions are independent window searches (orbm_fuse_search without the chi-square gates, accept <= TH_HIGH),
+    // then the mutual-agreement pass (:1303-1319).
+    template <class KeyFrameT, class MapPointT>
+    int SearchBySim3(KeyFrameT* pKF1, KeyFrameT* pKF2, std::vector<MapPointT*>& vpMatches12, const float& s12,
+                     const cv::Mat& R12, const cv::Mat& t12, const float th) {
+        float R1w[9], t1w[3], R2w[9], t2w[3], sR12[9], sR21[9], t21[3], t12f[3];
+        mat33(pKF1->GetRotation(), R1w); vec3(pKF1->GetTranslation(), t1w);
+        mat33(pKF2->GetRotation(), R2w); vec3(pKF2->GetTranslation(), t2w);
+        vec3(t12, t12f);
+        const float inv = (float)(1.0 / s12);  // (1.0/s12)*R12.t(): the scale reaches the elements as a float factor
+        for (int r = 0; r < 3; r++)
+            for (int c = 0; c < 3; c++) {
+                sR12[3 * r + c] = s12 * R12.at<float>(r, c);
+                sR21[3 * r + c] = inv * R12.at<float>(c, r);
+            }
+        for (int r = 0; r < 3; r++) {  // t21 = -sR21*t12
+            double acc = 0;
+            for (int c = 0; c < 3; c++) acc += (double)sR21[3 * r + c] * (double)t12f[c];
+            t21[r] = -(float)acc;
+        }
+        const std::vector<MapPointT*> vpMapPoints1 = pKF1->GetMapPointMatches(), vpMapPoints2 = pKF2->GetMapPointMatches();
+        const int N1 = (int)vpMapPoints1.size(), N2 = (int)vpMapPoints2.size();
+        std::vector<uint8_t> already1(N1, 0), already2(N2, 0);
+        for (int i = 0; i < N1; i++) {
+            MapPointT* pMP = vpMatches12[i];
+            if (pMP) {
+                already1[i] = 1;
+                const int idx2 = pMP->GetIndexInKeyFrame(pKF2);
+                if (idx2 >= 0 && idx2 < N2) already2[idx2] = 1;
+            }
+        }
+        std::vector<int> vnMatch1, vnMatch2;
+        sim3_direction(pKF2, vpMapPoints1, already1, R1w, t1w, sR21, t21, th, vnMatch1);  // KF1's points into KF2
+        sim3_direction(pKF1, vpMapPoints2, already2, R2w, t2w, sR12, t12f, th, vnMatch2);  // KF2's points into KF1
+        int nFound = 0;
+        for (int i1 = 0; i1 < N1; i1++) {
+            const int idx2 = vnMatch1[i1];
+            if (idx2 >= 0 && vnMatch2[idx2] == i1) {
+                vpMatches12[i1] = vpMapPoints2[idx2];
+                nFound++;
+            }
+        }
+        return nFound;
+    }
+
     // ORBmatcher::SearchByFboW(KeyFrame* pKF, Frame& F, std::vector<MapPoint*>& vpMapPointMatches)
     // (src/ORBmatcher.cc:157-283; TrackReferenceKeyFrame src/Tracking.cc:867, Relocalization :1476) on the device.
     // FeatVecT is fbow::fBow2 (std::map<uint32_t, std::vector<uint32_t>>).
@@ -455,6 +594,130 @@ public:
     }
 
 protected:
+    // ---- host half of the Sim3 searches (src/ORBmatcher.cc:293-298, 313-351 and 1003-1041) ---------------------------
+    struct Sim3Points {
+        std::vector<float> u, v;
+        std::vector<int32_t> lvl;
+        std::vector<uint8_t> valid, desc;
+    };
+    static void mat33(const cv::Mat& M, float* R) {
+        for (int r = 0; r < 3; r++)
+            for (int c = 0; c < 3; c++) R[3 * r + c] = M.at<float>(r, c);
+    }
+    static void vec3(const cv::Mat& M, float* t) {
+        for (int r = 0; r < 3; r++) t[r] = M.at<float>(r, 0);
+    }
+    // y = A*x + b as cv::Mat CV_32F evaluates it: the row's three products accumulate in double, one rounding, float add
+    static void mul_add(const float* A, const float* x, const float* b, float* y) {
+        for (int r = 0; r < 3; r++) {
+            double acc = 0;
+            for (int c = 0; c < 3; c++) acc += (double)A[3 * r + c] * (double)x[c];
+            y[r] = (float)acc + b[r];
+        }
+    }
+    template <class KeyFrameT>
+    static orbm_proj_params kf_grid_params(KeyFrameT* pKF, float th) {
+        orbm_proj_params P = orbm_proj_params();
+        P.minX = pKF->mnMinX; P.maxX = pKF->mnMaxX; P.minY = pKF->mnMinY; P.maxY = pKF->mnMaxY;
+        P.grid_w_inv = pKF->mfGridElementWidthInv; P.grid_h_inv = pKF->mfGridElementHeightInv;
+        P.nlevels = (int)pKF->mvScaleFactors.size();
+        for (int i = 0; i < P.nlevels && i < ORBX_MAX_LEVELS; i++) P.scale[i] = pKF->mvScaleFactors[i];
+        P.th = th;
+        return P;
+    }
+    // Decompose Scw (:293-298) and run the per-point gates of :313-351 / :1003-1041; a point that passes gets
+    // valid = 1, its projection, predicted level and descriptor.
+    template <class KeyFrameT, class MapPointT, class SetT>
+    static void project_sim3(KeyFrameT* pKF, const cv::Mat& Scw, const std::vector<MapPointT*>& vpPoints, const SetT& spAlreadyFound,
+                             Sim3Points& S) {
+        const float fx = pKF->fx, fy = pKF->fy, cx = pKF->cx, cy = pKF->cy;
+        double dot = 0;  // sRcw.row(0).dot(sRcw.row(0)): cv::Mat::dot returns the double sum
+        for (int c = 0; c < 3; c++) dot += (double)Scw.at<float>(0, c) * (double)Scw.at<float>(0, c);
+        const float scw = (float)std::sqrt(dot);
+        const float is = (float)(1.0 / scw);  // Mat / scalar: the elements are scaled by 1/scw as a float factor
+        float Rcw[9], tcw[3], Ow[3];
+        for (int r = 0; r < 3; r++) {
+            for (int c = 0; c < 3; c++) Rcw[3 * r + c] = Scw.at<float>(r, c) * is;
+            tcw[r] = Scw.at<float>(r, 3) * is;
+        }
+        for (int r = 0; r < 3; r++) {  // Ow = -Rcw.t()*tcw
+            double acc = 0;
+            for (int c = 0; c < 3; c++) acc += (double)Rcw[3 * c + r] * (double)tcw[c];
+            Ow[r] = -(float)acc;
+        }
+        const int n = (int)vpPoints.size();
+        S.u.assign(n, 0.f); S.v.assign(n, 0.f); S.lvl.assign(n, 0); S.valid.assign(n, 0); S.desc.assign((size_t)n * 32, 0);
+        for (int i = 0; i < n; i++) {
+            MapPointT* pMP = vpPoints[i];
+            if (pMP->isBad() || spAlreadyFound.count(pMP)) continue;
+            float w[3], pc[3];
+            vec3(pMP->GetWorldPos(), w);
+            mul_add(Rcw, w, tcw, pc);
+            if (pc[2] < 0.0f) continue;
+            const float invz = (float)(1.0 / pc[2]);
+            const float x = pc[0] * invz, y = pc[1] * invz;
+            const float u = fx * x + cx, v = fy * y + cy;
+            if (!pKF->IsInImage(u, v)) continue;
+            const cv::Mat Pn = pMP->GetNormal();
+            double n2 = 0, d = 0;
+            for (int k = 0; k < 3; k++) {
+                const float po = w[k] - Ow[k];
+                n2 += (double)po * (double)po;
+                d += (double)po * (double)Pn.at<float>(k, 0);
+            }
+            const float dist = (float)std::sqrt(n2);  // cv::norm(PO)
+            if (dist < pMP->GetMinDistanceInvariance() || dist > pMP->GetMaxDistanceInvariance()) continue;
+            if (d < 0.5 * dist) continue;
+            S.lvl[i] = pMP->PredictScale(dist, pKF);
+            S.u[i] = u; S.v[i] = v;
+            S.valid[i] = 1;
+            const cv::Mat dMP = pMP->GetDescriptor();
+            for (int k = 0; k < 32; k++) S.desc[(size_t)i * 32 + k] = dMP.ptr()[k];
+        }
+    }
+    // One direction of SearchBySim3 (:1140-1218 / :1221-1299): the points of the source keyframe go through their own
+    // camera pose (Rsw, tsw) and the relative Sim3 (sR, t) into the destination keyframe, whose grid is searched.
+    template <class KeyFrameT, class MapPointT>
+    int sim3_direction(KeyFrameT* pDst, const std::vector<MapPointT*>& pts, const std::vector<uint8_t>& already, const float* Rsw,
+                       const float* tsw, const float* sR, const float* t, float th, std::vector<int>& vnMatch) {
+        const int n = (int)pts.size(), nK = (int)pDst->mvKeysUn.size();
+        const float fx = pDst->fx, fy = pDst->fy, cx = pDst->cx, cy = pDst->cy;
+        std::vector<float> u(n, 0.f), v(n, 0.f), ur(n, 0.f), invSigma2(ORBX_MAX_LEVELS, 0.f);
+        std::vector<int32_t> lvl(n, 0);
+        std::vector<uint8_t> valid(n, 0), desc((size_t)n * 32, 0);
+        for (int i = 0; i < n; i++) {
+            MapPointT* pMP = pts[i];
+            if (!pMP || already[i] || pMP->isBad()) continue;
+            float w[3], c1[3], c2[3];
+            vec3(pMP->GetWorldPos(), w);
+            mul_add(Rsw, w, tsw, c1);
+            mul_add(sR, c1, t, c2);
+            if (c2[2] < 0.0f) continue;
+            const float invz = (float)(1.0 / c2[2]);
+            const float x = c2[0] * invz, y = c2[1] * invz;
+            const float pu = fx * x + cx, pv = fy * y + cy;
+            if (!pDst->IsInImage(pu, pv)) continue;
+            const float dist3D = (float)std::sqrt((double)c2[0] * c2[0] + (double)c2[1] * c2[1] + (double)c2[2] * c2[2]);
+            if (dist3D < pMP->GetMinDistanceInvariance() || dist3D > pMP->GetMaxDistanceInvariance()) continue;
+            lvl[i] = pMP->PredictScale(dist3D, pDst);
+            u[i] = pu; v[i] = pv;
+            valid[i] = 1;
+            const cv::Mat dMP = pMP->GetDescriptor();
+            for (int k = 0; k < 32; k++) desc[(size_t)i * 32 + k] = dMP.ptr()[k];
+        }
+        orbm_proj_params P = kf_grid_params(pDst, th);
+        orbm_fuse_points fp = {n, u.data(), v.data(), ur.data(), lvl.data(), valid.data(), desc.data()};
+        orbm_cur_frame kf = {nK, (const orbx_kp*)pDst->mvKeysUn.data(), nullptr, pDst->mDescriptors.ptr(), nullptr};
+        std::vector<int32_t> bestIdx(n, -1);
+        std::vector<uint16_t> bestDist(n, 256);
+        if (n) check(orbm_fuse_search(tls(), &P, invSigma2.data(), 0, &fp, &kf, bestIdx.data(), bestDist.data()), "orbm_fuse_search");
+        vnMatch.assign(n, -1);
+        int found = 0;
+        for (int i = 0; i < n; i++)
+            if (valid[i] && bestIdx[i] >= 0 && bestDist[i] <= TH_HIGH) { vnMatch[i] = bestIdx[i]; found++; }
+        return found;
+    }
+
     // std::map<node, vector<feature>> (fbow::fBow2) flattened to the CSR form of the C ABI
     struct BowCsr {
         std::vector<uint32_t> id, feat;

@@ -167,4 +167,41 @@ struct BowFrame : Frame { fbow::fBow2 mFbowFeatVec; };
 int instantiate3(ORB_SLAM2::ORBmatcher& m, KeyFrame* kf, BowFrame& F, std::vector<MapPoint*>& out) { return m.SearchByFboW(kf, F, out); }
 int instantiate4(ORB_SLAM2::ORBmatcher& m, KeyFrame* a, KeyFrame* b, std::vector<MapPoint*>& out) { return m.SearchByFboW(a, b, out); }
 int instantiate2(ORB_SLAM2::ORBmatcher& m, Frame& F, const std::vector<MapPoint*>& v) { return m.SearchByProjection(F, v, 3.f); }
+struct Sim3KeyFrame;
+struct Sim3MapPoint : FuseMapPoint {
+    int GetIndexInKeyFrame(Sim3KeyFrame*) { return -1; }
+    void AddObservation(Sim3KeyFrame*, int) {}
+    template <class K> int PredictScale(float, K*) { return 0; }
+};
+struct Sim3KeyFrame {
+    float fx = 0, fy = 0, cx = 0, cy = 0, mnMinX = 0, mnMaxX = 0, mnMinY = 0, mnMaxY = 0;
+    float mfGridElementWidthInv = 0, mfGridElementHeightInv = 0;
+    std::vector<float> mvScaleFactors;
+    std::vector<cv::KeyPoint> mvKeysUn;
+    cv::Mat mDescriptors, R, t;
+    std::vector<Sim3MapPoint*> mps;
+    cv::Mat GetRotation() { return R; }
+    cv::Mat GetTranslation() { return t; }
+    bool IsInImage(float x, float y) { return x >= mnMinX && x < mnMaxX && y >= mnMinY && y < mnMaxY; }
+    std::vector<Sim3MapPoint*> GetMapPointMatches() { return mps; }
+    std::set<Sim3MapPoint*> GetMapPoints() { return std::set<Sim3MapPoint*>(mps.begin(), mps.end()); }
+    Sim3MapPoint* GetMapPoint(int i) { return mps[i]; }
+    void AddMapPoint(Sim3MapPoint* p, int i) { mps[i] = p; }
+};
+int instantiate8(ORB_SLAM2::ORBmatcher& m, Frame& F1, Frame& F2, std::vector<cv::Point2f>& prev, std::vector<int>& m12) {
+    return m.SearchForInitialization(F1, F2, prev, m12, 100);
+}
+int instantiate9(ORB_SLAM2::ORBmatcher& m, Sim3KeyFrame* kf, cv::Mat Scw, const std::vector<Sim3MapPoint*>& pts,
+                 std::vector<Sim3MapPoint*>& matched) {
+    return m.SearchByProjection(kf, Scw, pts, matched, 10);
+}
+int instantiate10(ORB_SLAM2::ORBmatcher& m, Sim3KeyFrame* kf, cv::Mat Scw, const std::vector<Sim3MapPoint*>& pts,
+                  std::vector<Sim3MapPoint*>& repl) {
+    return m.Fuse(kf, Scw, pts, 4.0f, repl);
+}
+int instantiate11(ORB_SLAM2::ORBmatcher& m, Sim3KeyFrame* a, Sim3KeyFrame* b, std::vector<Sim3MapPoint*>& m12, const cv::Mat& R12,
+                  const cv::Mat& t12) {
+    const float s12 = 1.0f;
+    return m.SearchBySim3(a, b, m12, s12, R12, t12, 7.5f);
+}
 }  // namespace dropin_check
