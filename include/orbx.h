@@ -315,6 +315,14 @@ typedef struct {
 } orbm_bow_side;
 int orbm_search_by_bow(orbm_t* m, const orbm_bow_side* a, const orbm_bow_side* b, int n_pos_a, int n_pos_b, float nn_ratio,
                        int th, int strict, int check_orientation, int32_t* match_a, int* nmatches);
+/* The same search for npairs independent (a[k], b[k]) pairs in ONE launch sequence: Relocalization matches the current
+ * frame against every candidate keyframe (src/Tracking.cc:1465-1490: a[k] = candidate k, b[k] = the frame, the same
+ * pointers for every k — a host array passed several times is staged once), LoopClosing::ComputeSim3 the current keyframe
+ * against every loop candidate (src/LoopClosing.cc:290-312, strict = 1). A single pair is latency bound on the GPU; the
+ * batch shares the launches and the fixed-point rounds. match_a[k] (a[k].n entries) and nmatches[k] as above. */
+int orbm_search_by_bow_batch(orbm_t* m, int npairs, const orbm_bow_side* a, const orbm_bow_side* b, const int* n_pos_a,
+                             const int* n_pos_b, float nn_ratio, int th, int strict, int check_orientation,
+                             int32_t* const* match_a, int* nmatches);
 
 /* ORBmatcher::SearchForTriangulation (include/ORBmatcher.h:76-77, src/ORBmatcher.cc:652-819; LocalMapping::
  * CreateNewMapPoints src/LocalMapping.cc:268) on the same machinery: sides as above with

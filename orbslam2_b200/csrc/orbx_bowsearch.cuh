@@ -31,8 +31,7 @@ struct BowDev {
 };
 
 // per entry p of A's feature vector: the matching node of B (or -1), found once
-__global__ void k_bow_pair_nodes(BowDev S, int* __restrict__ posNodeB) {
-    const int j = blockIdx.x * blockDim.x + threadIdx.x;  // node of A
+__device__ __forceinline__ void d_bow_pair_nodes(const BowDev& S, int* __restrict__ posNodeB, int j /* node of A */) {
     if (j >= S.nNodesA) return;
     const uint32_t id = S.nodeIdA[j];
     int lo = 0, hi = S.nNodesB - 1, hit = -1;
@@ -44,20 +43,23 @@ __global__ void k_bow_pair_nodes(BowDev S, int* __restrict__ posNodeB) {
     }
     for (int p = S.offA[j]; p < S.offA[j + 1]; p++) posNodeB[p] = hit;
 }
+__global__ void k_bow_pair_nodes(BowDev S, int* __restrict__ posNodeB) {
+    d_bow_pair_nodes(S, posNodeB, blockIdx.x * blockDim.x + threadIdx.x);
+}
 
-__global__ void k_bow_claim(BowDev S, const int* __restrict__ choice, int* __restrict__ owner, const int* __restrict__ flag,
-                            int round) {
-    if (round > 0 && flag[round - 1] == 0) return;
-    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+__device__ __forceinline__ void d_bow_claim(const BowDev& S, const int* __restrict__ choice, int* __restrict__ owner, int p) {
     if (p >= S.nPosA) return;
     const int c = choice[p];
     if (c >= 0) atomicMin(&owner[c], p);
 }
-
-__global__ void __launch_bounds__(128) k_bow_choose(BowDev S, const int* __restrict__ posNodeB, int* __restrict__ choice,
-                                                    const int* __restrict__ owner, int* __restrict__ flag, int round) {
+__global__ void k_bow_claim(BowDev S, const int* __restrict__ choice, int* __restrict__ owner, const int* __restrict__ flag,
+                            int round) {
     if (round > 0 && flag[round - 1] == 0) return;
-    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    d_bow_claim(S, choice, owner, blockIdx.x * blockDim.x + threadIdx.x);
+}
+
+__device__ __forceinline__ void d_bow_choose(const BowDev& S, const int* __restrict__ posNodeB, int* __restrict__ choice,
+                                             const int* __restrict__ owner, int* __restrict__ flag, int round, int p) {
     if (p >= S.nPosA) return;
     int nc = -1;
     const int jb = posNodeB[p];
@@ -80,6 +82,11 @@ __global__ void __launch_bounds__(128) k_bow_choose(BowDev S, const int* __restr
         choice[p] = nc;
         flag[round] = 1;
     }
+}
+__global__ void __launch_bounds__(128) k_bow_choose(BowDev S, const int* __restrict__ posNodeB, int* __restrict__ choice,
+                                                    const int* __restrict__ owner, int* __restrict__ flag, int round) {
+    if (round > 0 && flag[round - 1] == 0) return;
+    d_bow_choose(S, posNodeB, choice, owner, flag, round, blockIdx.x * blockDim.x + threadIdx.x);
 }
 
 // ORBmatcher::SearchForTriangulation's scan (src/ORBmatcher.cc:697-749): best = TH_LOW; a candidate replaces the best
@@ -127,8 +134,8 @@ __global__ void __launch_bounds__(128) k_tri_choose(BowDev S, const int* __restr
     }
 }
 
-__global__ void __launch_bounds__(1024) k_bow_finish(BowDev S, const int* __restrict__ choice, int32_t* __restrict__ matchA,
-                                                     int* __restrict__ result) {
+__device__ __forceinline__ void d_bow_finish(const BowDev& S, const int* __restrict__ choice, int32_t* __restrict__ matchA,
+                                             int* __restrict__ result) {
     __shared__ int hist[SP_HISTO];
     __shared__ int keepBin[SP_HISTO];
     __shared__ int nKeep;
@@ -180,6 +187,39 @@ __global__ void __launch_bounds__(1024) k_bow_finish(BowDev S, const int* __rest
     if (mine) atomicAdd(&nKeep, mine);
     __syncthreads();
     if (tid == 0) result[0] = nKeep;
+}
+__global__ void __launch_bounds__(1024) k_bow_finish(BowDev S, const int* __restrict__ choice, int32_t* __restrict__ matchA,
+                                                     int* __restrict__ result) {
+    d_bow_finish(S, choice, matchA, result);
+}
+
+// ---- batched form: one launch sequence serves npairs independent (A, B) pairs (blockIdx.y = pair) -----------------------
+// Relocalization matches the current frame against every candidate keyframe (src/Tracking.cc:1465-1490), LoopClosing a
+// keyframe against every loop candidate (src/LoopClosing.cc:290-312): a single pair is latency bound on the GPU, the
+// batch amortises the launches and the fixed-point rounds (a round ends for all pairs when no pair changed).
+struct BowPair {
+    BowDev S;
+    int *posNodeB, *choice, *owner;
+    int32_t* oMatch;
+    int* result;
+};
+__global__ void k_bowb_pair_nodes(const BowPair* __restrict__ P) {
+    const BowPair& Q = P[blockIdx.y];
+    d_bow_pair_nodes(Q.S, Q.posNodeB, blockIdx.x * blockDim.x + threadIdx.x);
+}
+__global__ void k_bowb_claim(const BowPair* __restrict__ P, const int* __restrict__ flag, int round) {
+    if (round > 0 && flag[round - 1] == 0) return;
+    const BowPair& Q = P[blockIdx.y];
+    d_bow_claim(Q.S, Q.choice, Q.owner, blockIdx.x * blockDim.x + threadIdx.x);
+}
+__global__ void __launch_bounds__(128) k_bowb_choose(const BowPair* __restrict__ P, int* __restrict__ flag, int round) {
+    if (round > 0 && flag[round - 1] == 0) return;
+    const BowPair& Q = P[blockIdx.y];
+    d_bow_choose(Q.S, Q.posNodeB, Q.choice, Q.owner, flag, round, blockIdx.x * blockDim.x + threadIdx.x);
+}
+__global__ void __launch_bounds__(1024) k_bowb_finish(const BowPair* __restrict__ P) {
+    const BowPair& Q = P[blockIdx.y];
+    d_bow_finish(Q.S, Q.choice, Q.oMatch, Q.result);
 }
 
 static int bow_side_ok(const orbm_bow_side* s) {
@@ -306,4 +346,138 @@ extern "C" int orbm_search_for_triangulation(orbm_t* m, const orbm_bow_side* a, 
                                              int32_t* match_a, int* nmatches) {
     if (!T) FAIL(ORBX_EINVAL, "null argument");
     return bow_run(m, a, b, n_pos_a, n_pos_b, 0.f, th, 0, check_orientation, T, match_a, nmatches);
+}
+
+
+extern "C" int orbm_search_by_bow_batch(orbm_t* m, int npairs, const orbm_bow_side* a, const orbm_bow_side* b,
+                                        const int* n_pos_a, const int* n_pos_b, float nn_ratio, int th, int strict,
+                                        int check_orientation, int32_t* const* match_a, int* nmatches) {
+    if (!m || npairs < 0 || (npairs && (!a || !b || !n_pos_a || !n_pos_b || !match_a || !nmatches)))
+        FAIL(ORBX_EINVAL, "null argument");
+    if (npairs == 0) return ORBX_OK;
+    if (npairs > 65535) FAIL(ORBX_EINVAL, "too many pairs");
+    CK(cudaSetDevice(m->device));
+    cudaStream_t st = m->stream;
+    const bool hin = m->inSpace == ORBX_MEM_HOST, hout = m->outSpace == ORBX_MEM_HOST;
+    // sizes; a host array passed for several pairs (the current frame of a relocalisation) is staged once
+    std::vector<std::pair<const void*, const void*> > seen;  // (source, device copy)
+    size_t need = (size_t)npairs * (sizeof(BowPair) + 256) + 256 * 8;
+    int maxPosA = 0, maxNodesA = 0, sumPosA = 0;
+    for (int k = 0; k < npairs; k++) {
+        const orbm_bow_side *A = a + k, *B = b + k;
+        if (!bow_side_ok(A) || !bow_side_ok(B) || (A->n && !A->eligible) || n_pos_a[k] < 0 || n_pos_b[k] < 0 || (A->n && !match_a[k]))
+            FAIL(ORBX_EINVAL, "bad feature-vector arrays (pair %d)", k);
+        need += (size_t)A->n * (1 + 4 + 32 + 4) + (size_t)B->n * (1 + 4 + 32 + 4) + (size_t)(A->n_nodes + B->n_nodes + 2) * 8 +
+                (size_t)(n_pos_a[k] + n_pos_b[k]) * 4 + (size_t)n_pos_a[k] * 8 + 256 * 20;
+        maxPosA = std::max(maxPosA, n_pos_a[k]);
+        maxNodesA = std::max(maxNodesA, A->n_nodes);
+        sumPosA += n_pos_a[k];
+        nmatches[k] = 0;
+    }
+    const int maxRounds = maxPosA + 8;
+    need += (size_t)maxRounds * 4;
+    int rc;
+    if ((rc = ensure(m->dWs, m->wsCap, need))) return rc;
+    if (m->hFlagsCap < (size_t)std::max(maxRounds, npairs)) {
+        if (m->hFlags) cudaFreeHost(m->hFlags);
+        m->hFlags = nullptr;
+        CK(cudaMallocHost(&m->hFlags, (size_t)std::max(maxRounds, npairs) * sizeof(int)));
+        m->hFlagsCap = (size_t)std::max(maxRounds, npairs);
+    }
+    if ((hin || hout) && (rc = ensure_host_in(m, need))) return rc;
+    WsCursor W{m->dWs, 0};
+    BowPair* dPairs = W.take<BowPair>(npairs);
+    int* flags = W.take<int>(maxRounds);
+    int* dRes = W.take<int>(npairs);
+    Stager stg{m, &W, hin, (size_t)-1};
+    auto in = [&](const void* src, size_t bytes) -> const void* {
+        if (!src || !hin) return src;
+        for (size_t i = 0; i < seen.size(); i++)
+            if (seen[i].first == src) return seen[i].second;
+        const void* d = stg.in(src, bytes);
+        seen.push_back(std::make_pair(src, d));
+        return d;
+    };
+    std::vector<BowPair> hp((size_t)npairs);
+    for (int k = 0; k < npairs; k++) {
+        const orbm_bow_side *A = a + k, *B = b + k;
+        BowDev& S = hp[k].S;
+        memset(&S, 0, sizeof(S));
+        S.nA = A->n; S.nB = B->n; S.nPosA = n_pos_a[k];
+        S.eligA = (const uint8_t*)in(A->eligible, A->n);
+        S.eligB = (const uint8_t*)in(B->eligible, B->n);
+        S.angA = (const float*)in(A->angle, (size_t)A->n * 4);
+        S.angB = (const float*)in(B->angle, (size_t)B->n * 4);
+        S.descA = (const uint4*)in(A->desc, (size_t)A->n * 32);
+        S.descB = (const uint4*)in(B->desc, (size_t)B->n * 32);
+        S.nNodesA = A->n_nodes; S.nNodesB = B->n_nodes;
+        S.nodeIdA = (const uint32_t*)in(A->node_id, (size_t)A->n_nodes * 4);
+        S.nodeIdB = (const uint32_t*)in(B->node_id, (size_t)B->n_nodes * 4);
+        S.offA = (const int*)in(A->node_off, (size_t)(A->n_nodes + 1) * 4);
+        S.offB = (const int*)in(B->node_off, (size_t)(B->n_nodes + 1) * 4);
+        S.featA = (const uint32_t*)in(A->node_feat, (size_t)n_pos_a[k] * 4);
+        S.featB = (const uint32_t*)in(B->node_feat, (size_t)n_pos_b[k] * 4);
+        S.nnRatio = nn_ratio; S.th = th; S.strict = strict; S.checkOri = check_orientation;
+        if ((((uintptr_t)S.descA) | ((uintptr_t)S.descB)) & 15) FAIL(ORBX_EINVAL, "device descriptor matrices must be 16-byte aligned");
+        // a pair with an empty side or no nodes has no candidates: nPosA = 0 leaves match_a all -1
+        if (B->n == 0 || A->n_nodes == 0 || B->n_nodes == 0) { S.nPosA = 0; S.nNodesA = 0; }
+    }
+    if ((rc = stg.flush(st))) return rc;
+    // scratch: choice and owner of all pairs are contiguous so that one memset serves a round
+    int* choiceAll = W.take<int>((size_t)std::max(sumPosA, 1));
+    size_t sumB = 0;
+    for (int k = 0; k < npairs; k++) sumB += (size_t)b[k].n;
+    int* ownerAll = W.take<int>(std::max<size_t>(sumB, 1));
+    size_t sumA = 0;
+    for (int k = 0; k < npairs; k++) sumA += (size_t)a[k].n;
+    int32_t* matchAll = hout ? W.take<int32_t>(std::max<size_t>(sumA, 1)) : nullptr;  // leaves in one copy
+    size_t cOff = 0, oOff = 0, mOff = 0;
+    for (int k = 0; k < npairs; k++) {
+        hp[k].choice = choiceAll + cOff;
+        hp[k].owner = ownerAll + oOff;
+        cOff += (size_t)n_pos_a[k];
+        oOff += (size_t)b[k].n;
+        hp[k].posNodeB = W.take<int>((size_t)std::max(n_pos_a[k], 1));
+        hp[k].oMatch = hout ? matchAll + mOff : match_a[k];
+        mOff += (size_t)a[k].n;
+        hp[k].result = dRes + k;
+    }
+    if (W.off > m->wsCap) FAIL(ORBX_ECUDA, "internal: workspace estimate too small (%zu > %zu)", W.off, m->wsCap);
+    CK(cudaMemcpyAsync(dPairs, hp.data(), (size_t)npairs * sizeof(BowPair), cudaMemcpyHostToDevice, st));
+    if (maxNodesA) k_bowb_pair_nodes<<<dim3((maxNodesA + 127) / 128, npairs), 128, 0, st>>>(dPairs);
+    m->launches++;
+    CK(cudaMemsetAsync(choiceAll, 0xFF, (size_t)std::max(sumPosA, 1) * sizeof(int), st));
+    CK(cudaMemsetAsync(flags, 0, (size_t)maxRounds * sizeof(int), st));
+    int round = 0, rounds = 0;
+    while (maxPosA > 0) {
+        const int R = 4;
+        if (round + R > maxRounds) FAIL(ORBX_ECUDA, "internal: greedy resolution did not converge in %d rounds", maxRounds);
+        for (int r = 0; r < R; r++, round++) {
+            CK(cudaMemsetAsync(ownerAll, 0x7F, std::max<size_t>(sumB, 1) * sizeof(int), st));
+            k_bowb_claim<<<dim3((maxPosA + 255) / 256, npairs), 256, 0, st>>>(dPairs, flags, round);
+            k_bowb_choose<<<dim3((maxPosA + 127) / 128, npairs), 128, 0, st>>>(dPairs, flags, round);
+            m->launches += 2;
+        }
+        CK(cudaGetLastError());
+        CK(cudaMemcpyAsync(m->hFlags, flags, (size_t)round * sizeof(int), cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        rounds = 0;
+        while (rounds < round && m->hFlags[rounds]) rounds++;
+        if (rounds < round) break;
+    }
+    k_bowb_finish<<<dim3(1, npairs), 1024, 0, st>>>(dPairs);
+    m->launches++;
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(m->hFlags, dRes, (size_t)npairs * sizeof(int), cudaMemcpyDeviceToHost, st));
+    if (hout && sumA) CK(cudaMemcpyAsync(m->hIn, matchAll, sumA * 4, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    mOff = 0;
+    for (int k = 0; k < npairs; k++) {
+        nmatches[k] = m->hFlags[k];
+        if (hout && a[k].n) memcpy(match_a[k], m->hIn + mOff * 4, (size_t)a[k].n * 4);
+        mOff += (size_t)a[k].n;
+    }
+    m->lastRounds = rounds + 1;
+    m->lastCandidates = 0;
+    return ORBX_OK;
 }

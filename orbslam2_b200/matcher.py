@@ -334,6 +334,36 @@ class ORBmatcher:
                                               int(self.mbCheckOrientation), match.ctypes.data, C.byref(n)))
         return n.value, match
 
+    def SearchByFboWBatch(self, pairs, strict=False, th=None):
+        """SearchByFboW for a list of (a, b) pairs in one launch sequence (orbm_search_by_bow_batch): the candidate
+        keyframes of Relocalization / LoopClosing. pairs: [(a, b), ...] bow_side dicts as for SearchByFboW; the same b
+        dict may appear in every pair (it is staged once). Returns [(nmatches, match_a), ...]."""
+        self._set_space(_lib.MEM_HOST, _lib.MEM_HOST)
+        K = len(pairs)
+        keep = []
+
+        def side(d, need_elig):
+            elig = d["eligible"]
+            if elig is None and need_elig:
+                elig = d.setdefault("_ones", np.ones(d["n"], np.uint8))
+            keep.append(elig)
+            return _lib.BowSide(d["n"], None if elig is None else elig.ctypes.data, d["angle"].ctypes.data,
+                                d["desc"].ctypes.data, len(d["node_id"]), d["node_id"].ctypes.data,
+                                d["node_off"].ctypes.data, d["node_feat"].ctypes.data)
+
+        A = (_lib.BowSide * max(K, 1))(*[side(a, True) for a, _ in pairs])
+        B = (_lib.BowSide * max(K, 1))(*[side(b, False) for _, b in pairs])
+        npa = np.array([int(a["node_off"][-1]) for a, _ in pairs], np.int32)
+        npb = np.array([int(b["node_off"][-1]) for _, b in pairs], np.int32)
+        out = [np.full(a["n"], -1, np.int32) for a, _ in pairs]
+        ptrs = (C.c_void_p * max(K, 1))(*[o.ctypes.data for o in out])
+        nm = np.zeros(max(K, 1), np.int32)
+        _lib.check(self._L.orbm_search_by_bow_batch(self._h, K, C.cast(A, C.c_void_p), C.cast(B, C.c_void_p), npa.ctypes.data,
+                                                    npb.ctypes.data, float(self.mfNNratio),
+                                                    int(self.TH_LOW if th is None else th), int(strict),
+                                                    int(self.mbCheckOrientation), C.cast(ptrs, C.c_void_p), nm.ctypes.data))
+        return [(int(nm[k]), out[k]) for k in range(K)]
+
     def SearchForTriangulation(self, a, b, geo, th=None):
         """SearchForTriangulation(pKF1, pKF2, F12, vMatchedPairs, bOnlyStereo) (src/ORBmatcher.cc:652-819). a, b: bow_side
         dicts with eligible = "no map point (and stereo when bOnlyStereo)"; geo: dict(pt_a [nA,2], pt_b [nB,2], octave_b,

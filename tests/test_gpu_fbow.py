@@ -256,3 +256,60 @@ def test_search_for_triangulation_vs_oracle(ob, only_stereo):
             m.close()
     assert total > (100 if only_stereo else 400)
     voc.close()
+
+
+@pytest.mark.parametrize("strict", [False, True])
+def test_search_by_bow_batch_vs_oracle(ob, strict):
+    """orbm_search_by_bow_batch: K candidate keyframes against one frame (Relocalization) / keyframe (LoopClosing) in
+    one launch sequence — every pair bit-identical to the sequential restatement, incl. ragged sizes, an adversarial
+    chain pair that needs many rounds while the others converged long ago, a disjoint pair and empty sides."""
+    from oracle_lib import oracle_search_by_bow
+    blob = synth_vocabulary(k=10, levels=5, seed=33)
+    voc = ob.Vocabulary(); voc.fromStream(blob)
+    rng = np.random.default_rng(17)
+    nb = 1200
+    pairs = []
+    B = None
+    for k, na in enumerate([900, 1500, 300, 1100, 40, 700]):
+        da, ang_a, _, db, ang_b, _ = _bow_frames(ob, voc, blob, na, nb, 70 + k, 4)
+        fa = voc.transform(da, 4)[1]
+        elig_a = (rng.random(na) < 0.8).astype(np.uint8)
+        A = ob.ORBmatcher.bow_side(da, ang_a, fa, elig_a)
+        if strict or B is None:  # the relocalisation shape shares ONE frame among the pairs
+            fb = voc.transform(db, 4)[1]
+            elig_b = (rng.random(nb) < 0.85).astype(np.uint8) if strict else None
+            Bk = ob.ORBmatcher.bow_side(db, ang_b, fb, elig_b)
+            if B is None:
+                B = Bk
+        pairs.append((A, Bk if strict else B))
+    # adversarial chain, disjoint nodes, empty sides
+    n = 40
+    base = rng.integers(0, 256, 32, dtype=np.uint8)
+    bits = np.unpackbits(np.repeat(base[None], n, 0), axis=1)
+    for r in range(n):
+        bits[r, :2 * r] ^= 1
+    dbc = np.packbits(bits, axis=1)
+    dac = np.repeat(base[None], n, 0)
+    Ac = ob.ORBmatcher.bow_side(dac, np.zeros(n, np.float32), {7: np.arange(n, dtype=np.uint32)}, np.ones(n, np.uint8))
+    Bc = ob.ORBmatcher.bow_side(dbc, np.zeros(n, np.float32), {7: rng.permutation(n).astype(np.uint32)},
+                                np.ones(n, np.uint8) if strict else None)
+    Bd = ob.ORBmatcher.bow_side(dbc, np.zeros(n, np.float32), {9: np.arange(n, dtype=np.uint32)}, None)
+    E = ob.ORBmatcher.bow_side(np.zeros((0, 32), np.uint8), np.zeros(0, np.float32), {}, None)
+    pairs += [(Ac, Bc), (Ac, Bd), (Ac, E), (E, Bc)]
+    for ratio, ori in ((0.99, False), (0.75, True)):
+        m = ob.ORBmatcher(ratio, ori)
+        got = m.SearchByFboWBatch(pairs, strict=strict)
+        assert len(got) == len(pairs)
+        total = 0
+        for k, (A, Bk) in enumerate(pairs):
+            en, ematch = oracle_search_by_bow(A, Bk, ratio, 50, strict, ori)
+            assert got[k][0] == en and np.array_equal(got[k][1], ematch), (k, ratio, ori)
+            one = m.SearchByFboW(A, Bk, strict=strict)
+            assert one[0] == en and np.array_equal(one[1], ematch)
+            total += en
+        assert total > 500
+        if not ori:
+            assert got[6][0] >= 10
+        assert m.SearchByFboWBatch([], strict=strict) == []
+        m.close()
+    voc.close()
