@@ -976,10 +976,19 @@ extern "C" int orbm_search_for_initialization(orbm_t* m, const orbm_proj_params*
     int* candIdx = (int*)m->dCand;
     unsigned short* candDist = (unsigned short*)(m->dCand + ((total + 63) & ~(size_t)63) * 4);
     k_sp_candidates<true><<<qBlocks, 256, 0, st>>>(S, cellStart, items, nullptr, candOff, candIdx, candDist);
-    CK(cudaMemsetAsync(matchedDist, 0x7F, (size_t)nC * sizeof(int), st));  // 0x7F7F7F7F: above every distance
-    CK(cudaMemsetAsync(match21, 0xFF, (size_t)nC * sizeof(int), st));
     CK(cudaMemsetAsync(o12, 0xFF, (size_t)nL * sizeof(int), st));
-    k_init_greedy<<<1, 32, 0, st>>>(S, candOff, candIdx, candDist, th_low, matchedDist, match21, o12, bin12, oPrev, dRes);
+    CK(cudaMemsetAsync(bin12, 0xFF, (size_t)nL * sizeof(int), st));
+    const size_t stageBytes = 2 * ((size_t)INIT_STAGE * 4 + ((size_t)INIT_STAGE + 2) * 2) + 16;
+    const size_t smem = (size_t)nC * 8 + stageBytes;
+    if (smem <= 220 * 1024) {  // claim state in shared memory
+        CK(cudaFuncSetAttribute(k_init_greedy<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_init_greedy<true><<<1, 32, smem, st>>>(S, candOff, candIdx, candDist, th_low, nullptr, nullptr, o12, bin12, oPrev, dRes);
+    } else {
+        CK(cudaMemsetAsync(matchedDist, 0x7F, (size_t)nC * sizeof(int), st));  // 0x7F7F7F7F: above every distance
+        CK(cudaMemsetAsync(match21, 0xFF, (size_t)nC * sizeof(int), st));
+        CK(cudaFuncSetAttribute(k_init_greedy<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)stageBytes));
+        k_init_greedy<false><<<1, 32, stageBytes, st>>>(S, candOff, candIdx, candDist, th_low, matchedDist, match21, o12, bin12, oPrev, dRes);
+    }
     m->launches += 2;
     CK(cudaGetLastError());
     CK(cudaMemcpyAsync(m->hRes, dRes, sizeof(int), cudaMemcpyDeviceToHost, st));

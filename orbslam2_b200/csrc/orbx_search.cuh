@@ -452,61 +452,154 @@ __global__ void __launch_bounds__(1024) k_sp_finish_mp(SpDev S, const int* __res
 // lanes share each query's candidate list (best / second best with multiplicity, first position on ties, merged by
 // shuffles). Only level-0 keypoints query (a few hundred), so the replay is short. The rotation histogram counts every
 // accept, stolen or not, as the reference's rotHist does (:468-478).
+// The replay is latency-critical (one warp, query after query), so nothing state-independent is loaded on the critical
+// path: the offsets of 32 queries arrive with one coalesced load, the first 64 candidates (distance, keypoint) of the next
+// non-empty query are fetched while the current one is resolved, and with SMEM the claim state (vMatchedDistance,
+// vnMatches21) lives in shared memory.
+#define INIT_STAGE 4096  // candidates per staging buffer (two buffers: 2 x 24 KB)
+template <bool SMEM>
 __global__ void __launch_bounds__(32) k_init_greedy(SpDev S, const int* __restrict__ candOff, const int* __restrict__ candIdx,
                                                     const unsigned short* __restrict__ candDist, int thLow,
-                                                    int* matchedDist /* [nCur] preset >= INT_MAX/2 */,
-                                                    int* match21 /* [nCur] preset -1 */, int32_t* match12 /* [nLast] preset -1 */,
-                                                    int* bin12 /* [nLast] */, float* prevOut /* [nLast][2] */,
+                                                    int* gMatchedDist /* [nCur] preset >= INT_MAX/2 (SMEM = false) */,
+                                                    int* gMatch21 /* [nCur] preset -1 (SMEM = false) */,
+                                                    int32_t* match12 /* [nLast] preset -1 */,
+                                                    int* bin12 /* [nLast] preset -1 */, float* prevOut /* [nLast][2] */,
                                                     int* __restrict__ result) {
+    extern __shared__ int initSm[];
     __shared__ int hist[SP_HISTO];
     __shared__ int keepBin[SP_HISTO];
-    __shared__ int nm;
     const int lane = threadIdx.x;
     if (lane < SP_HISTO) { hist[lane] = 0; keepBin[lane] = 1; }
-    if (lane == 0) nm = 0;
+    volatile int* vMatchedDistance = SMEM ? initSm : gMatchedDist;
+    volatile int* vnMatches21 = SMEM ? initSm + S.nCur : gMatch21;
+    if (SMEM)
+        for (int k = lane; k < S.nCur; k += 32) { vMatchedDistance[k] = INT_MAX; vnMatches21[k] = -1; }
     __syncwarp();
-    volatile int* vMatchedDistance = matchedDist;
+    int nm = 0;  // lane 0's count
     const float factor = 1.0f / SP_HISTO;
     const int nL = S.nLast;
-    for (int i = 0; i < nL; i++) {
-        const int s = candOff[i], e = candOff[i + 1];
-        if (s == e) continue;
-        int b = INT_MAX, b2 = INT_MAX, bp = INT_MAX;
-        for (int c = s + lane; c < e; c += 32) {
-            const int dist = candDist[c];
-            if (vMatchedDistance[candIdx[c]] <= dist) continue;
-            if (dist < b) { b2 = b; b = dist; bp = c; }
-            else if (dist < b2) b2 = dist;
+    // Offsets of the queries of a block (lane l <-> query base + l) are loaded two blocks ahead. The candidates of 32
+    // consecutive queries are one contiguous CSR range: the range of the NEXT block is copied into shared memory with
+    // cp.async while the current block is replayed, so the replay itself reads no global memory.
+    const int total = candOff[nL];
+    int* stIdx[2] = {initSm + (SMEM ? 2 * S.nCur : 0), initSm + (SMEM ? 2 * S.nCur : 0) + INIT_STAGE};
+    unsigned short* stDist[2] = {(unsigned short*)(stIdx[1] + INIT_STAGE), (unsigned short*)(stIdx[1] + INIT_STAGE) + INIT_STAGE + 2};
+    auto loadOff = [&](int base, int& a, int& b) {
+        const int q = base + lane;
+        a = b = total;
+        if (q < nL) { a = candOff[q]; b = candOff[q + 1]; }
+    };
+    auto stage = [&](int buf, int bs, int be) {  // candidates [bs, min(be, bs + INIT_STAGE)) -> buffer `buf`
+        be = min(be, bs + INIT_STAGE);
+        for (int c = bs + lane; c < be; c += 32) {
+            const unsigned dst = (unsigned)__cvta_generic_to_shared(stIdx[buf] + (c - bs));
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(candIdx + c) : "memory");
         }
+        const int w0 = bs >> 1, w1 = (be + 1) >> 1;  // distances travel as 4-byte words (two candidates)
+        for (int w = w0 + lane; w < w1; w += 32) {
+            const unsigned dst = (unsigned)__cvta_generic_to_shared((unsigned*)stDist[buf] + (w - w0));
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"((const unsigned*)candDist + w) : "memory");
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    int qs, qe, nqs, nqe;
+    loadOff(0, qs, qe);
+    loadOff(32, nqs, nqe);
+    stage(0, __shfl_sync(0xffffffffu, qs, 0), __shfl_sync(0xffffffffu, qe, 31));
+    for (int base = 0, buf = 0; base < nL; base += 32, buf ^= 1) {
+        int n2s, n2e;
+        loadOff(base + 64, n2s, n2e);
+        asm volatile("cp.async.wait_all;" ::: "memory");
+        __syncwarp();
+        stage(buf ^ 1, __shfl_sync(0xffffffffu, nqs, 0), __shfl_sync(0xffffffffu, nqe, 31));
+        const int bs = __shfl_sync(0xffffffffu, qs, 0);
+        const int stEnd = min(__shfl_sync(0xffffffffu, qe, 31), bs + INIT_STAGE);
+        const int* sIdx = stIdx[buf];
+        const unsigned short* sDist = stDist[buf] - (bs & ~1);
+        unsigned pending = __ballot_sync(0xffffffffu, qs < qe);
+        while (pending) {
+            const int q = __ffs(pending) - 1;
+            pending &= pending - 1;
+            const int i = base + q;
+            const int s = __shfl_sync(0xffffffffu, qs, q), e = __shfl_sync(0xffffffffu, qe, q);
+            int d[4], ix[4], md[4];
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            const int ob = __shfl_xor_sync(0xffffffffu, b, o), ob2 = __shfl_xor_sync(0xffffffffu, b2, o),
-                      obp = __shfl_xor_sync(0xffffffffu, bp, o);
-            if (ob < b || (ob == b && obp < bp)) { b2 = min(ob2, b); b = ob; bp = obp; }
-            else b2 = min(b2, ob);
-        }
-        if (b <= thLow && (float)b < __fmul_rn((float)b2, S.nnRatio)) {
-            if (lane == 0) {
-                const int bestIdx2 = candIdx[bp];
-                const int prev = match21[bestIdx2];
-                int d = 1;
-                if (prev >= 0) { match12[prev] = -1; d = 0; }
-                match12[i] = bestIdx2;
-                match21[bestIdx2] = i;
-                vMatchedDistance[bestIdx2] = b;
-                nm += d;
-                if (S.p.check_orientation) {
-                    float rot = __fsub_rn(S.qkeys[i].angle, S.keys[bestIdx2].angle);
-                    if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
-                    int bin = (int)roundf(__fmul_rn(rot, factor));
-                    if (bin == SP_HISTO) bin = 0;
-                    hist[bin]++;
-                    bin12[i] = bin;
+            for (int k = 0; k < 4; k++) {
+                const int c = s + lane + 32 * k;
+                d[k] = -1;
+                ix[k] = 0;
+                if (c < e) {
+                    if (c < stEnd) { d[k] = sDist[c]; ix[k] = sIdx[c - bs]; }
+                    else { d[k] = candDist[c]; ix[k] = candIdx[c]; }
                 }
             }
-            __syncwarp();
+            // lane-local best / second best over its candidates in list order (positions s + lane + 32k)
+            int b = INT_MAX, b2 = INT_MAX, bp = 0, bi = -1;
+#pragma unroll
+            for (int k = 0; k < 4; k++) md[k] = vMatchedDistance[ix[k]];
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                if (d[k] < 0 || md[k] <= d[k]) continue;
+                if (d[k] < b) { b2 = b; b = d[k]; bp = lane + 32 * k; bi = ix[k]; }
+                else if (d[k] < b2) b2 = d[k];
+            }
+            for (int c0 = s + 128; c0 < e; c0 += 128) {  // long lists: further groups of 128, loads issued together
+#pragma unroll
+                for (int k = 0; k < 4; k++) {
+                    const int c = c0 + lane + 32 * k;
+                    d[k] = -1;
+                    ix[k] = 0;
+                    if (c < e) {
+                        if (c < stEnd) { d[k] = sDist[c]; ix[k] = sIdx[c - bs]; }
+                        else { d[k] = candDist[c]; ix[k] = candIdx[c]; }
+                    }
+                }
+#pragma unroll
+                for (int k = 0; k < 4; k++) md[k] = vMatchedDistance[ix[k]];
+#pragma unroll
+                for (int k = 0; k < 4; k++) {
+                    if (d[k] < 0 || md[k] <= d[k]) continue;
+                    if (d[k] < b) { b2 = b; b = d[k]; bp = c0 - s + lane + 32 * k; bi = ix[k]; }
+                    else if (d[k] < b2) b2 = d[k];
+                }
+            }
+            // warp merge: the winner is the smallest (distance, position); the second best is the smallest of every
+            // other lane's best and the winner lane's own second (two REDUX + one shuffle)
+            const unsigned key = b == INT_MAX ? 0xFFFFFFFFu : ((unsigned)b << 22) | (unsigned)bp;
+            const unsigned wkey = __reduce_min_sync(0xffffffffu, key);
+            const int wlane = (int)(wkey & 31u);  // position = lane + 32k
+            b2 = (int)__reduce_min_sync(0xffffffffu, (unsigned)(lane == wlane ? b2 : b));
+            bi = __shfl_sync(0xffffffffu, bi, wlane);
+            b = wkey == 0xFFFFFFFFu ? INT_MAX : (int)(wkey >> 22);
+            if (b <= thLow && (float)b < __fmul_rn((float)b2, S.nnRatio)) {
+                if (lane == 0) {
+                    const int bestIdx2 = bi;
+                    const int prev = vnMatches21[bestIdx2];
+                    int inc = 1;
+                    if (prev >= 0) { match12[prev] = -1; inc = 0; }
+                    match12[i] = bestIdx2;
+                    vnMatches21[bestIdx2] = i;
+                    vMatchedDistance[bestIdx2] = b;
+                    nm += inc;
+                    bin12[i] = bestIdx2;  // the accept is recorded; its histogram bin is computed after the replay
+                }
+                __syncwarp();
+            }
         }
+        qs = nqs; qe = nqe; nqs = n2s; nqe = n2e;
     }
+    __syncwarp();
+    if (S.p.check_orientation)  // rotHist of every accept (a query is accepted at most once), off the critical path
+        for (int i = lane; i < nL; i += 32) {
+            const int a = bin12[i];
+            if (a < 0) continue;
+            float rot = __fsub_rn(S.qkeys[i].angle, S.keys[a].angle);
+            if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
+            int bin = (int)roundf(__fmul_rn(rot, factor));
+            if (bin == SP_HISTO) bin = 0;
+            atomicAdd(&hist[bin], 1);
+            bin12[i] = bin;
+        }
     __syncwarp();
     if (lane == 0 && S.p.check_orientation) {  // ComputeThreeMaxima, :1597-1638
         int max1 = 0, max2 = 0, max3 = 0, ind1 = -1, ind2 = -1, ind3 = -1;

@@ -77,6 +77,78 @@ def main():
         mb.close()
     voc.close()
 
+    # Relocalization shape: K candidate keyframes against ONE frame — K single calls vs one batched call
+    # (orbm_search_by_bow_batch) vs the sequential CPU restatement
+    voc = ob.Vocabulary(); voc.fromStream(blob)
+    rng = np.random.default_rng(9)
+    for n, K in ((1000, 20), (2000, 20)):
+        dbF = synth_vocabulary_features(blob, n, seed=50)
+        fbF = voc.transform(dbF, 4)[1]
+        B = ob.ORBmatcher.bow_side(dbF, (rng.random(n) * 360).astype(np.float32), fbF, None)
+        pairs = []
+        for k in range(K):
+            pick = rng.permutation(n)[: int(0.5 * n)]
+            da = np.concatenate([dbF[pick], synth_vocabulary_features(blob, n - len(pick), seed=60 + k)])
+            bits = np.unpackbits(da[:len(pick)], axis=1)
+            for _ in range(6):
+                bits[np.arange(len(pick)), rng.integers(0, 256, len(pick))] ^= 1
+            da[:len(pick)] = np.packbits(bits, axis=1)
+            da = np.ascontiguousarray(da[rng.permutation(n)])
+            fa = voc.transform(da, 4)[1]
+            pairs.append((ob.ORBmatcher.bow_side(da, (rng.random(n) * 360).astype(np.float32), fa, np.ones(n, np.uint8)), B))
+        mb = ob.ORBmatcher(0.75, True)
+        for _ in range(3):
+            got = mb.SearchByFboWBatch(pairs)
+        t0 = time.perf_counter()
+        for _ in range(10):
+            got = mb.SearchByFboWBatch(pairs)
+        batch_ms = (time.perf_counter() - t0) / 10 * 1e3
+        rounds = mb.search_stats()[0]
+        t0 = time.perf_counter()
+        for _ in range(5):
+            single = [mb.SearchByFboW(a, b) for a, b in pairs]
+        single_ms = (time.perf_counter() - t0) / 5 * 1e3
+        t0 = time.perf_counter()
+        exp = [oracle_search_by_bow(a, b, 0.75, 50, False, True) for a, b in pairs]
+        cpu_ms = (time.perf_counter() - t0) * 1e3
+        same = all(g[0] == e[0] and np.array_equal(g[1], e[1]) for g, e in zip(got, exp)) and \
+            all(g[0] == e[0] and np.array_equal(g[1], e[1]) for g, e in zip(single, exp))
+        print(json.dumps({"metric": "search_by_bow_ms_per_relocalization", "candidate_keyframes": K, "features_per_side": n,
+                          "gpu_ms_batched_call": batch_ms, "gpu_ms_single_calls": single_ms, "cpu_oracle_ms_1_thread": cpu_ms,
+                          "fixed_point_rounds": rounds, "nmatches_total": int(sum(g[0] for g in got)),
+                          "identical_to_oracle": bool(same)}))
+        mb.close()
+    voc.close()
+
+    # SearchForInitialization (monocular initialisation, window 100): host call vs the sequential CPU restatement
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("tgs", os.path.join(ROOT, "tests", "test_gpu_search.py"))
+    tgs = importlib.util.module_from_spec(spec); spec.loader.exec_module(tgs)
+    from oracle_lib import oracle_search_for_initialization
+    for n in (1000, 2000):
+        F1, F2 = tgs._init_pair(3, n=n)
+        mi = ob.ORBmatcher(0.9, True)
+        start = np.ascontiguousarray(np.stack([F1.mvKeysUn["x"], F1.mvKeysUn["y"]], 1), np.float32)
+        for _ in range(3):
+            got = mi.SearchForInitialization(F1, F2, start.copy(), 100)
+        t0 = time.perf_counter()
+        for _ in range(20):
+            prev = start.copy()
+            got = mi.SearchForInitialization(F1, F2, prev, 100)
+        gpu_ms = (time.perf_counter() - t0) / 20 * 1e3
+        cands = mi.search_stats()[1]
+        t0 = time.perf_counter()
+        for _ in range(5):
+            eprev = start.copy()
+            exp = oracle_search_for_initialization(got[2], np.float32(0.9), F1, F2, eprev, 100)
+        cpu_ms = (time.perf_counter() - t0) / 5 * 1e3
+        print(json.dumps({"metric": "search_for_initialization_ms_per_frame_pair", "keypoints": n,
+                          "level0_queries": int((F1.mvKeysUn["octave"] == 0).sum()), "candidate_pairs": cands,
+                          "gpu_ms_host_call": gpu_ms, "cpu_oracle_ms_1_thread": cpu_ms, "nmatches": got[0],
+                          "identical_to_oracle": bool(got[0] == exp[0] and np.array_equal(got[1], exp[1]) and
+                                                      prev.tobytes() == eprev.tobytes())}))
+        mi.close()
+
     # batched MapPoint::ComputeDistinctiveDescriptors: 20 000 map points with 3..40 observations
     rng = np.random.default_rng(1)
     counts = rng.integers(3, 41, 20000).astype(np.int32)

@@ -316,19 +316,19 @@ def _init_pair(seed, n=1500, groups=60, width=640, height=480):
     return F1, F2
 
 
-@pytest.mark.parametrize("seed,window,ratio,ori", [(0, 100, 0.9, True), (1, 100, 0.9, False), (2, 30, 0.7, True), (3, 250, 1.0, True)])
-def test_search_for_initialization_vs_oracle(seed, window, ratio, ori):
+@pytest.mark.parametrize("seed,window,ratio,ori,n", [(0, 100, 0.9, True, 1500), (1, 100, 0.9, False, 1500), (2, 30, 0.7, True, 1500),
+                                                     (3, 250, 1.0, True, 1500), (4, 20, 0.9, True, 30000)])
+def test_search_for_initialization_vs_oracle(seed, window, ratio, ori, n):
     """ORBmatcher::SearchForInitialization (Tracking::MonocularInitialization): level-0 queries, the window over F2's
     grid, vMatchedDistance skip, ratio rule, stolen matches, rotation filter over every accept, vbPrevMatched update —
     bit-identical to the sequential loop; a second call with the updated vbPrevMatched (what the tracker does frame after
-    frame) stays identical too."""
+    frame) stays identical too. The 30000-keypoint case takes the kernel variant with the claim state in global memory."""
     import orbslam2_b200 as ob
     from oracle_lib import oracle_search_for_initialization
     m = ob.ORBmatcher(ratio, ori)
-    F1, F2 = _init_pair(seed)
+    F1, F2 = _init_pair(seed, n=n)
     prev = np.ascontiguousarray(np.stack([F1.mvKeysUn["x"], F1.mvKeysUn["y"]], 1), np.float32)
     eprev = prev.copy()
-    stolen_seen = False
     for it in range(2):
         n, m12, P = m.SearchForInitialization(F1, F2, prev, window)
         en, em12 = oracle_search_for_initialization(P, np.float32(ratio), F1, F2, eprev, window)
