@@ -344,6 +344,12 @@ typedef struct {
 int orbm_search_for_triangulation(orbm_t* m, const orbm_bow_side* a, const orbm_bow_side* b, int n_pos_a, int n_pos_b,
                                   const orbm_triangulation* t, int th, int check_orientation, int32_t* match_a,
                                   int* nmatches);
+/* The same for npairs (a[k], b[k], T[k]) pairs in one launch sequence: LocalMapping::CreateNewMapPoints matches the new
+ * keyframe against each of its ~20 covisible neighbours (src/LocalMapping.cc:225-268: a[k] = the new keyframe for every
+ * k, staged once; b[k], T[k] = neighbour k with its F12 and epipole). See orbm_search_by_bow_batch. */
+int orbm_search_for_triangulation_batch(orbm_t* m, int npairs, const orbm_bow_side* a, const orbm_bow_side* b,
+                                        const int* n_pos_a, const int* n_pos_b, const orbm_triangulation* T, int th,
+                                        int check_orientation, int32_t* const* match_a, int* nmatches);
 
 /* ---- vocabulary tree (bag of words): replaces fbow::Vocabulary as the reference uses it -------------------------------
  * (Thirdparty/fbow/src/fbow.h:51-125, fbow.cpp; called from Frame::ComputeFboW src/Frame.cc:395-400 and

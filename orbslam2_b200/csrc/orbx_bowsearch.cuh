@@ -92,10 +92,8 @@ __global__ void __launch_bounds__(128) k_bow_choose(BowDev S, const int* __restr
 // ORBmatcher::SearchForTriangulation's scan (src/ORBmatcher.cc:697-749): best = TH_LOW; a candidate replaces the best
 // when dist <= best (equal distance: the LAST one wins) and it passes the epipole and epipolar-line gates
 // (CheckDistEpipolarLine, :138-155; float arithmetic in the reference's order, no FMA contraction).
-__global__ void __launch_bounds__(128) k_tri_choose(BowDev S, const int* __restrict__ posNodeB, int* __restrict__ choice,
-                                                    const int* __restrict__ owner, int* __restrict__ flag, int round) {
-    if (round > 0 && flag[round - 1] == 0) return;
-    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+__device__ __forceinline__ void d_tri_choose(const BowDev& S, const int* __restrict__ posNodeB, int* __restrict__ choice,
+                                             const int* __restrict__ owner, int* __restrict__ flag, int round, int p) {
     if (p >= S.nPosA) return;
     int nc = -1;
     const int jb = posNodeB[p];
@@ -132,6 +130,11 @@ __global__ void __launch_bounds__(128) k_tri_choose(BowDev S, const int* __restr
         choice[p] = nc;
         flag[round] = 1;
     }
+}
+__global__ void __launch_bounds__(128) k_tri_choose(BowDev S, const int* __restrict__ posNodeB, int* __restrict__ choice,
+                                                    const int* __restrict__ owner, int* __restrict__ flag, int round) {
+    if (round > 0 && flag[round - 1] == 0) return;
+    d_tri_choose(S, posNodeB, choice, owner, flag, round, blockIdx.x * blockDim.x + threadIdx.x);
 }
 
 __device__ __forceinline__ void d_bow_finish(const BowDev& S, const int* __restrict__ choice, int32_t* __restrict__ matchA,
@@ -215,7 +218,8 @@ __global__ void k_bowb_claim(const BowPair* __restrict__ P, const int* __restric
 __global__ void __launch_bounds__(128) k_bowb_choose(const BowPair* __restrict__ P, int* __restrict__ flag, int round) {
     if (round > 0 && flag[round - 1] == 0) return;
     const BowPair& Q = P[blockIdx.y];
-    d_bow_choose(Q.S, Q.posNodeB, Q.choice, Q.owner, flag, round, blockIdx.x * blockDim.x + threadIdx.x);
+    if (Q.S.tri) d_tri_choose(Q.S, Q.posNodeB, Q.choice, Q.owner, flag, round, blockIdx.x * blockDim.x + threadIdx.x);
+    else d_bow_choose(Q.S, Q.posNodeB, Q.choice, Q.owner, flag, round, blockIdx.x * blockDim.x + threadIdx.x);
 }
 __global__ void __launch_bounds__(1024) k_bowb_finish(const BowPair* __restrict__ P) {
     const BowPair& Q = P[blockIdx.y];
@@ -349,9 +353,9 @@ extern "C" int orbm_search_for_triangulation(orbm_t* m, const orbm_bow_side* a, 
 }
 
 
-extern "C" int orbm_search_by_bow_batch(orbm_t* m, int npairs, const orbm_bow_side* a, const orbm_bow_side* b,
-                                        const int* n_pos_a, const int* n_pos_b, float nn_ratio, int th, int strict,
-                                        int check_orientation, int32_t* const* match_a, int* nmatches) {
+static int bow_batch_run(orbm_t* m, int npairs, const orbm_bow_side* a, const orbm_bow_side* b, const int* n_pos_a,
+                         const int* n_pos_b, float nn_ratio, int th, int strict, int check_orientation,
+                         const orbm_triangulation* T /* [npairs] or NULL */, int32_t* const* match_a, int* nmatches) {
     if (!m || npairs < 0 || (npairs && (!a || !b || !n_pos_a || !n_pos_b || !match_a || !nmatches)))
         FAIL(ORBX_EINVAL, "null argument");
     if (npairs == 0) return ORBX_OK;
@@ -367,8 +371,11 @@ extern "C" int orbm_search_by_bow_batch(orbm_t* m, int npairs, const orbm_bow_si
         const orbm_bow_side *A = a + k, *B = b + k;
         if (!bow_side_ok(A) || !bow_side_ok(B) || (A->n && !A->eligible) || n_pos_a[k] < 0 || n_pos_b[k] < 0 || (A->n && !match_a[k]))
             FAIL(ORBX_EINVAL, "bad feature-vector arrays (pair %d)", k);
-        need += (size_t)A->n * (1 + 4 + 32 + 4) + (size_t)B->n * (1 + 4 + 32 + 4) + (size_t)(A->n_nodes + B->n_nodes + 2) * 8 +
-                (size_t)(n_pos_a[k] + n_pos_b[k]) * 4 + (size_t)n_pos_a[k] * 8 + 256 * 20;
+        if (T && (!T[k].pt_a || !T[k].pt_b || !T[k].octave_b || !T[k].stereo_a || !T[k].stereo_b || !B->eligible ||
+                  T[k].nlevels < 1 || T[k].nlevels > ORBX_MAX_LEVELS))
+            FAIL(ORBX_EINVAL, "bad triangulation arguments (pair %d)", k);
+        need += (size_t)A->n * (1 + 4 + 32 + 4 + 8 + 1) + (size_t)B->n * (1 + 4 + 32 + 4 + 8 + 4 + 1) + (size_t)(A->n_nodes + B->n_nodes + 2) * 8 +
+                (size_t)(n_pos_a[k] + n_pos_b[k]) * 4 + (size_t)n_pos_a[k] * 8 + 256 * 28;
         maxPosA = std::max(maxPosA, n_pos_a[k]);
         maxNodesA = std::max(maxNodesA, A->n_nodes);
         sumPosA += n_pos_a[k];
@@ -418,6 +425,18 @@ extern "C" int orbm_search_by_bow_batch(orbm_t* m, int npairs, const orbm_bow_si
         S.featA = (const uint32_t*)in(A->node_feat, (size_t)n_pos_a[k] * 4);
         S.featB = (const uint32_t*)in(B->node_feat, (size_t)n_pos_b[k] * 4);
         S.nnRatio = nn_ratio; S.th = th; S.strict = strict; S.checkOri = check_orientation;
+        S.tri = T != nullptr;
+        if (T) {
+            const orbm_triangulation& G = T[k];
+            S.ptA = (const float2*)in(G.pt_a, (size_t)A->n * 8);
+            S.ptB = (const float2*)in(G.pt_b, (size_t)B->n * 8);
+            S.octB = (const int32_t*)in(G.octave_b, (size_t)B->n * 4);
+            S.stereoA = (const uint8_t*)in(G.stereo_a, A->n);
+            S.stereoB = (const uint8_t*)in(G.stereo_b, B->n);
+            for (int i = 0; i < 9; i++) S.F[i] = G.F12[i];
+            S.ex = G.ex; S.ey = G.ey;
+            for (int i = 0; i < G.nlevels; i++) { S.scale[i] = G.scale_factors[i]; S.sigma2[i] = G.level_sigma2[i]; }
+        }
         if ((((uintptr_t)S.descA) | ((uintptr_t)S.descB)) & 15) FAIL(ORBX_EINVAL, "device descriptor matrices must be 16-byte aligned");
         // a pair with an empty side or no nodes has no candidates: nPosA = 0 leaves match_a all -1
         if (B->n == 0 || A->n_nodes == 0 || B->n_nodes == 0) { S.nPosA = 0; S.nNodesA = 0; }
@@ -480,4 +499,17 @@ extern "C" int orbm_search_by_bow_batch(orbm_t* m, int npairs, const orbm_bow_si
     m->lastRounds = rounds + 1;
     m->lastCandidates = 0;
     return ORBX_OK;
+}
+
+extern "C" int orbm_search_by_bow_batch(orbm_t* m, int npairs, const orbm_bow_side* a, const orbm_bow_side* b,
+                                        const int* n_pos_a, const int* n_pos_b, float nn_ratio, int th, int strict,
+                                        int check_orientation, int32_t* const* match_a, int* nmatches) {
+    return bow_batch_run(m, npairs, a, b, n_pos_a, n_pos_b, nn_ratio, th, strict, check_orientation, nullptr, match_a, nmatches);
+}
+
+extern "C" int orbm_search_for_triangulation_batch(orbm_t* m, int npairs, const orbm_bow_side* a, const orbm_bow_side* b,
+                                                   const int* n_pos_a, const int* n_pos_b, const orbm_triangulation* T,
+                                                   int th, int check_orientation, int32_t* const* match_a, int* nmatches) {
+    if (npairs > 0 && !T) FAIL(ORBX_EINVAL, "null argument");
+    return bow_batch_run(m, npairs, a, b, n_pos_a, n_pos_b, 0.f, th, 0, check_orientation, T, match_a, nmatches);
 }

@@ -364,6 +364,55 @@ class ORBmatcher:
                                                     int(self.mbCheckOrientation), C.cast(ptrs, C.c_void_p), nm.ctypes.data))
         return [(int(nm[k]), out[k]) for k in range(K)]
 
+    @staticmethod
+    def _triangulation(geo, T=None):
+        """orbm_triangulation from a geo dict; returns (struct, arrays to keep alive)."""
+        g = {k: np.ascontiguousarray(geo[k], t) for k, t in (("pt_a", np.float32), ("pt_b", np.float32), ("octave_b", np.int32),
+                                                              ("stereo_a", np.uint8), ("stereo_b", np.uint8))}
+        T = _lib.Triangulation() if T is None else T
+        T.pt_a, T.pt_b, T.octave_b = g["pt_a"].ctypes.data, g["pt_b"].ctypes.data, g["octave_b"].ctypes.data
+        T.stereo_a, T.stereo_b = g["stereo_a"].ctypes.data, g["stereo_b"].ctypes.data
+        F = np.ascontiguousarray(geo["F12"], np.float32).ravel()
+        for i in range(9):
+            T.F12[i] = F[i]
+        T.ex, T.ey = float(np.float32(geo["ex"])), float(np.float32(geo["ey"]))
+        sf, s2 = np.asarray(geo["scale_factors"], np.float32), np.asarray(geo["level_sigma2"], np.float32)
+        T.nlevels = len(sf)
+        for i in range(len(sf)):
+            T.scale_factors[i], T.level_sigma2[i] = sf[i], s2[i]
+        return T, g
+
+    def SearchForTriangulationBatch(self, items, th=None):
+        """SearchForTriangulation for a list of (a, b, geo) in one launch sequence (orbm_search_for_triangulation_batch):
+        the new keyframe against its covisible neighbours in LocalMapping::CreateNewMapPoints. Arrays shared between the
+        items (the new keyframe's side) are staged once. Returns [(nmatches, vMatches12), ...]."""
+        self._set_space(_lib.MEM_HOST, _lib.MEM_HOST)
+        K = len(items)
+        keep = []
+
+        def side(d):
+            e = d["eligible"] if d["eligible"] is not None else d.setdefault("_ones", np.ones(d["n"], np.uint8))
+            keep.append(e)
+            return _lib.BowSide(d["n"], e.ctypes.data, d["angle"].ctypes.data, d["desc"].ctypes.data, len(d["node_id"]),
+                                d["node_id"].ctypes.data, d["node_off"].ctypes.data, d["node_feat"].ctypes.data)
+
+        A = (_lib.BowSide * max(K, 1))(*[side(a) for a, _, _ in items])
+        B = (_lib.BowSide * max(K, 1))(*[side(b) for _, b, _ in items])
+        T = (_lib.Triangulation * max(K, 1))()
+        for k, (_, _, geo) in enumerate(items):
+            keep.append(self._triangulation(geo, T[k])[1])
+        npa = np.array([int(a["node_off"][-1]) for a, _, _ in items], np.int32)
+        npb = np.array([int(b["node_off"][-1]) for _, b, _ in items], np.int32)
+        out = [np.full(a["n"], -1, np.int32) for a, _, _ in items]
+        ptrs = (C.c_void_p * max(K, 1))(*[o.ctypes.data for o in out])
+        nm = np.zeros(max(K, 1), np.int32)
+        _lib.check(self._L.orbm_search_for_triangulation_batch(self._h, K, C.cast(A, C.c_void_p), C.cast(B, C.c_void_p),
+                                                               npa.ctypes.data, npb.ctypes.data, C.cast(T, C.c_void_p),
+                                                               int(self.TH_LOW if th is None else th),
+                                                               int(self.mbCheckOrientation), C.cast(ptrs, C.c_void_p),
+                                                               nm.ctypes.data))
+        return [(int(nm[k]), out[k]) for k in range(K)]
+
     def SearchForTriangulation(self, a, b, geo, th=None):
         """SearchForTriangulation(pKF1, pKF2, F12, vMatchedPairs, bOnlyStereo) (src/ORBmatcher.cc:652-819). a, b: bow_side
         dicts with eligible = "no map point (and stereo when bOnlyStereo)"; geo: dict(pt_a [nA,2], pt_b [nB,2], octave_b,
@@ -377,19 +426,7 @@ class ORBmatcher:
                                 d["node_id"].ctypes.data, d["node_off"].ctypes.data, d["node_feat"].ctypes.data)
 
         A, B = side(a, ea), side(b, eb)
-        g = {k: np.ascontiguousarray(geo[k], t) for k, t in (("pt_a", np.float32), ("pt_b", np.float32), ("octave_b", np.int32),
-                                                              ("stereo_a", np.uint8), ("stereo_b", np.uint8))}
-        T = _lib.Triangulation()
-        T.pt_a, T.pt_b, T.octave_b = g["pt_a"].ctypes.data, g["pt_b"].ctypes.data, g["octave_b"].ctypes.data
-        T.stereo_a, T.stereo_b = g["stereo_a"].ctypes.data, g["stereo_b"].ctypes.data
-        F = np.ascontiguousarray(geo["F12"], np.float32).ravel()
-        for i in range(9):
-            T.F12[i] = F[i]
-        T.ex, T.ey = float(np.float32(geo["ex"])), float(np.float32(geo["ey"]))
-        sf, s2 = np.asarray(geo["scale_factors"], np.float32), np.asarray(geo["level_sigma2"], np.float32)
-        T.nlevels = len(sf)
-        for i in range(len(sf)):
-            T.scale_factors[i], T.level_sigma2[i] = sf[i], s2[i]
+        T, g = self._triangulation(geo)
         match = np.full(a["n"], -1, np.int32)
         n = C.c_int()
         _lib.check(self._L.orbm_search_for_triangulation(self._h, C.byref(A), C.byref(B), int(a["node_off"][-1]),

@@ -313,3 +313,54 @@ def test_search_by_bow_batch_vs_oracle(ob, strict):
         assert m.SearchByFboWBatch([], strict=strict) == []
         m.close()
     voc.close()
+
+
+def test_search_for_triangulation_batch_vs_oracle(ob):
+    """orbm_search_for_triangulation_batch: the new keyframe against K neighbours (LocalMapping::CreateNewMapPoints) in one
+    launch sequence; the keyframe's own arrays are shared by the pairs. Every pair equals the sequential restatement and
+    the single-pair call."""
+    from oracle_lib import oracle_search_for_triangulation
+    blob = synth_vocabulary(k=10, levels=5, seed=33)
+    voc = ob.Vocabulary(); voc.fromStream(blob)
+    na = 1200
+    rng = np.random.default_rng(91)
+    da = _features(blob, na, 170)
+    ang_a = (rng.random(na) * 360).astype(np.float32)
+    fa = voc.transform(da, 4)[1]
+    ea = (rng.random(na) < 0.7).astype(np.uint8)
+    A = ob.ORBmatcher.bow_side(da, ang_a, fa, ea)
+    items, geo0 = [], None
+    for k, nb in enumerate([1300, 900, 2000, 30, 1100]):
+        ns = int(min(na, nb) * 0.7)
+        pick = rng.permutation(na)[:ns]
+        db = np.concatenate([da[pick], _features(blob, nb - ns, 180 + k)])
+        bits = np.unpackbits(db[:ns], axis=1)
+        for _ in range(5):
+            bits[np.arange(ns), rng.integers(0, 256, ns)] ^= 1
+        db[:ns] = np.packbits(bits, axis=1)
+        perm = rng.permutation(nb)
+        db = np.ascontiguousarray(db[perm])
+        src = np.full(nb, -1); src[:ns] = pick; src = src[perm]
+        geo = _two_view_geometry(na, nb, src, 5)
+        if geo0 is None:
+            geo0 = geo
+        geo["pt_a"], geo["stereo_a"] = geo0["pt_a"], geo0["stereo_a"]
+        ang_b = (rng.random(nb) * 360).astype(np.float32)
+        ang_b[src >= 0] = np.mod(ang_a[src[src >= 0]] + np.float32(12.0) + rng.normal(0, 3, (src >= 0).sum()), 360).astype(np.float32)
+        fb = voc.transform(db, 4)[1]
+        eb = (rng.random(nb) < 0.7).astype(np.uint8)
+        items.append((A, ob.ORBmatcher.bow_side(db, ang_b, fb, eb), geo))
+    for ori in (True, False):
+        m = ob.ORBmatcher(0.6, ori)
+        got = m.SearchForTriangulationBatch(items)
+        total = 0
+        for k, (a, b, geo) in enumerate(items):
+            en, ematch = oracle_search_for_triangulation(a, b, geo, 50, ori)
+            assert got[k][0] == en and np.array_equal(got[k][1], ematch), (k, ori)
+            one = m.SearchForTriangulation(a, b, geo)
+            assert one[0] == en and np.array_equal(one[1], ematch)
+            total += en
+        assert total > 600
+        assert m.SearchForTriangulationBatch([]) == []
+        m.close()
+    voc.close()
