@@ -783,7 +783,7 @@ static int sp_run(orbm_handle* m, int mode, const orbm_proj_params* p, float nnR
     S.nCur = nC;
     S.mode = mode;
     S.nnRatio = nnRatio;
-    if (hin && (rc = ensure_host_in(m, need))) return rc;
+    if ((hin || hout) && (rc = ensure_host_in(m, need))) return rc;
     Stager stg{m, &W, hin, (size_t)-1};
     auto in = [&](const void* src, size_t bytes) -> const void* { return stg.in(src, bytes); };
     S.worldPos = (const float*)in(last->world_pos, (size_t)nL * 12);
@@ -809,13 +809,20 @@ static int sp_run(orbm_handle* m, int mode, const orbm_proj_params* p, float nnR
     int* candOff = W.take<int>(nL + 1);
     int* choice = W.take<int>(nL);
     int* owner = W.take<int>(nC);
-    int* dRes = W.take<int>(4);
     const int maxRounds = nL + 8;
-    int* flags = W.take<int>(maxRounds);
+    // everything the host reads back sits in one span: [outputs (host mode)] [dRes] [go flag, round flags]
     int32_t* oCur = hout ? W.take<int32_t>(nC) : cur_match;
     int32_t* oLast = hout ? W.take<int32_t>(nL) : last_match;
     uint8_t* oKeep = ((hout && last_keep) || (mode == 2 && !last_keep)) ? W.take<uint8_t>(nL) : last_keep;
+    int* dRes = W.take<int>(4);
+    int* flagsGo = W.take<int>(maxRounds + 1);
+    int* flags = flagsGo + 1;  // flags[-1] = go
     if (W.off > m->wsCap) FAIL(ORBX_ECUDA, "internal: workspace estimate too small (%zu > %zu)", W.off, m->wsCap);
+    const uint8_t* spanBegin = hout ? (const uint8_t*)oCur : (const uint8_t*)dRes;
+    const int SPEC = 4;  // rounds enqueued before the first look at the flags
+    const size_t spanBytes = (size_t)((const uint8_t*)(flags + SPEC) - spanBegin);
+    const uint8_t* hs = m->hIn;  // pinned mirror of the span (the staged inputs have left it when the copy back starts)
+    auto hostAt = [&](const void* dev) { return hs + ((const uint8_t*)dev - spanBegin); };
 
     // S1 grid
     CK(cudaMemsetAsync(cellCount, 0, SP_CELLS * sizeof(int), st));
@@ -823,54 +830,78 @@ static int sp_run(orbm_handle* m, int mode, const orbm_proj_params* p, float nnR
     k_sp_grid_scan<<<1, 1024, 0, st>>>(cellCount, cellStart, cursor);
     k_sp_grid_fill<<<(nC + 255) / 256, 256, 0, st>>>(S, cursor, items);
     k_sp_grid_sort<<<(SP_CELLS + 255) / 256, 256, 0, st>>>(cellStart, items);
-    // S2 candidates: count, scan, fill
+    // S2 candidates: count, scan, fill — without a host round trip for the total (k_sp_guard)
     const int qBlocks = (nL + 7) / 8;
     k_sp_candidates<false><<<qBlocks, 256, 0, st>>>(S, cellStart, items, candCount, nullptr, nullptr, nullptr);
     k_sp_scan<<<1, 1024, 0, st>>>(candCount, nL, candOff);
     m->launches += 6;
-    CK(cudaGetLastError());
-    CK(cudaMemcpyAsync(m->hRes + 2, candOff + nL, sizeof(int), cudaMemcpyDeviceToHost, st));
-    CK(cudaStreamSynchronize(st));
-    const size_t total = (size_t)m->hRes[2];
-    if ((rc = ensure(m->dCand, m->candCap, (total + 64) * 6))) return rc;
-    int* candIdx = (int*)m->dCand;
-    unsigned short* candDist = (unsigned short*)(m->dCand + ((total + 63) & ~(size_t)63) * 4);
-    k_sp_candidates<true><<<qBlocks, 256, 0, st>>>(S, cellStart, items, nullptr, candOff, candIdx, candDist);
-    // S3 greedy claims as a fixed point: a few rounds are enqueued speculatively (converged rounds return at once),
-    // then the flags are read; more rounds follow only if the last one still changed something
-    CK(cudaMemsetAsync(choice, 0xFF, (size_t)nL * sizeof(int), st));
-    CK(cudaMemsetAsync(flags, 0, (size_t)maxRounds * sizeof(int), st));
+    if ((rc = ensure(m->dCand, m->candCap, (std::max<size_t>((size_t)nL * 64, 1 << 16) + 64) * 6))) return rc;
+    size_t total = 0;
     int round = 0, rounds = 0;
-    for (;;) {
-        const int R = 4;
-        if (round + R > maxRounds) FAIL(ORBX_ECUDA, "internal: greedy resolution did not converge in %d rounds", maxRounds);
+    int* candIdx = nullptr;
+    unsigned short* candDist = nullptr;
+    auto enqueueRounds = [&](int R) {
         for (int r = 0; r < R; r++, round++) {
-            CK(cudaMemsetAsync(owner, 0x7F, (size_t)nC * sizeof(int), st));
+            cudaMemsetAsync(owner, 0x7F, (size_t)nC * sizeof(int), st);
             k_sp_claim<<<(nL + 255) / 256, 256, 0, st>>>(S, choice, owner, flags, round);
             if (mode != 1) k_sp_choose<<<qBlocks, 256, 0, st>>>(S, candOff, candIdx, candDist, choice, owner, flags, round);
             else k_sp_choose_mp<<<(nL + 255) / 256, 256, 0, st>>>(S, candOff, candIdx, candDist, choice, owner, flags, round);
             m->launches += 2;
         }
+    };
+    auto finishAndFetch = [&]() -> int {
+        if (mode != 1) k_sp_finish<<<1, 1024, 0, st>>>(S, choice, oCur, oLast, oKeep, dRes);
+        else k_sp_finish_mp<<<1, 1024, 0, st>>>(S, choice, oCur, oLast, dRes);
+        m->launches++;
         CK(cudaGetLastError());
-        CK(cudaMemcpyAsync(m->hFlags, flags, (size_t)round * sizeof(int), cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(m->hIn, spanBegin, spanBytes, cudaMemcpyDeviceToHost, st));
         CK(cudaStreamSynchronize(st));
-        rounds = 0;
-        while (rounds < round && m->hFlags[rounds]) rounds++;
-        if (rounds < round) break;  // round `rounds` changed nothing: fixed point reached
+        return ORBX_OK;
+    };
+    for (int attempt = 0;; attempt++) {
+        const size_t capEntries = ((m->candCap / 6) & ~(size_t)63) - 64;
+        candIdx = (int*)m->dCand;
+        candDist = (unsigned short*)(m->dCand + capEntries * 4);
+        // S3 greedy claims as a fixed point: SPEC rounds and the finishing kernel are enqueued speculatively (converged
+        // rounds return at once) and ONE copy brings back results, flags and the candidate total; more rounds follow
+        // only if the last speculative one still changed something
+        CK(cudaMemsetAsync(choice, 0xFF, (size_t)nL * sizeof(int), st));
+        CK(cudaMemsetAsync(flagsGo, 0, (size_t)(maxRounds + 1) * sizeof(int), st));
+        k_sp_guard<<<1, 1, 0, st>>>(candOff, nL, (int)std::min<size_t>(capEntries, 0x7FFFFFFF), flagsGo, dRes);
+        k_sp_candidates<true><<<qBlocks, 256, 0, st>>>(S, cellStart, items, nullptr, candOff, candIdx, candDist, flagsGo);
+        m->launches += 2;
+        round = 0;
+        enqueueRounds(SPEC);
+        if ((rc = finishAndFetch())) return rc;
+        total = (size_t)((const int*)hostAt(dRes))[2];
+        if (((const int*)hostAt(flagsGo))[0]) break;
+        if (attempt) FAIL(ORBX_ECUDA, "internal: candidate buffer still too small (%zu entries)", total);
+        if ((rc = ensure(m->dCand, m->candCap, (total + total / 2 + 128) * 6))) return rc;
+    }
+    const int* hf = (const int*)hostAt(flags);
+    rounds = 0;
+    while (rounds < SPEC && hf[rounds]) rounds++;
+    if (rounds == SPEC) {  // not converged yet: further rounds with the flags read in between, then finish again
+        for (;;) {
+            const int R = 4;
+            if (round + R > maxRounds) FAIL(ORBX_ECUDA, "internal: greedy resolution did not converge in %d rounds", maxRounds);
+            enqueueRounds(R);
+            CK(cudaGetLastError());
+            CK(cudaMemcpyAsync(m->hFlags, flags, (size_t)round * sizeof(int), cudaMemcpyDeviceToHost, st));
+            CK(cudaStreamSynchronize(st));
+            rounds = 0;
+            while (rounds < round && m->hFlags[rounds]) rounds++;
+            if (rounds < round) break;  // round `rounds` changed nothing: fixed point reached
+        }
+        if ((rc = finishAndFetch())) return rc;
     }
     rounds++;  // the confirming round
-    if (mode != 1) k_sp_finish<<<1, 1024, 0, st>>>(S, choice, oCur, oLast, oKeep, dRes);
-    else k_sp_finish_mp<<<1, 1024, 0, st>>>(S, choice, oCur, oLast, dRes);
-    m->launches += 2;
-    CK(cudaGetLastError());
-    CK(cudaMemcpyAsync(m->hRes, dRes, sizeof(int), cudaMemcpyDeviceToHost, st));
     if (hout) {
-        CK(cudaMemcpyAsync(cur_match, oCur, (size_t)nC * 4, cudaMemcpyDeviceToHost, st));
-        CK(cudaMemcpyAsync(last_match, oLast, (size_t)nL * 4, cudaMemcpyDeviceToHost, st));
-        if (last_keep) CK(cudaMemcpyAsync(last_keep, oKeep, nL, cudaMemcpyDeviceToHost, st));
+        memcpy(cur_match, hostAt(oCur), (size_t)nC * 4);
+        memcpy(last_match, hostAt(oLast), (size_t)nL * 4);
+        if (last_keep) memcpy(last_keep, hostAt(oKeep), nL);
     }
-    CK(cudaStreamSynchronize(st));
-    *nmatches = m->hRes[0];
+    *nmatches = ((const int*)hostAt(dRes))[0];
     m->lastRounds = rounds;
     m->lastCandidates = (int64_t)total;
     return ORBX_OK;

@@ -194,7 +194,8 @@ template <bool FILL>
 __global__ void __launch_bounds__(256) k_sp_candidates(SpDev S, const int* __restrict__ cellStart,
                                                        const int* __restrict__ items, int* __restrict__ candCount,
                                                        const int* __restrict__ candOff, int* __restrict__ candIdx,
-                                                       unsigned short* __restrict__ candDist) {
+                                                       unsigned short* __restrict__ candDist, const int* __restrict__ go = nullptr) {
+    if (FILL && go && *go == 0) return;  // the lists would not fit: the host grows the buffer and runs the call again
     const int lane = threadIdx.x & 31;
     const int i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (i >= S.nLast) return;
@@ -278,13 +279,22 @@ __global__ void k_sp_scan(const int* __restrict__ cnt, int n, int* __restrict__ 
     if (tid == 0) off[n] = carry;
 }
 
+// The candidate total is only known on the device. Instead of a host round trip to size the buffer, the call runs
+// against the buffer it has: go = (total fits); everything downstream returns at once when go == 0 and the host, which
+// reads go and the total together with the results, grows the buffer and repeats the call (first call of a handle only).
+__global__ void k_sp_guard(const int* __restrict__ candOff, int n, int capEntries, int* __restrict__ go, int* __restrict__ res) {
+    const int total = candOff[n];
+    *go = total <= capEntries;
+    res[2] = total;
+}
+
 // One round of the fixed point is two grid-wide kernels (the candidate lists of a dense frame are ~100 entries per
 // query, too much for one CTA): k_sp_claim rebuilds owner[] from the previous round's choices, k_sp_choose re-picks.
 // flag[r] = "round r changed something"; the kernels of round r + 1 return at once when flag[r] == 0 (converged), so
 // the host can enqueue a few rounds speculatively and look at the flags once.
 __global__ void k_sp_claim(SpDev S, const int* __restrict__ choice, int* __restrict__ owner, const int* __restrict__ flag,
                            int round) {
-    if (round > 0 && flag[round - 1] == 0) return;
+    if (flag[round - 1] == 0) return;  // flag[-1]: the call's go flag (0 = candidate buffer too small, see k_sp_guard)
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= S.nLast) return;
     // owner[i2] = lowest-index query that claimed i2 in the previous round with a point that blocks later queries
@@ -297,7 +307,7 @@ __global__ void k_sp_claim(SpDev S, const int* __restrict__ choice, int* __restr
 __global__ void __launch_bounds__(256) k_sp_choose(SpDev S, const int* __restrict__ candOff, const int* __restrict__ candIdx,
                                                    const unsigned short* __restrict__ candDist, int* __restrict__ choice,
                                                    const int* __restrict__ owner, int* __restrict__ flag, int round) {
-    if (round > 0 && flag[round - 1] == 0) return;
+    if (flag[round - 1] == 0) return;  // flag[-1]: the call's go flag (0 = candidate buffer too small, see k_sp_guard)
     const int lane = threadIdx.x & 31;
     const int i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (i >= S.nLast) return;
@@ -395,7 +405,7 @@ __global__ void __launch_bounds__(256) k_sp_choose_mp(SpDev S, const int* __rest
                                                       const int* __restrict__ candIdx,
                                                       const unsigned short* __restrict__ candDist, int* __restrict__ choice,
                                                       const int* __restrict__ owner, int* __restrict__ flag, int round) {
-    if (round > 0 && flag[round - 1] == 0) return;
+    if (flag[round - 1] == 0) return;  // flag[-1]: the call's go flag (0 = candidate buffer too small, see k_sp_guard)
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= S.nLast) return;
     int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1;
