@@ -265,7 +265,7 @@ static int bow_run(orbm_t* m, const orbm_bow_side* a, const orbm_bow_side* b, in
         m->hFlagsCap = (size_t)maxRounds;
     }
     WsCursor W{m->dWs, 0};
-    if (hin && (rc = ensure_host_in(m, need))) return rc;
+    if ((rc = ensure_host_in(m, need))) return rc;
     Stager stg{m, &W, hin, (size_t)-1};
     auto in = [&](const void* src, size_t bytes) -> const void* { return stg.in(src, bytes); };
     BowDev S;
@@ -300,40 +300,60 @@ static int bow_run(orbm_t* m, const orbm_bow_side* a, const orbm_bow_side* b, in
     int* posNodeB = W.take<int>(n_pos_a);
     int* choice = W.take<int>(n_pos_a);
     int* owner = W.take<int>(nB);
-    int* flags = W.take<int>(maxRounds);
+    // what the host reads back is one span: [dRes] [matches (host mode)] [round flags]
     int* dRes = W.take<int>(4);
     int32_t* oMatch = hout ? W.take<int32_t>(nA) : match_a;
+    int* flags = W.take<int>(maxRounds);
     if (W.off > m->wsCap) FAIL(ORBX_ECUDA, "internal: workspace estimate too small (%zu > %zu)", W.off, m->wsCap);
+    const int SPEC = 4;
+    const uint8_t* spanBegin = (const uint8_t*)dRes;
+    const size_t spanBytes = (size_t)((const uint8_t*)(flags + SPEC) - spanBegin);
+    auto hostAt = [&](const void* dev) { return m->hIn + ((const uint8_t*)dev - spanBegin); };
 
     k_bow_pair_nodes<<<(a->n_nodes + 127) / 128, 128, 0, st>>>(S, posNodeB);
     m->launches++;
     CK(cudaMemsetAsync(choice, 0xFF, (size_t)n_pos_a * sizeof(int), st));
     CK(cudaMemsetAsync(flags, 0, (size_t)maxRounds * sizeof(int), st));
     int round = 0, rounds = 0;
-    for (;;) {
-        const int R = 4;
-        if (round + R > maxRounds) FAIL(ORBX_ECUDA, "internal: greedy resolution did not converge in %d rounds", maxRounds);
+    auto enqueueRounds = [&](int R) {
         for (int r = 0; r < R; r++, round++) {
-            CK(cudaMemsetAsync(owner, 0x7F, (size_t)nB * sizeof(int), st));
+            cudaMemsetAsync(owner, 0x7F, (size_t)nB * sizeof(int), st);
             k_bow_claim<<<(n_pos_a + 255) / 256, 256, 0, st>>>(S, choice, owner, flags, round);
             if (T) k_tri_choose<<<(n_pos_a + 127) / 128, 128, 0, st>>>(S, posNodeB, choice, owner, flags, round);
             else k_bow_choose<<<(n_pos_a + 127) / 128, 128, 0, st>>>(S, posNodeB, choice, owner, flags, round);
             m->launches += 2;
         }
+    };
+    auto finishAndFetch = [&]() -> int {
+        k_bow_finish<<<1, 1024, 0, st>>>(S, choice, oMatch, dRes);
+        m->launches++;
         CK(cudaGetLastError());
-        CK(cudaMemcpyAsync(m->hFlags, flags, (size_t)round * sizeof(int), cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(m->hIn, spanBegin, spanBytes, cudaMemcpyDeviceToHost, st));
         CK(cudaStreamSynchronize(st));
-        rounds = 0;
-        while (rounds < round && m->hFlags[rounds]) rounds++;
-        if (rounds < round) break;
+        return ORBX_OK;
+    };
+    // SPEC rounds and the finishing kernel go out together; one copy returns matches, count and flags
+    if (SPEC > maxRounds) FAIL(ORBX_ECUDA, "internal: round budget");
+    enqueueRounds(SPEC);
+    if ((rc = finishAndFetch())) return rc;
+    const int* hf = (const int*)hostAt(flags);
+    while (rounds < SPEC && hf[rounds]) rounds++;
+    if (rounds == SPEC) {
+        for (;;) {
+            const int R = 4;
+            if (round + R > maxRounds) FAIL(ORBX_ECUDA, "internal: greedy resolution did not converge in %d rounds", maxRounds);
+            enqueueRounds(R);
+            CK(cudaGetLastError());
+            CK(cudaMemcpyAsync(m->hFlags, flags, (size_t)round * sizeof(int), cudaMemcpyDeviceToHost, st));
+            CK(cudaStreamSynchronize(st));
+            rounds = 0;
+            while (rounds < round && m->hFlags[rounds]) rounds++;
+            if (rounds < round) break;
+        }
+        if ((rc = finishAndFetch())) return rc;
     }
-    k_bow_finish<<<1, 1024, 0, st>>>(S, choice, oMatch, dRes);
-    m->launches++;
-    CK(cudaGetLastError());
-    CK(cudaMemcpyAsync(m->hRes, dRes, sizeof(int), cudaMemcpyDeviceToHost, st));
-    if (hout) CK(cudaMemcpyAsync(match_a, oMatch, (size_t)nA * 4, cudaMemcpyDeviceToHost, st));
-    CK(cudaStreamSynchronize(st));
-    *nmatches = m->hRes[0];
+    if (hout) memcpy(match_a, hostAt(oMatch), (size_t)nA * 4);
+    *nmatches = ((const int*)hostAt(dRes))[0];
     m->lastRounds = rounds + 1;
     m->lastCandidates = 0;
     return ORBX_OK;
