@@ -387,6 +387,7 @@ static int bow_batch_run(orbm_t* m, int npairs, const orbm_bow_side* a, const or
     std::vector<std::pair<const void*, const void*> > seen;  // (source, device copy)
     size_t need = (size_t)npairs * (sizeof(BowPair) + 256) + 256 * 8;
     int maxPosA = 0, maxNodesA = 0, sumPosA = 0;
+    size_t sumA = 0;
     for (int k = 0; k < npairs; k++) {
         const orbm_bow_side *A = a + k, *B = b + k;
         if (!bow_side_ok(A) || !bow_side_ok(B) || (A->n && !A->eligible) || n_pos_a[k] < 0 || n_pos_b[k] < 0 || (A->n && !match_a[k]))
@@ -399,6 +400,7 @@ static int bow_batch_run(orbm_t* m, int npairs, const orbm_bow_side* a, const or
         maxPosA = std::max(maxPosA, n_pos_a[k]);
         maxNodesA = std::max(maxNodesA, A->n_nodes);
         sumPosA += n_pos_a[k];
+        sumA += (size_t)A->n;
         nmatches[k] = 0;
     }
     const int maxRounds = maxPosA + 8;
@@ -411,11 +413,17 @@ static int bow_batch_run(orbm_t* m, int npairs, const orbm_bow_side* a, const or
         CK(cudaMallocHost(&m->hFlags, (size_t)std::max(maxRounds, npairs) * sizeof(int)));
         m->hFlagsCap = (size_t)std::max(maxRounds, npairs);
     }
-    if ((hin || hout) && (rc = ensure_host_in(m, need))) return rc;
+    if ((rc = ensure_host_in(m, need))) return rc;
     WsCursor W{m->dWs, 0};
     BowPair* dPairs = W.take<BowPair>(npairs);
-    int* flags = W.take<int>(maxRounds);
+    // what the host reads back is one span: [per-pair counts] [matches of all pairs (host mode)] [round flags]
     int* dRes = W.take<int>(npairs);
+    int32_t* matchAll = hout ? W.take<int32_t>(std::max<size_t>(sumA, 1)) : nullptr;
+    int* flags = W.take<int>(maxRounds);
+    const int SPEC = 4;
+    const uint8_t* spanBegin = (const uint8_t*)dRes;
+    const size_t spanBytes = (size_t)((const uint8_t*)(flags + SPEC) - spanBegin);
+    auto hostAt = [&](const void* dev) { return m->hIn + ((const uint8_t*)dev - spanBegin); };
     Stager stg{m, &W, hin, (size_t)-1};
     auto in = [&](const void* src, size_t bytes) -> const void* {
         if (!src || !hin) return src;
@@ -467,9 +475,6 @@ static int bow_batch_run(orbm_t* m, int npairs, const orbm_bow_side* a, const or
     size_t sumB = 0;
     for (int k = 0; k < npairs; k++) sumB += (size_t)b[k].n;
     int* ownerAll = W.take<int>(std::max<size_t>(sumB, 1));
-    size_t sumA = 0;
-    for (int k = 0; k < npairs; k++) sumA += (size_t)a[k].n;
-    int32_t* matchAll = hout ? W.take<int32_t>(std::max<size_t>(sumA, 1)) : nullptr;  // leaves in one copy
     size_t cOff = 0, oOff = 0, mOff = 0;
     for (int k = 0; k < npairs; k++) {
         hp[k].choice = choiceAll + cOff;
@@ -488,32 +493,46 @@ static int bow_batch_run(orbm_t* m, int npairs, const orbm_bow_side* a, const or
     CK(cudaMemsetAsync(choiceAll, 0xFF, (size_t)std::max(sumPosA, 1) * sizeof(int), st));
     CK(cudaMemsetAsync(flags, 0, (size_t)maxRounds * sizeof(int), st));
     int round = 0, rounds = 0;
-    while (maxPosA > 0) {
-        const int R = 4;
-        if (round + R > maxRounds) FAIL(ORBX_ECUDA, "internal: greedy resolution did not converge in %d rounds", maxRounds);
+    auto enqueueRounds = [&](int R) {
         for (int r = 0; r < R; r++, round++) {
-            CK(cudaMemsetAsync(ownerAll, 0x7F, std::max<size_t>(sumB, 1) * sizeof(int), st));
+            cudaMemsetAsync(ownerAll, 0x7F, std::max<size_t>(sumB, 1) * sizeof(int), st);
             k_bowb_claim<<<dim3((maxPosA + 255) / 256, npairs), 256, 0, st>>>(dPairs, flags, round);
             k_bowb_choose<<<dim3((maxPosA + 127) / 128, npairs), 128, 0, st>>>(dPairs, flags, round);
             m->launches += 2;
         }
+    };
+    auto finishAndFetch = [&]() -> int {
+        k_bowb_finish<<<dim3(1, npairs), 1024, 0, st>>>(dPairs);
+        m->launches++;
         CK(cudaGetLastError());
-        CK(cudaMemcpyAsync(m->hFlags, flags, (size_t)round * sizeof(int), cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(m->hIn, spanBegin, spanBytes, cudaMemcpyDeviceToHost, st));
         CK(cudaStreamSynchronize(st));
-        rounds = 0;
-        while (rounds < round && m->hFlags[rounds]) rounds++;
-        if (rounds < round) break;
+        return ORBX_OK;
+    };
+    if (maxPosA > 0) enqueueRounds(SPEC);  // SPEC rounds and the finishing kernel go out together
+    if ((rc = finishAndFetch())) return rc;
+    const int* hf = (const int*)hostAt(flags);
+    while (rounds < SPEC && hf[rounds]) rounds++;
+    if (maxPosA > 0 && rounds == SPEC) {
+        for (;;) {
+            const int R = 4;
+            if (round + R > maxRounds) FAIL(ORBX_ECUDA, "internal: greedy resolution did not converge in %d rounds", maxRounds);
+            enqueueRounds(R);
+            CK(cudaGetLastError());
+            CK(cudaMemcpyAsync(m->hFlags, flags, (size_t)round * sizeof(int), cudaMemcpyDeviceToHost, st));
+            CK(cudaStreamSynchronize(st));
+            rounds = 0;
+            while (rounds < round && m->hFlags[rounds]) rounds++;
+            if (rounds < round) break;
+        }
+        if ((rc = finishAndFetch())) return rc;
     }
-    k_bowb_finish<<<dim3(1, npairs), 1024, 0, st>>>(dPairs);
-    m->launches++;
-    CK(cudaGetLastError());
-    CK(cudaMemcpyAsync(m->hFlags, dRes, (size_t)npairs * sizeof(int), cudaMemcpyDeviceToHost, st));
-    if (hout && sumA) CK(cudaMemcpyAsync(m->hIn, matchAll, sumA * 4, cudaMemcpyDeviceToHost, st));
-    CK(cudaStreamSynchronize(st));
+    const int* hres = (const int*)hostAt(dRes);
+    const uint8_t* hmatch = hout ? hostAt(matchAll) : nullptr;
     mOff = 0;
     for (int k = 0; k < npairs; k++) {
-        nmatches[k] = m->hFlags[k];
-        if (hout && a[k].n) memcpy(match_a[k], m->hIn + mOff * 4, (size_t)a[k].n * 4);
+        nmatches[k] = hres[k];
+        if (hout && a[k].n) memcpy(match_a[k], hmatch + mOff * 4, (size_t)a[k].n * 4);
         mOff += (size_t)a[k].n;
     }
     m->lastRounds = rounds + 1;
