@@ -512,6 +512,57 @@ public:
         return nmatches;
     }
 
+    // Batched form of SearchByFboW(KeyFrame*, Frame&, ...) for the candidate loop of Tracking::Relocalization
+    // (src/Tracking.cc:1465-1490): every candidate keyframe against the SAME frame in one launch sequence
+    // (orbm_search_by_bow_batch; the frame's arrays are staged once). vvpMapPointMatches[k] and the returned
+    // nmatches[k] are what the k-th call of the single form would give; NULL / bad keyframes are the caller's to skip.
+    // Not part of the reference interface: it replaces the loop around the call, not the call.
+    template <class KeyFrameT, class FrameT, class MapPointT>
+    std::vector<int> SearchByFboW(const std::vector<KeyFrameT*>& vpKFs, FrameT& F,
+                                  std::vector<std::vector<MapPointT*> >& vvpMapPointMatches) {
+        const int K = (int)vpKFs.size(), nB = F.N;
+        vvpMapPointMatches.assign(K, std::vector<MapPointT*>(nB, static_cast<MapPointT*>(NULL)));
+        std::vector<int> nm(K, 0);
+        if (K == 0) return nm;
+        std::vector<float> angB(nB);
+        for (int i = 0; i < nB; i++) angB[i] = F.mvKeys[i].angle;
+        BowCsr b(F.mFbowFeatVec);
+        std::vector<std::vector<MapPointT*> > mps(K);
+        std::vector<std::vector<uint8_t> > elig(K);
+        std::vector<std::vector<float> > angA(K);
+        std::vector<BowCsr> csr;
+        csr.reserve(K);
+        std::vector<orbm_bow_side> A(K), B(K);
+        std::vector<int> npa(K), npb(K);
+        std::vector<std::vector<int32_t> > match(K);
+        std::vector<int32_t*> ptrs(K);
+        for (int k = 0; k < K; k++) {
+            KeyFrameT* pKF = vpKFs[k];
+            mps[k] = pKF->GetMapPointMatches();
+            const int nA = (int)mps[k].size();
+            elig[k].assign(nA, 0);
+            angA[k].resize(nA);
+            for (int i = 0; i < nA; i++) {
+                elig[k][i] = mps[k][i] && !mps[k][i]->isBad();
+                angA[k][i] = pKF->mvKeysUn[i].angle;
+            }
+            csr.push_back(BowCsr(pKF->mFbowFeatVec));
+            const BowCsr& a = csr.back();
+            orbm_bow_side sa = {nA, elig[k].data(), angA[k].data(), pKF->mDescriptors.ptr(), (int)a.id.size(), a.id.data(), a.off.data(), a.feat.data()};
+            orbm_bow_side sb = {nB, nullptr, angB.data(), F.mDescriptors.ptr(), (int)b.id.size(), b.id.data(), b.off.data(), b.feat.data()};
+            A[k] = sa; B[k] = sb;
+            npa[k] = a.off.back(); npb[k] = b.off.back();
+            match[k].assign(nA, -1);
+            ptrs[k] = match[k].data();
+        }
+        check(orbm_search_by_bow_batch(tls(), K, A.data(), B.data(), npa.data(), npb.data(), mfNNratio, TH_LOW, 0,
+                                       mbCheckOrientation ? 1 : 0, ptrs.data(), nm.data()), "orbm_search_by_bow_batch");
+        for (int k = 0; k < K; k++)
+            for (size_t i = 0; i < match[k].size(); i++)
+                if (match[k][i] >= 0) vvpMapPointMatches[k][match[k][i]] = mps[k][i];
+        return nm;
+    }
+
     // ORBmatcher::SearchByFboW(KeyFrame* pKF1, KeyFrame* pKF2, std::vector<MapPoint*>& vpMatches12)
     // (src/ORBmatcher.cc:517-650; LoopClosing::ComputeSim3 src/LoopClosing.cc:301) on the device.
     template <class KeyFrameT, class MapPointT>

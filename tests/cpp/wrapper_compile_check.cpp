@@ -204,4 +204,8 @@ int instantiate11(ORB_SLAM2::ORBmatcher& m, Sim3KeyFrame* a, Sim3KeyFrame* b, st
     const float s12 = 1.0f;
     return m.SearchBySim3(a, b, m12, s12, R12, t12, 7.5f);
 }
+std::vector<int> instantiate12(ORB_SLAM2::ORBmatcher& m, const std::vector<KeyFrame*>& kfs, BowFrame& F,
+                               std::vector<std::vector<MapPoint*> >& out) {
+    return m.SearchByFboW(kfs, F, out);
+}
 }  // namespace dropin_check
