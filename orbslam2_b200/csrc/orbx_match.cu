@@ -783,7 +783,7 @@ static int sp_run(orbm_handle* m, int mode, const orbm_proj_params* p, float nnR
     S.nCur = nC;
     S.mode = mode;
     S.nnRatio = nnRatio;
-    if ((hin || hout) && (rc = ensure_host_in(m, need))) return rc;
+    if ((rc = ensure_host_in(m, need))) return rc;  // staging of host inputs and the pinned mirror of the read-back span
     Stager stg{m, &W, hin, (size_t)-1};
     auto in = [&](const void* src, size_t bytes) -> const void* { return stg.in(src, bytes); };
     S.worldPos = (const float*)in(last->world_pos, (size_t)nL * 12);

@@ -130,7 +130,7 @@ class ORBmatcher:
         P.th, P.th_high, P.check_orientation = float(th), self.TH_HIGH, int(bool(self.mbCheckOrientation))
         return P
 
-    def SearchByProjection(self, CurrentFrame, LastFrame, th, bMono, taken=None):
+    def SearchByProjection(self, CurrentFrame, LastFrame, th, bMono, taken=None, device=False):
         """ORBmatcher::SearchByProjection(Frame &CurrentFrame, const Frame &LastFrame, th, bMono)
         (src/ORBmatcher.cc:1324-1466) entirely on the device: grid build, window candidates, Hamming scan, greedy claims
         in query order, rotation filter. Returns (nmatches, cur_match, last_match, last_keep); cur_match[i2] is the
@@ -146,8 +146,25 @@ class ORBmatcher:
                                 keep["ang"].ctypes.data, keep["ld"].ctypes.data)
         CA = _lib.CurFrameArgs(cur.N, cur.mvKeysUn.ctypes.data, None if cur.mvuRight is None else cur.mvuRight.ctypes.data,
                                cur.mDescriptors.ctypes.data, None if keep["tk"] is None else keep["tk"].ctypes.data)
-        cm = np.zeros(cur.N, np.int32); lm = np.zeros(last.N, np.int32); lk = np.zeros(last.N, np.uint8)
         n = C.c_int()
+        if device:  # the same call with every array resident on the GPU (ORBX_MEM_DEVICE in and out)
+            import torch
+            up = lambda a: None if a is None else torch.from_numpy(np.ascontiguousarray(a).view(np.uint8).reshape(-1).copy()).cuda()
+            ptr = lambda t: None if t is None else t.data_ptr()
+            d = {k: up(v) for k, v in keep.items()}
+            dk, dur, dd = up(cur.mvKeysUn), up(cur.mvuRight), up(cur.mDescriptors)
+            LA = _lib.LastFrameArgs(last.N, ptr(d["wp"]), ptr(d["flags"]), ptr(d["oct"]), ptr(d["ang"]), ptr(d["ld"]))
+            CA = _lib.CurFrameArgs(cur.N, ptr(dk), ptr(dur), ptr(dd), ptr(d["tk"]))
+            tcm = torch.zeros(max(cur.N, 1), dtype=torch.int32, device="cuda")
+            tlm = torch.zeros(max(last.N, 1), dtype=torch.int32, device="cuda")
+            tlk = torch.zeros(max(last.N, 1), dtype=torch.uint8, device="cuda")
+            torch.cuda.synchronize()
+            self._set_space(_lib.MEM_DEVICE, _lib.MEM_DEVICE)
+            _lib.check(self._L.orbm_search_by_projection(self._h, C.byref(P), C.byref(LA), C.byref(CA), tcm.data_ptr(),
+                                                         tlm.data_ptr(), tlk.data_ptr(), C.byref(n)))
+            self._set_space(_lib.MEM_HOST, _lib.MEM_HOST)
+            return n.value, tcm[:cur.N].cpu().numpy(), tlm[:last.N].cpu().numpy(), tlk[:last.N].cpu().numpy()
+        cm = np.zeros(cur.N, np.int32); lm = np.zeros(last.N, np.int32); lk = np.zeros(last.N, np.uint8)
         self._set_space(_lib.MEM_HOST, _lib.MEM_HOST)
         _lib.check(self._L.orbm_search_by_projection(self._h, C.byref(P), C.byref(LA), C.byref(CA), cm.ctypes.data,
                                                      lm.ctypes.data, lk.ctypes.data, C.byref(n)))

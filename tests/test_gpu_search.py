@@ -363,3 +363,23 @@ def test_search_for_initialization_edges():
     en, em12 = oracle_search_for_initialization(P, np.float32(0.9), F1, F2, efar, 100)
     assert n == en == 0 and np.array_equal(m12, em12) and np.array_equal(far, efar)
     m.close()
+
+
+def test_search_by_projection_device_buffers():
+    """The same entry point with ORBX_MEM_DEVICE in and out (a pipeline that keeps keypoints and descriptors on the GPU):
+    identical to the host-buffer call and to the oracle; the first call of a fresh handle also exercises the
+    candidate-buffer growth (k_sp_guard) on a dense pair."""
+    import orbslam2_b200 as ob
+    P = OraclePrims()
+    for n, th in ((1200, 15.0), (6000, 30.0)):
+        m = ob.ORBmatcher(0.9, True)   # fresh handle: default candidate capacity
+        last, cur = synth_tracking_pair(n, 21, conflicts=n // 8)
+        prm = m._proj_params(cur, last, th, False)
+        got_d = m.SearchByProjection(cur, last, th, False, device=True)
+        got_h = m.SearchByProjection(cur, last, th, False)
+        exp = P.search_by_projection(prm, cur, last)
+        for got in (got_d, got_h):
+            assert got[0] == exp[0]
+            for g, e, name in zip(got[1:], exp[1:], ("cur_match", "last_match", "last_keep")):
+                assert np.array_equal(g, e), name
+        m.close()
