@@ -328,7 +328,7 @@ class ORBmatcher:
                     eligible=None if eligible is None else np.ascontiguousarray(eligible, np.uint8),
                     node_id=np.array(keys, np.uint32), node_off=off, node_feat=np.ascontiguousarray(feat, np.uint32))
 
-    def SearchByFboW(self, a, b, strict=False, th=None):
+    def SearchByFboW(self, a, b, strict=False, th=None, device=False):
         """a: KeyFrame (queries; eligible = map point present and not bad), b: Frame (strict False) or second KeyFrame
         (strict True, eligible = map point present and not bad). Returns (nmatches, match_a [a.n] int32: index in b or -1)."""
         self._set_space(_lib.MEM_HOST, _lib.MEM_HOST)
@@ -343,9 +343,31 @@ class ORBmatcher:
                                 d["desc"].ctypes.data, len(d["node_id"]), d["node_id"].ctypes.data,
                                 d["node_off"].ctypes.data, d["node_feat"].ctypes.data)
 
+        n = C.c_int()
+        if device:  # every array resident on the GPU (ORBX_MEM_DEVICE in and out)
+            import torch
+            up = lambda x: None if x is None else torch.from_numpy(np.ascontiguousarray(x).view(np.uint8).reshape(-1).copy()).cuda()
+            ptr = lambda t: None if t is None else t.data_ptr()
+
+            def dside(d, need_elig):
+                elig = d["eligible"]
+                if elig is None and need_elig:
+                    elig = np.ones(d["n"], np.uint8)
+                t = [up(elig), up(d["angle"]), up(d["desc"]), up(d["node_id"]), up(d["node_off"]), up(d["node_feat"])]
+                keep.append(t)
+                return _lib.BowSide(d["n"], ptr(t[0]), ptr(t[1]), ptr(t[2]), len(d["node_id"]), ptr(t[3]), ptr(t[4]), ptr(t[5]))
+
+            A, B = dside(a, True), dside(b, False)
+            tm = torch.full((max(a["n"], 1),), -1, dtype=torch.int32, device="cuda")
+            torch.cuda.synchronize()
+            self._set_space(_lib.MEM_DEVICE, _lib.MEM_DEVICE)
+            _lib.check(self._L.orbm_search_by_bow(self._h, C.byref(A), C.byref(B), int(a["node_off"][-1]), int(b["node_off"][-1]),
+                                                  float(self.mfNNratio), int(self.TH_LOW if th is None else th), int(strict),
+                                                  int(self.mbCheckOrientation), tm.data_ptr(), C.byref(n)))
+            self._set_space(_lib.MEM_HOST, _lib.MEM_HOST)
+            return n.value, tm[:a["n"]].cpu().numpy()
         A, B = side(a, True), side(b, False)
         match = np.full(a["n"], -1, np.int32)
-        n = C.c_int()
         _lib.check(self._L.orbm_search_by_bow(self._h, C.byref(A), C.byref(B), int(a["node_off"][-1]), int(b["node_off"][-1]),
                                               float(self.mfNNratio), int(self.TH_LOW if th is None else th), int(strict),
                                               int(self.mbCheckOrientation), match.ctypes.data, C.byref(n)))

@@ -151,6 +151,9 @@ def test_search_by_bow_vs_oracle(ob, strict, level):
             n, match = m.SearchByFboW(A, B, strict=strict)
             en, ematch = oracle_search_by_bow(A, B, ratio, 50, strict, ori)
             assert n == en and np.array_equal(match, ematch), (seed, ratio, ori)
+            if ratio == 0.9:  # the same call with device buffers in and out
+                nd, md = m.SearchByFboW(A, B, strict=strict, device=True)
+                assert nd == en and np.array_equal(md, ematch), ("device", seed)
             total += n
             m.close()
     assert total > 500, "the synthetic frames must actually match"
