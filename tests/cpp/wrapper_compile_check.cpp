@@ -18,6 +18,10 @@ static std::vector<unsigned char> slurp(const char* path, size_t n) {
     return b;
 }
 
+static void run_initialization(int w, int h, const std::vector<cv::KeyPoint>& kL, const cv::Mat& dL,
+                               const std::vector<cv::KeyPoint>& kR, const cv::Mat& dR, const std::vector<float>& sf,
+                               const char* out);
+
 int main(int argc, char** argv) {
     if (argc < 6) return 1;
     const int w = atoi(argv[1]), h = atoi(argv[2]);
@@ -71,6 +75,7 @@ int main(int argc, char** argv) {
         fclose(g);
         printf("fbow ok: %zu words, %zu nodes, score %.6f\n", bL.size(), fL.size(), sc[0]);
     }
+    if (argc >= 9) run_initialization(w, h, kL, dL, kR, dR, exL.GetScaleFactors(), argv[8]);  // <out3.bin>
     return 0;
 }
 
@@ -209,3 +214,35 @@ std::vector<int> instantiate12(ORB_SLAM2::ORBmatcher& m, const std::vector<KeyFr
     return m.SearchByFboW(kfs, F, out);
 }
 }  // namespace dropin_check
+
+// Tracking::MonocularInitialization (/root/reference/src/Tracking.cc:690-699): ORBmatcher matcher(0.9, true);
+// matcher.SearchForInitialization(mInitialFrame, mCurrentFrame, mvbPrevMatched, mvIniMatches, 100) through the drop-in
+// template, on the two extracted frames. Output: n1, n2, nmatches, vnMatches12, vbPrevMatched, kR, dR.
+static void run_initialization(int w, int h, const std::vector<cv::KeyPoint>& kL, const cv::Mat& dL,
+                               const std::vector<cv::KeyPoint>& kR, const cv::Mat& dR, const std::vector<float>& sf,
+                               const char* out) {
+    dropin_check::Frame F1, F2;
+    dropin_check::Frame* F[2] = {&F1, &F2};
+    for (int k = 0; k < 2; k++) {
+        F[k]->mnMinX = 0; F[k]->mnMaxX = (float)w; F[k]->mnMinY = 0; F[k]->mnMaxY = (float)h;
+        F[k]->mfGridElementWidthInv = 64.0f / (F[k]->mnMaxX - F[k]->mnMinX);    // src/Frame.cc:101-102
+        F[k]->mfGridElementHeightInv = 48.0f / (F[k]->mnMaxY - F[k]->mnMinY);
+        F[k]->mvScaleFactors = sf;
+    }
+    F1.mvKeysUn = kL; F1.mDescriptors = dL; F1.N = (int)kL.size();
+    F2.mvKeysUn = kR; F2.mDescriptors = dR; F2.N = (int)kR.size();
+    std::vector<cv::Point2f> prev(kL.size());
+    for (size_t i = 0; i < kL.size(); i++) prev[i] = kL[i].pt;
+    std::vector<int> m12;
+    ORB_SLAM2::ORBmatcher matcher(0.9f, true);
+    const int nm = matcher.SearchForInitialization(F1, F2, prev, m12, 100);
+    FILE* f = fopen(out, "wb");
+    int hdr[3] = {(int)kL.size(), (int)kR.size(), nm};
+    fwrite(hdr, sizeof(int), 3, f);
+    fwrite(m12.data(), 4, m12.size(), f);
+    fwrite(prev.data(), 8, prev.size(), f);
+    fwrite(kR.data(), sizeof(cv::KeyPoint), kR.size(), f);
+    for (int i = 0; i < dR.rows; i++) fwrite(dR.ptr(i), 1, 32, f);
+    fclose(f);
+    printf("initialization ok: %d matches\n", nm);
+}

@@ -25,10 +25,11 @@ def test_cpp_dropin_end_to_end(tmp_path):
     left, right = synth_stereo_pair(w, h, 5)
     left.tofile(tmp_path / "l.raw"); right.tofile(tmp_path / "r.raw")
     out, out2, vfile = tmp_path / "out.bin", tmp_path / "out2.bin", tmp_path / "synthetic.fbow"
+    out3 = tmp_path / "out3.bin"
     blob = synth_vocabulary(k=10, levels=4, seed=21)
     vfile.write_bytes(blob)
     r = subprocess.run([exe, str(w), str(h), str(tmp_path / "l.raw"), str(tmp_path / "r.raw"), str(out), str(vfile),
-                        str(out2)], capture_output=True, text=True, timeout=120)
+                        str(out2), str(out3)], capture_output=True, text=True, timeout=120)
     assert r.returncode == 0, r.stdout + r.stderr
     raw = open(out, "rb").read()
     nL, nR, accepted, d01, levels, p3w = np.frombuffer(raw[:24], np.int32)
@@ -81,3 +82,28 @@ def test_cpp_dropin_end_to_end(tmp_path):
     sc = np.frombuffer(raw2[at:at + 16], np.float64)
     a, bR = voc.transform(desc), voc.transform(dr)  # (right descriptors: the oracle's own extraction, identical above)
     assert sc[0] == voc.score(a, bR) and sc[1] == voc.score(a, a)
+
+    # SearchForInitialization drop-in (Tracking::MonocularInitialization: ORBmatcher(0.9, true), window 100) on the two
+    # extracted frames, against the oracle's sequential restatement on the very same keypoints and descriptors
+    from oracle_lib import oracle_search_for_initialization
+    from orbslam2_b200 import _lib
+    import orbslam2_b200 as ob
+    raw3 = open(out3, "rb").read()
+    n1, n2, nm = np.frombuffer(raw3[:12], np.int32)
+    at = 12
+    m12 = np.frombuffer(raw3[at:at + 4 * n1], np.int32); at += 4 * n1
+    prev = np.frombuffer(raw3[at:at + 8 * n1], np.float32).reshape(n1, 2); at += 8 * n1
+    kR = np.frombuffer(raw3[at:at + 28 * n2], KP_DTYPE); at += 28 * n2
+    dR = np.frombuffer(raw3[at:at + 32 * n2], np.uint8).reshape(n2, 32)
+    assert n1 == nL and n2 == nR
+    sf = np.asarray(t[0], np.float32)
+    F1 = ob.Frame(kps, desc, sf, 520, 520, 320, 240, 0, w, h)
+    F2 = ob.Frame(kR, dR, sf, 520, 520, 320, 240, 0, w, h)
+    Pp = _lib.ProjParams()
+    Pp.minX, Pp.maxX, Pp.minY, Pp.maxY = 0, w, 0, h
+    Pp.grid_w_inv, Pp.grid_h_inv = float(F2.mfGridElementWidthInv), float(F2.mfGridElementHeightInv)
+    Pp.nlevels, Pp.check_orientation = 8, 1
+    eprev = np.ascontiguousarray(np.stack([kps["x"], kps["y"]], 1), np.float32)
+    en, em12 = oracle_search_for_initialization(Pp, np.float32(0.9), F1, F2, eprev, 100)
+    assert nm == en and np.array_equal(m12, em12) and prev.tobytes() == eprev.tobytes()
+    assert nm > 10, "the stereo pair must give initialisation matches"
