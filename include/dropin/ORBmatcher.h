@@ -110,7 +110,7 @@ public:
     // resulting mvpMapPoints back. FrameT is ORB_SLAM2::Frame (a template so this header needs none of its includes).
     template <class FrameT>
     int SearchByProjection(FrameT& CurrentFrame, const FrameT& LastFrame, const float th, const bool bMono) {
-        orbm_proj_params P;
+        orbm_proj_params P = orbm_proj_params();
         P.fx = CurrentFrame.fx; P.fy = CurrentFrame.fy; P.cx = CurrentFrame.cx; P.cy = CurrentFrame.cy;
         P.bf = CurrentFrame.mbf;
         P.minX = CurrentFrame.mnMinX; P.maxX = CurrentFrame.mnMaxX; P.minY = CurrentFrame.mnMinY; P.maxY = CurrentFrame.mnMaxY;

@@ -4,6 +4,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <set>
+#include <string>
 #include <vector>
 
 #include "dropin/ORBextractor.h"
@@ -21,8 +22,10 @@ static std::vector<unsigned char> slurp(const char* path, size_t n) {
 static void run_initialization(int w, int h, const std::vector<cv::KeyPoint>& kL, const cv::Mat& dL,
                                const std::vector<cv::KeyPoint>& kR, const cv::Mat& dR, const std::vector<float>& sf,
                                const char* out);
+static int run_tracking_search(const char* in, const char* out);
 
 int main(int argc, char** argv) {
+    if (argc == 4 && std::string(argv[1]) == "track") return run_tracking_search(argv[2], argv[3]);
     if (argc < 6) return 1;
     const int w = atoi(argv[1]), h = atoi(argv[2]);
     std::vector<unsigned char> L = slurp(argv[3], (size_t)w * h), R = slurp(argv[4], (size_t)w * h);
@@ -245,4 +248,66 @@ static void run_initialization(int w, int h, const std::vector<cv::KeyPoint>& kL
     for (int i = 0; i < dR.rows; i++) fwrite(dR.ptr(i), 1, 32, f);
     fclose(f);
     printf("initialization ok: %d matches\n", nm);
+}
+
+// Tracking::TrackWithMotionModel (/root/reference/src/Tracking.cc:985): matcher.SearchByProjection(mCurrentFrame,
+// mLastFrame, th, bMono) through the drop-in template on a frame pair dumped by tests/test_gpu_dropin.py.
+// Input: int32 nL, nC, stereo, bMono; float32 th, fx, fy, cx, cy, bf, w, h; Tcw_cur[16], Tcw_last[16], scale[8];
+// last: world[nL*3] f32, valid[nL], outlier[nL], observed[nL] u8, keys[nL] (28 B), desc[nL*32];
+// cur: keys[nC], uRight[nC] f32 (if stereo), desc[nC*32]. Output: nmatches, then per current keypoint the index of the
+// last-frame map point left in mvpMapPoints (-1 = none).
+static int run_tracking_search(const char* in, const char* out) {
+    FILE* f = fopen(in, "rb");
+    if (!f) return 2;
+    int hdr[4];
+    float cam[8], T[2][16], sc[8];
+    if (fread(hdr, 4, 4, f) != 4 || fread(cam, 4, 8, f) != 8 || fread(T, 4, 32, f) != 32 || fread(sc, 4, 8, f) != 8) return 2;
+    const int nL = hdr[0], nC = hdr[1], stereo = hdr[2], bMono = hdr[3];
+    std::vector<float> world((size_t)nL * 3), uR(nC);
+    std::vector<unsigned char> valid(nL), outlier(nL), observed(nL), dl((size_t)nL * 32), dc((size_t)nC * 32);
+    std::vector<cv::KeyPoint> keysL(nL), keysC(nC);
+    bool ok = fread(world.data(), 4, world.size(), f) == world.size() && fread(valid.data(), 1, nL, f) == (size_t)nL &&
+              fread(outlier.data(), 1, nL, f) == (size_t)nL && fread(observed.data(), 1, nL, f) == (size_t)nL &&
+              fread(keysL.data(), sizeof(cv::KeyPoint), nL, f) == (size_t)nL && fread(dl.data(), 1, dl.size(), f) == dl.size() &&
+              fread(keysC.data(), sizeof(cv::KeyPoint), nC, f) == (size_t)nC;
+    if (ok && stereo) ok = fread(uR.data(), 4, nC, f) == (size_t)nC;
+    ok = ok && fread(dc.data(), 1, dc.size(), f) == dc.size();
+    fclose(f);
+    if (!ok) return 2;
+    dropin_check::Frame cur, last;
+    dropin_check::Frame* F[2] = {&cur, &last};
+    for (int k = 0; k < 2; k++) {
+        dropin_check::Frame& X = *F[k];
+        X.fx = cam[1]; X.fy = cam[2]; X.cx = cam[3]; X.cy = cam[4]; X.mbf = cam[5]; X.mb = X.mbf / X.fx;
+        X.mnMinX = 0; X.mnMaxX = cam[6]; X.mnMinY = 0; X.mnMaxY = cam[7];
+        X.mfGridElementWidthInv = 64.0f / (X.mnMaxX - X.mnMinX);
+        X.mfGridElementHeightInv = 48.0f / (X.mnMaxY - X.mnMinY);
+        X.mvScaleFactors.assign(sc, sc + 8);
+        X.mTcw = cv::Mat(4, 4, CV_32FC1, T[k], 4 * sizeof(float));  // header over the floats read above
+    }
+    std::vector<dropin_check::MapPoint> mps(nL);
+    last.N = nL; last.mvKeys = keysL; last.mvKeysUn = keysL;
+    last.mvpMapPoints.assign(nL, nullptr); last.mvbOutlier.assign(nL, false);
+    for (int i = 0; i < nL; i++) {
+        mps[i].pos = cv::Mat(3, 1, CV_32FC1, world.data() + 3 * (size_t)i, sizeof(float));
+        mps[i].desc = cv::Mat(1, 32, CV_8UC1, dl.data() + (size_t)i * 32, 32);
+        mps[i].nObs = observed[i] ? 1 : 0;
+        if (valid[i]) last.mvpMapPoints[i] = &mps[i];
+        last.mvbOutlier[i] = outlier[i] != 0;
+    }
+    cur.N = nC; cur.mvKeys = keysC; cur.mvKeysUn = keysC;
+    cur.mDescriptors = cv::Mat(nC, 32, CV_8UC1, dc.data(), 32);
+    if (stereo) cur.mvuRight = uR;
+    cur.mvpMapPoints.assign(nC, nullptr);
+    ORB_SLAM2::ORBmatcher matcher(0.9f, true);
+    const int nm = matcher.SearchByProjection(cur, last, cam[0], bMono != 0);
+    FILE* g = fopen(out, "wb");
+    fwrite(&nm, 4, 1, g);
+    for (int i = 0; i < nC; i++) {
+        const int idx = cur.mvpMapPoints[i] ? (int)(cur.mvpMapPoints[i] - mps.data()) : -1;
+        fwrite(&idx, 4, 1, g);
+    }
+    fclose(g);
+    printf("tracking search ok: %d matches\n", nm);
+    return 0;
 }

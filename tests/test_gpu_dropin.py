@@ -107,3 +107,42 @@ def test_cpp_dropin_end_to_end(tmp_path):
     en, em12 = oracle_search_for_initialization(Pp, np.float32(0.9), F1, F2, eprev, 100)
     assert nm == en and np.array_equal(m12, em12) and prev.tobytes() == eprev.tobytes()
     assert nm > 10, "the stereo pair must give initialisation matches"
+
+
+@pytest.mark.parametrize("stereo,bMono,th", [(True, False, 15.0), (False, True, 7.0)])
+def test_cpp_tracking_search_dropin(tmp_path, stereo, bMono, th):
+    """The C++ template ORBmatcher::SearchByProjection(Frame&, const Frame&, th, bMono) (what Tracking.cc calls) run for
+    real on a dumped frame pair: its host half (pose algebra, flags, flattening, write-back of mvpMapPoints) plus the
+    device search must give the oracle's nmatches and final mvpMapPoints."""
+    from orbslam2_b200 import build
+    from orbslam2_b200.synth import synth_tracking_pair
+    import orbslam2_b200 as ob
+    lib = build.build()
+    exe = str(tmp_path / "dropin_run")
+    subprocess.check_call(["g++", "-std=c++14", "-O1", "-I", os.path.join(ROOT, "include"), "-I",
+                           os.path.join(ROOT, "oracle", "shim"), os.path.join(ROOT, "tests", "cpp", "wrapper_compile_check.cpp"),
+                           "-L", os.path.dirname(lib), "-lorbx", "-Wl,-rpath," + os.path.dirname(lib), "-o", exe])
+    last, cur = synth_tracking_pair(1500, 33, stereo=stereo, motion=(0.05, -0.02, 0.12), conflicts=200)
+    with open(tmp_path / "pair.bin", "wb") as f:
+        f.write(np.array([last.N, cur.N, int(stereo), int(bMono)], np.int32).tobytes())
+        f.write(np.array([th, cur.fx, cur.fy, cur.cx, cur.cy, cur.mbf, cur.mnMaxX, cur.mnMaxY], np.float32).tobytes())
+        f.write(np.ascontiguousarray(cur.mTcw, np.float32).tobytes()); f.write(np.ascontiguousarray(last.mTcw, np.float32).tobytes())
+        f.write(np.ascontiguousarray(cur.mvScaleFactors[:8], np.float32).tobytes())
+        f.write(np.ascontiguousarray(last.mp_world, np.float32).tobytes())
+        for a in (last.mp_valid, last.mvbOutlier, last.mp_observed):
+            f.write(np.ascontiguousarray(a, np.uint8).tobytes())
+        f.write(last.mvKeysUn.tobytes()); f.write(np.ascontiguousarray(last.mp_desc, np.uint8).tobytes())
+        f.write(cur.mvKeysUn.tobytes())
+        if stereo:
+            f.write(np.ascontiguousarray(cur.mvuRight, np.float32).tobytes())
+        f.write(cur.mDescriptors.tobytes())
+    r = subprocess.run([exe, "track", str(tmp_path / "pair.bin"), str(tmp_path / "track.bin")], capture_output=True, text=True,
+                       timeout=120)
+    assert r.returncode == 0, r.stdout + r.stderr
+    raw = np.fromfile(tmp_path / "track.bin", np.int32)
+    m = ob.ORBmatcher(0.9, True)
+    prm = m._proj_params(cur, last, th, bMono)
+    exp = OraclePrims().search_by_projection(prm, cur, last)
+    m.close()
+    assert raw[0] == exp[0] and np.array_equal(raw[1:], exp[1]), f"{(raw[1:] != exp[1]).sum()} keypoints differ"
+    assert raw[0] > 300
