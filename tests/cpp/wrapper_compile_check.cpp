@@ -23,6 +23,8 @@ static void run_initialization(int w, int h, const std::vector<cv::KeyPoint>& kL
                                const std::vector<cv::KeyPoint>& kR, const cv::Mat& dR, const std::vector<float>& sf,
                                const char* out);
 static int run_tracking_search(const char* in, const char* out);
+static void run_bow_search(const std::vector<cv::KeyPoint>& kL, const cv::Mat& dL, const fbow::fBow2& fL,
+                           const std::vector<cv::KeyPoint>& kR, const cv::Mat& dR, const fbow::fBow2& fR, const char* out);
 
 int main(int argc, char** argv) {
     if (argc == 4 && std::string(argv[1]) == "track") return run_tracking_search(argv[2], argv[3]);
@@ -77,6 +79,7 @@ int main(int argc, char** argv) {
         fwrite(sc, 8, 2, g);
         fclose(g);
         printf("fbow ok: %zu words, %zu nodes, score %.6f\n", bL.size(), fL.size(), sc[0]);
+        if (argc >= 10) run_bow_search(kL, dL, fL, kR, dR, fR, argv[9]);  // <out4.bin>
     }
     if (argc >= 9) run_initialization(w, h, kL, dL, kR, dR, exL.GetScaleFactors(), argv[8]);  // <out3.bin>
     return 0;
@@ -310,4 +313,32 @@ static int run_tracking_search(const char* in, const char* out) {
     fclose(g);
     printf("tracking search ok: %d matches\n", nm);
     return 0;
+}
+
+// Tracking::TrackReferenceKeyFrame (/root/reference/src/Tracking.cc:862-867): ORBmatcher matcher(0.7, true);
+// matcher.SearchByFboW(mpReferenceKF, mCurrentFrame, vpMapPointMatches) through the drop-in template: the left frame
+// plays the keyframe (every 5th keypoint has no map point), the right one the current frame; the feature vectors are
+// the ones fbow::Vocabulary::transform just produced. Output: nmatches, then per frame keypoint the keyframe index of
+// the map point in vpMapPointMatches (-1 = none).
+static void run_bow_search(const std::vector<cv::KeyPoint>& kL, const cv::Mat& dL, const fbow::fBow2& fL,
+                           const std::vector<cv::KeyPoint>& kR, const cv::Mat& dR, const fbow::fBow2& fR, const char* out) {
+    dropin_check::KeyFrame kf;
+    kf.mvKeysUn = kL; kf.mDescriptors = dL; kf.mFbowFeatVec = fL;
+    std::vector<dropin_check::MapPoint> mp(kL.size());
+    kf.mps.assign(kL.size(), nullptr);
+    for (size_t i = 0; i < kL.size(); i++)
+        if (i % 5 != 4) kf.mps[i] = &mp[i];
+    dropin_check::BowFrame F;
+    F.N = (int)kR.size(); F.mvKeys = kR; F.mvKeysUn = kR; F.mDescriptors = dR; F.mFbowFeatVec = fR;
+    std::vector<dropin_check::MapPoint*> matches;
+    ORB_SLAM2::ORBmatcher matcher(0.7f, true);
+    const int nm = matcher.SearchByFboW(&kf, F, matches);
+    FILE* g = fopen(out, "wb");
+    fwrite(&nm, 4, 1, g);
+    for (size_t i = 0; i < matches.size(); i++) {
+        const int idx = matches[i] ? (int)(matches[i] - mp.data()) : -1;
+        fwrite(&idx, 4, 1, g);
+    }
+    fclose(g);
+    printf("bow search ok: %d matches\n", nm);
 }

@@ -25,11 +25,11 @@ def test_cpp_dropin_end_to_end(tmp_path):
     left, right = synth_stereo_pair(w, h, 5)
     left.tofile(tmp_path / "l.raw"); right.tofile(tmp_path / "r.raw")
     out, out2, vfile = tmp_path / "out.bin", tmp_path / "out2.bin", tmp_path / "synthetic.fbow"
-    out3 = tmp_path / "out3.bin"
+    out3, out4 = tmp_path / "out3.bin", tmp_path / "out4.bin"
     blob = synth_vocabulary(k=10, levels=4, seed=21)
     vfile.write_bytes(blob)
     r = subprocess.run([exe, str(w), str(h), str(tmp_path / "l.raw"), str(tmp_path / "r.raw"), str(out), str(vfile),
-                        str(out2), str(out3)], capture_output=True, text=True, timeout=120)
+                        str(out2), str(out3), str(out4)], capture_output=True, text=True, timeout=120)
     assert r.returncode == 0, r.stdout + r.stderr
     raw = open(out, "rb").read()
     nL, nR, accepted, d01, levels, p3w = np.frombuffer(raw[:24], np.int32)
@@ -108,6 +108,19 @@ def test_cpp_dropin_end_to_end(tmp_path):
     assert nm == en and np.array_equal(m12, em12) and prev.tobytes() == eprev.tobytes()
     assert nm > 10, "the stereo pair must give initialisation matches"
 
+    # SearchByFboW(KeyFrame, Frame) drop-in (TrackReferenceKeyFrame: ORBmatcher(0.7, true)) on the same two frames and the
+    # feature vectors the fbow drop-in produced, against the oracle's sequential restatement
+    from oracle_lib import oracle_search_by_bow
+    raw4 = np.fromfile(out4, np.int32)
+    _, efvR = voc.transform(dR, 4)
+    elig = (np.arange(nL) % 5 != 4).astype(np.uint8)
+    A = ob.ORBmatcher.bow_side(desc, np.ascontiguousarray(kps["angle"]), efv, elig)
+    B = ob.ORBmatcher.bow_side(dR, np.ascontiguousarray(kR["angle"]), efvR, None)
+    en, ematch = oracle_search_by_bow(A, B, 0.7, 50, False, True)
+    expF = np.full(n2, -1, np.int32)
+    expF[ematch[ematch >= 0]] = np.flatnonzero(ematch >= 0)
+    assert raw4[0] == en and np.array_equal(raw4[1:], expF), f"{(raw4[1:] != expF).sum()} frame keypoints differ"
+    assert en > 5
 
 @pytest.mark.parametrize("stereo,bMono,th", [(True, False, 15.0), (False, True, 7.0)])
 def test_cpp_tracking_search_dropin(tmp_path, stereo, bMono, th):
