@@ -23,11 +23,13 @@ static void run_initialization(int w, int h, const std::vector<cv::KeyPoint>& kL
                                const std::vector<cv::KeyPoint>& kR, const cv::Mat& dR, const std::vector<float>& sf,
                                const char* out);
 static int run_tracking_search(const char* in, const char* out);
+static int run_sim3_projection(const char* in, const char* out);
 static void run_bow_search(const std::vector<cv::KeyPoint>& kL, const cv::Mat& dL, const fbow::fBow2& fL,
                            const std::vector<cv::KeyPoint>& kR, const cv::Mat& dR, const fbow::fBow2& fR, const char* out);
 
 int main(int argc, char** argv) {
     if (argc == 4 && std::string(argv[1]) == "track") return run_tracking_search(argv[2], argv[3]);
+    if (argc == 4 && std::string(argv[1]) == "sim3") return run_sim3_projection(argv[2], argv[3]);
     if (argc < 6) return 1;
     const int w = atoi(argv[1]), h = atoi(argv[2]);
     std::vector<unsigned char> L = slurp(argv[3], (size_t)w * h), R = slurp(argv[4], (size_t)w * h);
@@ -341,4 +343,85 @@ static void run_bow_search(const std::vector<cv::KeyPoint>& kL, const cv::Mat& d
     }
     fclose(g);
     printf("bow search ok: %d matches\n", nm);
+}
+
+// LoopClosing::ComputeSim3 (/root/reference/src/LoopClosing.cc:411): matcher.SearchByProjection(mpCurrentKF, mScw,
+// mvpLoopMapPoints, mvpCurrentMatchedPoints, 10) through the drop-in template on dumped data.
+// Input: int32 n, nK, th; float32 fx, fy, cx, cy, w, h; Scw[16]; scale[8]; points: world[n*3], normal[n*3], minDist[n],
+// maxDist[n] f32, level[n] i32, bad[n] u8, desc[n*32]; keyframe: keys[nK], desc[nK*32], matched[nK] u8.
+// Output: nmatches, then per keypoint: index in vpPoints of vpMatched[idx], -2 = the entry present on entry, -1 = NULL.
+namespace run_sim3 {
+struct KeyFrame;
+struct MapPoint {
+    const float *w, *nrm;
+    float dmin, dmax;
+    int level;
+    bool bad;
+    unsigned char* d;
+    bool isBad() { return bad; }
+    cv::Mat GetWorldPos() { return cv::Mat(3, 1, CV_32FC1, (void*)w, sizeof(float)); }
+    cv::Mat GetNormal() { return cv::Mat(3, 1, CV_32FC1, (void*)nrm, sizeof(float)); }
+    float GetMinDistanceInvariance() { return dmin; }
+    float GetMaxDistanceInvariance() { return dmax; }
+    int PredictScale(float, KeyFrame*) { return level; }
+    cv::Mat GetDescriptor() { return cv::Mat(1, 32, CV_8UC1, d, 32); }
+};
+struct KeyFrame {
+    float fx, fy, cx, cy, mnMinX, mnMaxX, mnMinY, mnMaxY, mfGridElementWidthInv, mfGridElementHeightInv;
+    std::vector<float> mvScaleFactors;
+    std::vector<cv::KeyPoint> mvKeysUn;
+    cv::Mat mDescriptors;
+    bool IsInImage(const float& x, const float& y) const { return x >= mnMinX && x < mnMaxX && y >= mnMinY && y < mnMaxY; }
+};
+}  // namespace run_sim3
+static int run_sim3_projection(const char* in, const char* out) {
+    FILE* f = fopen(in, "rb");
+    if (!f) return 2;
+    int hdr[3];
+    float cam[6], Scw[16], sc[8];
+    if (fread(hdr, 4, 3, f) != 3 || fread(cam, 4, 6, f) != 6 || fread(Scw, 4, 16, f) != 16 || fread(sc, 4, 8, f) != 8) return 2;
+    const int n = hdr[0], nK = hdr[1], th = hdr[2];
+    std::vector<float> world((size_t)n * 3), normal((size_t)n * 3), dmin(n), dmax(n);
+    std::vector<int> level(n);
+    std::vector<unsigned char> bad(n), dp((size_t)n * 32), dk((size_t)nK * 32), matched(nK);
+    std::vector<cv::KeyPoint> keys(nK);
+    const bool ok = fread(world.data(), 4, world.size(), f) == world.size() && fread(normal.data(), 4, normal.size(), f) == normal.size() &&
+                    fread(dmin.data(), 4, n, f) == (size_t)n && fread(dmax.data(), 4, n, f) == (size_t)n &&
+                    fread(level.data(), 4, n, f) == (size_t)n && fread(bad.data(), 1, n, f) == (size_t)n &&
+                    fread(dp.data(), 1, dp.size(), f) == dp.size() && fread(keys.data(), sizeof(cv::KeyPoint), nK, f) == (size_t)nK &&
+                    fread(dk.data(), 1, dk.size(), f) == dk.size() && fread(matched.data(), 1, nK, f) == (size_t)nK;
+    fclose(f);
+    if (!ok) return 2;
+    run_sim3::KeyFrame kf;
+    kf.fx = cam[0]; kf.fy = cam[1]; kf.cx = cam[2]; kf.cy = cam[3];
+    kf.mnMinX = 0; kf.mnMaxX = cam[4]; kf.mnMinY = 0; kf.mnMaxY = cam[5];
+    kf.mfGridElementWidthInv = 64.0f / (kf.mnMaxX - kf.mnMinX);
+    kf.mfGridElementHeightInv = 48.0f / (kf.mnMaxY - kf.mnMinY);
+    kf.mvScaleFactors.assign(sc, sc + 8);
+    kf.mvKeysUn = keys;
+    kf.mDescriptors = cv::Mat(nK, 32, CV_8UC1, dk.data(), 32);
+    std::vector<run_sim3::MapPoint> pts(n);
+    std::vector<run_sim3::MapPoint*> vpPoints(n);
+    for (int i = 0; i < n; i++) {
+        run_sim3::MapPoint p = {world.data() + 3 * (size_t)i, normal.data() + 3 * (size_t)i, dmin[i], dmax[i], level[i], bad[i] != 0,
+                                dp.data() + (size_t)i * 32};
+        pts[i] = p;
+        vpPoints[i] = &pts[i];
+    }
+    run_sim3::MapPoint present = pts.empty() ? run_sim3::MapPoint() : pts[0];  // stands for matches found earlier (not in vpPoints)
+    std::vector<run_sim3::MapPoint*> vpMatched(nK, nullptr);
+    for (int i = 0; i < nK; i++)
+        if (matched[i]) vpMatched[i] = &present;
+    cv::Mat S(4, 4, CV_32FC1, Scw, 4 * sizeof(float));
+    ORB_SLAM2::ORBmatcher matcher(0.75f, true);
+    const int nm = matcher.SearchByProjection(&kf, S, vpPoints, vpMatched, th);
+    FILE* g = fopen(out, "wb");
+    fwrite(&nm, 4, 1, g);
+    for (int i = 0; i < nK; i++) {
+        const int idx = !vpMatched[i] ? -1 : (vpMatched[i] == &present ? -2 : (int)(vpMatched[i] - pts.data()));
+        fwrite(&idx, 4, 1, g);
+    }
+    fclose(g);
+    printf("sim3 projection search ok: %d matches\n", nm);
+    return 0;
 }

@@ -159,3 +159,104 @@ def test_cpp_tracking_search_dropin(tmp_path, stereo, bMono, th):
     m.close()
     assert raw[0] == exp[0] and np.array_equal(raw[1:], exp[1]), f"{(raw[1:] != exp[1]).sum()} keypoints differ"
     assert raw[0] > 300
+
+
+def _build_exe(tmp_path):
+    from orbslam2_b200 import build
+    lib = build.build()
+    exe = str(tmp_path / "dropin_run")
+    subprocess.check_call(["g++", "-std=c++14", "-O1", "-I", os.path.join(ROOT, "include"), "-I",
+                           os.path.join(ROOT, "oracle", "shim"), os.path.join(ROOT, "tests", "cpp", "wrapper_compile_check.cpp"),
+                           "-L", os.path.dirname(lib), "-lorbx", "-Wl,-rpath," + os.path.dirname(lib), "-o", exe])
+    return exe
+
+
+def test_cpp_sim3_projection_dropin(tmp_path):
+    """The C++ template ORBmatcher::SearchByProjection(KeyFrame*, Scw, vpPoints, vpMatched, th) (LoopClosing::ComputeSim3)
+    run for real: Scw decomposition, projection and the MapPoint gates on the host (restated here in numpy with the same
+    float / double steps), window search with the vpMatched claims on the device — against the oracle's sequential loop."""
+    from orbslam2_b200.synth import synth_tracking_pair
+    from oracle_lib import oracle_search_kf_projection
+    from orbslam2_b200 import _lib
+    exe = _build_exe(tmp_path)
+    rng = np.random.default_rng(77)
+    kf, _ = synth_tracking_pair(1500, 44, stereo=False, motion=(0.03, 0.01, 0.05))
+    w, h, th = 640, 480, 10
+    f32, f64 = np.float32, np.float64
+    # Sim3 = scale * [R | t] with a small rotation; world points chosen so that they project near keypoints of kf
+    s_true, ang = f32(1.7), 0.04
+    R = np.array([[np.cos(ang), 0, np.sin(ang)], [0, 1, 0], [-np.sin(ang), 0, np.cos(ang)]])
+    t = np.array([0.1, -0.05, 0.2])
+    Scw = np.eye(4, dtype=f32); Scw[:3, :3] = (s_true * R).astype(f32); Scw[:3, 3] = (s_true * t).astype(f32)
+    n = 2500
+    src = rng.integers(0, kf.N, n)
+    z = rng.uniform(2, 10, n)
+    pc = np.stack([(kf.mvKeysUn["x"][src] + rng.normal(0, 1.2, n) - float(kf.cx)) / float(kf.fx) * z,
+                   (kf.mvKeysUn["y"][src] + rng.normal(0, 1.2, n) - float(kf.cy)) / float(kf.fy) * z, z], 1)
+    behind = rng.random(n) < 0.05
+    pc[behind, 2] *= -1
+    world = ((pc - t) @ R).astype(f32)                       # Rcw^T (pc - tcw)
+    bits = np.unpackbits(kf.mDescriptors[src], axis=1)
+    for _ in range(8):
+        bits[np.arange(n), rng.integers(0, 256, n)] ^= 1
+    desc = np.packbits(bits, axis=1)
+    level = np.clip(kf.mvKeysUn["octave"][src] + rng.integers(0, 2, n), 0, 7).astype(np.int32)
+    bad = (rng.random(n) < 0.05).astype(np.uint8)
+    dmin = rng.uniform(0.5, 3.0, n).astype(f32); dmax = rng.uniform(6.0, 14.0, n).astype(f32)
+    # restatement of project_sim3 (include/dropin/ORBmatcher.h) = src/ORBmatcher.cc:293-298, 313-351
+    sR = Scw[:3, :3]
+    scw = f32(np.sqrt(sum(f64(sR[0, c]) * f64(sR[0, c]) for c in range(3))))
+    inv = f32(1.0 / f64(scw))
+    Rcw = (sR * inv).astype(f32); tcw = (Scw[:3, 3] * inv).astype(f32)
+    Ow = np.array([-f32(sum(f64(Rcw[c, r]) * f64(tcw[c]) for c in range(3))) for r in range(3)], f32)
+    normal = np.zeros((n, 3), f32)
+    u = np.zeros(n, f32); v = np.zeros(n, f32); valid = np.zeros(n, np.uint8)
+    for i in range(n):
+        wv = world[i]
+        po = (wv - Ow).astype(f32)
+        nv = po / np.linalg.norm(po)
+        if rng.random() < 0.1:
+            nv = -nv                                            # viewing-angle gate fails
+        normal[i] = nv.astype(f32)
+    for i in range(n):
+        if bad[i]:
+            continue
+        wv = world[i]
+        p = [f32(f32(sum(f64(Rcw[r, c]) * f64(wv[c]) for c in range(3))) + tcw[r]) for r in range(3)]
+        if p[2] < 0:
+            continue
+        invz = f32(1.0 / f64(p[2]))
+        uu = f32(f32(kf.fx * f32(p[0] * invz)) + kf.cx); vv = f32(f32(kf.fy * f32(p[1] * invz)) + kf.cy)
+        if not (0 <= uu < w and 0 <= vv < h):
+            continue
+        po = [f32(wv[k] - Ow[k]) for k in range(3)]
+        dist = f32(np.sqrt(sum(f64(x) * f64(x) for x in po)))
+        if dist < dmin[i] or dist > dmax[i]:
+            continue
+        if sum(f64(po[k]) * f64(normal[i, k]) for k in range(3)) < 0.5 * f64(dist):
+            continue
+        u[i], v[i], valid[i] = uu, vv, 1
+    taken = (rng.random(kf.N) < 0.15).astype(np.uint8)
+    with open(tmp_path / "sim3.bin", "wb") as f:
+        f.write(np.array([n, kf.N, th], np.int32).tobytes())
+        f.write(np.array([kf.fx, kf.fy, kf.cx, kf.cy, w, h], f32).tobytes())
+        f.write(Scw.tobytes()); f.write(np.ascontiguousarray(kf.mvScaleFactors[:8], f32).tobytes())
+        for a in (world, normal, dmin, dmax, level, bad, desc):
+            f.write(np.ascontiguousarray(a).tobytes())
+        f.write(kf.mvKeysUn.tobytes()); f.write(kf.mDescriptors.tobytes()); f.write(taken.tobytes())
+    r = subprocess.run([exe, "sim3", str(tmp_path / "sim3.bin"), str(tmp_path / "sim3_out.bin")], capture_output=True, text=True,
+                       timeout=120)
+    assert r.returncode == 0, r.stdout + r.stderr
+    raw = np.fromfile(tmp_path / "sim3_out.bin", np.int32)
+    P = _lib.ProjParams()
+    P.minX, P.maxX, P.minY, P.maxY = 0, w, 0, h
+    P.grid_w_inv, P.grid_h_inv = float(kf.mfGridElementWidthInv), float(kf.mfGridElementHeightInv)
+    P.nlevels = 8
+    for i, sfv in enumerate(kf.mvScaleFactors[:8]):
+        P.scale[i] = float(sfv)
+    P.th, P.th_high = float(th), 50
+    pts = dict(u=u, v=v, level=level, valid=valid, desc=desc)
+    en, ekm, epm = oracle_search_kf_projection(P, pts, kf, taken)
+    exp = np.where(ekm >= 0, ekm, np.where(taken != 0, -2, -1)).astype(np.int32)
+    assert raw[0] == en and np.array_equal(raw[1:], exp), f"{(raw[1:] != exp).sum()} keypoints differ"
+    assert en > 300 and 0.3 < valid.mean() < 0.95
