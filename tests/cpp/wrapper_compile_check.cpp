@@ -24,12 +24,14 @@ static void run_initialization(int w, int h, const std::vector<cv::KeyPoint>& kL
                                const char* out);
 static int run_tracking_search(const char* in, const char* out);
 static int run_sim3_projection(const char* in, const char* out);
+static int run_search_by_sim3(const char* in, const char* out);
 static void run_bow_search(const std::vector<cv::KeyPoint>& kL, const cv::Mat& dL, const fbow::fBow2& fL,
                            const std::vector<cv::KeyPoint>& kR, const cv::Mat& dR, const fbow::fBow2& fR, const char* out);
 
 int main(int argc, char** argv) {
     if (argc == 4 && std::string(argv[1]) == "track") return run_tracking_search(argv[2], argv[3]);
     if (argc == 4 && std::string(argv[1]) == "sim3") return run_sim3_projection(argv[2], argv[3]);
+    if (argc == 4 && std::string(argv[1]) == "sim3b") return run_search_by_sim3(argv[2], argv[3]);
     if (argc < 6) return 1;
     const int w = atoi(argv[1]), h = atoi(argv[2]);
     std::vector<unsigned char> L = slurp(argv[3], (size_t)w * h), R = slurp(argv[4], (size_t)w * h);
@@ -423,5 +425,112 @@ static int run_sim3_projection(const char* in, const char* out) {
     }
     fclose(g);
     printf("sim3 projection search ok: %d matches\n", nm);
+    return 0;
+}
+
+// LoopClosing::ComputeSim3 (/root/reference/src/LoopClosing.cc:359): matcher.SearchBySim3(mpCurrentKF, pKF, vpMapPointMatches,
+// s, R, t, 7.5) through the drop-in template on dumped data.
+// Input: int32 n1, n2; float32 th, fx, fy, cx, cy, w, h, s12; R12[9], t12[3], R1w[9], t1w[3], R2w[9], t2w[3]; scale[8];
+// then for KF1 and KF2 each: keys[n], kfdesc[n*32], has[n] u8, bad[n] u8, world[n*3], dmin[n], dmax[n] f32, level[n] i32,
+// mpdesc[n*32]; finally pre[n1] i32: index in KF2 of the map point already in vpMatches12[i] (-1 = entry is NULL).
+// Output: nFound, then per KF1 keypoint the KF2 index of vpMatches12[i] (-1 = NULL).
+namespace run_sim3b {
+struct KeyFrame;
+struct MapPoint {
+    const float* w;
+    float dmin, dmax;
+    int level, idxIn2;
+    bool bad;
+    unsigned char* d;
+    bool isBad() { return bad; }
+    cv::Mat GetWorldPos() { return cv::Mat(3, 1, CV_32FC1, (void*)w, sizeof(float)); }
+    float GetMinDistanceInvariance() { return dmin; }
+    float GetMaxDistanceInvariance() { return dmax; }
+    int PredictScale(float, KeyFrame*) { return level; }
+    int GetIndexInKeyFrame(KeyFrame*) { return idxIn2; }
+    cv::Mat GetDescriptor() { return cv::Mat(1, 32, CV_8UC1, d, 32); }
+};
+struct KeyFrame {
+    float fx, fy, cx, cy, mnMinX, mnMaxX, mnMinY, mnMaxY, mfGridElementWidthInv, mfGridElementHeightInv;
+    std::vector<float> mvScaleFactors;
+    std::vector<cv::KeyPoint> mvKeysUn;
+    cv::Mat mDescriptors;
+    float R[9], t[3];
+    std::vector<MapPoint*> mps;
+    cv::Mat GetRotation() { return cv::Mat(3, 3, CV_32FC1, R, 3 * sizeof(float)); }
+    cv::Mat GetTranslation() { return cv::Mat(3, 1, CV_32FC1, t, sizeof(float)); }
+    std::vector<MapPoint*> GetMapPointMatches() { return mps; }
+    bool IsInImage(const float& x, const float& y) const { return x >= mnMinX && x < mnMaxX && y >= mnMinY && y < mnMaxY; }
+};
+struct Side {
+    std::vector<cv::KeyPoint> keys;
+    std::vector<unsigned char> kd, has, bad, md;
+    std::vector<float> world, dmin, dmax;
+    std::vector<int> level;
+    std::vector<MapPoint> pts;
+    bool read(FILE* f, int n) {
+        keys.resize(n); kd.resize((size_t)n * 32); has.resize(n); bad.resize(n); world.resize((size_t)n * 3);
+        dmin.resize(n); dmax.resize(n); level.resize(n); md.resize((size_t)n * 32);
+        return fread(keys.data(), sizeof(cv::KeyPoint), n, f) == (size_t)n && fread(kd.data(), 1, kd.size(), f) == kd.size() &&
+               fread(has.data(), 1, n, f) == (size_t)n && fread(bad.data(), 1, n, f) == (size_t)n &&
+               fread(world.data(), 4, world.size(), f) == world.size() && fread(dmin.data(), 4, n, f) == (size_t)n &&
+               fread(dmax.data(), 4, n, f) == (size_t)n && fread(level.data(), 4, n, f) == (size_t)n &&
+               fread(md.data(), 1, md.size(), f) == md.size();
+    }
+    void fill(KeyFrame& K, const float* cam, const float* sc, const float* R, const float* t) {
+        const int n = (int)keys.size();
+        K.fx = cam[1]; K.fy = cam[2]; K.cx = cam[3]; K.cy = cam[4];
+        K.mnMinX = 0; K.mnMaxX = cam[5]; K.mnMinY = 0; K.mnMaxY = cam[6];
+        K.mfGridElementWidthInv = 64.0f / (K.mnMaxX - K.mnMinX);
+        K.mfGridElementHeightInv = 48.0f / (K.mnMaxY - K.mnMinY);
+        K.mvScaleFactors.assign(sc, sc + 8);
+        K.mvKeysUn = keys;
+        K.mDescriptors = cv::Mat(n, 32, CV_8UC1, kd.data(), 32);
+        for (int i = 0; i < 9; i++) K.R[i] = R[i];
+        for (int i = 0; i < 3; i++) K.t[i] = t[i];
+        pts.resize(n);
+        K.mps.assign(n, nullptr);
+        for (int i = 0; i < n; i++) {
+            MapPoint p = {world.data() + 3 * (size_t)i, dmin[i], dmax[i], level[i], -1, bad[i] != 0, md.data() + (size_t)i * 32};
+            pts[i] = p;
+            if (has[i]) K.mps[i] = &pts[i];
+        }
+    }
+};
+}  // namespace run_sim3b
+static int run_search_by_sim3(const char* in, const char* out) {
+    FILE* f = fopen(in, "rb");
+    if (!f) return 2;
+    int hdr[2];
+    float cam[8], R12[9], t12[3], R1w[9], t1w[3], R2w[9], t2w[3], sc[8];
+    if (fread(hdr, 4, 2, f) != 2 || fread(cam, 4, 8, f) != 8 || fread(R12, 4, 9, f) != 9 || fread(t12, 4, 3, f) != 3 ||
+        fread(R1w, 4, 9, f) != 9 || fread(t1w, 4, 3, f) != 3 || fread(R2w, 4, 9, f) != 9 || fread(t2w, 4, 3, f) != 3 ||
+        fread(sc, 4, 8, f) != 8)
+        return 2;
+    const int n1 = hdr[0], n2 = hdr[1];
+    run_sim3b::Side S1, S2;
+    std::vector<int> pre(n1);
+    const bool ok = S1.read(f, n1) && S2.read(f, n2) && fread(pre.data(), 4, n1, f) == (size_t)n1;
+    fclose(f);
+    if (!ok) return 2;
+    run_sim3b::KeyFrame K1, K2;
+    S1.fill(K1, cam, sc, R1w, t1w);
+    S2.fill(K2, cam, sc, R2w, t2w);
+    for (int i = 0; i < n2; i++) S2.pts[i].idxIn2 = i;  // a map point of KF2 is observed in KF2 at its own index
+    std::vector<run_sim3b::MapPoint*> vpMatches12(n1, nullptr);
+    for (int i = 0; i < n1; i++)
+        if (pre[i] >= 0) vpMatches12[i] = &S2.pts[pre[i]];
+    const float s12 = cam[7];
+    cv::Mat R(3, 3, CV_32FC1, R12, 3 * sizeof(float)), t(3, 1, CV_32FC1, t12, sizeof(float));
+    ORB_SLAM2::ORBmatcher matcher(0.75f, true);
+    const int nFound = matcher.SearchBySim3(&K1, &K2, vpMatches12, s12, R, t, cam[0]);
+    FILE* g = fopen(out, "wb");
+    fwrite(&nFound, 4, 1, g);
+    for (int i = 0; i < n1; i++) {
+        const int idx = vpMatches12[i] ? (int)(vpMatches12[i] - S2.pts.data()) : -1;
+        fwrite(&idx, 4, 1, g);
+    }
+    fclose(g);
+    printf("SearchBySim3 ok: %d found\n", nFound);
     return 0;
 }

@@ -260,3 +260,121 @@ def test_cpp_sim3_projection_dropin(tmp_path):
     exp = np.where(ekm >= 0, ekm, np.where(taken != 0, -2, -1)).astype(np.int32)
     assert raw[0] == en and np.array_equal(raw[1:], exp), f"{(raw[1:] != exp).sum()} keypoints differ"
     assert en > 300 and 0.3 < valid.mean() < 0.95
+
+
+def test_cpp_search_by_sim3_dropin(tmp_path):
+    """The C++ template ORBmatcher::SearchBySim3 (LoopClosing::ComputeSim3) run for real on two synthetic keyframes seeing
+    the same 3-D points: relative Sim3 algebra, both projection directions and the already-matched masks on the host
+    (restated here in numpy with the same float / double steps), two device window searches, mutual agreement — against
+    the oracle's per-direction search."""
+    from oracle_lib import oracle_fuse_search
+    from orbslam2_b200 import _lib
+    from orbslam2_b200.extractor import KP_DTYPE as KPD
+    import orbslam2_b200 as ob
+    exe = _build_exe(tmp_path)
+    rng = np.random.default_rng(123)
+    f32, f64 = np.float32, np.float64
+    w, h, th = 640, 480, f32(7.5)
+    fx = fy = f32(520.0); cx, cy = f32(319.5), f32(240.25)
+    sf = np.ones(8, f32)
+    for i in range(1, 8):
+        sf[i] = f32(f64(sf[i - 1]) * f64(f32(1.2)))
+    n = 1400
+    z = rng.uniform(2.5, 10, n)
+    X = np.stack([(rng.uniform(30, w - 30, n) - cx) / fx * z, (rng.uniform(30, h - 30, n) - cy) / fy * z, z], 1)
+    ang = 0.06
+    R2 = np.array([[np.cos(ang), 0, np.sin(ang)], [0, 1, 0], [-np.sin(ang), 0, np.cos(ang)]])
+    t2 = np.array([0.15, -0.03, 0.1])
+    R1w, t1w = np.eye(3, dtype=f32), np.zeros(3, f32)
+    R2w, t2w = R2.astype(f32), t2.astype(f32)
+    s12 = f32(1.02)
+    R12 = (R1w.astype(f64) @ R2w.astype(f64).T).astype(f32)
+    t12 = (t1w.astype(f64) - R12.astype(f64) @ t2w.astype(f64) + rng.normal(0, 0.01, 3)).astype(f32)
+    base = rng.integers(0, 256, (n, 32), dtype=np.uint8)
+
+    def flips(d, k):
+        b = np.unpackbits(d, axis=1)
+        for _ in range(k):
+            b[np.arange(len(d)), rng.integers(0, 256, len(d))] ^= 1
+        return np.packbits(b, axis=1)
+
+    def make_side(Rw, tw, perm):
+        pc = X[perm] @ Rw.astype(f64).T + tw.astype(f64)
+        k = np.zeros(n, KPD)
+        k["x"] = (fx * pc[:, 0] / pc[:, 2] + cx + rng.normal(0, 0.8, n)).astype(f32)
+        k["y"] = (fy * pc[:, 1] / pc[:, 2] + cy + rng.normal(0, 0.8, n)).astype(f32)
+        k["octave"] = rng.integers(0, 8, n); k["angle"] = rng.uniform(0, 360, n); k["class_id"] = -1
+        k["size"] = 31 * sf[k["octave"]]
+        return dict(keys=k, kd=flips(base[perm], 4), has=(rng.random(n) < 0.9).astype(np.uint8),
+                    bad=(rng.random(n) < 0.04).astype(np.uint8), world=(X[perm] + rng.normal(0, 0.003, (n, 3))).astype(f32),
+                    dmin=rng.uniform(0.5, 2.4, n).astype(f32), dmax=rng.uniform(8.0, 14.0, n).astype(f32), md=flips(base[perm], 5),
+                    perm=perm)
+
+    S1, S2 = make_side(R1w, t1w, np.arange(n)), make_side(R2w, t2w, rng.permutation(n))
+    inv2 = np.empty(n, np.int64); inv2[S2["perm"]] = np.arange(n)
+    # predicted level of a point in the OTHER keyframe: the octave of its true partner there (+0/1)
+    S1["level"] = np.clip(S2["keys"]["octave"][inv2[S1["perm"]]] + rng.integers(0, 2, n), 0, 7).astype(np.int32)
+    S2["level"] = np.clip(S1["keys"]["octave"][S2["perm"]] + rng.integers(0, 2, n), 0, 7).astype(np.int32)
+    pre = np.where(rng.random(n) < 0.1, inv2[S1["perm"]], -1).astype(np.int32)   # matches found earlier by SearchByFboW
+    with open(tmp_path / "sim3b.bin", "wb") as f:
+        f.write(np.array([n, n], np.int32).tobytes())
+        f.write(np.array([th, fx, fy, cx, cy, w, h, s12], f32).tobytes())
+        for a in (R12, t12, R1w, t1w, R2w, t2w, sf):
+            f.write(np.ascontiguousarray(a, f32).tobytes())
+        for S in (S1, S2):
+            f.write(S["keys"].tobytes())
+            for key in ("kd", "has", "bad", "world", "dmin", "dmax", "level", "md"):
+                f.write(np.ascontiguousarray(S[key]).tobytes())
+        f.write(pre.tobytes())
+    r = subprocess.run([exe, "sim3b", str(tmp_path / "sim3b.bin"), str(tmp_path / "sim3b_out.bin")], capture_output=True,
+                       text=True, timeout=120)
+    assert r.returncode == 0, r.stdout + r.stderr
+    raw = np.fromfile(tmp_path / "sim3b_out.bin", np.int32)
+
+    # numpy restatement of the template's host half (src/ORBmatcher.cc:1108-1121, 1140-1177, 1221-1258)
+    def mul_add(A, x, b):
+        return np.array([f32(f32(sum(f64(A[r, c]) * f64(x[c]) for c in range(3))) + b[r]) for r in range(3)], f32)
+    inv = f32(1.0 / f64(s12))
+    sR12 = (s12 * R12).astype(f32); sR21 = (inv * R12.T).astype(f32)
+    t21 = np.array([-f32(sum(f64(sR21[r, c]) * f64(t12[c]) for c in range(3))) for r in range(3)], f32)
+    already1 = pre >= 0
+    already2 = np.zeros(n, bool); already2[pre[pre >= 0]] = True
+
+    def direction(S, already, Rsw, tsw, sR, t, dstS):
+        u = np.zeros(n, f32); v = np.zeros(n, f32); valid = np.zeros(n, np.uint8)
+        for i in range(n):
+            if not S["has"][i] or already[i] or S["bad"][i]:
+                continue
+            c2 = mul_add(sR, mul_add(Rsw, S["world"][i], tsw), t)
+            if c2[2] < 0:
+                continue
+            invz = f32(1.0 / f64(c2[2]))
+            uu = f32(f32(fx * f32(c2[0] * invz)) + cx); vv = f32(f32(fy * f32(c2[1] * invz)) + cy)
+            if not (0 <= uu < w and 0 <= vv < h):
+                continue
+            d3 = f32(np.sqrt(sum(f64(c) * f64(c) for c in c2)))
+            if d3 < S["dmin"][i] or d3 > S["dmax"][i]:
+                continue
+            u[i], v[i], valid[i] = uu, vv, 1
+        kf = ob.Frame(dstS["keys"], dstS["kd"], sf, fx, fy, cx, cy, 0, w, h)
+        P = _lib.ProjParams()
+        P.minX, P.maxX, P.minY, P.maxY = 0, w, 0, h
+        P.grid_w_inv, P.grid_h_inv = float(kf.mfGridElementWidthInv), float(kf.mfGridElementHeightInv)
+        P.nlevels = 8
+        for i, sfv in enumerate(sf):
+            P.scale[i] = float(sfv)
+        P.th = float(th)
+        pts = dict(u=u, v=v, ur=np.zeros(n, f32), level=S["level"], valid=valid, desc=S["md"])
+        bi, bd = oracle_fuse_search(P, np.zeros(16, f32), 0, pts, kf)
+        return np.where((valid != 0) & (bi >= 0) & (bd <= 100), bi, -1), valid
+
+    m1, v1 = direction(S1, already1, R1w, t1w, sR21, t21, S2)
+    m2, v2 = direction(S2, already2, R2w, t2w, sR12, t12, S1)
+    exp = np.where(pre >= 0, pre, -1).astype(np.int32)
+    found = 0
+    for i1 in range(n):
+        if m1[i1] >= 0 and m2[m1[i1]] == i1:
+            exp[i1] = m1[i1] if S2["has"][m1[i1]] else -1   # vpMatches12[i1] = vpMapPoints2[idx2] (NULL if KF2 has none there)
+            found += 1
+    assert raw[0] == found and np.array_equal(raw[1:], exp), f"{(raw[1:] != exp).sum()} entries differ"
+    assert found > 300 and v1.mean() > 0.5 and v2.mean() > 0.5
