@@ -25,6 +25,7 @@ static void run_initialization(int w, int h, const std::vector<cv::KeyPoint>& kL
 static int run_tracking_search(const char* in, const char* out);
 static int run_sim3_projection(const char* in, const char* out);
 static int run_search_by_sim3(const char* in, const char* out);
+static int run_fuse(const char* in, const char* out);
 static void run_bow_search(const std::vector<cv::KeyPoint>& kL, const cv::Mat& dL, const fbow::fBow2& fL,
                            const std::vector<cv::KeyPoint>& kR, const cv::Mat& dR, const fbow::fBow2& fR, const char* out);
 
@@ -32,6 +33,7 @@ int main(int argc, char** argv) {
     if (argc == 4 && std::string(argv[1]) == "track") return run_tracking_search(argv[2], argv[3]);
     if (argc == 4 && std::string(argv[1]) == "sim3") return run_sim3_projection(argv[2], argv[3]);
     if (argc == 4 && std::string(argv[1]) == "sim3b") return run_search_by_sim3(argv[2], argv[3]);
+    if (argc == 4 && std::string(argv[1]) == "fuse") return run_fuse(argv[2], argv[3]);
     if (argc < 6) return 1;
     const int w = atoi(argv[1]), h = atoi(argv[2]);
     std::vector<unsigned char> L = slurp(argv[3], (size_t)w * h), R = slurp(argv[4], (size_t)w * h);
@@ -532,5 +534,114 @@ static int run_search_by_sim3(const char* in, const char* out) {
     }
     fclose(g);
     printf("SearchBySim3 ok: %d found\n", nFound);
+    return 0;
+}
+
+// LocalMapping::SearchInNeighbors (/root/reference/src/LocalMapping.cc:487): matcher.Fuse(pKFi, vpMapPointMatches) through
+// the drop-in template on dumped data.
+// Input: int32 n, nK; float32 th, fx, fy, cx, cy, bf, w, h; Rcw[9], tcw[3], Ow[3]; scale[8], invSigma2[8];
+// points: world[n*3], normal[n*3], dmin[n], dmax[n] f32, level[n], nobs[n] i32, bad[n] u8, desc[n*32];
+// keyframe: keys[nK], uRight[nK] f32, desc[nK*32], kfobs[nK] i32 (observations of the map point at that keypoint, -1 = none).
+// Output: nFused, then per point: action (0 none, 1 pMP replaced by the keyframe's point, 2 keyframe's point replaced by
+// pMP, 3 added as a new observation, 4 counted but the keyframe's point is bad) and the keypoint index.
+namespace run_fuse_ns {
+struct KeyFrame;
+struct MapPoint {
+    const float *w, *nrm;
+    float dmin, dmax;
+    int level, nobs;
+    bool bad;
+    unsigned char* d;
+    int action, where;
+    bool isBad() { return bad; }
+    cv::Mat GetWorldPos() { return cv::Mat(3, 1, CV_32FC1, (void*)w, sizeof(float)); }
+    cv::Mat GetNormal() { return cv::Mat(3, 1, CV_32FC1, (void*)nrm, sizeof(float)); }
+    float GetMinDistanceInvariance() { return dmin; }
+    float GetMaxDistanceInvariance() { return dmax; }
+    int PredictScale(float, KeyFrame*) { return level; }
+    cv::Mat GetDescriptor() { return cv::Mat(1, 32, CV_8UC1, d, 32); }
+    int Observations() { return nobs; }
+    bool IsInKeyFrame(KeyFrame*) { return false; }
+    void Replace(MapPoint*) { action = -1; }   // marks "this point was replaced"; the caller records who replaced whom
+    void AddObservation(KeyFrame*, int idx) { action = 3; where = idx; }
+};
+struct KeyFrame {
+    int N;
+    float fx, fy, cx, cy, mbf, mnMinX, mnMaxX, mnMinY, mnMaxY, mfGridElementWidthInv, mfGridElementHeightInv;
+    std::vector<float> mvScaleFactors, mvInvLevelSigma2, mvuRight;
+    std::vector<cv::KeyPoint> mvKeysUn;
+    cv::Mat mDescriptors;
+    float R[9], t[3], O[3];
+    std::vector<MapPoint*> mps;
+    cv::Mat GetRotation() { return cv::Mat(3, 3, CV_32FC1, R, 3 * sizeof(float)); }
+    cv::Mat GetTranslation() { return cv::Mat(3, 1, CV_32FC1, t, sizeof(float)); }
+    cv::Mat GetCameraCenter() { return cv::Mat(3, 1, CV_32FC1, O, sizeof(float)); }
+    bool IsInImage(const float& x, const float& y) const { return x >= mnMinX && x < mnMaxX && y >= mnMinY && y < mnMaxY; }
+    MapPoint* GetMapPoint(int i) { return mps[i]; }
+    void AddMapPoint(MapPoint* p, int i) { mps[i] = p; }
+};
+}  // namespace run_fuse_ns
+static int run_fuse(const char* in, const char* out) {
+    using namespace run_fuse_ns;
+    FILE* f = fopen(in, "rb");
+    if (!f) return 2;
+    int hdr[2];
+    float cam[8], pose[15], sc[8], is2[8];
+    if (fread(hdr, 4, 2, f) != 2 || fread(cam, 4, 8, f) != 8 || fread(pose, 4, 15, f) != 15 || fread(sc, 4, 8, f) != 8 ||
+        fread(is2, 4, 8, f) != 8)
+        return 2;
+    const int n = hdr[0], nK = hdr[1];
+    std::vector<float> world((size_t)n * 3), normal((size_t)n * 3), dmin(n), dmax(n), uR(nK);
+    std::vector<int> level(n), nobs(n), kfobs(nK);
+    std::vector<unsigned char> bad(n), dp((size_t)n * 32), dk((size_t)nK * 32);
+    std::vector<cv::KeyPoint> keys(nK);
+    const bool ok = fread(world.data(), 4, world.size(), f) == world.size() && fread(normal.data(), 4, normal.size(), f) == normal.size() &&
+                    fread(dmin.data(), 4, n, f) == (size_t)n && fread(dmax.data(), 4, n, f) == (size_t)n &&
+                    fread(level.data(), 4, n, f) == (size_t)n && fread(nobs.data(), 4, n, f) == (size_t)n &&
+                    fread(bad.data(), 1, n, f) == (size_t)n && fread(dp.data(), 1, dp.size(), f) == dp.size() &&
+                    fread(keys.data(), sizeof(cv::KeyPoint), nK, f) == (size_t)nK && fread(uR.data(), 4, nK, f) == (size_t)nK &&
+                    fread(dk.data(), 1, dk.size(), f) == dk.size() && fread(kfobs.data(), 4, nK, f) == (size_t)nK;
+    fclose(f);
+    if (!ok) return 2;
+    KeyFrame kf;
+    kf.N = nK;
+    kf.fx = cam[1]; kf.fy = cam[2]; kf.cx = cam[3]; kf.cy = cam[4]; kf.mbf = cam[5];
+    kf.mnMinX = 0; kf.mnMaxX = cam[6]; kf.mnMinY = 0; kf.mnMaxY = cam[7];
+    kf.mfGridElementWidthInv = 64.0f / (kf.mnMaxX - kf.mnMinX);
+    kf.mfGridElementHeightInv = 48.0f / (kf.mnMaxY - kf.mnMinY);
+    kf.mvScaleFactors.assign(sc, sc + 8); kf.mvInvLevelSigma2.assign(is2, is2 + 8); kf.mvuRight = uR;
+    kf.mvKeysUn = keys;
+    kf.mDescriptors = cv::Mat(nK, 32, CV_8UC1, dk.data(), 32);
+    for (int i = 0; i < 9; i++) kf.R[i] = pose[i];
+    for (int i = 0; i < 3; i++) { kf.t[i] = pose[9 + i]; kf.O[i] = pose[12 + i]; }
+    std::vector<MapPoint> own(nK), pts(n);
+    kf.mps.assign(nK, nullptr);
+    static float zero3[3] = {0, 0, 0};
+    for (int i = 0; i < nK; i++)
+        if (kfobs[i] >= 0) {
+            MapPoint p = {zero3, zero3, 0, 0, 0, kfobs[i] % 1000, kfobs[i] >= 1000, nullptr, 0, -1};
+            own[i] = p;
+            kf.mps[i] = &own[i];
+        }
+    std::vector<MapPoint*> vp(n);
+    for (int i = 0; i < n; i++) {
+        MapPoint p = {world.data() + 3 * (size_t)i, normal.data() + 3 * (size_t)i, dmin[i], dmax[i], level[i], nobs[i], bad[i] != 0,
+                      dp.data() + (size_t)i * 32, 0, -1};
+        pts[i] = p;
+        vp[i] = &pts[i];
+    }
+    ORB_SLAM2::ORBmatcher matcher(0.6f, true);
+    const int nFused = matcher.Fuse(&kf, vp, cam[0]);
+    FILE* g = fopen(out, "wb");
+    fwrite(&nFused, 4, 1, g);
+    for (int i = 0; i < n; i++) {
+        int rec[2] = {pts[i].action, pts[i].where};
+        fwrite(rec, 4, 2, g);
+    }
+    int nrep = 0;
+    for (int i = 0; i < nK; i++) nrep += (kf.mps[i] == &own[i] && own[i].action == -1);
+    fwrite(&nrep, 4, 1, g);
+    fclose(g);
+    printf("Fuse ok: %d fused\n", nFused);
     return 0;
 }

@@ -378,3 +378,116 @@ def test_cpp_search_by_sim3_dropin(tmp_path):
             found += 1
     assert raw[0] == found and np.array_equal(raw[1:], exp), f"{(raw[1:] != exp).sum()} entries differ"
     assert found > 300 and v1.mean() > 0.5 and v2.mean() > 0.5
+
+
+def test_cpp_fuse_dropin(tmp_path):
+    """The C++ template ORBmatcher::Fuse(KeyFrame*, vpMapPoints, th) (LocalMapping::SearchInNeighbors) run for real:
+    projection and MapPoint gates on the host (restated in numpy with the same float / double steps), KeyFrame window
+    search with the octave and chi-square gates on the device, Replace / AddObservation / AddMapPoint in point order."""
+    from orbslam2_b200.synth import synth_tracking_pair
+    from oracle_lib import oracle_fuse_search
+    from orbslam2_b200 import _lib
+    exe = _build_exe(tmp_path)
+    rng = np.random.default_rng(321)
+    f32, f64 = np.float32, np.float64
+    kf, _ = synth_tracking_pair(1500, 55, stereo=True, motion=(0.03, 0.01, 0.05))
+    w, h, th = 640, 480, f32(3.0)
+    ang = -0.03
+    R = np.array([[np.cos(ang), 0, np.sin(ang)], [0, 1, 0], [-np.sin(ang), 0, np.cos(ang)]])
+    Rcw = R.astype(f32); tcw = np.array([0.05, 0.02, -0.1], f32)
+    Ow = np.array([-f32(sum(f64(Rcw[c, r]) * f64(tcw[c]) for c in range(3))) for r in range(3)], f32)
+    n = 2200
+    src = rng.integers(0, kf.N, n)
+    dupmask = rng.random(n) < 0.35
+    src[dupmask] = src[rng.integers(0, 80, dupmask.sum())]          # several points aim at the same keypoint
+    z = rng.uniform(2, 10, n)
+    pc = np.stack([(kf.mvKeysUn["x"][src] + rng.normal(0, 0.7, n) - float(kf.cx)) / float(kf.fx) * z,
+                   (kf.mvKeysUn["y"][src] + rng.normal(0, 0.7, n) - float(kf.cy)) / float(kf.fy) * z, z], 1)
+    pc[rng.random(n) < 0.04, 2] *= -1
+    world = ((pc - tcw.astype(f64)) @ R).astype(f32)
+    bits = np.unpackbits(kf.mDescriptors[src], axis=1)
+    for _ in range(8):
+        bits[np.arange(n), rng.integers(0, 256, n)] ^= 1
+    desc = np.packbits(bits, axis=1)
+    level = np.clip(kf.mvKeysUn["octave"][src] + rng.integers(0, 2, n), 0, 7).astype(np.int32)
+    bad = (rng.random(n) < 0.05).astype(np.uint8)
+    nobs = rng.integers(1, 12, n).astype(np.int32)
+    dmin = rng.uniform(0.5, 3.0, n).astype(f32); dmax = rng.uniform(6.0, 14.0, n).astype(f32)
+    normal = np.zeros((n, 3), f32)
+    for i in range(n):
+        po = (world[i] - Ow).astype(f64)
+        nv = po / np.linalg.norm(po)
+        normal[i] = (-nv if rng.random() < 0.08 else nv).astype(f32)
+    sf = np.asarray(kf.mvScaleFactors[:8], f32)
+    is2 = (f32(1.0) / (sf * sf)).astype(f32)
+    kfobs = np.where(rng.random(kf.N) < 0.6, rng.integers(0, 12, kf.N) + 1000 * (rng.random(kf.N) < 0.1), -1).astype(np.int32)
+    # the template's host half (include/dropin/ORBmatcher.h Fuse) = src/ORBmatcher.cc:855-905
+    u = np.zeros(n, f32); v = np.zeros(n, f32); ur = np.zeros(n, f32); valid = np.zeros(n, np.uint8)
+    for i in range(n):
+        if bad[i]:
+            continue
+        wv = world[i]
+        p = [f32(f32(sum(f64(Rcw[r, c]) * f64(wv[c]) for c in range(3))) + tcw[r]) for r in range(3)]
+        if p[2] < 0:
+            continue
+        invz = f32(f32(1) / p[2])
+        uu = f32(f32(kf.fx * f32(p[0] * invz)) + kf.cx); vv = f32(f32(kf.fy * f32(p[1] * invz)) + kf.cy)
+        if not (0 <= uu < w and 0 <= vv < h):
+            continue
+        po = [f32(wv[k] - Ow[k]) for k in range(3)]
+        dist = f32(np.sqrt(sum(f64(x) * f64(x) for x in po)))
+        if dist < dmin[i] or dist > dmax[i]:
+            continue
+        if sum(f64(po[k]) * f64(normal[i, k]) for k in range(3)) < 0.5 * f64(dist):
+            continue
+        u[i], v[i], ur[i], valid[i] = uu, vv, f32(uu - f32(kf.mbf * invz)), 1
+    with open(tmp_path / "fuse.bin", "wb") as f:
+        f.write(np.array([n, kf.N], np.int32).tobytes())
+        f.write(np.array([th, kf.fx, kf.fy, kf.cx, kf.cy, kf.mbf, w, h], f32).tobytes())
+        f.write(Rcw.tobytes()); f.write(tcw.tobytes()); f.write(Ow.tobytes()); f.write(sf.tobytes()); f.write(is2.tobytes())
+        for a in (world, normal, dmin, dmax, level, nobs, bad, desc):
+            f.write(np.ascontiguousarray(a).tobytes())
+        f.write(kf.mvKeysUn.tobytes()); f.write(np.ascontiguousarray(kf.mvuRight, f32).tobytes())
+        f.write(kf.mDescriptors.tobytes()); f.write(kfobs.tobytes())
+    r = subprocess.run([exe, "fuse", str(tmp_path / "fuse.bin"), str(tmp_path / "fuse_out.bin")], capture_output=True, text=True,
+                       timeout=120)
+    assert r.returncode == 0, r.stdout + r.stderr
+    raw = np.fromfile(tmp_path / "fuse_out.bin", np.int32)
+    P = _lib.ProjParams()
+    P.minX, P.maxX, P.minY, P.maxY = 0, w, 0, h
+    P.grid_w_inv, P.grid_h_inv = float(kf.mfGridElementWidthInv), float(kf.mfGridElementHeightInv)
+    P.nlevels = 8
+    for i, sfv in enumerate(sf):
+        P.scale[i] = float(sfv)
+    P.th = float(th)
+    inv16 = np.zeros(16, f32); inv16[:8] = is2
+    bi, bd = oracle_fuse_search(P, inv16, 1, dict(u=u, v=v, ur=ur, level=level, valid=valid, desc=desc), kf)
+    # the mutation loop in point order (src/ORBmatcher.cc:948-967)
+    action = np.zeros(n, np.int32); where = np.full(n, -1, np.int32)
+    holder = {i: ("own", i) for i in range(kf.N) if kfobs[i] >= 0}
+    own_replaced = set()
+    fused = 0
+    for i in range(n):
+        if not valid[i] or bad[i] or bi[i] < 0 or bd[i] > 50:
+            continue
+        idx = int(bi[i])
+        if idx in holder:
+            kind, j = holder[idx]
+            hbad = (kfobs[j] >= 1000) if kind == "own" else bool(bad[j])
+            hobs = (kfobs[j] % 1000) if kind == "own" else nobs[j]
+            if not hbad:
+                if hobs > nobs[i]:
+                    action[i] = -1                         # pMP->Replace(pMPinKF)
+                elif kind == "own":
+                    own_replaced.add(j)                    # pMPinKF->Replace(pMP)
+                else:
+                    action[j] = -1
+        else:
+            action[i], where[i] = 3, idx                   # AddObservation + AddMapPoint
+            holder[idx] = ("pt", i)
+        fused += 1
+    assert raw[0] == fused, (raw[0], fused)
+    got = raw[1:1 + 2 * n].reshape(n, 2)
+    assert np.array_equal(got[:, 0], action) and np.array_equal(got[:, 1], where)
+    assert raw[1 + 2 * n] == len(own_replaced)
+    assert fused > 300 and (action == 3).sum() > 50 and (action == -1).sum() > 20 and len(own_replaced) > 20
