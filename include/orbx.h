@@ -143,6 +143,12 @@ int orbm_set_train(orbm_t* m, const uint8_t* t, int nt);
 /* Brute-force 2-NN of every query against the train set: i1 = index of the best (lowest index wins ties),
  * d1 = its distance, d2 = second-smallest distance with multiplicity (256 if nt < 2). t == NULL reuses set_train. */
 int orbm_knn2(orbm_t* m, const uint8_t* q, int nq, const uint8_t* t, int nt, int32_t* i1, uint16_t* d1, uint16_t* d2);
+/* Which kernel orbm_knn2 runs. 0 (default): the tensor-core kernel (tcgen05.mma kind::i8: Hamming distance as a
+ * binary GEMM, |q| + |t| - 2<q,t>; csrc/orbx_knn_tc.cuh) when nq * nt >= 2^24 and the train set holds a full 256-row
+ * tile, else the POPC kernel; 1: POPC kernel only; 2: tensor cores whenever a full tile exists. Results are
+ * bit-identical on every path. orbm_last_knn_path: 1 = POPC, 2 = tensor cores (+ POPC for the < 256-row remainder). */
+int orbm_set_knn_mode(orbm_t* m, int mode);
+int orbm_last_knn_path(orbm_t* m);
 /* Windowed search: query a scans candidates cand_idx[cand_off[a] .. cand_off[a+1]) in list order, skipping entries
  * with cand_skip[c] != 0 (cand_skip may be NULL). Outputs best/second index (-1 = none) and distance (256 = none). */
 int orbm_window_search(orbm_t* m, const uint8_t* q, int nq, const int32_t* cand_off, const int32_t* cand_idx,

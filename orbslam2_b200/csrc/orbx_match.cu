@@ -2,6 +2,8 @@
 //
 // K7  k_knn2           brute-force 2-NN over a train matrix   (ref: inner scan of ORBmatcher::SearchByFboW,
 //                                                              /root/reference/src/ORBmatcher.cc:195-229)
+//                      small problems and the < 256-row train remainder; the bulk runs on the tensor cores:
+// K7t k_knn_tc         orbx_knn_tc.cuh (tcgen05.mma kind::i8 + TMEM + TMA), bit-identical results
 // K7m k_knn2_merge     ordered merge of train-split partials (lowest index wins ties, as a sequential scan would)
 // K8  k_window_search  CSR candidate lists, one warp per query (ref: every ORBmatcher search loop)
 // K8d k_distance       batched DescriptorDistance              (ref: src/ORBmatcher.cc:1643-1659)
@@ -9,9 +11,12 @@
 // K10 k_stereo_cut     median outlier cut                      (ref: src/Frame.cc:628-641)
 #include <algorithm>
 #include <climits>
+#include <cmath>
+#include <mutex>
 #include <vector>
 
 #include "orbx_internal.cuh"
+#include "orbx_knn_tc.cuh"
 
 struct orbx_handle;
 struct OrbxView {
@@ -40,7 +45,7 @@ __device__ __forceinline__ void best2_push(Best2& b, int d, int j) {
 }
 
 __global__ void __launch_bounds__(KNN_THREADS) k_knn2(const uint4* __restrict__ q, int nq, const uint4* __restrict__ t,
-                                                      int nt, int chunk, int4* __restrict__ partial,
+                                                      int nt, int chunk, int idxBase, int4* __restrict__ partial,
                                                       int32_t* __restrict__ i1, uint16_t* __restrict__ d1,
                                                       uint16_t* __restrict__ d2) {
     __shared__ uint4 tile[KNN_TILE * 2];
@@ -75,6 +80,7 @@ __global__ void __launch_bounds__(KNN_THREADS) k_knn2(const uint4* __restrict__ 
     for (int k = 0; k < KNN_QPT; k++) {
         const int qi = qbase + k * KNN_THREADS + tid;
         if (qi >= nq) continue;
+        if (b[k].i1 >= 0) b[k].i1 += idxBase;
         if (partial) partial[(size_t)split * nq + qi] = make_int4(b[k].d1, b[k].i1, b[k].d2, 0);
         else {
             i1[qi] = b[k].i1;
@@ -374,6 +380,12 @@ struct orbm_handle {
     uint8_t* dQ = nullptr; size_t qCap = 0;
     uint8_t* dB = nullptr; size_t bCap = 0;
     int4* dPartial = nullptr; size_t partialCap = 0;
+    // tensor-core 2-NN (orbx_knn_tc.cuh): int8 expansions of the queries (per call) and of the resident train set
+    uint8_t* dAm = nullptr; size_t amCap = 0; uint8_t* dAe = nullptr; size_t aeCap = 0;
+    uint8_t* dBm = nullptr; size_t bmCap = 0; uint8_t* dBe = nullptr; size_t beCap = 0;
+    bool trainExpanded = false;
+    int knnMode = 0;     // 0 auto, 1 POPC kernel only, 2 tensor-core kernel whenever a full tile exists
+    int lastKnnPath = 0; // 1 POPC, 2 tensor cores (+ POPC remainder)
     int32_t* dI1 = nullptr; int32_t* dI2 = nullptr; uint16_t* dD1 = nullptr; uint16_t* dD2 = nullptr; size_t outCap = 0;
     int* dOff = nullptr; size_t offCap = 0;
     int* dIdx = nullptr; size_t idxCap = 0;
@@ -425,6 +437,7 @@ extern "C" int orbm_destroy(orbm_t* m) {
     cudaSetDevice(m->device);
     cudaStreamSynchronize(m->stream);
     if (!m->trainAdopted) cudaFree(m->dTrain);
+    cudaFree(m->dAm); cudaFree(m->dAe); cudaFree(m->dBm); cudaFree(m->dBe);
     cudaFree(m->dQ); cudaFree(m->dB); cudaFree(m->dPartial); cudaFree(m->dI1); cudaFree(m->dI2); cudaFree(m->dD1);
     cudaFree(m->dD2); cudaFree(m->dOff); cudaFree(m->dIdx); cudaFree(m->dSkip); cudaFree(m->dWs); cudaFree(m->dCand); if (m->hRes) cudaFreeHost(m->hRes); if (m->hFlags) cudaFreeHost(m->hFlags); if (m->hIn) cudaFreeHost(m->hIn);
     cudaStreamDestroy(m->stream);
@@ -465,7 +478,28 @@ extern "C" int orbm_set_train(orbm_t* m, const uint8_t* t, int nt) {
         CK(cudaMemcpyAsync(m->dTrain, t, (size_t)nt * 32, cudaMemcpyHostToDevice, m->stream));
     }
     m->nTrain = nt;
+    m->trainExpanded = false;
     return ORBX_OK;
+}
+
+extern "C" int orbm_set_knn_mode(orbm_t* m, int mode) {
+    if (!m || mode < 0 || mode > 2) FAIL(ORBX_EINVAL, "knn mode must be 0 (auto), 1 (POPC) or 2 (tensor cores)");
+    m->knnMode = mode;
+    return ORBX_OK;
+}
+extern "C" int orbm_last_knn_path(orbm_t* m) { return m ? m->lastKnnPath : 0; }
+
+static ktc_encode_fn knn_encode() {
+    static ktc_encode_fn fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = (ktc_encode_fn)p;
+    });
+    return fn;
 }
 
 // stage a caller array on the device if it is host memory
@@ -514,6 +548,59 @@ extern "C" int orbm_knn2(orbm_t* m, const uint8_t* q, int nq, const uint8_t* t, 
         o1 = m->dI1; od1 = m->dD1; od2 = m->dD2;
     }
     const int qblocks = (nq + KNN_THREADS * KNN_QPT - 1) / (KNN_THREADS * KNN_QPT);
+    const int nTiles = nt / KTC_N;
+    const bool useTc = m->knnMode != 1 && nTiles >= 1 && (m->knnMode == 2 || (size_t)nq * (size_t)nt >= ((size_t)1 << 24));
+    if (useTc) {
+        // ---- tensor-core path: full 256-row train tiles through k_knn_tc, the remainder through k_knn2, ordered merge
+        ktc_encode_fn enc = knn_encode();
+        if (!enc) FAIL(ORBX_ECUDA, "cuTensorMapEncodeTiled entry point not available from the driver");
+        const int qRows = (nq + KTC_M - 1) / KTC_M * KTC_M, qTiles = qRows / KTC_M;
+        const int bRows = nTiles * KTC_N, tail = nt - bRows;
+        if ((rc = ensure(m->dAm, m->amCap, (size_t)qRows * KTC_KMAIN))) return rc;
+        if ((rc = ensure(m->dAe, m->aeCap, (size_t)qRows * KTC_KEXT))) return rc;
+        if (!m->trainExpanded) {
+            if ((rc = ensure(m->dBm, m->bmCap, (size_t)bRows * KTC_KMAIN))) return rc;
+            if ((rc = ensure(m->dBe, m->beCap, (size_t)bRows * KTC_KEXT))) return rc;
+            k_knn_expand<<<(bRows * 8 + 255) / 256, 256, 0, m->stream>>>((const uint32_t*)m->dTrain, bRows, bRows, 0, m->dBm,
+                                                                         m->dBe);
+            m->launches++;
+            m->trainExpanded = true;
+        }
+        k_knn_expand<<<(qRows * 8 + 255) / 256, 256, 0, m->stream>>>((const uint32_t*)dq, nq, qRows, 1, m->dAm, m->dAe);
+        m->launches++;
+        // train splits: rows inside a split must fit the 22-bit index of the running keys; beyond that, pick the count
+        // that fills whole waves of one CTA per SM
+        const int minSplits = (nTiles + 16383) / 16384;
+        int splits = minSplits;
+        double bestScore = -1;
+        for (int sp = minSplits; sp <= 64 && (sp == minSplits || nTiles / sp >= 32); sp++) {
+            const int tps = (nTiles + sp - 1) / sp, real = (nTiles + tps - 1) / tps;
+            const double ctas = (double)qTiles * real, waves = ctas / m->smCount;
+            const double eff = waves / ceil(waves);
+            const double score = eff - 0.25 / (waves + 1) - 0.001 * real;   // prefer many short waves, few partials
+            if (score > bestScore) {
+                bestScore = score;
+                splits = sp;
+            }
+        }
+        const int tilesPerSplit = (nTiles + splits - 1) / splits;
+        splits = (nTiles + tilesPerSplit - 1) / tilesPerSplit;
+        const int parts = splits + (tail > 0 ? 1 : 0);
+        if ((rc = ensure(m->dPartial, m->partialCap, (size_t)parts * nq))) return rc;
+        const int lrc = ktc_launch(enc, m->dAm, m->dAe, qRows, m->dBm, m->dBe, nTiles, nq, tilesPerSplit, splits,
+                                   m->dPartial, m->stream);
+        if (lrc) FAIL(ORBX_ECUDA, "k_knn_tc launch failed at step %d: %s", lrc, cudaGetErrorString(cudaGetLastError()));
+        m->launches++;
+        if (tail > 0) {
+            k_knn2<<<dim3(qblocks, 1), KNN_THREADS, 0, m->stream>>>((const uint4*)dq, nq, (const uint4*)m->dTrain + 2 * (size_t)bRows,
+                                                                    tail, (tail + KNN_TILE - 1) / KNN_TILE * KNN_TILE, bRows,
+                                                                    m->dPartial + (size_t)splits * nq, nullptr, nullptr, nullptr);
+            m->launches++;
+        }
+        k_knn2_merge<<<(nq + 255) / 256, 256, 0, m->stream>>>(m->dPartial, nq, parts, o1, od1, od2);
+        m->launches++;
+        m->lastKnnPath = 2;
+    } else {
     // split the train set so that the grid fills the machine for small query counts
     int splits = 1;
     const int target = m->smCount * 8;
@@ -526,12 +613,14 @@ extern "C" int orbm_knn2(orbm_t* m, const uint8_t* q, int nq, const uint8_t* t, 
         if ((rc = ensure(m->dPartial, m->partialCap, (size_t)splits * nq))) return rc;
         partial = m->dPartial;
     }
-    k_knn2<<<dim3(qblocks, splits), KNN_THREADS, 0, m->stream>>>((const uint4*)dq, nq, (const uint4*)m->dTrain, nt, chunk,
+    k_knn2<<<dim3(qblocks, splits), KNN_THREADS, 0, m->stream>>>((const uint4*)dq, nq, (const uint4*)m->dTrain, nt, chunk, 0,
                                                                  partial, o1, od1, od2);
     m->launches++;
     if (splits > 1) {
         k_knn2_merge<<<(nq + 255) / 256, 256, 0, m->stream>>>(partial, nq, splits, o1, od1, od2);
         m->launches++;
+    }
+    m->lastKnnPath = 1;
     }
     CK(cudaGetLastError());
     if (m->outSpace == ORBX_MEM_HOST) {

@@ -62,6 +62,14 @@ class ORBmatcher:
         self._train = t  # keep alive
         _lib.check(self._L.orbm_set_train(self._h, _ptr(t), int(t.shape[0])))
 
+    def set_knn_mode(self, mode):
+        """0 auto, 1 POPC kernel only, 2 tensor-core kernel (tcgen05) whenever a full 256-row train tile exists."""
+        _lib.check(self._L.orbm_set_knn_mode(self._h, int(mode)))
+
+    def last_knn_path(self):
+        """1 = POPC kernel, 2 = tensor-core kernel (+ POPC remainder) for the last knn2 call."""
+        return int(self._L.orbm_last_knn_path(self._h))
+
     def knn2(self, q, t=None):
         """(i1, d1, d2) per query; lowest train index wins ties; d2 counts multiplicity."""
         if _is_torch(q):

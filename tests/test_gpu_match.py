@@ -54,6 +54,55 @@ def test_knn2_split_train_large(ob):
     assert np.array_equal(i1, o1) and np.array_equal(d1, e1) and np.array_equal(d2, e2)
 
 
+@pytest.mark.parametrize("nt,nq", [(256, 1), (257, 130), (511, 128), (512, 129), (1000, 300), (20000, 1500),
+                                   (70001, 777)])
+def test_knn2_tensor_core_path_vs_oracle(ob, nt, nq):
+    """orbm_knn2 forced onto the tcgen05 kernel (full 256-row tiles) + the POPC remainder + the ordered merge, against
+    the sequential scan: indices (lowest wins ties), distances and second-best with multiplicity, bit-exact; the same
+    call on the POPC-only path must return the same arrays."""
+    m = ob.ORBmatcher(); P = OraclePrims()
+    t, q = synth_descriptors(nt, nq, seed=nt + 1, dup=min(100, nt // 4))
+    # ties that straddle tile and parity boundaries, all-zero / all-one rows (distance 0 and 256)
+    t[0] = 0; t[min(nt - 1, 255)] = 0; t[nt - 1] = 0
+    q[0] = 0
+    if nq > 1:
+        q[1] = 255
+    if nt > 300:
+        t[256] = t[3]; t[257] = t[3]
+    m.set_knn_mode(2)
+    i1, d1, d2 = m.knn2(q, t)
+    assert m.last_knn_path() == 2
+    o1, e1, e2 = P.knn2(q, t, popcnt=True)
+    assert np.array_equal(i1, o1) and np.array_equal(d1, e1) and np.array_equal(d2, e2)
+    m.set_knn_mode(1)
+    j1, f1, f2 = m.knn2(q, t)
+    assert m.last_knn_path() == 1
+    assert np.array_equal(i1, j1) and np.array_equal(d1, f1) and np.array_equal(d2, f2)
+
+
+def test_knn2_tensor_core_resident_train_and_device_buffers(ob):
+    """Resident train set (expanded once), several query batches, device tensors in and out; auto mode picks the
+    tensor-core kernel at this size."""
+    import torch
+    m = ob.ORBmatcher(); P = OraclePrims()
+    t, q = synth_descriptors(150000, 3000, seed=21, dup=500)
+    dt = torch.from_numpy(t).cuda()
+    m.set_train(dt)
+    for lo, hi in ((0, 3000), (100, 1300), (2999, 3000)):
+        dq = torch.from_numpy(q[lo:hi].copy()).cuda()
+        i1, d1, d2 = m.knn2(dq)
+        assert m.last_knn_path() == (2 if (hi - lo) * len(t) >= 1 << 24 else 1)
+        o1, e1, e2 = P.knn2(q[lo:hi], t, popcnt=True)
+        assert np.array_equal(i1.cpu().numpy(), o1)
+        assert np.array_equal(d1.cpu().numpy().view(np.uint16), e1) and np.array_equal(d2.cpu().numpy().view(np.uint16), e2)
+    # a new train set must invalidate the expansion
+    t2 = t[::-1].copy()
+    m.set_train(torch.from_numpy(t2).cuda())
+    i1, d1, d2 = m.knn2(torch.from_numpy(q[:500].copy()).cuda())
+    o1, e1, e2 = P.knn2(q[:500], t2, popcnt=True)
+    assert np.array_equal(i1.cpu().numpy(), o1) and np.array_equal(d2.cpu().numpy().view(np.uint16), e2)
+
+
 def test_ratio_rule(ob):
     m = ob.ORBmatcher(nnratio=0.7)
     t, q = synth_descriptors(20000, 2000, seed=5)
