@@ -123,7 +123,8 @@ public:
             for (int c = 0; c < 3; c++) P.Rcw[3 * r + c] = Tcw.template at<float>(r, c);
             P.tcw[r] = Tcw.template at<float>(r, 3);
         }
-        // twc = -Rcw.t()*tcw; tlc = Rlw*twc + tlw (src/ORBmatcher.cc:1334-1341; CV_32F products accumulate in double)
+        // twc = -Rcw.t()*tcw; tlc = Rlw*twc + tlw (src/ORBmatcher.cc:1334-1341). cv::gemm evaluates a transposed-operand
+        // product with a double accumulator and a plain 3x3 * 3x1 product in float (see row3 / gemm_add below).
         float twc[3], tlcz;
         for (int r = 0; r < 3; r++) {
             double a = 0;
@@ -131,9 +132,8 @@ public:
             twc[r] = (float)a;
         }
         {
-            double a = 0;
-            for (int k = 0; k < 3; k++) a += (double)Tlw.template at<float>(2, k) * (double)twc[k];
-            tlcz = (float)a + Tlw.template at<float>(2, 3);
+            const float Rl2[3] = {Tlw.template at<float>(2, 0), Tlw.template at<float>(2, 1), Tlw.template at<float>(2, 2)};
+            tlcz = gemm_add(row3(Rl2, twc), Tlw.template at<float>(2, 3));
         }
         P.forward = (tlcz > CurrentFrame.mb && !bMono) ? 1 : 0;
         P.backward = (-tlcz > CurrentFrame.mb && !bMono) ? 1 : 0;
@@ -291,10 +291,9 @@ public:
             const cv::Mat p3Dw = pMP->GetWorldPos();
             float pc[3], w[3];
             for (int k = 0; k < 3; k++) w[k] = p3Dw.template at<float>(k, 0);
-            for (int r = 0; r < 3; r++) {  // Rcw*p3Dw + tcw: CV_32F product = double accumulation rounded once
-                double acc = 0;
-                for (int c = 0; c < 3; c++) acc += (double)Rcw.template at<float>(r, c) * (double)w[c];
-                pc[r] = (float)acc + tcw.template at<float>(r, 0);
+            for (int r = 0; r < 3; r++) {  // Rcw*p3Dw + tcw (cv::gemm small-matrix path, see row3)
+                const float Rr[3] = {Rcw.template at<float>(r, 0), Rcw.template at<float>(r, 1), Rcw.template at<float>(r, 2)};
+                pc[r] = gemm_add(row3(Rr, w), tcw.template at<float>(r, 0));
             }
             if (pc[2] < 0.0f) continue;
             const float invz = 1 / pc[2];
@@ -455,11 +454,7 @@ public:
                 sR12[3 * r + c] = s12 * R12.at<float>(r, c);
                 sR21[3 * r + c] = inv * R12.at<float>(c, r);
             }
-        for (int r = 0; r < 3; r++) {  // t21 = -sR21*t12
-            double acc = 0;
-            for (int c = 0; c < 3; c++) acc += (double)sR21[3 * r + c] * (double)t12f[c];
-            t21[r] = -(float)acc;
-        }
+        for (int r = 0; r < 3; r++) t21[r] = -row3(sR21 + 3 * r, t12f);  // t21 = -sR21*t12: gemm with alpha = -1
         const std::vector<MapPointT*> vpMapPoints1 = pKF1->GetMapPointMatches(), vpMapPoints2 = pKF2->GetMapPointMatches();
         const int N1 = (int)vpMapPoints1.size(), N2 = (int)vpMapPoints2.size();
         std::vector<uint8_t> already1(N1, 0), already2(N2, 0);
@@ -472,8 +467,8 @@ public:
             }
         }
         std::vector<int> vnMatch1, vnMatch2;
-        sim3_direction(pKF2, vpMapPoints1, already1, R1w, t1w, sR21, t21, th, vnMatch1);  // KF1's points into KF2
-        sim3_direction(pKF1, vpMapPoints2, already2, R2w, t2w, sR12, t12f, th, vnMatch2);  // KF2's points into KF1
+        sim3_direction(pKF2, pKF1, vpMapPoints1, already1, R1w, t1w, sR21, t21, th, vnMatch1);  // KF1's points into KF2
+        sim3_direction(pKF1, pKF1, vpMapPoints2, already2, R2w, t2w, sR12, t12f, th, vnMatch2);  // KF2's points into KF1
         int nFound = 0;
         for (int i1 = 0; i1 < N1; i1++) {
             const int idx2 = vnMatch1[i1];
@@ -593,13 +588,14 @@ public:
     int SearchForTriangulation(KeyFrameT* pKF1, KeyFrameT* pKF2, cv::Mat F12,
                                std::vector<std::pair<size_t, size_t> >& vMatchedPairs, const bool bOnlyStereo) {
         // epipole of KF1's centre in KF2 (:657-664), CV_32F algebra as cv::Mat evaluates it
-        // (R2w*Cw: double accumulation rounded once to float, then the float add of t2w)
+        // (R2w*Cw + t2w: cv::gemm small-matrix path, see row3 / gemm_add)
         const cv::Mat Cw = pKF1->GetCameraCenter(), R2w = pKF2->GetRotation(), t2w = pKF2->GetTranslation();
         float C2[3];
+        float Cwf[3];
+        vec3(Cw, Cwf);
         for (int r = 0; r < 3; r++) {
-            double acc = 0;
-            for (int c = 0; c < 3; c++) acc += (double)R2w.template at<float>(r, c) * (double)Cw.template at<float>(c, 0);
-            C2[r] = (float)acc + t2w.template at<float>(r, 0);
+            const float Rr[3] = {R2w.template at<float>(r, 0), R2w.template at<float>(r, 1), R2w.template at<float>(r, 2)};
+            C2[r] = gemm_add(row3(Rr, Cwf), t2w.template at<float>(r, 0));
         }
         const float invz = 1.0f / C2[2];
         orbm_triangulation T = orbm_triangulation();
@@ -658,13 +654,26 @@ protected:
     static void vec3(const cv::Mat& M, float* t) {
         for (int r = 0; r < 3; r++) t[r] = M.at<float>(r, 0);
     }
-    // y = A*x + b as cv::Mat CV_32F evaluates it: the row's three products accumulate in double, one rounding, float add
+    // How OpenCV evaluates the reference's CV_32F matrix expressions (cv::gemm, core/src/matmul.dispatch.cpp; pinned
+    // against the real library by tests/golden/cv2_matops.npz and against the unmodified ORBmatcher.cc by the scene tests):
+    //   * A*x (+ b), A 3x3, x 3x1, no transpose flag: the small-matrix path — the row's three products are formed and
+    //     summed left to right IN FLOAT (no fused multiply-add), then d = (float)((double)t*alpha + (double)b*beta);
+    //   * A.t()*x: the generic path — double accumulator, d = (float)(s*alpha);
+    //   * Mat::dot, cv::norm: double accumulators.
+    static float mul_rn(float a, float b) {  // a float product that the compiler cannot fuse into the following add
+        volatile float p = a * b;
+        return p;
+    }
+    static float row3(const float* a, const float* x) {
+        float t = mul_rn(a[0], x[0]);
+        t = t + mul_rn(a[1], x[1]);
+        t = t + mul_rn(a[2], x[2]);
+        return t;
+    }
+    static float gemm_add(float t, float c) { return (float)((double)t + (double)c); }
+    // y = A*x + b
     static void mul_add(const float* A, const float* x, const float* b, float* y) {
-        for (int r = 0; r < 3; r++) {
-            double acc = 0;
-            for (int c = 0; c < 3; c++) acc += (double)A[3 * r + c] * (double)x[c];
-            y[r] = (float)acc + b[r];
-        }
+        for (int r = 0; r < 3; r++) y[r] = gemm_add(row3(A + 3 * r, x), b[r]);
     }
     template <class KeyFrameT>
     static orbm_proj_params kf_grid_params(KeyFrameT* pKF, float th) {
@@ -729,10 +738,11 @@ protected:
     // One direction of SearchBySim3 (:1140-1218 / :1221-1299): the points of the source keyframe go through their own
     // camera pose (Rsw, tsw) and the relative Sim3 (sR, t) into the destination keyframe, whose grid is searched.
     template <class KeyFrameT, class MapPointT>
-    int sim3_direction(KeyFrameT* pDst, const std::vector<MapPointT*>& pts, const std::vector<uint8_t>& already, const float* Rsw,
+    int sim3_direction(KeyFrameT* pDst, KeyFrameT* pIntr, const std::vector<MapPointT*>& pts, const std::vector<uint8_t>& already, const float* Rsw,
                        const float* tsw, const float* sR, const float* t, float th, std::vector<int>& vnMatch) {
         const int n = (int)pts.size(), nK = (int)pDst->mvKeysUn.size();
-        const float fx = pDst->fx, fy = pDst->fy, cx = pDst->cx, cy = pDst->cy;
+        // both directions project with pKF1's intrinsics (src/ORBmatcher.cc:1101-1104)
+        const float fx = pIntr->fx, fy = pIntr->fy, cx = pIntr->cx, cy = pIntr->cy;
         std::vector<float> u(n, 0.f), v(n, 0.f), ur(n, 0.f), invSigma2(ORBX_MAX_LEVELS, 0.f);
         std::vector<int32_t> lvl(n, 0);
         std::vector<uint8_t> valid(n, 0), desc((size_t)n * 32, 0);

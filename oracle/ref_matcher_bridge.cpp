@@ -96,3 +96,28 @@ void refm_distinctive_descriptors(const uint8_t* desc, const int32_t* off, int n
 }
 
 }  // extern "C"
+
+// The cv::Mat expression forms the reference sources use, evaluated through oracle/shim_matcher/cvmat_shim.hpp, so that
+// tests/test_cpu_refmatcher.py can compare the shim with the real OpenCV (tests/golden/cv2_matops.npz, made with cv2).
+//   op 0: A*B   1: A*B + C   2: A.t()*B   3: -A.t()*B   4: -A*B   5: norm(A)   6: norm(A, B, NORM_L1)   7: A.dot(B)
+// out receives the result matrix (row major) or out[0] for the scalar forms; returns the number of floats written.
+extern "C" int refm_mat_eval(int op, const float* a, int ar, int ac, const float* b, int br, int bc, const float* c,
+                             float* out, double* scalar) {
+    cv::Mat A(ar, ac, CV_32F, (void*)a), B, C;
+    if (b) B = cv::Mat(br, bc, CV_32F, (void*)b);
+    cv::Mat D;
+    switch (op) {
+    case 0: D = A * B; break;
+    case 1: C = cv::Mat(ar, bc, CV_32F, (void*)c); D = A * B + C; break;
+    case 2: D = A.t() * B; break;
+    case 3: D = -A.t() * B; break;
+    case 4: D = -A * B; break;
+    case 5: *scalar = cv::norm(A); return 0;
+    case 6: *scalar = cv::norm(A, B, cv::NORM_L1); return 0;
+    case 7: *scalar = A.dot(B); return 0;
+    default: return -1;
+    }
+    for (int i = 0; i < D.rows; i++)
+        for (int j = 0; j < D.cols; j++) out[i * D.cols + j] = D.at<float>(i, j);
+    return D.rows * D.cols;
+}

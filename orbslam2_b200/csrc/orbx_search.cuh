@@ -156,11 +156,11 @@ __device__ __forceinline__ SpQuery sp_query(const SpDev& S, int i) {
     const float X = S.worldPos[3 * i], Y = S.worldPos[3 * i + 1], Z = S.worldPos[3 * i + 2];
     float c3[3];
 #pragma unroll
-    for (int r = 0; r < 3; r++) {  // CV_32F matrix product: double accumulation, one rounding, then + tcw in float
-        const double acc = __dadd_rn(__dadd_rn(__dmul_rn((double)S.p.Rcw[3 * r], (double)X),
-                                               __dmul_rn((double)S.p.Rcw[3 * r + 1], (double)Y)),
-                                     __dmul_rn((double)S.p.Rcw[3 * r + 2], (double)Z));
-        c3[r] = __fadd_rn((float)acc, S.p.tcw[r]);
+    for (int r = 0; r < 3; r++) {  // Rcw*x3Dw + tcw as cv::gemm's small-matrix path evaluates it: float products summed
+                                   // left to right in float (no FMA), then d = (float)((double)t + (double)tcw)
+        const float t = __fadd_rn(__fadd_rn(__fmul_rn(S.p.Rcw[3 * r], X), __fmul_rn(S.p.Rcw[3 * r + 1], Y)),
+                                  __fmul_rn(S.p.Rcw[3 * r + 2], Z));
+        c3[r] = (float)__dadd_rn((double)t, (double)S.p.tcw[r]);
     }
     q.invzc = (float)(1.0 / (double)c3[2]);
     if (q.invzc < 0 && !S.p.skip_depth_test) return q;
