@@ -13,6 +13,7 @@
 
 #include <cmath>
 #include <cstdint>
+#include <cstring>
 #include <set>
 #include <stdexcept>
 #include <string>
@@ -33,10 +34,22 @@ public:
     static const int HISTO_LENGTH = 30;
 
     // Hamming distance of two 1x32 CV_8U descriptors (src/ORBmatcher.cc:1643-1659).
+    // One pair stays on the host (eight 32-bit popcounts, the reference's own bit trick): the reference calls this
+    // static inside O(N^2) host loops (MapPoint::ComputeDistinctiveDescriptors, src/MapPoint.cc:280-290), where a
+    // device round trip per pair would be orders of magnitude slower. The batched overload below runs on the device.
     static int DescriptorDistance(const cv::Mat& a, const cv::Mat& b) {
-        uint16_t d = 0;
-        check(orbm_distance(tls(), a.ptr(), b.ptr(), 1, &d), "orbm_distance");
-        return (int)d;
+        const unsigned char *pa = a.ptr(), *pb = b.ptr();
+        int dist = 0;
+        for (int i = 0; i < 8; i++) {
+            uint32_t x, y;
+            std::memcpy(&x, pa + 4 * i, 4);
+            std::memcpy(&y, pb + 4 * i, 4);
+            uint32_t v = x ^ y;
+            v = v - ((v >> 1) & 0x55555555u);
+            v = (v & 0x33333333u) + ((v >> 2) & 0x33333333u);
+            dist += (int)((((v + (v >> 4)) & 0xF0F0F0Fu) * 0x1010101u) >> 24);
+        }
+        return dist;
     }
     // Batched form: d[i] = distance(a.row(i), b.row(i)); a and b are continuous N x 32 CV_8U.
     static void DescriptorDistance(const cv::Mat& a, const cv::Mat& b, std::vector<uint16_t>& d) {
