@@ -47,9 +47,13 @@ N_DISTINCT = 16  # distinct synthetic frames; a batch tiles them (content repeat
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=None, help="timed steps (default: 200 for config 1, 10 otherwise)")
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--config", type=int, default=1, choices=[1, 2, 3, 4, 5],
+                    help="BASELINE.json config: 1 = 640x480/1000kp extraction (the headline, default), 2 = KITTI-shape stereo, "
+                         "3 = EuRoC-shape stereo, 256 pairs sharded over the ranks (strong scaling), 4 = Hamming 2-NN 100k x 1M, "
+                         "5 = 4K frames")
     ap.add_argument("--batch", type=int, default=384, help="frames per step per GPU")
     ap.add_argument("--chunk", type=int, default=0, help="frames per pipeline chunk of the host-buffer path (0 = default)")
     ap.add_argument("--dev-chunk", type=int, default=0, help="frames per chunk of the device-buffer path (0 = one launch sequence)")
@@ -58,7 +62,10 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-match", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline leg")
-    return ap.parse_args()
+    a = ap.parse_args()
+    if a.steps is None:
+        a.steps = 200 if a.config == 1 and a.impl == "ours" else (20 if a.config == 1 else 10)
+    return a
 
 
 def peaks():
@@ -335,6 +342,10 @@ def run_ours(args):
 
     B = args.batch
     frames = distinct_frames()
+    # parity gate: one frame of the workload through the public call and through the CPU oracle, before timing
+    import bench_configs
+    cfg1 = dict(name="orb_extract_640x480_1000kp_tum1", w=W, h=H, nf=NFEAT, stereo=False)
+    parity = bench_configs.parity_shape(cfg1, ob, local, frames[rank % N_DISTINCT][None], None) if rank == 0 else None
     # every rank gets its own shard of the synthetic frame sequence (different rotation of the distinct frames)
     idx = (np.arange(B) + rank * B) % N_DISTINCT
     host = torch.from_numpy(frames[idx]).pin_memory()          # [B,H,W] u8, pinned
@@ -485,7 +496,7 @@ def run_ours(args):
                     "h2d_copy_only_gbs_per_gpu": h2d_gbs,
                     "h2d_copy_only_frames_per_s": world * h2d_gbs * 1e9 / (W * H)},
             "gpu_launches": total_launches, "clocks": clocks, "host_affinity": numa, "roofline": roofline, "cpu_baseline": cpu,
-            "match": match}))
+            "parity": parity, "match": match}))
     if world > 1:
         dist.destroy_process_group()
 
@@ -512,18 +523,22 @@ def bench_match(ob, torch, dev, rank, world, barrier, max_over_ranks, nq_total=1
     sec = max_over_ranks(e0.elapsed_time(e1) * 1e-3) / reps
     pairs = per * world * nt
     acc = ((d1.int() <= 50) & (d1.float() < 0.7 * d2.float())).sum().item()
-    popc_peak = 148 * 16 * 1.965e9 / 8  # pairs/s per GPU at 16 POPC/clk/SM (nominal), 8 POPC per pair
+    import bench_configs
+    ql = q[rank * per:(rank + 1) * per]
+    parity = bench_configs.parity_knn(m, ql, t, i1.cpu().numpy(), d1.cpu().numpy().view(np.uint16),
+                                      d2.cpu().numpy().view(np.uint16), rank * per) if rank == 0 else None
     return {"metric": "hamming_knn2_gpairs_per_s", "value": pairs / sec / 1e9, "unit": "Gpairs/s",
             "config": {"workload": "knn2_100k_x_1M_256bit", "queries": per * world, "train": nt, "ratio": 0.7},
             "ms": sec * 1e3, "gpu_launches": (m.launch_count() - l0) * world, "accepted_th50_rank0": int(acc),
-            "roofline": {"bound": "popc", "achieved": pairs / sec / 1e9 / world, "peak": popc_peak / 1e9,
-                         "unit": "Gpairs/s/GPU", "frac": pairs / sec / world / popc_peak,
-                         "peak_source": "nominal 148 SM x 16 POPC/clk x 1.965 GHz / 8 POPC per pair"}}
+            "roofline": bench_configs.knn_roofline(m.last_knn_path(), pairs / sec / world), "parity": parity}
 
 
 if __name__ == "__main__":
     a = parse_args()
-    if a.impl == "reference":
+    if a.config != 1:
+        import bench_configs
+        bench_configs.main(a)
+    elif a.impl == "reference":
         run_reference(a)
     else:
         run_ours(a)
