@@ -223,10 +223,11 @@ def cpu_baseline(frames, seconds):
                       f"{dt:.1f} s wall; {nk / count:.0f} keypoints/frame"}
 
 
-def cpu_match_baseline(nt=1000000, q_per_thread=32):
+def cpu_match_baseline(nt=1000000, q_per_thread=2500):
     """The reference's DescriptorDistance loop (SWAR popcount on 8 x int32, src/ORBmatcher.cc:1643-1659) scanning the
-    whole train matrix with the best / second-best rule, one block of queries per host thread (oracle port: ORBmatcher.cc
-    cannot be compiled here). A bounded sample: threads x q_per_thread queries x 1M train rows."""
+    whole train matrix with the best / second-best rule, one block of queries per host thread (the oracle's restatement of the
+    scan, pinned to the unmodified ORBmatcher.cc by tests/test_cpu_refmatcher.py). A bounded sample of ~10-15 s:
+    threads x q_per_thread queries x 1M train rows."""
     import oracle_lib
     from orbslam2_b200.synth import synth_descriptors
     threads = cpu_cores()

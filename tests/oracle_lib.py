@@ -117,6 +117,11 @@ class Oracle(_ExtractorBase):
         self.lib.orc_blur_copy(self.h, l, _p(out))
         return out
 
+    def tie_at_cut(self, l):
+        """True when the last sorted quadtree sweep of level l was cut between two nodes of equal key count: the only
+        case in which the reference's selection depends on heap addresses (src/ORBextractor.cc:678)."""
+        return bool(self.lib.orc_tie_at_cut(self.h, l))
+
     def set_tiebreak(self, m):
         self.lib.orc_set_tiebreak(self.h, m)
 
