@@ -25,6 +25,8 @@ extern "C" const char* orbx_version(void) { return "orbx 0.1 (sm_100a)"; }
 struct orbx_handle {
     orbx_params prm;
     int device = 0;
+    bool fastV1 = true;   // k_fast (every pixel scored in one pass). ORBX_FAST_V2=1 selects k_fast2 (two-threshold pre-test
+                          // + work lists): identical candidates, measured 1.47x SLOWER (profiles/r02d_fast2_analysis.md)
     cudaStream_t stream = nullptr;
     int inSpace = ORBX_MEM_HOST, outSpace = ORBX_MEM_HOST;
     // reference ctor tables
@@ -251,7 +253,14 @@ static int build_plan(orbx_handle* h, int w, int hgt, int batch) {
             G.ytabOff = (int)tabs.size();
             linear_table(D.lv[l - 1].h, G.h, false, tabs);
         }
-        fastSmem = std::max(fastSmem, (size_t)2 * G.boxW * G.boxH + ((G.boxW * G.boxH / 2 + 15) & ~15) + sizeof(FastSmemHdr));
+        G.fastUnits = ((G.stCX * G.wCell + 3) / 4 + 2) * (G.stCY * G.hCell);
+        if (G.fastUnits >= 16384 || (G.stCX * G.wCell + 3) / 4 + 2 > 64 || G.stCY * G.hCell > 128)
+            FAIL(ORBX_ESHAPE, "level %d supertile of %d words exceeds k_fast2's tables", l, G.fastUnits);
+        if (h->fastV1)
+            fastSmem = std::max(fastSmem, (size_t)2 * G.boxW * G.boxH + ((G.boxW * G.boxH / 2 + 15) & ~15) + sizeof(FastSmemHdr));
+        else
+            fastSmem = std::max(fastSmem, (size_t)2 * G.boxW * G.boxH + ((2 * G.fastUnits + 15) & ~15) + (size_t)8 * G.fastUnits +
+                                              sizeof(Fast2Hdr));
     }
     D.totalSt = cellBase;
     D.totalBlurTiles = blurBase;
@@ -307,7 +316,8 @@ static int build_plan(orbx_handle* h, int w, int hgt, int batch) {
                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         if (r != CUDA_SUCCESS) FAIL(ORBX_ECUDA, "cuTensorMapEncodeTiled failed for level %d (CUresult %d)", l, (int)r);
     }
-    CK(cudaFuncSetAttribute(k_fast, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->fastSmem));
+    if (h->fastV1) CK(cudaFuncSetAttribute(k_fast, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->fastSmem));
+    else CK(cudaFuncSetAttribute(k_fast2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->fastSmem));
     CK(cudaFuncSetAttribute(k_quadtree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->qtSmem));
     h->planW = w;
     h->planH = hgt;
@@ -336,6 +346,7 @@ extern "C" int orbx_create(const orbx_params* p, int device, orbx_t** out) {
     orbx_handle* h = new orbx_handle();
     h->prm = *p;
     h->device = device;
+    { const char* v = getenv("ORBX_FAST_V2"); h->fastV1 = !(v && v[0] == '1'); }
     init_tables(h);
     cudaError_t e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
     if (e != cudaSuccess) {
@@ -463,7 +474,10 @@ static int launch_chain(orbx_handle* h, cudaStream_t cs, int f0, int nb, bool st
         KCHECK(h, "k_blur");
         CK(cudaEventRecord(h->evJoin, h->sSide));
     }
-    k_fast<<<dim3(D.totalSt, nb), FAST_THREADS, h->fastSmem, cs>>>(h->maps, h->dPlan, h->dCand, h->dCandCount, h->dErr, f0);
+    if (h->fastV1)
+        k_fast<<<dim3(D.totalSt, nb), FAST_THREADS, h->fastSmem, cs>>>(h->maps, h->dPlan, h->dCand, h->dCandCount, h->dErr, f0);
+    else
+        k_fast2<<<dim3(D.totalSt, nb), FAST_THREADS, h->fastSmem, cs>>>(h->maps, h->dPlan, h->dCand, h->dCandCount, h->dErr, f0);
     KCHECK(h, "k_fast");
     if (stamps) stamp(h, 3);
     // a few frames: one CTA per level is all the parallelism there is, so give it the widest CTA

@@ -39,6 +39,7 @@ struct LevelGeo {
     int nStX, nStY, stBase; // supertile grid of this level; first block index in the fused FAST launch
     int boxW, boxH;         // TMA box of a supertile: roundup16(stCX*wCell + 28) x (stCY*hCell + 6)
     int maxSurv;            // upper bound of NMS survivors in one cell
+    int fastUnits;          // upper bound of 4-pixel words in the detection area of one supertile (k_fast2 list capacity)
     // quadtree
     int quota, nIni, treeW, treeH;
     float hX;

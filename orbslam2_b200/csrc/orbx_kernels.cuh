@@ -135,6 +135,7 @@ __global__ void __launch_bounds__(256) k_resize(const DevPlan* __restrict__ P, i
 
 // ------------------------------------------------------------------------------------------------ K2 FAST
 #include "orbx_fast.cuh"
+#include "orbx_fast2.cuh"
 
 // ------------------------------------------------------------------------------------------------ K3 quadtree
 // DistributeOctTree without lists or pointers. Nodes live in shared memory as rectangles + key counts; every key

@@ -222,3 +222,90 @@ def test_4k_frame_all_stages(ob):
     kb, db, nb = ex.extract_batch(np.stack([img, img[::-1].copy()]))
     assert kb[0, :nb[0]].tobytes() == kps.tobytes() and np.array_equal(db[0, :nb[0]], desc)
     ex.close()
+
+
+# ---- wider inputs: many seeds per shape (final outputs), portrait, odd widths that move the 16-byte
+# TMA realignment of k_fast, a pyramid whose top level is a single row of FAST cells, and low-contrast frames in which
+# (almost) every cell takes the minThFAST retry
+def _final_outputs_equal(ex, orc, img, stats):
+    p = orc.params
+    ko, do = canonical(*orc.extract(img, 4 * p["nfeatures"]))
+    kps, desc = ex(img)
+    assert len(kps) == len(ko), f"{len(kps)} vs {len(ko)} keypoints"
+    for f in ("octave", "response", "size", "class_id"):
+        assert np.array_equal(kps[f], ko[f]), f
+    assert np.abs(kps["x"] - ko["x"]).max() <= 1e-4 and np.abs(kps["y"] - ko["y"]).max() <= 1e-4
+    assert np.abs(kps["angle"] - ko["angle"]).max() <= 1e-2
+    same = (desc == do).all(axis=1)
+    stats[0] += int(same.sum()); stats[1] += len(same)
+
+
+@pytest.mark.parametrize("w,h,nf,seeds", [(640, 480, 1000, 20), (752, 480, 1200, 20), (1241, 376, 2000, 20), (480, 640, 1000, 8),
+                                          (641, 479, 1000, 6), (757, 483, 1200, 6), (643, 481, 1000, 4), (650, 490, 700, 4)])
+def test_many_seeds_and_odd_shapes(ob, w, h, nf, seeds):
+    p = _params(nf)
+    ex = ob.ORBextractor(**p); orc = Oracle(**p)
+    stats = [0, 0]
+    for seed in range(100, 100 + seeds):
+        _final_outputs_equal(ex, orc, synth_image(w, h, seed), stats)
+    assert stats[0] >= 0.9999 * stats[1], f"descriptors identical {stats[0]}/{stats[1]}"
+    ex.close()
+
+
+def test_single_cell_row_top_level(ob):
+    """Height chosen so that the top pyramid level holds exactly one row of FAST cells (nRows = 1)."""
+    p = _params(600)
+    orc = Oracle(**p)
+    h = None
+    for cand in range(150, 260):
+        orc.extract(synth_image(640, cand, 3), 2400)
+        hh = orc.level_size(7)[1]
+        if (hh - 2 * 16) // 30 == 1:
+            h = cand
+            break
+    assert h is not None
+    ex = ob.ORBextractor(**p)
+    stats = [0, 0]
+    for seed in (3, 4):
+        img = synth_image(640, h, seed)
+        kps, desc = ex(img)
+        _compare_frame(ex, orc, img, 0, stats, kps, desc)
+    assert stats[0] >= 0.9999 * stats[1]
+    ex.close()
+
+
+@pytest.mark.parametrize("contrast", [0.15, 0.3])
+def test_low_contrast_retry_cells(ob, contrast):
+    """Contrast scaled down so that FAST at iniThFAST = 20 finds (almost) nothing and the cells fall back to minThFAST."""
+    p = _params(1000)
+    ex = ob.ORBextractor(**p); orc = Oracle(**p)
+    stats = [0, 0]
+    for seed in (0, 1, 2):
+        img = synth_image(640, 480, seed).astype(np.float32)
+        img = np.clip((img - 128.0) * contrast + 128.0, 0, 255).astype(np.uint8)
+        kps, desc = ex(img)
+        _compare_frame(ex, orc, img, 0, stats, kps, desc)
+        ini = sum(int((orc.candidates(l)[:, 2] >= 20).sum()) for l in range(8))
+        tot = sum(len(orc.candidates(l)) for l in range(8))
+        assert tot > 500 and (contrast > 0.2 or ini < 0.2 * tot), (ini, tot)
+    assert stats[0] >= 0.9999 * stats[1]
+    ex.close()
+
+
+def test_two_pass_fast_kernel_gives_identical_candidates(ob, monkeypatch):
+    """k_fast2 (ORBX_FAST_V2=1: iniThFAST pre-test + work lists, the reference's two-threshold structure) against the
+    default k_fast and the oracle: candidates, scores and final outputs identical (kept as a measured alternative,
+    profiles/r02d_fast2_analysis.md)."""
+    monkeypatch.setenv("ORBX_FAST_V2", "1")
+    p = _params(1000)
+    ex2 = ob.ORBextractor(**p)
+    monkeypatch.delenv("ORBX_FAST_V2")
+    ex1 = ob.ORBextractor(**p)
+    orc = Oracle(**p)
+    for seed, contrast in ((7, 1.0), (8, 0.2)):
+        img = synth_image(640, 480, seed).astype(np.float32)
+        img = np.clip((img - 128.0) * contrast + 128.0, 0, 255).astype(np.uint8)
+        k2, d2 = ex2(img); k1, d1 = ex1(img)
+        assert k1.tobytes() == k2.tobytes() and np.array_equal(d1, d2)
+        _compare_frame(ex2, orc, img, 0, None, k2, d2)
+    ex1.close(); ex2.close()
