@@ -127,15 +127,20 @@ public:
     orbx_t* handle() { return h_; }  // for ComputeStereoMatchesDevice / batch calls on the C ABI
 
 protected:
+    // mvImagePyramid after operator(): every level as an ROI at (edgeThreshold, edgeThreshold) of its padded buffer. One
+    // export kernel and one device-to-host copy for all levels (orbx_pyramid_all) into one host block.
     void refreshPyramid() {
-        padded_.resize(nlevels);
+        size_t bytes = 0;
+        check(orbx_pyramid_bytes(h_, 1, &bytes), "orbx_pyramid_bytes");
+        if (pyr_.empty() || (size_t)pyr_.rows * pyr_.cols < bytes) pyr_.create(1, (int)bytes, CV_8UC1);
+        std::vector<size_t> off(nlevels);
+        check(orbx_pyramid_all(h_, 0, pyr_.data, bytes, 1, off.data()), "orbx_pyramid_all");
         for (int l = 0; l < nlevels; l++) {
             int w = 0, hgt = 0;
             check(orbx_level_size(h_, l, &w, &hgt), "orbx_level_size");
             const int W = w + 2 * edgeThreshold, H = hgt + 2 * edgeThreshold;
-            padded_[l].create(H, W, CV_8UC1);
-            check(orbx_pyramid_level(h_, 0, l, padded_[l].data, padded_[l].step, 1), "orbx_pyramid_level");
-            mvImagePyramid[l] = padded_[l](cv::Rect(edgeThreshold, edgeThreshold, w, hgt));
+            cv::Mat padded(H, W, CV_8UC1, pyr_.data + off[l], (size_t)W);
+            mvImagePyramid[l] = padded(cv::Rect(edgeThreshold, edgeThreshold, w, hgt));
         }
     }
     static void check(int rc, const char* what) {
@@ -162,7 +167,7 @@ private:
     orbx_t* h_ = nullptr;
     std::vector<orbx_kp> kp_;
     std::vector<uint8_t> desc_;
-    std::vector<cv::Mat> padded_;
+    cv::Mat pyr_;  // all padded levels back to back (mvImagePyramid[l] are ROIs into it)
 };
 
 // Frame::ComputeStereoMatches (src/Frame.cc:464-642) on the device state of two extractors that have just processed the

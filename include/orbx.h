@@ -82,6 +82,13 @@ int orbx_extract_batch(orbx_t* h, const uint8_t* imgs, int batch, int w, int hgt
 int orbx_extract_batch_submit(orbx_t* h, const uint8_t* imgs, int batch, int w, int hgt, size_t stride,
                               size_t img_stride, orbx_kp* kps, uint8_t* desc, int cap_per_frame);
 int orbx_extract_batch_wait(orbx_t* h, int* n);
+/* Single-process multi-GPU batch: `ndev` handles, one per device, each driven by its own host thread. Frames are split
+ * into contiguous blocks (handle k owns the k-th block; the first batch % ndev blocks hold one frame more) and every
+ * block's keypoints / descriptors / counts land in its own slice of the caller's HOST arrays; no collective, frames are
+ * independent (the reference is a single process with std::thread workers, src/System.cc:104-112, and
+ * has no multi-device counterpart). Same results, byte for byte, as one orbx_extract_batch on one device. */
+int orbx_extract_batch_multi(orbx_t** handles, int ndev, const uint8_t* imgs, int batch, int w, int hgt, size_t stride,
+                             size_t img_stride, orbx_kp* kps, uint8_t* desc, int cap, int* n);
 /* ---- upstream image prep fused into the ingest (the calls the reference makes before the extractor) -----------------
  * Pixel format of the images handed to orbx_extract*: colour input is converted exactly as
  * cv::cvtColor(.., COLOR_{RGB,BGR,RGBA,BGRA}2GRAY) (src/Tracking.cc:269-294, 308-321, 337-350) while it is written into
@@ -119,6 +126,11 @@ int orbx_pyramid_level(orbx_t* h, int frame, int level, uint8_t* dst, size_t dst
 /* Parity/debug taps (host outputs): the 7x7 sigma-2 blurred level (src/ORBextractor.cc:899-900) and the per-cell FAST
  * candidates handed to DistributeOctTree (src/ORBextractor.cc:783-823) as (x, y, score) int triples in level pixel
  * coordinates, unordered. */
+/* The whole padded pyramid of one frame in ONE kernel launch and ONE device-to-host copy (what ORBextractor::mvImagePyramid
+ * holds after operator(), src/ORBextractor.cc:921-946): level l lands at dst + offsets[l] as a dense (w+2e) x (h+2e)
+ * buffer, e = edgeThreshold when with_border. offsets (nlevels entries) is an output. */
+int orbx_pyramid_bytes(orbx_t* h, int with_border, size_t* bytes);
+int orbx_pyramid_all(orbx_t* h, int frame, uint8_t* dst, size_t dst_bytes, int with_border, size_t* offsets);
 int orbx_blurred_level(orbx_t* h, int frame, int level, uint8_t* dst, size_t dst_stride);
 int orbx_candidates(orbx_t* h, int frame, int level, int32_t* xys, int cap, int* n);
 

@@ -26,10 +26,10 @@ class OrbxParams(C.Structure):
 
 # every symbol include/orbx.h declares (tests check the export table against this list and the header)
 SYMBOLS = ["orbx_create", "orbx_destroy", "orbx_set_memory_space", "orbx_extract", "orbx_extract_batch",
-           "orbx_extract_batch_submit", "orbx_extract_batch_wait", "orbx_set_input_format", "orbx_set_rectify_maps",
+           "orbx_extract_batch_submit", "orbx_extract_batch_wait", "orbx_extract_batch_multi", "orbx_set_input_format", "orbx_set_rectify_maps",
            "orbx_undistort_keypoints",
            "orbx_max_keypoints", "orbx_set_chunk", "orbx_level_count", "orbx_tables", "orbx_level_size", "orbx_pyramid_level",
-           "orbx_blurred_level", "orbx_candidates", "orbx_stereo_match", "orbx_stereo_match_batch", "orbm_create",
+           "orbx_blurred_level", "orbx_pyramid_bytes", "orbx_pyramid_all", "orbx_candidates", "orbx_stereo_match", "orbx_stereo_match_batch", "orbm_create",
            "orbm_destroy", "orbm_set_memory_space", "orbm_set_train", "orbm_knn2", "orbm_set_knn_mode", "orbm_last_knn_path", "orbm_window_search", "orbm_distance",
            "orbm_search_by_projection", "orbm_search_by_bow", "orbm_search_by_bow_batch", "orbm_fuse_search", "orbm_search_kf_projection", "orbm_search_for_initialization", "orbm_search_for_triangulation", "orbm_search_for_triangulation_batch", "orbm_search_local_points", "orbm_search_stats", "orbm_distinctive_descriptors",
            "orbx_stream", "orbm_stream", "orbx_launch_count", "orbm_launch_count", "orbx_stage_ms", "orbx_set_profiling",
@@ -98,6 +98,9 @@ def lib():
     L.orbx_extract_batch.argtypes = [vp, vp, ci, ci, ci, sz, sz, vp, vp, ci, vp]
     L.orbx_extract_batch_submit.argtypes = [vp, vp, ci, ci, ci, sz, sz, vp, vp, ci]
     L.orbx_extract_batch_wait.argtypes = [vp, vp]
+    L.orbx_pyramid_bytes.argtypes = [vp, ci, vp]
+    L.orbx_pyramid_all.argtypes = [vp, ci, vp, sz, ci, vp]
+    L.orbx_extract_batch_multi.argtypes = [vp, ci, vp, ci, ci, ci, sz, sz, vp, vp, ci, vp]
     L.orbx_set_input_format.argtypes = [vp, ci]
     L.orbx_set_rectify_maps.argtypes = [vp, vp, vp, ci, ci]
     L.orbx_undistort_keypoints.argtypes = [vp, vp, vp, ci, vp, ci]

@@ -6,6 +6,8 @@
 #include <cstdlib>
 #include <cstring>
 #include <mutex>
+#include <string>
+#include <thread>
 #include <vector>
 
 #include "orbx_kernels.cuh"
@@ -505,7 +507,19 @@ static inline int fmt_channels(int fmt) { return fmt == ORBX_FMT_GRAY8 ? 1 : (fm
 // staging for colour / rectified input: the raw source images (host input only) and the grey source of the remap
 static int ensure_ingest(orbx_handle* h, int batch, int w, int hgt) {
     const int ch = fmt_channels(h->inFmt);
-    if (ch == 1 && !h->dMapX) return ORBX_OK;
+    if (ch == 1 && !h->dMapX) {
+        // grey host input whose width is not the level-0 pitch (a multiple of 64): a pitched host-to-device copy moves such rows one DMA
+        // descriptor at a time (measured 4.0 ms for 64 x 1241x376 against 0.6 ms flat), so the frames cross PCIe as one
+        // flat copy into this staging block and k_repitch lays them out in level 0
+        if (h->inSpace == ORBX_MEM_HOST && (w & 63) && (size_t)batch * hgt * w > h->rawCap) {
+            cudaFree(h->dRaw);
+            h->dRaw = nullptr;
+            h->rawCap = 0;
+            CK(cudaMalloc(&h->dRaw, (size_t)batch * hgt * w));
+            h->rawCap = (size_t)batch * hgt * w;
+        }
+        return ORBX_OK;
+    }
     const size_t raw = (size_t)batch * hgt * w * ch, gray = (size_t)batch * hgt * w;
     if (h->inSpace == ORBX_MEM_HOST && raw > h->rawCap) {
         cudaFree(h->dRaw);
@@ -567,7 +581,17 @@ static int copy_in(orbx_handle* h, cudaStream_t cs, const uint8_t* imgs, int f0,
         }
         return ORBX_OK;
     }
-    if (nb == 1 || img_stride == stride * (size_t)hgt) {
+    if (h->inSpace == ORBX_MEM_HOST && (w & 63) && stride == (size_t)w && h->dRaw &&
+        (size_t)(f0 + nb) * hgt * w <= h->rawCap) {
+        uint8_t* raw = h->dRaw + (size_t)f0 * hgt * w;
+        if (nb == 1 || img_stride == stride * (size_t)hgt) {
+            CK(cudaMemcpyAsync(raw, src, (size_t)nb * hgt * w, kin, cs));
+        } else {
+            for (int f = 0; f < nb; f++) CK(cudaMemcpyAsync(raw + (size_t)f * hgt * w, src + f * img_stride, (size_t)hgt * w, kin, cs));
+        }
+        k_repitch<<<dim3((w + 255) / 256, (hgt + 3) / 4, nb), dim3(64, 4), 0, cs>>>(raw, w, hgt, dst, L0.pitch, L0.frameStride);
+        KCHECK(h, "k_repitch");
+    } else if (nb == 1 || img_stride == stride * (size_t)hgt) {
         CK(cudaMemcpy2DAsync(dst, L0.pitch, src, stride, w, (size_t)hgt * nb, kin, cs));
     } else {
         for (int f = 0; f < nb; f++)
@@ -775,6 +799,36 @@ extern "C" int orbx_extract_batch(orbx_t* h, const uint8_t* imgs, int batch, int
     return orbx_extract_batch_wait(h, n);
 }
 
+/* Single-process multi-GPU form of orbx_extract_batch: `ndev` handles, one per device (created with
+ * orbx_create(.., device, ..)), each driven by its own host thread; the batch is split into contiguous blocks — handle k
+ * owns frames [k*base + min(k, extra), ...) with base = batch / ndev, extra = batch % ndev, the same rule as
+ * orbslam2_b200/sharding.py:shard_range — and every block's results land in its own slice of the caller's arrays. No
+ * collective: frames are independent. Host buffers only (each device copies its own slice). Returns the first error. */
+extern "C" int orbx_extract_batch_multi(orbx_t** hs, int ndev, const uint8_t* imgs, int batch, int w, int hgt, size_t stride,
+                                        size_t img_stride, orbx_kp* kps, uint8_t* desc, int cap, int* n) {
+    if (!hs || ndev < 1 || !n || batch < 0) FAIL(ORBX_EINVAL, "bad argument");
+    for (int k = 0; k < ndev; k++)
+        if (!hs[k] || hs[k]->inSpace != ORBX_MEM_HOST || hs[k]->outSpace != ORBX_MEM_HOST)
+            FAIL(ORBX_EINVAL, "orbx_extract_batch_multi takes host buffers (handle %d)", k);
+    std::vector<int> rc(ndev, ORBX_OK);
+    std::vector<std::string> msg(ndev);
+    std::vector<std::thread> th;
+    const int base = batch / ndev, extra = batch % ndev;
+    for (int k = 0; k < ndev; k++) {
+        const int lo = k * base + std::min(k, extra), cnt = base + (k < extra ? 1 : 0);
+        if (cnt == 0) continue;
+        th.emplace_back([=, &rc, &msg]() {
+            rc[k] = orbx_extract_batch(hs[k], imgs + (size_t)lo * img_stride, cnt, w, hgt, stride, img_stride,
+                                       kps + (size_t)lo * cap, desc + (size_t)lo * cap * 32, cap, n + lo);
+            if (rc[k] != ORBX_OK) msg[k] = orbx_last_error_string();  // the error text is thread-local
+        });
+    }
+    for (auto& t : th) t.join();
+    for (int k = 0; k < ndev; k++)
+        if (rc[k] != ORBX_OK) FAIL(rc[k], "device block %d: %s", k, msg[k].c_str());
+    return ORBX_OK;
+}
+
 /* Pixel format of the images handed to orbx_extract*: colour input is converted as cv::cvtColor(.., COLOR_x2GRAY) does
  * (src/Tracking.cc:269-294) while it is written into pyramid level 0. Strides are in bytes. */
 extern "C" int orbx_set_input_format(orbx_t* h, int fmt) {
@@ -886,6 +940,49 @@ static int export_level(orbx_handle* h, const uint8_t* base, int frame, int leve
 extern "C" int orbx_pyramid_level(orbx_t* h, int frame, int level, uint8_t* dst, size_t dst_stride, int with_border) {
     if (!h) FAIL(ORBX_EINVAL, "null handle");
     return export_level(h, h->dPyr, frame, level, dst, dst_stride, with_border ? h->prm.edgeThreshold : 0);
+}
+
+/* The whole pyramid of one frame in one launch and one copy: level l is written to dst + offsets[l] (offsets are an
+ * OUTPUT: cumulative dense sizes) as a dense (w + 2e) x (h + 2e) buffer, e = edgeThreshold if with_border else 0.
+ * dst_bytes must hold the sum (orbx_pyramid_bytes gives it). Replaces nlevels orbx_pyramid_level calls (each its own
+ * kernel, copy and synchronisation) in the drop-in's mvImagePyramid refresh. dst is a host pointer. */
+extern "C" int orbx_pyramid_bytes(orbx_t* h, int with_border, size_t* bytes) {
+    if (!h || !bytes) FAIL(ORBX_EINVAL, "null argument");
+    if (!h->lastBatch) FAIL(ORBX_ESTATE, "no frame extracted yet");
+    const int e = with_border ? h->prm.edgeThreshold : 0;
+    size_t tot = 0;
+    for (int l = 0; l < h->prm.nlevels; l++) tot += (size_t)(h->hp.lv[l].w + 2 * e) * (h->hp.lv[l].h + 2 * e);
+    *bytes = tot;
+    return ORBX_OK;
+}
+extern "C" int orbx_pyramid_all(orbx_t* h, int frame, uint8_t* dst, size_t dst_bytes, int with_border, size_t* offsets) {
+    if (!h || !dst || !offsets) FAIL(ORBX_EINVAL, "null argument");
+    if (!h->lastBatch || frame < 0 || frame >= h->lastBatch) FAIL(ORBX_ESTATE, "frame %d not in the last extracted batch", frame);
+    CK(cudaSetDevice(h->device));
+    const int e = with_border ? h->prm.edgeThreshold : 0, nl = h->prm.nlevels;
+    ExportOffsets offs;
+    size_t tot = 0;
+    for (int l = 0; l < nl; l++) {
+        offs.off[l] = (long long)tot;
+        offsets[l] = tot;
+        tot += (size_t)(h->hp.lv[l].w + 2 * e) * (h->hp.lv[l].h + 2 * e);
+    }
+    if (dst_bytes < tot) FAIL(ORBX_ECAP, "dst holds %zu bytes, the pyramid needs %zu", dst_bytes, tot);
+    if (tot > h->exportBytes) {
+        cudaFree(h->dExport);
+        h->dExport = nullptr;
+        h->exportBytes = 0;
+        CK(cudaMalloc(&h->dExport, tot));
+        h->exportBytes = tot;
+    }
+    const int W0 = h->hp.lv[0].w + 2 * e, H0 = h->hp.lv[0].h + 2 * e;
+    dim3 block(64, 4), grid((W0 + 63) / 64, (H0 + 3) / 4, nl);
+    k_export_all<<<grid, block, 0, h->stream>>>(h->dPlan, h->dPyr, frame, e, offs, h->dExport);
+    h->launches++;
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(dst, h->dExport, tot, cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    return ORBX_OK;
 }
 
 extern "C" int orbx_blurred_level(orbx_t* h, int frame, int level, uint8_t* dst, size_t dst_stride) {

@@ -407,3 +407,17 @@ __global__ void k_export(const DevPlan* __restrict__ P, const uint8_t* __restric
     const uint8_t* s = src + G.pyrOff + (long long)f * G.frameStride;
     dst[(long long)y * W + x] = s[(long long)reflect101(y - e, G.h) * G.pitch + reflect101(x - e, G.w)];
 }
+
+// All levels of one frame in ONE launch: level l goes to dst + off[l] as a dense (w+2e) x (h+2e) reflect-101 buffer.
+// blockIdx.z = level; the grid is sized for level 0 and the smaller levels exit early.
+struct ExportOffsets { long long off[ORBX_MAX_LEVELS]; };
+__global__ void k_export_all(const DevPlan* __restrict__ P, const uint8_t* __restrict__ src, int f, int e,
+                             const __grid_constant__ ExportOffsets offs, uint8_t* __restrict__ dst) {
+    const int level = blockIdx.z;
+    const LevelGeo& G = P->lv[level];
+    const int W = G.w + 2 * e, H = G.h + 2 * e;
+    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y * blockDim.y + threadIdx.y;
+    if (x >= W || y >= H) return;
+    const uint8_t* s = src + G.pyrOff + (long long)f * G.frameStride;
+    dst[offs.off[level] + (long long)y * W + x] = s[(long long)reflect101(y - e, G.h) * G.pitch + reflect101(x - e, G.w)];
+}

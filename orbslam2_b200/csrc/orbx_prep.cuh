@@ -130,3 +130,17 @@ __global__ void __launch_bounds__(128) k_undistort(const orbx_kp* __restrict__ k
     }
     out[(size_t)f * stride + i] = kp;
 }
+
+// Dense w x hgt frames (rows back to back, any alignment) -> pitched level-0 rows; one thread writes one 32-bit word.
+__global__ void __launch_bounds__(256) k_repitch(const uint8_t* __restrict__ src, int w, int hgt, uint8_t* __restrict__ dst,
+                                                 int pitch, long long frameStride) {
+    const int x = (blockIdx.x * 64 + threadIdx.x) * 4, y = blockIdx.y * 4 + threadIdx.y;
+    if (x >= w || y >= hgt) return;
+    const uint8_t* s = src + ((size_t)blockIdx.z * hgt + y) * w + x;
+    uint8_t* d = dst + (long long)blockIdx.z * frameStride + (long long)y * pitch + x;
+    if (x + 4 <= w) {
+        *(unsigned*)d = (unsigned)s[0] | ((unsigned)s[1] << 8) | ((unsigned)s[2] << 16) | ((unsigned)s[3] << 24);
+    } else {
+        for (int b = 0; b < w - x; b++) d[b] = s[b];
+    }
+}

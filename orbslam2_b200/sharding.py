@@ -62,3 +62,33 @@ def knn2_sharded(knn2_fn, queries, rank, world):
     if hi == lo:
         return lo, hi, None
     return lo, hi, knn2_fn(queries[lo:hi])
+
+
+class MultiGpuExtractor:
+    """Single-process multi-GPU extraction (orbx_extract_batch_multi, include/orbx.h): one ORBextractor handle per device,
+    each driven by its own host thread inside the C library; frames are split into the contiguous shard_range blocks and
+    the results land in disjoint slices of ONE set of host arrays. `devices` may name a device more than once (two
+    handles on one GPU: what a single-GPU box can test)."""
+
+    def __init__(self, devices, **params):
+        from .extractor import ORBextractor
+        self.ex = [ORBextractor(device=d, **params) for d in devices]
+
+    def extract_batch(self, images):
+        import ctypes as C
+        from . import _lib
+        from .extractor import KP_DTYPE
+        images = np.ascontiguousarray(images, np.uint8)
+        B, H, W = images.shape
+        cap = self.ex[0].max_keypoints(W, H)
+        kps = np.zeros((B, cap), KP_DTYPE); desc = np.zeros((B, cap, 32), np.uint8); n = np.zeros(B, np.int32)
+        for e in self.ex:
+            e._set_space(_lib.MEM_HOST, _lib.MEM_HOST)
+        hs = (C.c_void_p * len(self.ex))(*[e._h for e in self.ex])
+        _lib.check(self.ex[0]._L.orbx_extract_batch_multi(hs, len(self.ex), images.ctypes.data, B, W, H, W, W * H,
+                                                          kps.ctypes.data, desc.ctypes.data, cap, n.ctypes.data))
+        return kps, desc, n
+
+    def close(self):
+        for e in self.ex:
+            e.close()

@@ -309,3 +309,26 @@ def test_two_pass_fast_kernel_gives_identical_candidates(ob, monkeypatch):
         assert k1.tobytes() == k2.tobytes() and np.array_equal(d1, d2)
         _compare_frame(ex2, orc, img, 0, None, k2, d2)
     ex1.close(); ex2.close()
+
+
+def test_single_process_multi_gpu_entry_point(ob):
+    """orbx_extract_batch_multi: contiguous blocks of the batch on several handles (every visible GPU, at least two handles
+    so that a one-GPU box still exercises the split), results in disjoint slices — bytes equal to one device's call."""
+    import torch
+    from orbslam2_b200.sharding import MultiGpuExtractor, shard_sizes
+    p = _params(1000)
+    imgs = np.stack([synth_image(640, 480, 40 + s) for s in range(7)])
+    ex = ob.ORBextractor(**p)
+    k1, d1, n1 = ex.extract_batch(imgs)
+    ndev = torch.cuda.device_count()
+    devices = list(range(ndev)) if ndev >= 2 else [0, 0, 0]
+    assert shard_sizes(7, len(devices))[0] >= 1
+    mg = MultiGpuExtractor(devices, **p)
+    k2, d2, n2 = mg.extract_batch(imgs)
+    assert np.array_equal(n1, n2)
+    for f in range(7):
+        assert k1[f, :n1[f]].tobytes() == k2[f, :n2[f]].tobytes() and np.array_equal(d1[f, :n1[f]], d2[f, :n2[f]])
+    # fewer frames than handles: the empty blocks are skipped
+    k3, d3, n3 = mg.extract_batch(imgs[:2])
+    assert np.array_equal(n3, n1[:2]) and k3[1, :n3[1]].tobytes() == k1[1, :n1[1]].tobytes()
+    mg.close(); ex.close()
