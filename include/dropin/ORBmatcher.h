@@ -339,6 +339,7 @@ public:
                              pKF->mDescriptors.ptr(), nullptr};
         std::vector<int32_t> bestIdx(nMPs, -1);
         std::vector<uint16_t> bestDist(nMPs, 256);
+        check(orbm_keyframe_hint(tls(), (uint64_t)pKF->mnId + 1), "orbm_keyframe_hint");  // keyframe arrays are immutable: cache
         check(orbm_fuse_search(tls(), &P, pKF->mvInvLevelSigma2.data(), 1, &pts, &kf, bestIdx.data(), bestDist.data()),
               "orbm_fuse_search");
         int nFused = 0;
@@ -432,6 +433,7 @@ public:
         orbm_cur_frame kf = {nK, (const orbx_kp*)pKF->mvKeysUn.data(), nullptr, pKF->mDescriptors.ptr(), nullptr};
         std::vector<int32_t> bestIdx(n, -1);
         std::vector<uint16_t> bestDist(n, 256);
+        check(orbm_keyframe_hint(tls(), (uint64_t)pKF->mnId + 1), "orbm_keyframe_hint");
         check(orbm_fuse_search(tls(), &P, invSigma2.data(), 0, &pts, &kf, bestIdx.data(), bestDist.data()), "orbm_fuse_search");
         int nFused = 0;
         for (int i = 0; i < n; i++) {
@@ -784,7 +786,10 @@ protected:
         orbm_cur_frame kf = {nK, (const orbx_kp*)pDst->mvKeysUn.data(), nullptr, pDst->mDescriptors.ptr(), nullptr};
         std::vector<int32_t> bestIdx(n, -1);
         std::vector<uint16_t> bestDist(n, 256);
-        if (n) check(orbm_fuse_search(tls(), &P, invSigma2.data(), 0, &fp, &kf, bestIdx.data(), bestDist.data()), "orbm_fuse_search");
+        if (n) {
+            check(orbm_keyframe_hint(tls(), (uint64_t)pDst->mnId + 1), "orbm_keyframe_hint");
+            check(orbm_fuse_search(tls(), &P, invSigma2.data(), 0, &fp, &kf, bestIdx.data(), bestDist.data()), "orbm_fuse_search");
+        }
         vnMatch.assign(n, -1);
         int found = 0;
         for (int i = 0; i < n; i++)

@@ -283,6 +283,13 @@ typedef struct {
 } orbm_fuse_points;
 int orbm_fuse_search(orbm_t* m, const orbm_proj_params* p, const float* inv_level_sigma2, int check_chi2,
                      const orbm_fuse_points* pts, const orbm_cur_frame* kf, int32_t* best_idx, uint16_t* best_dist);
+/* Keyframe cache. A KeyFrame's mvKeysUn / mvuRight / mDescriptors never change after construction (src/KeyFrame.cc:31-57),
+ * yet Fuse, SearchBySim3 and SearchInNeighbors search the same keyframes again and again. orbm_keyframe_hint declares
+ * that the `kf` argument of the NEXT orbm_fuse_search call is keyframe `key` (the drop-in passes pKF->mnId + 1; 0 = no
+ * hint): if the handle still holds that keyframe (same n, same grid constants; 8 entries, least recently used replaced)
+ * its upload and the four grid kernels are skipped, otherwise it is remembered. The hint is consumed by that call. */
+int orbm_keyframe_hint(orbm_t* m, uint64_t key);
+int64_t orbm_keyframe_cache_hits(orbm_t* m);
 
 /* Replaces the search of ORBmatcher::SearchByProjection(KeyFrame* pKF, cv::Mat Scw, const vector<MapPoint*>& vpPoints,
  * vector<MapPoint*>& vpMatched, int th) (include/ORBmatcher.h:64, src/ORBmatcher.cc:285-398; LoopClosing::ComputeSim3

@@ -398,6 +398,16 @@ struct orbm_handle {
     int smCount = 148;
     int64_t launches = 0;
     int lastRounds = 0; int64_t lastCandidates = 0;
+    // keyframe cache (orbm_keyframe_hint): staged keypoints / uRight / descriptors and the built 64 x 48 grid of immutable
+    // keyframes, so that repeated Fuse / SearchBySim3 searches against one keyframe skip the upload and four grid kernels
+    struct KfEntry {
+        uint64_t key = 0; int n = 0; bool hasUR = false; float geo[4] = {0, 0, 0, 0}; uint64_t stamp = 0;
+        uint8_t* mem = nullptr; size_t cap = 0;
+        orbx_kp* keys = nullptr; float* uRight = nullptr; uint4* desc = nullptr; int* cellStart = nullptr; int* items = nullptr;
+    };
+    KfEntry kfc[8];
+    uint64_t kfHint = 0, kfClock = 0;
+    int64_t kfHits = 0;
 };
 
 template <typename T>
@@ -440,6 +450,7 @@ extern "C" int orbm_destroy(orbm_t* m) {
     cudaFree(m->dAm); cudaFree(m->dAe); cudaFree(m->dBm); cudaFree(m->dBe);
     cudaFree(m->dQ); cudaFree(m->dB); cudaFree(m->dPartial); cudaFree(m->dI1); cudaFree(m->dI2); cudaFree(m->dD1);
     cudaFree(m->dD2); cudaFree(m->dOff); cudaFree(m->dIdx); cudaFree(m->dSkip); cudaFree(m->dWs); cudaFree(m->dCand); if (m->hRes) cudaFreeHost(m->hRes); if (m->hFlags) cudaFreeHost(m->hFlags); if (m->hIn) cudaFreeHost(m->hIn);
+    for (auto& e : m->kfc) cudaFree(e.mem);
     cudaStreamDestroy(m->stream);
     delete m;
     return ORBX_OK;
@@ -747,6 +758,18 @@ extern "C" int orbx_stereo_match_batch(orbx_t* left, orbx_t* right, float mbf, f
                                                                g_ss.dSad, oStride);
     int P2 = 1;
     while (P2 < maxN) P2 <<= 1;
+    // more than 6144 left keypoints need over 48 KB of dynamic shared memory: opt in (up to 227 KB = 16384 keypoints,
+    // the 4K / 8000-keypoint config has ~8000), and say so clearly beyond that instead of failing the launch
+    if ((size_t)P2 * 8 > 227 * 1024) FAIL(ORBX_ESHAPE, "%d left keypoints exceed the stereo median cut's 28k-entry sort buffer", maxN);
+    if ((size_t)P2 * 8 > 48 * 1024) {
+        static std::mutex mu;
+        static int optedIn[64] = {0};
+        std::lock_guard<std::mutex> lk(mu);
+        if (A.device < 64 && optedIn[A.device] < P2 * 8) {
+            CK(cudaFuncSetAttribute(k_stereo_cut, cudaFuncAttributeMaxDynamicSharedMemorySize, P2 * 8));
+            optedIn[A.device] = P2 * 8;
+        }
+    }
     k_stereo_cut<<<batch, 1024, (size_t)P2 * 8, st>>>(A.dPlan, A.dNOut, g_ss.dSad, oU, oZ, oStride, P2);
     orbx_count_launch((orbx_handle*)left, 2);
     CK(cudaGetLastError());
@@ -1177,7 +1200,49 @@ extern "C" int orbm_distinctive_descriptors(orbm_t* m, const uint8_t* desc, cons
     return ORBX_OK;
 }
 
-/* Diagnostics of the last orbm_search_by_projection call: fixed-point rounds and candidate pairs evaluated. */
+extern "C" int orbm_keyframe_hint(orbm_t* m, uint64_t key) {
+    if (!m) FAIL(ORBX_EINVAL, "null handle");
+    m->kfHint = key;
+    return ORBX_OK;
+}
+extern "C" int64_t orbm_keyframe_cache_hits(orbm_t* m) { return m ? m->kfHits : 0; }
+
+static orbm_handle::KfEntry* kf_lookup(orbm_handle* m, uint64_t key, int n, bool hasUR, const orbm_proj_params* p) {
+    for (auto& e : m->kfc)
+        if (e.key == key && e.n == n && e.hasUR == hasUR && e.geo[0] == p->minX && e.geo[1] == p->minY &&
+            e.geo[2] == p->grid_w_inv && e.geo[3] == p->grid_h_inv) {
+            e.stamp = ++m->kfClock;
+            return &e;
+        }
+    return nullptr;
+}
+// (re)allocates the least recently used entry for a keyframe of n keypoints; device pointers are carved out of one block
+static int kf_claim(orbm_handle* m, uint64_t key, int n, bool hasUR, const orbm_proj_params* p, orbm_handle::KfEntry** out) {
+    orbm_handle::KfEntry* e = &m->kfc[0];
+    for (auto& c : m->kfc)
+        if (c.stamp < e->stamp) e = &c;
+    const size_t a = 256;
+    auto up = [&](size_t x) { return (x + a - 1) / a * a; };
+    const size_t need = up((size_t)n * sizeof(orbx_kp)) + up((size_t)n * 4) + up((size_t)n * 32) + up((SP_CELLS + 1) * 4) +
+                        up((size_t)std::max(n, 1) * 4);
+    if (need > e->cap) {
+        cudaFree(e->mem);
+        e->mem = nullptr; e->cap = 0; e->key = 0;
+        CK(cudaMalloc(&e->mem, need));
+        e->cap = need;
+    }
+    uint8_t* q = e->mem;
+    e->keys = (orbx_kp*)q; q += up((size_t)n * sizeof(orbx_kp));
+    e->uRight = (float*)q; q += up((size_t)n * 4);
+    e->desc = (uint4*)q; q += up((size_t)n * 32);
+    e->cellStart = (int*)q; q += up((SP_CELLS + 1) * 4);
+    e->items = (int*)q;
+    e->key = key; e->n = n; e->hasUR = hasUR; e->stamp = ++m->kfClock;
+    e->geo[0] = p->minX; e->geo[1] = p->minY; e->geo[2] = p->grid_w_inv; e->geo[3] = p->grid_h_inv;
+    *out = e;
+    return ORBX_OK;
+}
+
 extern "C" int orbm_fuse_search(orbm_t* m, const orbm_proj_params* p, const float* inv_level_sigma2, int check_chi2,
                                 const orbm_fuse_points* pts, const orbm_cur_frame* kf, int32_t* best_idx,
                                 uint16_t* best_dist) {
@@ -1210,9 +1275,18 @@ extern "C" int orbm_fuse_search(orbm_t* m, const orbm_proj_params* p, const floa
     F.level = (const int32_t*)stg.in(pts->level, (size_t)n * 4);
     F.valid = (const uint8_t*)stg.in(pts->valid, n);
     F.desc = (const uint4*)stg.in(pts->desc, (size_t)n * 32);
-    S.keys = (const orbx_kp*)stg.in(kf->keys_un, (size_t)nC * sizeof(orbx_kp));
-    S.uRight = (const float*)stg.in(kf->u_right, (size_t)nC * 4);
-    S.cdesc = (const uint4*)stg.in(kf->desc, (size_t)nC * 32);
+    // keyframe cache: a hinted keyframe (orbm_keyframe_hint) that is resident skips its upload and the grid build
+    const uint64_t hint = m->kfHint;
+    m->kfHint = 0;
+    orbm_handle::KfEntry* hit = (hint && nC) ? kf_lookup(m, hint, nC, kf->u_right != nullptr, p) : nullptr;
+    if (hit) {
+        m->kfHits++;
+        S.keys = hit->keys; S.uRight = hit->hasUR ? hit->uRight : nullptr; S.cdesc = hit->desc;
+    } else {
+        S.keys = (const orbx_kp*)stg.in(kf->keys_un, (size_t)nC * sizeof(orbx_kp));
+        S.uRight = (const float*)stg.in(kf->u_right, (size_t)nC * 4);
+        S.cdesc = (const uint4*)stg.in(kf->desc, (size_t)nC * 32);
+    }
     for (int i = 0; i < ORBX_MAX_LEVELS; i++) F.invSigma2[i] = i < p->nlevels ? inv_level_sigma2[i] : 0.f;
     F.chi2 = check_chi2;
     if ((((uintptr_t)F.desc) | ((uintptr_t)S.cdesc)) & 15) FAIL(ORBX_EINVAL, "device descriptor matrices must be 16-byte aligned");
@@ -1224,13 +1298,28 @@ extern "C" int orbm_fuse_search(orbm_t* m, const orbm_proj_params* p, const floa
     int32_t* oIdx = hout ? W.take<int32_t>(n) : best_idx;
     unsigned short* oDist = hout ? W.take<unsigned short>(n) : best_dist;
     if (W.off > m->wsCap) FAIL(ORBX_ECUDA, "internal: workspace estimate too small (%zu > %zu)", W.off, m->wsCap);
-    CK(cudaMemsetAsync(cellCount, 0, SP_CELLS * sizeof(int), st));
-    if (nC) k_sp_grid_count<<<(nC + 255) / 256, 256, 0, st>>>(S, cellCount);
-    k_sp_grid_scan<<<1, 1024, 0, st>>>(cellCount, cellStart, cursor);
-    if (nC) k_sp_grid_fill<<<(nC + 255) / 256, 256, 0, st>>>(S, cursor, items);
-    k_sp_grid_sort<<<(SP_CELLS + 255) / 256, 256, 0, st>>>(cellStart, items);
+    if (hit) {
+        cellStart = hit->cellStart;
+        items = hit->items;
+    } else {
+        CK(cudaMemsetAsync(cellCount, 0, SP_CELLS * sizeof(int), st));
+        if (nC) k_sp_grid_count<<<(nC + 255) / 256, 256, 0, st>>>(S, cellCount);
+        k_sp_grid_scan<<<1, 1024, 0, st>>>(cellCount, cellStart, cursor);
+        if (nC) k_sp_grid_fill<<<(nC + 255) / 256, 256, 0, st>>>(S, cursor, items);
+        k_sp_grid_sort<<<(SP_CELLS + 255) / 256, 256, 0, st>>>(cellStart, items);
+        m->launches += 4;
+        if (hint && nC) {  // remember this keyframe (device-to-device copies of what was just staged and built)
+            orbm_handle::KfEntry* e = nullptr;
+            if ((rc = kf_claim(m, hint, nC, kf->u_right != nullptr, p, &e))) return rc;
+            CK(cudaMemcpyAsync(e->keys, S.keys, (size_t)nC * sizeof(orbx_kp), cudaMemcpyDeviceToDevice, st));
+            if (S.uRight) CK(cudaMemcpyAsync(e->uRight, S.uRight, (size_t)nC * 4, cudaMemcpyDeviceToDevice, st));
+            CK(cudaMemcpyAsync(e->desc, S.cdesc, (size_t)nC * 32, cudaMemcpyDeviceToDevice, st));
+            CK(cudaMemcpyAsync(e->cellStart, cellStart, (SP_CELLS + 1) * sizeof(int), cudaMemcpyDeviceToDevice, st));
+            CK(cudaMemcpyAsync(e->items, items, (size_t)nC * sizeof(int), cudaMemcpyDeviceToDevice, st));
+        }
+    }
     k_fuse_search<<<(n + 7) / 8, 256, 0, st>>>(S, F, cellStart, items, oIdx, oDist);
-    m->launches += 5;
+    m->launches += 1;
     CK(cudaGetLastError());
     if (hout) {
         CK(cudaMemcpyAsync(best_idx, oIdx, (size_t)n * 4, cudaMemcpyDeviceToHost, st));

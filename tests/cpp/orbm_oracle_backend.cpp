@@ -69,6 +69,7 @@ extern "C" {
 
 int orbm_create(int, orbm_t** out) { *out = new orbm_handle(); return ORBX_OK; }
 int orbm_destroy(orbm_t* m) { delete m; return ORBX_OK; }
+int orbm_keyframe_hint(orbm_t*, uint64_t) { return ORBX_OK; }
 const char* orbx_last_error_string(void) { return "oracle backend"; }
 
 int orbm_distance(orbm_t*, const uint8_t* a, const uint8_t* b, int n, uint16_t* d) {

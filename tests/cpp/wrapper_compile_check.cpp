@@ -165,6 +165,7 @@ struct FuseMapPoint : RelocMapPoint {
     void AddObservation(FuseKeyFrame*, int) {}
 };
 struct FuseKeyFrame {
+    long unsigned int mnId = 0;
     int N = 0;
     float fx = 0, fy = 0, cx = 0, cy = 0, mbf = 0, mnMinX = 0, mnMaxX = 0, mnMinY = 0, mnMaxY = 0;
     float mfGridElementWidthInv = 0, mfGridElementHeightInv = 0;
@@ -191,6 +192,7 @@ struct Sim3MapPoint : FuseMapPoint {
     template <class K> int PredictScale(float, K*) { return 0; }
 };
 struct Sim3KeyFrame {
+    long unsigned int mnId = 0;
     float fx = 0, fy = 0, cx = 0, cy = 0, mnMinX = 0, mnMaxX = 0, mnMinY = 0, mnMaxY = 0;
     float mfGridElementWidthInv = 0, mfGridElementHeightInv = 0;
     std::vector<float> mvScaleFactors;
@@ -371,6 +373,7 @@ struct MapPoint {
     cv::Mat GetDescriptor() { return cv::Mat(1, 32, CV_8UC1, d, 32); }
 };
 struct KeyFrame {
+    long unsigned int mnId = 0;
     float fx, fy, cx, cy, mnMinX, mnMaxX, mnMinY, mnMaxY, mfGridElementWidthInv, mfGridElementHeightInv;
     std::vector<float> mvScaleFactors;
     std::vector<cv::KeyPoint> mvKeysUn;
@@ -453,6 +456,7 @@ struct MapPoint {
     cv::Mat GetDescriptor() { return cv::Mat(1, 32, CV_8UC1, d, 32); }
 };
 struct KeyFrame {
+    long unsigned int mnId = 0;
     float fx, fy, cx, cy, mnMinX, mnMaxX, mnMinY, mnMaxY, mfGridElementWidthInv, mfGridElementHeightInv;
     std::vector<float> mvScaleFactors;
     std::vector<cv::KeyPoint> mvKeysUn;
@@ -516,6 +520,7 @@ static int run_search_by_sim3(const char* in, const char* out) {
     fclose(f);
     if (!ok) return 2;
     run_sim3b::KeyFrame K1, K2;
+    K1.mnId = 1; K2.mnId = 2;  // keyframe ids are unique (they key the device-side keyframe cache)
     S1.fill(K1, cam, sc, R1w, t1w);
     S2.fill(K2, cam, sc, R2w, t2w);
     for (int i = 0; i < n2; i++) S2.pts[i].idxIn2 = i;  // a map point of KF2 is observed in KF2 at its own index
@@ -566,6 +571,7 @@ struct MapPoint {
     void AddObservation(KeyFrame*, int idx) { action = 3; where = idx; }
 };
 struct KeyFrame {
+    long unsigned int mnId = 0;
     int N;
     float fx, fy, cx, cy, mbf, mnMinX, mnMaxX, mnMinY, mnMaxY, mfGridElementWidthInv, mfGridElementHeightInv;
     std::vector<float> mvScaleFactors, mvInvLevelSigma2, mvuRight;

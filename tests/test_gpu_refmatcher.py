@@ -30,3 +30,38 @@ def test_dropin_on_gpu_vs_reference_method(gpu_exe, tmp_path, name, make):
         assert a.shape == b.shape and np.array_equal(a, b), \
             f"{S.METHOD_NAMES[sc.method]} seed {seed}: reference returned {pa['ret']}, GPU drop-in {int(b[0])}, " \
             f"{int((a != b).sum()) if a.shape == b.shape else 'shape'} dump words differ"
+
+
+def test_keyframe_cache_reuses_staged_keyframe(tmp_path):
+    """orbm_keyframe_hint: the second orbm_fuse_search against the same (immutable) keyframe takes its keypoints,
+    descriptors and grid from the handle's cache — same results, one cache hit, four launches fewer; a different
+    keyframe under another key misses."""
+    import ctypes as C
+    import orbslam2_b200 as ob
+    from orbslam2_b200 import _lib
+    from orbslam2_b200.synth import synth_tracking_pair
+    kf, other = synth_tracking_pair(1200, 3, stereo=True)
+    m = ob.ORBmatcher()
+    L = m._L
+    L.orbm_keyframe_hint.argtypes = [C.c_void_p, C.c_uint64]
+    L.orbm_keyframe_cache_hits.restype = C.c_int64
+    L.orbm_keyframe_cache_hits.argtypes = [C.c_void_p]
+    rng = np.random.default_rng(1)
+    n = 900
+    src = rng.integers(0, kf.N, n)
+    pts = dict(u=kf.mvKeysUn["x"][src] + rng.normal(0, 1, n).astype(np.float32), v=kf.mvKeysUn["y"][src] + rng.normal(0, 1, n).astype(np.float32),
+               ur=np.zeros(n, np.float32), level=kf.mvKeysUn["octave"][src].astype(np.int32), valid=np.ones(n, np.uint8),
+               desc=kf.mDescriptors[src].copy())
+    base = m.FuseSearch(kf, pts, th=3.0, check_chi2=False)
+    res, launches = [], []
+    for key in (7, 7, 7, 9):
+        _lib.check(L.orbm_keyframe_hint(m._h, key))
+        l0 = m.launch_count()
+        res.append(m.FuseSearch(kf if key == 7 else other, pts, th=3.0, check_chi2=False))
+        launches.append(m.launch_count() - l0)
+    assert L.orbm_keyframe_cache_hits(m._h) == 2
+    assert launches[0] - launches[1] == 4 and launches[1] == launches[2] and launches[3] == launches[0]
+    for r in res[:3]:
+        assert np.array_equal(r[0], base[0]) and np.array_equal(r[1], base[1])
+    assert not np.array_equal(res[3][0], base[0])
+    m.close()
