@@ -41,7 +41,7 @@ PARAMS = dict(nfeatures=NFEAT, scaleFactor=1.2, nlevels=8, iniThFAST=20, minThFA
               edgeThreshold=19)
 METRIC = "orb_extract_frames_per_s_640x480_1000kp"
 UNIT = "frames/s"
-N_DISTINCT = 16  # distinct synthetic frames; a batch tiles them (content repeats, addresses do not)
+N_DISTINCT = 64  # distinct synthetic frames; a batch tiles them (content repeats, addresses do not)
 
 
 def parse_args():

@@ -2,7 +2,7 @@ import sys, time; sys.path.insert(0,'.'); sys.path.insert(0,'tests')
 import numpy as np, torch
 import orbslam2_b200 as ob
 import bench_configs as BC
-import os; cfg = BC.CFG[int(os.environ.get("CFG","2"))]; n=64
+import os; cfg = BC.CFG[int(os.environ.get("CFG","2"))]; n=int(os.environ.get("NPAIRS","64"))
 left,right = BC.synth_inputs(cfg, 0, n)
 p = BC.params_for(cfg)
 exL, exR = ob.ORBextractor(**p), ob.ORBextractor(**p)
@@ -34,3 +34,7 @@ def dev():
 def devfull():
     dev(); ob.compute_stereo_matches(exL,exR,386.1,0.0,718.8)
 print("device both ms", T(dev), "device full", T(devfull))
+
+for ch in (0, n, max(n // 4, 1)):
+    exL.set_chunk(ch); exR.set_chunk(ch)
+    print("device chunk", ch, "both ms", T(dev), "full", T(devfull))
