@@ -340,8 +340,10 @@ static int bow_run(orbm_t* m, const orbm_bow_side* a, const orbm_bow_side* b, in
     while (rounds < SPEC && hf[rounds]) rounds++;
     if (rounds == SPEC) {
         for (;;) {
-            const int R = 4;
-            if (round + R > maxRounds) FAIL(ORBX_ECUDA, "internal: greedy resolution did not converge in %d rounds", maxRounds);
+            // rounds per host synchronisation double (4, 8, 16, ...): a long claim chain (dense repeated texture, every
+            // query displaced by the previous one) costs O(log) synchronisations and at most twice the rounds it needs
+            const int R = std::min(std::max(4, round), maxRounds - round);
+            if (R <= 0) FAIL(ORBX_ECUDA, "internal: greedy resolution did not converge in %d rounds", maxRounds);
             enqueueRounds(R);
             CK(cudaGetLastError());
             CK(cudaMemcpyAsync(m->hFlags, flags, (size_t)round * sizeof(int), cudaMemcpyDeviceToHost, st));
@@ -515,8 +517,10 @@ static int bow_batch_run(orbm_t* m, int npairs, const orbm_bow_side* a, const or
     while (rounds < SPEC && hf[rounds]) rounds++;
     if (maxPosA > 0 && rounds == SPEC) {
         for (;;) {
-            const int R = 4;
-            if (round + R > maxRounds) FAIL(ORBX_ECUDA, "internal: greedy resolution did not converge in %d rounds", maxRounds);
+            // rounds per host synchronisation double (4, 8, 16, ...): a long claim chain (dense repeated texture, every
+            // query displaced by the previous one) costs O(log) synchronisations and at most twice the rounds it needs
+            const int R = std::min(std::max(4, round), maxRounds - round);
+            if (R <= 0) FAIL(ORBX_ECUDA, "internal: greedy resolution did not converge in %d rounds", maxRounds);
             enqueueRounds(R);
             CK(cudaGetLastError());
             CK(cudaMemcpyAsync(m->hFlags, flags, (size_t)round * sizeof(int), cudaMemcpyDeviceToHost, st));

@@ -663,8 +663,12 @@ extern "C" int orbx_extract_batch_submit(orbx_t* h, const uint8_t* imgs, int bat
     int chunk = batch;
     if (!h->profiling) {
         if (hostIO || h->chunk > 0) {
-            chunk = h->chunk > 0 ? h->chunk : 48;
-            if (batch < 2 * chunk) chunk = batch;
+            // default chunk: about 14.7 MB of input (48 frames of 640x480, the measured optimum there), so that larger
+            // frames still pipeline (KITTI-shape frames 31 at a time), but never fewer than 8 frames: the quadtree and the
+            // launch sequence are latency bound, so 2-frame chunks of 4K images were measured slower than one 16-frame chunk
+            const int byBytes = (int)std::max<size_t>(8, std::min<size_t>(48, (size_t)48 * 640 * 480 / ((size_t)w * hgt)));
+            chunk = h->chunk > 0 ? h->chunk : byBytes;
+            if (batch < 2 * chunk) chunk = h->chunk > 0 || batch < 4 ? batch : std::max(1, batch / 2);
         } else if (batch >= 96) {
             chunk = (batch + 1) / 2;  // device buffers: two halves on the two compute streams, so one half's kernel
                                       // tails and its latency-bound quadtree overlap the other's kernels (measured +2 %)

@@ -995,8 +995,10 @@ static int sp_run(orbm_handle* m, int mode, const orbm_proj_params* p, float nnR
     while (rounds < SPEC && hf[rounds]) rounds++;
     if (rounds == SPEC) {  // not converged yet: further rounds with the flags read in between, then finish again
         for (;;) {
-            const int R = 4;
-            if (round + R > maxRounds) FAIL(ORBX_ECUDA, "internal: greedy resolution did not converge in %d rounds", maxRounds);
+            // rounds per host synchronisation double (4, 8, 16, ...): a long claim chain (dense repeated texture, every
+            // query displaced by the previous one) costs O(log) synchronisations and at most twice the rounds it needs
+            const int R = std::min(std::max(4, round), maxRounds - round);
+            if (R <= 0) FAIL(ORBX_ECUDA, "internal: greedy resolution did not converge in %d rounds", maxRounds);
             enqueueRounds(R);
             CK(cudaGetLastError());
             CK(cudaMemcpyAsync(m->hFlags, flags, (size_t)round * sizeof(int), cudaMemcpyDeviceToHost, st));

@@ -59,15 +59,16 @@ def test_taken_mask_no_orientation_and_empty():
     assert got[0] == 0 and (got[1] < 0).all()
 
 
-def test_chain_of_claims():
+@pytest.mark.parametrize("K", [12, 70])
+def test_chain_of_claims(K):
     """A worst case for the fixed point: K queries with identical descriptors all prefer keypoint 0, then 1, ... —
-    query k must end on keypoint k (K rounds), exactly as the sequential loop."""
+    query k must end on keypoint k (K rounds), exactly as the sequential loop. K = 70 goes through several of the
+    doubling round groups (4 speculative rounds, then 4, 8, 16, 32, ... per host synchronisation)."""
     import orbslam2_b200 as ob
     from orbslam2_b200.frame import Frame
     from orbslam2_b200.extractor import KP_DTYPE
-    K = 12
     sf = np.float32(1.2) ** np.arange(8, dtype=np.float32)
-    kc = np.zeros(K, KP_DTYPE); kc["x"] = 320 + np.arange(K) * 0.5; kc["y"] = 240; kc["octave"] = 0
+    kc = np.zeros(K, KP_DTYPE); kc["x"] = 320 + np.arange(K) * 0.25; kc["y"] = 240; kc["octave"] = 0
     dc = np.zeros((K, 32), np.uint8)
     for k in range(K):  # keypoint k differs from the query descriptor in k bits -> strictly increasing distance
         for b in range(k):
