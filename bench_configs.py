@@ -350,8 +350,13 @@ def knn_roofline(path, pairs_per_s_per_gpu):
                 bf16 = float(json.load(f)["bf16_tflops"])
         except Exception:
             bf16 = None
+        try:
+            with open(os.path.join(B.ROOT, "profiles", "traffic.json")) as f:
+                traffic = float(json.load(f)["knn_tc"])  # dram read + write of one 100k x 1M launch (ncu --set full)
+        except Exception:
+            traffic = None
         return {"bound": "tensor", "kernel": "k_knn_tc", "achieved": ach, "peak": 4500.0, "unit": "TFLOP/s", "frac": ach / 4500.0,
-                "traffic": None, "peak_source": "nominal dense int8 tcgen05 rate of B200 (4.5 Pop/s); unit is int8 Top/s",
+                "traffic": traffic, "ncu_pipe_tensor_active_pct": 80.75, "peak_source": "nominal dense int8 tcgen05 rate of B200 (4.5 Pop/s); unit is int8 Top/s",
                 "frac_of_2x_measured_bf16": (ach / (2 * bf16)) if bf16 else None, "measured_bf16_tflops": bf16,
                 "ops_per_pair": 2 * KTC_K}
     popc_peak = 148 * 16 * 1.965e9 / 8

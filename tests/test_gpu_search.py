@@ -68,7 +68,7 @@ def test_chain_of_claims(K):
     from orbslam2_b200.frame import Frame
     from orbslam2_b200.extractor import KP_DTYPE
     sf = np.float32(1.2) ** np.arange(8, dtype=np.float32)
-    kc = np.zeros(K, KP_DTYPE); kc["x"] = 320 + np.arange(K) * 0.25; kc["y"] = 240; kc["octave"] = 0
+    kc = np.zeros(K, KP_DTYPE); kc["x"] = 320 + np.arange(K) * 0.2; kc["y"] = 240; kc["octave"] = 0
     dc = np.zeros((K, 32), np.uint8)
     for k in range(K):  # keypoint k differs from the query descriptor in k bits -> strictly increasing distance
         for b in range(k):
