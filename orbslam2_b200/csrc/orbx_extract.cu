@@ -705,7 +705,7 @@ extern "C" int orbx_extract_batch_submit(orbx_t* h, const uint8_t* imgs, int bat
         rc = copy_in(h, st, imgs, 0, batch, w, hgt, stride, img_stride);
         if (rc != ORBX_OK) return rc;
         stamp(h, 1);
-        rc = launch_chain(h, st, 0, batch, true);
+        rc = launch_chain(h, st, 0, batch, h->profiling);  // (stamps off => a small batch forks the blur onto the side stream)
         if (rc != ORBX_OK) return rc;
         CK(cudaGetLastError());
         if (oneCopy) {

@@ -152,3 +152,35 @@ def test_distinctive_descriptors_vs_oracle(ob):
     ei, em = P.distinctive_descriptors(desc, off)
     assert np.array_equal(bi, ei) and np.array_equal(bm[counts > 0], em[counts > 0])
     assert bi[0] == -1 and bi[1] == 0 and bi[8] == 0
+
+
+def test_knn2_full_size_properties(ob):
+    """BASELINE config 4 at full size (100k x 1M) on the tensor-core kernel, checked through size-independent properties
+    (the oracle cannot scan 10^11 pairs in a test): the reported best distance IS the distance to the reported index
+    (recomputed with the batched DescriptorDistance), best <= second best, a query that is an exact copy of train rows
+    reports distance 0 at the LOWEST such row, and 2000 sampled queries equal the oracle's sequential scan."""
+    import torch
+    m = ob.ORBmatcher(); P = OraclePrims()
+    t, q = synth_descriptors(1000000, 100000, seed=7, dup=1000)
+    # plant exact copies: query j (j < 500) = train row 5000 + 7 j, which is also copied to two later rows
+    for j in range(500):
+        r = 5000 + 7 * j
+        t[500000 + j] = t[r]; t[900000 + 3 * j] = t[r]; q[j] = t[r]
+    dt = torch.from_numpy(t).cuda(); dq = torch.from_numpy(q).cuda()
+    m.set_train(dt)
+    i1, d1, d2 = m.knn2(dq)
+    assert m.last_knn_path() == 2
+    i1 = i1.cpu().numpy(); d1 = d1.cpu().numpy().view(np.uint16); d2 = d2.cpu().numpy().view(np.uint16)
+    assert i1.min() >= 0 and i1.max() < len(t)
+    assert (d1 <= d2).all() and d2.max() <= 256
+    bits = np.unpackbits(q ^ t[i1], axis=1).sum(axis=1)
+    assert np.array_equal(bits.astype(np.uint16), d1), "best distance is not the distance to the reported index"
+    for j in range(500):
+        assert d1[j] == 0 and d2[j] == 0            # three identical train rows: the second best counts multiplicity
+    # lowest index wins: no earlier row of t may equal the query
+    for j in (0, 17, 499):
+        eq = np.flatnonzero((t[:i1[j] + 1] == q[j]).all(axis=1))
+        assert eq[0] == i1[j]
+    pick = np.sort(np.random.default_rng(3).choice(len(q), 2000, replace=False))
+    o1, e1, e2 = P.knn2(q[pick], t, popcnt=True)
+    assert np.array_equal(i1[pick], o1) and np.array_equal(d1[pick], e1) and np.array_equal(d2[pick], e2)
