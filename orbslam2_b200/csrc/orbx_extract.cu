@@ -82,6 +82,7 @@ struct orbx_handle {
     float *dMapX = nullptr, *dMapY = nullptr;  // rectification maps (output size mapW x mapH)
     int mapW = 0, mapH = 0;
     uint8_t *dRaw = nullptr, *dGray = nullptr;  // staged source images / grey source of the remap
+    int* dStSad = nullptr; float *dStU = nullptr, *dStZ = nullptr; size_t stCap = 0;  // stereo scratch (orbx_stereo_match*)
     size_t rawCap = 0, grayCap = 0;
     orbx_kp* dKpsUn = nullptr;
     size_t kpsUnCap = 0;
@@ -378,6 +379,7 @@ extern "C" int orbx_destroy(orbx_t* h) {
         cudaStreamDestroy(h->sComp[1]);
     }
     cudaFree(h->dMapX); cudaFree(h->dMapY); cudaFree(h->dRaw); cudaFree(h->dGray); cudaFree(h->dKpsUn);
+    cudaFree(h->dStSad); cudaFree(h->dStU); cudaFree(h->dStZ);
     if (h->sSide) {
         cudaEventDestroy(h->evFork);
         cudaEventDestroy(h->evJoin);
@@ -1047,3 +1049,17 @@ OrbxView orbx_view(orbx_handle* h) {
                     h->hCounts, h->dSelCount};
 }
 void orbx_count_launch(orbx_handle* h, int k) { h->launches += k; }
+// Scratch of Frame::ComputeStereoMatches on the LEFT extractor's handle (freed by orbx_destroy): SAD per left keypoint and,
+// for host outputs, the device copies of mvuRight / mvDepth.
+int orbx_stereo_scratch(orbx_handle* h, size_t need, int** sad, float** u, float** z) {
+    if (need > h->stCap) {
+        cudaFree(h->dStSad); cudaFree(h->dStU); cudaFree(h->dStZ);
+        h->dStSad = nullptr; h->dStU = h->dStZ = nullptr; h->stCap = 0;
+        CK(cudaMalloc(&h->dStSad, need * 4));
+        CK(cudaMalloc(&h->dStU, need * 4));
+        CK(cudaMalloc(&h->dStZ, need * 4));
+        h->stCap = need;
+    }
+    *sad = h->dStSad; *u = h->dStU; *z = h->dStZ;
+    return ORBX_OK;
+}

@@ -25,6 +25,7 @@ struct OrbxView {
 };
 OrbxView orbx_view(orbx_handle* h);
 void orbx_count_launch(orbx_handle* h, int k);
+int orbx_stereo_scratch(orbx_handle* h, size_t need, int** sad, float** u, float** z);
 
 // ------------------------------------------------------------------------------------------------ K7 knn2
 #define KNN_THREADS 128
@@ -718,10 +719,7 @@ extern "C" int orbm_distance(orbm_t* m, const uint8_t* a, const uint8_t* b, int 
 }
 
 // ------------------------------------------------------------------------------------------------ stereo ABI
-struct StereoScratch {
-    int* dSad = nullptr; float* dU = nullptr; float* dZ = nullptr; size_t cap = 0; int device = -1;
-};
-static thread_local StereoScratch g_ss;
+// (the SAD / uRight / depth scratch lives on the left extractor's handle: orbx_stereo_scratch, freed by orbx_destroy)
 
 extern "C" int orbx_stereo_match_batch(orbx_t* left, orbx_t* right, float mbf, float minD, float maxD, float* uRight,
                                        float* depth, int cap) {
@@ -735,19 +733,12 @@ extern "C" int orbx_stereo_match_batch(orbx_t* left, orbx_t* right, float mbf, f
     CK(cudaSetDevice(A.device));
     const int batch = A.lastBatch, stride = A.hp->selStride;
     const size_t need = (size_t)batch * stride;
-    if (g_ss.device != A.device || g_ss.cap < need) {
-        cudaFree(g_ss.dSad); cudaFree(g_ss.dU); cudaFree(g_ss.dZ);
-        g_ss = StereoScratch();
-        CK(cudaMalloc(&g_ss.dSad, need * 4));
-        CK(cudaMalloc(&g_ss.dU, need * 4));
-        CK(cudaMalloc(&g_ss.dZ, need * 4));
-        g_ss.cap = need;
-        g_ss.device = A.device;
-    }
+    int* dSad = nullptr; float *dU = nullptr, *dZ = nullptr;
+    { int rcS = orbx_stereo_scratch((orbx_handle*)left, need, &dSad, &dU, &dZ); if (rcS != ORBX_OK) return rcS; }
     cudaStream_t st = A.stream;
     CK(cudaStreamSynchronize(B.stream));  // right extractor's results must be complete (its extract call already synced)
-    float* oU = A.outSpace == ORBX_MEM_DEVICE ? uRight : g_ss.dU;
-    float* oZ = A.outSpace == ORBX_MEM_DEVICE ? depth : g_ss.dZ;
+    float* oU = A.outSpace == ORBX_MEM_DEVICE ? uRight : dU;
+    float* oZ = A.outSpace == ORBX_MEM_DEVICE ? depth : dZ;
     const int oStride = A.outSpace == ORBX_MEM_DEVICE ? cap : stride;
     int maxN = 0;
     for (int f = 0; f < batch; f++) maxN = std::max(maxN, A.hCounts[f]);
@@ -755,7 +746,7 @@ extern "C" int orbx_stereo_match_batch(orbx_t* left, orbx_t* right, float mbf, f
     if (maxN == 0) maxN = 1;
     k_stereo_match<<<dim3((maxN + 7) / 8, batch), 256, 0, st>>>(A.dPlan, A.dKps, A.dDesc, A.dNOut, A.dPyr, B.dKps, B.dDesc,
                                                                B.dNOut, B.dSelCount, B.dPyr, mbf, minD, maxD, oU, oZ,
-                                                               g_ss.dSad, oStride);
+                                                               dSad, oStride);
     int P2 = 1;
     while (P2 < maxN) P2 <<= 1;
     // more than 6144 left keypoints need over 48 KB of dynamic shared memory: opt in (up to 227 KB = 16384 keypoints,
@@ -770,7 +761,7 @@ extern "C" int orbx_stereo_match_batch(orbx_t* left, orbx_t* right, float mbf, f
             optedIn[A.device] = P2 * 8;
         }
     }
-    k_stereo_cut<<<batch, 1024, (size_t)P2 * 8, st>>>(A.dPlan, A.dNOut, g_ss.dSad, oU, oZ, oStride, P2);
+    k_stereo_cut<<<batch, 1024, (size_t)P2 * 8, st>>>(A.dPlan, A.dNOut, dSad, oU, oZ, oStride, P2);
     orbx_count_launch((orbx_handle*)left, 2);
     CK(cudaGetLastError());
     if (A.outSpace == ORBX_MEM_HOST) {

@@ -133,6 +133,14 @@ int orbm_search_by_bow(orbm_t*, const orbm_bow_side* a, const orbm_bow_side* b, 
     return ORBX_OK;
 }
 
+int orbm_search_by_bow_batch(orbm_t* m, int npairs, const orbm_bow_side* a, const orbm_bow_side* b, const int* n_pos_a,
+                             const int* n_pos_b, float nn_ratio, int th, int strict, int check_orientation,
+                             int32_t* const* match_a, int* nmatches) {
+    for (int k = 0; k < npairs; k++)
+        orbm_search_by_bow(m, a + k, b + k, n_pos_a[k], n_pos_b[k], nn_ratio, th, strict, check_orientation, match_a[k], nmatches + k);
+    return ORBX_OK;
+}
+
 int orbm_search_for_triangulation(orbm_t*, const orbm_bow_side* a, const orbm_bow_side* b, int, int,
                                   const orbm_triangulation* t, int th, int check_orientation, int32_t* match_a, int* nmatches) {
     std::vector<uint8_t> oa, ob;

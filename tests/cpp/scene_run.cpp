@@ -319,6 +319,27 @@ int main(int argc, char** argv) {
         putList(out, o);
         break;
     }
+    case 12: {  // Tracking::Relocalization, src/Tracking.cc:1465-1490: every candidate keyframe against the current frame.
+                // The reference loops over the single call; the drop-in's batched overload replaces the loop.
+        const int K = W.nViews - 1;
+        std::vector<std::vector<MapPoint*> > vvp(K);
+        std::vector<int> nm(K, 0);
+#ifdef SCENE_REF
+        for (int k = 0; k < K; k++) nm[k] = matcher.SearchByFboW(&W.kfs[k + 1], W.frames[0], vvp[k]);
+#else
+        std::vector<KeyFrame*> vpKFs(K);
+        for (int k = 0; k < K; k++) vpKFs[k] = &W.kfs[k + 1];
+        nm = matcher.SearchByFboW(vpKFs, W.frames[0], vvp);
+#endif
+        ret = 0;
+        for (int k = 0; k < K; k++) {
+            ret += nm[k];
+            std::vector<int32_t> o(1, nm[k]);
+            for (MapPoint* p : vvp[k]) o.push_back(W.id(p));
+            putList(out, o);
+        }
+        break;
+    }
     default:
         fprintf(stderr, "unknown method %d\n", method);
         return 2;

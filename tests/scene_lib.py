@@ -628,3 +628,29 @@ def scene_fuse_sim3(seed, th=4.0, s=1.0, n_points=1300):
     Scw[:3, :3] = (f64(s) * T[:3, :3].astype(f64)).astype(f32); Scw[:3, 3] = (f64(s) * T[:3, 3].astype(f64)).astype(f32)
     S.farr = [Scw]
     return S
+
+
+BOW_RELOC_BATCH = 12
+METHOD_NAMES[BOW_RELOC_BATCH] = "SearchByFboW(candidate KFs, F) batched"
+
+
+def scene_bow_reloc_batch(seed, K=5, nnratio=0.75, n_points=1000):
+    """Tracking::Relocalization (src/Tracking.cc:1465-1490): ORBmatcher(0.75, true).SearchByFboW(pKF, mCurrentFrame, ...) for
+    every candidate keyframe. The reference side loops over the single call; the drop-in side uses the batched overload."""
+    blob, voc = _vocab()
+    cal = default_cal(stereo=True)
+    poses = [pose(0.03, t=(0.08, 0.0, 0.1), rz=0.05)] + [pose(0.01 * k, t=(0.05 * k, 0.0, 0.02 * k)) for k in range(K)]
+    W = PhysWorld(seed, n_points, poses, cal, vocab_blob=blob, dup_frac=0.2)
+    S = _new_scene(BOW_RELOC_BATCH, W, 0, nnratio, True)
+    F = W.view(0, 0, roll=3.0)
+    attach_featvec(F, voc)
+    S.views = [F]
+    for k in range(K):
+        kf = W.view(k + 1, 1, detect=0.85 - 0.1 * k)   # ragged keyframe sizes
+        _mps_for_view(S, W, kf, frac=0.8)
+        _observe(S, kf, k + 1)
+        attach_featvec(kf, voc)
+        S.views.append(kf)
+    for m in S.mps:
+        m.bad = int(W.rng.random() < 0.04)
+    return S

@@ -179,6 +179,7 @@ SCENES = [
     ("fuse_mono", lambda s: S.scene_fuse(s + 10, stereo=False, th=5.0)),
     ("fuse_sim3", lambda s: S.scene_fuse_sim3(s)),
     ("fuse_sim3_s.9", lambda s: S.scene_fuse_sim3(s + 10, s=0.9, th=6.0)),
+    ("bow_reloc_batch", lambda s: S.scene_bow_reloc_batch(s)),
 ]
 MIN_RET = {"sim3_s1.05": 50}
 
