@@ -181,7 +181,13 @@ __global__ void __launch_bounds__(256, 3) k_orient_desc(const DevPlan* __restric
         // ---- steered BRIEF on the blurred level
         const float factorPI = (float)(3.1415926535897932384626433832795 / 180.f);
         const float rad = __fmul_rn(angle, factorPI);
-        const float a = (float)cos((double)rad), b = (float)sin((double)rad);
+        // cos / sin of the float angle as glibc's cosf / sinf give them (double evaluation, one rounding); sincos shares the
+        // argument reduction between the two (orient_desc 0.410 -> 0.383 ms per 384 frames). Measured and dropped: evaluating
+        // the warp's four keypoints in one sincos (lane k = keypoint k) with four blurred patches staged per warp — 0.42 ms,
+        // the two-phase loop costs more than the three saved evaluations.
+        double sd, cd;
+        sincos((double)rad, &sd, &cd);
+        const float a = (float)cd, b = (float)sd;
         const uint8_t* ctr = (const uint8_t*)blr + 18 * 40 + 18 + shB;  // (row, col) of the keypoint inside the staged patch
         int t[16];
 #pragma unroll
