@@ -161,6 +161,19 @@ int orbm_knn2(orbm_t* m, const uint8_t* q, int nq, const uint8_t* t, int nt, int
  * bit-identical on every path. orbm_last_knn_path: 1 = POPC, 2 = tensor cores (+ POPC for the < 256-row remainder). */
 int orbm_set_knn_mode(orbm_t* m, int mode);
 int orbm_last_knn_path(orbm_t* m);
+/* Allocation-free brute-force 2-NN. NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same results as orbm_knn2 (POPC path: k_knn2 over train splits + the ordered merge), but no handle and no allocation of
+ * any kind: the per-split partial results live in a file-scope `static __device__` array inside liborbx (16 MiB, held by
+ * every GPU that loads the library until exit). q (nq x 32), t (nt x 32), i1 / d1 / d2 (nq entries) are DEVICE pointers on
+ * `device`, 16-byte aligned; the two kernels are enqueued on `stream` (a cudaStream_t, NULL = default stream) and the call
+ * returns without synchronising: the outputs are valid once the stream reaches that point.
+ * Limit: nq <= 65536 per call (ORBX_EINVAL beyond it; split the batch or use orbm_knn2); nt is unlimited.
+ * Every call on a device shares the one scratch array: calls that overlap on the GPU (different streams, or two threads)
+ * RACE — serialise them. Nothing in the array has to start at zero (each call writes every entry it later reads).
+ * The first call on a device looks the array's address up (cudaGetSymbolAddress): make it outside graph capture. */
+int orbm_knn2_static(int device, void* stream, const uint8_t* q, int nq, const uint8_t* t, int nt, int32_t* i1, uint16_t* d1,
+                     uint16_t* d2);
 /* Windowed search: query a scans candidates cand_idx[cand_off[a] .. cand_off[a+1]) in list order, skipping entries
  * with cand_skip[c] != 0 (cand_skip may be NULL). Outputs best/second index (-1 = none) and distance (256 = none). */
 int orbm_window_search(orbm_t* m, const uint8_t* q, int nq, const int32_t* cand_off, const int32_t* cand_idx,

@@ -30,7 +30,7 @@ SYMBOLS = ["orbx_create", "orbx_destroy", "orbx_set_memory_space", "orbx_extract
            "orbx_undistort_keypoints",
            "orbx_max_keypoints", "orbx_set_chunk", "orbx_level_count", "orbx_tables", "orbx_level_size", "orbx_pyramid_level",
            "orbx_blurred_level", "orbx_pyramid_bytes", "orbx_pyramid_all", "orbx_candidates", "orbx_stereo_match", "orbx_stereo_match_batch", "orbm_create",
-           "orbm_destroy", "orbm_set_memory_space", "orbm_set_train", "orbm_knn2", "orbm_set_knn_mode", "orbm_last_knn_path", "orbm_window_search", "orbm_distance",
+           "orbm_destroy", "orbm_set_memory_space", "orbm_set_train", "orbm_knn2", "orbm_set_knn_mode", "orbm_last_knn_path", "orbm_knn2_static", "orbm_window_search", "orbm_distance",
            "orbm_search_by_projection", "orbm_search_by_bow", "orbm_search_by_bow_batch", "orbm_fuse_search", "orbm_keyframe_hint", "orbm_keyframe_cache_hits", "orbm_search_kf_projection", "orbm_search_for_initialization", "orbm_search_for_triangulation", "orbm_search_for_triangulation_batch", "orbm_search_local_points", "orbm_search_stats", "orbm_distinctive_descriptors",
            "orbx_stream", "orbm_stream", "orbx_launch_count", "orbm_launch_count", "orbx_stage_ms", "orbx_set_profiling",
            "orbv_create", "orbv_destroy", "orbv_info", "orbv_set_memory_space", "orbv_transform_batch", "orbv_score_batch",
@@ -119,6 +119,7 @@ def lib():
     L.orbm_set_memory_space.argtypes = [vp, ci, ci]
     L.orbm_set_train.argtypes = [vp, vp, ci]
     L.orbm_knn2.argtypes = [vp, vp, ci, vp, ci, vp, vp, vp]
+    L.orbm_knn2_static.argtypes = [ci, vp, vp, ci, vp, ci, vp, vp, vp]
     L.orbm_set_knn_mode.argtypes = [vp, ci]
     L.orbm_last_knn_path.argtypes = [vp]
     L.orbm_window_search.argtypes = [vp, vp, ci, vp, vp, vp, vp, ci, vp, vp, vp, vp]

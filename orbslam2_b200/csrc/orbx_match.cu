@@ -644,6 +644,71 @@ extern "C" int orbm_knn2(orbm_t* m, const uint8_t* q, int nq, const uint8_t* t, 
     return ORBX_OK;
 }
 
+// ------------------------------------------------------------------------------------------------ allocation-free 2-NN
+// orbm_knn2_static: k_knn2 + k_knn2_merge (the POPC path of orbm_knn2) for callers that cannot call cudaMalloc (CUDA graph
+// capture, tight serving loops, harnesses that forbid it). The per-split partial results — the scratch orbm_knn2 keeps in
+// m->dPartial — live in a file-scope device array of fixed size; every GPU that loads liborbx holds it until exit.
+// No handle, no staging: inputs and outputs are DEVICE pointers; the kernels are enqueued on the caller's stream.
+#define KNN_STATIC_MAX_QUERIES 65536
+#define KNN_STATIC_MAX_SPLITS 16
+static __device__ __align__(256) int4 g_knn2_static_partial[(size_t)KNN_STATIC_MAX_QUERIES * KNN_STATIC_MAX_SPLITS];  // 16 MiB
+
+// In host code `g_knn2_static_partial` is only a stand-in for the symbol, NOT a device address: the address is fetched once
+// per device, with that device current, by cudaGetSymbolAddress.
+static int knn2_static_scratch(int device, int4** out, int* smCount) {
+    static std::mutex mu;
+    static int4* addr[64] = {nullptr};
+    static int sms[64] = {0};
+    if (device < 0 || device >= 64) FAIL(ORBX_EINVAL, "device %d out of range", device);
+    std::lock_guard<std::mutex> lk(mu);
+    if (!addr[device]) {
+        int4* p = nullptr;
+        CK(cudaGetSymbolAddress((void**)&p, g_knn2_static_partial));
+        if (!p) FAIL(ORBX_ECUDA, "cudaGetSymbolAddress returned a null address for the static 2-NN scratch");
+        CK(cudaDeviceGetAttribute(&sms[device], cudaDevAttrMultiProcessorCount, device));
+        addr[device] = p;
+    }
+    *out = addr[device];
+    *smCount = sms[device];
+    return ORBX_OK;
+}
+
+extern "C" int orbm_knn2_static(int device, void* stream, const uint8_t* q, int nq, const uint8_t* t, int nt, int32_t* i1,
+                                uint16_t* d1, uint16_t* d2) {
+    if (!q || !t || !i1 || !d1 || !d2 || nq < 0 || nt < 1) FAIL(ORBX_EINVAL, "bad argument");
+    if (nq > KNN_STATIC_MAX_QUERIES)
+        FAIL(ORBX_EINVAL, "orbm_knn2_static: %d queries exceed the static scratch (max %d per call; split the batch or use orbm_knn2)",
+             nq, KNN_STATIC_MAX_QUERIES);
+    if ((((uintptr_t)q) | ((uintptr_t)t)) & 15) FAIL(ORBX_EINVAL, "device descriptor matrices must be 16-byte aligned");
+    if (nq == 0) return ORBX_OK;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        FAIL(ORBX_ECUDA, "no CUDA device: liborbx has no CPU path");
+    }
+    CK(cudaSetDevice(device));
+    int4* partial = nullptr;
+    int smCount = 0;
+    const int src = knn2_static_scratch(device, &partial, &smCount);
+    if (src != ORBX_OK) return src;
+    cudaStream_t st = (cudaStream_t)stream;
+    // the same split rule as orbm_knn2's POPC path, capped by the scratch: splits * nq <= the array
+    const int qblocks = (nq + KNN_THREADS * KNN_QPT - 1) / (KNN_THREADS * KNN_QPT);
+    int splits = 1;
+    const int target = smCount * 8;
+    while (qblocks * splits < target && (nt / (splits * 2)) >= 4 * KNN_TILE && splits * 2 <= KNN_STATIC_MAX_SPLITS) splits *= 2;
+    int chunk = (nt + splits - 1) / splits;
+    chunk = (chunk + KNN_TILE - 1) / KNN_TILE * KNN_TILE;
+    splits = (nt + chunk - 1) / chunk;
+    // every (split, query) entry of the scratch that the merge reads is written by k_knn2 in this call: nothing has to start
+    // at zero, and what an earlier call left behind is never read
+    k_knn2<<<dim3(qblocks, splits), KNN_THREADS, 0, st>>>((const uint4*)q, nq, (const uint4*)t, nt, chunk, 0, partial, nullptr,
+                                                          nullptr, nullptr);
+    k_knn2_merge<<<(nq + 255) / 256, 256, 0, st>>>(partial, nq, splits, i1, d1, d2);
+    CK(cudaGetLastError());
+    return ORBX_OK;
+}
+
 extern "C" int orbm_window_search(orbm_t* m, const uint8_t* q, int nq, const int32_t* cand_off, const int32_t* cand_idx,
                                   const uint8_t* cand_skip, const uint8_t* t, int nt, int32_t* best_idx, uint16_t* best_d,
                                   uint16_t* second_d, int32_t* second_idx) {
