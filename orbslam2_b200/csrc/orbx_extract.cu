@@ -58,6 +58,10 @@ struct orbx_handle {
     uint8_t* dOutBlock = nullptr;  // [dKps | dDesc | dNOut | dErr]
     size_t outBlockBytes = 0;
     uint8_t* hStage = nullptr;     // pinned mirror of the block (plans with batch == 1)
+    // single-frame path as a CUDA graph: [clear candidate counts, the kernel chain with its side-stream blur, result block to
+    // the pinned mirror] captured once per plan and replayed per call (the copy-in stays a stream operation: its source is
+    // the caller's pointer). ORBX_NO_GRAPH=1 disables it.
+    cudaGraphExec_t gExec = nullptr; int64_t gLaunches = 0; bool gDisabled = false;
     int qtC = 0, qtC2 = 0, qtThreads = 256;
     size_t qtSmem = 0, fastSmem = 0;
     int lastBatch = 0;
@@ -165,6 +169,7 @@ static PFN_encodeTiled get_encode() {
 }
 
 static void free_plan(orbx_handle* h) {
+    if (h->gExec) { cudaGraphExecDestroy(h->gExec); h->gExec = nullptr; }
     cudaFree(h->dPlan); cudaFree(h->dPyr); cudaFree(h->dBlur); cudaFree(h->dTabs); cudaFree(h->dCand);
     cudaFree(h->dNodeOf); cudaFree(h->dCandCount); cudaFree(h->dSel); cudaFree(h->dSelCount); cudaFree(h->dOutBlock);
     cudaFree(h->dExport);
@@ -350,6 +355,7 @@ extern "C" int orbx_create(const orbx_params* p, int device, orbx_t** out) {
     h->prm = *p;
     h->device = device;
     { const char* v = getenv("ORBX_FAST_V2"); h->fastV1 = !(v && v[0] == '1'); }
+    { const char* v = getenv("ORBX_NO_GRAPH"); h->gDisabled = v && v[0] == '1'; }
     init_tables(h);
     cudaError_t e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
     if (e != cudaSuccess) {
@@ -707,10 +713,48 @@ extern "C" int orbx_extract_batch_submit(orbx_t* h, const uint8_t* imgs, int bat
         rc = copy_in(h, st, imgs, 0, batch, w, hgt, stride, img_stride);
         if (rc != ORBX_OK) return rc;
         stamp(h, 1);
+        bool replayed = false;
+        if (oneCopy && !h->gDisabled && !debug_sync()) {
+            if (!h->gExec) {  // capture once per plan; any failure falls back to plain stream launches for good
+                if (!h->sSide) {
+                    CK(cudaStreamCreateWithFlags(&h->sSide, cudaStreamNonBlocking));
+                    CK(cudaEventCreateWithFlags(&h->evFork, cudaEventDisableTiming));
+                    CK(cudaEventCreateWithFlags(&h->evJoin, cudaEventDisableTiming));
+                }
+                const int64_t l0 = h->launches;
+                cudaGraph_t g = nullptr;
+                bool ok = cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal) == cudaSuccess;
+                if (ok) {
+                    ok = cudaMemsetAsync(h->dCandCount, 0, (size_t)nl * sizeof(int), st) == cudaSuccess;
+                    ok = ok && launch_chain(h, st, 0, 1, false) == ORBX_OK;
+                    ok = ok && cudaMemcpyAsync(h->hStage, h->dOutBlock, h->outBlockBytes, cudaMemcpyDeviceToHost, st) == cudaSuccess;
+                    ok = (cudaStreamEndCapture(st, &g) == cudaSuccess) && ok && g;
+                }
+                if (ok) ok = cudaGraphInstantiate(&h->gExec, g, 0) == cudaSuccess;
+                if (g) cudaGraphDestroy(g);
+                h->gLaunches = h->launches - l0;
+                h->launches = l0;
+                if (!ok) {
+                    cudaGetLastError();
+                    h->gExec = nullptr;
+                    h->gDisabled = true;
+                }
+            }
+            if (h->gExec) {
+                CK(cudaGraphLaunch(h->gExec, st));
+                h->launches += h->gLaunches;
+                replayed = true;
+            }
+        }
+        if (replayed) {
+            // (the memset enqueued above ran before the copy-in; the graph clears the counts again: harmless)
+        } else {
         rc = launch_chain(h, st, 0, batch, h->profiling);  // (stamps off => a small batch forks the blur onto the side stream)
         if (rc != ORBX_OK) return rc;
         CK(cudaGetLastError());
-        if (oneCopy) {
+        }
+        if (replayed) {
+        } else if (oneCopy) {
             CK(cudaMemcpyAsync(h->hStage, h->dOutBlock, h->outBlockBytes, cudaMemcpyDeviceToHost, st));
         } else {
             rc = copy_out(h, st, kps, desc, cap, 0, batch);
