@@ -211,6 +211,11 @@ class CpuExtractorPool:
         return time.perf_counter() - t0, sum(nk)
 
 
+CPU_ARM_NOTE = ("unmodified reference src/ORBextractor.cc, g++ -O3 -march=x86-64-v3 -ffp-contract=off, on the cv shim (OpenCV's "
+                "resize / copyMakeBorder / FAST / GaussianBlur restated bit-exactly in oracle/cvprim.hpp with vectorisable loops); "
+                "within 25 % of the cv2-hybrid baseline on real OpenCV 4.13 (profiles/r02_cv2_hybrid_cpu_baseline.json)")
+
+
 def cpu_baseline(frames, seconds):
     pool = CpuExtractorPool()
     dt, _ = pool.run(frames, pool.threads)  # warm-up + rate estimate
@@ -218,7 +223,7 @@ def cpu_baseline(frames, seconds):
     rounds = int(max(1, min(64, (seconds - dt) / per_round)))
     count = pool.threads * rounds
     dt, nk = pool.run(frames, count)
-    return {"value": count / dt, "unit": UNIT, "cores": pool.threads, "kind": pool.kind,
+    return {"value": count / dt, "unit": UNIT, "cores": pool.threads, "kind": pool.kind, "build": CPU_ARM_NOTE,
             "sample": f"{count} synthetic 640x480 frames, {pool.threads} threads x {rounds} frames each, "
                       f"{dt:.1f} s wall; {nk / count:.0f} keypoints/frame"}
 
@@ -272,7 +277,7 @@ def run_reference(args):
         "vs_baseline": None, "dtype": "u8", "data": "synthetic",
         "config": {"workload": "orb_extract_640x480_1000kp_tum1", "frames_per_step": per_step, "kp": NFEAT,
                    "levels": 8, "scale": 1.2, "fast": [20, 7]},
-        "cpu_baseline": {"value": v, "unit": UNIT, "cores": pool.threads, "kind": pool.kind, "sample": sample},
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": pool.threads, "kind": pool.kind, "build": CPU_ARM_NOTE, "sample": sample},
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0}))
 
