@@ -196,6 +196,37 @@ __global__ void __launch_bounds__(1024) k_bow_finish(BowDev S, const int* __rest
     d_bow_finish(S, choice, matchA, result);
 }
 
+// ---- one pair, one CTA: a single SearchByFboW / SearchForTriangulation call on camera-sized frames (~1000 features) is
+// launch-latency bound as a kernel sequence (node pairing, 3-4 rounds of clear / claim / choose, finish: ~16 launches).
+// Here one 1024-thread CTA runs the same device functions back to back with __syncthreads between the phases and loops
+// until a round changes nothing — the same fixed point, one launch. result[1] = rounds executed.
+__global__ void __launch_bounds__(1024) k_bow_fused(BowDev S, int* __restrict__ posNodeB, int* __restrict__ choice,
+                                                    int* __restrict__ owner, int32_t* __restrict__ matchA,
+                                                    int* __restrict__ result, int maxRounds) {
+    __shared__ int changed[1];
+    const int tid = threadIdx.x, T = blockDim.x;
+    for (int j = tid; j < S.nNodesA; j += T) d_bow_pair_nodes(S, posNodeB, j);
+    for (int p = tid; p < S.nPosA; p += T) choice[p] = -1;
+    int round = 0;
+    for (;; round++) {
+        for (int i = tid; i < S.nB; i += T) owner[i] = 0x7F7F7F7F;
+        if (tid == 0) changed[0] = 0;
+        __syncthreads();
+        for (int p = tid; p < S.nPosA; p += T) d_bow_claim(S, choice, owner, p);
+        __syncthreads();
+        for (int p = tid; p < S.nPosA; p += T) {
+            if (S.tri) d_tri_choose(S, posNodeB, choice, owner, changed, 0, p);
+            else d_bow_choose(S, posNodeB, choice, owner, changed, 0, p);
+        }
+        __syncthreads();
+        const int ch = changed[0];
+        __syncthreads();
+        if (!ch || round + 1 >= maxRounds) break;
+    }
+    d_bow_finish(S, choice, matchA, result);
+    if (tid == 0) result[1] = round + 1;
+}
+
 // ---- batched form: one launch sequence serves npairs independent (A, B) pairs (blockIdx.y = pair) -----------------------
 // Relocalization matches the current frame against every candidate keyframe (src/Tracking.cc:1465-1490), LoopClosing a
 // keyframe against every loop candidate (src/LoopClosing.cc:290-312): a single pair is latency bound on the GPU, the
@@ -310,6 +341,18 @@ static int bow_run(orbm_t* m, const orbm_bow_side* a, const orbm_bow_side* b, in
     const size_t spanBytes = (size_t)((const uint8_t*)(flags + SPEC) - spanBegin);
     auto hostAt = [&](const void* dev) { return m->hIn + ((const uint8_t*)dev - spanBegin); };
 
+    if (n_pos_a <= m->bowFusedMax) {  // camera-sized pair: everything in one CTA, one launch, one copy back
+        k_bow_fused<<<1, 1024, 0, st>>>(S, posNodeB, choice, owner, oMatch, dRes, maxRounds);
+        m->launches++;
+        CK(cudaGetLastError());
+        CK(cudaMemcpyAsync(m->hIn, spanBegin, (size_t)((const uint8_t*)flags - spanBegin), cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        if (hout) memcpy(match_a, hostAt(oMatch), (size_t)nA * 4);
+        *nmatches = ((const int*)hostAt(dRes))[0];
+        m->lastRounds = ((const int*)hostAt(dRes))[1];
+        m->lastCandidates = 0;
+        return ORBX_OK;
+    }
     k_bow_pair_nodes<<<(a->n_nodes + 127) / 128, 128, 0, st>>>(S, posNodeB);
     m->launches++;
     CK(cudaMemsetAsync(choice, 0xFF, (size_t)n_pos_a * sizeof(int), st));

@@ -12,6 +12,7 @@
 #include <algorithm>
 #include <climits>
 #include <cmath>
+#include <cstdlib>
 #include <mutex>
 #include <vector>
 
@@ -399,6 +400,7 @@ struct orbm_handle {
     int smCount = 148;
     int64_t launches = 0;
     int lastRounds = 0; int64_t lastCandidates = 0;
+    int bowFusedMax = 4096;  // feature-vector entries up to which a bag-of-words pair runs in one CTA (ORBX_BOW_FUSED_MAX)
     // keyframe cache (orbm_keyframe_hint): staged keypoints / uRight / descriptors and the built 64 x 48 grid of immutable
     // keyframes, so that repeated Fuse / SearchBySim3 searches against one keyframe skip the upload and four grid kernels
     struct KfEntry {
@@ -439,6 +441,7 @@ extern "C" int orbm_create(int device, orbm_t** out) {
         FAIL(ORBX_ECUDA, "cudaStreamCreate: %s", cudaGetErrorString(e));
     }
     cudaDeviceGetAttribute(&m->smCount, cudaDevAttrMultiProcessorCount, device);
+    if (const char* v = getenv("ORBX_BOW_FUSED_MAX")) m->bowFusedMax = atoi(v);
     *out = m;
     return ORBX_OK;
 }

@@ -131,10 +131,15 @@ def _bow_frames(ob, voc, blob, n_a, n_b, seed, level=4, shared=0.7):
     return da, ang_a, None, db, ang_b, None
 
 
+@pytest.mark.parametrize("fused", [True, False])
 @pytest.mark.parametrize("strict", [False, True])
 @pytest.mark.parametrize("level", [4, 2])
-def test_search_by_bow_vs_oracle(ob, strict, level):
+def test_search_by_bow_vs_oracle(ob, strict, level, fused, monkeypatch):
+    """fused: the one-CTA kernel (k_bow_fused, feature vectors up to 4096 entries); not fused: the multi-launch rounds
+    that larger frames take (forced here with ORBX_BOW_FUSED_MAX=0, read when the matcher handle is created)."""
     from oracle_lib import oracle_search_by_bow
+    if not fused:
+        monkeypatch.setenv("ORBX_BOW_FUSED_MAX", "0")
     blob = synth_vocabulary(k=10, levels=5, seed=31)
     voc = ob.Vocabulary(); voc.fromStream(blob)
     rng = np.random.default_rng(7)
@@ -148,7 +153,10 @@ def test_search_by_bow_vs_oracle(ob, strict, level):
         B = ob.ORBmatcher.bow_side(db, ang_b, fb, elig_b)
         for ratio, ori in ((0.7, True), (0.9, True), (0.75, False)):
             m = ob.ORBmatcher(ratio, ori)
+            l0 = m.launch_count()
             n, match = m.SearchByFboW(A, B, strict=strict)
+            if na > 5:
+                assert (m.launch_count() - l0 == 1) == fused
             en, ematch = oracle_search_by_bow(A, B, ratio, 50, strict, ori)
             assert n == en and np.array_equal(match, ematch), (seed, ratio, ori)
             if ratio == 0.9:  # the same call with device buffers in and out
