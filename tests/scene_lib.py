@@ -654,3 +654,45 @@ def scene_bow_reloc_batch(seed, K=5, nnratio=0.75, n_points=1000):
     for m in S.mps:
         m.bad = int(W.rng.random() < 0.04)
     return S
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# Degenerate scenes: empty inputs of every search (the reference returns 0 matches and touches nothing).
+# ------------------------------------------------------------------------------------------------------------------
+def _empty_view(V):
+    """A copy of view V with no keypoints at all."""
+    E = View(np.zeros(0, KP_DTYPE), np.zeros((0, 32), np.uint8), np.zeros(0, f32), np.zeros(0, f32), V.Tcw, V.kind)
+    return E
+
+
+def _mutate(sc, fn):
+    fn(sc)
+    return sc
+
+
+def _no_level0(sc):
+    sc.views[0].keys["octave"][:] = 1
+    sc.views[0].keys_un = sc.views[0].keys.copy()
+
+
+def _all_have_points(sc):
+    sc.views[0].mp[:] = np.arange(sc.views[0].N) % max(len(sc.mps), 1)
+
+
+EDGE_SCENES = [
+    ("frame_last_without_points", lambda: _mutate(scene_frame(0), lambda s: s.views[1].mp.fill(-1))),
+    ("frame_current_without_keypoints", lambda: _mutate(scene_frame(1), lambda s: s.views.__setitem__(0, _empty_view(s.views[0])))),
+    ("local_empty_list", lambda: _mutate(scene_local(0), lambda s: setattr(s, "lists", [np.zeros(0, np.int32)]))),
+    ("local_nothing_in_view", lambda: _mutate(scene_local(1), lambda s: [setattr(m, "in_view", 0) for m in s.mps])),
+    ("local_frame_without_keypoints", lambda: _mutate(scene_local(2), lambda s: s.views.__setitem__(0, _empty_view(s.views[0])))),
+    ("reloc_kf_without_points", lambda: _mutate(scene_reloc(0), lambda s: s.views[1].mp.fill(-1))),
+    ("kfproj_no_points", lambda: _mutate(scene_kfproj(0), lambda s: s.lists.__setitem__(0, np.zeros(0, np.int32)))),
+    ("bow_kf_without_points", lambda: _mutate(scene_bow_kf_f(0), lambda s: s.views[0].mp.fill(-1))),
+    ("bow_frame_empty_featvec", lambda: _mutate(scene_bow_kf_f(1), lambda s: setattr(s.views[1], "featvec", {}))),
+    ("bow_kfkf_second_without_points", lambda: _mutate(scene_bow_kf_kf(0), lambda s: s.views[1].mp.fill(-1))),
+    ("triang_all_keypoints_have_points", lambda: _mutate(scene_triang(0), _all_have_points)),
+    ("sim3_kf2_without_points", lambda: _mutate(scene_sim3(0), lambda s: s.views[1].mp.fill(-1))),
+    ("fuse_empty_list", lambda: _mutate(scene_fuse(0), lambda s: setattr(s, "lists", [np.zeros(0, np.int32)]))),
+    ("fuse_sim3_empty_list", lambda: _mutate(scene_fuse_sim3(0), lambda s: setattr(s, "lists", [np.zeros(0, np.int32)]))),
+    ("init_no_level0_keypoint", lambda: _mutate(scene_init(0), _no_level0)),
+]

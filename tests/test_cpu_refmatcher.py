@@ -196,3 +196,15 @@ def test_reference_method_vs_hostcheck(hostcheck, tmp_path, name, make):
         assert pa["ret"] >= MIN_RET.get(name, 100), f"{name}: scene too easy ({pa['ret']} matches)"
         assert a.shape == b.shape and np.array_equal(a, b), \
             f"{S.METHOD_NAMES[sc.method]} seed {seed}: reference returned {pa['ret']}, host half + oracle {int(b[0])}"
+
+
+@pytest.mark.skipif(not S.have_ref_matcher(), reason="oracle/_ref/scene_run_ref not built")
+@pytest.mark.parametrize("name,make", S.EDGE_SCENES, ids=[n for n, _ in S.EDGE_SCENES])
+def test_degenerate_scenes_vs_reference(hostcheck, tmp_path, name, make):
+    """Empty inputs of every search (no map points, no keypoints, empty lists, empty feature vectors): the reference
+    returns 0 and leaves the map untouched; so must the drop-in."""
+    sc = make()
+    a = S.run_scene(S.REF_EXE, sc, tmp_path, "ref")
+    b = S.run_scene(hostcheck, sc, tmp_path, "host")
+    assert int(a[0]) == 0
+    assert a.shape == b.shape and np.array_equal(a, b), f"{name}: reference returned {int(a[0])}, drop-in {int(b[0])}"

@@ -65,3 +65,15 @@ def test_keyframe_cache_reuses_staged_keyframe(tmp_path):
         assert np.array_equal(r[0], base[0]) and np.array_equal(r[1], base[1])
     assert not np.array_equal(res[3][0], base[0])
     m.close()
+
+
+@pytest.mark.skipif(not S.have_ref_matcher(), reason="oracle/_ref/scene_run_ref not built")
+@pytest.mark.parametrize("name,make", S.EDGE_SCENES, ids=[n for n, _ in S.EDGE_SCENES])
+def test_degenerate_scenes_vs_reference(gpu_exe, tmp_path, name, make):
+    """Empty inputs of every search (no map points, no keypoints, empty lists, empty feature vectors): the reference
+    returns 0 and leaves the map untouched; so must the drop-in."""
+    sc = make()
+    a = S.run_scene(S.REF_EXE, sc, tmp_path, "ref")
+    b = S.run_scene(gpu_exe, sc, tmp_path, "gpu")
+    assert int(a[0]) == 0
+    assert a.shape == b.shape and np.array_equal(a, b), f"{name}: reference returned {int(a[0])}, drop-in {int(b[0])}"
