@@ -400,6 +400,7 @@ struct orbm_handle {
     int smCount = 148;
     int64_t launches = 0;
     int lastRounds = 0; int64_t lastCandidates = 0;
+    int gridFusedMax = 32768;  // keypoints up to which the 64 x 48 grid is built by one CTA (ORBX_GRID_FUSED_MAX)
     int bowFusedMax = 4096;  // feature-vector entries up to which a bag-of-words pair runs in one CTA (ORBX_BOW_FUSED_MAX)
     // keyframe cache (orbm_keyframe_hint): staged keypoints / uRight / descriptors and the built 64 x 48 grid of immutable
     // keyframes, so that repeated Fuse / SearchBySim3 searches against one keyframe skip the upload and four grid kernels
@@ -442,6 +443,7 @@ extern "C" int orbm_create(int device, orbm_t** out) {
     }
     cudaDeviceGetAttribute(&m->smCount, cudaDevAttrMultiProcessorCount, device);
     if (const char* v = getenv("ORBX_BOW_FUSED_MAX")) m->bowFusedMax = atoi(v);
+    if (const char* v = getenv("ORBX_GRID_FUSED_MAX")) m->gridFusedMax = atoi(v);
     *out = m;
     return ORBX_OK;
 }
@@ -996,11 +998,16 @@ static int sp_run(orbm_handle* m, int mode, const orbm_proj_params* p, float nnR
     auto hostAt = [&](const void* dev) { return hs + ((const uint8_t*)dev - spanBegin); };
 
     // S1 grid
+    if (nC <= m->gridFusedMax) {  // camera-sized frame: the whole grid build in one CTA, one launch
+        k_sp_grid_build<<<1, 1024, 0, st>>>(S, cellStart, items);
+        m->launches -= 3;  // (the call sites below count the four kernels of the sequence)
+    } else {
     CK(cudaMemsetAsync(cellCount, 0, SP_CELLS * sizeof(int), st));
     k_sp_grid_count<<<(nC + 255) / 256, 256, 0, st>>>(S, cellCount);
     k_sp_grid_scan<<<1, 1024, 0, st>>>(cellCount, cellStart, cursor);
     k_sp_grid_fill<<<(nC + 255) / 256, 256, 0, st>>>(S, cursor, items);
     k_sp_grid_sort<<<(SP_CELLS + 255) / 256, 256, 0, st>>>(cellStart, items);
+    }
     // S2 candidates: count, scan, fill — without a host round trip for the total (k_sp_guard)
     const int qBlocks = (nL + 7) / 8;
     k_sp_candidates<false><<<qBlocks, 256, 0, st>>>(S, cellStart, items, candCount, nullptr, nullptr, nullptr);
@@ -1163,11 +1170,16 @@ extern "C" int orbm_search_for_initialization(orbm_t* m, const orbm_proj_params*
     float* oPrev = hout ? W.take<float>((size_t)nL * 2) : prev_matched;
     if (W.off > m->wsCap) FAIL(ORBX_ECUDA, "internal: workspace estimate too small (%zu > %zu)", W.off, m->wsCap);
 
+    if (nC <= m->gridFusedMax) {  // camera-sized frame: the whole grid build in one CTA, one launch
+        k_sp_grid_build<<<1, 1024, 0, st>>>(S, cellStart, items);
+        m->launches -= 3;  // (the call sites below count the four kernels of the sequence)
+    } else {
     CK(cudaMemsetAsync(cellCount, 0, SP_CELLS * sizeof(int), st));
     k_sp_grid_count<<<(nC + 255) / 256, 256, 0, st>>>(S, cellCount);
     k_sp_grid_scan<<<1, 1024, 0, st>>>(cellCount, cellStart, cursor);
     k_sp_grid_fill<<<(nC + 255) / 256, 256, 0, st>>>(S, cursor, items);
     k_sp_grid_sort<<<(SP_CELLS + 255) / 256, 256, 0, st>>>(cellStart, items);
+    }
     const int qBlocks = (nL + 7) / 8;
     k_sp_candidates<false><<<qBlocks, 256, 0, st>>>(S, cellStart, items, candCount, nullptr, nullptr, nullptr);
     k_sp_scan<<<1, 1024, 0, st>>>(candCount, nL, candOff);
@@ -1363,12 +1375,17 @@ extern "C" int orbm_fuse_search(orbm_t* m, const orbm_proj_params* p, const floa
         cellStart = hit->cellStart;
         items = hit->items;
     } else {
-        CK(cudaMemsetAsync(cellCount, 0, SP_CELLS * sizeof(int), st));
-        if (nC) k_sp_grid_count<<<(nC + 255) / 256, 256, 0, st>>>(S, cellCount);
-        k_sp_grid_scan<<<1, 1024, 0, st>>>(cellCount, cellStart, cursor);
-        if (nC) k_sp_grid_fill<<<(nC + 255) / 256, 256, 0, st>>>(S, cursor, items);
-        k_sp_grid_sort<<<(SP_CELLS + 255) / 256, 256, 0, st>>>(cellStart, items);
-        m->launches += 4;
+        if (nC <= m->gridFusedMax) {
+            k_sp_grid_build<<<1, 1024, 0, st>>>(S, cellStart, items);
+            m->launches += 1;
+        } else {
+            CK(cudaMemsetAsync(cellCount, 0, SP_CELLS * sizeof(int), st));
+            if (nC) k_sp_grid_count<<<(nC + 255) / 256, 256, 0, st>>>(S, cellCount);
+            k_sp_grid_scan<<<1, 1024, 0, st>>>(cellCount, cellStart, cursor);
+            if (nC) k_sp_grid_fill<<<(nC + 255) / 256, 256, 0, st>>>(S, cursor, items);
+            k_sp_grid_sort<<<(SP_CELLS + 255) / 256, 256, 0, st>>>(cellStart, items);
+            m->launches += 4;
+        }
         if (hint && nC) {  // remember this keyframe (device-to-device copies of what was just staged and built)
             orbm_handle::KfEntry* e = nullptr;
             if ((rc = kf_claim(m, hint, nC, kf->u_right != nullptr, p, &e))) return rc;

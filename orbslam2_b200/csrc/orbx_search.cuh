@@ -109,6 +109,62 @@ __global__ void k_sp_grid_sort(const int* __restrict__ cellStart, int* __restric
     }
 }
 
+// The whole grid build (clear, count, scan, fill, per-cell sort) in ONE 1024-thread CTA with the counters in shared memory:
+// a camera frame has a few thousand keypoints, far too few to need a grid of CTAs, and the four launches + memset cost more
+// than the work. Same cellStart / items as the kernel sequence above.
+__global__ void __launch_bounds__(1024) k_sp_grid_build(SpDev S, int* __restrict__ cellStart, int* __restrict__ items) {
+    __shared__ int cnt[SP_CELLS];
+    __shared__ int part[1024];
+    const int tid = threadIdx.x;
+    for (int c = tid; c < SP_CELLS; c += 1024) cnt[c] = 0;
+    __syncthreads();
+    for (int i = tid; i < S.nCur; i += 1024) {
+        const int c = sp_cell_of(S, i);
+        if (c >= 0) atomicAdd(&cnt[c], 1);
+    }
+    __syncthreads();
+    int c3[3], s = 0;
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        c3[k] = cnt[tid * 3 + k];
+        s += c3[k];
+    }
+    part[tid] = s;
+    __syncthreads();
+    for (int o = 1; o < 1024; o <<= 1) {
+        const int v = tid >= o ? part[tid - o] : 0;
+        __syncthreads();
+        part[tid] += v;
+        __syncthreads();
+    }
+    int base = part[tid] - s;
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        cellStart[tid * 3 + k] = base;
+        cnt[tid * 3 + k] = base;  // fill cursor
+        base += c3[k];
+    }
+    if (tid == 1023) cellStart[SP_CELLS] = base;
+    __syncthreads();
+    for (int i = tid; i < S.nCur; i += 1024) {
+        const int c = sp_cell_of(S, i);
+        if (c >= 0) items[atomicAdd(&cnt[c], 1)] = i;
+    }
+    __syncthreads();
+    for (int c = tid; c < SP_CELLS; c += 1024) {  // restore keypoint-index order inside the cell
+        const int b0 = cellStart[c], e = cnt[c];  // the cursor ended at the cell's end
+        for (int a = b0 + 1; a < e; a++) {
+            const int v = items[a];
+            int b = a - 1;
+            while (b >= b0 && items[b] > v) {
+                items[b + 1] = items[b];
+                b--;
+            }
+            items[b + 1] = v;
+        }
+    }
+}
+
 // Projection of last-frame point i into the current frame and its search window (src/ORBmatcher.cc:1353-1386).
 struct SpQuery {
     float u, v, invzc, radius, ur;  // ur = expected right-image coordinate for the stereo gate

@@ -384,3 +384,21 @@ def test_search_by_projection_device_buffers():
             for g, e, name in zip(got[1:], exp[1:], ("cur_match", "last_match", "last_keep")):
                 assert np.array_equal(g, e), name
         m.close()
+
+
+def test_grid_build_fused_and_kernel_sequence_agree(monkeypatch):
+    """The 64 x 48 grid is built by one CTA (k_sp_grid_build) for camera-sized frames and by the count / scan / fill / sort
+    kernel sequence above ORBX_GRID_FUSED_MAX keypoints: both must give the oracle's result on the same pair."""
+    import orbslam2_b200 as ob
+    P = OraclePrims()
+    last, cur = synth_tracking_pair(2500, 12, stereo=True, motion=(0.05, -0.02, 0.12))
+    fused = ob.ORBmatcher(0.9, True)
+    monkeypatch.setenv("ORBX_GRID_FUSED_MAX", "0")
+    seq = ob.ORBmatcher(0.9, True)
+    monkeypatch.delenv("ORBX_GRID_FUSED_MAX")
+    l0 = fused.launch_count(); a, _ = _run(fused, P, last, cur, 15.0, False); la = fused.launch_count() - l0
+    l0 = seq.launch_count(); b, _ = _run(seq, P, last, cur, 15.0, False); lb = seq.launch_count() - l0
+    assert lb - la == 3
+    for x, y in zip(a[1:], b[1:]):
+        assert np.array_equal(x, y)
+    fused.close(); seq.close()
