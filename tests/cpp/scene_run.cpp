@@ -180,6 +180,10 @@ int main(int argc, char** argv) {
             K.mnGridCols = FRAME_GRID_COLS; K.mnGridRows = FRAME_GRID_ROWS;
             K.mfGridElementWidthInv = Frame::mfGridElementWidthInv; K.mfGridElementHeightInv = Frame::mfGridElementHeightInv;
             K.fx = Frame::fx; K.fy = Frame::fy; K.cx = Frame::cx; K.cy = Frame::cy; K.invfx = Frame::invfx; K.invfy = Frame::invfy;
+            if (v == 1 && fpar[4] > 0.f) {  // a second keyframe from another camera (fpar[4..7] = its fx, fy, cx, cy)
+                K.fx = fpar[4]; K.fy = fpar[5]; K.cx = fpar[6]; K.cy = fpar[7];
+                K.invfx = 1.0f / K.fx; K.invfy = 1.0f / K.fy;
+            }
             K.mbf = F.mbf; K.mb = F.mb; K.mThDepth = F.mThDepth; K.N = N;
             K.mvKeys = F.mvKeys; K.mvKeysUn = F.mvKeysUn; K.mvuRight = F.mvuRight; K.mvDepth = F.mvDepth;
             K.mDescriptors = F.mDescriptors.clone();

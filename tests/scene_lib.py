@@ -80,7 +80,7 @@ class Scene:
         self.nlevels, self.scale = nlevels, f32(scale)
         self.sf, self.isf, self.s2, self.is2 = scale_tables(nlevels, scale)
         self.views, self.mps = [], []
-        self.fpar = np.zeros(8, f32)    # [0] th  [1] nnratio  [2] s12
+        self.fpar = np.zeros(8, f32)    # [0] th  [1] nnratio  [2] s12  [4..7] fx, fy, cx, cy of keyframe view 1 (0 = shared)
         self.ipar = np.zeros(8, np.int32)  # [0] checkOrientation  [1] method-specific int
         self.lists, self.farr = [], []
 
@@ -563,6 +563,8 @@ def scene_sim3(seed, th=7.5, s12=1.0, n_points=1200, other_cal=False):
     R12 = T1[:3, :3] @ T2[:3, :3].T
     t12 = -R12 @ T2[:3, 3] + T1[:3, 3]
     S.farr = [R12.astype(f32), (t12 * s12).astype(f32)]
+    if other_cal:  # KF2 comes from another camera: the reference projects BOTH directions with pKF1's intrinsics
+        S.fpar[4:8] = [cal["fx"] * 1.07, cal["fy"] * 0.95, cal["cx"] + 6.0, cal["cy"] - 4.0]
     return S
 
 

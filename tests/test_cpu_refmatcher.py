@@ -175,13 +175,14 @@ SCENES = [
     ("triang_mono_ori", lambda s: S.scene_triang(s + 20, stereo=False, check_ori=True)),
     ("sim3", lambda s: S.scene_sim3(s)),
     ("sim3_s1.05", lambda s: S.scene_sim3(s + 10, s12=1.05, th=5.0)),
+    ("sim3_two_cameras", lambda s: S.scene_sim3(s + 20, other_cal=True)),
     ("fuse", lambda s: S.scene_fuse(s)),
     ("fuse_mono", lambda s: S.scene_fuse(s + 10, stereo=False, th=5.0)),
     ("fuse_sim3", lambda s: S.scene_fuse_sim3(s)),
     ("fuse_sim3_s.9", lambda s: S.scene_fuse_sim3(s + 10, s=0.9, th=6.0)),
     ("bow_reloc_batch", lambda s: S.scene_bow_reloc_batch(s)),
 ]
-MIN_RET = {"sim3_s1.05": 50}
+MIN_RET = {"sim3_s1.05": 50, "sim3_two_cameras": 20}
 
 
 @needs_ref
