@@ -23,12 +23,25 @@ void orbx_set_err(const char* fmt, ...) {
 extern "C" const char* orbx_last_error_string(void) { return g_err; }
 extern "C" const char* orbx_version(void) { return "orbx 0.1 (sm_100a)"; }
 
+typedef void (*fast_kernel_t)(const TmapPack, const FastSt*, u64*, int*, int*, int);
+// the FAST kernel instantiations: variant 1 (default), and variant 3 with NF1 / NF2 min-max pairs on the FMA pipe
+// (8 / 4 balances the ALU pipe against the issue slots; 0 / 0 keeps every min/max on the ALU pipe)
+static fast_kernel_t fast_kernel(int ver, int nf) {
+    if (ver != 3) return k_fast_t<1, 0, 0>;
+    return nf == 1 ? k_fast_t<3, 0, 0> : k_fast_t<3, 8, 4>;
+}
+
 // ------------------------------------------------------------------------------------------------ handle
 struct orbx_handle {
     orbx_params prm;
     int device = 0;
-    bool fastV1 = true;   // k_fast (every pixel scored in one pass). ORBX_FAST_V2=1 selects k_fast2 (two-threshold pre-test
-                          // + work lists): identical candidates, measured 1.47x SLOWER (profiles/r02d_fast2_analysis.md)
+    int fastVer = 1;      // FAST kernel: 1 = k_fast_t<1> (byte tile, every pixel scored in one pass, ALU pipe only);
+                          // 3 = k_fast_t<3> (expanded fp16-lane tile, min/max split over the ALU and FMA pipes: identical
+                          // candidates, measured the SAME speed — issue-slot bound instead of ALU bound,
+                          // profiles/r02x_fast3_analysis.md);
+                          // 2 = k_fast2 (two-threshold pre-test + work lists: identical candidates, measured 1.47x SLOWER,
+                          // profiles/r02d_fast2_analysis.md). ORBX_FAST=1|2|3 selects; ORBX_FAST_V2=1 is the old spelling of 2.
+    int fastNF = 0;       // variant 3: which (NF1, NF2) instantiation (ORBX_FAST3_NF, tuning only)
     cudaStream_t stream = nullptr;
     int inSpace = ORBX_MEM_HOST, outSpace = ORBX_MEM_HOST;
     // reference ctor tables
@@ -38,6 +51,7 @@ struct orbx_handle {
     int planW = 0, planH = 0, planBatch = 0;
     DevPlan hp;             // host copy
     DevPlan* dPlan = nullptr;
+    FastSt* dFastSt = nullptr;  // one record per FAST supertile
     TmapPack maps;
     uint8_t* dPyr = nullptr;
     uint8_t* dBlur = nullptr;
@@ -170,13 +184,13 @@ static PFN_encodeTiled get_encode() {
 
 static void free_plan(orbx_handle* h) {
     if (h->gExec) { cudaGraphExecDestroy(h->gExec); h->gExec = nullptr; }
-    cudaFree(h->dPlan); cudaFree(h->dPyr); cudaFree(h->dBlur); cudaFree(h->dTabs); cudaFree(h->dCand);
+    cudaFree(h->dPlan); cudaFree(h->dFastSt); cudaFree(h->dPyr); cudaFree(h->dBlur); cudaFree(h->dTabs); cudaFree(h->dCand);
     cudaFree(h->dNodeOf); cudaFree(h->dCandCount); cudaFree(h->dSel); cudaFree(h->dSelCount); cudaFree(h->dOutBlock);
     cudaFree(h->dExport);
     if (h->hCounts) cudaFreeHost(h->hCounts);
     if (h->hStage) cudaFreeHost(h->hStage);
     h->hStage = nullptr; h->dOutBlock = nullptr; h->dErr = nullptr;
-    h->dPlan = nullptr; h->dPyr = h->dBlur = nullptr; h->dTabs = nullptr; h->dCand = nullptr; h->dNodeOf = nullptr;
+    h->dPlan = nullptr; h->dFastSt = nullptr; h->dPyr = h->dBlur = nullptr; h->dTabs = nullptr; h->dCand = nullptr; h->dNodeOf = nullptr;
     h->dCandCount = nullptr; h->dSel = nullptr; h->dSelCount = nullptr; h->dKps = nullptr; h->dDesc = nullptr;
     h->dNOut = nullptr; h->dExport = nullptr; h->exportBytes = 0; h->hCounts = nullptr;
     h->planW = h->planH = h->planBatch = 0;
@@ -264,8 +278,8 @@ static int build_plan(orbx_handle* h, int w, int hgt, int batch) {
         G.fastUnits = ((G.stCX * G.wCell + 3) / 4 + 2) * (G.stCY * G.hCell);
         if (G.fastUnits >= 16384 || (G.stCX * G.wCell + 3) / 4 + 2 > 64 || G.stCY * G.hCell > 128)
             FAIL(ORBX_ESHAPE, "level %d supertile of %d words exceeds k_fast2's tables", l, G.fastUnits);
-        if (h->fastV1)
-            fastSmem = std::max(fastSmem, (size_t)2 * G.boxW * G.boxH + ((G.boxW * G.boxH / 2 + 15) & ~15) + sizeof(FastSmemHdr));
+        if (h->fastVer != 2)
+            fastSmem = std::max(fastSmem, (size_t)2 * G.boxW * G.boxH + fast_region3_bytes(h->fastVer, G.boxW, G.boxH) + sizeof(FastSmemHdr));
         else
             fastSmem = std::max(fastSmem, (size_t)2 * G.boxW * G.boxH + ((2 * G.fastUnits + 15) & ~15) + (size_t)8 * G.fastUnits +
                                               sizeof(Fast2Hdr));
@@ -283,6 +297,27 @@ static int build_plan(orbx_handle* h, int w, int hgt, int batch) {
     h->pyrBytes = (size_t)pyrOff + 256;
 
     CK(cudaMalloc(&h->dPlan, sizeof(DevPlan)));
+    std::vector<FastSt> sts((size_t)D.totalSt);
+    for (int l = 0; l < p.nlevels; l++) {
+        const LevelGeo& G = D.lv[l];
+        for (int st = 0; st < G.nStX * G.nStY; st++) {
+            FastSt& S = sts[(size_t)G.stBase + st];
+            memset(&S, 0, sizeof(S));
+            const int sy = st / G.nStX, sx = st - sy * G.nStX;
+            const int cj0 = sx * G.stCX, ci0 = sy * G.stCY;
+            const int ncx = std::min(G.stCX, G.nCols - cj0), ncy = std::min(G.stCY, G.nRows - ci0);
+            S.level = (unsigned short)l; S.stCX = (unsigned short)G.stCX; S.cj0 = (unsigned short)cj0; S.ci0 = (unsigned short)ci0;
+            S.xFirst = (unsigned short)(e + cj0 * G.wCell); S.xEnd = (unsigned short)std::min(e + (cj0 + ncx) * G.wCell, G.w - e);
+            S.yFirst = (unsigned short)(e + ci0 * G.hCell); S.yEnd = (unsigned short)std::min(e + (ci0 + ncy) * G.hCell, G.h - e);
+            S.boxW = (short)G.boxW; S.boxH = (short)G.boxH; S.wCell = (short)G.wCell; S.hCell = (short)G.hCell;
+            S.nlevels = (short)p.nlevels; S.minTh = (short)p.minThFAST; S.iniTh = (short)p.iniThFAST;
+            S.nCells = (short)(G.stCX * G.stCY);
+            S.divCw = (65536u + G.wCell - 1) / G.wCell; S.divCh = (65536u + G.hCell - 1) / G.hCell;
+            S.candCap = G.candCap; S.candOff = G.candOff;
+        }
+    }
+    CK(cudaMalloc(&h->dFastSt, std::max<size_t>(sts.size(), 1) * sizeof(FastSt)));
+    CK(cudaMemcpyAsync(h->dFastSt, sts.data(), sts.size() * sizeof(FastSt), cudaMemcpyHostToDevice, h->stream));
     CK(cudaMalloc(&h->dPyr, h->pyrBytes));
     CK(cudaMalloc(&h->dBlur, h->pyrBytes));
     CK(cudaMalloc(&h->dTabs, std::max<size_t>(tabs.size(), 1) * sizeof(int2)));
@@ -324,8 +359,9 @@ static int build_plan(orbx_handle* h, int w, int hgt, int batch) {
                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         if (r != CUDA_SUCCESS) FAIL(ORBX_ECUDA, "cuTensorMapEncodeTiled failed for level %d (CUresult %d)", l, (int)r);
     }
-    if (h->fastV1) CK(cudaFuncSetAttribute(k_fast, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->fastSmem));
-    else CK(cudaFuncSetAttribute(k_fast2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->fastSmem));
+    if (h->fastSmem > 227 * 1024) FAIL(ORBX_ESHAPE, "FAST supertile needs %zu bytes of shared memory", h->fastSmem);
+    if (h->fastVer == 2) CK(cudaFuncSetAttribute(k_fast2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->fastSmem));
+    else CK(cudaFuncSetAttribute(fast_kernel(h->fastVer, h->fastNF), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->fastSmem));
     CK(cudaFuncSetAttribute(k_quadtree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->qtSmem));
     h->planW = w;
     h->planH = hgt;
@@ -354,7 +390,9 @@ extern "C" int orbx_create(const orbx_params* p, int device, orbx_t** out) {
     orbx_handle* h = new orbx_handle();
     h->prm = *p;
     h->device = device;
-    { const char* v = getenv("ORBX_FAST_V2"); h->fastV1 = !(v && v[0] == '1'); }
+    { const char* v = getenv("ORBX_FAST_V2"); if (v && v[0] == '1') h->fastVer = 2; }
+    { const char* v = getenv("ORBX_FAST"); if (v && v[0] >= '1' && v[0] <= '3') h->fastVer = v[0] - '0'; }
+    { const char* v = getenv("ORBX_FAST3_NF"); if (v && v[0] >= '0' && v[0] <= '9') h->fastNF = v[0] - '0'; }
     { const char* v = getenv("ORBX_NO_GRAPH"); h->gDisabled = v && v[0] == '1'; }
     init_tables(h);
     cudaError_t e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
@@ -484,8 +522,8 @@ static int launch_chain(orbx_handle* h, cudaStream_t cs, int f0, int nb, bool st
         KCHECK(h, "k_blur");
         CK(cudaEventRecord(h->evJoin, h->sSide));
     }
-    if (h->fastV1)
-        k_fast<<<dim3(D.totalSt, nb), FAST_THREADS, h->fastSmem, cs>>>(h->maps, h->dPlan, h->dCand, h->dCandCount, h->dErr, f0);
+    if (h->fastVer != 2)
+        fast_kernel(h->fastVer, h->fastNF)<<<dim3(D.totalSt, nb), FAST_THREADS, h->fastSmem, cs>>>(h->maps, h->dFastSt, h->dCand, h->dCandCount, h->dErr, f0);
     else
         k_fast2<<<dim3(D.totalSt, nb), FAST_THREADS, h->fastSmem, cs>>>(h->maps, h->dPlan, h->dCand, h->dCandCount, h->dErr, f0);
     KCHECK(h, "k_fast");

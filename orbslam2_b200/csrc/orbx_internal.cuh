@@ -62,6 +62,15 @@ struct DevPlan {
     LevelGeo lv[ORBX_MAX_LEVELS];
 };
 
+// One record per FAST supertile (blockIdx.x of k_fast_t), built by the host.
+struct __align__(16) FastSt {
+    unsigned short level, stCX, xFirst, xEnd, yFirst, yEnd, cj0, ci0;  // detection area [xFirst, xEnd) x [yFirst, yEnd), first cell
+    short boxW, boxH, wCell, hCell, nlevels, minTh, iniTh, nCells;
+    unsigned divCw, divCh;                                    // ceil(65536 / wCell), ceil(65536 / hCell)
+    int candCap, pad;
+    long long candOff, pad2;
+};
+
 struct TmapPack {
     CUtensorMap m[ORBX_MAX_LEVELS];
 };

@@ -311,6 +311,29 @@ def test_two_pass_fast_kernel_gives_identical_candidates(ob, monkeypatch):
     ex1.close(); ex2.close()
 
 
+@pytest.mark.parametrize("nf", ["0", "1"])
+def test_fp16_lane_fast_kernel_gives_identical_candidates(ob, monkeypatch, nf):
+    """k_fast_t<3> (ORBX_FAST=3: tile expanded to fp16 lanes 1024 + p, circle operands by aligned LDS, part of the min/max
+    tree as HFMA2.RELU pairs on the FMA pipe; ORBX_FAST3_NF=1 keeps the whole tree on the ALU pipe) against the default
+    kernel and the oracle on shapes with different supertile geometry (profiles/r02x_fast3_analysis.md)."""
+    monkeypatch.setenv("ORBX_FAST", "3")
+    monkeypatch.setenv("ORBX_FAST3_NF", nf)
+    p = _params(1000)
+    ex3 = ob.ORBextractor(**p)
+    monkeypatch.delenv("ORBX_FAST")
+    monkeypatch.delenv("ORBX_FAST3_NF")
+    ex1 = ob.ORBextractor(**p)
+    orc = Oracle(**p)
+    for (w, h), seed, contrast in (((640, 480), 7, 1.0), ((640, 480), 8, 0.2), ((757, 483), 9, 1.0), ((480, 640), 10, 1.0),
+                                   ((1241, 376), 11, 0.5)):
+        img = synth_image(w, h, seed).astype(np.float32)
+        img = np.clip((img - 128.0) * contrast + 128.0, 0, 255).astype(np.uint8)
+        k3, d3 = ex3(img); k1, d1 = ex1(img)
+        assert k1.tobytes() == k3.tobytes() and np.array_equal(d1, d3)
+        _compare_frame(ex3, orc, img, 0, None, k3, d3)
+    ex1.close(); ex3.close()
+
+
 def test_single_process_multi_gpu_entry_point(ob):
     """orbx_extract_batch_multi: contiguous blocks of the batch on several handles (every visible GPU, at least two handles
     so that a one-GPU box still exercises the split), results in disjoint slices — bytes equal to one device's call."""
