@@ -42,9 +42,22 @@ __device__ __forceinline__ void blur_strip(const uint8_t* __restrict__ src, uint
     const unsigned V01 = 18u | (34u << 8), V23 = 48u | (56u << 8), V45 = 48u | (34u << 8);
     const bool redge = EDGE && x0 + 8 > w;
     const bool ledge = EDGE && x0 == 0;
-    int ridx[8];
+    // Right edge: bytes x0 .. x0+7 with BORDER_REFLECT_101 past w - 1. A reflected byte lies at most 4 left of x0, so every
+    // byte comes from the 12-byte window (wm, w0, wp) the lane loads anyway: two PRMT per word with per-lane selectors
+    // (identity for the lanes that are not on the edge) — no byte gathers, no divergence in the row loop.
+    unsigned s1a = 0x7654u, s2a = 0x3210u, s1b = 0x7654u, s2b = 0x7654u;
+    if (redge) {
+        s1a = s2a = s1b = s2b = 0u;
 #pragma unroll
-    for (int j = 0; j < 8; j++) ridx[j] = redge ? blur_reflect(x0 + j, w) - x0 : j;
+        for (int j = 0; j < 8; j++) {
+            // index into (wm, w0, wp): 0 .. 11 for every byte a real pixel needs (x + 3 <= w + 2 reflects to >= w - 4 >= x0 - 3);
+            // bytes that only feed the padding pixels past w - 1 may fall outside: clamped, their value does not matter
+            const unsigned t = (unsigned)max(0, min(11, blur_reflect(x0 + j, w) - x0 + 4));
+            const unsigned n1 = t < 8u ? t : 0u, n2 = t < 8u ? (unsigned)(j & 3) : t - 4u;
+            if (j < 4) { s1a |= n1 << (4 * j); s2a |= n2 << (4 * j); }
+            else { s1b |= n1 << (4 * (j - 4)); s2b |= n2 << (4 * (j - 4)); }
+        }
+    }
     const int lback = ledge ? 0 : 4;
     const uint8_t* col = src + x0;
 
@@ -61,11 +74,10 @@ __device__ __forceinline__ void blur_strip(const uint8_t* __restrict__ src, uint
     auto hsum = [&](const BlurRows& R, int n, int i, unsigned (&H)[4]) {
         unsigned w0 = R.z[i], wp = R.q[i], wm = R.m[i];
         if (EDGE) {
-            if (redge) {  // gather the reflected bytes (the lines are in L1 by now)
-                const uint8_t* rp = col + blur_reflect(min(y0 + n - 3, h + 2), h) * pitch;
-                w0 = rp[ridx[0]] | (rp[ridx[1]] << 8) | (rp[ridx[2]] << 16) | (rp[ridx[3]] << 24);
-                wp = rp[ridx[4]] | (rp[ridx[5]] << 8) | (rp[ridx[6]] << 16) | (rp[ridx[7]] << 24);
-            }
+            const unsigned n0 = __byte_perm(__byte_perm(wm, w0, s1a), wp, s2a);
+            const unsigned n1 = __byte_perm(__byte_perm(wm, w0, s1b), wp, s2b);
+            w0 = n0;
+            wp = n1;
             if (ledge) wm = __byte_perm(w0, wp, 0x1234);  // x = -4..-1 -> pixels 4, 3, 2, 1
         }
         H[0] = __dp4a(__byte_perm(w0, wp, 0x4321), K2, __dp4a(__byte_perm(wm, w0, 0x4321), K1, 0u));
@@ -115,11 +127,8 @@ __device__ __forceinline__ void blur_strip(const uint8_t* __restrict__ src, uint
             // result byte p = bits 16..23 of sum[p]
             const unsigned out = __byte_perm(__byte_perm(sum[0], sum[1], 0x0062), __byte_perm(sum[2], sum[3], 0x0062), 0x5410);
             if (y0 + n0 + i - 6 < h) {
-                if (!EDGE || x0 + 4 <= w) {
-                    *(unsigned*)(orow + i * pitch) = out;
-                } else {
-                    for (int p = 0; p < w - x0; p++) orow[i * pitch + p] = (uint8_t)(out >> (8 * p));
-                }
+                // (the last word of a row may reach into the row padding, pitch = roundup64(w): nothing reads it)
+                *(unsigned*)(orow + i * pitch) = out;
             }
         }
     }

@@ -502,8 +502,8 @@ static int launch_chain(orbx_handle* h, cudaStream_t cs, int f0, int nb, bool st
         const LevelGeo& G = D.lv[l];
         dim3 grid((G.w + 255) / 256, (G.h + 3) / 4, nb), block(64, 4);
         dim3 gridFast((G.w + 255) / 256, (G.h + 4 * RESIZE_ROWS - 1) / (4 * RESIZE_ROWS), nb);
-        if (G.resizeFast) k_resize_fast<<<gridFast, block, 0, cs>>>(h->dPlan, l, h->dPyr, h->dTabs, f0);
-        else k_resize<<<grid, block, 0, cs>>>(h->dPlan, l, h->dPyr, h->dTabs, f0);
+        if (G.resizeFast) k_resize_fast<<<gridFast, block, 0, cs>>>(h->hp, l, h->dPyr, h->dTabs, f0);
+        else k_resize<<<grid, block, 0, cs>>>(h->hp, l, h->dPyr, h->dTabs, f0);
         KCHECK(h, "k_resize");
     }
     if (stamps) stamp(h, 2);
@@ -530,7 +530,7 @@ static int launch_chain(orbx_handle* h, cudaStream_t cs, int f0, int nb, bool st
     if (stamps) stamp(h, 3);
     // a few frames: one CTA per level is all the parallelism there is, so give it the widest CTA
     // (measured, single 640x480 / 1241x376 frame: 256 thr 160 / 278 us per call, 512 thr 155 / 220, 1024 thr 160 / 215)
-    k_quadtree<<<dim3(nl, nb), nb <= 4 ? std::max(512, h->qtThreads) : h->qtThreads, h->qtSmem, cs>>>(h->dPlan, h->dCand, h->dCandCount, h->dNodeOf, h->dSel,
+    k_quadtree<<<dim3(nl, nb), nb <= 4 ? std::max(512, h->qtThreads) : h->qtThreads, h->qtSmem, cs>>>(h->hp, h->dCand, h->dCandCount, h->dNodeOf, h->dSel,
                                                              h->dSelCount, h->qtC, h->qtC2, h->dErr, f0);
     KCHECK(h, "k_quadtree");
     if (stamps) stamp(h, 4);

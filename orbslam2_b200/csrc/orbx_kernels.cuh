@@ -84,8 +84,9 @@ __device__ __forceinline__ int next_pow2(int v) {
 // OpenCV 8U INTER_LINEAR fixed point: H = S[s]*a0 + S[s+1]*a1 (scale 2^11); out = ((b0*(H0>>4))>>16 + (b1*(H1>>4))>>16 + 2)>>2.
 // Tables (host-computed with OpenCV's float/double expressions): int2 {source index, a0 | a1<<16}.
 // One thread = 4 consecutive output pixels (one aligned 32-bit store).
-__global__ void __launch_bounds__(256) k_resize(const DevPlan* __restrict__ P, int level, uint8_t* __restrict__ pyr,
+__global__ void __launch_bounds__(256) k_resize(const __grid_constant__ DevPlan Pc, int level, uint8_t* __restrict__ pyr,
                                                 const int2* __restrict__ tabs, int f0) {
+    const DevPlan* P = &Pc;  // the plan rides in the kernel parameters (constant bank): no global loads in the prologue
     const LevelGeo& D = P->lv[level];
     const LevelGeo& S = P->lv[level - 1];
     const int x4 = (blockIdx.x * 64 + threadIdx.x) * 4;
@@ -158,9 +159,10 @@ __device__ __forceinline__ int quadrant_of(const short4 g, int x, int y) {
     return (x < mx ? 0 : 1) + (y < my ? 0 : 2);
 }
 
-__global__ void k_quadtree(const DevPlan* __restrict__ P, const u64* __restrict__ cand,
+__global__ void k_quadtree(const __grid_constant__ DevPlan Pc, const u64* __restrict__ cand,
                            const int* __restrict__ candCount, int* __restrict__ nodeOf, uint2* __restrict__ sel,
                            int* __restrict__ selCount, int C, int C2, int* __restrict__ err, int f0) {
+    const DevPlan* P = &Pc;  // the plan rides in the kernel parameters (constant bank): no global loads in the prologue
     extern __shared__ __align__(16) uint8_t qt_smem[];
     uint8_t* smem = qt_smem;
     const int level = blockIdx.x, f = f0 + blockIdx.y;

@@ -21,8 +21,9 @@ __device__ __forceinline__ unsigned dp2a_lo_u32(unsigned a16x2, unsigned b8x4, u
 
 #define RESIZE_ROWS 4  // output rows per thread
 
-__global__ void __launch_bounds__(256) k_resize_fast(const DevPlan* __restrict__ P, int level, uint8_t* __restrict__ pyr,
+__global__ void __launch_bounds__(256) k_resize_fast(const __grid_constant__ DevPlan Pc, int level, uint8_t* __restrict__ pyr,
                                                      const int2* __restrict__ tabs, int f0) {
+    const DevPlan* P = &Pc;  // the plan rides in the kernel parameters (constant bank): no global loads in the prologue
     const LevelGeo& D = P->lv[level];
     const LevelGeo& S = P->lv[level - 1];
     const int x4 = (blockIdx.x * 64 + threadIdx.x) * 4;
