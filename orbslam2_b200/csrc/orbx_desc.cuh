@@ -2,12 +2,14 @@
 // Reference: IC_Angle /root/reference/src/ORBextractor.cc:72-99 (+ cv::fastAtan2), computeOrbDescriptor :103-142,
 // border offset / octave / size :831-841, level scaling :909-915.
 //
-// One warp per keypoint, each warp walks KPW consecutive keypoints of one frame so that everything that depends only
+// One warp per keypoint, each warp walks kpw consecutive keypoints of one frame so that everything that depends only
 // on the lane is computed once: the circular-patch byte masks (lane = patch row v = lane-15, |u| <= umax[|v|]) and the
 // lane's 8 BRIEF pairs as floats (lane i produces descriptor byte i = pairs 8i..8i+7, LSB first).
-//   staging:     the 31x31 un-blurred patch and the 37x37 blurred patch (pattern reach +-18) are copied to shared memory
-//                with flat, row-crossing warp loads (~4 rows per load instead of one row per lane: 8x fewer L1 wavefronts)
-//   orientation: 9 words per row from shared memory, funnel-shift to the patch start, mask, two DP4A per word
+//   staging:     the 31x31 un-blurred patch and the 37x37 blurred patch (pattern reach +-18) arrive in shared memory as two
+//                TMA box loads per keypoint (48 x 31 and 64 x 37 bytes, x start rounded down to 16), double buffered, with
+//                the selection records fetched two keypoints ahead (round 1 / early round 2: 21 flat warp loads + 21 shared
+//                stores per keypoint, which held the kernel at 74 % of the L1 data pipe's wavefront rate)
+//   orientation: 9 words of the lane's box row from shared memory, funnel-shift to the patch start, mask, two DP4A per word
 //                (m10 += sum u*I with constant s8 weights, row sum for m01 = v * sum I), warp-shuffle reduction,
 //                OpenCV's fastAtan2 polynomial op for op in fp32 without FMA contraction.
 //   descriptor:  a = cos(angle), b = sin(angle); sample (round(x*b + y*a), round(x*a - y*b)) from the blurred level;
@@ -15,9 +17,13 @@
 #pragma once
 #include "orbx_internal.cuh"
 
-#define DESC_KPW 4  // keypoints per warp
-#define DESC_RAW_WORDS 288  // 31 rows x 9 words, rounded up to a multiple of 32
-#define DESC_BLR_WORDS 384  // 37 rows x 10 words, rounded up to a multiple of 32
+#define DESC_KPW 2         // keypoints per warp on the single-frame path (measured 2 / 4 / 8: 0.109 / 0.111 / 0.121 ms per call)
+#define DESC_KPW_BATCH 16  // ... and for large batches (measured 2 / 4 / 8 / 16 / 32: 0.330 / 0.300 / 0.292 / 0.290 / 0.305 ms)
+#define DESC_RAW_BW 48      // TMA box width of the un-blurred patch: 15 bytes of alignment slack + 31, rounded up to 16
+#define DESC_BLR_BW 64      // TMA box width of the blurred patch: 15 + 37, rounded up to 16
+#define DESC_RAW_BYTES 1536 // 48 x 31 = 1488, rounded up to 128 (TMA destination alignment)
+#define DESC_BUF_BYTES (DESC_RAW_BYTES + 2432)  // + 64 x 37 = 2368, rounded up to 128: one keypoint's two boxes
+#define DESC_SMEM_BYTES (8 * 2 * DESC_BUF_BYTES + 8 * 2 * 8)  // 8 warps x 2 buffers + their mbarriers
 
 __device__ signed char d_pattern[1024];  // 256 x (x1, y1, x2, y2), the reference's bit_pattern_31_
 
@@ -58,10 +64,12 @@ __host__ __device__ constexpr int desc_uweights(int j) {
                  ((unsigned)((4 * j - 13) & 0xFF) << 16) | ((unsigned)((4 * j - 12) & 0xFF) << 24));
 }
 
-__global__ void __launch_bounds__(256, 3) k_orient_desc(const DevPlan* __restrict__ P, const uint8_t* __restrict__ pyr,
-                                                     const uint8_t* __restrict__ blur, const uint2* __restrict__ sel,
-                                                     const int* __restrict__ selCount, orbx_kp* __restrict__ kps,
-                                                     uint8_t* __restrict__ desc, int* __restrict__ nOut, int f0) {
+// tmaps[l] / tmaps[ORBX_MAX_LEVELS + l]: 3-D (x, y, frame) u8 tensor maps of pyramid / blurred level l with boxes
+// DESC_RAW_BW x 31 and DESC_BLR_BW x 37 (device memory, written by the host before the launch).
+__global__ void __launch_bounds__(256, 3) k_orient_desc(const DevPlan* __restrict__ P, const CUtensorMap* __restrict__ tmaps,
+                                                     const uint2* __restrict__ sel, const int* __restrict__ selCount,
+                                                     orbx_kp* __restrict__ kps, uint8_t* __restrict__ desc,
+                                                     int* __restrict__ nOut, int* __restrict__ err, int f0, int kpw) {
     const int lane = threadIdx.x & 31;
     const int f = f0 + blockIdx.y;
     const int nl = P->nlevels;
@@ -76,7 +84,7 @@ __global__ void __launch_bounds__(256, 3) k_orient_desc(const DevPlan* __restric
     const int total = __shfl_sync(0xffffffffu, endOff, nl - 1);
     const int warpGlobal = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (warpGlobal == 0 && lane == 0) nOut[f] = total;
-    const int o0 = warpGlobal * DESC_KPW;
+    const int o0 = warpGlobal * kpw;  // kpw consecutive keypoints per warp (host: 4 for a few frames, more for large batches)
     if (o0 >= total) return;
 
     // lane constants: patch-row byte masks and the lane's 8 pattern pairs
@@ -111,55 +119,94 @@ __global__ void __launch_bounds__(256, 3) k_orient_desc(const DevPlan* __restric
         }
     }
 
-    // per-warp staging buffers: the un-blurred 31-row patch (9 words per row) and the blurred 37-row patch (10 words per
-    // row). Both are fetched with flat lane -> (row, word) indexing, so one warp-load touches ~4 rows instead of 32.
-    __shared__ unsigned sh_raw[256 / 32][DESC_RAW_WORDS];
-    __shared__ unsigned sh_blr[256 / 32][DESC_BLR_WORDS];
-    unsigned* raw = sh_raw[threadIdx.x >> 5];
-    unsigned* blr = sh_blr[threadIdx.x >> 5];
+    // Per-warp staging buffers, double buffered: the un-blurred 31-row patch and the blurred 37-row patch (pattern reach
+    // +-18) of a keypoint arrive as TWO TMA box loads (cp.async.bulk.tensor, one elected lane, completion on an mbarrier) —
+    // the patches of keypoint k+1 are in flight while keypoint k is evaluated. The box starts at the patch's x rounded
+    // down to 16 bytes (TMA's innermost start coordinate must be 16-byte aligned on sm_100a), hence the 48- and 64-byte
+    // rows. Before (21 flat warp loads + 21 shared stores per keypoint) the kernel sat at 74 % of the L1 data pipe's
+    // wavefront rate: ~105 cache-line touches per keypoint for the loads alone. TMA traffic does not pass through the LSU.
+    extern __shared__ __align__(128) uint8_t desc_smem[];
+    const int wib = threadIdx.x >> 5;
+    uint8_t* wbuf = desc_smem + wib * (2 * DESC_BUF_BYTES);
+    unsigned long long* bars = (unsigned long long*)(desc_smem + 8 * 2 * DESC_BUF_BYTES) + 2 * wib;
+    const uint32_t bar0 = (uint32_t)__cvta_generic_to_shared(bars);
+    if (lane == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar0));
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar0 + 8u));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncwarp();
 
-    for (int o = o0; o < min(o0 + DESC_KPW, total); o++) {
-        // level of output index o
+    // selection records run two keypoints ahead of the evaluation (record k+2 is requested while keypoint k is evaluated,
+    // its boxes one iteration later), so neither the record nor the patch latency sits on the warp's critical path
+    const int nk = min(kpw, total - o0);
+    auto fetch = [&](int k, int& level, uint2& s) {
+        const int o = o0 + k;
         const unsigned ge = __ballot_sync(0xffffffffu, lane < nl && o >= endOff);
-        const int level = __popc(ge);
+        level = __popc(ge);
         const int before = level ? __shfl_sync(0xffffffffu, endOff, level - 1) : 0;
-        const LevelGeo& G = P->lv[level];
-        const uint2 s = sel[(long long)f * P->selStride + G.selOff + (o - before)];
-        const int x = s.x & 0xFFFF, y = s.x >> 16;
-        const long long lvlOff = G.pyrOff + (long long)f * G.frameStride;
-        const int pitch = G.pitch;
-
-        // ---- stage both patches (all loads of the keypoint are in flight together)
-        const int xs = x - 15, a0 = xs & ~3, sh = (xs & 3) * 8;
-        const int xb = x - 18, b0 = xb & ~3, shB = xb & 3;
-        {
-            const uint8_t* rbase = pyr + lvlOff + (long long)(y - 15) * pitch + a0;
-            const uint8_t* bbase = blur + lvlOff + (long long)(y - 18) * pitch + b0;
-            unsigned rv[DESC_RAW_WORDS / 32], bv[DESC_BLR_WORDS / 32];
-#pragma unroll
-            for (int i = 0; i < DESC_RAW_WORDS / 32; i++) {
-                const int idx = lane + 32 * i;
-                const int row = (idx * 7282) >> 16;  // idx / 9 for idx < 288
-                rv[i] = (idx < 31 * 9) ? *(const unsigned*)(rbase + row * pitch + 4 * (idx - row * 9)) : 0u;
-            }
-#pragma unroll
-            for (int i = 0; i < DESC_BLR_WORDS / 32; i++) {
-                const int idx = lane + 32 * i;
-                const int row = (idx * 6554) >> 16;  // idx / 10 for idx < 384
-                bv[i] = (idx < 37 * 10) ? *(const unsigned*)(bbase + row * pitch + 4 * (idx - row * 10)) : 0u;
-            }
-            __syncwarp();  // the previous keypoint's readers are done with the buffers
-#pragma unroll
-            for (int i = 0; i < DESC_RAW_WORDS / 32; i++) raw[lane + 32 * i] = rv[i];
-#pragma unroll
-            for (int i = 0; i < DESC_BLR_WORDS / 32; i++) blr[lane + 32 * i] = bv[i];
-            __syncwarp();
+        s = sel[(long long)f * P->selStride + P->lv[level].selOff + (o - before)];
+    };
+    int lvA = 0, lvB = 0, lvC = 0;
+    uint2 svA = make_uint2(0u, 0u), svB = svA, svC = svA;
+    fetch(0, lvA, svA);
+    if (nk > 1) fetch(1, lvB, svB);
+    auto stage = [&](int level, uint2 s, int buf) {  // lane 0: request both boxes of one keypoint
+        if (lane == 0) {
+            const int x = s.x & 0xFFFF, y = s.x >> 16;
+            const uint32_t dst = (uint32_t)__cvta_generic_to_shared(wbuf + buf * DESC_BUF_BYTES);
+            const uint32_t bar = bar0 + 8u * buf;
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar),
+                         "r"((uint32_t)(DESC_RAW_BW * 31 + DESC_BLR_BW * 37))
+                         : "memory");
+            asm volatile(
+                "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+                ::"r"(dst), "l"(tmaps + level), "r"((x - 15) & ~15), "r"(y - 15), "r"(f), "r"(bar)
+                : "memory");
+            asm volatile(
+                "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+                ::"r"(dst + DESC_RAW_BYTES), "l"(tmaps + ORBX_MAX_LEVELS + level), "r"((x - 18) & ~15), "r"(y - 18), "r"(f), "r"(bar)
+                : "memory");
         }
+    };
+    stage(lvA, svA, 0);
+
+    for (int k = 0; k < nk; k++) {
+        const int o = o0 + k;
+        const int level = lvA;
+        const uint2 s = svA;
+        const LevelGeo& G = P->lv[level];
+        const int x = s.x & 0xFFFF, y = s.x >> 16;
+        const int xs = x - 15, sh = (xs & 3) * 8;
+        if (k + 1 < nk) stage(lvB, svB, (k + 1) & 1);
+        if (k + 2 < nk) fetch(k + 2, lvC, svC);
+        {   // bounded wait for this keypoint's boxes (a lost TMA must not hang the GPU: flag the error and go on)
+            const uint32_t bar = bar0 + 8u * (k & 1), parity = (uint32_t)((k >> 1) & 1);
+            uint32_t done = 0;
+            int spins = 0;
+            while (!done) {
+                asm volatile(
+                    "{\n\t.reg .pred p;\n\t"
+                    "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+                    "selp.u32 %0, 1, 0, p;\n\t}"
+                    : "=r"(done)
+                    : "r"(bar), "r"(parity)
+                    : "memory");
+                if (!done && ++spins > (1 << 22)) {
+                    atomicExch(err, 6);
+                    break;
+                }
+            }
+        }
+        const unsigned* raw = (const unsigned*)(wbuf + (k & 1) * DESC_BUF_BYTES);
+        const uint8_t* blr = wbuf + (k & 1) * DESC_BUF_BYTES + DESC_RAW_BYTES;
 
         // ---- IC_Angle
         int m10 = 0, rs = 0;
         if (rowOn) {
-            const unsigned* rowp = raw + lane * 9;  // bank = (9 * lane + j) % 32: conflict free
+            // row = lane; the patch starts (xs & 15) bytes into the 48-byte box row (12-word pitch: rows l, l+8, l+16, l+24
+            // share banks, a 4-way conflict on 9 loads — still far fewer wavefronts than staging the patch by hand)
+            const unsigned* rowp = raw + lane * (DESC_RAW_BW / 4) + ((xs & 15) >> 2);
             unsigned w[9];
 #pragma unroll
             for (int j = 0; j < 9; j++) w[j] = rowp[j];
@@ -188,13 +235,13 @@ __global__ void __launch_bounds__(256, 3) k_orient_desc(const DevPlan* __restric
         double sd, cd;
         sincos((double)rad, &sd, &cd);
         const float a = (float)cd, b = (float)sd;
-        const uint8_t* ctr = (const uint8_t*)blr + 18 * 40 + 18 + shB;  // (row, col) of the keypoint inside the staged patch
+        const uint8_t* ctr = blr + 18 * DESC_BLR_BW + 18 + ((x - 18) & 15);  // (row, col) of the keypoint inside the staged box
         int t[16];
 #pragma unroll
         for (int k = 0; k < 16; k++) {
             const int r = round_half_even(__fadd_rn(__fmul_rn(px[k], b), __fmul_rn(py[k], a)));
             const int c = round_half_even(__fsub_rn(__fmul_rn(px[k], a), __fmul_rn(py[k], b)));
-            t[k] = ctr[r * 40 + c];
+            t[k] = ctr[r * DESC_BLR_BW + c];
         }
         int val = 0;
 #pragma unroll
@@ -212,5 +259,8 @@ __global__ void __launch_bounds__(256, 3) k_orient_desc(const DevPlan* __restric
             kp.class_id = -1;
             kps[oo] = kp;
         }
+        __syncwarp();  // every lane is done with this buffer before lane 0 requests keypoint k + 2 into it
+        lvA = lvB; svA = svB;
+        lvB = lvC; svB = svC;
     }
 }

@@ -42,6 +42,7 @@ struct orbx_handle {
                           // 2 = k_fast2 (two-threshold pre-test + work lists: identical candidates, measured 1.47x SLOWER,
                           // profiles/r02d_fast2_analysis.md). ORBX_FAST=1|2|3 selects; ORBX_FAST_V2=1 is the old spelling of 2.
     int fastNF = 0;       // variant 3: which (NF1, NF2) instantiation (ORBX_FAST3_NF, tuning only)
+    int descKpw = 0;      // k_orient_desc keypoints per warp override (ORBX_DESC_KPW, tuning only)
     cudaStream_t stream = nullptr;
     int inSpace = ORBX_MEM_HOST, outSpace = ORBX_MEM_HOST;
     // reference ctor tables
@@ -57,6 +58,7 @@ struct orbx_handle {
     uint8_t* dBlur = nullptr;
     size_t pyrBytes = 0;
     int2* dTabs = nullptr;
+    CUtensorMap* dDescMaps = nullptr;  // k_orient_desc: [level] pyramid boxes, [ORBX_MAX_LEVELS + level] blurred boxes
     u64* dCand = nullptr;
     int* dNodeOf = nullptr;
     int* dCandCount = nullptr;
@@ -184,13 +186,13 @@ static PFN_encodeTiled get_encode() {
 
 static void free_plan(orbx_handle* h) {
     if (h->gExec) { cudaGraphExecDestroy(h->gExec); h->gExec = nullptr; }
-    cudaFree(h->dPlan); cudaFree(h->dFastSt); cudaFree(h->dPyr); cudaFree(h->dBlur); cudaFree(h->dTabs); cudaFree(h->dCand);
+    cudaFree(h->dPlan); cudaFree(h->dFastSt); cudaFree(h->dPyr); cudaFree(h->dBlur); cudaFree(h->dTabs); cudaFree(h->dDescMaps); cudaFree(h->dCand);
     cudaFree(h->dNodeOf); cudaFree(h->dCandCount); cudaFree(h->dSel); cudaFree(h->dSelCount); cudaFree(h->dOutBlock);
     cudaFree(h->dExport);
     if (h->hCounts) cudaFreeHost(h->hCounts);
     if (h->hStage) cudaFreeHost(h->hStage);
     h->hStage = nullptr; h->dOutBlock = nullptr; h->dErr = nullptr;
-    h->dPlan = nullptr; h->dFastSt = nullptr; h->dPyr = h->dBlur = nullptr; h->dTabs = nullptr; h->dCand = nullptr; h->dNodeOf = nullptr;
+    h->dPlan = nullptr; h->dFastSt = nullptr; h->dPyr = h->dBlur = nullptr; h->dTabs = nullptr; h->dDescMaps = nullptr; h->dCand = nullptr; h->dNodeOf = nullptr;
     h->dCandCount = nullptr; h->dSel = nullptr; h->dSelCount = nullptr; h->dKps = nullptr; h->dDesc = nullptr;
     h->dNOut = nullptr; h->dExport = nullptr; h->exportBytes = 0; h->hCounts = nullptr;
     h->planW = h->planH = h->planBatch = 0;
@@ -359,6 +361,26 @@ static int build_plan(orbx_handle* h, int w, int hgt, int batch) {
                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         if (r != CUDA_SUCCESS) FAIL(ORBX_ECUDA, "cuTensorMapEncodeTiled failed for level %d (CUresult %d)", l, (int)r);
     }
+    {   // k_orient_desc fetches a keypoint's two patches as TMA boxes: same tensors, boxes 48 x 31 and 64 x 37
+        std::vector<CUtensorMap> dm(2 * ORBX_MAX_LEVELS);
+        memset(dm.data(), 0, dm.size() * sizeof(CUtensorMap));
+        for (int l = 0; l < p.nlevels; l++) {
+            const LevelGeo& G = D.lv[l];
+            cuuint64_t gdim[3] = {(cuuint64_t)G.w, (cuuint64_t)G.h, (cuuint64_t)batch};
+            cuuint64_t gstr[2] = {(cuuint64_t)G.pitch, (cuuint64_t)G.frameStride};
+            cuuint32_t estr[3] = {1, 1, 1};
+            for (int which = 0; which < 2; which++) {
+                cuuint32_t box[3] = {(cuuint32_t)(which ? DESC_BLR_BW : DESC_RAW_BW), (cuuint32_t)(which ? 37 : 31), 1};
+                CUresult r = enc(&dm[which * ORBX_MAX_LEVELS + l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3,
+                                 (which ? h->dBlur : h->dPyr) + G.pyrOff, gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                                 CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                if (r != CUDA_SUCCESS) FAIL(ORBX_ECUDA, "cuTensorMapEncodeTiled failed for the patch boxes of level %d (CUresult %d)", l, (int)r);
+            }
+        }
+        CK(cudaMalloc(&h->dDescMaps, dm.size() * sizeof(CUtensorMap)));
+        CK(cudaMemcpy(h->dDescMaps, dm.data(), dm.size() * sizeof(CUtensorMap), cudaMemcpyHostToDevice));
+        CK(cudaFuncSetAttribute(k_orient_desc, cudaFuncAttributeMaxDynamicSharedMemorySize, DESC_SMEM_BYTES));
+    }
     if (h->fastSmem > 227 * 1024) FAIL(ORBX_ESHAPE, "FAST supertile needs %zu bytes of shared memory", h->fastSmem);
     if (h->fastVer == 2) CK(cudaFuncSetAttribute(k_fast2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->fastSmem));
     else CK(cudaFuncSetAttribute(fast_kernel(h->fastVer, h->fastNF), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->fastSmem));
@@ -392,6 +414,7 @@ extern "C" int orbx_create(const orbx_params* p, int device, orbx_t** out) {
     h->device = device;
     { const char* v = getenv("ORBX_FAST_V2"); if (v && v[0] == '1') h->fastVer = 2; }
     { const char* v = getenv("ORBX_FAST"); if (v && v[0] >= '1' && v[0] <= '3') h->fastVer = v[0] - '0'; }
+    { const char* v = getenv("ORBX_DESC_KPW"); if (v && atoi(v) >= 1 && atoi(v) <= 64) h->descKpw = atoi(v); }
     { const char* v = getenv("ORBX_FAST3_NF"); if (v && v[0] >= '0' && v[0] <= '9') h->fastNF = v[0] - '0'; }
     { const char* v = getenv("ORBX_NO_GRAPH"); h->gDisabled = v && v[0] == '1'; }
     init_tables(h);
@@ -541,8 +564,14 @@ static int launch_chain(orbx_handle* h, cudaStream_t cs, int f0, int nb, bool st
         KCHECK(h, "k_blur");
     }
     if (stamps) stamp(h, 5);
-    k_orient_desc<<<dim3((D.selStride + 8 * DESC_KPW - 1) / (8 * DESC_KPW), nb), 256, 0, cs>>>(
-        h->dPlan, h->dPyr, h->dBlur, h->dSel, h->dSelCount, h->dKps, h->dDesc, h->dNOut, f0);
+    {
+        // keypoints per warp: a warp's prologue (level prefix, pattern, first record and first boxes: ~36 % of its time at 4
+        // keypoints) amortises over more keypoints when there are enough frames to keep every SM busy anyway
+        int kpw = nb <= 4 ? DESC_KPW : DESC_KPW_BATCH;
+        if (h->descKpw > 0) kpw = h->descKpw;
+        k_orient_desc<<<dim3((D.selStride + 8 * kpw - 1) / (8 * kpw), nb), 256, DESC_SMEM_BYTES, cs>>>(
+            h->dPlan, h->dDescMaps, h->dSel, h->dSelCount, h->dKps, h->dDesc, h->dNOut, h->dErr, f0, kpw);
+    }
     KCHECK(h, "k_orient_desc");
     if (stamps) stamp(h, 6);
     return ORBX_OK;
@@ -865,7 +894,7 @@ extern "C" int orbx_extract_batch_wait(orbx_t* h, int* n) {
     if (h->hCounts[batch] != 0) {
         const int code = h->hCounts[batch];
         cudaMemsetAsync(h->dErr, 0, sizeof(int), st);
-        FAIL(ORBX_ECUDA, "device-side error flag %d (2 = TMA wait timed out, 3 = candidate overflow, 4/5 = quadtree bound)", code);
+        FAIL(ORBX_ECUDA, "device-side error flag %d (2 = FAST TMA wait timed out, 3 = candidate overflow, 4/5 = quadtree bound, 6 = descriptor TMA wait timed out)", code);
     }
     int worst = 0;
     for (int f = 0; f < batch; f++) {
