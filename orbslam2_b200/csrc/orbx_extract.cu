@@ -553,7 +553,7 @@ static int launch_chain(orbx_handle* h, cudaStream_t cs, int f0, int nb, bool st
     if (stamps) stamp(h, 3);
     // a few frames: one CTA per level is all the parallelism there is, so give it the widest CTA
     // (measured, single 640x480 / 1241x376 frame: 256 thr 160 / 278 us per call, 512 thr 155 / 220, 1024 thr 160 / 215)
-    k_quadtree<<<dim3(nl, nb), nb <= 4 ? std::max(512, h->qtThreads) : h->qtThreads, h->qtSmem, cs>>>(h->hp, h->dCand, h->dCandCount, h->dNodeOf, h->dSel,
+    k_quadtree<<<dim3(nb, nl), nb <= 4 ? std::max(512, h->qtThreads) : h->qtThreads, h->qtSmem, cs>>>(h->hp, h->dCand, h->dCandCount, h->dNodeOf, h->dSel,
                                                              h->dSelCount, h->qtC, h->qtC2, h->dErr, f0);
     KCHECK(h, "k_quadtree");
     if (stamps) stamp(h, 4);

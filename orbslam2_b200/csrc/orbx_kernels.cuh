@@ -165,7 +165,8 @@ __global__ void k_quadtree(const __grid_constant__ DevPlan Pc, const u64* __rest
     const DevPlan* P = &Pc;  // the plan rides in the kernel parameters (constant bank): no global loads in the prologue
     extern __shared__ __align__(16) uint8_t qt_smem[];
     uint8_t* smem = qt_smem;
-    const int level = blockIdx.x, f = f0 + blockIdx.y;
+    // (frame-major launch order: the level-0 CTAs of all frames — the longest — are dispatched first)
+    const int level = blockIdx.y, f = f0 + blockIdx.x;
     const LevelGeo& G = P->lv[level];
     const int nl = P->nlevels;
     const int tid = threadIdx.x, T = blockDim.x;
