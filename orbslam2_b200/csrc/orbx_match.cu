@@ -174,14 +174,16 @@ __device__ __forceinline__ int reflect101_i(int p, int len) {
 // the band radius is constant inside a level: so per octave the candidates are ONE contiguous run found by two binary
 // searches on y (a superset, (row - r - 1, row + r + 1); the exact band test is still applied) instead of a scan of all
 // right keypoints — the role of vRowIndices in the reference (src/Frame.cc:476-492).
-__global__ void __launch_bounds__(256) k_stereo_match(const DevPlan* __restrict__ P, const orbx_kp* __restrict__ kL,
-                                                      const uint8_t* __restrict__ dL, const int* __restrict__ nL,
-                                                      const uint8_t* __restrict__ pyrL, const orbx_kp* __restrict__ kR,
-                                                      const uint8_t* __restrict__ dR, const int* __restrict__ nR,
-                                                      const int* __restrict__ selCountR,
-                                                      const uint8_t* __restrict__ pyrR, float mbf, float minD, float maxD,
-                                                      float* __restrict__ uRight, float* __restrict__ depth,
-                                                      int* __restrict__ sad, int outStride) {
+// Two kernels (round 2): the candidate search is a chain of dependent loads per warp (ncu of the fused kernel: 8 warps per
+// issue slot waiting on the long scoreboard, issue 40 %), so it runs as its own kernel at 40 registers and 1.5x the resident
+// warps, leaving the right keypoint's index (or -1) in sad[]; k_stereo_sad, which needs the 22 accumulators, then runs the
+// 11-shift sweep for the keypoints that have a candidate.
+__global__ void __launch_bounds__(256, 6) k_stereo_match(const DevPlan* __restrict__ P, const orbx_kp* __restrict__ kL,
+                                                         const uint8_t* __restrict__ dL, const int* __restrict__ nL,
+                                                         const orbx_kp* __restrict__ kR, const uint8_t* __restrict__ dR,
+                                                         const int* __restrict__ nR, const int* __restrict__ selCountR,
+                                                         float minD, float maxD, float* __restrict__ uRight,
+                                                         float* __restrict__ depth, int* __restrict__ sad, int outStride) {
     const int lane = threadIdx.x & 31;
     const int iL = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     const int f = blockIdx.y;
@@ -249,7 +251,27 @@ __global__ void __launch_bounds__(256) k_stereo_match(const DevPlan* __restrict_
     best = shfl_min_u64(best);
     const int bestDist = (int)(best >> 32);
     if (bestDist >= 75 || (best & 0xFFFFFFFFull) == 0xFFFFFFFFull) return;  // thOrbDist = (TH_HIGH+TH_LOW)/2
-    const int bestIdxR = (int)(best & 0xFFFFFFFFull);
+    if (lane == 0) sad[kb + iL] = (int)(best & 0xFFFFFFFFull);  // for k_stereo_sad
+}
+
+__global__ void __launch_bounds__(256) k_stereo_sad(const DevPlan* __restrict__ P, const orbx_kp* __restrict__ kL,
+                                                    const int* __restrict__ nL, const uint8_t* __restrict__ pyrL,
+                                                    const orbx_kp* __restrict__ kR, const uint8_t* __restrict__ pyrR, float mbf,
+                                                    float minD, float maxD, float* __restrict__ uRight,
+                                                    float* __restrict__ depth, int* __restrict__ sad, int outStride) {
+    const int lane = threadIdx.x & 31;
+    const int iL = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int f = blockIdx.y;
+    if (iL >= nL[f]) return;
+    const long long kb = (long long)f * P->selStride;
+    const long long ob = (long long)f * outStride;
+    const int bestIdxR = sad[kb + iL];
+    if (bestIdxR < 0) return;
+    __syncwarp();  // every lane has read the index before lane 0 overwrites it
+    if (lane == 0) sad[kb + iL] = -1;
+    const orbx_kp kp = kL[kb + iL];
+    const int levelL = kp.octave;
+    const float uL = kp.x;
 
     const LevelGeo& G = P->lv[levelL];
     const float uR0 = kR[kb + bestIdxR].x;
@@ -814,9 +836,10 @@ extern "C" int orbx_stereo_match_batch(orbx_t* left, orbx_t* right, float mbf, f
     for (int f = 0; f < batch; f++) maxN = std::max(maxN, A.hCounts[f]);
     if (maxN > cap) FAIL(ORBX_ECAP, "cap_per_frame %d < %d left keypoints", cap, maxN);
     if (maxN == 0) maxN = 1;
-    k_stereo_match<<<dim3((maxN + 7) / 8, batch), 256, 0, st>>>(A.dPlan, A.dKps, A.dDesc, A.dNOut, A.dPyr, B.dKps, B.dDesc,
-                                                               B.dNOut, B.dSelCount, B.dPyr, mbf, minD, maxD, oU, oZ,
-                                                               dSad, oStride);
+    k_stereo_match<<<dim3((maxN + 7) / 8, batch), 256, 0, st>>>(A.dPlan, A.dKps, A.dDesc, A.dNOut, B.dKps, B.dDesc, B.dNOut,
+                                                               B.dSelCount, minD, maxD, oU, oZ, dSad, oStride);
+    k_stereo_sad<<<dim3((maxN + 7) / 8, batch), 256, 0, st>>>(A.dPlan, A.dKps, A.dNOut, A.dPyr, B.dKps, B.dPyr, mbf, minD, maxD, oU,
+                                                             oZ, dSad, oStride);
     int P2 = 1;
     while (P2 < maxN) P2 <<= 1;
     // more than 6144 left keypoints need over 48 KB of dynamic shared memory: opt in (up to 227 KB = 16384 keypoints,
@@ -832,7 +855,7 @@ extern "C" int orbx_stereo_match_batch(orbx_t* left, orbx_t* right, float mbf, f
         }
     }
     k_stereo_cut<<<batch, 1024, (size_t)P2 * 8, st>>>(A.dPlan, A.dNOut, dSad, oU, oZ, oStride, P2);
-    orbx_count_launch((orbx_handle*)left, 2);
+    orbx_count_launch((orbx_handle*)left, 3);
     CK(cudaGetLastError());
     if (A.outSpace == ORBX_MEM_HOST) {
         const int cols = std::min(cap, stride);
