@@ -553,8 +553,12 @@ static int launch_chain(orbx_handle* h, cudaStream_t cs, int f0, int nb, bool st
     if (stamps) stamp(h, 3);
     // a few frames: one CTA per level is all the parallelism there is, so give it the widest CTA
     // (measured, single 640x480 / 1241x376 frame: 256 thr 160 / 278 us per call, 512 thr 155 / 220, 1024 thr 160 / 215)
-    k_quadtree<<<dim3(nb, nl), nb <= 4 ? std::max(512, h->qtThreads) : h->qtThreads, h->qtSmem, cs>>>(h->hp, h->dCand, h->dCandCount, h->dNodeOf, h->dSel,
-                                                             h->dSelCount, h->qtC, h->qtC2, h->dErr, f0);
+    // ... and the same holds while every CTA of the launch is resident at once (the kernel then lasts as long as its level-0
+    // CTA): 512 threads as long as nb x levels such CTAs fit on the 148 SMs (config 2, 32-64 frames of 2000 keypoints:
+    // 117 us at 256 threads, one wave, 30 % of the warp slots busy)
+    const int qtT = (nb <= 4 || (long long)nb * nl * 512 <= 148LL * 2048) ? std::max(512, h->qtThreads) : h->qtThreads;
+    k_quadtree<<<dim3(nb, nl), qtT, h->qtSmem, cs>>>(h->hp, h->dCand, h->dCandCount, h->dNodeOf, h->dSel,
+                                                     h->dSelCount, h->qtC, h->qtC2, h->dErr, f0);
     KCHECK(h, "k_quadtree");
     if (stamps) stamp(h, 4);
     if (fork) {
@@ -567,7 +571,10 @@ static int launch_chain(orbx_handle* h, cudaStream_t cs, int f0, int nb, bool st
     {
         // keypoints per warp: a warp's prologue (level prefix, pattern, first record and first boxes: ~36 % of its time at 4
         // keypoints) amortises over more keypoints when there are enough frames to keep every SM busy anyway
-        int kpw = nb <= 4 ? DESC_KPW : DESC_KPW_BATCH;
+        // (by the number of keypoint slots of the launch: 16 needs a few waves of warps to pay, 4K frames in small batches
+        // measured slower with it: config 5, 16 frames x 8000 keypoints, 0.153 ms at 4 against 0.201 at 16)
+        const long long slots = (long long)nb * D.selStride;
+        int kpw = nb <= 4 ? DESC_KPW : slots >= 400000 ? DESC_KPW_BATCH : slots >= 150000 ? 8 : 4;
         if (h->descKpw > 0) kpw = h->descKpw;
         k_orient_desc<<<dim3((D.selStride + 8 * kpw - 1) / (8 * kpw), nb), 256, DESC_SMEM_BYTES, cs>>>(
             h->dPlan, h->dDescMaps, h->dSel, h->dSelCount, h->dKps, h->dDesc, h->dNOut, h->dErr, f0, kpw);
