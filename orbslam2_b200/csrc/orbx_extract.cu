@@ -751,7 +751,7 @@ extern "C" int orbx_extract_batch_submit(orbx_t* h, const uint8_t* imgs, int bat
             const int byBytes = (int)std::max<size_t>(8, std::min<size_t>(48, (size_t)48 * 640 * 480 / ((size_t)w * hgt)));
             chunk = h->chunk > 0 ? h->chunk : byBytes;
             if (batch < 2 * chunk) chunk = h->chunk > 0 || batch < 4 ? batch : std::max(1, batch / 2);
-        } else if (batch >= 96) {
+        } else if (batch >= 96 || (batch >= 2 && (long long)batch * w * hgt >= 96LL * 640 * 480)) {  // (or as many pixels in fewer frames)
             chunk = (batch + 1) / 2;  // device buffers: two halves on the two compute streams, so one half's kernel
                                       // tails and its latency-bound quadtree overlap the other's kernels (measured +2 %)
         }

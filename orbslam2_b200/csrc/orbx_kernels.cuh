@@ -153,6 +153,8 @@ struct QtSmem {
     int* ws;
 };
 
+#define QT_U 4  // candidates per thread and trip in the passes over the candidate list
+
 __device__ __forceinline__ int quadrant_of(const short4 g, int x, int y) {
     const int mx = g.x + ((g.y - g.x + 1) >> 1);  // UL.x + ceil((UR.x-UL.x)/2)
     const int my = g.z + ((g.w - g.z + 1) >> 1);
@@ -206,13 +208,24 @@ __global__ void k_quadtree(const __grid_constant__ DevPlan Pc, const u64* __rest
         S.geoA[i] = make_short4((short)(int)__fmul_rn(hX, (float)i), (short)(int)__fmul_rn(hX, (float)(i + 1)), 0,
                                 (short)G.treeH);
     __syncthreads();
-    for (int k = tid; k < n; k += T) {
-        int x, y, s;
-        cand_unpack(keys[k], G, x, y, s);
-        int idx = (int)__fdiv_rn((float)x, hX);
-        idx = min(idx, nNodes - 1);
-        nod[k] = idx;
-        atomicAdd(&S.cntA[idx], 1);
+    // (every pass over the candidates takes QT_U of them per trip with all their loads issued first: a trip is one global
+    // round trip, and the level-0 CTA of a large frame makes dozens of trips per pass — 4K frames: 558 us per launch before)
+    for (int k0 = tid; k0 < n; k0 += QT_U * T) {
+        u64 kk[QT_U];
+#pragma unroll
+        for (int j = 0; j < QT_U; j++) kk[j] = (k0 + j * T < n) ? keys[k0 + j * T] : 0ull;
+#pragma unroll
+        for (int j = 0; j < QT_U; j++) {
+            const int k = k0 + j * T;
+            if (k < n) {
+                int x, y, s;
+                cand_unpack(kk[j], G, x, y, s);
+                int idx = (int)__fdiv_rn((float)x, hX);
+                idx = min(idx, nNodes - 1);
+                nod[k] = idx;
+                atomicAdd(&S.cntA[idx], 1);
+            }
+        }
     }
     __syncthreads();
 
@@ -271,13 +284,25 @@ __global__ void k_quadtree(const __grid_constant__ DevPlan Pc, const u64* __rest
         }
         __syncthreads();
         // child key counts
-        for (int k = tid; k < n; k += T) {
-            const int nd = nod[k];
-            const int s = S.slotOf[nd];
-            if (s >= 0) {
-                int x, y, sc;
-                cand_unpack(keys[k], G, x, y, sc);
-                atomicAdd(&S.childCnt[4 * s + quadrant_of(S.geoA[nd], x, y)], 1);
+        for (int k0 = tid; k0 < n; k0 += QT_U * T) {
+            u64 kk[QT_U];
+            int nn[QT_U];
+#pragma unroll
+            for (int j = 0; j < QT_U; j++) {
+                const bool in = k0 + j * T < n;
+                kk[j] = in ? keys[k0 + j * T] : 0ull;
+                nn[j] = in ? nod[k0 + j * T] : -1;
+            }
+#pragma unroll
+            for (int j = 0; j < QT_U; j++) {
+                if (nn[j] < 0) continue;
+                const int nd = nn[j];
+                const int s = S.slotOf[nd];
+                if (s >= 0) {
+                    int x, y, sc;
+                    cand_unpack(kk[j], G, x, y, sc);
+                    atomicAdd(&S.childCnt[4 * s + quadrant_of(S.geoA[nd], x, y)], 1);
+                }
             }
         }
         __syncthreads();
@@ -342,15 +367,27 @@ __global__ void k_quadtree(const __grid_constant__ DevPlan Pc, const u64* __rest
             S.cntB[id] = cc;
         }
         __syncthreads();
-        for (int k = tid; k < n; k += T) {
-            const int nd = nod[k];
-            const int s = S.slotOf[nd];
-            if (s >= 0 && S.rankOfSlot[s] < expandCount) {
-                int x, y, sc;
-                cand_unpack(keys[k], G, x, y, sc);
-                nod[k] = nSurv + S.childNew[4 * S.rankOfSlot[s] + quadrant_of(S.geoA[nd], x, y)];
-            } else
-                nod[k] = S.remap[nd];
+        for (int k0 = tid; k0 < n; k0 += QT_U * T) {
+            u64 kk[QT_U];
+            int nn[QT_U];
+#pragma unroll
+            for (int j = 0; j < QT_U; j++) {
+                const bool in = k0 + j * T < n;
+                kk[j] = in ? keys[k0 + j * T] : 0ull;
+                nn[j] = in ? nod[k0 + j * T] : -1;
+            }
+#pragma unroll
+            for (int j = 0; j < QT_U; j++) {
+                if (nn[j] < 0) continue;
+                const int nd = nn[j];
+                const int s = S.slotOf[nd];
+                if (s >= 0 && S.rankOfSlot[s] < expandCount) {
+                    int x, y, sc;
+                    cand_unpack(kk[j], G, x, y, sc);
+                    nod[k0 + j * T] = nSurv + S.childNew[4 * S.rankOfSlot[s] + quadrant_of(S.geoA[nd], x, y)];
+                } else
+                    nod[k0 + j * T] = S.remap[nd];
+            }
         }
         __syncthreads();
         {
@@ -366,7 +403,19 @@ __global__ void k_quadtree(const __grid_constant__ DevPlan Pc, const u64* __rest
     u64* best = (u64*)S.childCnt;  // 2*C u64 available
     for (int i = tid; i < nNodes; i += T) best[i] = 0;
     __syncthreads();
-    for (int k = tid; k < n; k += T) atomicMax(&best[nod[k]], keys[k]);
+    for (int k0 = tid; k0 < n; k0 += QT_U * T) {
+        u64 kk[QT_U];
+        int nn[QT_U];
+#pragma unroll
+        for (int j = 0; j < QT_U; j++) {
+            const bool in = k0 + j * T < n;
+            kk[j] = in ? keys[k0 + j * T] : 0ull;
+            nn[j] = in ? nod[k0 + j * T] : -1;
+        }
+#pragma unroll
+        for (int j = 0; j < QT_U; j++)
+            if (nn[j] >= 0) atomicMax(&best[nn[j]], kk[j]);
+    }
     __syncthreads();
     const int P2 = next_pow2(nNodes);
     for (int i = tid; i < P2; i += T) {
