@@ -135,11 +135,11 @@ __device__ __forceinline__ void blur_strip(const uint8_t* __restrict__ src, uint
 }
 
 __global__ void __launch_bounds__(32 * BLUR_WARPS, 6) k_blur(const DevPlan* __restrict__ P, const uint8_t* __restrict__ pyr,
-                                                          uint8_t* __restrict__ blur, int f0) {
+                                                          uint8_t* __restrict__ blur, int f0, int tile0, int tileEnd) {
     const int lane = threadIdx.x & 31;
     const int f = f0 + blockIdx.y;
-    int unit = blockIdx.x * BLUR_WARPS + (threadIdx.x >> 5);
-    if (unit >= P->totalBlurTiles) return;
+    int unit = tile0 + blockIdx.x * BLUR_WARPS + (threadIdx.x >> 5);  // strips [tile0, tileEnd): all levels, or one level's
+    if (unit >= tileEnd) return;
     int level = 0;
     while (level + 1 < P->nlevels && unit >= P->lv[level + 1].blurTileBase) level++;
     const LevelGeo& G = P->lv[level];

@@ -23,7 +23,7 @@ void orbx_set_err(const char* fmt, ...) {
 extern "C" const char* orbx_last_error_string(void) { return g_err; }
 extern "C" const char* orbx_version(void) { return "orbx 0.1 (sm_100a)"; }
 
-typedef void (*fast_kernel_t)(const TmapPack, const FastSt*, u64*, int*, int*, int);
+typedef void (*fast_kernel_t)(const TmapPack, const FastSt*, u64*, int*, int*, int, int);
 // the FAST kernel instantiations: variant 1 (default), and variant 3 with NF1 / NF2 min-max pairs on the FMA pipe
 // (8 / 4 balances the ALU pipe against the issue slots; 0 / 0 keeps every min/max on the ALU pipe)
 static fast_kernel_t fast_kernel(int ver, int nf) {
@@ -82,6 +82,9 @@ struct orbx_handle {
     size_t qtSmem = 0, fastSmem = 0;
     int lastBatch = 0;
     cudaStream_t sSide = nullptr;  // small batches: blur beside FAST + quadtree
+    cudaStream_t sLvl[ORBX_MAX_LEVELS] = {nullptr};  // small batches: FAST + quadtree of each level on its own stream
+    cudaEvent_t evLvlFork[ORBX_MAX_LEVELS] = {nullptr}, evLvlJoin[ORBX_MAX_LEVELS] = {nullptr};
+    bool levelStreams = true;  // ORBX_LEVEL_STREAMS=0: the single-frame path as one FAST and one quadtree launch
     cudaEvent_t evFork = nullptr, evJoin = nullptr;
     bool pendingOneCopy = false;
     orbx_kp* pendingKps = nullptr;
@@ -414,6 +417,7 @@ extern "C" int orbx_create(const orbx_params* p, int device, orbx_t** out) {
     h->device = device;
     { const char* v = getenv("ORBX_FAST_V2"); if (v && v[0] == '1') h->fastVer = 2; }
     { const char* v = getenv("ORBX_FAST"); if (v && v[0] >= '1' && v[0] <= '3') h->fastVer = v[0] - '0'; }
+    { const char* v = getenv("ORBX_LEVEL_STREAMS"); if (v && v[0] == '0') h->levelStreams = false; }
     { const char* v = getenv("ORBX_DESC_KPW"); if (v && atoi(v) >= 1 && atoi(v) <= 64) h->descKpw = atoi(v); }
     { const char* v = getenv("ORBX_FAST3_NF"); if (v && v[0] >= '0' && v[0] <= '9') h->fastNF = v[0] - '0'; }
     { const char* v = getenv("ORBX_NO_GRAPH"); h->gDisabled = v && v[0] == '1'; }
@@ -452,6 +456,12 @@ extern "C" int orbx_destroy(orbx_t* h) {
         cudaEventDestroy(h->evJoin);
         cudaStreamDestroy(h->sSide);
     }
+    for (int l = 0; l < ORBX_MAX_LEVELS; l++)
+        if (h->sLvl[l]) {
+            cudaEventDestroy(h->evLvlFork[l]);
+            cudaEventDestroy(h->evLvlJoin[l]);
+            cudaStreamDestroy(h->sLvl[l]);
+        }
     cudaStreamDestroy(h->stream);
     delete h;
     return ORBX_OK;
@@ -516,56 +526,113 @@ static bool debug_sync() {
         }                                                                                            \
     } while (0)
 
+// side streams of the single-frame path (created outside any stream capture)
+static int ensure_side_streams(orbx_handle* h, int nl) {
+    if (!h->sSide) {
+        CK(cudaStreamCreateWithFlags(&h->sSide, cudaStreamNonBlocking));
+        CK(cudaEventCreateWithFlags(&h->evFork, cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&h->evJoin, cudaEventDisableTiming));
+    }
+    for (int l = 0; l < nl && l < ORBX_MAX_LEVELS; l++)
+        if (!h->sLvl[l]) {
+            CK(cudaStreamCreateWithFlags(&h->sLvl[l], cudaStreamNonBlocking));
+            CK(cudaEventCreateWithFlags(&h->evLvlFork[l], cudaEventDisableTiming));
+            CK(cudaEventCreateWithFlags(&h->evLvlJoin[l], cudaEventDisableTiming));
+        }
+    return ORBX_OK;
+}
+
 // One chunk of frames [f0, f0 + nb) through the whole kernel chain on stream `cs`. Every arena is indexed by the
 // absolute frame number, so chunks of one batch never touch each other's memory.
-static int launch_chain(orbx_handle* h, cudaStream_t cs, int f0, int nb, bool stamps) {
+static int launch_chain(orbx_handle* h, cudaStream_t cs, int f0, int nb, bool stamps, bool captured = false) {
     const DevPlan& D = h->hp;
     const int nl = D.nlevels;
-    for (int l = 1; l < nl; l++) {
+    const int blurCtas = (D.totalBlurTiles + BLUR_WARPS - 1) / BLUR_WARPS;
+    const int qtT = (nb <= 4 || (long long)nb * nl * 512 <= 148LL * 2048) ? std::max(512, h->qtThreads) : h->qtThreads;
+    auto resize = [&](int l) {
         const LevelGeo& G = D.lv[l];
         dim3 grid((G.w + 255) / 256, (G.h + 3) / 4, nb), block(64, 4);
         dim3 gridFast((G.w + 255) / 256, (G.h + 4 * RESIZE_ROWS - 1) / (4 * RESIZE_ROWS), nb);
         if (G.resizeFast) k_resize_fast<<<gridFast, block, 0, cs>>>(h->hp, l, h->dPyr, h->dTabs, f0);
         else k_resize<<<grid, block, 0, cs>>>(h->hp, l, h->dPyr, h->dTabs, f0);
-        KCHECK(h, "k_resize");
-    }
-    if (stamps) stamp(h, 2);
-    // a few frames do not fill the GPU: the blur (it reads only the pyramid) then runs on a side stream next to FAST and
-    // the quadtree and joins before the descriptors. (For large batches this was measured: no gain, FAST fills every SM.)
+    };
+    // A few frames do not fill the GPU, and the chain pyramid -> FAST -> quadtree is a sequence of latency-bound launches
+    // (single 640x480 frame: 7 x 4.8 + 14 + 37 us). But level l's FAST and quadtree only need level l: on this path every
+    // level gets its own stream, forked as soon as its resize is enqueued, so the critical path is the longest level chain
+    // instead of the sum; the blur of level 0 runs beside them from the start, that of the other levels after the last resize.
+    // (Large batches: every kernel fills the GPU, one launch per stage.)
+    // Only inside the captured single-frame graph: as plain stream launches the 26 launches and 20 event operations cost the
+    // host more than the overlap gives (measured 0.206 ms per call against 0.140); there the blur alone forks.
     const bool fork = nb <= 4 && !stamps && cs == h->stream;
-    if (fork) {
-        if (!h->sSide) {
-            CK(cudaStreamCreateWithFlags(&h->sSide, cudaStreamNonBlocking));
-            CK(cudaEventCreateWithFlags(&h->evFork, cudaEventDisableTiming));
-            CK(cudaEventCreateWithFlags(&h->evJoin, cudaEventDisableTiming));
+    const bool levelPar = fork && captured && h->fastVer != 2 && h->levelStreams;
+    if (levelPar) {
+        { const int rcS = ensure_side_streams(h, nl); if (rcS != ORBX_OK) return rcS; }
+        for (int l = 0; l < nl; l++) {
+            const LevelGeo& G = D.lv[l];
+            if (l > 0) {
+                resize(l);
+                KCHECK(h, "k_resize");
+            }
+            CK(cudaEventRecord(h->evLvlFork[l], cs));
+            CK(cudaStreamWaitEvent(h->sLvl[l], h->evLvlFork[l], 0));
+            if (l == 0) {
+                CK(cudaStreamWaitEvent(h->sSide, h->evLvlFork[0], 0));
+                const int t1 = nl > 1 ? D.lv[1].blurTileBase : D.totalBlurTiles;
+                k_blur<<<dim3((t1 + BLUR_WARPS - 1) / BLUR_WARPS, nb), 32 * BLUR_WARPS, 0, h->sSide>>>(h->dPlan, h->dPyr, h->dBlur, f0, 0, t1);
+                KCHECK(h, "k_blur");
+                CK(cudaEventRecord(h->evJoin, h->sSide));
+            }
+            fast_kernel(h->fastVer, h->fastNF)<<<dim3(G.nStX * G.nStY, nb), FAST_THREADS, h->fastSmem, h->sLvl[l]>>>(
+                h->maps, h->dFastSt, h->dCand, h->dCandCount, h->dErr, f0, G.stBase);
+            KCHECK(h, "k_fast");
+            k_quadtree<<<dim3(nb, 1), qtT, h->qtSmem, h->sLvl[l]>>>(h->hp, h->dCand, h->dCandCount, h->dNodeOf, h->dSel, h->dSelCount,
+                                                                  h->qtC, h->qtC2, h->dErr, f0, l);
+            KCHECK(h, "k_quadtree");
+            CK(cudaEventRecord(h->evLvlJoin[l], h->sLvl[l]));
         }
-        CK(cudaEventRecord(h->evFork, cs));
-        CK(cudaStreamWaitEvent(h->sSide, h->evFork, 0));
-        k_blur<<<dim3((D.totalBlurTiles + BLUR_WARPS - 1) / BLUR_WARPS, nb), 32 * BLUR_WARPS, 0, h->sSide>>>(h->dPlan, h->dPyr, h->dBlur, f0);
-        KCHECK(h, "k_blur");
-        CK(cudaEventRecord(h->evJoin, h->sSide));
-    }
-    if (h->fastVer != 2)
-        fast_kernel(h->fastVer, h->fastNF)<<<dim3(D.totalSt, nb), FAST_THREADS, h->fastSmem, cs>>>(h->maps, h->dFastSt, h->dCand, h->dCandCount, h->dErr, f0);
-    else
-        k_fast2<<<dim3(D.totalSt, nb), FAST_THREADS, h->fastSmem, cs>>>(h->maps, h->dPlan, h->dCand, h->dCandCount, h->dErr, f0);
-    KCHECK(h, "k_fast");
-    if (stamps) stamp(h, 3);
-    // a few frames: one CTA per level is all the parallelism there is, so give it the widest CTA
-    // (measured, single 640x480 / 1241x376 frame: 256 thr 160 / 278 us per call, 512 thr 155 / 220, 1024 thr 160 / 215)
-    // ... and the same holds while every CTA of the launch is resident at once (the kernel then lasts as long as its level-0
-    // CTA): 512 threads as long as nb x levels such CTAs fit on the 148 SMs (config 2, 32-64 frames of 2000 keypoints:
-    // 117 us at 256 threads, one wave, 30 % of the warp slots busy)
-    const int qtT = (nb <= 4 || (long long)nb * nl * 512 <= 148LL * 2048) ? std::max(512, h->qtThreads) : h->qtThreads;
-    k_quadtree<<<dim3(nb, nl), qtT, h->qtSmem, cs>>>(h->hp, h->dCand, h->dCandCount, h->dNodeOf, h->dSel,
-                                                     h->dSelCount, h->qtC, h->qtC2, h->dErr, f0);
-    KCHECK(h, "k_quadtree");
-    if (stamps) stamp(h, 4);
-    if (fork) {
+        if (nl > 1) {
+            const int t1 = D.lv[1].blurTileBase;
+            k_blur<<<dim3((D.totalBlurTiles - t1 + BLUR_WARPS - 1) / BLUR_WARPS, nb), 32 * BLUR_WARPS, 0, cs>>>(h->dPlan, h->dPyr, h->dBlur, f0, t1, D.totalBlurTiles);
+            KCHECK(h, "k_blur");
+        }
         CK(cudaStreamWaitEvent(cs, h->evJoin, 0));
+        for (int l = 0; l < nl; l++) CK(cudaStreamWaitEvent(cs, h->evLvlJoin[l], 0));
     } else {
-        k_blur<<<dim3((D.totalBlurTiles + BLUR_WARPS - 1) / BLUR_WARPS, nb), 32 * BLUR_WARPS, 0, cs>>>(h->dPlan, h->dPyr, h->dBlur, f0);
-        KCHECK(h, "k_blur");
+        for (int l = 1; l < nl; l++) {
+            resize(l);
+            KCHECK(h, "k_resize");
+        }
+        if (stamps) stamp(h, 2);
+        if (fork) {  // the blur (it reads only the pyramid) beside FAST and the quadtree
+            const int rcS = ensure_side_streams(h, 0);
+            if (rcS != ORBX_OK) return rcS;
+            CK(cudaEventRecord(h->evFork, cs));
+            CK(cudaStreamWaitEvent(h->sSide, h->evFork, 0));
+            k_blur<<<dim3(blurCtas, nb), 32 * BLUR_WARPS, 0, h->sSide>>>(h->dPlan, h->dPyr, h->dBlur, f0, 0, D.totalBlurTiles);
+            KCHECK(h, "k_blur");
+            CK(cudaEventRecord(h->evJoin, h->sSide));
+        }
+        if (h->fastVer != 2)
+            fast_kernel(h->fastVer, h->fastNF)<<<dim3(D.totalSt, nb), FAST_THREADS, h->fastSmem, cs>>>(h->maps, h->dFastSt, h->dCand, h->dCandCount, h->dErr, f0, 0);
+        else
+            k_fast2<<<dim3(D.totalSt, nb), FAST_THREADS, h->fastSmem, cs>>>(h->maps, h->dPlan, h->dCand, h->dCandCount, h->dErr, f0);
+        KCHECK(h, "k_fast");
+        if (stamps) stamp(h, 3);
+        // a few frames: one CTA per level is all the parallelism there is, so give it the widest CTA
+        // (measured, single 640x480 / 1241x376 frame: 256 thr 160 / 278 us per call, 512 thr 155 / 220, 1024 thr 160 / 215)
+        // ... and the same holds while every CTA of the launch is resident at once (the kernel then lasts as long as its
+        // level-0 CTA): 512 threads as long as nb x levels such CTAs fit on the 148 SMs (config 2, 32-64 frames of 2000
+        // keypoints: 117 us at 256 threads, one wave, 30 % of the warp slots busy)
+        k_quadtree<<<dim3(nb, nl), qtT, h->qtSmem, cs>>>(h->hp, h->dCand, h->dCandCount, h->dNodeOf, h->dSel, h->dSelCount, h->qtC,
+                                                         h->qtC2, h->dErr, f0, 0);
+        KCHECK(h, "k_quadtree");
+        if (stamps) stamp(h, 4);
+        if (fork) {
+            CK(cudaStreamWaitEvent(cs, h->evJoin, 0));
+        } else {
+            k_blur<<<dim3(blurCtas, nb), 32 * BLUR_WARPS, 0, cs>>>(h->dPlan, h->dPyr, h->dBlur, f0, 0, D.totalBlurTiles);
+            KCHECK(h, "k_blur");
+        }
     }
     if (stamps) stamp(h, 5);
     {
@@ -790,17 +857,13 @@ extern "C" int orbx_extract_batch_submit(orbx_t* h, const uint8_t* imgs, int bat
         bool replayed = false;
         if (oneCopy && !h->gDisabled && !debug_sync()) {
             if (!h->gExec) {  // capture once per plan; any failure falls back to plain stream launches for good
-                if (!h->sSide) {
-                    CK(cudaStreamCreateWithFlags(&h->sSide, cudaStreamNonBlocking));
-                    CK(cudaEventCreateWithFlags(&h->evFork, cudaEventDisableTiming));
-                    CK(cudaEventCreateWithFlags(&h->evJoin, cudaEventDisableTiming));
-                }
+                { const int rcS = ensure_side_streams(h, nl); if (rcS != ORBX_OK) return rcS; }
                 const int64_t l0 = h->launches;
                 cudaGraph_t g = nullptr;
                 bool ok = cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal) == cudaSuccess;
                 if (ok) {
                     ok = cudaMemsetAsync(h->dCandCount, 0, (size_t)nl * sizeof(int), st) == cudaSuccess;
-                    ok = ok && launch_chain(h, st, 0, 1, false) == ORBX_OK;
+                    ok = ok && launch_chain(h, st, 0, 1, false, true) == ORBX_OK;
                     ok = ok && cudaMemcpyAsync(h->hStage, h->dOutBlock, h->outBlockBytes, cudaMemcpyDeviceToHost, st) == cudaSuccess;
                     ok = (cudaStreamEndCapture(st, &g) == cudaSuccess) && ok && g;
                 }

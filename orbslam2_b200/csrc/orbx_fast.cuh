@@ -206,13 +206,13 @@ __host__ __device__ inline size_t fast_region3_bytes(int V, int boxW, int boxH) 
 template <int V, int NF1, int NF2>
 __global__ void __launch_bounds__(FAST_THREADS, 4) k_fast_t(const __grid_constant__ TmapPack maps,
                                                          const FastSt* __restrict__ stTab, u64* __restrict__ cand,
-                                                         int* __restrict__ candCount, int* __restrict__ err, int f0) {
+                                                         int* __restrict__ candCount, int* __restrict__ err, int f0, int st0) {
     extern __shared__ __align__(128) uint8_t fast_smem[];
     const int tid = threadIdx.x;
     const int f = f0 + blockIdx.y;
     // everything a supertile needs arrives as ONE 64-byte record built by the host (build_plan): no level search, no
     // division, no chain of dependent global loads in front of the TMA request
-    const FastSt S = stTab[blockIdx.x];
+    const FastSt S = stTab[st0 + blockIdx.x];  // (st0: the single-frame path launches the levels separately)
     const int level = S.level;
     const int cj0 = S.cj0, ci0 = S.ci0;
     const int xFirst = S.xFirst, xEnd = S.xEnd, yFirst = S.yFirst, yEnd = S.yEnd;

@@ -163,12 +163,12 @@ __device__ __forceinline__ int quadrant_of(const short4 g, int x, int y) {
 
 __global__ void k_quadtree(const __grid_constant__ DevPlan Pc, const u64* __restrict__ cand,
                            const int* __restrict__ candCount, int* __restrict__ nodeOf, uint2* __restrict__ sel,
-                           int* __restrict__ selCount, int C, int C2, int* __restrict__ err, int f0) {
+                           int* __restrict__ selCount, int C, int C2, int* __restrict__ err, int f0, int level0) {
     const DevPlan* P = &Pc;  // the plan rides in the kernel parameters (constant bank): no global loads in the prologue
     extern __shared__ __align__(16) uint8_t qt_smem[];
     uint8_t* smem = qt_smem;
     // (frame-major launch order: the level-0 CTAs of all frames — the longest — are dispatched first)
-    const int level = blockIdx.y, f = f0 + blockIdx.x;
+    const int level = level0 + blockIdx.y, f = f0 + blockIdx.x;
     const LevelGeo& G = P->lv[level];
     const int nl = P->nlevels;
     const int tid = threadIdx.x, T = blockDim.x;
