@@ -154,6 +154,7 @@ struct QtSmem {
 };
 
 #define QT_U 4  // candidates per thread and trip in the passes over the candidate list
+#define QT_RANK_MAX 256  // up to this many keys a sort is a rank-by-counting pass
 
 __device__ __forceinline__ int quadrant_of(const short4 g, int x, int y) {
     const int mx = g.x + ((g.y - g.x + 1) >> 1);  // UL.x + ceil((UR.x-UL.x)/2)
@@ -270,11 +271,23 @@ __global__ void k_quadtree(const __grid_constant__ DevPlan Pc, const u64* __rest
                 S.sortbuf[s] = key;
             }
             __syncthreads();
-            block_bitonic_sort(S.sortbuf, P2);
-            for (int r = tid; r < nE; r += T) {
-                const int s = (int)(S.sortbuf[r] & 0xFFFull);
-                S.orderSlot[r] = s;
-                S.rankOfSlot[s] = r;
+            if (nE <= QT_RANK_MAX) {
+                // few keys: rank by counting (the keys are distinct: the slot is their low bits) — one pass of broadcast
+                // reads and no barrier, against log^2 barrier steps of the bitonic network
+                for (int sl = tid; sl < nE; sl += T) {
+                    const u64 key = S.sortbuf[sl];
+                    int r = 0;
+                    for (int j = 0; j < nE; j++) r += S.sortbuf[j] < key;
+                    S.orderSlot[r] = sl;
+                    S.rankOfSlot[sl] = r;
+                }
+            } else {
+                block_bitonic_sort(S.sortbuf, P2);
+                for (int r = tid; r < nE; r += T) {
+                    const int s = (int)(S.sortbuf[r] & 0xFFFull);
+                    S.orderSlot[r] = s;
+                    S.rankOfSlot[s] = r;
+                }
             }
         } else {
             for (int r = tid; r < nE; r += T) {
@@ -430,13 +443,27 @@ __global__ void k_quadtree(const __grid_constant__ DevPlan Pc, const u64* __rest
         S.sortbuf[i] = key;
     }
     __syncthreads();
-    block_bitonic_sort(S.sortbuf, P2);
     const int nOut = min(size, G.selCap);
     if (size > G.selCap && tid == 0) atomicExch(err, 5);
     uint2* out = sel + (long long)f * P->selStride + G.selOff;
-    for (int i = tid; i < nOut; i += T) {
-        const u64 k = S.sortbuf[i];
-        out[i] = make_uint2((unsigned)(k >> 32), (unsigned)(k & 0xFFFFFFFFull));
+    if (nNodes <= QT_RANK_MAX) {
+        // rank by counting (empty nodes carry the key ~0 and rank past every keypoint; equal keys ordered by index)
+        for (int i = tid; i < nNodes; i += T) {
+            const u64 key = S.sortbuf[i];
+            if (key == ~0ull) continue;
+            int r = 0;
+            for (int j = 0; j < nNodes; j++) {
+                const u64 o = S.sortbuf[j];
+                r += (o < key) || (o == key && j < i);
+            }
+            if (r < nOut) out[r] = make_uint2((unsigned)(key >> 32), (unsigned)(key & 0xFFFFFFFFull));
+        }
+    } else {
+        block_bitonic_sort(S.sortbuf, P2);
+        for (int i = tid; i < nOut; i += T) {
+            const u64 k = S.sortbuf[i];
+            out[i] = make_uint2((unsigned)(k >> 32), (unsigned)(k & 0xFFFFFFFFull));
+        }
     }
     if (tid == 0) selCount[f * nl + level] = nOut;
 }
