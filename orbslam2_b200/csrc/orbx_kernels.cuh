@@ -55,6 +55,32 @@ __device__ int block_excl_scan(int* a, int m, int* ws) {
     return carry;
 }
 
+// Exclusive scan of a 0/1 predicate over i in [0, m): a[i] = number of true predicates before i; returns the total. Every
+// thread of the block must call. Ballot + popc inside a warp, one barrier per blockDim-sized chunk for the warp totals
+// (ws: 2 x 32 ints, alternated between chunks and calls by *phase, so no barrier is needed to recycle them): the quadtree
+// sweeps are bound by their barriers, and three of their four scans are predicate scans (block_excl_scan costs three
+// barriers a chunk plus one for the flags it reads).
+template <typename F>
+__device__ __forceinline__ int block_flag_scan(int* a, int m, int* ws, int* phase, F pred) {
+    const int tid = threadIdx.x, T = blockDim.x, lane = tid & 31, wid = tid >> 5, nw = T >> 5;
+    int carry = 0;
+    for (int base = 0; base < m; base += T) {
+        const int i = base + tid;
+        const bool p = i < m && pred(i);
+        const unsigned bal = __ballot_sync(0xffffffffu, p);
+        int* w = ws + ((*phase) & 1) * 32;
+        (*phase)++;
+        if (lane == 0) w[wid] = __popc(bal);
+        __syncthreads();
+        const int wt = lane < nw ? w[lane] : 0;
+        const int pre = __reduce_add_sync(0xffffffffu, lane < wid ? wt : 0);
+        const int tot = __reduce_add_sync(0xffffffffu, wt);
+        if (i < m) a[i] = carry + pre + __popc(bal & ((1u << lane) - 1u));
+        carry += tot;
+    }
+    return carry;
+}
+
 // Ascending bitonic sort of a[0..P2) (P2 a power of two) in shared memory.
 __device__ void block_bitonic_sort(u64* a, int P2) {
     for (int k = 2; k <= P2; k <<= 1)
@@ -232,16 +258,12 @@ __global__ void k_quadtree(const __grid_constant__ DevPlan Pc, const u64* __rest
 
     bool sortedMode = false, first = true;
     int size = 0, prevSize = 0;
-    {   // alive count
-        for (int i = tid; i < nNodes; i += T) S.flags[i] = S.cntA[i] > 0;
-        __syncthreads();
-        size = block_excl_scan(S.flags, nNodes, S.ws);
-    }
+    __shared__ int qt_fs[64];  // block_flag_scan's warp totals
+    int fsPhase = 0;
+    size = block_flag_scan(S.flags, nNodes, qt_fs, &fsPhase, [&](int i) { return S.cntA[i] > 0; });  // alive count
     for (int sweep = 0; sweep < 64; sweep++) {
-        // expandable nodes -> slots
-        for (int i = tid; i < nNodes; i += T) S.flags[i] = S.cntA[i] > 1;
-        __syncthreads();
-        const int nE = block_excl_scan(S.flags, nNodes, S.ws);
+        // expandable nodes -> slots (a thread reads back only the flags it wrote itself)
+        const int nE = block_flag_scan(S.flags, nNodes, qt_fs, &fsPhase, [&](int i) { return S.cntA[i] > 1; });
         if (!first) {
             if (size >= N || size == prevSize) break;
             if (!sortedMode && size + 3 * nE > N) sortedMode = true;
@@ -337,18 +359,14 @@ __global__ void k_quadtree(const __grid_constant__ DevPlan Pc, const u64* __rest
         __syncthreads();
         const int expandCount = S.ws[36];
         // survivors (alive, not divided in this sweep)
-        for (int i = tid; i < nNodes; i += T) {
+        const int nSurv = block_flag_scan(S.flags, nNodes, qt_fs, &fsPhase, [&](int i) {
             const int s = S.slotOf[i];
-            S.flags[i] = (S.cntA[i] > 0) && (s < 0 || S.rankOfSlot[s] >= expandCount);
-        }
-        __syncthreads();
-        const int nSurv = block_excl_scan(S.flags, nNodes, S.ws);
-        for (int j = tid; j < 4 * nE; j += T) {
+            return (S.cntA[i] > 0) && (s < 0 || S.rankOfSlot[s] >= expandCount);
+        });
+        const int nCh = block_flag_scan(S.childNew, 4 * nE, qt_fs, &fsPhase, [&](int j) {
             const int r = j >> 2, q = j & 3;
-            S.childNew[j] = (r < expandCount) && (S.childCnt[4 * S.orderSlot[r] + q] > 0);
-        }
-        __syncthreads();
-        const int nCh = block_excl_scan(S.childNew, 4 * nE, S.ws);
+            return (r < expandCount) && (S.childCnt[4 * S.orderSlot[r] + q] > 0);
+        });
         if (nSurv + nCh > C) {  // cannot happen (node bound); guard against smem overrun
             if (tid == 0) atomicExch(err, 4);
             break;
