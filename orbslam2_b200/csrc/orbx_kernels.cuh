@@ -81,6 +81,35 @@ __device__ __forceinline__ int block_flag_scan(int* a, int m, int* ws, int* phas
     return carry;
 }
 
+// The same for values in [0, 2^BITS): one ballot per bit.
+template <int BITS, typename F>
+__device__ __forceinline__ int block_small_scan(int* a, int m, int* ws, int* phase, F val) {
+    const int tid = threadIdx.x, T = blockDim.x, lane = tid & 31, wid = tid >> 5, nw = T >> 5;
+    const unsigned lt = (1u << lane) - 1u;
+    int carry = 0;
+    for (int base = 0; base < m; base += T) {
+        const int i = base + tid;
+        const int v = i < m ? val(i) : 0;
+        int inw = 0, wsum = 0;
+#pragma unroll
+        for (int b = 0; b < BITS; b++) {
+            const unsigned bal = __ballot_sync(0xffffffffu, (v >> b) & 1);
+            inw += __popc(bal & lt) << b;
+            wsum += __popc(bal) << b;
+        }
+        int* w = ws + ((*phase) & 1) * 32;
+        (*phase)++;
+        if (lane == 0) w[wid] = wsum;
+        __syncthreads();
+        const int wt = lane < nw ? w[lane] : 0;
+        const int pre = __reduce_add_sync(0xffffffffu, lane < wid ? wt : 0);
+        const int tot = __reduce_add_sync(0xffffffffu, wt);
+        if (i < m) a[i] = carry + pre + inw;
+        carry += tot;
+    }
+    return carry;
+}
+
 // Ascending bitonic sort of a[0..P2) (P2 a power of two) in shared memory.
 __device__ void block_bitonic_sort(u64* a, int P2) {
     for (int k = 2; k <= P2; k <<= 1)
@@ -341,14 +370,14 @@ __global__ void k_quadtree(const __grid_constant__ DevPlan Pc, const u64* __rest
             }
         }
         __syncthreads();
-        // gains in rank order, prefix sum, cut
-        for (int r = tid; r < nE; r += T) {
-            const int* cc = S.childCnt + 4 * S.orderSlot[r];
-            S.gain[r] = (cc[0] > 0) + (cc[1] > 0) + (cc[2] > 0) + (cc[3] > 0) - 1;
-        }
+        // gains in rank order, prefix sum, cut: gain + 1 = the number of non-empty children (0..4) is scanned bit by bit with
+        // ballots (one barrier), and the prefix of the gains is that prefix minus the rank
         if (tid == 0) S.ws[36] = nE;  // expandCount
-        __syncthreads();
-        block_excl_scan(S.gain, nE, S.ws);
+        block_small_scan<3>(S.gain, nE, qt_fs, &fsPhase, [&](int r) {
+            const int* cc = S.childCnt + 4 * S.orderSlot[r];
+            return (cc[0] > 0) + (cc[1] > 0) + (cc[2] > 0) + (cc[3] > 0);
+        });
+        for (int r = tid; r < nE; r += T) S.gain[r] -= r;  // (own elements)
         if (sortedMode) {
             for (int r = tid; r < nE; r += T) {
                 const int* cc = S.childCnt + 4 * S.orderSlot[r];
