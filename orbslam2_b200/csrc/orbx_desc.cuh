@@ -17,7 +17,7 @@
 #pragma once
 #include "orbx_internal.cuh"
 
-#define DESC_KPW 2         // keypoints per warp on the single-frame path (measured 2 / 4 / 8: 0.109 / 0.111 / 0.121 ms per call)
+#define DESC_KPW 1         // keypoints per warp on the single-frame path (measured 1 / 2 / 4 / 8: 0.094 / 0.097 / 0.111 / 0.121 ms per call)
 #define DESC_KPW_BATCH 16  // ... and for large batches (measured 2 / 4 / 8 / 16 / 32: 0.330 / 0.300 / 0.292 / 0.290 / 0.305 ms)
 #define DESC_RAW_BW 48      // TMA box width of the un-blurred patch: 15 bytes of alignment slack + 31, rounded up to 16
 #define DESC_BLR_BW 64      // TMA box width of the blurred patch: 15 + 37, rounded up to 16

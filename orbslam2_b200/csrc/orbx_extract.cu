@@ -242,7 +242,9 @@ static int build_plan(orbx_handle* h, int w, int hgt, int batch) {
         G.pyrOff = pyrOff;
         pyrOff += ((G.frameStride * batch + 255) / 256) * 256;
         G.stCX = std::max(1, std::min(4, (256 - 28) / G.wCell));
-        G.stCY = 2;
+        // two cell rows per supertile for throughput; a plan for a few frames takes one (twice the CTAs, each half as long:
+        // single 752x480 frame 0.107 -> 0.094 ms per call, 640x480 0.097 -> 0.094)
+        G.stCY = batch <= 4 ? 1 : 2;
         G.nStX = (G.nCols + G.stCX - 1) / G.stCX;
         G.nStY = (G.nRows + G.stCY - 1) / G.stCY;
         G.stBase = cellBase;
