@@ -13,7 +13,7 @@
 // IADD3 — issues at 2 warp-inst/clk/SM, so this kernel is bound by its ALU-pipe instruction count; IMAD/DP4A go to the
 // FMA pipe (also 2/clk/SM) and overlap. One thread scores 4 horizontally adjacent pixels (one 32-bit word of the tile).
 //
-// One CTA = a "supertile" of stCX x stCY cells of one level of one frame:
+// One CTA = a "supertile" of stCX x stCY cells of one level of one frame (its geometry arrives as one host-built FastSt record):
 //   TMA 3-D tile load (x start rounded down to 16 bytes — an unaligned innermost coordinate faults on sm_100a)
 //   phase 1  score map  (u8, value = score - (minTh-1), 0 = not a corner at minTh), same coordinates as the tile
 //   phase 2  SWAR non-maximum suppression, strictly greater than the 8 neighbours; a neighbour in another cell
