@@ -27,7 +27,14 @@ typedef void (*fast_kernel_t)(const TmapPack, const FastSt*, u64*, int*, int*, i
 // the FAST kernel instantiations: variant 1 (default), and variant 3 with NF1 / NF2 min-max pairs on the FMA pipe
 // (8 / 4 balances the ALU pipe against the issue slots; 0 / 0 keeps every min/max on the ALU pipe)
 static fast_kernel_t fast_kernel(int ver, int nf) {
-    if (ver != 3) return k_fast_t<1, 0, 0>;
+    if (ver != 3) {  // variant 1: nf = which (NI1, NI2) max-by-IMAD instantiation (ORBX_FAST1_NI, A/B measurement only)
+        switch (nf) {    // measured per 384 frames: (0,0) 1.178 ms, (8,0) 1.124, (8,4) 1.123, (8,8) 1.119
+            case 0: return k_fast_t<1, 0, 0>;
+            case 2: return k_fast_t<1, 8, 0>;
+            case 5: return k_fast_t<1, 8, 4>;
+            default: return k_fast_t<1, 8, 8>;
+        }
+    }
     return nf == 1 ? k_fast_t<3, 0, 0> : k_fast_t<3, 8, 4>;
 }
 
@@ -35,13 +42,14 @@ static fast_kernel_t fast_kernel(int ver, int nf) {
 struct orbx_handle {
     orbx_params prm;
     int device = 0;
-    int fastVer = 1;      // FAST kernel: 1 = k_fast_t<1> (byte tile, every pixel scored in one pass, ALU pipe only);
+    int fastVer = 1;      // FAST kernel: 1 = k_fast_t<1> (byte tile, every pixel scored in one pass; 16 of the 72 min/max per
+                          // pixel pair as IMAD pairs on the FMA pipe, ORBX_FAST1_NI=0 keeps all on the ALU pipe);
                           // 3 = k_fast_t<3> (expanded fp16-lane tile, min/max split over the ALU and FMA pipes: identical
                           // candidates, measured the SAME speed — issue-slot bound instead of ALU bound,
                           // profiles/r02x_fast3_analysis.md);
                           // 2 = k_fast2 (two-threshold pre-test + work lists: identical candidates, measured 1.47x SLOWER,
                           // profiles/r02d_fast2_analysis.md). ORBX_FAST=1|2|3 selects; ORBX_FAST_V2=1 is the old spelling of 2.
-    int fastNF = 0;       // variant 3: which (NF1, NF2) instantiation (ORBX_FAST3_NF, tuning only)
+    int fastNF = 0;       // variant 3: which (NF1, NF2) instantiation (ORBX_FAST3_NF); variant 1: which (NI1, NI2) (ORBX_FAST1_NI)
     int descKpw = 0;      // k_orient_desc keypoints per warp override (ORBX_DESC_KPW, tuning only)
     cudaStream_t stream = nullptr;
     int inSpace = ORBX_MEM_HOST, outSpace = ORBX_MEM_HOST;
@@ -422,6 +430,7 @@ extern "C" int orbx_create(const orbx_params* p, int device, orbx_t** out) {
     { const char* v = getenv("ORBX_LEVEL_STREAMS"); if (v && v[0] == '0') h->levelStreams = false; }
     { const char* v = getenv("ORBX_DESC_KPW"); if (v && atoi(v) >= 1 && atoi(v) <= 64) h->descKpw = atoi(v); }
     { const char* v = getenv("ORBX_FAST3_NF"); if (v && v[0] >= '0' && v[0] <= '9') h->fastNF = v[0] - '0'; }
+    if (h->fastVer == 1) { const char* v = getenv("ORBX_FAST1_NI"); h->fastNF = (v && v[0] >= '0' && v[0] <= '9') ? v[0] - '0' : 1; }
     { const char* v = getenv("ORBX_NO_GRAPH"); h->gDisabled = v && v[0] == '1'; }
     init_tables(h);
     cudaError_t e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);

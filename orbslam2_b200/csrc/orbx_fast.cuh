@@ -11,7 +11,8 @@
 // (VIMNMX.U16x2 / VIMNMX3.U16x2) in the paired-arc formulation of fast_score2: 36 instructions per polarity and pixel
 // pair. Measured on B200 (scripts/pipe_probe.cu): every ALU-pipe instruction — VIMNMX 2- or 3-input, HMNMX2, PRMT, LOP3,
 // IADD3 — issues at 2 warp-inst/clk/SM, so this kernel is bound by its ALU-pipe instruction count; IMAD/DP4A go to the
-// FMA pipe (also 2/clk/SM) and overlap. One thread scores 4 horizontally adjacent pixels (one 32-bit word of the tile).
+// FMA pipe (also 2/clk/SM) and overlap. That is why 16 of the 72 min/max come from max(a, b) = a + b - min(a, b) as two
+// IMADs (fast_score2<NI1, NI2>). One thread scores 4 horizontally adjacent pixels (one 32-bit word of the tile).
 //
 // One CTA = a "supertile" of stCX x stCY cells of one level of one frame (its geometry arrives as one host-built FastSt record):
 //   TMA 3-D tile load (x start rounded down to 16 bytes — an unaligned innermost coordinate faults on sm_100a)
@@ -45,12 +46,27 @@ __device__ __forceinline__ unsigned fast_align(unsigned wm, unsigned w0, unsigne
 // The 16 arcs of 9 pair up around the 8 even-aligned runs of 8: with A8[k] = min(c[k..k+7]) (k even, by doubling),
 //   arc9(k) = min(A8[k], c[k+8])   arc9(k-1) = min(c[k-1], A8[k])   =>   max of the two = min(A8[k], max(c[k+8], c[k-1]))
 // so M = max over the 8 even k of min(A8[k], max(c[k+8], c[k-1])): 36 instructions per polarity instead of 40.
+// NI1 of the 8 first-stage pairs and NI2 of the 8 (c[k+8], c[k-1]) pairs take their max from the identity
+//   max(a, b) = a + b - min(a, b)
+// which holds for the PACKED words modulo 2^32 (the per-lane results fit their 16 bits, so the carries between the lanes
+// cancel): two IMADs on the otherwise idle FMA pipe (multipliers 1 and -1 read from constant memory so ptxas keeps them
+// IMADs) replace one VIMNMX on the ALU pipe that bounds the kernel.
+__constant__ unsigned g_fast_mul[2] = {1u, 0xFFFFFFFFu};
+__device__ __forceinline__ unsigned fast_imad(unsigned a, unsigned b, unsigned c) {
+    unsigned d;
+    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+template <int NI1, int NI2>
 __device__ __forceinline__ unsigned fast_score2(const unsigned (&c)[16], unsigned vh, unsigned negThm1) {
     unsigned a2[8], b2[8], a4[8], b4[8];
+    const unsigned one = g_fast_mul[0], mone = g_fast_mul[1];
 #pragma unroll
     for (int j = 0; j < 8; j++) {
         a2[j] = __vminu2(c[2 * j], c[2 * j + 1]);
-        b2[j] = __vmaxu2(c[2 * j], c[2 * j + 1]);
+        // odd j first so that the FMA-pipe pairs are spread over the tree when NI1 < 8
+        if (((j >> 1) + ((j & 1) ? 0 : 4)) < NI1) b2[j] = fast_imad(a2[j], mone, fast_imad(c[2 * j], one, c[2 * j + 1]));
+        else b2[j] = __vmaxu2(c[2 * j], c[2 * j + 1]);
     }
 #pragma unroll
     for (int j = 0; j < 8; j++) {
@@ -62,7 +78,9 @@ __device__ __forceinline__ unsigned fast_score2(const unsigned (&c)[16], unsigne
     for (int j = 0; j < 8; j++) {
         const int k = 2 * j;
         const unsigned dmax = __vmaxu2(c[(k + 8) & 15], c[(k + 15) & 15]);
-        const unsigned dmin = __vminu2(c[(k + 8) & 15], c[(k + 15) & 15]);
+        unsigned dmin;
+        if (((j >> 1) + ((j & 1) ? 0 : 4)) < NI2) dmin = fast_imad(dmax, mone, fast_imad(c[(k + 8) & 15], one, c[(k + 15) & 15]));
+        else dmin = __vminu2(c[(k + 8) & 15], c[(k + 15) & 15]);
         r[j] = __vimin3_u16x2(a4[j], a4[(j + 2) & 7], dmax);
         q[j] = __vimax3_u16x2(b4[j], b4[(j + 2) & 7], dmin);
     }
@@ -356,8 +374,8 @@ __global__ void __launch_bounds__(FAST_THREADS, 4) k_fast_t(const __grid_constan
             const unsigned m2 = fast_align(a, b, c, -2), m1 = b << 8, p1 = fast_align(a, b, c, 1);
             ce[9] = m2; co[9] = m1; ce[8] = m1; co[8] = b; ce[7] = b; co[7] = p1;
         }
-        const unsigned se = fast_score2(ce, ve, negThm1);
-        const unsigned so = fast_score2(co, vo, negThm1);
+        const unsigned se = fast_score2<NF1, NF2>(ce, ve, negThm1);
+        const unsigned so = fast_score2<NF1, NF2>(co, vo, negThm1);
         const unsigned s = (se | (so << 8)) & H->valid[wi];  // drop bytes outside the detection columns
         sc[(wy + 3) * pitchW + wx] = s;
         if (s) {  // remember the words that hold a corner: phase 2 visits only those (warp-aggregated append)

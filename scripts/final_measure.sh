@@ -10,3 +10,5 @@ python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/${T}_ref.json
 python scripts/bench_latency.py > gpurun_out/${T}_latency.json 2>/dev/null
 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/${T}_launches.csv python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-match > gpurun_out/${T}_ncu_bench.log 2>&1
 cat gpurun_out/${T}_pytest.log; tail -1 gpurun_out/${T}_smoke.log
+# one full-set capture of the dominant kernel (launch 10 = a 192-frame batch launch; 0-7 are the per-level launches of the parity gate), summarised on the build side into profiles/
+ncu --set full --clock-control none --import-source on -k regex:k_fast_t -s 10 -c 1 -f -o gpurun_out/${T}_k_fast python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-match > gpurun_out/${T}_ncu_fast.log 2>&1

@@ -334,6 +334,26 @@ def test_fp16_lane_fast_kernel_gives_identical_candidates(ob, monkeypatch, nf):
     ex1.close(); ex3.close()
 
 
+@pytest.mark.parametrize("ni", ["0", "2", "5"])
+def test_imad_max_fast_kernel_gives_identical_candidates(ob, monkeypatch, ni):
+    """The default k_fast_t<1, 8, 8> takes 16 of the 72 min/max per pixel pair from max(a, b) = a + b - min(a, b) on the
+    packed words (two IMADs on the FMA pipe); ORBX_FAST1_NI=0 / 2 / 5 select the (0, 0) / (8, 0) / (8, 4) instantiations.
+    All must give the same bytes as the default and the oracle."""
+    monkeypatch.setenv("ORBX_FAST1_NI", ni)
+    p = _params(1000)
+    exv = ob.ORBextractor(**p)
+    monkeypatch.delenv("ORBX_FAST1_NI")
+    ex1 = ob.ORBextractor(**p)
+    orc = Oracle(**p)
+    for (w, h), seed, contrast in (((640, 480), 7, 1.0), ((640, 480), 8, 0.2), ((757, 483), 9, 1.0), ((480, 640), 10, 1.0)):
+        img = synth_image(w, h, seed).astype(np.float32)
+        img = np.clip((img - 128.0) * contrast + 128.0, 0, 255).astype(np.uint8)
+        kv, dv = exv(img); k1, d1 = ex1(img)
+        assert k1.tobytes() == kv.tobytes() and np.array_equal(d1, dv)
+        _compare_frame(exv, orc, img, 0, None, kv, dv)
+    ex1.close(); exv.close()
+
+
 def test_single_process_multi_gpu_entry_point(ob):
     """orbx_extract_batch_multi: contiguous blocks of the batch on several handles (every visible GPU, at least two handles
     so that a one-GPU box still exercises the split), results in disjoint slices — bytes equal to one device's call."""
