@@ -4,7 +4,8 @@
 //
 // One warp = 128 px x BLUR_ROWS output rows of one level of one frame; a thread owns 4 adjacent pixels (one aligned
 // 32-bit word) and slides down the rows, so every input row is loaded and filtered horizontally once per strip:
-//   horizontal: byte windows x-3..x and x+1..x+4 cut by PRMT, two DP4A per pixel (a row sum is <= 255*256 = 65280);
+//   horizontal: the three aligned words around the thread's pixels against per-pixel tap vectors (the taps are shifted,
+//               not the bytes): 2 + 3 + 3 + 2 DP4A per 4 pixels, no PRMT (a row sum is <= 255*256 = 65280);
 //   vertical:   row sums of adjacent rows packed in 16-bit pairs, three DP2A + one IMAD per pixel over a 6-pair register
 //               window (loop unrolled by the window period 6, so the window is renamed, not moved);
 //   pipes (B200, scripts/pipe_probe.cu): DP4A/DP2A/IMAD issue on the FMA pipe, PRMT on the ALU pipe, and they overlap;
@@ -40,6 +41,10 @@ __device__ __forceinline__ void blur_strip(const uint8_t* __restrict__ src, uint
     const unsigned K1 = 18u | (34u << 8) | (48u << 16) | (56u << 24);  // taps of x-3 .. x
     const unsigned K2 = 48u | (34u << 8) | (18u << 16);                // taps of x+1 .. x+3 (x+4 weighs 0)
     const unsigned V01 = 18u | (34u << 8), V23 = 48u | (56u << 8), V45 = 48u | (34u << 8);
+    // tap vectors of pixel x0+i against the aligned words (wm: x0-4..x0-1, w0: x0..x0+3, wp: x0+4..x0+7)
+    const unsigned T0m = (18u << 8) | (34u << 16) | (48u << 24), T0z = 56u | (48u << 8) | (34u << 16) | (18u << 24);
+    const unsigned T1m = (18u << 16) | (34u << 24), T1z = 48u | (56u << 8) | (48u << 16) | (34u << 24), T1q = 18u;
+    const unsigned T2m = 18u << 24, T2z = 34u | (48u << 8) | (56u << 16) | (48u << 24), T2q = 34u | (18u << 8);
     const bool redge = EDGE && x0 + 8 > w;
     const bool ledge = EDGE && x0 == 0;
     // Right edge: bytes x0 .. x0+7 with BORDER_REFLECT_101 past w - 1. A reflected byte lies at most 4 left of x0, so every
@@ -80,9 +85,11 @@ __device__ __forceinline__ void blur_strip(const uint8_t* __restrict__ src, uint
             wp = n1;
             if (ledge) wm = __byte_perm(w0, wp, 0x1234);  // x = -4..-1 -> pixels 4, 3, 2, 1
         }
-        H[0] = __dp4a(__byte_perm(w0, wp, 0x4321), K2, __dp4a(__byte_perm(wm, w0, 0x4321), K1, 0u));
-        H[1] = __dp4a(__byte_perm(w0, wp, 0x5432), K2, __dp4a(__byte_perm(wm, w0, 0x5432), K1, 0u));
-        H[2] = __dp4a(__byte_perm(w0, wp, 0x6543), K2, __dp4a(__byte_perm(wm, w0, 0x6543), K1, 0u));
+        // the taps are shifted instead of the bytes: every DP4A reads an ALIGNED word against a constant tap vector
+        // (10 DP4A on the FMA pipe and no PRMT, instead of 8 DP4A + 6 PRMT on the busier ALU pipe)
+        H[0] = __dp4a(w0, T0z, __dp4a(wm, T0m, 0u));
+        H[1] = __dp4a(wp, T1q, __dp4a(w0, T1z, __dp4a(wm, T1m, 0u)));
+        H[2] = __dp4a(wp, T2q, __dp4a(w0, T2z, __dp4a(wm, T2m, 0u)));
         H[3] = __dp4a(wp, K2, __dp4a(w0, K1, 0u));
     };
 

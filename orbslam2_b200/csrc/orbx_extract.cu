@@ -175,7 +175,10 @@ static void linear_table(int src, int dst, bool clampFrac, std::vector<int2>& ou
             if (s >= src - 1) { f = 0; s = src - 1; }
         }
         const int a0 = (short)lrintf((1.f - f) * 2048.f), a1 = (short)lrintf(f * 2048.f);
-        out.push_back(make_int2(s, (a0 & 0xffff) | (a1 << 16)));
+        // x table: the source index; y table: the two source rows already clamped to the image, packed row0 | row1 << 16
+        // (two instructions to unpack in the kernels instead of four min/max per output row)
+        const int idx = clampFrac ? s : (std::min(std::max(s, 0), src - 1) | (std::min(std::max(s + 1, 0), src - 1) << 16));
+        out.push_back(make_int2(idx, (a0 & 0xffff) | (a1 << 16)));
     }
 }
 
@@ -287,8 +290,18 @@ static int build_plan(orbx_handle* h, int w, int hgt, int batch) {
             G.resizeFast = !(D.lv[l - 1].w == 2 * G.w && D.lv[l - 1].h == 2 * G.h);
             for (size_t i = G.xtabOff; i + 3 < tabs.size(); i += 4)
                 if (tabs[i + 3].x - tabs[i].x > 6 || tabs[i + 3].x < tabs[i].x) G.resizeFast = 0;
-            G.ytabOff = (int)tabs.size();
+            // x entries become {PRMT selector | source index << 16}: the selector picks source bytes (rel, rel + 1) of the
+            // 8-byte window that starts at the first source pixel of the entry's group of four (k_resize_fast uses it as is)
+            for (size_t g = G.xtabOff; g < tabs.size(); g += 4) {
+                const int s0 = tabs[g].x;
+                for (size_t i = g; i < g + 4; i++) {
+                    const int rel = std::min(std::max(tabs[i].x - s0, 0), 6);  // <= 6 where k_resize_fast applies
+                    tabs[i].x = (rel * 0x11 + 0x10) | (tabs[i].x << 16);
+                }
+            }
+            G.ytabOff = (int)tabs.size();  // even (the x table is 16-byte aligned and padded to 4 entries)
             linear_table(D.lv[l - 1].h, G.h, false, tabs);
+            while ((tabs.size() - G.ytabOff) & 3) tabs.push_back(tabs.back());  // k_resize_fast reads 4 rows' entries as two uint4
         }
         G.fastUnits = ((G.stCX * G.wCell + 3) / 4 + 2) * (G.stCY * G.hCell);
         if (G.fastUnits >= 16384 || (G.stCX * G.wCell + 3) / 4 + 2 > 64 || G.stCY * G.hCell > 128)

@@ -137,7 +137,8 @@ __device__ __forceinline__ int next_pow2(int v) {
 
 // ------------------------------------------------------------------------------------------------ K1 resize
 // OpenCV 8U INTER_LINEAR fixed point: H = S[s]*a0 + S[s+1]*a1 (scale 2^11); out = ((b0*(H0>>4))>>16 + (b1*(H1>>4))>>16 + 2)>>2.
-// Tables (host-computed with OpenCV's float/double expressions): int2 {source index, a0 | a1<<16}.
+// Tables (host-computed with OpenCV's float/double expressions): int2 {PRMT selector | source index << 16, a0 | a1<<16}; the y table holds
+// {row0 | row1 << 16, b0 | b1 << 16} with both source rows already clamped to the image.
 // One thread = 4 consecutive output pixels (one aligned 32-bit store).
 __global__ void __launch_bounds__(256) k_resize(const __grid_constant__ DevPlan Pc, int level, uint8_t* __restrict__ pyr,
                                                 const int2* __restrict__ tabs, int f0) {
@@ -167,7 +168,7 @@ __global__ void __launch_bounds__(256) k_resize(const __grid_constant__ DevPlan 
     }
     const int2* xt = tabs + D.xtabOff;
     const int2 ty = tabs[D.ytabOff + y];
-    const int sy0 = min(max(ty.x, 0), S.h - 1), sy1 = min(max(ty.x + 1, 0), S.h - 1);
+    const int sy0 = ty.x & 0xffff, sy1 = (int)((unsigned)ty.x >> 16);  // clamped on the host (linear_table)
     const int b0 = (short)(ty.y & 0xffff), b1 = ty.y >> 16;
     const uint8_t* r0 = src + (long long)sy0 * S.pitch;
     const uint8_t* r1 = src + (long long)sy1 * S.pitch;
@@ -176,7 +177,7 @@ __global__ void __launch_bounds__(256) k_resize(const __grid_constant__ DevPlan 
         const int x = x4 + i;
         if (x < D.w) {
             const int2 tx = xt[x];
-            const int sx = tx.x, sx1 = min(sx + 1, S.w - 1);
+            const int sx = tx.x >> 16, sx1 = min(sx + 1, S.w - 1);  // (the low half is k_resize_fast's PRMT selector)
             const int a0 = (short)(tx.y & 0xffff), a1 = tx.y >> 16;
             const int H0 = r0[sx] * a0 + r0[sx1] * a1;
             const int H1 = r1[sx] * a0 + r1[sx1] * a1;
