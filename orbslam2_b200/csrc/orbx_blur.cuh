@@ -2,7 +2,7 @@
 // Reference call site: /root/reference/src/ORBextractor.cc:898-900. OpenCV's 8U path is fixed point: separable taps
 // {18,34,48,56,48,34,18}/256 per axis, exact accumulation, ONE rounding at the end: (sum + 32768) >> 16.
 //
-// One warp = 128 px x BLUR_ROWS output rows of one level of one frame; a thread owns 4 adjacent pixels (one aligned
+// One half-warp = 64 px x BLUR_ROWS output rows of one level of one frame; a thread owns 4 adjacent pixels (one aligned
 // 32-bit word) and slides down the rows, so every input row is loaded and filtered horizontally once per strip:
 //   horizontal: the three aligned words around the thread's pixels against per-pixel tap vectors (the taps are shifted,
 //               not the bytes): 2 + 3 + 3 + 2 DP4A per 4 pixels, no PRMT (a row sum is <= 255*256 = 65280);
@@ -145,18 +145,27 @@ __global__ void __launch_bounds__(32 * BLUR_WARPS, 6) k_blur(const DevPlan* __re
                                                           uint8_t* __restrict__ blur, int f0, int tile0, int tileEnd) {
     const int lane = threadIdx.x & 31;
     const int f = f0 + blockIdx.y;
-    int unit = tile0 + blockIdx.x * BLUR_WARPS + (threadIdx.x >> 5);  // strips [tile0, tileEnd): all levels, or one level's
+    int unit = tile0 + blockIdx.x * BLUR_WARPS + (threadIdx.x >> 5);  // units [tile0, tileEnd): all levels, or one level's
     if (unit >= tileEnd) return;
     int level = 0;
     while (level + 1 < P->nlevels && unit >= P->lv[level + 1].blurTileBase) level++;
     const LevelGeo& G = P->lv[level];
     unit -= G.blurTileBase;
-    const int ty = unit / G.blurTilesX, tx = unit - ty * G.blurTilesX;
-    const int x0 = (tx * 32 + lane) * 4, y0 = ty * BLUR_ROWS;
+    // A unit (one warp) is TWO strips of 64 px x BLUR_ROWS rows, consecutive in the level's row-major strip order: lanes 0-15
+    // take strip 2u, lanes 16-31 strip 2u + 1. (With one 128-px strip per warp 17 % of the lanes of a 640x480 pyramid lay
+    // past the right edge: level widths are 533, 444, 370, ...)
+    const int nX = G.blurTilesX, nS = nX * G.blurTilesY;
     const int w = G.w, h = G.h;
+    const int sA = 2 * unit, sB = sA + 1;
+    const int tyA = sA / nX, txA = sA - tyA * nX;
+    const int tyB = sB / nX, txB = sB - tyB * nX;
+    // warp-uniform: does either strip hold the first column or a lane whose 8-byte window crosses the right border?
+    const bool edge = txA == 0 || txA * 64 + 68 > w || (sB < nS && (txB == 0 || txB * 64 + 68 > w));
+    const bool hi = lane >= 16;
+    if (hi && sB >= nS) return;
+    const int x0 = ((hi ? txB : txA) * 16 + (lane & 15)) * 4, y0 = (hi ? tyB : tyA) * BLUR_ROWS;
     if (x0 >= w) return;
     const long long lvlOff = G.pyrOff + (long long)f * G.frameStride;
-    // warp-uniform: does this warp hold the first column or a lane whose 8-byte window crosses the right border?
-    if (tx == 0 || tx * 128 + 132 > w) blur_strip<true>(pyr + lvlOff, blur + lvlOff, G.pitch, w, h, x0, y0);
+    if (edge) blur_strip<true>(pyr + lvlOff, blur + lvlOff, G.pitch, w, h, x0, y0);
     else blur_strip<false>(pyr + lvlOff, blur + lvlOff, G.pitch, w, h, x0, y0);
 }

@@ -278,10 +278,10 @@ static int build_plan(orbx_handle* h, int w, int hgt, int batch) {
         maxSel = std::max(maxSel, G.selCap);
         G.scale = h->sf[l];
         G.sizeField = (float)(int)(p.patchSize * h->sf[l]);  // src/ORBextractor.cc:831
-        G.blurTilesX = (G.w + 127) / 128;
+        G.blurTilesX = (G.w + 63) / 64;  // strips of 64 px x BLUR_ROWS rows; a k_blur unit (warp) takes two consecutive ones
         G.blurTilesY = (G.h + BLUR_ROWS - 1) / BLUR_ROWS;
         G.blurTileBase = blurBase;
-        blurBase += G.blurTilesX * G.blurTilesY;
+        blurBase += (G.blurTilesX * G.blurTilesY + 1) / 2;
         if (l > 0) {
             if (tabs.size() & 1) tabs.push_back(make_int2(0, 0));  // 16-byte alignment of the x table
             G.xtabOff = (int)tabs.size();
@@ -576,8 +576,8 @@ static int launch_chain(orbx_handle* h, cudaStream_t cs, int f0, int nb, bool st
     auto resize = [&](int l) {
         const LevelGeo& G = D.lv[l];
         dim3 grid((G.w + 255) / 256, (G.h + 3) / 4, nb), block(64, 4);
-        dim3 gridFast((G.w + 255) / 256, (G.h + 4 * RESIZE_ROWS - 1) / (4 * RESIZE_ROWS), nb);
-        if (G.resizeFast) k_resize_fast<<<gridFast, block, 0, cs>>>(h->hp, l, h->dPyr, h->dTabs, f0);
+        dim3 gridFast((G.w + 4 * RESIZE_BX - 1) / (4 * RESIZE_BX), (G.h + RESIZE_BY * RESIZE_ROWS - 1) / (RESIZE_BY * RESIZE_ROWS), nb);
+        if (G.resizeFast) k_resize_fast<<<gridFast, dim3(RESIZE_BX, RESIZE_BY), 0, cs>>>(h->hp, l, h->dPyr, h->dTabs, f0);
         else k_resize<<<grid, block, 0, cs>>>(h->hp, l, h->dPyr, h->dTabs, f0);
     };
     // A few frames do not fill the GPU, and the chain pyramid -> FAST -> quadtree is a sequence of latency-bound launches
