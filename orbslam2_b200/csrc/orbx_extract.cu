@@ -26,6 +26,8 @@ extern "C" const char* orbx_version(void) { return "orbx 0.1 (sm_100a)"; }
 typedef void (*fast_kernel_t)(const TmapPack, const FastSt*, u64*, int*, int*, int, int);
 // the FAST kernel instantiations: variant 1 (default), and variant 3 with NF1 / NF2 min-max pairs on the FMA pipe
 // (8 / 4 balances the ALU pipe against the issue slots; 0 / 0 keeps every min/max on the ALU pipe)
+typedef void (*blur_kernel_t)(const DevPlan*, const uint8_t*, uint8_t*, int, int, int);
+static blur_kernel_t blur_kernel(int rows) { return rows == BLUR_ROWS_SMALL ? k_blur<BLUR_ROWS_SMALL> : k_blur<BLUR_ROWS>; }
 static fast_kernel_t fast_kernel(int ver, int nf) {
     if (ver != 3) {  // variant 1: nf = which (NI1, NI2) max-by-IMAD instantiation (ORBX_FAST1_NI, A/B measurement only)
         switch (nf) {    // measured per 384 frames: (0,0) 1.178 ms, (8,0) 1.124, (8,4) 1.123, (8,8) 1.119
@@ -50,6 +52,8 @@ struct orbx_handle {
                           // 2 = k_fast2 (two-threshold pre-test + work lists: identical candidates, measured 1.47x SLOWER,
                           // profiles/r02d_fast2_analysis.md). ORBX_FAST=1|2|3 selects; ORBX_FAST_V2=1 is the old spelling of 2.
     int fastNF = 0;       // variant 3: which (NF1, NF2) instantiation (ORBX_FAST3_NF); variant 1: which (NI1, NI2) (ORBX_FAST1_NI)
+    int blurRows = BLUR_ROWS;  // k_blur strip height of the current plan (BLUR_ROWS, or BLUR_ROWS_SMALL for a few frames)
+    int resizeBX = RESIZE_BX, resizeBY = RESIZE_BY;  // k_resize_fast CTA shape (ORBX_RESIZE_SHAPE=bx,by: A/B measurement only)
     int descKpw = 0;      // k_orient_desc keypoints per warp override (ORBX_DESC_KPW, tuning only)
     cudaStream_t stream = nullptr;
     int inSpace = ORBX_MEM_HOST, outSpace = ORBX_MEM_HOST;
@@ -226,6 +230,8 @@ static int build_plan(orbx_handle* h, int w, int hgt, int batch) {
     D.iniTh = p.iniThFAST;
     D.minTh = p.minThFAST;
     D.halfPatch = p.halfPatchSize;
+    h->blurRows = batch <= 4 ? BLUR_ROWS_SMALL : BLUR_ROWS;
+    D.blurRows = h->blurRows;
     D.edge = e;
     for (int v = 0; v <= p.halfPatchSize; v++) D.umax[v] = h->umax[v];
 
@@ -279,7 +285,7 @@ static int build_plan(orbx_handle* h, int w, int hgt, int batch) {
         G.scale = h->sf[l];
         G.sizeField = (float)(int)(p.patchSize * h->sf[l]);  // src/ORBextractor.cc:831
         G.blurTilesX = (G.w + 63) / 64;  // strips of 64 px x BLUR_ROWS rows; a k_blur unit (warp) takes two consecutive ones
-        G.blurTilesY = (G.h + BLUR_ROWS - 1) / BLUR_ROWS;
+        G.blurTilesY = (G.h + h->blurRows - 1) / h->blurRows;
         G.blurTileBase = blurBase;
         blurBase += (G.blurTilesX * G.blurTilesY + 1) / 2;
         if (l > 0) {
@@ -444,6 +450,8 @@ extern "C" int orbx_create(const orbx_params* p, int device, orbx_t** out) {
     { const char* v = getenv("ORBX_DESC_KPW"); if (v && atoi(v) >= 1 && atoi(v) <= 64) h->descKpw = atoi(v); }
     { const char* v = getenv("ORBX_FAST3_NF"); if (v && v[0] >= '0' && v[0] <= '9') h->fastNF = v[0] - '0'; }
     if (h->fastVer == 1) { const char* v = getenv("ORBX_FAST1_NI"); h->fastNF = (v && v[0] >= '0' && v[0] <= '9') ? v[0] - '0' : 1; }
+    { const char* v = getenv("ORBX_RESIZE_SHAPE"); int bx = 0, by = 0;
+      if (v && sscanf(v, "%d,%d", &bx, &by) == 2 && bx >= 1 && by >= 1 && bx * by <= 256 && (bx * by) % 32 == 0) { h->resizeBX = bx; h->resizeBY = by; } }
     { const char* v = getenv("ORBX_NO_GRAPH"); h->gDisabled = v && v[0] == '1'; }
     init_tables(h);
     cudaError_t e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
@@ -576,8 +584,9 @@ static int launch_chain(orbx_handle* h, cudaStream_t cs, int f0, int nb, bool st
     auto resize = [&](int l) {
         const LevelGeo& G = D.lv[l];
         dim3 grid((G.w + 255) / 256, (G.h + 3) / 4, nb), block(64, 4);
-        dim3 gridFast((G.w + 4 * RESIZE_BX - 1) / (4 * RESIZE_BX), (G.h + RESIZE_BY * RESIZE_ROWS - 1) / (RESIZE_BY * RESIZE_ROWS), nb);
-        if (G.resizeFast) k_resize_fast<<<gridFast, dim3(RESIZE_BX, RESIZE_BY), 0, cs>>>(h->hp, l, h->dPyr, h->dTabs, f0);
+        const int bx = h->resizeBX, by = h->resizeBY;
+        dim3 gridFast((G.w + 4 * bx - 1) / (4 * bx), (G.h + by * RESIZE_ROWS - 1) / (by * RESIZE_ROWS), nb);
+        if (G.resizeFast) k_resize_fast<<<gridFast, dim3(bx, by), 0, cs>>>(h->hp, l, h->dPyr, h->dTabs, f0);
         else k_resize<<<grid, block, 0, cs>>>(h->hp, l, h->dPyr, h->dTabs, f0);
     };
     // A few frames do not fill the GPU, and the chain pyramid -> FAST -> quadtree is a sequence of latency-bound launches
@@ -602,7 +611,7 @@ static int launch_chain(orbx_handle* h, cudaStream_t cs, int f0, int nb, bool st
             if (l == 0) {
                 CK(cudaStreamWaitEvent(h->sSide, h->evLvlFork[0], 0));
                 const int t1 = nl > 1 ? D.lv[1].blurTileBase : D.totalBlurTiles;
-                k_blur<<<dim3((t1 + BLUR_WARPS - 1) / BLUR_WARPS, nb), 32 * BLUR_WARPS, 0, h->sSide>>>(h->dPlan, h->dPyr, h->dBlur, f0, 0, t1);
+                blur_kernel(h->blurRows)<<<dim3((t1 + BLUR_WARPS - 1) / BLUR_WARPS, nb), 32 * BLUR_WARPS, 0, h->sSide>>>(h->dPlan, h->dPyr, h->dBlur, f0, 0, t1);
                 KCHECK(h, "k_blur");
                 CK(cudaEventRecord(h->evJoin, h->sSide));
             }
@@ -616,7 +625,7 @@ static int launch_chain(orbx_handle* h, cudaStream_t cs, int f0, int nb, bool st
         }
         if (nl > 1) {
             const int t1 = D.lv[1].blurTileBase;
-            k_blur<<<dim3((D.totalBlurTiles - t1 + BLUR_WARPS - 1) / BLUR_WARPS, nb), 32 * BLUR_WARPS, 0, cs>>>(h->dPlan, h->dPyr, h->dBlur, f0, t1, D.totalBlurTiles);
+            blur_kernel(h->blurRows)<<<dim3((D.totalBlurTiles - t1 + BLUR_WARPS - 1) / BLUR_WARPS, nb), 32 * BLUR_WARPS, 0, cs>>>(h->dPlan, h->dPyr, h->dBlur, f0, t1, D.totalBlurTiles);
             KCHECK(h, "k_blur");
         }
         CK(cudaStreamWaitEvent(cs, h->evJoin, 0));
@@ -632,7 +641,7 @@ static int launch_chain(orbx_handle* h, cudaStream_t cs, int f0, int nb, bool st
             if (rcS != ORBX_OK) return rcS;
             CK(cudaEventRecord(h->evFork, cs));
             CK(cudaStreamWaitEvent(h->sSide, h->evFork, 0));
-            k_blur<<<dim3(blurCtas, nb), 32 * BLUR_WARPS, 0, h->sSide>>>(h->dPlan, h->dPyr, h->dBlur, f0, 0, D.totalBlurTiles);
+            blur_kernel(h->blurRows)<<<dim3(blurCtas, nb), 32 * BLUR_WARPS, 0, h->sSide>>>(h->dPlan, h->dPyr, h->dBlur, f0, 0, D.totalBlurTiles);
             KCHECK(h, "k_blur");
             CK(cudaEventRecord(h->evJoin, h->sSide));
         }
@@ -654,7 +663,7 @@ static int launch_chain(orbx_handle* h, cudaStream_t cs, int f0, int nb, bool st
         if (fork) {
             CK(cudaStreamWaitEvent(cs, h->evJoin, 0));
         } else {
-            k_blur<<<dim3(blurCtas, nb), 32 * BLUR_WARPS, 0, cs>>>(h->dPlan, h->dPyr, h->dBlur, f0, 0, D.totalBlurTiles);
+            blur_kernel(h->blurRows)<<<dim3(blurCtas, nb), 32 * BLUR_WARPS, 0, cs>>>(h->dPlan, h->dPyr, h->dBlur, f0, 0, D.totalBlurTiles);
             KCHECK(h, "k_blur");
         }
     }

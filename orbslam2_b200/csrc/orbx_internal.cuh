@@ -57,6 +57,7 @@ struct DevPlan {
     int nlevels, batch;
     int iniTh, minTh, halfPatch, edge;
     int totalSt, totalBlurTiles;
+    int blurRows;   // output rows per k_blur strip (a multiple of 6)
     int selStride;  // selected-keypoint slots per frame (sum of selCap)
     int umax[32];
     LevelGeo lv[ORBX_MAX_LEVELS];

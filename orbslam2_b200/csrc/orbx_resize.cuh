@@ -21,7 +21,7 @@ __device__ __forceinline__ unsigned dp2a_lo_u32(unsigned a16x2, unsigned b8x4, u
 
 #define RESIZE_ROWS 4  // output rows per thread
 #define RESIZE_BX 16   // CTA shape of k_resize_fast (threads)
-#define RESIZE_BY 16
+#define RESIZE_BY 8    // measured per 384 frames: 16x16 0.278 ms, 16x8 0.269, 32x8 0.293, 8x16 0.290, 8x32 0.307, 4x64 0.444
 
 // multipliers of the result packing, read from constant memory so that ptxas keeps the IMADs (FMA pipe) instead of
 // strength-reducing them to LEA / shifts on the ALU pipe
@@ -37,10 +37,10 @@ __global__ void __launch_bounds__(256) k_resize_fast(const __grid_constant__ Dev
     const DevPlan* P = &Pc;  // the plan rides in the kernel parameters (constant bank): no global loads in the prologue
     const LevelGeo& D = P->lv[level];
     const LevelGeo& S = P->lv[level - 1];
-    // CTA = 16 x 16 threads = 64 pixels x 64 rows, so a warp is 64 pixels x 8 rows: level widths are not multiples of anything
+    // CTA = 16 x 8 threads = 64 pixels x 32 rows, so a warp is 64 pixels x 8 rows: level widths are not multiples of anything
     // useful, and with 128-pixel warps (64 x 4 threads) 17 % of the lanes of a 640x480 pyramid lay past the right edge
-    const int x4 = (blockIdx.x * RESIZE_BX + threadIdx.x) * 4;
-    const int yb = (blockIdx.y * RESIZE_BY + threadIdx.y) * RESIZE_ROWS;
+    const int x4 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    const int yb = (blockIdx.y * blockDim.y + threadIdx.y) * RESIZE_ROWS;
     const int f = f0 + blockIdx.z;
     if (x4 >= D.w || yb >= D.h) return;
     const uint8_t* src = pyr + S.pyrOff + (long long)f * S.frameStride;
