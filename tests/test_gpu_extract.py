@@ -334,6 +334,26 @@ def test_fp16_lane_fast_kernel_gives_identical_candidates(ob, monkeypatch, nf):
     ex1.close(); ex3.close()
 
 
+@pytest.mark.parametrize("sf", [1.5, 1.9, 2.0, 2.5, 3.0])
+def test_other_scale_factors(ob, sf):
+    """The pyramid tables are packed for k_resize_fast (PRMT selectors in the x entries, both clamped source rows in the y
+    entries); the generic k_resize reads the same tables. Scale factors other than 1.2 take every branch: 1.5 / 1.9 the fast
+    kernel with other spans, 2.0 OpenCV's exact-2x shortcut, 2.5 / 3.0 the generic kernel (4 output pixels span > 8 source
+    bytes). Everything against the oracle, as for the default configuration."""
+    p = _params(500); p["scaleFactor"] = sf; p["nlevels"] = 3 if sf < 3 else 2  # (a third level at 3.0 is smaller than one FAST cell)
+    ex = ob.ORBextractor(**p); orc = Oracle(**p)
+    stats = [0, 0]
+    for (w, h), seed in (((640, 480), 3), ((757, 483), 4)):
+        img = synth_image(w, h, seed)
+        kps, desc = ex(img)
+        _compare_frame(ex, orc, img, 0, stats, kps, desc)
+    imgs = np.stack([synth_image(640, 480, 20 + s) for s in range(5)])  # batch plan (72-row blur strips)
+    kb, db, nb = ex.extract_batch(imgs)
+    _compare_frame(ex, orc, imgs[4], 4, stats, kb[4, :nb[4]], db[4, :nb[4]])
+    assert stats[0] >= 0.9999 * stats[1]
+    ex.close()
+
+
 @pytest.mark.parametrize("ni", ["0", "2", "5"])
 def test_imad_max_fast_kernel_gives_identical_candidates(ob, monkeypatch, ni):
     """The default k_fast_t<1, 8, 8> takes 16 of the 72 min/max per pixel pair from max(a, b) = a + b - min(a, b) on the
