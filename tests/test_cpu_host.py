@@ -35,6 +35,30 @@ def test_bench_accounting_matches_survey():
     assert peak > 1000 and ("measured" in src or "fallback" in src)
 
 
+def test_reference_arm_prints_one_contract_line():
+    """bench.py --impl reference (the reference's CPU ORBextractor on the host cores) needs no GPU: one JSON line with the
+    metric / unit of the product arm, impl, cpu_baseline and a zero-copy e2e block. The product arm on a box without a GPU
+    must refuse loudly instead of falling back to the CPU."""
+    import json
+    import subprocess
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0"],
+                       capture_output=True, text=True, timeout=600, cwd=ROOT)
+    assert r.returncode == 0, r.stderr[-2000:]
+    lines = [l for l in r.stdout.splitlines() if l.strip()]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    assert d["impl"] == "reference" and d["metric"] == "orb_extract_frames_per_s_640x480_1000kp" and d["unit"] == "frames/s"
+    assert d["value"] > 0 and d["higher_is_better"] is True and d["gpu_launches"] == 0
+    assert d["cpu_baseline"]["kind"] in ("reference", "port") and d["cpu_baseline"]["cores"] >= 1
+    assert d["e2e"] == {"value": d["value"], "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+    assert d["config"]["frames_per_step"] == 8 * d["cpu_baseline"]["cores"]
+    import torch
+    if not torch.cuda.is_available():
+        r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--steps", "1", "--warmup", "0"],
+                           capture_output=True, text=True, timeout=600, cwd=ROOT)
+        assert r.returncode != 0 and "no CPU fallback" in (r.stderr + r.stdout)
+
+
 def test_shard_range_partitions():
     for n in (0, 1, 7, 256, 1001):
         for world in (1, 2, 3, 8):
